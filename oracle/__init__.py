@@ -1,0 +1,92 @@
+"""ctypes loader for the CPU oracle (oracle/oracle.c).  TEST INFRASTRUCTURE ONLY:
+imported by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+legs - never by the go_raytracer_b200 package."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+
+class Stats(ctypes.Structure):
+    _fields_ = [("ms_total", ctypes.c_double), ("ms_kernels", ctypes.c_double), ("ms_h2d", ctypes.c_double),
+                ("ms_d2h", ctypes.c_double), ("rays_primary", ctypes.c_uint64), ("rays_reflect", ctypes.c_uint64),
+                ("rays_refract", ctypes.c_uint64), ("rays_shadow", ctypes.c_uint64), ("shadow_occluded", ctypes.c_uint64),
+                ("leaf_tests", ctypes.c_uint64), ("flops_credited", ctypes.c_double), ("kernel_launches", ctypes.c_uint64),
+                ("n_devices", ctypes.c_uint32), ("n_leaves", ctypes.c_uint32)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+    @property
+    def rays_total(self):
+        return self.rays_primary + self.rays_reflect + self.rays_refract + self.rays_shadow
+
+
+def build(force=False):
+    so = os.path.join(_HERE, "liboracle.so")
+    srcs = [os.path.join(_HERE, f) for f in ("oracle.c", "gomath.h")] + [os.path.join(_HERE, "..", "include", "gmlrt.h")]
+    if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs if os.path.exists(s)):
+        subprocess.check_call(["make", "-C", _HERE, "-B", "liboracle.so"], stdout=subprocess.DEVNULL)
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        L = ctypes.CDLL(build())
+        d, p = ctypes.c_double, ctypes.c_void_p
+        L.oracle_render.restype = ctypes.c_int
+        L.oracle_render.argtypes = [p, ctypes.c_size_t, p, ctypes.c_size_t, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                    ctypes.c_int, ctypes.c_int, ctypes.POINTER(Stats), p]
+        L.oracle_eval_surface.restype = ctypes.c_int
+        L.oracle_eval_surface.argtypes = [p, ctypes.c_size_t, ctypes.c_uint32, ctypes.c_int, d, d, ctypes.POINTER(d)]
+        L.oracle_intersect.restype = ctypes.c_int
+        L.oracle_intersect.argtypes = [ctypes.c_int] + [ctypes.POINTER(d)] * 5 + [ctypes.POINTER(ctypes.c_int)]
+        L.oracle_normal.restype = ctypes.c_int
+        L.oracle_normal.argtypes = [ctypes.c_int, ctypes.POINTER(d), ctypes.POINTER(d), ctypes.c_int, ctypes.POINTER(d),
+                                    ctypes.POINTER(d)]
+        for name in ("tan", "sin", "cos", "acos"):
+            f = getattr(L, "oracle_go_" + name)
+            f.restype, f.argtypes = d, [d]
+        for name in ("pow", "atan2"):
+            f = getattr(L, "oracle_go_" + name)
+            f.restype, f.argtypes = d, [d, d]
+        L.oracle_pcg.restype = None
+        L.oracle_pcg.argtypes = [ctypes.c_uint64, ctypes.c_uint64, ctypes.c_int, ctypes.POINTER(ctypes.c_uint64)]
+        _LIB = L
+    return _LIB
+
+
+class OracleError(RuntimeError):
+    def __init__(self, code):
+        super().__init__(f"oracle error {code}")
+        self.code = code
+
+
+def render(blob, threads=8, crop=None, want_ids=False):
+    """-> (rgba uint8 [H,W,4], Stats[, ids int32 [H,W,4]]).  crop = (x0, y0, x1, y1)."""
+    import struct
+    w, h = struct.unpack_from("<ii", blob, 16)
+    out = np.zeros((h, w, 4), dtype=np.uint8)
+    ids = np.full((h, w, 4), -2, dtype=np.int32) if want_ids else None
+    st = Stats()
+    x0, y0, x1, y1 = crop if crop else (0, 0, w, h)
+    buf = ctypes.create_string_buffer(bytes(blob), len(blob))
+    rc = lib().oracle_render(buf, len(blob), out.ctypes.data, out.nbytes, threads, x0, y0, x1, y1, ctypes.byref(st),
+                             ids.ctypes.data if want_ids else None)
+    if rc:
+        raise OracleError(rc)
+    return (out, st, ids) if want_ids else (out, st)
+
+
+def eval_surface(blob, surface, face, u, v):
+    m = (ctypes.c_double * 10)()
+    buf = ctypes.create_string_buffer(bytes(blob), len(blob))
+    rc = lib().oracle_eval_surface(buf, len(blob), surface, face, u, v, m)
+    if rc:
+        raise OracleError(rc)
+    return tuple(m)
