@@ -455,9 +455,11 @@ class _DeadCode(Exception):
 
 
 def compile_surface(closure, pools):
-    """Returns ("const", material_tuple) or ("code", code_off, code_len, n_regs)."""
+    """Returns ("const", material_tuple) or ("code", code_off, code_len, n_regs, known) where
+    known[k] is material component k when it is a compile-time constant, else NaN."""
     c = _Compiler(pools)
     stack = [A("i", reg=0), A("f", reg=1), A("f", reg=2)]
+    known = (float("nan"),) * 10
     try:
         c.run(closure.code, _LazyEnv(closure.env), stack)
         if not stack:
@@ -476,6 +478,7 @@ def compile_surface(closure, pools):
             comps = list(color.comps) + [ks, zero, zero, zero, kd, ks, n]
         if all(x.is_const for x in comps):
             return ("const", tuple(float(x.const) for x in comps))
+        known = tuple(float(x.const) if x.is_const else float("nan") for x in comps)
         base = c.new_reg(10)
         c.code.extend(c.flush_moves([(base + i, x if x.is_const else x.reg) for i, x in enumerate(comps)]))
         c.emit("RET", 0, base, 0)
@@ -483,7 +486,7 @@ def compile_surface(closure, pools):
         pass  # every path faults; the code already ends in ERR
     off = len(pools.code)
     pools.code.extend(c.code)
-    return ("code", off, len(c.code), c.nreg)
+    return ("code", off, len(c.code), c.nreg, known)
 
 
 def disassemble(code):

@@ -1,0 +1,271 @@
+// gmlrt_api.cu - the C ABI of include/gmlrt.h: context, blob validation, row-band scheduling
+// across devices, NVLink peer gather, copy-back.  This is the "internal/cuda bridge" of the
+// north_star: it owns device memory, streams and the result copy; the host language (Go via cgo,
+// Python via ctypes, ...) only hands over a blob pointer and an RGBA buffer.
+//
+// Multi-GPU: pixels are independent, so the image is cut into row bands that
+// are dealt round-robin to the devices; the scene is replicated; each finished band is copied
+// into device 0's frame with cudaMemcpyPeerAsync (NVLink 5 through NVSwitch).  No collective.
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "../../include/gmlrt.h"
+#include "host_scene.h"
+#include "renderer.h"
+
+using namespace gmlrt;
+
+struct gmlrt_ctx {
+    unsigned flags = 0;
+    std::vector<int> devices;
+    std::vector<std::unique_ptr<IRenderer>> r;
+    HostScene scene;
+    bool have_scene = false, have_frame = false, counting = false;
+    std::string err;
+    uint8_t* pinned = nullptr; size_t pinned_bytes = 0;     // staging for pageable caller buffers
+    cudaEvent_t ev_a = nullptr, ev_b = nullptr;
+    std::vector<cudaEvent_t> ev_done;                        // per device: its bands are in device 0's frame
+    int band_rows = 0;
+};
+
+static thread_local std::string g_last_error = "";
+
+static int fail(gmlrt_ctx* c, int code, const std::string& msg) {
+    if (c) c->err = msg;
+    g_last_error = msg;
+    return code;
+}
+
+#define API_CU(expr)                                                                   \
+    do {                                                                               \
+        cudaError_t e_ = (expr);                                                       \
+        if (e_ != cudaSuccess)                                                         \
+            return fail(c, e_ == cudaErrorMemoryAllocation ? GMLRT_E_OOM : GMLRT_E_CUDA, \
+                        std::string(#expr) + ": " + cudaGetErrorString(e_));           \
+    } while (0)
+
+extern "C" {
+
+int gmlrt_blob_version(void) { return (int)GMLRT_BLOB_VERSION; }
+
+const char* gmlrt_build_info(void) {
+    return "gmlrt sm_100a; CUDA "
+#define STR2(x) #x
+#define STR(x) STR2(x)
+           STR(CUDART_VERSION) "; precision modes: f32 (FMA), f64-parity (-fmad=false); no CPU fallback";
+}
+
+int gmlrt_create(gmlrt_ctx** out, const int* devices, int n, unsigned flags) {
+    if (!out) return fail(nullptr, GMLRT_E_BAD_ARG, "out is null");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count <= 0)
+        return fail(nullptr, GMLRT_E_NO_DEVICE, std::string("no usable CUDA device (there is no CPU fallback): ") +
+                                                     (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0"));
+    std::vector<int> devs;
+    if (!devices || n <= 0) devs.push_back(0);
+    else devs.assign(devices, devices + n);
+    for (int d : devs) if (d < 0 || d >= count) return fail(nullptr, GMLRT_E_BAD_ARG, "device ordinal out of range");
+    std::unique_ptr<gmlrt_ctx> c(new gmlrt_ctx);
+    c->flags = flags;
+    c->devices = devs;
+    for (int d : devs) {
+        IRenderer* r = (flags & GMLRT_PRECISION_MASK) == GMLRT_PRECISION_F64_PARITY ? make_renderer_f64(d) : make_renderer_f32(d);
+        if (!r) return fail(nullptr, GMLRT_E_CUDA, "renderer initialisation failed on device " + std::to_string(d));
+        c->r.emplace_back(r);
+    }
+    // peer access to device 0 for the band gather (ignored when unsupported: cudaMemcpyPeer still works, staged)
+    for (size_t i = 1; i < devs.size(); i++) {
+        int can = 0;
+        if (cudaDeviceCanAccessPeer(&can, devs[i], devs[0]) == cudaSuccess && can) {
+            cudaSetDevice(devs[i]);
+            cudaError_t pe = cudaDeviceEnablePeerAccess(devs[0], 0);
+            if (pe != cudaSuccess) cudaGetLastError();
+        }
+    }
+    cudaSetDevice(devs[0]);
+    if (cudaEventCreate(&c->ev_a) != cudaSuccess || cudaEventCreate(&c->ev_b) != cudaSuccess)
+        return fail(nullptr, GMLRT_E_CUDA, "cudaEventCreate failed");
+    c->ev_done.resize(devs.size(), nullptr);
+    for (size_t i = 0; i < devs.size(); i++) {
+        cudaSetDevice(devs[i]);
+        if (cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming) != cudaSuccess)
+            return fail(nullptr, GMLRT_E_CUDA, "cudaEventCreate failed");
+    }
+    cudaSetDevice(devs[0]);
+    *out = c.release();
+    return GMLRT_OK;
+}
+
+void gmlrt_destroy(gmlrt_ctx* c) {
+    if (!c) return;
+    for (auto& r : c->r) { cudaSetDevice(r->device()); cudaStreamSynchronize(r->stream()); }
+    if (c->pinned) cudaFreeHost(c->pinned);
+    if (c->ev_a) cudaEventDestroy(c->ev_a);
+    if (c->ev_b) cudaEventDestroy(c->ev_b);
+    for (auto ev : c->ev_done) if (ev) cudaEventDestroy(ev);
+    c->r.clear();
+    delete c;
+}
+
+const char* gmlrt_last_error(gmlrt_ctx* c) { return c ? c->err.c_str() : g_last_error.c_str(); }
+
+void* gmlrt_stream(gmlrt_ctx* c) { return c && !c->r.empty() ? (void*)c->r[0]->stream() : nullptr; }
+
+int gmlrt_set_counting(gmlrt_ctx* c, int enabled) {
+    if (!c) return GMLRT_E_BAD_ARG;
+    c->counting = enabled != 0;
+    return GMLRT_OK;
+}
+
+int gmlrt_upload(gmlrt_ctx* c, const void* blob, size_t blob_bytes) {
+    if (!c) return fail(nullptr, GMLRT_E_BAD_ARG, "ctx is null");
+    c->have_scene = false; c->have_frame = false;
+    std::string err;
+    int rc = parse_blob(blob, blob_bytes, c->scene, err);
+    if (rc != GMLRT_OK) return fail(c, rc, err);
+    int min_rows = c->scene.height;
+    for (auto& r : c->r) {
+        rc = r->upload(c->scene, err);
+        if (rc != GMLRT_OK) return fail(c, rc, err);
+        min_rows = std::min(min_rows, r->max_rows_per_tile());
+    }
+    // band height: whole tiles on one device; with several devices at least ~8 bands each (tail balance)
+    const int nd = (int)c->r.size();
+    int rows = min_rows;
+    if (nd > 1) rows = std::max(1, std::min(rows, (c->scene.height + 8 * nd - 1) / (8 * nd)));
+    c->band_rows = rows;
+    c->have_scene = true;
+    return GMLRT_OK;
+}
+
+int gmlrt_trace(gmlrt_ctx* c, gmlrt_stats* stats) {
+    if (!c) return fail(nullptr, GMLRT_E_BAD_ARG, "ctx is null");
+    if (!c->have_scene) return fail(c, GMLRT_E_BAD_ARG, "gmlrt_trace before a successful gmlrt_upload");
+    std::string err;
+    const int nd = (int)c->r.size();
+    const int H = c->scene.height, W = c->scene.width;
+    IRenderer* r0 = c->r[0].get();
+    API_CU(cudaSetDevice(r0->device()));
+    for (auto& r : c->r) r->reset_totals();
+    API_CU(cudaEventRecord(c->ev_a, r0->stream()));
+    // the other devices start after ev_a so that ev_a..ev_b on device 0 brackets the whole job
+    for (int i = 1; i < nd; i++) { API_CU(cudaSetDevice(c->r[i]->device())); API_CU(cudaStreamWaitEvent(c->r[i]->stream(), c->ev_a, 0)); }
+    int band = 0;
+    for (int y0 = 0; y0 < H; y0 += c->band_rows, band++) {
+        const int y1 = std::min(H, y0 + c->band_rows);
+        const int di = band % nd;
+        IRenderer* r = c->r[di].get();
+        int rc = r->trace_rows(y0, y1, c->counting, err);
+        if (rc != GMLRT_OK) return fail(c, rc, err);
+        if (di != 0) {   // gather: finished band -> device 0's frame, on the producing device's stream
+            API_CU(cudaSetDevice(r->device()));
+            const size_t off = (size_t)y0 * W * 4, bytes = (size_t)(y1 - y0) * W * 4;
+            API_CU(cudaMemcpyPeerAsync(r0->frame() + off, r0->device(), r->frame() + off, r->device(), bytes, r->stream()));
+            if (c->counting && r->primary_ids() && r0->primary_ids())
+                API_CU(cudaMemcpyPeerAsync(r0->primary_ids() + off, r0->device(), r->primary_ids() + off, r->device(), bytes * 4, r->stream()));
+        }
+    }
+    for (int i = 1; i < nd; i++) {
+        API_CU(cudaSetDevice(c->r[i]->device()));
+        API_CU(cudaEventRecord(c->ev_done[i], c->r[i]->stream()));
+        API_CU(cudaSetDevice(r0->device()));
+        API_CU(cudaStreamWaitEvent(r0->stream(), c->ev_done[i], 0));
+    }
+    API_CU(cudaSetDevice(r0->device()));
+    API_CU(cudaEventRecord(c->ev_b, r0->stream()));
+    API_CU(cudaStreamSynchronize(r0->stream()));
+    for (int i = 1; i < nd; i++) { API_CU(cudaSetDevice(c->r[i]->device())); API_CU(cudaStreamSynchronize(c->r[i]->stream())); }
+    API_CU(cudaSetDevice(r0->device()));
+    c->have_frame = true;
+    float ms = 0;
+    API_CU(cudaEventElapsedTime(&ms, c->ev_a, c->ev_b));
+    TraceTotals sum;
+    for (auto& r : c->r) {
+        TraceTotals t;
+        int rc = r->fetch_totals(t, err);
+        if (rc != GMLRT_OK) return fail(c, rc, err);
+        sum.rays_primary += t.rays_primary; sum.rays_reflect += t.rays_reflect; sum.rays_refract += t.rays_refract;
+        sum.rays_shadow += t.rays_shadow; sum.shadow_occluded += t.shadow_occluded; sum.launches += t.launches;
+        for (int k = 0; k < K_COUNT; k++) sum.shadow_tests[k] += t.shadow_tests[k];
+        sum.error |= t.error;
+    }
+    if (stats) {
+        std::memset(stats, 0, sizeof *stats);
+        stats->ms_total = ms; stats->ms_kernels = ms;
+        stats->rays_primary = sum.rays_primary; stats->rays_reflect = sum.rays_reflect; stats->rays_refract = sum.rays_refract;
+        stats->rays_shadow = sum.rays_shadow; stats->shadow_occluded = sum.shadow_occluded;
+        stats->kernel_launches = sum.launches; stats->n_devices = (uint32_t)nd; stats->n_leaves = (uint32_t)c->scene.n_objects;
+        // credited work: a closest-hit query tests every leaf; a shadow query is credited
+        // with the tests its lane ran up to its own first occluder (counting mode only)
+        double all = 0; unsigned long long nleaf = 0;
+        for (int i = 0; i < c->scene.n_plain; i++) { all += kFlopsByKind[c->scene.leaves[i].kind]; nleaf++; }
+        const unsigned long long closest = sum.rays_primary + sum.rays_reflect + sum.rays_refract;
+        stats->leaf_tests = closest * nleaf;
+        stats->flops_credited = (double)closest * all;
+        for (int k = 0; k < K_COUNT; k++) {
+            stats->leaf_tests += sum.shadow_tests[k];
+            stats->flops_credited += (double)sum.shadow_tests[k] * kFlopsByKind[k];
+        }
+    }
+    if (sum.error) return fail(c, GMLRT_E_SURFACE, "a surface function faulted at render time (the reference panics here, raytracer.go:499-501)");
+    return GMLRT_OK;
+}
+
+int gmlrt_download(gmlrt_ctx* c, uint8_t* rgba, size_t rgba_bytes) {
+    if (!c) return fail(nullptr, GMLRT_E_BAD_ARG, "ctx is null");
+    if (!c->have_frame) return fail(c, GMLRT_E_BAD_ARG, "gmlrt_download before a successful gmlrt_trace");
+    const size_t need = (size_t)c->scene.width * c->scene.height * 4;
+    if (!rgba || rgba_bytes != need) return fail(c, GMLRT_E_BAD_ARG, "rgba buffer must be exactly 4*width*height bytes");
+    IRenderer* r0 = c->r[0].get();
+    API_CU(cudaSetDevice(r0->device()));
+    API_CU(cudaMemcpyAsync(rgba, r0->frame(), need, cudaMemcpyDeviceToHost, r0->stream()));
+    API_CU(cudaStreamSynchronize(r0->stream()));
+    return GMLRT_OK;
+}
+
+int gmlrt_primary_hits(gmlrt_ctx* c, int32_t* ids, size_t n_ids) {
+    if (!c) return fail(nullptr, GMLRT_E_BAD_ARG, "ctx is null");
+    if (!c->have_frame || !c->counting || !c->r[0]->primary_ids())
+        return fail(c, GMLRT_E_BAD_ARG, "primary hit ids need gmlrt_set_counting(ctx, 1) before gmlrt_trace");
+    const size_t need = (size_t)c->scene.width * c->scene.height * 4;
+    if (!ids || n_ids != need) return fail(c, GMLRT_E_BAD_ARG, "ids must hold 4*width*height entries");
+    IRenderer* r0 = c->r[0].get();
+    API_CU(cudaSetDevice(r0->device()));
+    API_CU(cudaMemcpyAsync(ids, r0->primary_ids(), need * sizeof(int32_t), cudaMemcpyDeviceToHost, r0->stream()));
+    API_CU(cudaStreamSynchronize(r0->stream()));
+    return GMLRT_OK;
+}
+
+int gmlrt_render(gmlrt_ctx* c, const void* blob, size_t blob_bytes, uint8_t* rgba, size_t rgba_bytes, gmlrt_stats* stats) {
+    if (!c) return fail(nullptr, GMLRT_E_BAD_ARG, "ctx is null");
+    using clk = std::chrono::steady_clock;
+    auto t0 = clk::now();
+    int rc = gmlrt_upload(c, blob, blob_bytes);
+    if (rc != GMLRT_OK) return rc;
+    if (!rgba || rgba_bytes != (size_t)c->scene.width * c->scene.height * 4)
+        return fail(c, GMLRT_E_BAD_ARG, "rgba buffer must be exactly 4*width*height bytes");
+    auto t1 = clk::now();
+    gmlrt_stats st;
+    rc = gmlrt_trace(c, &st);
+    if (rc != GMLRT_OK) return rc;
+    auto t2 = clk::now();
+    rc = gmlrt_download(c, rgba, rgba_bytes);
+    if (rc != GMLRT_OK) return rc;
+    auto t3 = clk::now();
+    if (stats) {
+        *stats = st;
+        auto ms = [](clk::time_point a, clk::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+        stats->ms_h2d = ms(t0, t1); stats->ms_d2h = ms(t2, t3); stats->ms_total = ms(t0, t3);
+    }
+    return GMLRT_OK;
+}
+
+}  // extern "C"

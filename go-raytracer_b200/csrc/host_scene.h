@@ -1,0 +1,186 @@
+// host_scene.h - blob validation + the one-off scene conversion, on the host, in double.
+//
+// Replaces convertGMLSceneObjects (/root/reference/raytracer.go:756-830): breadth-first
+// flattening of Union nodes into the scan-order object list (top-of-stack operand first),
+// per-leaf matrices, plane / cube-face world normals (createPlane :764-774) and the camera
+// set-up of Render (:592-603).  The reference repeats this 8 times (once per goroutine,
+// :738-751); here it runs once per gmlrt_upload.
+#pragma once
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/gmlrt.h"
+#include "gomath.cuh"
+
+namespace gmlrt {
+
+// device-order kind slots (scan kernels walk the leaves kind by kind)
+enum Kind { K_SPHERE = 0, K_CUBE = 1, K_CYLINDER = 2, K_CONE = 3, K_PLANE = 4, K_COUNT = 5 };
+static const double kFlopsByKind[K_COUNT] = {56, 81, 74, 70, 47};
+
+struct HostLeaf {
+    int kind;                 // Kind
+    uint32_t surface;
+    double o2w[12], w2o[12];
+    double face_normal[6][3]; // plane: [0]; cube: per face
+    int scan_index;           // position in the reference's []SceneObject (-1 inside a CSG object)
+    int csg_object;           // index of the owning CSG object, -1 for plain objects
+    uint32_t node;            // blob node index
+};
+
+// One CSG object = a subtree rooted at an intersect/difference node, in postfix order.
+struct HostCsgOp { int op; int leaf; };   // op: -1 push leaf `leaf` (index into leaves), else GMLRT_NODE_* operator
+struct HostCsgObject { int scan_index; std::vector<HostCsgOp> postfix; int max_stack; };
+
+struct HostScene {
+    gmlrt_blob_header h;
+    int width = 0, height = 0, depth = 0;
+    double vw = 0, vh = 0;
+    std::vector<HostLeaf> leaves;          // plain objects first (scan order), then CSG members
+    int n_plain = 0;                       // leaves[0..n_plain) are plain scan-order objects
+    int n_objects = 0;                     // scan-order objects = plain leaves + CSG objects
+    std::vector<int> object_of_scan;       // scan index -> leaf index (>=0) or -(csg index)-1
+    std::vector<HostCsgObject> csg;
+    std::vector<gmlrt_light> lights;
+    std::vector<gmlrt_surface> surfaces;
+    std::vector<double> fpool;
+    std::vector<int32_t> itab;
+    std::vector<uint32_t> code;
+    bool may_branch = false;               // some material can spawn reflection AND refraction
+    bool any_reflect = false, any_refract = false;
+};
+
+inline bool is_leaf_kind(uint32_t k) { return k >= 16 && k <= 20; }
+
+inline void mul_dir_t(const double* m, const double* v, double* out) {   // (M^T) v, NormalMat.MulDir
+    out[0] = m[0] * v[0] + m[4] * v[1] + m[8] * v[2];
+    out[1] = m[1] * v[0] + m[5] * v[1] + m[9] * v[2];
+    out[2] = m[2] * v[0] + m[6] * v[1] + m[10] * v[2];
+}
+inline void normalize3(double* v) {
+    double m = std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+    v[0] /= m; v[1] /= m; v[2] /= m;
+}
+
+static const double kCubeNormals[6][3] = {{0, 0, -1}, {0, 0, 1}, {-1, 0, 0}, {1, 0, 0}, {0, 1, 0}, {0, -1, 0}};
+
+inline void init_leaf(HostLeaf& L, const gmlrt_node& n, uint32_t node_index) {
+    static const int map[5] = {K_SPHERE, K_CUBE, K_CYLINDER, K_CONE, K_PLANE};
+    L.kind = map[n.kind - 16];
+    L.surface = n.surface;
+    L.node = node_index;
+    std::memcpy(L.o2w, n.o2w, sizeof L.o2w);
+    std::memcpy(L.w2o, n.w2o, sizeof L.w2o);
+    std::memset(L.face_normal, 0, sizeof L.face_normal);
+    L.scan_index = -1; L.csg_object = -1;
+    if (L.kind == K_PLANE) {
+        const double up[3] = {0, 1, 0};
+        mul_dir_t(L.w2o, up, L.face_normal[0]);
+        normalize3(L.face_normal[0]);
+    } else if (L.kind == K_CUBE) {
+        for (int f = 0; f < 6; f++) { mul_dir_t(L.w2o, kCubeNormals[f], L.face_normal[f]); normalize3(L.face_normal[f]); }
+    }
+}
+
+// returns GMLRT_OK or an error code; `err` gets the text
+inline int parse_blob(const void* blob, size_t nbytes, HostScene& S, std::string& err) {
+    if (!blob || nbytes < sizeof(gmlrt_blob_header)) { err = "blob too small"; return GMLRT_E_BAD_BLOB; }
+    std::memcpy(&S.h, blob, sizeof S.h);
+    const gmlrt_blob_header& h = S.h;
+    if (h.magic != GMLRT_BLOB_MAGIC) { err = "bad magic"; return GMLRT_E_BAD_BLOB; }
+    if (h.version != GMLRT_BLOB_VERSION) { err = "unsupported blob version"; return GMLRT_E_BAD_BLOB; }
+    if (h.total_bytes != nbytes) { err = "total_bytes does not match the buffer size"; return GMLRT_E_BAD_BLOB; }
+    auto fits = [&](uint64_t off, uint64_t n, uint64_t sz) { return off <= nbytes && n * sz <= nbytes - off && off % 8 == 0; };
+    if (!fits(h.off_nodes, h.n_nodes, sizeof(gmlrt_node)) || !fits(h.off_lights, h.n_lights, sizeof(gmlrt_light)) ||
+        !fits(h.off_surfaces, h.n_surfaces, sizeof(gmlrt_surface)) || !fits(h.off_fpool, h.n_fpool, 8) ||
+        !fits(h.off_itab, h.n_itab, 4) || !fits(h.off_code, h.n_code, 4)) { err = "section out of bounds"; return GMLRT_E_BAD_BLOB; }
+    if (h.n_nodes == 0 || h.root >= h.n_nodes) { err = "bad root"; return GMLRT_E_BAD_BLOB; }
+    if (h.width <= 0 || h.height <= 0 || (uint64_t)h.width * (uint64_t)h.height > (1ull << 28)) { err = "bad image size"; return GMLRT_E_BAD_BLOB; }
+    const uint8_t* base = (const uint8_t*)blob;
+    std::vector<gmlrt_node> nodes(h.n_nodes);
+    std::memcpy(nodes.data(), base + h.off_nodes, sizeof(gmlrt_node) * h.n_nodes);
+    S.lights.resize(h.n_lights);   if (h.n_lights) std::memcpy(S.lights.data(), base + h.off_lights, sizeof(gmlrt_light) * h.n_lights);
+    S.surfaces.resize(h.n_surfaces); if (h.n_surfaces) std::memcpy(S.surfaces.data(), base + h.off_surfaces, sizeof(gmlrt_surface) * h.n_surfaces);
+    S.fpool.resize(h.n_fpool);     if (h.n_fpool) std::memcpy(S.fpool.data(), base + h.off_fpool, 8 * (size_t)h.n_fpool);
+    S.itab.resize(h.n_itab);       if (h.n_itab) std::memcpy(S.itab.data(), base + h.off_itab, 4 * (size_t)h.n_itab);
+    S.code.resize(h.n_code);       if (h.n_code) std::memcpy(S.code.data(), base + h.off_code, 4 * (size_t)h.n_code);
+    for (auto& l : S.lights) if (l.kind > GMLRT_LIGHT_SPOT) { err = "unknown light kind"; return GMLRT_E_UNSUPPORTED; }
+    for (auto& sf : S.surfaces) {
+        if (sf.kind > GMLRT_SURFACE_CODE) { err = "unknown surface kind"; return GMLRT_E_BAD_BLOB; }
+        if (sf.kind == GMLRT_SURFACE_CODE && ((uint64_t)sf.code_off + sf.code_len > h.n_code || sf.n_regs > GMLRT_VM_MAX_REGS)) {
+            err = "surface code out of bounds"; return GMLRT_E_BAD_BLOB;
+        }
+        // a component is "possibly > 0" unless it is a known constant <= 0
+        bool refl = !(sf.material[3] <= 0.0), transp = !(sf.material[5] <= 0.0);
+        S.any_reflect |= refl; S.any_refract |= transp;
+        S.may_branch |= (refl && transp);
+    }
+
+    S.width = h.width; S.height = h.height;
+    S.depth = h.depth > 0 ? h.depth : 3;                                  // raytracer.go:592-595
+    double fov = h.fov > 0.0 ? h.fov : 90.0;                              // raytracer.go:597-600
+    double fov_rad = fov * GM_PI / 180.0;
+    S.vw = 2.0 / gomath::go_tan(fov_rad / 2.0);                           // raytracer.go:601-602 (Go's Tan)
+    S.vh = S.vw * ((double)S.height / (double)S.width);
+
+    // breadth-first flattening of unions (raytracer.go:776-828)
+    std::vector<uint32_t> queue{h.root};
+    std::vector<HostLeaf> csg_members;
+    S.leaves.clear(); S.csg.clear(); S.object_of_scan.clear();
+    for (size_t qh = 0; qh < queue.size(); qh++) {
+        if (queue.size() > (size_t)h.n_nodes) { err = "scene graph is not a tree"; return GMLRT_E_BAD_BLOB; }
+        uint32_t ni = queue[qh];
+        const gmlrt_node& n = nodes[ni];
+        if (n.kind == GMLRT_NODE_UNION) {
+            if (n.a >= h.n_nodes || n.b >= h.n_nodes) { err = "child index out of range"; return GMLRT_E_BAD_BLOB; }
+            queue.push_back(n.a); queue.push_back(n.b);
+        } else if (is_leaf_kind(n.kind)) {
+            if (n.surface >= h.n_surfaces) { err = "surface index out of range"; return GMLRT_E_BAD_BLOB; }
+            HostLeaf L; init_leaf(L, n, ni);
+            L.scan_index = (int)S.object_of_scan.size();
+            S.object_of_scan.push_back((int)S.leaves.size());
+            S.leaves.push_back(L);
+        } else if (n.kind == GMLRT_NODE_INTERSECT || n.kind == GMLRT_NODE_DIFFERENCE) {
+            // EXTENSION: the reference rejects these (raytracer.go:825-826).  Postfix walk, no recursion.
+            HostCsgObject obj; obj.scan_index = (int)S.object_of_scan.size(); obj.max_stack = 0;
+            struct Frame { uint32_t node; int state; };
+            std::vector<Frame> st{{ni, 0}};
+            int depth = 0;
+            size_t visited = 0;
+            while (!st.empty()) {
+                Frame& f = st.back();
+                if (++visited > 4 * (size_t)h.n_nodes + 8) { err = "scene graph is not a tree"; return GMLRT_E_BAD_BLOB; }
+                const gmlrt_node& m = nodes[f.node];
+                if (is_leaf_kind(m.kind)) {
+                    if (m.surface >= h.n_surfaces) { err = "surface index out of range"; return GMLRT_E_BAD_BLOB; }
+                    HostLeaf L; init_leaf(L, m, f.node);
+                    L.csg_object = (int)S.csg.size();
+                    obj.postfix.push_back({-1, (int)csg_members.size()});
+                    csg_members.push_back(L);
+                    if (++depth > obj.max_stack) obj.max_stack = depth;
+                    st.pop_back();
+                } else if (m.kind <= GMLRT_NODE_DIFFERENCE) {
+                    if (m.a >= h.n_nodes || m.b >= h.n_nodes) { err = "child index out of range"; return GMLRT_E_BAD_BLOB; }
+                    if (f.state == 0) { f.state = 1; st.push_back({m.a, 0}); }
+                    else if (f.state == 1) { f.state = 2; st.push_back({m.b, 0}); }
+                    else { obj.postfix.push_back({(int)m.kind, -1}); depth--; st.pop_back(); }
+                } else { err = "unknown scene object type"; return GMLRT_E_UNSUPPORTED; }
+            }
+            S.object_of_scan.push_back(-(int)S.csg.size() - 1);
+            S.csg.push_back(std::move(obj));
+        } else {
+            err = "unknown scene object type";                           // raytracer.go:825-826
+            return GMLRT_E_UNSUPPORTED;
+        }
+    }
+    S.n_plain = (int)S.leaves.size();
+    S.n_objects = (int)S.object_of_scan.size();
+    for (auto& obj : S.csg) for (auto& op : obj.postfix) if (op.op < 0) op.leaf += S.n_plain;
+    S.leaves.insert(S.leaves.end(), csg_members.begin(), csg_members.end());
+    return GMLRT_OK;
+}
+
+}  // namespace gmlrt

@@ -1,0 +1,1195 @@
+// render_impl.cuh - the wavefront ray tracer, templated on the arithmetic type.
+//
+// Replaces Render / traceRay / closestHit / computeLighting / inShadow and the per-primitive
+// Intersect / ComputeSurfaceProps of /root/reference/raytracer.go (line references at each
+// function).  The reference is a recursive tracer run by 8 goroutines; this is a wavefront:
+//
+//   gen        camera rays for a band of rows, PCG jitter by jump-ahead        (Render :632-652)
+//   closest    every ray x every leaf, leaves staged in shared memory by TMA   (closestHit :469-483)
+//   shade      surface function (bytecode), material, shadow + child rays      (traceRay :498-556)
+//   shadow     any-hit scan with early exit                                    (inShadow :411-429)
+//   resolve    lighting + clamp per recursion level, deepest level first       (:372-401, :506-561)
+//   pixels     mean of 4 samples -> RGBA8                                      (:656, vec.go:104-107)
+//
+// Rays of one recursion level live in SoA queues; children are appended with warp-aggregated
+// (__ballot_sync/__popc) atomics, so the scan kernels always run on dense queues.  Colour is
+// clamped at every level in the reference, hence the per-level records and the
+// back-to-front resolve instead of a throughput-weighted accumulation.
+//
+// This header is compiled twice: render_f64.cu (R = double, -fmad=false: reference operation
+// order, bit-parity mode) and render_f32.cu (R = float, FMA contraction: throughput mode).
+#pragma once
+#include <cstdint>
+#include <cstdio>
+#include <algorithm>
+#include <cstdlib>
+#include <string>
+#include <type_traits>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "gomath.cuh"
+#include "host_scene.h"
+#include "renderer.h"
+
+namespace gmlrt {
+
+using gomath::gm;
+
+#define GMLRT_MAX_DEPTH 64
+#define NREC 16   // per-node shading record: P(3) N(3) colour(3) refl transp kr kd ks n |d|
+
+template <typename R> struct DevLight { int kind; R pos[3], color[3], axis[3], cos_cutoff, exponent; };
+template <typename R> struct DevSurface { int kind, code_off, code_len, n_regs; R material[10]; };
+
+template <typename R> struct DevScene {
+    int n_leaves;                  // plain objects, device order (sorted by kind)
+    int kind_begin[K_COUNT + 1];
+    const R* w2o;                  // [n][12] rows 0..2 of WorldToObject           (hot: staged in smem)
+    const int* scan_of;            // device index -> scan-order index (tie-breaks, ids)
+    const R* o2w;                  // [n][12]
+    const R* fnormal;              // [n][18] world normals of plane / cube faces
+    const int* surface;            // [n]
+    const int* kind;               // [n]
+    int n_lights;
+    const DevLight<R>* lights;
+    const DevSurface<R>* surfaces;
+    const R* fpool; const int* itab; const uint32_t* code;
+    int n_fpool, n_itab;
+    int W, H, depth;
+    double vw, vh;
+    R ambient[3], bg0[3], bg1[3];
+};
+
+// One recursion level of the wavefront (SoA, `cap` entries each).
+template <typename R> struct Level {
+    R* ray;       // [6][cap] origin xyz, direction xyz
+    int* parent;  // [cap] index in the previous level | (1<<31 for the refraction slot)
+    int* hit;     // [cap] device leaf index | face << 28, or -1
+    R* t;         // [cap]
+    R* rec;       // [NREC][cap]
+    R* child;     // [6][cap] colour returned by the reflection / refraction child
+    int cap;
+};
+
+template <typename R> struct ShadowQueue {
+    R* q;         // [8][cap] origin xyz, direction xyz, distance to light, |incoming direction|
+    int* skip;    // [cap] device leaf index of the shaded object (inShadow skips it)
+    int* target;  // [cap] node * n_lights + light
+    int cap;
+};
+
+struct Counters {                  // device-resident, zeroed per trace
+    int count[GMLRT_MAX_DEPTH + 1];     // rays per level
+    int shadow_count;
+    int error;
+    unsigned long long rays_reflect, rays_refract, rays_shadow, shadow_occluded;
+    unsigned long long shadow_tests[K_COUNT];
+};
+
+template <typename R> struct Ray { R ox, oy, oz, dx, dy, dz; };
+
+// ------------------------------------------------------------------ leaf matrix in shared memory
+template <typename R> struct Mat34 { R m[12]; };
+
+__device__ __forceinline__ void load_mat(const float* sm, int i, Mat34<float>& M) {
+    const float4* p = reinterpret_cast<const float4*>(sm) + 3 * i;
+    float4 a = p[0], b = p[1], c = p[2];
+    M.m[0] = a.x; M.m[1] = a.y; M.m[2] = a.z; M.m[3] = a.w;
+    M.m[4] = b.x; M.m[5] = b.y; M.m[6] = b.z; M.m[7] = b.w;
+    M.m[8] = c.x; M.m[9] = c.y; M.m[10] = c.z; M.m[11] = c.w;
+}
+__device__ __forceinline__ void load_mat(const double* sm, int i, Mat34<double>& M) {
+    const double2* p = reinterpret_cast<const double2*>(sm) + 6 * i;
+#pragma unroll
+    for (int k = 0; k < 6; k++) { double2 v = p[k]; M.m[2 * k] = v.x; M.m[2 * k + 1] = v.y; }
+}
+
+// rayToObjectSpace (raytracer.go:51-56) with Mat4.MulPoint / MulDir's operand order (vec.go:298-313)
+template <typename R> __device__ __forceinline__ void to_object(const R* m, const Ray<R>& w, Ray<R>& o) {
+    o.ox = m[0] * w.ox + m[1] * w.oy + m[2] * w.oz + m[3];
+    o.oy = m[4] * w.ox + m[5] * w.oy + m[6] * w.oz + m[7];
+    o.oz = m[8] * w.ox + m[9] * w.oy + m[10] * w.oz + m[11];
+    o.dx = m[0] * w.dx + m[1] * w.dy + m[2] * w.dz;
+    o.dy = m[4] * w.dx + m[5] * w.dy + m[6] * w.dz;
+    o.dz = m[8] * w.dx + m[9] * w.dy + m[10] * w.dz;
+}
+
+// ------------------------------------------------------------------ first-hit rule per primitive
+// Each returns true and (t, face) exactly as <Type>.Intersect would.
+
+template <typename R> __device__ __forceinline__ bool hit_sphere(const Ray<R>& r, R& t, int& face) {   // :78-103
+    R a = r.dx * r.dx + r.dy * r.dy + r.dz * r.dz;
+    R hb = r.ox * r.dx + r.oy * r.dy + r.oz * r.dz;
+    R c = r.ox * r.ox + r.oy * r.oy + r.oz * r.oz - R(1);
+    R disc = hb * hb - a * c;
+    if (disc < R(0)) return false;
+    R t0 = (-hb - gm<R>::sqrt(disc)) / a;
+    if (t0 > R(0)) { t = t0; face = 0; return true; }
+    return false;                       // the far root is never used (:98-102)
+}
+
+template <typename R> __device__ __forceinline__ bool hit_plane(const Ray<R>& r, R& t, int& face) {    // :164-180
+    R den = r.dy;                       // N = (0,1,0), D = 0 (evaluator.go:816-822)
+    if (gm<R>::abs(den) < R(1e-6)) return false;
+    R tt = (R(0) - r.oy) / den;
+    if (tt <= R(0)) return false;
+    t = tt; face = 0;
+    return true;
+}
+
+// one cube face: plane test + inclusive bounds (:218-237).  The reference also bounds-checks the
+// coordinate of the face's own plane, which is 0 or 1 only up to rounding: in float64 that test
+// randomly rejects ~1.5% of cube.gml's pixels and parity mode reproduces it bit for
+// bit.  In float32 with FMA the residual o + d*(num/den) is almost never exactly on the plane, so
+// throughput mode skips the own-axis test (AXIS) - a documented deviation.
+template <typename R, int AXIS>
+__device__ __forceinline__ void cube_face(const Ray<R>& r, R num, R den, int f, R& best, int& bf) {
+    constexpr bool strict = std::is_same<R, double>::value;
+    if (gm<R>::abs(den) < R(1e-6)) return;
+    R t = num / den;
+    if (t <= R(0)) return;
+    R px = r.ox + r.dx * t, py = r.oy + r.dy * t, pz = r.oz + r.dz * t;
+    if ((strict || AXIS != 0) && (px < R(0) || px > R(1))) return;
+    if ((strict || AXIS != 1) && (py < R(0) || py > R(1))) return;
+    if ((strict || AXIS != 2) && (pz < R(0) || pz > R(1))) return;
+    if (bf < 0 || t < best) { best = t; bf = f; }
+}
+template <typename R> __device__ __forceinline__ bool hit_cube(const Ray<R>& r, R& t, int& face) {     // :214-240
+    R best = R(0); int bf = -1;
+    cube_face<R, 2>(r, r.oz, -r.dz, 0, best, bf);             // Front  z=0, n=(0,0,-1)   (plane.go:29-38)
+    cube_face<R, 2>(r, R(1) - r.oz, r.dz, 1, best, bf);       // Back   z=1
+    cube_face<R, 0>(r, r.ox, -r.dx, 2, best, bf);             // Left   x=0
+    cube_face<R, 0>(r, R(1) - r.ox, r.dx, 3, best, bf);       // Right  x=1
+    cube_face<R, 1>(r, R(1) - r.oy, r.dy, 4, best, bf);       // Top    y=1
+    cube_face<R, 1>(r, r.oy, -r.dy, 5, best, bf);             // Bottom y=0
+    if (bf < 0) return false;
+    t = best; face = bf;
+    return true;
+}
+
+template <typename R> __device__ __forceinline__ bool hit_cylinder(const Ray<R>& r, R& t, int& face) { // :279-337
+    R best = gm<R>::inf(); int bf = -1;
+    R a = r.dx * r.dx + r.dz * r.dz;
+    if (a > R(1e-12)) {
+        R hb = r.ox * r.dx + r.oz * r.dz;
+        R c0 = r.ox * r.ox + r.oz * r.oz - R(1);
+        R disc = hb * hb - a * c0;
+        if (disc >= R(0)) {
+            R sq = gm<R>::sqrt(disc);
+            R t0 = (-hb - sq) / a, t1 = (-hb + sq) / a;
+            R y0 = r.oy + r.dy * t0;
+            if (y0 >= R(0) && y0 <= R(1) && t0 > R(0) && t0 < best) { best = t0; bf = 0; }
+            R y1 = r.oy + r.dy * t1;
+            if (y1 >= R(0) && y1 <= R(1) && t1 > R(0) && t1 < best) { best = t1; bf = 0; }
+        }
+    }
+    if (gm<R>::abs(r.dy) > R(1e-12)) {
+        R tt = (R(1) - r.oy) / r.dy;
+        R px = r.ox + r.dx * tt, pz = r.oz + r.dz * tt;
+        if (px * px + pz * pz <= R(1) && tt > R(0) && tt < best) { best = tt; bf = 1; }
+        R tb = -r.oy / r.dy;
+        px = r.ox + r.dx * tb; pz = r.oz + r.dz * tb;
+        if (px * px + pz * pz <= R(1) && tb > R(0) && tb < best) { best = tb; bf = 2; }
+    }
+    if (bf < 0) return false;
+    t = best; face = bf;
+    return true;
+}
+
+// EXTENSION (no reference behaviour): x^2 + z^2 <= y^2, 0 <= y <= 1; same candidate rule as the cylinder
+template <typename R> __device__ __forceinline__ bool hit_cone(const Ray<R>& r, R& t, int& face) {
+    R best = gm<R>::inf(); int bf = -1;
+    R a = r.dx * r.dx + r.dz * r.dz - r.dy * r.dy;
+    R hb = r.ox * r.dx + r.oz * r.dz - r.oy * r.dy;
+    R c0 = r.ox * r.ox + r.oz * r.oz - r.oy * r.oy;
+    if (gm<R>::abs(a) > R(1e-12)) {
+        R disc = hb * hb - a * c0;
+        if (disc >= R(0)) {
+            R sq = gm<R>::sqrt(disc);
+            R t0 = (-hb - sq) / a, t1 = (-hb + sq) / a;
+            R y0 = r.oy + r.dy * t0;
+            if (y0 >= R(0) && y0 <= R(1) && t0 > R(0) && t0 < best) { best = t0; bf = 0; }
+            R y1 = r.oy + r.dy * t1;
+            if (y1 >= R(0) && y1 <= R(1) && t1 > R(0) && t1 < best) { best = t1; bf = 0; }
+        }
+    } else if (gm<R>::abs(hb) > R(1e-12)) {
+        R t0 = -c0 / (R(2) * hb);
+        R y0 = r.oy + r.dy * t0;
+        if (y0 >= R(0) && y0 <= R(1) && t0 > R(0) && t0 < best) { best = t0; bf = 0; }
+    }
+    if (gm<R>::abs(r.dy) > R(1e-12)) {
+        R tt = (R(1) - r.oy) / r.dy;
+        R px = r.ox + r.dx * tt, pz = r.oz + r.dz * tt;
+        if (px * px + pz * pz <= R(1) && tt > R(0) && tt < best) { best = tt; bf = 1; }
+    }
+    if (bf < 0) return false;
+    t = best; face = bf;
+    return true;
+}
+
+template <typename R, int KIND> __device__ __forceinline__ bool hit_kind(const Ray<R>& r, R& t, int& face) {
+    if (KIND == K_SPHERE) return hit_sphere(r, t, face);
+    if (KIND == K_CUBE) return hit_cube(r, t, face);
+    if (KIND == K_CYLINDER) return hit_cylinder(r, t, face);
+    if (KIND == K_CONE) return hit_cone(r, t, face);
+    return hit_plane(r, t, face);
+}
+
+// ------------------------------------------------------------------ TMA bulk copy + mbarrier (sm_90+/sm_100a)
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// global -> shared, `bytes` a multiple of 16, completion signalled on `bar` (SASS: UBLKCP)
+__device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+// ------------------------------------------------------------------ closest-hit scan of one staged chunk
+// Leaves [base, base+cnt) of the device-ordered array are in `sm`.  Keeps the reference's
+// tie rule: strictly smaller T wins, equal T keeps the object that comes first in scan order.
+template <typename R, int KIND>
+__device__ __forceinline__ void closest_kind(const DevScene<R>& sc, const R* sm, int base, int cnt, const Ray<R>& w,
+                                             R& best_t, int& best_i, int& best_face) {
+    int lo = max(sc.kind_begin[KIND], base), hi = min(sc.kind_begin[KIND + 1], base + cnt);
+#pragma unroll 2
+    for (int i = lo; i < hi; i++) {
+        Mat34<R> M;
+        load_mat(sm, i - base, M);
+        Ray<R> o;
+        to_object(M.m, w, o);
+        R t; int face;
+        if (hit_kind<R, KIND>(o, t, face)) {
+            if (best_i < 0 || t < best_t || (t == best_t && sc.scan_of[i] < sc.scan_of[best_i])) {
+                best_t = t; best_i = i; best_face = face;
+            }
+        }
+    }
+}
+
+template <typename R>
+__device__ __forceinline__ void closest_chunk(const DevScene<R>& sc, const R* sm, int base, int cnt, const Ray<R>& w,
+                                              R& best_t, int& best_i, int& best_face) {
+    closest_kind<R, K_SPHERE>(sc, sm, base, cnt, w, best_t, best_i, best_face);
+    closest_kind<R, K_CUBE>(sc, sm, base, cnt, w, best_t, best_i, best_face);
+    closest_kind<R, K_CYLINDER>(sc, sm, base, cnt, w, best_t, best_i, best_face);
+    closest_kind<R, K_CONE>(sc, sm, base, cnt, w, best_t, best_i, best_face);
+    closest_kind<R, K_PLANE>(sc, sm, base, cnt, w, best_t, best_i, best_face);
+}
+
+// any-hit scan: inShadow's test  shadowHit.T * |ray.Direction| < distToLight  (raytracer.go:424)
+template <typename R, int KIND, bool COUNT>
+__device__ __forceinline__ void shadow_kind(const DevScene<R>& sc, const R* sm, int base, int cnt, const Ray<R>& w, R dist,
+                                            R in_len, int skip, bool& done, unsigned& tests) {
+    int lo = max(sc.kind_begin[KIND], base), hi = min(sc.kind_begin[KIND + 1], base + cnt);
+    for (int i = lo; i < hi; i++) {
+        if (__all_sync(0xffffffffu, done)) return;
+        if (!done) {
+            Mat34<R> M;
+            load_mat(sm, i - base, M);
+            Ray<R> o;
+            to_object(M.m, w, o);
+            R t; int face;
+            bool h = hit_kind<R, KIND>(o, t, face);
+            if (COUNT && i != skip) tests++;
+            if (h && i != skip && t * in_len < dist) done = true;
+        }
+    }
+}
+
+constexpr int SCAN_THREADS = 256;
+
+// Stage chunk c of the leaf matrices into `dst` (thread 0 only).
+template <typename R>
+__device__ __forceinline__ void stage_chunk(const DevScene<R>& sc, int c, int chunk_leaves, R* dst, uint64_t* bar) {
+    int base = c * chunk_leaves;
+    int cnt = min(chunk_leaves, sc.n_leaves - base);
+    uint32_t bytes = (uint32_t)(cnt * 12 * sizeof(R));
+    mbar_expect_tx(bar, bytes);
+    tma_load_1d(dst, sc.w2o + (size_t)base * 12, bytes, bar);
+}
+
+// closestHit for one recursion level (raytracer.go:469-483).  Persistent CTAs; the scene is
+// staged once per CTA when it fits one buffer ("resident"), else streamed through two
+// buffers per block of rays.
+template <typename R>
+__global__ void __launch_bounds__(SCAN_THREADS) k_closest(DevScene<R> sc, Level<R> lv, const Counters* ctr, int level,
+                                                          int chunk_leaves, int resident) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ __align__(8) uint64_t bar[2];
+    R* buf[2] = {reinterpret_cast<R*>(smem_raw), reinterpret_cast<R*>(smem_raw) + (size_t)chunk_leaves * 12};
+    const int n = ctr->count[level];
+    const int nblocks = (n + SCAN_THREADS - 1) / SCAN_THREADS;
+    if ((int)blockIdx.x >= nblocks) return;
+    const int tid = threadIdx.x;
+    const int N = sc.n_leaves;
+    const int nchunks = (N + chunk_leaves - 1) / chunk_leaves;
+    if (tid == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_fence_init(); }
+    __syncthreads();
+    uint32_t phase[2] = {0, 0};
+    if (resident && N > 0) {
+        if (tid == 0) stage_chunk(sc, 0, chunk_leaves, buf[0], &bar[0]);
+        mbar_wait(&bar[0], 0);
+    }
+    for (int blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
+        const int i = blk * SCAN_THREADS + tid;
+        const bool active = i < n;
+        Ray<R> w = {R(0), R(0), R(0), R(0), R(0), R(1)};
+        if (active) {
+            const int cap = lv.cap;
+            w.ox = lv.ray[i]; w.oy = lv.ray[cap + i]; w.oz = lv.ray[2 * cap + i];
+            w.dx = lv.ray[3 * cap + i]; w.dy = lv.ray[4 * cap + i]; w.dz = lv.ray[5 * cap + i];
+        }
+        R best_t = R(0); int best_i = -1, best_face = 0;
+        if (resident) {
+            closest_chunk(sc, buf[0], 0, N, w, best_t, best_i, best_face);
+        } else {
+            if (tid == 0) {
+                stage_chunk(sc, 0, chunk_leaves, buf[0], &bar[0]);
+                if (nchunks > 1) stage_chunk(sc, 1, chunk_leaves, buf[1], &bar[1]);
+            }
+            for (int c = 0; c < nchunks; c++) {
+                const int b = c & 1;
+                mbar_wait(&bar[b], phase[b]);
+                phase[b] ^= 1;
+                const int base = c * chunk_leaves;
+                closest_chunk(sc, buf[b], base, min(chunk_leaves, N - base), w, best_t, best_i, best_face);
+                __syncthreads();                       // everyone is done reading buf[b]
+                if (tid == 0 && c + 2 < nchunks) stage_chunk(sc, c + 2, chunk_leaves, buf[b], &bar[b]);
+            }
+        }
+        if (active) {
+            lv.hit[i] = best_i < 0 ? -1 : (best_i | (best_face << 28));
+            lv.t[i] = best_t;
+        }
+    }
+}
+
+// inShadow for every queued (hit, light) pair (raytracer.go:411-429): writes occl[target] = 1.
+template <typename R, bool COUNT>
+__global__ void __launch_bounds__(SCAN_THREADS) k_shadow(DevScene<R> sc, ShadowQueue<R> sq, unsigned char* occl,
+                                                         Counters* ctr, int chunk_leaves, int resident) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ __align__(8) uint64_t bar[2];
+    R* buf[2] = {reinterpret_cast<R*>(smem_raw), reinterpret_cast<R*>(smem_raw) + (size_t)chunk_leaves * 12};
+    const int n = ctr->shadow_count;
+    const int nblocks = (n + SCAN_THREADS - 1) / SCAN_THREADS;
+    if ((int)blockIdx.x >= nblocks) return;
+    const int tid = threadIdx.x;
+    const int N = sc.n_leaves;
+    const int nchunks = (N + chunk_leaves - 1) / chunk_leaves;
+    if (tid == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_fence_init(); }
+    __syncthreads();
+    uint32_t phase[2] = {0, 0};
+    if (resident && N > 0) {
+        if (tid == 0) stage_chunk(sc, 0, chunk_leaves, buf[0], &bar[0]);
+        mbar_wait(&bar[0], 0);
+    }
+    unsigned tests[K_COUNT] = {0, 0, 0, 0, 0};
+    unsigned n_occluded = 0;
+    if (blockIdx.x == 0 && tid == 0) atomicAdd(&ctr->rays_shadow, (unsigned long long)n);
+    for (int blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
+        const int i = blk * SCAN_THREADS + tid;
+        const bool active = i < n;
+        Ray<R> w = {R(0), R(0), R(0), R(0), R(0), R(1)};
+        R dist = R(0), in_len = R(1);
+        int skip = -1;
+        if (active) {
+            const int cap = sq.cap;
+            w.ox = sq.q[i]; w.oy = sq.q[cap + i]; w.oz = sq.q[2 * cap + i];
+            w.dx = sq.q[3 * cap + i]; w.dy = sq.q[4 * cap + i]; w.dz = sq.q[5 * cap + i];
+            dist = sq.q[6 * cap + i]; in_len = sq.q[7 * cap + i];
+            skip = sq.skip[i];
+        }
+        bool done = !active;
+#define SHADOW_CHUNK(SM, BASE, CNT)                                                                         \
+        shadow_kind<R, K_SPHERE, COUNT>(sc, SM, BASE, CNT, w, dist, in_len, skip, done, tests[K_SPHERE]);   \
+        shadow_kind<R, K_CUBE, COUNT>(sc, SM, BASE, CNT, w, dist, in_len, skip, done, tests[K_CUBE]);       \
+        shadow_kind<R, K_CYLINDER, COUNT>(sc, SM, BASE, CNT, w, dist, in_len, skip, done, tests[K_CYLINDER]); \
+        shadow_kind<R, K_CONE, COUNT>(sc, SM, BASE, CNT, w, dist, in_len, skip, done, tests[K_CONE]);       \
+        shadow_kind<R, K_PLANE, COUNT>(sc, SM, BASE, CNT, w, dist, in_len, skip, done, tests[K_PLANE]);
+        if (resident) {
+            SHADOW_CHUNK(buf[0], 0, N)
+        } else {
+            if (tid == 0) {
+                stage_chunk(sc, 0, chunk_leaves, buf[0], &bar[0]);
+                if (nchunks > 1) stage_chunk(sc, 1, chunk_leaves, buf[1], &bar[1]);
+            }
+            for (int c = 0; c < nchunks; c++) {
+                const int b = c & 1;
+                mbar_wait(&bar[b], phase[b]);
+                phase[b] ^= 1;
+                const int base = c * chunk_leaves;
+                const int cnt = min(chunk_leaves, N - base);
+                SHADOW_CHUNK(buf[b], base, cnt)
+                __syncthreads();
+                if (tid == 0 && c + 2 < nchunks) stage_chunk(sc, c + 2, chunk_leaves, buf[b], &bar[b]);
+            }
+        }
+#undef SHADOW_CHUNK
+        if (active && done) { occl[sq.target[i]] = 1; n_occluded++; }
+    }
+    // per-warp totals -> one atomic each
+    for (int off = 16; off > 0; off >>= 1) n_occluded += __shfl_down_sync(0xffffffffu, n_occluded, off);
+    if ((tid & 31) == 0 && n_occluded) atomicAdd(&ctr->shadow_occluded, (unsigned long long)n_occluded);
+    if (COUNT) {
+        for (int k = 0; k < K_COUNT; k++) {
+            unsigned v = tests[k];
+            for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
+            if ((tid & 31) == 0 && v) atomicAdd(&ctr->shadow_tests[k], (unsigned long long)v);
+        }
+    }
+}
+
+// ------------------------------------------------------------------ surface bytecode interpreter
+// EvalSurfaceFn (internal/gml/evaluator.go:672-727) after host-side partial evaluation: typed
+// register code, see include/gmlrt.h.  Registers live in local memory (dynamic indexing).
+template <typename R> struct IntOf;
+template <> struct IntOf<float> { typedef int type; };
+template <> struct IntOf<double> { typedef long long type; };
+
+template <typename R> union Cell { R f; typename IntOf<R>::type i; };
+
+// returns false on a fault (index out of range, integer division by zero, ERR, malformed code)
+template <typename R>
+__device__ __noinline__ bool run_surface(const DevScene<R>& sc, const DevSurface<R>& sf, int face, R u, R v, R* mat) {
+    typedef typename IntOf<R>::type I;
+    typedef typename std::make_unsigned<I>::type U;
+    Cell<R> r[GMLRT_VM_MAX_REGS];
+    const uint32_t* code = sc.code + sf.code_off;
+    uint32_t pc = 0;
+    const uint32_t n = sf.code_len;
+    const R deg = R(GM_PI / 180.0);
+    r[0].i = face; r[1].f = u; r[2].f = v;
+    while (pc < n) {
+        const uint32_t w = code[pc++];
+        const uint32_t op = w & 0xFF, d = (w >> 8) & 0x7F, a = (w >> 16) & 0x7F, b = (w >> 24) & 0x7F;
+        switch (op) {
+        case GMLRT_OP_RET:
+            if (a + 10 > GMLRT_VM_MAX_REGS) return false;
+            for (int k = 0; k < 10; k++) mat[k] = r[a + k].f;
+            return true;
+        case GMLRT_OP_LDK: { uint32_t k = ((w >> 16) & 0xFF) | ((w >> 24) << 8); if ((int)k >= sc.n_fpool) return false; r[d].f = sc.fpool[k]; break; }
+        case GMLRT_OP_LDI: r[d].i = (int32_t)code[pc++]; break;
+        case GMLRT_OP_MOV: r[d] = r[a]; break;
+        case GMLRT_OP_ADDF: r[d].f = r[a].f + r[b].f; break;
+        case GMLRT_OP_SUBF: r[d].f = r[a].f - r[b].f; break;
+        case GMLRT_OP_MULF: r[d].f = r[a].f * r[b].f; break;
+        case GMLRT_OP_DIVF: r[d].f = r[a].f / r[b].f; break;
+        case GMLRT_OP_NEGF: r[d].f = -r[a].f; break;
+        case GMLRT_OP_ADDI: r[d].i = (I)((U)r[a].i + (U)r[b].i); break;
+        case GMLRT_OP_SUBI: r[d].i = (I)((U)r[a].i - (U)r[b].i); break;
+        case GMLRT_OP_MULI: r[d].i = (I)((U)r[a].i * (U)r[b].i); break;
+        case GMLRT_OP_DIVI: if (r[b].i == 0) return false; r[d].i = (r[b].i == -1) ? (I)(U(0) - (U)r[a].i) : r[a].i / r[b].i; break;
+        case GMLRT_OP_MODI: if (r[b].i == 0) return false; r[d].i = (r[b].i == -1) ? 0 : r[a].i % r[b].i; break;
+        case GMLRT_OP_NEGI: r[d].i = (I)(U(0) - (U)r[a].i); break;
+        case GMLRT_OP_EQF: r[d].i = r[a].f == r[b].f; break;
+        case GMLRT_OP_LESSF: r[d].i = r[a].f < r[b].f; break;
+        case GMLRT_OP_EQI: r[d].i = r[a].i == r[b].i; break;
+        case GMLRT_OP_LESSI: r[d].i = r[a].i < r[b].i; break;
+        case GMLRT_OP_SIN: r[d].f = gm<R>::sin(deg * r[a].f); break;
+        case GMLRT_OP_COS: r[d].f = gm<R>::cos(deg * r[a].f); break;
+        case GMLRT_OP_SQRT: r[d].f = gm<R>::sqrt(r[a].f); break;
+        case GMLRT_OP_CLAMPF: { R x = r[a].f; if (x < R(0)) x = R(0); else if (x > R(1)) x = R(1); r[d].f = x; break; }
+        case GMLRT_OP_FLOOR: r[d].i = (I)gm<R>::floor(r[a].f); break;
+        case GMLRT_OP_FRAC: r[d].f = r[a].f - (R)(I)r[a].f; break;
+        case GMLRT_OP_REAL: r[d].f = (R)r[a].i; break;
+        case GMLRT_OP_ACOS: r[d].f = gm<R>::acos(r[a].f) / deg; break;
+        case GMLRT_OP_ASIN: r[d].f = gm<R>::asin(r[a].f) / deg; break;
+        case GMLRT_OP_LDARR: r[d].i = code[pc]; r[(d + 1) & 0x7F].i = code[pc + 1]; pc += 2; break;
+        case GMLRT_OP_LEN: r[d].i = r[(a + 1) & 0x7F].i; break;
+        case GMLRT_OP_GETF: case GMLRT_OP_GETP: case GMLRT_OP_GETI: case GMLRT_OP_GETA: {
+            const long long off = r[a].i, len = r[(a + 1) & 0x7F].i, idx = r[b].i;
+            if (idx < 0 || idx >= len) return false;                        // evaluator.go:989-995
+            if (op == GMLRT_OP_GETF) { if (off + idx >= sc.n_fpool) return false; r[d].f = sc.fpool[off + idx]; }
+            else if (op == GMLRT_OP_GETP) {
+                if (off + 3 * idx + 2 >= sc.n_fpool || d + 2 >= GMLRT_VM_MAX_REGS) return false;
+                for (int k = 0; k < 3; k++) r[d + k].f = sc.fpool[off + 3 * idx + k];
+            } else if (op == GMLRT_OP_GETI) { if (off + idx >= sc.n_itab) return false; r[d].i = sc.itab[off + idx]; }
+            else {
+                if (off + 2 * idx + 1 >= sc.n_itab) return false;
+                r[d].i = sc.itab[off + 2 * idx]; r[(d + 1) & 0x7F].i = sc.itab[off + 2 * idx + 1];
+            }
+            break;
+        }
+        case GMLRT_OP_JMP: pc += 1 + code[pc]; break;
+        case GMLRT_OP_JMPF: if (r[a].i == 0) pc += 1 + code[pc]; else pc += 1; break;
+        default: return false;   // GMLRT_OP_ERR and anything unknown
+        }
+    }
+    return false;
+}
+
+// ------------------------------------------------------------------ small vector helpers (Vec3, vec.go:23-116)
+template <typename R> struct V3 { R x, y, z; };
+template <typename R> __device__ __forceinline__ V3<R> mk(R x, R y, R z) { V3<R> v = {x, y, z}; return v; }
+template <typename R> __device__ __forceinline__ V3<R> operator+(V3<R> a, V3<R> b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+template <typename R> __device__ __forceinline__ V3<R> operator-(V3<R> a, V3<R> b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+template <typename R> __device__ __forceinline__ V3<R> operator*(V3<R> a, R s) { return mk(a.x * s, a.y * s, a.z * s); }
+template <typename R> __device__ __forceinline__ V3<R> hadamard(V3<R> a, V3<R> b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
+template <typename R> __device__ __forceinline__ R dot(V3<R> a, V3<R> b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+template <typename R> __device__ __forceinline__ R length(V3<R> a) { return gm<R>::sqrt(a.x * a.x + a.y * a.y + a.z * a.z); }
+template <typename R> __device__ __forceinline__ V3<R> normalize(V3<R> a) {
+    R m = gm<R>::sqrt(a.x * a.x + a.y * a.y + a.z * a.z);
+    return mk(a.x / m, a.y / m, a.z / m);
+}
+template <typename R> __device__ __forceinline__ V3<R> neg(V3<R> a) { return mk(-a.x, -a.y, -a.z); }
+template <typename R> __device__ __forceinline__ V3<R> clamp3(V3<R> a) {
+    return mk(gomath::clamp01(a.x), gomath::clamp01(a.y), gomath::clamp01(a.z));
+}
+template <typename R> __device__ __forceinline__ V3<R> ld3(const R* p) { return mk(p[0], p[1], p[2]); }
+// (M^T) v : NormalMat.MulDir with NormalMat = WorldToObject^T (raytracer.go:367, 790)
+template <typename R> __device__ __forceinline__ V3<R> mul_dir_t(const R* m, V3<R> v) {
+    return mk(m[0] * v.x + m[4] * v.y + m[8] * v.z, m[1] * v.x + m[5] * v.y + m[9] * v.z, m[2] * v.x + m[6] * v.y + m[10] * v.z);
+}
+template <typename R> __device__ __forceinline__ V3<R> mul_point(const R* m, V3<R> v) {
+    return mk(m[0] * v.x + m[1] * v.y + m[2] * v.z + m[3], m[4] * v.x + m[5] * v.y + m[6] * v.z + m[7],
+              m[8] * v.x + m[9] * v.y + m[10] * v.z + m[11]);
+}
+
+// queue append with one atomic per warp (ballot + popc compaction).  Must be called by all 32 lanes.
+__device__ __forceinline__ int warp_append(int* counter, bool want) {
+    const unsigned m = __ballot_sync(0xffffffffu, want);
+    if (m == 0) return -1;
+    const int lane = threadIdx.x & 31;
+    const int leader = __ffs(m) - 1;
+    int base = 0;
+    if (lane == leader) base = atomicAdd(counter, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return want ? base + __popc(m & ((1u << lane) - 1u)) : -1;
+}
+
+// direction to a light, distance, and its colour at P (spot falloff is an EXTENSION); false = unlit
+template <typename R>
+__device__ __forceinline__ bool light_at(const DevLight<R>& L, V3<R> P, V3<R>& ldir, R& dist, V3<R>& lcol) {
+    lcol = ld3(L.color);
+    if (L.kind == GMLRT_LIGHT_DIRECTIONAL) {
+        ldir = normalize(neg(ld3(L.pos)));
+        dist = gm<R>::inf();
+        return true;
+    }
+    V3<R> l2h = ld3(L.pos) - P;                       // raytracer.go:379-381
+    dist = length(l2h);
+    ldir = normalize(l2h);
+    if (L.kind == GMLRT_LIGHT_SPOT) {
+        R cosang = dot(ld3(L.axis), neg(ldir));
+        if (cosang < L.cos_cutoff) return false;
+        lcol = lcol * gm<R>::pow(cosang, L.exponent);
+    }
+    return true;
+}
+
+// ------------------------------------------------------------------ gen: camera rays (Render, raytracer.go:632-652)
+__constant__ gomath::PcgJump c_pcg_jump[160];   // affine maps advancing the PCG stream by 0..159 draws
+
+constexpr int SHADE_THREADS = 128;
+
+template <typename R>
+__global__ void __launch_bounds__(256) k_gen(DevScene<R> sc, Level<R> lv, Counters* ctr, int y0, int rows) {
+    const int S = rows * sc.W * 4;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) {
+        for (int l = 1; l <= GMLRT_MAX_DEPTH; l++) ctr->count[l] = 0;
+        ctr->count[0] = S;
+        ctr->shadow_count = 0;
+    }
+    if (i >= S) return;
+    const int s = i & 3, pix = i >> 2;
+    const int x = pix % sc.W, y = y0 + pix / sc.W;
+    const int ymin = (y / 20) * 20;                       // work item = (column, 20-row batch), :663-672
+    const int q = 8 * (y - ymin) + 2 * s;                 // draws consumed before this sample
+    gomath::Pcg rng;
+    rng.hi = 0xDEADull ^ (uint64_t)x;                     // :632-634
+    rng.lo = 0xBEEFull ^ (uint64_t)ymin;
+    const gomath::PcgJump J = c_pcg_jump[q];
+    gomath::affine128(rng.hi, rng.lo, J.mh, J.ml, J.ih, J.il);
+    const double dx = gomath::pcg_float64(rng) - 0.5;     // dx is drawn before dy (:642-643)
+    const double dy = gomath::pcg_float64(rng) - 0.5;
+    const double u = ((double)x + dx) / (double)(sc.W - 1) * sc.vw - sc.vw / 2.0;
+    const double v = ((double)y + dy) / (double)(sc.H - 1) * sc.vh - sc.vh / 2.0;
+    const double ox = u, oy = -v, oz = 0.0;               // screen point; eye = (0,0,-1)
+    const double ex = ox - 0.0, ey = oy - 0.0, ez = oz - (-1.0);
+    const double m = sqrt(ex * ex + ey * ey + ez * ez);
+    const int cap = lv.cap;
+    lv.ray[i] = (R)ox; lv.ray[cap + i] = (R)oy; lv.ray[2 * cap + i] = (R)oz;
+    lv.ray[3 * cap + i] = (R)(ex / m); lv.ray[4 * cap + i] = (R)(ey / m); lv.ray[5 * cap + i] = (R)(ez / m);
+}
+
+// ------------------------------------------------------------------ shade (traceRay :498-556 minus the recursion)
+// rec slots
+enum { REC_P = 0, REC_N = 3, REC_COL = 6, REC_REFL = 9, REC_TRANSP = 10, REC_KR = 11, REC_KD = 12, REC_KS = 13, REC_NEXP = 14, REC_INLEN = 15 };
+
+template <typename R>
+__global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R> lv, Level<R> next, ShadowQueue<R> sq,
+                                                         unsigned char* occl, Counters* ctr, int level, int spawn,
+                                                         int32_t* ids, int y0) {
+    const int n = ctr->count[level];
+    for (int blk0 = blockIdx.x * blockDim.x; blk0 < n; blk0 += gridDim.x * blockDim.x) {   // uniform per block
+    const int i = blk0 + threadIdx.x;
+    const int cap = lv.cap;
+    bool live = i < n;
+    int h = live ? lv.hit[i] : -1;
+    if (ids && live) {                                     // level 0 only: primary hit ids in (y, x, sample) order
+        ids[(size_t)y0 * sc.W * 4 + i] = h < 0 ? -1 : sc.scan_of[h & 0x0fffffff];
+    }
+    live = live && h >= 0;
+    Ray<R> w = {R(0), R(0), R(0), R(0), R(0), R(1)};
+    V3<R> P = mk(R(0), R(0), R(0)), N = P;
+    R mat[10];
+    for (int k = 0; k < 10; k++) mat[k] = R(0);
+    int leaf = 0;
+    if (live) {
+        leaf = h & 0x0fffffff;
+        int face = h >> 28;
+        w.ox = lv.ray[i]; w.oy = lv.ray[cap + i]; w.oz = lv.ray[2 * cap + i];
+        w.dx = lv.ray[3 * cap + i]; w.dy = lv.ray[4 * cap + i]; w.dz = lv.ray[5 * cap + i];
+        const R t = lv.t[i];
+        const R* Mw = sc.w2o + (size_t)leaf * 12;
+        Ray<R> o;
+        to_object(Mw, w, o);
+        const V3<R> p = mk(o.ox + o.dx * t, o.oy + o.dy * t, o.oz + o.dz * t);       // Hit.PointObj
+        const int kind = sc.kind[leaf];
+        const DevSurface<R>& sf = sc.surfaces[sc.surface[leaf]];
+        R u = R(0), v = R(0);
+        bool ok = true;
+        if (kind == K_SPHERE) {                                                      // :106-150
+            face = 0;
+            if (sf.kind != GMLRT_SURFACE_CONST) {
+                if (gm<R>::abs(p.y) > R(1)) ok = false;
+                v = (p.y + R(1)) / R(2);
+                u = gm<R>::acos(p.z / gm<R>::sqrt(R(1) - p.y * p.y)) / (R(2) * R(GM_PI));
+            }
+            N = p;                                                                   // :119 (sic: object-space point)
+        } else if (kind == K_PLANE) {                                                // :182-205
+            u = p.x; v = p.z; face = 0;
+            N = ld3(sc.fnormal + (size_t)leaf * 18);
+        } else if (kind == K_CUBE) {                                                 // :242-260
+            u = p.x; v = p.z;
+            N = ld3(sc.fnormal + (size_t)leaf * 18 + 3 * face);
+        } else if (kind == K_CYLINDER) {                                             // :339-370
+            V3<R> no;
+            if (face == 0) { no = mk(p.x, R(0), p.z); u = (gm<R>::atan2(p.x, p.z) + R(GM_PI)) / (R(2) * R(GM_PI)); v = p.y; }
+            else if (face == 1) { no = mk(R(0), R(1), R(0)); u = p.x; v = p.z; }
+            else { no = mk(R(0), R(-1), R(0)); u = p.x; v = p.z; }
+            N = normalize(mul_dir_t(Mw, no));
+        } else {                                                                     // cone (EXTENSION)
+            V3<R> no;
+            if (face == 0) { no = mk(p.x, -p.y, p.z); u = (gm<R>::atan2(p.x, p.z) + R(GM_PI)) / (R(2) * R(GM_PI)); v = p.y; }
+            else { no = mk(R(0), R(1), R(0)); u = p.x; v = p.z; }
+            N = normalize(mul_dir_t(Mw, no));
+        }
+        if (ok) {
+            if (sf.kind == GMLRT_SURFACE_CONST) { for (int k = 0; k < 10; k++) mat[k] = sf.material[k]; }
+            else ok = run_surface(sc, sf, face, u, v, mat);
+        }
+        if (!ok) {                                   // the reference panics here (:499-501)
+            atomicExch(&ctr->error, 1);
+            live = false;
+            lv.hit[i] = -1;
+        } else {
+            P = mul_point(sc.o2w + (size_t)leaf * 12, p);
+        }
+    }
+    const R refl = mat[3], fuzz = mat[4], transp = mat[5], ior = mat[6];
+    const V3<R> D = mk(w.dx, w.dy, w.dz);
+    if (live) {
+        R* rec = lv.rec + i;
+        rec[(REC_P + 0) * cap] = P.x; rec[(REC_P + 1) * cap] = P.y; rec[(REC_P + 2) * cap] = P.z;
+        rec[(REC_N + 0) * cap] = N.x; rec[(REC_N + 1) * cap] = N.y; rec[(REC_N + 2) * cap] = N.z;
+        rec[(REC_COL + 0) * cap] = mat[0]; rec[(REC_COL + 1) * cap] = mat[1]; rec[(REC_COL + 2) * cap] = mat[2];
+        rec[REC_REFL * cap] = refl; rec[REC_TRANSP * cap] = transp;
+        R kr = R(0);
+        if (transp > R(0)) {                                                         // fresnel :456-467
+            R cosi = dot(D, N) / (length(D) * length(N));
+            R r0 = (R(1) - ior) / (R(1) + ior);
+            r0 = r0 * r0;
+            kr = r0 + (R(1) - r0) * gm<R>::pow(R(1) - gm<R>::abs(cosi), R(5));
+        }
+        rec[REC_KR * cap] = kr;
+        rec[REC_KD * cap] = mat[7]; rec[REC_KS * cap] = mat[8]; rec[REC_NEXP * cap] = mat[9];
+        rec[REC_INLEN * cap] = length(D);
+        for (int k = 0; k < 6; k++) lv.child[k * cap + i] = R(0);
+    }
+    // shadow queries, one per light that can reach P (inShadow :411-414)
+    for (int li = 0; li < sc.n_lights; li++) {
+        V3<R> ldir = mk(R(0), R(0), R(1)), lcol; R dist = R(0);
+        bool want = live && light_at(sc.lights[li], P, ldir, dist, lcol);
+        const int slot = warp_append(&ctr->shadow_count, want);
+        if (want) {
+            const V3<R> so = P + N * R(1e-4);
+            const int qc = sq.cap;
+            sq.q[slot] = so.x; sq.q[qc + slot] = so.y; sq.q[2 * qc + slot] = so.z;
+            sq.q[3 * qc + slot] = ldir.x; sq.q[4 * qc + slot] = ldir.y; sq.q[5 * qc + slot] = ldir.z;
+            sq.q[6 * qc + slot] = dist; sq.q[7 * qc + slot] = length(D);
+            sq.skip[slot] = leaf;
+            sq.target[slot] = i * sc.n_lights + li;
+            occl[i * sc.n_lights + li] = 0;
+        }
+    }
+    if (!spawn) continue;                                  // uniform
+    // reflection child (:512-529)
+    {
+        const bool want = live && refl > R(0);
+        const int slot = warp_append(&ctr->count[level + 1], want);
+        if (want) {
+            V3<R> rd = D - N * (R(2) * dot(D, N));
+            if (fuzz >= R(0)) rd = rd + mk(fuzz * gm<R>::cos(fuzz) * gm<R>::cos(fuzz), fuzz * gm<R>::sin(fuzz) * gm<R>::sin(fuzz), R(0));
+            const V3<R> ro = P + N * R(1e-4);
+            rd = normalize(rd);
+            const int nc = next.cap;
+            next.ray[slot] = ro.x; next.ray[nc + slot] = ro.y; next.ray[2 * nc + slot] = ro.z;
+            next.ray[3 * nc + slot] = rd.x; next.ray[4 * nc + slot] = rd.y; next.ray[5 * nc + slot] = rd.z;
+            next.parent[slot] = i;
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, want);
+        if ((threadIdx.x & 31) == 0 && m) atomicAdd(&ctr->rays_reflect, (unsigned long long)__popc(m));
+    }
+    // refraction child (:532-556); direction is not re-normalised, zero vector = total internal reflection
+    {
+        bool want = live && transp > R(0);
+        V3<R> rd = mk(R(0), R(0), R(0)), nn = N;
+        if (want) {
+            R n1 = R(1), n2 = ior;
+            if (dot(D, nn) > R(0)) { R tmp = n1; n1 = n2; n2 = tmp; nn = nn * R(-1); }
+            const R ratio = n1 / n2;                                                 // refract :438-450
+            const R cosI = -dot(nn, D);
+            const R sinT2 = ratio * ratio * (R(1) - cosI * cosI);
+            if (sinT2 > R(1)) want = false;
+            else {
+                const R cosT = gm<R>::sqrt(R(1) - sinT2);
+                rd = D * ratio + nn * (ratio * cosI - cosT);
+                if (rd.x == R(0) && rd.y == R(0) && rd.z == R(0)) want = false;
+            }
+        }
+        const int slot = warp_append(&ctr->count[level + 1], want);
+        if (want) {
+            const V3<R> ro = P - nn * R(1e-4);
+            const int nc = next.cap;
+            next.ray[slot] = ro.x; next.ray[nc + slot] = ro.y; next.ray[2 * nc + slot] = ro.z;
+            next.ray[3 * nc + slot] = rd.x; next.ray[4 * nc + slot] = rd.y; next.ray[5 * nc + slot] = rd.z;
+            next.parent[slot] = i | 0x80000000;
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, want);
+        if ((threadIdx.x & 31) == 0 && m) atomicAdd(&ctr->rays_refract, (unsigned long long)__popc(m));
+    }
+    }  // grid-stride loop
+}
+
+// ------------------------------------------------------------------ resolve one level (deepest first)
+// computeLighting (:372-401) with the shadow flags, then the combine + clamp of traceRay
+// (:493-497, :506-508, :557-561); the result goes into the parent's child slot, or into the
+// sample buffer at level 0.
+template <typename R>
+__global__ void __launch_bounds__(SHADE_THREADS) k_resolve(DevScene<R> sc, Level<R> lv, Level<R> prev, const unsigned char* occl,
+                                                           const Counters* ctr, int level, R* samples, int sample_cap) {
+    const int n = ctr->count[level];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const int cap = lv.cap;
+    const V3<R> D = mk(lv.ray[3 * cap + i], lv.ray[4 * cap + i], lv.ray[5 * cap + i]);
+    V3<R> out;
+    if (lv.hit[i] < 0) {
+        const R t = R(0.5) * (D.y + R(1));                                           // :495-496
+        const V3<R> a = ld3(sc.bg0), b = ld3(sc.bg1);
+        out = mk(a.x + (b.x - a.x) * t, a.y + (b.y - a.y) * t, a.z + (b.z - a.z) * t);
+    } else {
+        const R* rec = lv.rec + i;
+        const V3<R> P = mk(rec[(REC_P + 0) * cap], rec[(REC_P + 1) * cap], rec[(REC_P + 2) * cap]);
+        const V3<R> N = mk(rec[(REC_N + 0) * cap], rec[(REC_N + 1) * cap], rec[(REC_N + 2) * cap]);
+        const V3<R> C = mk(rec[(REC_COL + 0) * cap], rec[(REC_COL + 1) * cap], rec[(REC_COL + 2) * cap]);
+        const R refl = rec[REC_REFL * cap], transp = rec[REC_TRANSP * cap], kr = rec[REC_KR * cap];
+        const R kd = rec[REC_KD * cap], ks = rec[REC_KS * cap], nexp = rec[REC_NEXP * cap];
+        const V3<R> Vv = neg(D);
+        V3<R> L = ld3(sc.ambient) * kd;
+        for (int li = 0; li < sc.n_lights; li++) {
+            V3<R> ldir, lcol; R dist;
+            if (!light_at(sc.lights[li], P, ldir, dist, lcol)) continue;
+            if (occl[i * sc.n_lights + li]) continue;
+            const R nDotL = gomath::max0(dot(N, ldir));
+            const V3<R> diffuse = lcol * (nDotL * kd);
+            const V3<R> H = normalize(Vv + ldir);
+            const R spec = gomath::max0(dot(N, H));
+            const V3<R> specular = lcol * (ks * gm<R>::pow(spec, nexp));
+            L = (L + diffuse) + specular;
+        }
+        if (refl == R(0) && transp == R(0)) {
+            out = clamp3(hadamard(L, C));
+        } else {
+            const V3<R> rc = mk(lv.child[i], lv.child[cap + i], lv.child[2 * cap + i]);
+            if (transp == R(0)) {
+                out = clamp3(hadamard(L + rc * refl, C));
+            } else {
+                const V3<R> fc = mk(lv.child[3 * cap + i], lv.child[4 * cap + i], lv.child[5 * cap + i]);
+                out = clamp3(hadamard(L * (R(1) - transp) + (rc * kr + fc * (R(1) - kr)), C));
+            }
+        }
+    }
+    if (level == 0) {
+        samples[i] = out.x; samples[sample_cap + i] = out.y; samples[2 * sample_cap + i] = out.z;
+    } else {
+        const int p = lv.parent[i];
+        const int pi = p & 0x7fffffff;
+        const int base = (p < 0) ? 3 : 0;
+        const int pc = prev.cap;
+        prev.child[(base + 0) * pc + pi] = out.x; prev.child[(base + 1) * pc + pi] = out.y; prev.child[(base + 2) * pc + pi] = out.z;
+    }
+    }  // grid-stride loop
+}
+
+// mean of the 4 samples and quantisation: img.Set(x, y, total*0.25) -> Vec3.RGBA -> RGBAModel
+// (raytracer.go:656, vec.go:104-107): uint8(uint32(c*65535) >> 8), alpha 0xFF.
+template <typename R>
+__global__ void __launch_bounds__(256) k_pixels(DevScene<R> sc, const R* samples, int sample_cap, uchar4* frame, int y0, int rows) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= rows * sc.W) return;
+    R c[3];
+    for (int k = 0; k < 3; k++) {
+        const R* s = samples + (size_t)k * sample_cap + 4 * p;
+        R tot = R(0);
+        tot = tot + s[0]; tot = tot + s[1]; tot = tot + s[2]; tot = tot + s[3];
+        c[k] = tot * R(0.25);
+    }
+    uchar4 px;
+    px.x = (unsigned char)((unsigned)(c[0] * R(65535)) >> 8);
+    px.y = (unsigned char)((unsigned)(c[1] * R(65535)) >> 8);
+    px.z = (unsigned char)((unsigned)(c[2] * R(65535)) >> 8);
+    px.w = 0xFF;
+    frame[(size_t)y0 * sc.W + p] = px;
+}
+
+// ------------------------------------------------------------------ host side: one renderer per device
+#define CU_TRY(expr)                                                                                   \
+    do {                                                                                               \
+        cudaError_t e_ = (expr);                                                                       \
+        if (e_ != cudaSuccess) {                                                                       \
+            err = std::string(#expr) + ": " + cudaGetErrorString(e_);                                  \
+            return e_ == cudaErrorMemoryAllocation ? GMLRT_E_OOM : GMLRT_E_CUDA;                       \
+        }                                                                                              \
+    } while (0)
+
+inline size_t env_size(const char* name, size_t dflt) {
+    const char* v = std::getenv(name);
+    return (v && *v) ? (size_t)std::strtoull(v, nullptr, 10) : dflt;
+}
+
+template <typename R>
+class Renderer : public IRenderer {
+public:
+    explicit Renderer(int device) : dev_(device) {}
+    ~Renderer() override { release(); }
+
+    int device() const override { return dev_; }
+    cudaStream_t stream() override { return stream_; }
+    uint8_t* frame() override { return reinterpret_cast<uint8_t*>(frame_); }
+    int32_t* primary_ids() override { return ids_; }
+    int max_rows_per_tile() const override { return rows_per_tile_; }
+
+    int init(std::string& err) {
+        CU_TRY(cudaSetDevice(dev_));
+        CU_TRY(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
+        cudaDeviceProp prop;
+        CU_TRY(cudaGetDeviceProperties(&prop, dev_));
+        sms_ = prop.multiProcessorCount;
+        // PCG jump table: J_k advances the 128-bit LCG by k steps (affine map powers)
+        gomath::PcgJump tab[160];
+        unsigned __int128 m = 1, inc = 0;
+        const unsigned __int128 MUL = ((unsigned __int128)gomath::PCG_MUL_HI << 64) | gomath::PCG_MUL_LO;
+        const unsigned __int128 INC = ((unsigned __int128)gomath::PCG_INC_HI << 64) | gomath::PCG_INC_LO;
+        for (int k = 0; k < 160; k++) {
+            tab[k].mh = (uint64_t)(m >> 64); tab[k].ml = (uint64_t)m;
+            tab[k].ih = (uint64_t)(inc >> 64); tab[k].il = (uint64_t)inc;
+            m = m * MUL; inc = inc * MUL + INC;
+        }
+        CU_TRY(cudaMemcpyToSymbol(c_pcg_jump, tab, sizeof tab));
+        CU_TRY(cudaMalloc(&ctr_, sizeof(Counters)));
+        CU_TRY(cudaMemset(ctr_, 0, sizeof(Counters)));
+        CU_TRY(cudaFuncSetAttribute(k_closest<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU_TRY(cudaFuncSetAttribute(k_shadow<R, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU_TRY(cudaFuncSetAttribute(k_shadow<R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        return GMLRT_OK;
+    }
+
+    void reset_totals() override { totals_ = TraceTotals(); need_ctr_reset_ = true; }
+
+    int fetch_totals(TraceTotals& out, std::string& err) override {
+        CU_TRY(cudaSetDevice(dev_));
+        Counters c;
+        CU_TRY(cudaMemcpy(&c, ctr_, sizeof c, cudaMemcpyDeviceToHost));
+        out = totals_;
+        out.rays_reflect = c.rays_reflect; out.rays_refract = c.rays_refract;
+        out.rays_shadow = c.rays_shadow; out.shadow_occluded = c.shadow_occluded;
+        for (int k = 0; k < K_COUNT; k++) out.shadow_tests[k] = c.shadow_tests[k];
+        out.error = c.error;
+        return GMLRT_OK;
+    }
+
+    int upload(const HostScene& S, std::string& err) override;
+    int trace_rows(int y0, int y1, bool counting, std::string& err) override;
+
+private:
+    template <typename T> int to_device(const std::vector<T>& v, T** out, std::string& err) {
+        *out = nullptr;
+        size_t bytes = std::max<size_t>(v.size() * sizeof(T), 256);
+        void* p = nullptr;
+        CU_TRY(cudaMalloc(&p, bytes));
+        scene_allocs_.push_back(p);
+        if (!v.empty()) CU_TRY(cudaMemcpyAsync(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, stream_));
+        *out = reinterpret_cast<T*>(p);
+        return GMLRT_OK;
+    }
+    void free_scene() {
+        for (void* p : scene_allocs_) cudaFree(p);
+        scene_allocs_.clear();
+    }
+    void free_tiles() {
+        if (pool_) cudaFree(pool_);
+        pool_ = nullptr; pool_bytes_ = 0;
+    }
+    void release() {
+        cudaSetDevice(dev_);
+        free_scene(); free_tiles();
+        if (frame_) cudaFree(frame_);
+        if (ids_) cudaFree(ids_);
+        if (ctr_) cudaFree(ctr_);
+        if (stream_) cudaStreamDestroy(stream_);
+        frame_ = nullptr; ids_ = nullptr; ctr_ = nullptr; stream_ = nullptr;
+    }
+    int plan_tiles(const HostScene& S, std::string& err);
+
+    int dev_, sms_ = 148;
+    cudaStream_t stream_ = nullptr;
+    DevScene<R> sc_{};
+    std::vector<void*> scene_allocs_;
+    // tile buffers
+    void* pool_ = nullptr; size_t pool_bytes_ = 0;
+    std::vector<Level<R>> levels_;
+    std::vector<unsigned char*> occl_;
+    ShadowQueue<R> sq_{};
+    R* samples_ = nullptr; int sample_cap_ = 0;
+    int rows_per_tile_ = 0, depth_eff_ = 1;
+    uchar4* frame_ = nullptr; size_t frame_px_ = 0;
+    int32_t* ids_ = nullptr; size_t ids_n_ = 0;
+    Counters* ctr_ = nullptr;
+    TraceTotals totals_;
+    bool need_ctr_reset_ = true;
+    // scan kernel configuration
+    int chunk_leaves_ = 1, resident_ = 1; size_t scan_smem_ = 0;
+    int grid_closest_ = 148, grid_shadow_ = 148, grid_shadow_cnt_ = 148;
+    std::vector<int> kind_host_;
+};
+
+template <typename R>
+int Renderer<R>::upload(const HostScene& S, std::string& err) {
+    CU_TRY(cudaSetDevice(dev_));
+    if (!S.csg.empty()) { err = "intersect/difference objects are not supported by this build"; return GMLRT_E_UNSUPPORTED; }
+    if (S.depth > GMLRT_MAX_DEPTH) { err = "recursion depth above GMLRT_MAX_DEPTH"; return GMLRT_E_UNSUPPORTED; }
+    CU_TRY(cudaStreamSynchronize(stream_));
+    free_scene();
+    const int n = S.n_plain;
+    if (n >= (1 << 28)) { err = "too many leaves"; return GMLRT_E_UNSUPPORTED; }
+    // device order: stable sort by kind, so that equal kinds keep scan order
+    std::vector<int> order(n);
+    for (int i = 0; i < n; i++) order[i] = i;
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return S.leaves[a].kind < S.leaves[b].kind; });
+    std::vector<R> w2o((size_t)n * 12), o2w((size_t)n * 12), fn((size_t)n * 18);
+    std::vector<int> scan_of(n), surface(n), kind(n);
+    DevScene<R> sc{};
+    sc.n_leaves = n;
+    for (int k = 0; k <= K_COUNT; k++) sc.kind_begin[k] = 0;
+    for (int d = 0; d < n; d++) {
+        const HostLeaf& L = S.leaves[order[d]];
+        for (int k = 0; k < 12; k++) { w2o[(size_t)d * 12 + k] = (R)L.w2o[k]; o2w[(size_t)d * 12 + k] = (R)L.o2w[k]; }
+        for (int f = 0; f < 6; f++) for (int k = 0; k < 3; k++) fn[(size_t)d * 18 + 3 * f + k] = (R)L.face_normal[f][k];
+        scan_of[d] = L.scan_index; surface[d] = (int)L.surface; kind[d] = L.kind;
+        sc.kind_begin[L.kind + 1]++;
+    }
+    for (int k = 0; k < K_COUNT; k++) sc.kind_begin[k + 1] += sc.kind_begin[k];
+    kind_host_ = kind;
+    std::vector<DevLight<R>> lights(S.lights.size());
+    for (size_t i = 0; i < S.lights.size(); i++) {
+        const gmlrt_light& l = S.lights[i];
+        DevLight<R>& d = lights[i];
+        d.kind = (int)l.kind;
+        for (int k = 0; k < 3; k++) { d.pos[k] = (R)l.pos[k]; d.color[k] = (R)l.color[k]; d.axis[k] = R(0); }
+        d.cos_cutoff = R(0); d.exponent = (R)l.exponent;
+        if (l.kind == GMLRT_LIGHT_SPOT) {            // EXTENSION
+            double a[3] = {l.at[0] - l.pos[0], l.at[1] - l.pos[1], l.at[2] - l.pos[2]};
+            normalize3(a);
+            for (int k = 0; k < 3; k++) d.axis[k] = (R)a[k];
+            d.cos_cutoff = (R)gomath::go_cos(l.cutoff * GM_PI / 180.0);
+        }
+    }
+    std::vector<DevSurface<R>> surfaces(S.surfaces.size());
+    for (size_t i = 0; i < S.surfaces.size(); i++) {
+        const gmlrt_surface& s = S.surfaces[i];
+        surfaces[i].kind = (int)s.kind; surfaces[i].code_off = (int)s.code_off;
+        surfaces[i].code_len = (int)s.code_len; surfaces[i].n_regs = (int)s.n_regs;
+        for (int k = 0; k < 10; k++) surfaces[i].material[k] = (R)s.material[k];
+    }
+    std::vector<R> fpool(S.fpool.size());
+    for (size_t i = 0; i < S.fpool.size(); i++) fpool[i] = (R)S.fpool[i];
+    int rc;
+    R *d_w2o, *d_o2w, *d_fn, *d_fpool; int *d_scan, *d_surf, *d_kind, *d_itab; uint32_t* d_code;
+    DevLight<R>* d_lights; DevSurface<R>* d_surfaces;
+    if ((rc = to_device(w2o, &d_w2o, err)) || (rc = to_device(o2w, &d_o2w, err)) || (rc = to_device(fn, &d_fn, err)) ||
+        (rc = to_device(scan_of, &d_scan, err)) || (rc = to_device(surface, &d_surf, err)) || (rc = to_device(kind, &d_kind, err)) ||
+        (rc = to_device(lights, &d_lights, err)) || (rc = to_device(surfaces, &d_surfaces, err)) ||
+        (rc = to_device(fpool, &d_fpool, err)) || (rc = to_device(S.itab, &d_itab, err)) || (rc = to_device(S.code, &d_code, err)))
+        return rc;
+    sc.w2o = d_w2o; sc.o2w = d_o2w; sc.fnormal = d_fn; sc.scan_of = d_scan; sc.surface = d_surf; sc.kind = d_kind;
+    sc.n_lights = (int)lights.size(); sc.lights = d_lights; sc.surfaces = d_surfaces;
+    sc.fpool = d_fpool; sc.itab = d_itab; sc.code = d_code;
+    sc.n_fpool = (int)fpool.size(); sc.n_itab = (int)S.itab.size();
+    sc.W = S.width; sc.H = S.height; sc.depth = S.depth; sc.vw = S.vw; sc.vh = S.vh;
+    for (int k = 0; k < 3; k++) { sc.ambient[k] = (R)S.h.ambient[k]; sc.bg0[k] = (R)S.h.bg_start[k]; sc.bg1[k] = (R)S.h.bg_end[k]; }
+    sc_ = sc;
+    CU_TRY(cudaStreamSynchronize(stream_));      // host vectors go out of scope
+
+    // frame + ids
+    const size_t px = (size_t)S.width * S.height;
+    if (px != frame_px_) {
+        if (frame_) cudaFree(frame_);
+        frame_ = nullptr; frame_px_ = 0;
+        CU_TRY(cudaMalloc(&frame_, px * sizeof(uchar4)));
+        frame_px_ = px;
+    }
+    return plan_tiles(S, err);
+}
+
+template <typename R>
+int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
+    const int W = S.width, H = S.height, nl = (int)S.lights.size();
+    depth_eff_ = (S.any_reflect || S.any_refract) ? S.depth : 1;   // no material can spawn a child ray
+    std::vector<double> mult(depth_eff_);
+    double sum_mult = 0, max_mult = 0;
+    for (int l = 0; l < depth_eff_; l++) {
+        mult[l] = S.may_branch ? std::ldexp(1.0, std::min(l, 30)) : 1.0;     // binary ray tree only when a material asks for it
+        sum_mult += mult[l]; max_mult = std::max(max_mult, mult[l]);
+    }
+    const double node_bytes = (6 + 1 + NREC + 6) * sizeof(R) + 8 + nl;
+    const double shadow_bytes = nl * (8.0 * sizeof(R) + 8);
+    const double per_sample = sum_mult * node_bytes + max_mult * shadow_bytes + 3 * sizeof(R);
+    size_t free_b = 0, total_b = 0;
+    CU_TRY(cudaMemGetInfo(&free_b, &total_b));
+    free_b += pool_bytes_;
+    double budget = std::min((double)free_b * 0.6, (double)env_size("GMLRT_POOL_MB", 24 * 1024) * 1048576.0);
+    double max_samples = std::min(budget / per_sample, (double)env_size("GMLRT_TILE_SAMPLES", 16u << 20));
+    max_samples = std::min(max_samples, 2.0e9 / (max_mult * std::max(nl, 1)));       // int32 indexing of node*n_lights
+    int rows = (int)std::min<double>(H, std::floor(max_samples / (4.0 * W)));
+    if (rows < 1) { err = "image row does not fit the device queue budget"; return GMLRT_E_OOM; }
+    rows_per_tile_ = rows;
+    const size_t S0 = (size_t)rows * W * 4;
+    // carve one pool
+    auto align = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off = align(off + bytes); return o; };
+    struct LvOff { size_t ray, parent, hit, t, rec, child, occl; size_t cap; };
+    std::vector<LvOff> lo(depth_eff_);
+    size_t max_cap = 0;
+    for (int l = 0; l < depth_eff_; l++) {
+        size_t cap = (size_t)std::min((double)S0 * mult[l], 2.0e9);
+        lo[l].cap = cap; max_cap = std::max(max_cap, cap);
+        lo[l].ray = take(6 * cap * sizeof(R)); lo[l].parent = take(cap * 4); lo[l].hit = take(cap * 4);
+        lo[l].t = take(cap * sizeof(R)); lo[l].rec = take(NREC * cap * sizeof(R)); lo[l].child = take(6 * cap * sizeof(R));
+        lo[l].occl = take(cap * std::max(nl, 1));
+    }
+    const size_t sq_cap = max_cap * std::max(nl, 1);
+    size_t o_sq = take(8 * sq_cap * sizeof(R)), o_skip = take(sq_cap * 4), o_tgt = take(sq_cap * 4);
+    size_t o_samples = take(3 * S0 * sizeof(R));
+    if (off > pool_bytes_) {
+        free_tiles();
+        CU_TRY(cudaMalloc(&pool_, off));
+        pool_bytes_ = off;
+    }
+    char* base = reinterpret_cast<char*>(pool_);
+    levels_.assign(depth_eff_, Level<R>{});
+    occl_.assign(depth_eff_, nullptr);
+    for (int l = 0; l < depth_eff_; l++) {
+        Level<R>& L = levels_[l];
+        L.cap = (int)lo[l].cap;
+        L.ray = (R*)(base + lo[l].ray); L.parent = (int*)(base + lo[l].parent); L.hit = (int*)(base + lo[l].hit);
+        L.t = (R*)(base + lo[l].t); L.rec = (R*)(base + lo[l].rec); L.child = (R*)(base + lo[l].child);
+        occl_[l] = (unsigned char*)(base + lo[l].occl);
+    }
+    sq_.q = (R*)(base + o_sq); sq_.skip = (int*)(base + o_skip); sq_.target = (int*)(base + o_tgt); sq_.cap = (int)sq_cap;
+    samples_ = (R*)(base + o_samples); sample_cap_ = (int)S0;
+
+    // scan kernels: resident scene when it fits, else two streaming buffers
+    const size_t leaf_bytes = 12 * sizeof(R);
+    const size_t resident_max = env_size("GMLRT_RESIDENT_KB", 64) * 1024;
+    const size_t chunk_bytes = env_size("GMLRT_CHUNK_KB", 32) * 1024;
+    const size_t all = std::max<size_t>((size_t)sc_.n_leaves * leaf_bytes, 16);
+    if (all <= resident_max) { resident_ = 1; chunk_leaves_ = std::max(sc_.n_leaves, 1); scan_smem_ = all; }
+    else { resident_ = 0; chunk_leaves_ = (int)(chunk_bytes / leaf_bytes); scan_smem_ = 2 * (size_t)chunk_leaves_ * leaf_bytes; }
+    int occ = 1;
+    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_closest<R>, SCAN_THREADS, scan_smem_));
+    grid_closest_ = sms_ * std::max(occ, 1);
+    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shadow<R, false>, SCAN_THREADS, scan_smem_));
+    grid_shadow_ = sms_ * std::max(occ, 1);
+    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shadow<R, true>, SCAN_THREADS, scan_smem_));
+    grid_shadow_cnt_ = sms_ * std::max(occ, 1);
+    return GMLRT_OK;
+}
+
+template <typename R>
+int Renderer<R>::trace_rows(int y0, int y1, bool counting, std::string& err) {
+    CU_TRY(cudaSetDevice(dev_));
+    const int W = sc_.W;
+    if (need_ctr_reset_) { CU_TRY(cudaMemsetAsync(ctr_, 0, sizeof(Counters), stream_)); need_ctr_reset_ = false; }
+    if (counting && ids_n_ != (size_t)W * sc_.H * 4) {
+        if (ids_) cudaFree(ids_);
+        ids_ = nullptr; ids_n_ = 0;
+        CU_TRY(cudaMalloc(&ids_, (size_t)W * sc_.H * 4 * sizeof(int32_t)));
+        ids_n_ = (size_t)W * sc_.H * 4;
+    }
+    const int wide = sms_ * 16;
+    for (int ty = y0; ty < y1; ty += rows_per_tile_) {
+        const int rows = std::min(rows_per_tile_, y1 - ty);
+        const int S = rows * W * 4;
+        k_gen<R><<<(S + 255) / 256, 256, 0, stream_>>>(sc_, levels_[0], ctr_, ty, rows);
+        totals_.launches++;
+        totals_.rays_primary += (unsigned long long)S;
+        for (int l = 0; l < depth_eff_; l++) {
+            const int cap_blocks = (levels_[l].cap + SHADE_THREADS - 1) / SHADE_THREADS;
+            k_closest<R><<<grid_closest_, SCAN_THREADS, scan_smem_, stream_>>>(sc_, levels_[l], ctr_, l, chunk_leaves_, resident_);
+            const bool spawn = l + 1 < depth_eff_;
+            k_shade<R><<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
+                sc_, levels_[l], spawn ? levels_[l + 1] : levels_[l], sq_, occl_[l], ctr_, l, spawn ? 1 : 0,
+                (counting && l == 0) ? ids_ : nullptr, ty);
+            totals_.launches += 2;
+            if (sc_.n_lights > 0) {
+                if (counting) k_shadow<R, true><<<grid_shadow_cnt_, SCAN_THREADS, scan_smem_, stream_>>>(sc_, sq_, occl_[l], ctr_, chunk_leaves_, resident_);
+                else k_shadow<R, false><<<grid_shadow_, SCAN_THREADS, scan_smem_, stream_>>>(sc_, sq_, occl_[l], ctr_, chunk_leaves_, resident_);
+                CU_TRY(cudaMemsetAsync(&ctr_->shadow_count, 0, sizeof(int), stream_));
+                totals_.launches++;
+            }
+        }
+        for (int l = depth_eff_ - 1; l >= 0; l--) {
+            const int cap_blocks = (levels_[l].cap + SHADE_THREADS - 1) / SHADE_THREADS;
+            k_resolve<R><<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
+                sc_, levels_[l], l > 0 ? levels_[l - 1] : levels_[l], occl_[l], ctr_, l, samples_, sample_cap_);
+            totals_.launches++;
+        }
+        k_pixels<R><<<(rows * W + 255) / 256, 256, 0, stream_>>>(sc_, samples_, sample_cap_, frame_, ty, rows);
+        totals_.launches++;
+    }
+    CU_TRY(cudaGetLastError());
+    return GMLRT_OK;
+}
+
+}  // namespace gmlrt

@@ -1,0 +1,41 @@
+// renderer.h - precision-independent interface between the C ABI (gmlrt_api.cu) and the two
+// instantiations of the wavefront tracer (render_f32.cu / render_f64.cu).  One object per device.
+#pragma once
+#include <cstdint>
+#include <string>
+
+#include <cuda_runtime.h>
+
+#include "../../include/gmlrt.h"
+#include "host_scene.h"
+
+namespace gmlrt {
+
+struct TraceTotals {                   // summed over the tiles a device rendered
+    unsigned long long rays_primary = 0, rays_reflect = 0, rays_refract = 0, rays_shadow = 0, shadow_occluded = 0;
+    unsigned long long shadow_tests[K_COUNT] = {0, 0, 0, 0, 0};
+    unsigned long long launches = 0;
+    int error = 0;
+};
+
+class IRenderer {
+public:
+    virtual ~IRenderer() {}
+    // copy the converted scene to this device; (re)allocate queues for rows_per_tile rows
+    virtual int upload(const HostScene& S, std::string& err) = 0;
+    // enqueue the kernels for image rows [y0, y1) on this device's stream (no host sync)
+    virtual int trace_rows(int y0, int y1, bool counting, std::string& err) = 0;
+    // after the stream is synchronised: fetch counters accumulated since reset_totals()
+    virtual int fetch_totals(TraceTotals& out, std::string& err) = 0;
+    virtual void reset_totals() = 0;
+    virtual uint8_t* frame() = 0;          // device RGBA8 frame, full size (only own rows valid)
+    virtual int32_t* primary_ids() = 0;    // device [H][W][4] scan-order ids (counting mode), may be null
+    virtual cudaStream_t stream() = 0;
+    virtual int device() const = 0;
+    virtual int max_rows_per_tile() const = 0;
+};
+
+IRenderer* make_renderer_f32(int device);
+IRenderer* make_renderer_f64(int device);
+
+}  // namespace gmlrt

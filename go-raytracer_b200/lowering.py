@@ -50,7 +50,7 @@ def lower(args, state=None):
             if res[0] == "const":
                 rec = (0, 0, 0, 0, res[1])
             else:
-                rec = (1, res[1], res[2], res[3], (0.0,) * 10)
+                rec = (1, res[1], res[2], res[3], res[4])
         surface_index[key] = len(surfaces)
         surfaces.append(rec)
         return surface_index[key]

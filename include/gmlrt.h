@@ -105,7 +105,8 @@ typedef struct gmlrt_surface {
     uint32_t code_off;      /* in uint32 words from off_code */
     uint32_t code_len;
     uint32_t n_regs;        /* registers the bytecode uses (<= GMLRT_VM_MAX_REGS) */
-    double   material[10];
+    double   material[10];  /* CODE: components the host proved constant, NaN where computed per hit
+                               (lets the renderer see e.g. Transparency == 0 and size its queues) */
 } gmlrt_surface;            /* 96 bytes */
 
 /* ------------------------------------------------------------------ surface bytecode
