@@ -33,6 +33,10 @@
 #include "host_scene.h"
 #include "renderer.h"
 
+#ifndef GMLRT_PARITY_TU
+#define GMLRT_PARITY_TU 0   // render_f64.cu defines it to 1 (and is built with -fmad=false)
+#endif
+
 namespace gmlrt {
 
 using gomath::gm;
@@ -48,6 +52,7 @@ template <typename R> struct DevScene {
     int kind_begin[K_COUNT + 1];
     const R* w2o;                  // [n][12] rows 0..2 of WorldToObject           (hot: staged in smem)
     const int* scan_of;            // device index -> scan-order index (tie-breaks, ids)
+    const double* w2o64;           // [n][12] the same matrices in double, for the robust primary-ray tests (f32 mode)
     const R* o2w;                  // [n][12]
     const R* fnormal;              // [n][18] world normals of plane / cube faces
     const int* surface;            // [n]
@@ -70,6 +75,7 @@ template <typename R> struct Level {
     R* t;         // [cap]
     R* rec;       // [NREC][cap]
     R* child;     // [6][cap] colour returned by the reflection / refraction child
+    double* ray64; // [6][cap] level 0 in f32 mode only: the camera ray before rounding to float
     int cap;
 };
 
@@ -143,10 +149,11 @@ template <typename R> __device__ __forceinline__ bool hit_plane(const Ray<R>& r,
 // coordinate of the face's own plane, which is 0 or 1 only up to rounding: in float64 that test
 // randomly rejects ~1.5% of cube.gml's pixels and parity mode reproduces it bit for
 // bit.  In float32 with FMA the residual o + d*(num/den) is almost never exactly on the plane, so
-// throughput mode skips the own-axis test (AXIS) - a documented deviation.
+// throughput mode skips the own-axis test (AXIS) - a documented deviation - also in its
+// double-precision re-tests, which are built with FMA contraction like the rest of that unit.
 template <typename R, int AXIS>
 __device__ __forceinline__ void cube_face(const Ray<R>& r, R num, R den, int f, R& best, int& bf) {
-    constexpr bool strict = std::is_same<R, double>::value;
+    constexpr bool strict = GMLRT_PARITY_TU != 0;   // only the -fmad=false translation unit can honour the own-axis test
     if (gm<R>::abs(den) < R(1e-6)) return;
     R t = num / den;
     if (t <= R(0)) return;
@@ -264,18 +271,61 @@ __device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem
 // ------------------------------------------------------------------ closest-hit scan of one staged chunk
 // Leaves [base, base+cnt) of the device-ordered array are in `sm`.  Keeps the reference's
 // tie rule: strictly smaller T wins, equal T keeps the object that comes first in scan order.
-template <typename R, int KIND>
+// Robust primary-ray test (throughput mode only).  The north_star asks for ZERO hit/miss flips on
+// primary rays against the float64 reference.  A float32 sphere test is trusted unless its
+// discriminant is inside the rounding band |disc| < 2^-17 (hb^2 + |a c|) or the origin is that
+// close to the surface; then - and for the non-quadric kinds always - the test is redone in
+// double from the unrounded camera ray and the double matrices (a few tests per million).
+template <int KIND>
+__device__ __noinline__ bool hit_kind_f64(const double* w2o64, int i, const Ray<double>& w, float& t, int& face) {
+    Ray<double> o;
+    to_object(w2o64 + (size_t)i * 12, w, o);
+    double td = 0.0;
+    const bool h = hit_kind<double, KIND>(o, td, face);
+    t = (float)td;
+    return h;
+}
+
+template <typename R, int KIND, bool ROBUST>
 __device__ __forceinline__ void closest_kind(const DevScene<R>& sc, const R* sm, int base, int cnt, const Ray<R>& w,
-                                             R& best_t, int& best_i, int& best_face) {
+                                             const Ray<double>& w64, R& best_t, int& best_i, int& best_face) {
     int lo = max(sc.kind_begin[KIND], base), hi = min(sc.kind_begin[KIND + 1], base + cnt);
 #pragma unroll 2
     for (int i = lo; i < hi; i++) {
-        Mat34<R> M;
-        load_mat(sm, i - base, M);
-        Ray<R> o;
-        to_object(M.m, w, o);
-        R t; int face;
-        if (hit_kind<R, KIND>(o, t, face)) {
+        R t; int face; bool h;
+        if constexpr (ROBUST && KIND != K_SPHERE) {
+            float tf;
+            h = hit_kind_f64<KIND>(sc.w2o64, i, w64, tf, face);
+            t = (R)tf;
+        } else {
+            Mat34<R> M;
+            load_mat(sm, i - base, M);
+            Ray<R> o;
+            to_object(M.m, w, o);
+            if constexpr (ROBUST) {
+                const R a = o.dx * o.dx + o.dy * o.dy + o.dz * o.dz;
+                const R hb = o.ox * o.dx + o.oy * o.dy + o.oz * o.dz;
+                const R oo = o.ox * o.ox + o.oy * o.oy + o.oz * o.oz;
+                const R c = oo - R(1);
+                const R p = a * c;
+                const R disc = hb * hb - p;
+                const R band = R(7.62939453125e-6) * (hb * hb + gm<R>::abs(p));     // 2^-17
+                if (gm<R>::abs(disc) < band || gm<R>::abs(c) < R(7.62939453125e-6) * (oo + R(1))) {
+                    float tf;
+                    h = hit_kind_f64<K_SPHERE>(sc.w2o64, i, w64, tf, face);
+                    t = (R)tf;
+                } else {
+                    h = false;
+                    if (disc >= R(0)) {
+                        const R t0 = (-hb - gm<R>::sqrt(disc)) / a;
+                        if (t0 > R(0)) { t = t0; face = 0; h = true; }
+                    }
+                }
+            } else {
+                h = hit_kind<R, KIND>(o, t, face);
+            }
+        }
+        if (h) {
             if (best_i < 0 || t < best_t || (t == best_t && sc.scan_of[i] < sc.scan_of[best_i])) {
                 best_t = t; best_i = i; best_face = face;
             }
@@ -283,14 +333,14 @@ __device__ __forceinline__ void closest_kind(const DevScene<R>& sc, const R* sm,
     }
 }
 
-template <typename R>
+template <typename R, bool ROBUST>
 __device__ __forceinline__ void closest_chunk(const DevScene<R>& sc, const R* sm, int base, int cnt, const Ray<R>& w,
-                                              R& best_t, int& best_i, int& best_face) {
-    closest_kind<R, K_SPHERE>(sc, sm, base, cnt, w, best_t, best_i, best_face);
-    closest_kind<R, K_CUBE>(sc, sm, base, cnt, w, best_t, best_i, best_face);
-    closest_kind<R, K_CYLINDER>(sc, sm, base, cnt, w, best_t, best_i, best_face);
-    closest_kind<R, K_CONE>(sc, sm, base, cnt, w, best_t, best_i, best_face);
-    closest_kind<R, K_PLANE>(sc, sm, base, cnt, w, best_t, best_i, best_face);
+                                              const Ray<double>& w64, R& best_t, int& best_i, int& best_face) {
+    closest_kind<R, K_SPHERE, ROBUST>(sc, sm, base, cnt, w, w64, best_t, best_i, best_face);
+    closest_kind<R, K_CUBE, ROBUST>(sc, sm, base, cnt, w, w64, best_t, best_i, best_face);
+    closest_kind<R, K_CYLINDER, ROBUST>(sc, sm, base, cnt, w, w64, best_t, best_i, best_face);
+    closest_kind<R, K_CONE, ROBUST>(sc, sm, base, cnt, w, w64, best_t, best_i, best_face);
+    closest_kind<R, K_PLANE, ROBUST>(sc, sm, base, cnt, w, w64, best_t, best_i, best_face);
 }
 
 // any-hit scan: inShadow's test  shadowHit.T * |ray.Direction| < distToLight  (raytracer.go:424)
@@ -328,7 +378,7 @@ __device__ __forceinline__ void stage_chunk(const DevScene<R>& sc, int c, int ch
 // closestHit for one recursion level (raytracer.go:469-483).  Persistent CTAs; the scene is
 // staged once per CTA when it fits one buffer ("resident"), else streamed through two
 // buffers per block of rays.
-template <typename R>
+template <typename R, bool ROBUST>
 __global__ void __launch_bounds__(SCAN_THREADS) k_closest(DevScene<R> sc, Level<R> lv, const Counters* ctr, int level,
                                                           int chunk_leaves, int resident) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -356,9 +406,15 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_closest(DevScene<R> sc, Level<
             w.ox = lv.ray[i]; w.oy = lv.ray[cap + i]; w.oz = lv.ray[2 * cap + i];
             w.dx = lv.ray[3 * cap + i]; w.dy = lv.ray[4 * cap + i]; w.dz = lv.ray[5 * cap + i];
         }
+        Ray<double> w64 = {0.0, 0.0, 0.0, 0.0, 0.0, 1.0};
+        if (ROBUST && active) {
+            const int cap = lv.cap;
+            w64.ox = lv.ray64[i]; w64.oy = lv.ray64[cap + i]; w64.oz = lv.ray64[2 * cap + i];
+            w64.dx = lv.ray64[3 * cap + i]; w64.dy = lv.ray64[4 * cap + i]; w64.dz = lv.ray64[5 * cap + i];
+        }
         R best_t = R(0); int best_i = -1, best_face = 0;
         if (resident) {
-            closest_chunk(sc, buf[0], 0, N, w, best_t, best_i, best_face);
+            closest_chunk<R, ROBUST>(sc, buf[0], 0, N, w, w64, best_t, best_i, best_face);
         } else {
             if (tid == 0) {
                 stage_chunk(sc, 0, chunk_leaves, buf[0], &bar[0]);
@@ -369,7 +425,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_closest(DevScene<R> sc, Level<
                 mbar_wait(&bar[b], phase[b]);
                 phase[b] ^= 1;
                 const int base = c * chunk_leaves;
-                closest_chunk(sc, buf[b], base, min(chunk_leaves, N - base), w, best_t, best_i, best_face);
+                closest_chunk<R, ROBUST>(sc, buf[b], base, min(chunk_leaves, N - base), w, w64, best_t, best_i, best_face);
                 __syncthreads();                       // everyone is done reading buf[b]
                 if (tid == 0 && c + 2 < nchunks) stage_chunk(sc, c + 2, chunk_leaves, buf[b], &bar[b]);
             }
@@ -629,6 +685,10 @@ __global__ void __launch_bounds__(256) k_gen(DevScene<R> sc, Level<R> lv, Counte
     const int cap = lv.cap;
     lv.ray[i] = (R)ox; lv.ray[cap + i] = (R)oy; lv.ray[2 * cap + i] = (R)oz;
     lv.ray[3 * cap + i] = (R)(ex / m); lv.ray[4 * cap + i] = (R)(ey / m); lv.ray[5 * cap + i] = (R)(ez / m);
+    if (lv.ray64) {
+        lv.ray64[i] = ox; lv.ray64[cap + i] = oy; lv.ray64[2 * cap + i] = oz;
+        lv.ray64[3 * cap + i] = ex / m; lv.ray64[4 * cap + i] = ey / m; lv.ray64[5 * cap + i] = ez / m;
+    }
 }
 
 // ------------------------------------------------------------------ shade (traceRay :498-556 minus the recursion)
@@ -673,7 +733,9 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
             if (sf.kind != GMLRT_SURFACE_CONST) {
                 if (gm<R>::abs(p.y) > R(1)) ok = false;
                 v = (p.y + R(1)) / R(2);
-                u = gm<R>::acos(p.z / gm<R>::sqrt(R(1) - p.y * p.y)) / (R(2) * R(GM_PI));
+                R ca = p.z / gm<R>::sqrt(R(1) - p.y * p.y);
+                if (!GMLRT_PARITY_TU) ca = fminf(fmaxf((float)ca, -1.0f), 1.0f);   // float rounding can leave |ca| = 1 + ulp on the x = 0 meridian
+                u = gm<R>::acos(ca) / (R(2) * R(GM_PI));
             }
             N = p;                                                                   // :119 (sic: object-space point)
         } else if (kind == K_PLANE) {                                                // :182-205
@@ -918,11 +980,14 @@ public:
         CU_TRY(cudaMemcpyToSymbol(c_pcg_jump, tab, sizeof tab));
         CU_TRY(cudaMalloc(&ctr_, sizeof(Counters)));
         CU_TRY(cudaMemset(ctr_, 0, sizeof(Counters)));
-        CU_TRY(cudaFuncSetAttribute(k_closest<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU_TRY(cudaFuncSetAttribute(k_closest<R, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        if (kRobustPrimary) CU_TRY(cudaFuncSetAttribute(k_closest<R, kRobustPrimary>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU_TRY(cudaFuncSetAttribute(k_shadow<R, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU_TRY(cudaFuncSetAttribute(k_shadow<R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         return GMLRT_OK;
     }
+
+    static constexpr bool kRobustPrimary = std::is_same<R, float>::value;   // f32: double re-test of borderline primary hits
 
     void reset_totals() override { totals_ = TraceTotals(); need_ctr_reset_ = true; }
 
@@ -989,7 +1054,7 @@ private:
     bool need_ctr_reset_ = true;
     // scan kernel configuration
     int chunk_leaves_ = 1, resident_ = 1; size_t scan_smem_ = 0;
-    int grid_closest_ = 148, grid_shadow_ = 148, grid_shadow_cnt_ = 148;
+    int grid_closest0_ = 148, grid_closest_ = 148, grid_shadow_ = 148, grid_shadow_cnt_ = 148;
     std::vector<int> kind_host_;
 };
 
@@ -1007,6 +1072,7 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     for (int i = 0; i < n; i++) order[i] = i;
     std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return S.leaves[a].kind < S.leaves[b].kind; });
     std::vector<R> w2o((size_t)n * 12), o2w((size_t)n * 12), fn((size_t)n * 18);
+    std::vector<double> w2o64(kRobustPrimary ? (size_t)n * 12 : 0);
     std::vector<int> scan_of(n), surface(n), kind(n);
     DevScene<R> sc{};
     sc.n_leaves = n;
@@ -1014,6 +1080,7 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     for (int d = 0; d < n; d++) {
         const HostLeaf& L = S.leaves[order[d]];
         for (int k = 0; k < 12; k++) { w2o[(size_t)d * 12 + k] = (R)L.w2o[k]; o2w[(size_t)d * 12 + k] = (R)L.o2w[k]; }
+        if (kRobustPrimary) for (int k = 0; k < 12; k++) w2o64[(size_t)d * 12 + k] = L.w2o[k];
         for (int f = 0; f < 6; f++) for (int k = 0; k < 3; k++) fn[(size_t)d * 18 + 3 * f + k] = (R)L.face_normal[f][k];
         scan_of[d] = L.scan_index; surface[d] = (int)L.surface; kind[d] = L.kind;
         sc.kind_begin[L.kind + 1]++;
@@ -1044,6 +1111,8 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     std::vector<R> fpool(S.fpool.size());
     for (size_t i = 0; i < S.fpool.size(); i++) fpool[i] = (R)S.fpool[i];
     int rc;
+    double* d_w2o64 = nullptr;
+    if ((rc = to_device(w2o64, &d_w2o64, err))) return rc;
     R *d_w2o, *d_o2w, *d_fn, *d_fpool; int *d_scan, *d_surf, *d_kind, *d_itab; uint32_t* d_code;
     DevLight<R>* d_lights; DevSurface<R>* d_surfaces;
     if ((rc = to_device(w2o, &d_w2o, err)) || (rc = to_device(o2w, &d_o2w, err)) || (rc = to_device(fn, &d_fn, err)) ||
@@ -1051,6 +1120,7 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
         (rc = to_device(lights, &d_lights, err)) || (rc = to_device(surfaces, &d_surfaces, err)) ||
         (rc = to_device(fpool, &d_fpool, err)) || (rc = to_device(S.itab, &d_itab, err)) || (rc = to_device(S.code, &d_code, err)))
         return rc;
+    sc.w2o64 = kRobustPrimary ? d_w2o64 : nullptr;
     sc.w2o = d_w2o; sc.o2w = d_o2w; sc.fnormal = d_fn; sc.scan_of = d_scan; sc.surface = d_surf; sc.kind = d_kind;
     sc.n_lights = (int)lights.size(); sc.lights = d_lights; sc.surfaces = d_surfaces;
     sc.fpool = d_fpool; sc.itab = d_itab; sc.code = d_code;
@@ -1083,7 +1153,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     }
     const double node_bytes = (6 + 1 + NREC + 6) * sizeof(R) + 8 + nl;
     const double shadow_bytes = nl * (8.0 * sizeof(R) + 8);
-    const double per_sample = sum_mult * node_bytes + max_mult * shadow_bytes + 3 * sizeof(R);
+    const double per_sample = sum_mult * node_bytes + max_mult * shadow_bytes + 3 * sizeof(R) + (kRobustPrimary ? 48 : 0);
     size_t free_b = 0, total_b = 0;
     CU_TRY(cudaMemGetInfo(&free_b, &total_b));
     free_b += pool_bytes_;
@@ -1111,6 +1181,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     const size_t sq_cap = max_cap * std::max(nl, 1);
     size_t o_sq = take(8 * sq_cap * sizeof(R)), o_skip = take(sq_cap * 4), o_tgt = take(sq_cap * 4);
     size_t o_samples = take(3 * S0 * sizeof(R));
+    size_t o_ray64 = kRobustPrimary ? take(6 * S0 * sizeof(double)) : 0;
     if (off > pool_bytes_) {
         free_tiles();
         CU_TRY(cudaMalloc(&pool_, off));
@@ -1125,6 +1196,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
         L.ray = (R*)(base + lo[l].ray); L.parent = (int*)(base + lo[l].parent); L.hit = (int*)(base + lo[l].hit);
         L.t = (R*)(base + lo[l].t); L.rec = (R*)(base + lo[l].rec); L.child = (R*)(base + lo[l].child);
         occl_[l] = (unsigned char*)(base + lo[l].occl);
+        L.ray64 = (kRobustPrimary && l == 0) ? (double*)(base + o_ray64) : nullptr;
     }
     sq_.q = (R*)(base + o_sq); sq_.skip = (int*)(base + o_skip); sq_.target = (int*)(base + o_tgt); sq_.cap = (int)sq_cap;
     samples_ = (R*)(base + o_samples); sample_cap_ = (int)S0;
@@ -1137,8 +1209,10 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     if (all <= resident_max) { resident_ = 1; chunk_leaves_ = std::max(sc_.n_leaves, 1); scan_smem_ = all; }
     else { resident_ = 0; chunk_leaves_ = (int)(chunk_bytes / leaf_bytes); scan_smem_ = 2 * (size_t)chunk_leaves_ * leaf_bytes; }
     int occ = 1;
-    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_closest<R>, SCAN_THREADS, scan_smem_));
+    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_closest<R, false>, SCAN_THREADS, scan_smem_));
     grid_closest_ = sms_ * std::max(occ, 1);
+    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_closest<R, kRobustPrimary>, SCAN_THREADS, scan_smem_));
+    grid_closest0_ = sms_ * std::max(occ, 1);
     CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shadow<R, false>, SCAN_THREADS, scan_smem_));
     grid_shadow_ = sms_ * std::max(occ, 1);
     CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shadow<R, true>, SCAN_THREADS, scan_smem_));
@@ -1166,7 +1240,10 @@ int Renderer<R>::trace_rows(int y0, int y1, bool counting, std::string& err) {
         totals_.rays_primary += (unsigned long long)S;
         for (int l = 0; l < depth_eff_; l++) {
             const int cap_blocks = (levels_[l].cap + SHADE_THREADS - 1) / SHADE_THREADS;
-            k_closest<R><<<grid_closest_, SCAN_THREADS, scan_smem_, stream_>>>(sc_, levels_[l], ctr_, l, chunk_leaves_, resident_);
+            if (l == 0 && kRobustPrimary)
+                k_closest<R, kRobustPrimary><<<grid_closest0_, SCAN_THREADS, scan_smem_, stream_>>>(sc_, levels_[l], ctr_, l, chunk_leaves_, resident_);
+            else
+                k_closest<R, false><<<grid_closest_, SCAN_THREADS, scan_smem_, stream_>>>(sc_, levels_[l], ctr_, l, chunk_leaves_, resident_);
             const bool spawn = l + 1 < depth_eff_;
             k_shade<R><<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
                 sc_, levels_[l], spawn ? levels_[l + 1] : levels_[l], sq_, occl_[l], ctr_, l, spawn ? 1 : 0,

@@ -55,29 +55,38 @@ def lower(args, state=None):
         surfaces.append(rec)
         return surface_index[key]
 
-    def add(obj):
-        kind = NODE_KIND.get(type(obj))
-        if kind is None:
-            raise LoweringError(f"unknown scene object type {type(obj).__name__}")
-        idx = len(nodes)
-        nodes.append(None)
-        if kind < 16:
-            if isinstance(obj, ev.Union):
-                if len(obj.objects) != 2:
-                    raise LoweringError("union nodes are binary")
-                a, b = obj.objects
+    def add(root_obj):
+        """Iterative (union chains of thousands of nodes are normal): node i is created when first
+        seen, its operand indices are patched in once the operands have been numbered."""
+        todo = [(root_obj, None, 0)]           # (object, parent node index, which operand)
+        root_idx = None
+        while todo:
+            obj, parent, slot = todo.pop()
+            kind = NODE_KIND.get(type(obj))
+            if kind is None:
+                raise LoweringError(f"unknown scene object type {type(obj).__name__}")
+            idx = len(nodes)
+            if parent is None:
+                root_idx = idx
             else:
-                a, b = obj.a, obj.b
-            ia = add(a)
-            ib = add(b)
-            nodes[idx] = (kind, ia, ib, 0, [0.0] * 12, [0.0] * 12)
-        else:
-            o2w = obj.transform_mat if obj.transform_mat is not None else prim.identity()
-            w2o = prim.inverse(o2w) if obj.transform_mat is not None else prim.identity()
-            if w2o is None:
-                raise LoweringError("singular transform (the reference dereferences nil here, vec.go:343-347)")
-            nodes[idx] = (kind, 0, 0, surface_of(obj.surface_fn), _rows(o2w), _rows(w2o))
-        return idx
+                nodes[parent][1 + slot] = idx
+            if kind < 16:
+                if isinstance(obj, ev.Union):
+                    if len(obj.objects) != 2:
+                        raise LoweringError("union nodes are binary")
+                    a, b = obj.objects
+                else:
+                    a, b = obj.a, obj.b
+                nodes.append([kind, 0, 0, 0, [0.0] * 12, [0.0] * 12])
+                todo.append((b, idx, 1))
+                todo.append((a, idx, 0))
+            else:
+                o2w = obj.transform_mat if obj.transform_mat is not None else prim.identity()
+                w2o = prim.inverse(o2w) if obj.transform_mat is not None else prim.identity()
+                if w2o is None:
+                    raise LoweringError("singular transform (the reference dereferences nil here, vec.go:343-347)")
+                nodes.append([kind, 0, 0, surface_of(obj.surface_fn), _rows(o2w), _rows(w2o)])
+        return root_idx
 
     root = add(args.Scene)
 

@@ -8,8 +8,6 @@ re-derives these, it receives them in the scene blob.
 """
 import math
 
-from .gml import gomath
-
 
 class Vec3:
     __slots__ = ("x", "y", "z")
@@ -142,18 +140,23 @@ def scale(x, y, z):
     return ((x, 0.0, 0.0, 0.0), (0.0, y, 0.0, 0.0), (0.0, 0.0, z, 0.0), (0.0, 0.0, 0.0, 1.0))
 
 
+def _cs(a):
+    from .gml import gomath   # late import: gml.evaluator imports this module
+    return gomath.cos(a), gomath.sin(a)
+
+
 def rotate_x(a):
-    c, s = gomath.cos(a), gomath.sin(a)
+    c, s = _cs(a)
     return ((1.0, 0.0, 0.0, 0.0), (0.0, c, -s, 0.0), (0.0, s, c, 0.0), (0.0, 0.0, 0.0, 1.0))
 
 
 def rotate_y(a):
-    c, s = gomath.cos(a), gomath.sin(a)
+    c, s = _cs(a)
     return ((c, 0.0, s, 0.0), (0.0, 1.0, 0.0, 0.0), (-s, 0.0, c, 0.0), (0.0, 0.0, 0.0, 1.0))
 
 
 def rotate_z(a):
-    c, s = gomath.cos(a), gomath.sin(a)
+    c, s = _cs(a)
     return ((c, -s, 0.0, 0.0), (s, c, 0.0, 0.0), (0.0, 0.0, 1.0, 0.0), (0.0, 0.0, 0.0, 1.0))
 
 
