@@ -1,0 +1,303 @@
+#!/usr/bin/env python
+"""bench.py - the reference's headline metric on BASELINE.json's config 2:
+Mrays/s (primary + shadow + reflect [+ refract] queries per second) and frame ms for the
+synthetic 1024-sphere reflective scene, 1 point + 1 directional light, depth 3, 3840x2160.
+
+    python bench.py --gpus N --steps K --warmup W          our arm (libgmlrt.so, sm_100a CUDA)
+    python bench.py --impl reference --steps K --warmup W   CPU arm: the float64 restatement of the
+                                                            reference's Go renderer (oracle/) on
+                                                            all host cores, on a bounded crop
+
+A "step" = one full frame of the hot path.  `value` times gmlrt_trace (scene resident in HBM,
+raster left in HBM); `e2e` times gmlrt_render (host blob in, host raster out).  For N > 1 the
+driver launches one process per GPU with torchrun; each rank renders every N-th row band of the
+same frame (scene replicated, strong scaling) and the bands are summed onto rank 0 with one NCCL
+reduce over NVLink (frames are zero outside a rank's own bands).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "Mrays/s (primary+shadow+reflect)"
+
+
+def build_blob(args):
+    from go_raytracer_b200 import scenes
+    if args.config == "spheres1024":
+        text = scenes.spheres_lattice(args.width, args.height, depth=args.depth)
+    elif args.config == "spheres1024p":
+        text = scenes.spheres_lattice(args.width, args.height, depth=args.depth, directional=False, name="spheres1024p")
+    elif args.config == "mixed4096":
+        text = scenes.mixed(args.width, args.height, depth=args.depth)
+    elif args.config == "proctex":
+        text = scenes.proctex(args.width, args.height, depth=args.depth)
+    elif args.config == "csg256":
+        text = scenes.csg(args.width, args.height, depth=args.depth)
+    else:
+        raise SystemExit(f"unknown config {args.config}")
+    return scenes.to_blob(text)
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        self.stop_flag = True
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        sm = sorted(float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(r[3 + k].lower().startswith("active") for r in self.rows if len(r) > 3 + k)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+def central_crop(w, h, cw, ch):
+    x0, y0 = (w - cw) // 2, (h - ch) // 2
+    y0 -= y0 % 20                      # keep whole PCG work items (20-row batches)
+    return (x0, y0, x0 + cw, y0 + ch)
+
+
+def run_reference(args, blob):
+    """CPU arm: oracle/ (float64 restatement of raytracer.go; the Go toolchain is absent so the Go
+    renderer itself is 'unavailable on this box') with every host core, bounded crop per step."""
+    import oracle
+    cores = os.cpu_count() or 8
+    crop = central_crop(args.width, args.height, args.ref_crop[0], args.ref_crop[1])
+    for _ in range(args.warmup):
+        oracle.render(blob, threads=cores, crop=crop)
+    rays, t0 = 0, time.perf_counter()
+    for _ in range(args.steps):
+        _, st = oracle.render(blob, threads=cores, crop=crop)
+        rays += st.rays_total
+    dt = time.perf_counter() - t0
+    value = rays / dt / 1e6
+    frame_px = args.width * args.height
+    crop_px = (crop[2] - crop[0]) * (crop[3] - crop[1])
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"{args.config} {args.width}x{args.height} depth {args.depth}, 4 spp"},
+        "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": "port",
+                         "sample": f"central {crop[2]-crop[0]}x{crop[3]-crop[1]} px crop of the frame, all 4 spp, per step"},
+        "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "frame_ms_extrapolated": dt / args.steps * 1e3 * frame_px / crop_px,
+        "note": "Go toolchain absent: the reference's own renderer is unavailable on this box; this is its float64 C restatement "
+                "(oracle/), which flatters it (no interface dispatch, no per-hit allocation, no GC)",
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="spheres1024")
+    ap.add_argument("--width", type=int, default=3840)
+    ap.add_argument("--height", type=int, default=2160)
+    ap.add_argument("--depth", type=int, default=None)
+    ap.add_argument("--precision", default="f32", choices=["f32", "f64"])
+    ap.add_argument("--ref-crop", type=int, nargs=2, default=[240, 140])
+    ap.add_argument("--cpu-crop", type=int, nargs=2, default=[480, 260])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.depth is None:
+        args.depth = {"mixed4096": 5, "proctex": 2, "csg256": 2}.get(args.config, 3)
+    if args.config == "mixed4096" and "--width" not in sys.argv:
+        args.width, args.height = 7680, 4320
+    args.warmup = max(args.warmup, 0)
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        if rank == 0:
+            run_reference(args, build_blob(args))
+        return
+
+    import numpy as np
+    import torch
+    from go_raytracer_b200 import cuda
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    blob = build_blob(args)
+    W, H = args.width, args.height
+    prec = cuda.PRECISION_F32 if args.precision == "f32" else cuda.PRECISION_F64_PARITY
+    ctx = cuda.Context((local_rank,), prec)
+    ctx.set_partition(rank, world)
+    ctx.upload(blob)
+    ext = torch.cuda.ExternalStream(ctx.stream, device=local_rank)
+
+    class _Frame:   # the library's device frame as a torch tensor (no copy)
+        __cuda_array_interface__ = {"shape": (H, W, 4), "typestr": "|u1", "data": (ctx.frame_device_ptr, False), "version": 2}
+    frame = torch.as_tensor(_Frame(), device=f"cuda:{local_rank}") if world > 1 else None
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    gathered = [None]
+
+    def step():
+        st = ctx.trace()
+        if dist is not None:
+            with torch.cuda.stream(ext):
+                buf = frame.clone()                                  # rank frames are zero outside their own bands
+                dist.reduce(buf, dst=0, op=dist.ReduceOp.SUM)        # => SUM gathers the disjoint bands onto rank 0
+                gathered[0] = buf
+        return st
+
+    # counting pass (untimed): ray classes and credited flops are deterministic per scene
+    ctx.set_counting(True)
+    cst = ctx.trace()
+    ctx.set_counting(False)
+    counts = torch.tensor([cst.rays_primary, cst.rays_reflect, cst.rays_refract, cst.rays_shadow, cst.shadow_occluded,
+                           cst.leaf_tests, int(cst.flops_credited / 1e3)], dtype=torch.int64, device=f"cuda:{local_rank}")
+    if dist is not None:
+        dist.all_reduce(counts)
+    rays_frame = int(counts[:4].sum())
+    flops_frame = float(counts[6]) * 1e3
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches, kernel_ms = 0, 0.0
+    with torch.cuda.stream(ext):
+        e0.record()
+    for _ in range(args.steps):
+        st = step()
+        launches += st.kernel_launches
+        kernel_ms += st.ms_kernels
+    with torch.cuda.stream(ext):
+        e1.record()
+    barrier()
+    clocks = sampler.summary()
+    ms_total = e0.elapsed_time(e1)
+    t = torch.tensor([ms_total, kernel_ms, float(launches)], dtype=torch.float64, device=f"cuda:{local_rank}")
+    if dist is not None:
+        tmax = t.clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = t.clone()
+        dist.all_reduce(tsum)
+        ms_total, kernel_ms, launches = float(tmax[0]), float(tmax[1]), int(tsum[2])
+    ms_step = ms_total / args.steps
+    value = rays_frame / (ms_step * 1e-3) / 1e6
+
+    # end to end through the public C ABI: host blob in, host raster out, every step
+    host = np.empty((H, W, 4), dtype=np.uint8)
+    pinned = torch.empty((H, W, 4), dtype=torch.uint8, pin_memory=True) if rank == 0 else None
+
+    def e2e_step():
+        ctx.upload(blob)                                    # H2D of this step's input
+        step()
+        if rank == 0:                                       # D2H of the step's result
+            if dist is None:
+                ctx.download(pinned.numpy())
+            else:
+                with torch.cuda.stream(ext):
+                    pinned.copy_(gathered[0], non_blocking=True)
+                ext.synchronize()
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    e2e_steps = max(3, min(args.steps, 10))
+    for _ in range(e2e_steps):
+        e2e_step()
+    barrier()
+    e2e_ms = (time.perf_counter() - t0) / e2e_steps * 1e3
+    if dist is not None:
+        tt = torch.tensor([e2e_ms], dtype=torch.float64, device=f"cuda:{local_rank}")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e_ms = float(tt[0])
+    e2e_value = rays_frame / (e2e_ms * 1e-3) / 1e6
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    props = torch.cuda.get_device_properties(local_rank)
+    sm_max_mhz = float(peaks.get("sm_max_mhz") or clocks.get("sm_max_mhz") or 1965.0)
+    fp32_peak = props.multi_processor_count * 128 * 2 * sm_max_mhz * 1e6 / 1e12 * world     # TFLOP/s, derived (no measured FP32 figure)
+    achieved = flops_frame / (kernel_ms / args.steps * 1e-3) / 1e12
+    line = {
+        "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_step, "frame_ms": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": args.precision, "data": "synthetic",
+        "config": {"workload": f"{args.config} {W}x{H} depth {args.depth}, 4 spp, {cst.n_leaves} leaves", "precision": args.precision,
+                   "l2": "inputs larger than L2: the per-level ray queues of one frame are GBs, no flush needed",
+                   "parallelism": f"row bands over {world} GPU(s), scene replicated, NCCL reduce of disjoint bands to rank 0" if world > 1 else "1 GPU"},
+        "rays_per_frame": {"primary": int(counts[0]), "reflect": int(counts[1]), "refract": int(counts[2]), "shadow": int(counts[3]),
+                           "shadow_occluded": int(counts[4])},
+        "gpu_launches": launches,
+        "clocks": clocks,
+        "e2e": {"value": e2e_value, "unit": "Mrays/s", "frame_ms": e2e_ms, "h2d_bytes_per_step": len(blob), "d2h_bytes_per_step": W * H * 4},
+        "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak,
+                     "traffic": None,
+                     "note": "credited flops per SURVEY 8(d) (sphere 56, plane 47, cube 81, cylinder 74, cone 70 per ray x leaf test; "
+                             "closest-hit queries test every leaf, shadow queries up to their first occluder) over the trace kernels' "
+                             f"CUDA-event time; peak derived = SMs x 128 x 2 x {sm_max_mhz:.0f} MHz (MEASURED_PEAKS.json has no FP32 figure)",
+                     "flops_per_frame": flops_frame, "leaf_tests_per_frame": int(counts[5])},
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        import oracle
+        cores = os.cpu_count() or 8
+        crop = central_crop(W, H, args.cpu_crop[0], args.cpu_crop[1])
+        t0 = time.perf_counter()
+        _, ost = oracle.render(blob, threads=cores, crop=crop)
+        dt = time.perf_counter() - t0
+        line["cpu_baseline"] = {"value": ost.rays_total / dt / 1e6, "unit": "Mrays/s", "cores": cores, "kind": "port",
+                                "sample": f"central {crop[2]-crop[0]}x{crop[3]-crop[1]} px crop of the same frame, all 4 spp, {dt:.1f} s",
+                                "note": "float64 C restatement of the reference (oracle/); the Go renderer is unavailable on this box"}
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

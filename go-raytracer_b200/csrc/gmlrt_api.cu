@@ -32,6 +32,7 @@ struct gmlrt_ctx {
     cudaEvent_t ev_a = nullptr, ev_b = nullptr;
     std::vector<cudaEvent_t> ev_done;                        // per device: its bands are in device 0's frame
     int band_rows = 0;
+    int part = 0, n_parts = 1;                               // multi-process sharding: this context renders bands part, part+n_parts, ...
 };
 
 static thread_local std::string g_last_error = "";
@@ -138,13 +139,29 @@ int gmlrt_upload(gmlrt_ctx* c, const void* blob, size_t blob_bytes) {
         min_rows = std::min(min_rows, r->max_rows_per_tile());
     }
     // band height: whole tiles on one device; with several devices at least ~8 bands each (tail balance)
-    const int nd = (int)c->r.size();
+    const int nd = (int)c->r.size() * c->n_parts;
     int rows = min_rows;
     if (nd > 1) rows = std::max(1, std::min(rows, (c->scene.height + 8 * nd - 1) / (8 * nd)));
     c->band_rows = rows;
+    if (c->n_parts > 1) {   // rows owned by other processes stay zero, so the rank frames can be summed
+        for (auto& r : c->r) {
+            API_CU(cudaSetDevice(r->device()));
+            API_CU(cudaMemsetAsync(r->frame(), 0, (size_t)c->scene.width * c->scene.height * 4, r->stream()));
+        }
+    }
     c->have_scene = true;
     return GMLRT_OK;
 }
+
+int gmlrt_set_partition(gmlrt_ctx* c, int part, int n_parts) {
+    if (!c) return fail(nullptr, GMLRT_E_BAD_ARG, "ctx is null");
+    if (n_parts < 1 || part < 0 || part >= n_parts) return fail(c, GMLRT_E_BAD_ARG, "need 0 <= part < n_parts");
+    c->part = part; c->n_parts = n_parts;
+    c->have_scene = false;      // band height depends on the partition: upload again
+    return GMLRT_OK;
+}
+
+void* gmlrt_frame_device(gmlrt_ctx* c) { return c && !c->r.empty() ? (void*)c->r[0]->frame() : nullptr; }
 
 int gmlrt_trace(gmlrt_ctx* c, gmlrt_stats* stats) {
     if (!c) return fail(nullptr, GMLRT_E_BAD_ARG, "ctx is null");
@@ -161,7 +178,8 @@ int gmlrt_trace(gmlrt_ctx* c, gmlrt_stats* stats) {
     int band = 0;
     for (int y0 = 0; y0 < H; y0 += c->band_rows, band++) {
         const int y1 = std::min(H, y0 + c->band_rows);
-        const int di = band % nd;
+        if (band % c->n_parts != c->part) continue;
+        const int di = (band / c->n_parts) % nd;
         IRenderer* r = c->r[di].get();
         int rc = r->trace_rows(y0, y1, c->counting, err);
         if (rc != GMLRT_OK) return fail(c, rc, err);

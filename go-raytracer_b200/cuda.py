@@ -39,7 +39,7 @@ class GmlrtError(RuntimeError):
         self.code = code
 
 
-EXPORTS = ("gmlrt_create", "gmlrt_render", "gmlrt_upload", "gmlrt_trace", "gmlrt_download", "gmlrt_set_counting",
+EXPORTS = ("gmlrt_set_partition", "gmlrt_frame_device", "gmlrt_create", "gmlrt_render", "gmlrt_upload", "gmlrt_trace", "gmlrt_download", "gmlrt_set_counting",
            "gmlrt_primary_hits", "gmlrt_stream", "gmlrt_last_error", "gmlrt_destroy", "gmlrt_blob_version", "gmlrt_build_info")
 
 _lib = None
@@ -62,6 +62,8 @@ def load():
         L.gmlrt_set_counting.restype, L.gmlrt_set_counting.argtypes = i, [p, i]
         L.gmlrt_primary_hits.restype, L.gmlrt_primary_hits.argtypes = i, [p, p, sz]
         L.gmlrt_stream.restype, L.gmlrt_stream.argtypes = p, [p]
+        L.gmlrt_set_partition.restype, L.gmlrt_set_partition.argtypes = i, [p, i, i]
+        L.gmlrt_frame_device.restype, L.gmlrt_frame_device.argtypes = p, [p]
         L.gmlrt_last_error.restype, L.gmlrt_last_error.argtypes = ctypes.c_char_p, [p]
         L.gmlrt_destroy.restype, L.gmlrt_destroy.argtypes = None, [p]
         L.gmlrt_blob_version.restype, L.gmlrt_blob_version.argtypes = i, []
@@ -136,6 +138,13 @@ class Context:
         ids = np.empty((h, w, 4), dtype=np.int32)
         self._check(self._L.gmlrt_primary_hits(self._h, ids.ctypes.data, ids.size))
         return ids
+
+    def set_partition(self, part, n_parts):
+        self._check(self._L.gmlrt_set_partition(self._h, part, n_parts))
+
+    @property
+    def frame_device_ptr(self):
+        return self._L.gmlrt_frame_device(self._h)
 
     @property
     def stream(self):

@@ -206,6 +206,16 @@ int gmlrt_upload(gmlrt_ctx*, const void* blob, size_t blob_bytes);
 int gmlrt_trace(gmlrt_ctx*, gmlrt_stats* stats /* nullable */);
 int gmlrt_download(gmlrt_ctx*, uint8_t* rgba, size_t rgba_bytes);
 
+/* Multi-process sharding (one process per GPU, e.g. under torchrun): this context renders only the
+ * row bands  part, part + n_parts, ...  of the frame and leaves the other rows zero, so that the
+ * per-process frames can be summed / gathered by the caller (NCCL, or peer copies).  Call before
+ * gmlrt_upload.  The default (0, 1) renders the whole frame.                                     */
+int gmlrt_set_partition(gmlrt_ctx*, int part, int n_parts);
+
+/* Device pointer of the RGBA8 frame on devices[0] (valid after gmlrt_upload), for callers that
+ * keep the raster on the GPU.                                                                    */
+void* gmlrt_frame_device(gmlrt_ctx*);
+
 /* Enable (1) / disable (0) the counting kernels that fill the ray and flop fields of
  * gmlrt_stats; counting costs a few percent, so timed runs leave it off.              */
 int gmlrt_set_counting(gmlrt_ctx*, int enabled);
