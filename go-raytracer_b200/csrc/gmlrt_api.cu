@@ -212,7 +212,7 @@ int gmlrt_trace(gmlrt_ctx* c, gmlrt_stats* stats) {
         if (rc != GMLRT_OK) return fail(c, rc, err);
         sum.rays_primary += t.rays_primary; sum.rays_reflect += t.rays_reflect; sum.rays_refract += t.rays_refract;
         sum.rays_shadow += t.rays_shadow; sum.shadow_occluded += t.shadow_occluded; sum.launches += t.launches;
-        for (int k = 0; k < K_COUNT; k++) sum.shadow_tests[k] += t.shadow_tests[k];
+        sum.shadow_tests += t.shadow_tests; sum.shadow_flops += t.shadow_flops; sum.exact_tests += t.exact_tests;
         sum.error |= t.error;
     }
     if (stats) {
@@ -228,10 +228,11 @@ int gmlrt_trace(gmlrt_ctx* c, gmlrt_stats* stats) {
         const unsigned long long closest = sum.rays_primary + sum.rays_reflect + sum.rays_refract;
         stats->leaf_tests = closest * nleaf;
         stats->flops_credited = (double)closest * all;
-        for (int k = 0; k < K_COUNT; k++) {
-            stats->leaf_tests += sum.shadow_tests[k];
-            stats->flops_credited += (double)sum.shadow_tests[k] * kFlopsByKind[k];
-        }
+        stats->leaf_tests += sum.shadow_tests;
+        stats->flops_credited += (double)sum.shadow_flops;
+        // executed work: every query runs the 7-FFMA cull test against every object, the exact test only on survivors
+        stats->cull_tests = (closest + sum.rays_shadow) * nleaf;
+        stats->exact_tests = sum.exact_tests;
     }
     if (sum.error) return fail(c, GMLRT_E_SURFACE, "a surface function faulted at render time (the reference panics here, raytracer.go:499-501)");
     return GMLRT_OK;

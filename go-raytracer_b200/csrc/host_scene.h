@@ -65,6 +65,40 @@ inline void normalize3(double* v) {
     v[0] /= m; v[1] /= m; v[2] /= m;
 }
 
+// largest eigenvalue of the symmetric 3x3 matrix {a00,a01,a02,a11,a12,a22} (trigonometric closed form)
+inline double sym3_max_eig(const double* a) {
+    const double a00 = a[0], a01 = a[1], a02 = a[2], a11 = a[3], a12 = a[4], a22 = a[5];
+    const double p1 = a01 * a01 + a02 * a02 + a12 * a12;
+    if (p1 == 0.0) return std::fmax(a00, std::fmax(a11, a22));
+    const double q = (a00 + a11 + a22) / 3.0;
+    const double p2 = (a00 - q) * (a00 - q) + (a11 - q) * (a11 - q) + (a22 - q) * (a22 - q) + 2.0 * p1;
+    const double p = std::sqrt(p2 / 6.0);
+    const double b00 = (a00 - q) / p, b11 = (a11 - q) / p, b22 = (a22 - q) / p, b01 = a01 / p, b02 = a02 / p, b12 = a12 / p;
+    double r = (b00 * (b11 * b22 - b12 * b12) - b01 * (b01 * b22 - b12 * b02) + b02 * (b01 * b12 - b11 * b02)) / 2.0;
+    r = r < -1.0 ? -1.0 : (r > 1.0 ? 1.0 : r);
+    return q + 2.0 * p * std::cos(std::acos(r) / 3.0);
+}
+
+// World-space bounding sphere of a leaf, for the cull phase of the scan kernels (render_impl.cuh):
+// the object-space solid's enclosing sphere mapped through ObjectToWorld, radius scaled by the
+// largest singular value of its linear part.  Planes are unbounded (radius = +inf).
+inline void leaf_bound(int kind, const double* o2w, double* C, double& Rw) {
+    static const double c0[K_COUNT][3] = {{0, 0, 0}, {0.5, 0.5, 0.5}, {0, 0.5, 0}, {0, 1, 0}, {0, 0, 0}};
+    static const double r0[K_COUNT] = {1.0, 0.8660254037844387 /* sqrt(3)/2 */, 1.118033988749895 /* sqrt(5)/2 */, 1.0, 0.0};
+    const double* c = c0[kind];
+    for (int r = 0; r < 3; r++) C[r] = o2w[4 * r] * c[0] + o2w[4 * r + 1] * c[1] + o2w[4 * r + 2] * c[2] + o2w[4 * r + 3];
+    if (kind == K_PLANE) { C[0] = C[1] = C[2] = 0.0; Rw = INFINITY; return; }
+    double ata[6] = {0, 0, 0, 0, 0, 0};
+    int k = 0;
+    for (int i = 0; i < 3; i++) for (int j = i; j < 3; j++, k++)
+        for (int r = 0; r < 3; r++) ata[k] += o2w[4 * r + i] * o2w[4 * r + j];
+    const double frob = std::sqrt(ata[0] + ata[3] + ata[5]);                   // always >= sigma_max
+    double smax = std::sqrt(std::fmax(sym3_max_eig(ata), 0.0)) * (1.0 + 1e-9);
+    if (!(smax <= frob)) smax = frob;                                          // NaN or closed-form trouble: fall back to the safe bound
+    Rw = r0[kind] * (smax > 0.0 ? smax : frob) * (1.0 + 1e-9);
+    if (!(Rw == Rw)) Rw = INFINITY;
+}
+
 static const double kCubeNormals[6][3] = {{0, 0, -1}, {0, 0, 1}, {-1, 0, 0}, {1, 0, 0}, {0, 1, 0}, {0, -1, 0}};
 
 inline void init_leaf(HostLeaf& L, const gmlrt_node& n, uint32_t node_index) {

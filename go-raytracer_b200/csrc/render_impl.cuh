@@ -50,7 +50,11 @@ template <typename R> struct DevSurface { int kind, code_off, code_len, n_regs; 
 template <typename R> struct DevScene {
     int n_leaves;                  // plain objects, device order (sorted by kind)
     int kind_begin[K_COUNT + 1];
-    const R* w2o;                  // [n][12] rows 0..2 of WorldToObject           (hot: staged in smem)
+    int n_cull;                    // n_leaves rounded up to a multiple of GROUP
+    const R* cull;                 // [n_cull][4] bounding sphere centre xyz, K = |C|^2 - R^2 - margin   (hot: staged in smem)
+    const unsigned long long* cum_flops;   // [n] credited flops of scan-order objects 0..s
+    int flops_of_kind[K_COUNT];
+    const R* w2o;                  // [n][12] rows 0..2 of WorldToObject
     const int* scan_of;            // device index -> scan-order index (tie-breaks, ids)
     const double* w2o64;           // [n][12] the same matrices in double, for the robust primary-ray tests (f32 mode)
     const R* o2w;                  // [n][12]
@@ -91,7 +95,8 @@ struct Counters {                  // device-resident, zeroed per trace
     int shadow_count;
     int error;
     unsigned long long rays_reflect, rays_refract, rays_shadow, shadow_occluded;
-    unsigned long long shadow_tests[K_COUNT];
+    unsigned long long shadow_tests, shadow_flops;   // credited: the reference's scan up to its first occluder (counting mode)
+    unsigned long long exact_tests;                  // executed second-phase tests (counting mode)
 };
 
 template <typename R> struct Ray { R ox, oy, oz, dx, dy, dz; };
@@ -268,250 +273,363 @@ __device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem
                  ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
-// ------------------------------------------------------------------ closest-hit scan of one staged chunk
-// Leaves [base, base+cnt) of the device-ordered array are in `sm`.  Keeps the reference's
-// tie rule: strictly smaller T wins, equal T keeps the object that comes first in scan order.
+// ------------------------------------------------------------------ two-phase scan: cull, then exact test
+// closestHit / inShadow visit every object for every ray (raytracer.go:469-483, 411-429).  The scan
+// kernels keep that all-pairs structure (no hierarchy), but split each ray x object test in two:
+//
+//   cull   7 FFMA + 1 compare against the object's bounding sphere, from a 16-byte (f32) record in
+//          shared memory:  reject iff |C-o|^2 - ((C-o).d^)^2 > R^2  (+ a rounding margin, so a reject
+//          is always a true miss).  Expanded so that everything per-ray is hoisted:
+//              A = C.(-2o) + K          K = |C|^2 - R^2 - margin|C|^2   (per object)
+//              B = C.d^ - o.d^
+//              reject  <=>  A - B^2 > -|o|^2 + margin|o|^2
+//   exact  the reference's own test (<Type>.Intersect) - only for the survivors, which each ray
+//          collects as (group, 16-bit mask) entries in a private shared-memory list and processes
+//          every FLUSH_GROUPS groups, so that lanes run their exact tests side by side instead of
+//          one lane at a time.
+//
+// Each thread carries RPT rays so that the record load and the loop overhead are shared.
+constexpr int SCAN_THREADS = 256;
+constexpr int RPT = 2;                      // rays per thread
+constexpr int GROUP = 16;                   // objects per survivor bitmask
+constexpr int FLUSH_GROUPS = 8;             // groups between two exact-test flushes = list capacity per ray
+constexpr int RAYS_PER_BLOCK = SCAN_THREADS * RPT;
+constexpr size_t LIST_BYTES = (size_t)FLUSH_GROUPS * RAYS_PER_BLOCK * sizeof(uint32_t);
+
+__device__ __forceinline__ float fma_(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+__device__ __forceinline__ double fma_(double a, double b, double c) { return __fma_rn(a, b, c); }
+
+template <typename R> struct CullMargin;
+template <> struct CullMargin<float> { static constexpr double rel = 7.62939453125e-6;  /* 2^-17 */ static constexpr double radius = 9.765625e-4; /* 2^-10 */ };
+template <> struct CullMargin<double> { static constexpr double rel = 5.6843418860808015e-14; /* 2^-44 */ static constexpr double radius = 9.313225746154785e-10; /* 2^-30 */ };
+
+template <typename R> struct Cull4 { R x, y, z, k; };
+__device__ __forceinline__ Cull4<float> load_cull(const float* sm, int i) {
+    const float4 v = reinterpret_cast<const float4*>(sm)[i];
+    Cull4<float> c = {v.x, v.y, v.z, v.w};
+    return c;
+}
+__device__ __forceinline__ Cull4<double> load_cull(const double* sm, int i) {
+    const double2 a = reinterpret_cast<const double2*>(sm)[2 * i], b = reinterpret_cast<const double2*>(sm)[2 * i + 1];
+    Cull4<double> c = {a.x, a.y, b.x, b.y};
+    return c;
+}
+
+template <typename R> struct CullRay { R o2x, o2y, o2z, dx, dy, dz, nod, cmp; };
+
+template <typename R> __device__ __forceinline__ void make_cull_ray(const Ray<R>& w, bool active, CullRay<R>& c) {
+    const R inv = R(1) / gm<R>::sqrt(fma_(w.dx, w.dx, fma_(w.dy, w.dy, w.dz * w.dz)));
+    c.dx = w.dx * inv; c.dy = w.dy * inv; c.dz = w.dz * inv;
+    c.o2x = R(-2) * w.ox; c.o2y = R(-2) * w.oy; c.o2z = R(-2) * w.oz;
+    c.nod = -fma_(w.ox, c.dx, fma_(w.oy, c.dy, w.oz * c.dz));
+    const R oo = fma_(w.ox, w.ox, fma_(w.oy, w.oy, w.oz * w.oz));
+    c.cmp = active ? fma_(oo, R(CullMargin<R>::rel), -oo) : -gm<R>::inf();    // inactive: everything is rejected
+}
+
+// objects [g0, g1) * GROUP of the staged table `sm` (whose first record is object sm_base); survivors of
+// ray r go to list[slot][r * SCAN_THREADS + tid] as  (global group index) << 16 | mask
+template <typename R>
+__device__ __forceinline__ void cull_groups(const R* sm, int sm_base, int g0, int g1, const CullRay<R> (&cr)[RPT],
+                                            uint32_t* list, int (&cnt)[RPT]) {
+    for (int g = g0; g < g1; g++) {
+        uint32_t m[RPT];
+#pragma unroll
+        for (int r = 0; r < RPT; r++) m[r] = 0;
+#pragma unroll
+        for (int j = 0; j < GROUP; j++) {
+            const Cull4<R> L = load_cull(sm, g * GROUP + j - sm_base);
+#pragma unroll
+            for (int r = 0; r < RPT; r++) {
+                const R A = fma_(L.x, cr[r].o2x, fma_(L.y, cr[r].o2y, fma_(L.z, cr[r].o2z, L.k)));
+                const R B = fma_(L.x, cr[r].dx, fma_(L.y, cr[r].dy, fma_(L.z, cr[r].dz, cr[r].nod)));
+                const R f = fma_(-B, B, A);
+                if (!(f > cr[r].cmp)) m[r] |= 1u << j;          // NaN survives
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < RPT; r++)
+            if (m[r]) { list[cnt[r] * RAYS_PER_BLOCK + r * SCAN_THREADS + threadIdx.x] = ((uint32_t)g << 16) | m[r]; cnt[r]++; }
+    }
+}
+
+template <typename R> __device__ __forceinline__ void load_w2o(const R* w2o, int i, Mat34<R>& M) { load_mat(w2o, i, M); }   // global, same layout
+
+__device__ __forceinline__ int kind_of(const int* kind_begin, int i) {
+    return (i >= kind_begin[1]) + (i >= kind_begin[2]) + (i >= kind_begin[3]) + (i >= kind_begin[4]);
+}
+
+template <typename R> __device__ __forceinline__ bool hit_any_kind(int kind, const Ray<R>& o, R& t, int& face) {
+    switch (kind) {
+    case K_SPHERE: return hit_sphere(o, t, face);
+    case K_CUBE: return hit_cube(o, t, face);
+    case K_CYLINDER: return hit_cylinder(o, t, face);
+    case K_CONE: return hit_cone(o, t, face);
+    default: return hit_plane(o, t, face);
+    }
+}
+
 // Robust primary-ray test (throughput mode only).  The north_star asks for ZERO hit/miss flips on
 // primary rays against the float64 reference.  A float32 sphere test is trusted unless its
 // discriminant is inside the rounding band |disc| < 2^-17 (hb^2 + |a c|) or the origin is that
 // close to the surface; then - and for the non-quadric kinds always - the test is redone in
-// double from the unrounded camera ray and the double matrices (a few tests per million).
-template <int KIND>
-__device__ __noinline__ bool hit_kind_f64(const double* w2o64, int i, const Ray<double>& w, float& t, int& face) {
-    Ray<double> o;
+// double from the unrounded camera ray and the double matrices.
+static __device__ __noinline__ bool hit_f64(const double* w2o64, int kind, int i, const double* ray64, int cap, int ri, float& t, int& face) {
+    Ray<double> w, o;
+    w.ox = ray64[ri]; w.oy = ray64[cap + ri]; w.oz = ray64[2 * (size_t)cap + ri];
+    w.dx = ray64[3 * (size_t)cap + ri]; w.dy = ray64[4 * (size_t)cap + ri]; w.dz = ray64[5 * (size_t)cap + ri];
     to_object(w2o64 + (size_t)i * 12, w, o);
     double td = 0.0;
-    const bool h = hit_kind<double, KIND>(o, td, face);
+    const bool h = hit_any_kind<double>(kind, o, td, face);
     t = (float)td;
     return h;
 }
 
-template <typename R, int KIND, bool ROBUST>
-__device__ __forceinline__ void closest_kind(const DevScene<R>& sc, const R* sm, int base, int cnt, const Ray<R>& w,
-                                             const Ray<double>& w64, R& best_t, int& best_i, int& best_face) {
-    int lo = max(sc.kind_begin[KIND], base), hi = min(sc.kind_begin[KIND + 1], base + cnt);
-#pragma unroll 2
-    for (int i = lo; i < hi; i++) {
-        R t; int face; bool h;
-        if constexpr (ROBUST && KIND != K_SPHERE) {
-            float tf;
-            h = hit_kind_f64<KIND>(sc.w2o64, i, w64, tf, face);
-            t = (R)tf;
-        } else {
-            Mat34<R> M;
-            load_mat(sm, i - base, M);
-            Ray<R> o;
-            to_object(M.m, w, o);
-            if constexpr (ROBUST) {
-                const R a = o.dx * o.dx + o.dy * o.dy + o.dz * o.dz;
-                const R hb = o.ox * o.dx + o.oy * o.dy + o.oz * o.dz;
-                const R oo = o.ox * o.ox + o.oy * o.oy + o.oz * o.oz;
-                const R c = oo - R(1);
-                const R p = a * c;
-                const R disc = hb * hb - p;
-                const R band = R(7.62939453125e-6) * (hb * hb + gm<R>::abs(p));     // 2^-17
-                if (gm<R>::abs(disc) < band || gm<R>::abs(c) < R(7.62939453125e-6) * (oo + R(1))) {
-                    float tf;
-                    h = hit_kind_f64<K_SPHERE>(sc.w2o64, i, w64, tf, face);
-                    t = (R)tf;
-                } else {
-                    h = false;
-                    if (disc >= R(0)) {
-                        const R t0 = (-hb - gm<R>::sqrt(disc)) / a;
-                        if (t0 > R(0)) { t = t0; face = 0; h = true; }
+// the exact test of ray `w` against object i, exactly as <Type>.Intersect would decide it
+template <typename R, bool ROBUST>
+__device__ __forceinline__ bool exact_hit(const DevScene<R>& sc, int i, const Ray<R>& w, const double* ray64, int cap, int ri, R& t, int& face) {
+    const int kind = kind_of(sc.kind_begin, i);
+    if constexpr (ROBUST) {
+        if (kind != K_SPHERE) { float tf; const bool h = hit_f64(sc.w2o64, kind, i, ray64, cap, ri, tf, face); t = (R)tf; return h; }
+    }
+    Mat34<R> M;
+    load_w2o(sc.w2o, i, M);
+    Ray<R> o;
+    to_object(M.m, w, o);
+    if constexpr (ROBUST) {
+        const R a = o.dx * o.dx + o.dy * o.dy + o.dz * o.dz;
+        const R hb = o.ox * o.dx + o.oy * o.dy + o.oz * o.dz;
+        const R oo = o.ox * o.ox + o.oy * o.oy + o.oz * o.oz;
+        const R c = oo - R(1);
+        const R p = a * c;
+        const R disc = hb * hb - p;
+        const R band = R(7.62939453125e-6) * (hb * hb + gm<R>::abs(p));     // 2^-17
+        if (gm<R>::abs(disc) < band || gm<R>::abs(c) < R(7.62939453125e-6) * (oo + R(1))) {
+            float tf; const bool h = hit_f64(sc.w2o64, K_SPHERE, i, ray64, cap, ri, tf, face); t = (R)tf; return h;
+        }
+        if (disc >= R(0)) {
+            const R t0 = (-hb - gm<R>::sqrt(disc)) / a;
+            if (t0 > R(0)) { t = t0; face = 0; return true; }
+        }
+        return false;
+    } else {
+        return hit_any_kind<R>(kind, o, t, face);
+    }
+}
+
+// Stage `cnt` cull records starting at object `base` into `dst` (one thread).
+template <typename R>
+__device__ __forceinline__ void stage_cull(const DevScene<R>& sc, int base, int cnt, R* dst, uint64_t* bar) {
+    const uint32_t bytes = (uint32_t)(cnt * 4 * sizeof(R));
+    mbar_expect_tx(bar, bytes);
+    tma_load_1d(dst, sc.cull + (size_t)base * 4, bytes, bar);
+}
+
+// Shared skeleton of the two scan kernels: persistent CTAs over blocks of RAYS_PER_BLOCK rays; the
+// cull table is staged once per CTA when it fits ("resident"), else streamed through two buffers
+// per block of rays.  `Visit` supplies setup(r, ray index) / exact(r, object) / finish(r).
+template <typename R, typename Visit>
+__device__ __forceinline__ void scan_rays(const DevScene<R>& sc, int n, int chunk_objs, int resident, Visit& V) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ __align__(8) uint64_t bar[2];
+    uint32_t* list = reinterpret_cast<uint32_t*>(smem_raw);
+    R* const tab = reinterpret_cast<R*>(smem_raw + LIST_BYTES);        // buffer b starts at tab + b * chunk_objs * 4
+    const int nblocks = (n + RAYS_PER_BLOCK - 1) / RAYS_PER_BLOCK;
+    if ((int)blockIdx.x >= nblocks) return;
+    const int tid = threadIdx.x;
+    const int NP = sc.n_cull;                                  // padded to a multiple of GROUP
+    const int nchunks = (NP + chunk_objs - 1) / chunk_objs;
+    if (tid == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_fence_init(); }
+    __syncthreads();
+    uint32_t phase[2] = {0, 0};
+    if (resident && NP > 0) {
+        if (tid == 0) stage_cull(sc, 0, NP, tab, &bar[0]);
+        mbar_wait(&bar[0], 0);
+    }
+    for (int blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
+        CullRay<R> cr[RPT];
+        int cnt[RPT];
+#pragma unroll
+        for (int r = 0; r < RPT; r++) {
+            const int ri = blk * RAYS_PER_BLOCK + r * SCAN_THREADS + tid;
+            Ray<R> w = {R(0), R(0), R(0), R(0), R(0), R(1)};
+            const bool active = V.setup(r, ri, ri < n, w);
+            make_cull_ray(w, active, cr[r]);
+            cnt[r] = 0;
+        }
+        auto flush = [&]() {
+#pragma unroll
+            for (int r = 0; r < RPT; r++) {
+                const int c = V.active[r] ? cnt[r] : 0;
+                for (int s = 0; s < c; s++) {
+                    const uint32_t e = list[s * RAYS_PER_BLOCK + r * SCAN_THREADS + tid];
+                    uint32_t m = e & 0xffffu;
+                    const int base = (int)(e >> 16) * GROUP;
+                    while (m) {
+                        const int j = __ffs(m) - 1;
+                        m &= m - 1;
+                        if (base + j < sc.n_leaves) V.exact(r, base + j);
                     }
                 }
-            } else {
-                h = hit_kind<R, KIND>(o, t, face);
+                cnt[r] = 0;
+                if (V.done(r)) cr[r].cmp = -gm<R>::inf();
             }
-        }
-        if (h) {
-            if (best_i < 0 || t < best_t || (t == best_t && sc.scan_of[i] < sc.scan_of[best_i])) {
-                best_t = t; best_i = i; best_face = face;
-            }
-        }
-    }
-}
-
-template <typename R, bool ROBUST>
-__device__ __forceinline__ void closest_chunk(const DevScene<R>& sc, const R* sm, int base, int cnt, const Ray<R>& w,
-                                              const Ray<double>& w64, R& best_t, int& best_i, int& best_face) {
-    closest_kind<R, K_SPHERE, ROBUST>(sc, sm, base, cnt, w, w64, best_t, best_i, best_face);
-    closest_kind<R, K_CUBE, ROBUST>(sc, sm, base, cnt, w, w64, best_t, best_i, best_face);
-    closest_kind<R, K_CYLINDER, ROBUST>(sc, sm, base, cnt, w, w64, best_t, best_i, best_face);
-    closest_kind<R, K_CONE, ROBUST>(sc, sm, base, cnt, w, w64, best_t, best_i, best_face);
-    closest_kind<R, K_PLANE, ROBUST>(sc, sm, base, cnt, w, w64, best_t, best_i, best_face);
-}
-
-// any-hit scan: inShadow's test  shadowHit.T * |ray.Direction| < distToLight  (raytracer.go:424)
-template <typename R, int KIND, bool COUNT>
-__device__ __forceinline__ void shadow_kind(const DevScene<R>& sc, const R* sm, int base, int cnt, const Ray<R>& w, R dist,
-                                            R in_len, int skip, bool& done, unsigned& tests) {
-    int lo = max(sc.kind_begin[KIND], base), hi = min(sc.kind_begin[KIND + 1], base + cnt);
-    for (int i = lo; i < hi; i++) {
-        if (__all_sync(0xffffffffu, done)) return;
-        if (!done) {
-            Mat34<R> M;
-            load_mat(sm, i - base, M);
-            Ray<R> o;
-            to_object(M.m, w, o);
-            R t; int face;
-            bool h = hit_kind<R, KIND>(o, t, face);
-            if (COUNT && i != skip) tests++;
-            if (h && i != skip && t * in_len < dist) done = true;
-        }
-    }
-}
-
-constexpr int SCAN_THREADS = 256;
-
-// Stage chunk c of the leaf matrices into `dst` (thread 0 only).
-template <typename R>
-__device__ __forceinline__ void stage_chunk(const DevScene<R>& sc, int c, int chunk_leaves, R* dst, uint64_t* bar) {
-    int base = c * chunk_leaves;
-    int cnt = min(chunk_leaves, sc.n_leaves - base);
-    uint32_t bytes = (uint32_t)(cnt * 12 * sizeof(R));
-    mbar_expect_tx(bar, bytes);
-    tma_load_1d(dst, sc.w2o + (size_t)base * 12, bytes, bar);
-}
-
-// closestHit for one recursion level (raytracer.go:469-483).  Persistent CTAs; the scene is
-// staged once per CTA when it fits one buffer ("resident"), else streamed through two
-// buffers per block of rays.
-template <typename R, bool ROBUST>
-__global__ void __launch_bounds__(SCAN_THREADS) k_closest(DevScene<R> sc, Level<R> lv, const Counters* ctr, int level,
-                                                          int chunk_leaves, int resident) {
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    __shared__ __align__(8) uint64_t bar[2];
-    R* buf[2] = {reinterpret_cast<R*>(smem_raw), reinterpret_cast<R*>(smem_raw) + (size_t)chunk_leaves * 12};
-    const int n = ctr->count[level];
-    const int nblocks = (n + SCAN_THREADS - 1) / SCAN_THREADS;
-    if ((int)blockIdx.x >= nblocks) return;
-    const int tid = threadIdx.x;
-    const int N = sc.n_leaves;
-    const int nchunks = (N + chunk_leaves - 1) / chunk_leaves;
-    if (tid == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_fence_init(); }
-    __syncthreads();
-    uint32_t phase[2] = {0, 0};
-    if (resident && N > 0) {
-        if (tid == 0) stage_chunk(sc, 0, chunk_leaves, buf[0], &bar[0]);
-        mbar_wait(&bar[0], 0);
-    }
-    for (int blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
-        const int i = blk * SCAN_THREADS + tid;
-        const bool active = i < n;
-        Ray<R> w = {R(0), R(0), R(0), R(0), R(0), R(1)};
-        if (active) {
-            const int cap = lv.cap;
-            w.ox = lv.ray[i]; w.oy = lv.ray[cap + i]; w.oz = lv.ray[2 * cap + i];
-            w.dx = lv.ray[3 * cap + i]; w.dy = lv.ray[4 * cap + i]; w.dz = lv.ray[5 * cap + i];
-        }
-        Ray<double> w64 = {0.0, 0.0, 0.0, 0.0, 0.0, 1.0};
-        if (ROBUST && active) {
-            const int cap = lv.cap;
-            w64.ox = lv.ray64[i]; w64.oy = lv.ray64[cap + i]; w64.oz = lv.ray64[2 * cap + i];
-            w64.dx = lv.ray64[3 * cap + i]; w64.dy = lv.ray64[4 * cap + i]; w64.dz = lv.ray64[5 * cap + i];
-        }
-        R best_t = R(0); int best_i = -1, best_face = 0;
+        };
         if (resident) {
-            closest_chunk<R, ROBUST>(sc, buf[0], 0, N, w, w64, best_t, best_i, best_face);
+            const int ngroups = NP / GROUP;
+            for (int g0 = 0; g0 < ngroups; g0 += FLUSH_GROUPS) {
+                cull_groups<R>(tab, 0, g0, min(g0 + FLUSH_GROUPS, ngroups), cr, list, cnt);
+                flush();
+                if (V.all_done()) break;
+            }
         } else {
             if (tid == 0) {
-                stage_chunk(sc, 0, chunk_leaves, buf[0], &bar[0]);
-                if (nchunks > 1) stage_chunk(sc, 1, chunk_leaves, buf[1], &bar[1]);
+                stage_cull(sc, 0, min(chunk_objs, NP), tab, &bar[0]);
+                if (nchunks > 1) stage_cull(sc, chunk_objs, min(chunk_objs, NP - chunk_objs), tab + (size_t)chunk_objs * 4, &bar[1]);
             }
             for (int c = 0; c < nchunks; c++) {
                 const int b = c & 1;
                 mbar_wait(&bar[b], phase[b]);
                 phase[b] ^= 1;
-                const int base = c * chunk_leaves;
-                closest_chunk<R, ROBUST>(sc, buf[b], base, min(chunk_leaves, N - base), w, w64, best_t, best_i, best_face);
+                const int base = c * chunk_objs;
+                const int gbeg = base / GROUP, gend = (base + min(chunk_objs, NP - base)) / GROUP;
+                for (int g0 = gbeg; g0 < gend; g0 += FLUSH_GROUPS) {
+                    cull_groups<R>(tab + (size_t)b * chunk_objs * 4, base, g0, min(g0 + FLUSH_GROUPS, gend), cr, list, cnt);
+                    flush();
+                }
                 __syncthreads();                       // everyone is done reading buf[b]
-                if (tid == 0 && c + 2 < nchunks) stage_chunk(sc, c + 2, chunk_leaves, buf[b], &bar[b]);
+                if (tid == 0 && c + 2 < nchunks) {
+                    const int nb = (c + 2) * chunk_objs;
+                    stage_cull(sc, nb, min(chunk_objs, NP - nb), tab + (size_t)b * chunk_objs * 4, &bar[b]);
+                }
             }
         }
-        if (active) {
-            lv.hit[i] = best_i < 0 ? -1 : (best_i | (best_face << 28));
-            lv.t[i] = best_t;
-        }
+#pragma unroll
+        for (int r = 0; r < RPT; r++) V.finish(r);
     }
 }
 
-// inShadow for every queued (hit, light) pair (raytracer.go:411-429): writes occl[target] = 1.
-template <typename R, bool COUNT>
-__global__ void __launch_bounds__(SCAN_THREADS) k_shadow(DevScene<R> sc, ShadowQueue<R> sq, unsigned char* occl,
-                                                         Counters* ctr, int chunk_leaves, int resident) {
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    __shared__ __align__(8) uint64_t bar[2];
-    R* buf[2] = {reinterpret_cast<R*>(smem_raw), reinterpret_cast<R*>(smem_raw) + (size_t)chunk_leaves * 12};
-    const int n = ctr->shadow_count;
-    const int nblocks = (n + SCAN_THREADS - 1) / SCAN_THREADS;
-    if ((int)blockIdx.x >= nblocks) return;
-    const int tid = threadIdx.x;
-    const int N = sc.n_leaves;
-    const int nchunks = (N + chunk_leaves - 1) / chunk_leaves;
-    if (tid == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_fence_init(); }
-    __syncthreads();
-    uint32_t phase[2] = {0, 0};
-    if (resident && N > 0) {
-        if (tid == 0) stage_chunk(sc, 0, chunk_leaves, buf[0], &bar[0]);
-        mbar_wait(&bar[0], 0);
-    }
-    unsigned tests[K_COUNT] = {0, 0, 0, 0, 0};
-    unsigned n_occluded = 0;
-    if (blockIdx.x == 0 && tid == 0) atomicAdd(&ctr->rays_shadow, (unsigned long long)n);
-    for (int blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
-        const int i = blk * SCAN_THREADS + tid;
-        const bool active = i < n;
-        Ray<R> w = {R(0), R(0), R(0), R(0), R(0), R(1)};
-        R dist = R(0), in_len = R(1);
-        int skip = -1;
-        if (active) {
-            const int cap = sq.cap;
-            w.ox = sq.q[i]; w.oy = sq.q[cap + i]; w.oz = sq.q[2 * cap + i];
-            w.dx = sq.q[3 * cap + i]; w.dy = sq.q[4 * cap + i]; w.dz = sq.q[5 * cap + i];
-            dist = sq.q[6 * cap + i]; in_len = sq.q[7 * cap + i];
-            skip = sq.skip[i];
+__device__ __forceinline__ void warp_add(unsigned long long* dst, unsigned long long v) {
+    for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
+    if ((threadIdx.x & 31) == 0 && v) atomicAdd(dst, v);
+}
+
+// closestHit for one recursion level (raytracer.go:469-483): strictly smaller T wins, equal T keeps
+// the object that comes first in scan order.
+template <typename R, bool ROBUST, bool COUNT> struct ClosestVisit {
+    const DevScene<R>& sc; const Level<R>& lv;
+    Ray<R> w[RPT]; int ri[RPT]; bool active[RPT];
+    R best_t[RPT]; int best_i[RPT], best_face[RPT];
+    unsigned long long n_exact;
+    __device__ ClosestVisit(const DevScene<R>& s, const Level<R>& l) : sc(s), lv(l), n_exact(0) {}
+    __device__ __forceinline__ bool setup(int r, int i, bool act, Ray<R>& out) {
+        ri[r] = i; active[r] = act; best_t[r] = R(0); best_i[r] = -1; best_face[r] = 0;
+        if (act) {
+            const size_t cap = (size_t)lv.cap;
+            out.ox = lv.ray[i]; out.oy = lv.ray[cap + i]; out.oz = lv.ray[2 * cap + i];
+            out.dx = lv.ray[3 * cap + i]; out.dy = lv.ray[4 * cap + i]; out.dz = lv.ray[5 * cap + i];
         }
-        bool done = !active;
-#define SHADOW_CHUNK(SM, BASE, CNT)                                                                         \
-        shadow_kind<R, K_SPHERE, COUNT>(sc, SM, BASE, CNT, w, dist, in_len, skip, done, tests[K_SPHERE]);   \
-        shadow_kind<R, K_CUBE, COUNT>(sc, SM, BASE, CNT, w, dist, in_len, skip, done, tests[K_CUBE]);       \
-        shadow_kind<R, K_CYLINDER, COUNT>(sc, SM, BASE, CNT, w, dist, in_len, skip, done, tests[K_CYLINDER]); \
-        shadow_kind<R, K_CONE, COUNT>(sc, SM, BASE, CNT, w, dist, in_len, skip, done, tests[K_CONE]);       \
-        shadow_kind<R, K_PLANE, COUNT>(sc, SM, BASE, CNT, w, dist, in_len, skip, done, tests[K_PLANE]);
-        if (resident) {
-            SHADOW_CHUNK(buf[0], 0, N)
-        } else {
-            if (tid == 0) {
-                stage_chunk(sc, 0, chunk_leaves, buf[0], &bar[0]);
-                if (nchunks > 1) stage_chunk(sc, 1, chunk_leaves, buf[1], &bar[1]);
-            }
-            for (int c = 0; c < nchunks; c++) {
-                const int b = c & 1;
-                mbar_wait(&bar[b], phase[b]);
-                phase[b] ^= 1;
-                const int base = c * chunk_leaves;
-                const int cnt = min(chunk_leaves, N - base);
-                SHADOW_CHUNK(buf[b], base, cnt)
-                __syncthreads();
-                if (tid == 0 && c + 2 < nchunks) stage_chunk(sc, c + 2, chunk_leaves, buf[b], &bar[b]);
-            }
-        }
-#undef SHADOW_CHUNK
-        if (active && done) { occl[sq.target[i]] = 1; n_occluded++; }
+        w[r] = out;
+        return act;
     }
-    // per-warp totals -> one atomic each
-    for (int off = 16; off > 0; off >>= 1) n_occluded += __shfl_down_sync(0xffffffffu, n_occluded, off);
-    if ((tid & 31) == 0 && n_occluded) atomicAdd(&ctr->shadow_occluded, (unsigned long long)n_occluded);
+    __device__ __forceinline__ void exact(int r, int i) {
+        R t; int face;
+        if (COUNT) n_exact++;
+        if (!exact_hit<R, ROBUST>(sc, i, w[r], lv.ray64, lv.cap, ri[r], t, face)) return;
+        if (best_i[r] < 0 || t < best_t[r] || (t == best_t[r] && sc.scan_of[i] < sc.scan_of[best_i[r]])) {
+            best_t[r] = t; best_i[r] = i; best_face[r] = face;
+        }
+    }
+    __device__ __forceinline__ bool done(int) const { return false; }
+    __device__ __forceinline__ bool all_done() const { return false; }
+    __device__ __forceinline__ void finish(int r) {
+        if (active[r]) {
+            lv.hit[ri[r]] = best_i[r] < 0 ? -1 : (best_i[r] | (best_face[r] << 28));
+            lv.t[ri[r]] = best_t[r];
+        }
+    }
+};
+
+template <typename R, bool ROBUST, bool COUNT>
+__global__ void __launch_bounds__(SCAN_THREADS) k_closest(const __grid_constant__ DevScene<R> sc, const __grid_constant__ Level<R> lv,
+                                                          Counters* ctr, int level, int chunk_objs, int resident) {
+    ClosestVisit<R, ROBUST, COUNT> V(sc, lv);
+    scan_rays<R>(sc, ctr->count[level], chunk_objs, resident, V);
     if (COUNT) {
-        for (int k = 0; k < K_COUNT; k++) {
-            unsigned v = tests[k];
-            for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
-            if ((tid & 31) == 0 && v) atomicAdd(&ctr->shadow_tests[k], (unsigned long long)v);
-        }
+        warp_add(&ctr->exact_tests, V.n_exact);
     }
 }
+
+// inShadow for every queued (hit, light) pair (raytracer.go:411-429): writes occl[target] = 1 when some
+// object other than the shaded one has  shadowHit.T * |ray.Direction| < distToLight  (:424).  The answer
+// does not depend on the order objects are visited in; COUNT additionally finds the FIRST occluder in
+// the reference's scan order to credit the tests the reference itself would have run.
+template <typename R, bool COUNT> struct ShadowVisit {
+    const DevScene<R>& sc; const ShadowQueue<R>& sq; unsigned char* occl;
+    Ray<R> w[RPT]; int ri[RPT], skip[RPT]; bool active[RPT], occluded[RPT];
+    R dist[RPT], in_len[RPT]; int first[RPT];
+    unsigned long long n_exact, n_occluded, cred_tests, cred_flops;
+    __device__ ShadowVisit(const DevScene<R>& s, const ShadowQueue<R>& q, unsigned char* o)
+        : sc(s), sq(q), occl(o), n_exact(0), n_occluded(0), cred_tests(0), cred_flops(0) {}
+    __device__ __forceinline__ bool setup(int r, int i, bool act, Ray<R>& out) {
+        ri[r] = i; active[r] = act; occluded[r] = false; skip[r] = -1; dist[r] = R(0); in_len[r] = R(1); first[r] = 0x7fffffff;
+        if (act) {
+            const size_t cap = (size_t)sq.cap;
+            out.ox = sq.q[i]; out.oy = sq.q[cap + i]; out.oz = sq.q[2 * cap + i];
+            out.dx = sq.q[3 * cap + i]; out.dy = sq.q[4 * cap + i]; out.dz = sq.q[5 * cap + i];
+            dist[r] = sq.q[6 * cap + i]; in_len[r] = sq.q[7 * cap + i];
+            skip[r] = sq.skip[i];
+        }
+        w[r] = out;
+        return act;
+    }
+    __device__ __forceinline__ void exact(int r, int i) {
+        if (i == skip[r] || (!COUNT && occluded[r])) return;
+        R t; int face;
+        if (COUNT) n_exact++;
+        if (!exact_hit<R, false>(sc, i, w[r], nullptr, 0, 0, t, face)) return;
+        if (t * in_len[r] < dist[r]) {
+            occluded[r] = true;
+            if (COUNT) first[r] = min(first[r], sc.scan_of[i]);
+        }
+    }
+    __device__ __forceinline__ bool done(int r) const { return !COUNT && (occluded[r] || !active[r]); }
+    __device__ __forceinline__ bool all_done() const {
+        bool d = true;
+#pragma unroll
+        for (int r = 0; r < RPT; r++) d = d && done(r);
+        return __all_sync(0xffffffffu, d);
+    }
+    __device__ __forceinline__ void finish(int r) {
+        if (!active[r]) return;
+        if (occluded[r]) { occl[sq.target[ri[r]]] = 1; n_occluded++; }
+        if (COUNT) {
+            // objects 0..last of the scan order are tested, minus the shaded one (raytracer.go:416-427)
+            const int last = occluded[r] ? first[r] : sc.n_leaves - 1;
+            if (last >= 0) {
+                unsigned long long tests = (unsigned long long)last + 1, flops = sc.cum_flops[last];
+                const int ss = skip[r] >= 0 ? sc.scan_of[skip[r]] : 0x7fffffff;
+                if (ss <= last) { tests--; flops -= (unsigned long long)sc.flops_of_kind[kind_of(sc.kind_begin, skip[r])]; }
+                cred_tests += tests; cred_flops += flops;
+            }
+        }
+    }
+};
+
+template <typename R, bool COUNT>
+__global__ void __launch_bounds__(SCAN_THREADS) k_shadow(const __grid_constant__ DevScene<R> sc, const __grid_constant__ ShadowQueue<R> sq,
+                                                         unsigned char* occl, Counters* ctr, int chunk_objs, int resident) {
+    const int n = ctr->shadow_count;
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ctr->rays_shadow, (unsigned long long)n);
+    ShadowVisit<R, COUNT> V(sc, sq, occl);
+    scan_rays<R>(sc, n, chunk_objs, resident, V);
+    warp_add(&ctr->shadow_occluded, V.n_occluded);
+    if (COUNT) {
+        warp_add(&ctr->exact_tests, V.n_exact);
+        warp_add(&ctr->shadow_tests, V.cred_tests);
+        warp_add(&ctr->shadow_flops, V.cred_flops);
+    }
+}
+
 
 // ------------------------------------------------------------------ surface bytecode interpreter
 // EvalSurfaceFn (internal/gml/evaluator.go:672-727) after host-side partial evaluation: typed
@@ -980,10 +1098,15 @@ public:
         CU_TRY(cudaMemcpyToSymbol(c_pcg_jump, tab, sizeof tab));
         CU_TRY(cudaMalloc(&ctr_, sizeof(Counters)));
         CU_TRY(cudaMemset(ctr_, 0, sizeof(Counters)));
-        CU_TRY(cudaFuncSetAttribute(k_closest<R, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        if (kRobustPrimary) CU_TRY(cudaFuncSetAttribute(k_closest<R, kRobustPrimary>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        CU_TRY(cudaFuncSetAttribute(k_shadow<R, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        CU_TRY(cudaFuncSetAttribute(k_shadow<R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        const int smem_max = 200 * 1024;
+        CU_TRY(cudaFuncSetAttribute(k_closest<R, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+        CU_TRY(cudaFuncSetAttribute(k_closest<R, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+        if (kRobustPrimary) {
+            CU_TRY(cudaFuncSetAttribute(k_closest<R, kRobustPrimary, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+            CU_TRY(cudaFuncSetAttribute(k_closest<R, kRobustPrimary, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+        }
+        CU_TRY(cudaFuncSetAttribute(k_shadow<R, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+        CU_TRY(cudaFuncSetAttribute(k_shadow<R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
         return GMLRT_OK;
     }
 
@@ -998,7 +1121,7 @@ public:
         out = totals_;
         out.rays_reflect = c.rays_reflect; out.rays_refract = c.rays_refract;
         out.rays_shadow = c.rays_shadow; out.shadow_occluded = c.shadow_occluded;
-        for (int k = 0; k < K_COUNT; k++) out.shadow_tests[k] = c.shadow_tests[k];
+        out.shadow_tests = c.shadow_tests; out.shadow_flops = c.shadow_flops; out.exact_tests = c.exact_tests;
         out.error = c.error;
         return GMLRT_OK;
     }
@@ -1053,8 +1176,8 @@ private:
     TraceTotals totals_;
     bool need_ctr_reset_ = true;
     // scan kernel configuration
-    int chunk_leaves_ = 1, resident_ = 1; size_t scan_smem_ = 0;
-    int grid_closest0_ = 148, grid_closest_ = 148, grid_shadow_ = 148, grid_shadow_cnt_ = 148;
+    int chunk_objs_ = GROUP, resident_ = 1; size_t scan_smem_ = 0;
+    int grid_closest_[2][2] = {{148, 148}, {148, 148}}, grid_shadow_[2] = {148, 148};   // [robust][counting], [counting]
     std::vector<int> kind_host_;
 };
 
@@ -1074,8 +1197,13 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     std::vector<R> w2o((size_t)n * 12), o2w((size_t)n * 12), fn((size_t)n * 18);
     std::vector<double> w2o64(kRobustPrimary ? (size_t)n * 12 : 0);
     std::vector<int> scan_of(n), surface(n), kind(n);
+    if (n > 0xffff * GROUP) { err = "too many leaves for the 16-bit group index of the scan kernels"; return GMLRT_E_UNSUPPORTED; }
+    const int n_cull = (n + GROUP - 1) / GROUP * GROUP;
+    std::vector<R> cull((size_t)std::max(n_cull, GROUP) * 4);
+    std::vector<unsigned long long> cum_flops(std::max(n, 1), 0ull);
     DevScene<R> sc{};
-    sc.n_leaves = n;
+    sc.n_leaves = n; sc.n_cull = n_cull;
+    for (int k = 0; k < K_COUNT; k++) sc.flops_of_kind[k] = (int)kFlopsByKind[k];
     for (int k = 0; k <= K_COUNT; k++) sc.kind_begin[k] = 0;
     for (int d = 0; d < n; d++) {
         const HostLeaf& L = S.leaves[order[d]];
@@ -1084,7 +1212,23 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
         for (int f = 0; f < 6; f++) for (int k = 0; k < 3; k++) fn[(size_t)d * 18 + 3 * f + k] = (R)L.face_normal[f][k];
         scan_of[d] = L.scan_index; surface[d] = (int)L.surface; kind[d] = L.kind;
         sc.kind_begin[L.kind + 1]++;
+        // cull record: bounding sphere, radius inflated so that a reject is always a true miss (see the scan section)
+        double C[3], Rw;
+        leaf_bound(L.kind, L.o2w, C, Rw);
+        const R cx = (R)C[0], cy = (R)C[1], cz = (R)C[2];
+        const double cc = (double)cx * cx + (double)cy * cy + (double)cz * cz;
+        const double Rm = Rw * (1.0 + CullMargin<R>::radius);
+        double K = cc - Rm * Rm - CullMargin<R>::rel * cc;
+        if (!(K == K) || std::isinf(Rw)) K = -INFINITY;                      // unbounded (plane) or degenerate: never rejected
+        cull[(size_t)d * 4 + 0] = cx; cull[(size_t)d * 4 + 1] = cy; cull[(size_t)d * 4 + 2] = cz; cull[(size_t)d * 4 + 3] = (R)K;
+        if ((double)cull[(size_t)d * 4 + 3] > K) cull[(size_t)d * 4 + 3] = std::nextafter(cull[(size_t)d * 4 + 3], (R)-INFINITY);
+        cum_flops[L.scan_index] = (unsigned long long)kFlopsByKind[L.kind];
     }
+    for (int d = n; d < std::max(n_cull, GROUP); d++) {                      // padding: always rejected
+        cull[(size_t)d * 4 + 0] = cull[(size_t)d * 4 + 1] = cull[(size_t)d * 4 + 2] = R(0);
+        cull[(size_t)d * 4 + 3] = (R)INFINITY;
+    }
+    for (int i = 1; i < n; i++) cum_flops[i] += cum_flops[i - 1];
     for (int k = 0; k < K_COUNT; k++) sc.kind_begin[k + 1] += sc.kind_begin[k];
     kind_host_ = kind;
     std::vector<DevLight<R>> lights(S.lights.size());
@@ -1113,6 +1257,9 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     int rc;
     double* d_w2o64 = nullptr;
     if ((rc = to_device(w2o64, &d_w2o64, err))) return rc;
+    R* d_cull; unsigned long long* d_cum;
+    if ((rc = to_device(cull, &d_cull, err)) || (rc = to_device(cum_flops, &d_cum, err))) return rc;
+    sc.cull = d_cull; sc.cum_flops = d_cum;
     R *d_w2o, *d_o2w, *d_fn, *d_fpool; int *d_scan, *d_surf, *d_kind, *d_itab; uint32_t* d_code;
     DevLight<R>* d_lights; DevSurface<R>* d_surfaces;
     if ((rc = to_device(w2o, &d_w2o, err)) || (rc = to_device(o2w, &d_o2w, err)) || (rc = to_device(fn, &d_fn, err)) ||
@@ -1201,22 +1348,24 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     sq_.q = (R*)(base + o_sq); sq_.skip = (int*)(base + o_skip); sq_.target = (int*)(base + o_tgt); sq_.cap = (int)sq_cap;
     samples_ = (R*)(base + o_samples); sample_cap_ = (int)S0;
 
-    // scan kernels: resident scene when it fits, else two streaming buffers
-    const size_t leaf_bytes = 12 * sizeof(R);
-    const size_t resident_max = env_size("GMLRT_RESIDENT_KB", 64) * 1024;
-    const size_t chunk_bytes = env_size("GMLRT_CHUNK_KB", 32) * 1024;
-    const size_t all = std::max<size_t>((size_t)sc_.n_leaves * leaf_bytes, 16);
-    if (all <= resident_max) { resident_ = 1; chunk_leaves_ = std::max(sc_.n_leaves, 1); scan_smem_ = all; }
-    else { resident_ = 0; chunk_leaves_ = (int)(chunk_bytes / leaf_bytes); scan_smem_ = 2 * (size_t)chunk_leaves_ * leaf_bytes; }
-    int occ = 1;
-    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_closest<R, false>, SCAN_THREADS, scan_smem_));
-    grid_closest_ = sms_ * std::max(occ, 1);
-    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_closest<R, kRobustPrimary>, SCAN_THREADS, scan_smem_));
-    grid_closest0_ = sms_ * std::max(occ, 1);
-    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shadow<R, false>, SCAN_THREADS, scan_smem_));
-    grid_shadow_ = sms_ * std::max(occ, 1);
-    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_shadow<R, true>, SCAN_THREADS, scan_smem_));
-    grid_shadow_cnt_ = sms_ * std::max(occ, 1);
+    // scan kernels: resident cull table when it fits, else two streaming buffers (chunks of whole groups)
+    const size_t rec_bytes = 4 * sizeof(R);
+    const size_t resident_max = env_size("GMLRT_RESIDENT_KB", 128) * 1024;
+    const size_t chunk_bytes = std::max<size_t>(env_size("GMLRT_CHUNK_KB", 32) * 1024, GROUP * rec_bytes);
+    const size_t all = (size_t)std::max(sc_.n_cull, GROUP) * rec_bytes;
+    if (all <= resident_max) { resident_ = 1; chunk_objs_ = std::max(sc_.n_cull, GROUP); scan_smem_ = LIST_BYTES + all; }
+    else { resident_ = 0; chunk_objs_ = (int)(chunk_bytes / rec_bytes) / GROUP * GROUP; scan_smem_ = LIST_BYTES + 2 * (size_t)chunk_objs_ * rec_bytes; }
+    auto grid_for = [&](auto kernel, int& grid) -> int {
+        int occ = 1;
+        CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, SCAN_THREADS, scan_smem_));
+        grid = sms_ * std::max(occ, 1);
+        return GMLRT_OK;
+    };
+    int rc;
+    if ((rc = grid_for(k_closest<R, false, false>, grid_closest_[0][0])) || (rc = grid_for(k_closest<R, false, true>, grid_closest_[0][1])) ||
+        (rc = grid_for(k_closest<R, kRobustPrimary, false>, grid_closest_[1][0])) || (rc = grid_for(k_closest<R, kRobustPrimary, true>, grid_closest_[1][1])) ||
+        (rc = grid_for(k_shadow<R, false>, grid_shadow_[0])) || (rc = grid_for(k_shadow<R, true>, grid_shadow_[1])))
+        return rc;
     return GMLRT_OK;
 }
 
@@ -1240,18 +1389,23 @@ int Renderer<R>::trace_rows(int y0, int y1, bool counting, std::string& err) {
         totals_.rays_primary += (unsigned long long)S;
         for (int l = 0; l < depth_eff_; l++) {
             const int cap_blocks = (levels_[l].cap + SHADE_THREADS - 1) / SHADE_THREADS;
-            if (l == 0 && kRobustPrimary)
-                k_closest<R, kRobustPrimary><<<grid_closest0_, SCAN_THREADS, scan_smem_, stream_>>>(sc_, levels_[l], ctr_, l, chunk_leaves_, resident_);
-            else
-                k_closest<R, false><<<grid_closest_, SCAN_THREADS, scan_smem_, stream_>>>(sc_, levels_[l], ctr_, l, chunk_leaves_, resident_);
+            const bool robust = (l == 0 && kRobustPrimary);
+            const int gc = grid_closest_[robust][counting];
+            if (robust) {
+                if (counting) k_closest<R, kRobustPrimary, true><<<gc, SCAN_THREADS, scan_smem_, stream_>>>(sc_, levels_[l], ctr_, l, chunk_objs_, resident_);
+                else k_closest<R, kRobustPrimary, false><<<gc, SCAN_THREADS, scan_smem_, stream_>>>(sc_, levels_[l], ctr_, l, chunk_objs_, resident_);
+            } else {
+                if (counting) k_closest<R, false, true><<<gc, SCAN_THREADS, scan_smem_, stream_>>>(sc_, levels_[l], ctr_, l, chunk_objs_, resident_);
+                else k_closest<R, false, false><<<gc, SCAN_THREADS, scan_smem_, stream_>>>(sc_, levels_[l], ctr_, l, chunk_objs_, resident_);
+            }
             const bool spawn = l + 1 < depth_eff_;
             k_shade<R><<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
                 sc_, levels_[l], spawn ? levels_[l + 1] : levels_[l], sq_, occl_[l], ctr_, l, spawn ? 1 : 0,
                 (counting && l == 0) ? ids_ : nullptr, ty);
             totals_.launches += 2;
             if (sc_.n_lights > 0) {
-                if (counting) k_shadow<R, true><<<grid_shadow_cnt_, SCAN_THREADS, scan_smem_, stream_>>>(sc_, sq_, occl_[l], ctr_, chunk_leaves_, resident_);
-                else k_shadow<R, false><<<grid_shadow_, SCAN_THREADS, scan_smem_, stream_>>>(sc_, sq_, occl_[l], ctr_, chunk_leaves_, resident_);
+                if (counting) k_shadow<R, true><<<grid_shadow_[1], SCAN_THREADS, scan_smem_, stream_>>>(sc_, sq_, occl_[l], ctr_, chunk_objs_, resident_);
+                else k_shadow<R, false><<<grid_shadow_[0], SCAN_THREADS, scan_smem_, stream_>>>(sc_, sq_, occl_[l], ctr_, chunk_objs_, resident_);
                 CU_TRY(cudaMemsetAsync(&ctr_->shadow_count, 0, sizeof(int), stream_));
                 totals_.launches++;
             }

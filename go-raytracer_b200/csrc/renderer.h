@@ -13,7 +13,8 @@ namespace gmlrt {
 
 struct TraceTotals {                   // summed over the tiles a device rendered
     unsigned long long rays_primary = 0, rays_reflect = 0, rays_refract = 0, rays_shadow = 0, shadow_occluded = 0;
-    unsigned long long shadow_tests[K_COUNT] = {0, 0, 0, 0, 0};
+    unsigned long long shadow_tests = 0, shadow_flops = 0;   // credited (reference scan order), counting mode
+    unsigned long long cull_tests = 0, exact_tests = 0;      // executed: first-phase (all pairs) and second-phase tests
     unsigned long long launches = 0;
     int error = 0;
 };

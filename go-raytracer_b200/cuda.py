@@ -23,7 +23,8 @@ class Stats(ctypes.Structure):
                 ("ms_d2h", ctypes.c_double), ("rays_primary", ctypes.c_uint64), ("rays_reflect", ctypes.c_uint64),
                 ("rays_refract", ctypes.c_uint64), ("rays_shadow", ctypes.c_uint64), ("shadow_occluded", ctypes.c_uint64),
                 ("leaf_tests", ctypes.c_uint64), ("flops_credited", ctypes.c_double), ("kernel_launches", ctypes.c_uint64),
-                ("n_devices", ctypes.c_uint32), ("n_leaves", ctypes.c_uint32)]
+                ("n_devices", ctypes.c_uint32), ("n_leaves", ctypes.c_uint32),
+                ("cull_tests", ctypes.c_uint64), ("exact_tests", ctypes.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

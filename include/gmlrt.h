@@ -181,11 +181,13 @@ typedef struct gmlrt_stats {
     uint64_t rays_refract;      /* closest-hit queries from refraction (raytracer.go:532-556) */
     uint64_t rays_shadow;       /* inShadow queries (raytracer.go:411-429) */
     uint64_t shadow_occluded;   /* ... that found an occluder */
-    uint64_t leaf_tests;        /* ray x leaf tests credited */
-    double   flops_credited;    /* sum over tests of the per-leaf-type flop table */
+    uint64_t leaf_tests;        /* ray x leaf tests the REFERENCE runs for these queries */
+    double   flops_credited;    /* ... times the per-leaf-type flop table: the brute-force-equivalent work */
     uint64_t kernel_launches;   /* kernels launched by this call */
     uint32_t n_devices;
     uint32_t n_leaves;
+    uint64_t cull_tests;        /* executed: first-phase bounding-sphere tests (every query x every object) */
+    uint64_t exact_tests;       /* executed: second-phase <Type>.Intersect tests on the survivors (counting mode) */
 } gmlrt_stats;
 
 /* Create a context on `n` devices (`devices` = CUDA ordinals; n >= 1).  With n > 1 the
