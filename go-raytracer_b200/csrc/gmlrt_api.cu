@@ -6,6 +6,7 @@
 // Multi-GPU: pixels are independent, so the image is cut into row bands that
 // are dealt round-robin to the devices; the scene is replicated; each finished band is copied
 // into device 0's frame with cudaMemcpyPeerAsync (NVLink 5 through NVSwitch).  No collective.
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <cstring>
@@ -51,7 +52,46 @@ static int fail(gmlrt_ctx* c, int code, const std::string& msg) {
                         std::string(#expr) + ": " + cudaGetErrorString(e_));           \
     } while (0)
 
+// FP32 roofline denominator measured on the box: 8 independent FFMA chains per thread, every SM saturated.
+__global__ void __launch_bounds__(256) k_fma_peak(float* out, int iters, float a, float b) {
+    float x0 = threadIdx.x * 1e-3f, x1 = x0 + 1.f, x2 = x0 + 2.f, x3 = x0 + 3.f, x4 = x0 + 4.f, x5 = x0 + 5.f, x6 = x0 + 6.f, x7 = x0 + 7.f;
+#pragma unroll 1
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            x0 = fmaf(x0, a, b); x1 = fmaf(x1, a, b); x2 = fmaf(x2, a, b); x3 = fmaf(x3, a, b);
+            x4 = fmaf(x4, a, b); x5 = fmaf(x5, a, b); x6 = fmaf(x6, a, b); x7 = fmaf(x7, a, b);
+        }
+    }
+    const float s = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+    if (s == 12345.678f) out[0] = s;          // keeps the chains alive
+}
+
 extern "C" {
+
+double gmlrt_measure_fp32_tflops(int device) {
+    if (cudaSetDevice(device) != cudaSuccess) return -1.0;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return -1.0;
+    float* out = nullptr;
+    if (cudaMalloc(&out, 256) != cudaSuccess) return -1.0;
+    cudaEvent_t a, b;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    const int blocks = prop.multiProcessorCount * 8, iters = 1 << 15;
+    double best = 0.0;
+    for (int rep = 0; rep < 6; rep++) {              // first rep warms up
+        cudaEventRecord(a);
+        k_fma_peak<<<blocks, 256>>>(out, iters, 0.999f, 1e-3f);
+        cudaEventRecord(b);
+        if (cudaEventSynchronize(b) != cudaSuccess) { best = -1.0; break; }
+        float ms = 0;
+        cudaEventElapsedTime(&ms, a, b);
+        const double flops = (double)blocks * 256.0 * (double)iters * 64.0 * 2.0;
+        if (rep > 0) best = std::max(best, flops / (ms * 1e-3) / 1e12);
+    }
+    cudaEventDestroy(a); cudaEventDestroy(b); cudaFree(out);
+    return best;
+}
 
 int gmlrt_blob_version(void) { return (int)GMLRT_BLOB_VERSION; }
 
@@ -123,6 +163,12 @@ void* gmlrt_stream(gmlrt_ctx* c) { return c && !c->r.empty() ? (void*)c->r[0]->s
 int gmlrt_set_counting(gmlrt_ctx* c, int enabled) {
     if (!c) return GMLRT_E_BAD_ARG;
     c->counting = enabled != 0;
+    return GMLRT_OK;
+}
+
+int gmlrt_set_profiling(gmlrt_ctx* c, int enabled) {
+    if (!c) return GMLRT_E_BAD_ARG;
+    for (auto& r : c->r) r->set_profiling(enabled != 0);
     return GMLRT_OK;
 }
 
@@ -212,7 +258,8 @@ int gmlrt_trace(gmlrt_ctx* c, gmlrt_stats* stats) {
         if (rc != GMLRT_OK) return fail(c, rc, err);
         sum.rays_primary += t.rays_primary; sum.rays_reflect += t.rays_reflect; sum.rays_refract += t.rays_refract;
         sum.rays_shadow += t.rays_shadow; sum.shadow_occluded += t.shadow_occluded; sum.launches += t.launches;
-        sum.shadow_tests += t.shadow_tests; sum.shadow_flops += t.shadow_flops; sum.exact_tests += t.exact_tests;
+        sum.shadow_tests += t.shadow_tests; sum.shadow_flops += t.shadow_flops; sum.exact_tests += t.exact_tests; sum.exact_flops += t.exact_flops;
+        for (int k = 0; k < KC_COUNT; k++) { sum.ms_class[k] = std::max(sum.ms_class[k], t.ms_class[k]); sum.launches_class[k] += t.launches_class[k]; }
         sum.error |= t.error;
     }
     if (stats) {
@@ -225,6 +272,7 @@ int gmlrt_trace(gmlrt_ctx* c, gmlrt_stats* stats) {
         // with the tests its lane ran up to its own first occluder (counting mode only)
         double all = 0; unsigned long long nleaf = 0;
         for (int i = 0; i < c->scene.n_plain; i++) { all += kFlopsByKind[c->scene.leaves[i].kind]; nleaf++; }
+        for (auto& obj : c->scene.csg) { all += obj.flops; nleaf++; }
         const unsigned long long closest = sum.rays_primary + sum.rays_reflect + sum.rays_refract;
         stats->leaf_tests = closest * nleaf;
         stats->flops_credited = (double)closest * all;
@@ -233,6 +281,8 @@ int gmlrt_trace(gmlrt_ctx* c, gmlrt_stats* stats) {
         // executed work: every query runs the 7-FFMA cull test against every object, the exact test only on survivors
         stats->cull_tests = (closest + sum.rays_shadow) * nleaf;
         stats->exact_tests = sum.exact_tests;
+        stats->flops_executed = 14.0 * (double)stats->cull_tests + (double)sum.exact_flops;   // cull = 7 FFMA
+        for (int k = 0; k < KC_COUNT; k++) { stats->ms_class[k] = sum.ms_class[k]; stats->launches_class[k] = sum.launches_class[k]; }
     }
     if (sum.error) return fail(c, GMLRT_E_SURFACE, "a surface function faulted at render time (the reference panics here, raytracer.go:499-501)");
     return GMLRT_OK;

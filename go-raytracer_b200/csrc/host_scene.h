@@ -18,7 +18,9 @@
 namespace gmlrt {
 
 // device-order kind slots (scan kernels walk the leaves kind by kind)
-enum Kind { K_SPHERE = 0, K_CUBE = 1, K_CYLINDER = 2, K_CONE = 3, K_PLANE = 4, K_COUNT = 5 };
+enum Kind { K_SPHERE = 0, K_CUBE = 1, K_CYLINDER = 2, K_CONE = 3, K_PLANE = 4, K_COUNT = 5,
+            K_CSG = 5, K_OBJ_KINDS = 6 };   // K_CSG: a scan-order object that is an intersect/difference subtree (EXTENSION)
+#define GMLRT_CSG_MAX_STACK 6               // span-list stack depth of the device evaluator (left-deep trees need 2)
 static const double kFlopsByKind[K_COUNT] = {56, 81, 74, 70, 47};
 
 struct HostLeaf {
@@ -33,7 +35,11 @@ struct HostLeaf {
 
 // One CSG object = a subtree rooted at an intersect/difference node, in postfix order.
 struct HostCsgOp { int op; int leaf; };   // op: -1 push leaf `leaf` (index into leaves), else GMLRT_NODE_* operator
-struct HostCsgObject { int scan_index; std::vector<HostCsgOp> postfix; int max_stack; };
+struct HostCsgObject {
+    int scan_index; std::vector<HostCsgOp> postfix; int max_stack;
+    double C[3]; double R;   // bounding sphere (cull phase)
+    double flops;            // credited per test: member table flops, +2 per quadric (both roots), SURVEY.md 8(d)
+};
 
 struct HostScene {
     gmlrt_blob_header h;
@@ -97,6 +103,18 @@ inline void leaf_bound(int kind, const double* o2w, double* C, double& Rw) {
     if (!(smax <= frob)) smax = frob;                                          // NaN or closed-form trouble: fall back to the safe bound
     Rw = r0[kind] * (smax > 0.0 ? smax : frob) * (1.0 + 1e-9);
     if (!(Rw == Rw)) Rw = INFINITY;
+}
+
+// smallest sphere enclosing two spheres
+inline void sphere_union(const double* C1, double R1, const double* C2, double R2, double* C, double& R) {
+    if (std::isinf(R1) || std::isinf(R2)) { C[0] = C[1] = C[2] = 0; R = INFINITY; return; }
+    const double d[3] = {C2[0] - C1[0], C2[1] - C1[1], C2[2] - C1[2]};
+    const double dist = std::sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+    if (dist + R2 <= R1) { C[0] = C1[0]; C[1] = C1[1]; C[2] = C1[2]; R = R1; return; }
+    if (dist + R1 <= R2) { C[0] = C2[0]; C[1] = C2[1]; C[2] = C2[2]; R = R2; return; }
+    R = 0.5 * (dist + R1 + R2) * (1.0 + 1e-12);
+    const double f = (R - R1) / dist;
+    for (int k = 0; k < 3; k++) C[k] = C1[k] + d[k] * f;
 }
 
 static const double kCubeNormals[6][3] = {{0, 0, -1}, {0, 0, 1}, {-1, 0, 0}, {1, 0, 0}, {0, 1, 0}, {0, -1, 0}};
@@ -214,6 +232,29 @@ inline int parse_blob(const void* blob, size_t nbytes, HostScene& S, std::string
     S.n_objects = (int)S.object_of_scan.size();
     for (auto& obj : S.csg) for (auto& op : obj.postfix) if (op.op < 0) op.leaf += S.n_plain;
     S.leaves.insert(S.leaves.end(), csg_members.begin(), csg_members.end());
+    for (auto& obj : S.csg) {
+        if (obj.max_stack > GMLRT_CSG_MAX_STACK) { err = "CSG tree needs a deeper span stack than GMLRT_CSG_MAX_STACK"; return GMLRT_E_UNSUPPORTED; }
+        struct B { double C[3], R; };
+        std::vector<B> st;
+        obj.flops = 0;
+        for (auto& op : obj.postfix) {
+            if (op.op < 0) {
+                const HostLeaf& L = S.leaves[op.leaf];
+                B b; leaf_bound(L.kind, L.o2w, b.C, b.R);
+                st.push_back(b);
+                obj.flops += kFlopsByKind[L.kind] + ((L.kind == K_SPHERE || L.kind == K_CYLINDER || L.kind == K_CONE) ? 2 : 0);
+            } else {
+                B b = st.back(); st.pop_back();
+                B a = st.back(); st.pop_back();
+                B r;
+                if (op.op == GMLRT_NODE_DIFFERENCE) r = a;                                   // a - b lies inside a
+                else if (op.op == GMLRT_NODE_INTERSECT) r = (b.R < a.R) ? b : a;            // inside both: keep the smaller bound
+                else sphere_union(a.C, a.R, b.C, b.R, r.C, r.R);
+                st.push_back(r);
+            }
+        }
+        obj.C[0] = st.back().C[0]; obj.C[1] = st.back().C[1]; obj.C[2] = st.back().C[2]; obj.R = st.back().R;
+    }
     return GMLRT_OK;
 }
 

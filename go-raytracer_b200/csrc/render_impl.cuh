@@ -49,11 +49,14 @@ template <typename R> struct DevSurface { int kind, code_off, code_len, n_regs; 
 
 template <typename R> struct DevScene {
     int n_leaves;                  // plain objects, device order (sorted by kind)
-    int kind_begin[K_COUNT + 1];
+    int kind_begin[K_OBJ_KINDS + 1];   // objects [0, n_leaves) sorted by kind; CSG objects last
+    int n_all;                     // objects + CSG member leaves (the per-leaf arrays below have n_all entries)
+    const int* csg_prog;           // postfix programs: >= 0 push member leaf (device index), -1 - GMLRT_NODE_* operator
+    const int2* csg_range;         // [n_csg] (offset, length) into csg_prog, indexed by object - kind_begin[K_CSG]
+    const int* obj_flops;          // [n_leaves] credited flops of one test of the object
     int n_cull;                    // n_leaves rounded up to a multiple of GROUP
     const R* cull;                 // [n_cull][4] bounding sphere centre xyz, K = |C|^2 - R^2 - margin   (hot: staged in smem)
     const unsigned long long* cum_flops;   // [n] credited flops of scan-order objects 0..s
-    int flops_of_kind[K_COUNT];
     const R* w2o;                  // [n][12] rows 0..2 of WorldToObject
     const int* scan_of;            // device index -> scan-order index (tie-breaks, ids)
     const double* w2o64;           // [n][12] the same matrices in double, for the robust primary-ray tests (f32 mode)
@@ -96,7 +99,7 @@ struct Counters {                  // device-resident, zeroed per trace
     int error;
     unsigned long long rays_reflect, rays_refract, rays_shadow, shadow_occluded;
     unsigned long long shadow_tests, shadow_flops;   // credited: the reference's scan up to its first occluder (counting mode)
-    unsigned long long exact_tests;                  // executed second-phase tests (counting mode)
+    unsigned long long exact_tests, exact_flops;     // executed second-phase tests and their table flops (counting mode)
 };
 
 template <typename R> struct Ray { R ox, oy, oz, dx, dy, dz; };
@@ -249,6 +252,182 @@ template <typename R, int KIND> __device__ __forceinline__ bool hit_kind(const R
     return hit_plane(r, t, face);
 }
 
+// ------------------------------------------------------------------ CSG objects: interval span lists (EXTENSION)
+// The reference rejects intersect / difference nodes (raytracer.go:825-826); semantics follow the
+// ICFP-2000 text as restated by oracle/oracle.c (leaf_spans, spans_complement, spans_intersect,
+// csg_spans, csg_intersect) - operation for operation, so that parity mode is bit-identical to it.
+// A solid along a ray is a sorted list of disjoint parameter intervals; every finite bound remembers
+// the member leaf, face and orientation of the surface it lies on.  The tree is walked as a postfix
+// program over a small stack of lists (no recursion); lists live in local memory, which is fine
+// because only rays that survive the object's bounding-sphere cull get here.
+#define GMLRT_MAXSPANS 16
+#define HIT_LEAF_MASK 0x07ffffff      // hit code: leaf | flip << 27 | face << 28
+#define HIT_NONE_LEAF 0x07ffffff
+
+template <typename R> struct Spans {
+    int n;
+    R t[2 * GMLRT_MAXSPANS];          // [2s] = entry bound of span s, [2s+1] = exit bound
+    int info[2 * GMLRT_MAXSPANS];     // hit code of the surface at that bound (leaf = HIT_NONE_LEAF: at infinity)
+};
+
+__device__ __forceinline__ int bound_info(int leaf, int face) { return leaf | (face << 28); }
+
+template <typename R> __device__ __forceinline__ void spans_push(Spans<R>& L, R tin, int iin, R tout, int iout) {
+    if (!(tin < tout) || L.n >= GMLRT_MAXSPANS) return;
+    L.t[2 * L.n] = tin; L.info[2 * L.n] = iin; L.t[2 * L.n + 1] = tout; L.info[2 * L.n + 1] = iout;
+    L.n++;
+}
+
+// oracle.c leaf_spans: the parameter interval(s) where the object-space ray `r` is inside the leaf
+template <typename R> __device__ __noinline__ void leaf_spans(int kind, int leaf, const Ray<R>& r, Spans<R>& L) {
+    const R INF = gm<R>::inf();
+    const int NONE = HIT_NONE_LEAF;
+    L.n = 0;
+    if (kind == K_SPHERE) {
+        const R a = r.dx * r.dx + r.dy * r.dy + r.dz * r.dz, hb = r.ox * r.dx + r.oy * r.dy + r.oz * r.dz;
+        const R c = r.ox * r.ox + r.oy * r.oy + r.oz * r.oz - R(1);
+        const R disc = hb * hb - a * c;
+        if (disc < R(0)) return;
+        const R sq = gm<R>::sqrt(disc);
+        spans_push(L, (-hb - sq) / a, bound_info(leaf, 0), (-hb + sq) / a, bound_info(leaf, 0));
+    } else if (kind == K_PLANE) {                        // the half space y <= 0
+        if (gm<R>::abs(r.dy) < R(1e-6)) {
+            if (r.oy <= R(0)) spans_push(L, -INF, NONE, INF, NONE);
+            return;
+        }
+        const R t = (R(0) - r.oy) / r.dy;
+        if (r.dy > R(0)) spans_push(L, -INF, NONE, t, bound_info(leaf, 0));
+        else spans_push(L, t, bound_info(leaf, 0), INF, NONE);
+    } else if (kind == K_CUBE) {                         // slabs; faces as plane.go:29-38
+        const int FACE_LO[3] = {2, 5, 0}, FACE_HI[3] = {3, 4, 1};
+        const R oo[3] = {r.ox, r.oy, r.oz}, dd[3] = {r.dx, r.dy, r.dz};
+        R lo = -INF, hi = INF; int ilo = NONE, ihi = NONE;
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            if (gm<R>::abs(dd[k]) < R(1e-12)) { if (oo[k] < R(0) || oo[k] > R(1)) return; continue; }
+            R ta = (R(0) - oo[k]) / dd[k], tb = (R(1) - oo[k]) / dd[k];
+            int ia = bound_info(leaf, FACE_LO[k]), ib = bound_info(leaf, FACE_HI[k]);
+            if (ta > tb) { const R tt = ta; ta = tb; tb = tt; const int ii = ia; ia = ib; ib = ii; }
+            if (ta > lo) { lo = ta; ilo = ia; }
+            if (tb < hi) { hi = tb; ihi = ib; }
+        }
+        spans_push(L, lo, ilo, hi, ihi);
+    } else if (kind == K_CYLINDER) {
+        R lo = -INF, hi = INF; int ilo = NONE, ihi = NONE;
+        const R a = r.dx * r.dx + r.dz * r.dz;
+        const R hb = r.ox * r.dx + r.oz * r.dz;
+        const R c0 = r.ox * r.ox + r.oz * r.oz - R(1);
+        if (a > R(1e-12)) {
+            const R disc = hb * hb - a * c0;
+            if (disc < R(0)) return;
+            const R sq = gm<R>::sqrt(disc);
+            lo = (-hb - sq) / a; ilo = bound_info(leaf, 0); hi = (-hb + sq) / a; ihi = bound_info(leaf, 0);
+        } else if (c0 > R(0)) return;
+        if (gm<R>::abs(r.dy) > R(1e-12)) {
+            R t0 = (R(0) - r.oy) / r.dy, t1 = (R(1) - r.oy) / r.dy;
+            int i0 = bound_info(leaf, 2), i1 = bound_info(leaf, 1);
+            if (t0 > t1) { const R tt = t0; t0 = t1; t1 = tt; const int ii = i0; i0 = i1; i1 = ii; }
+            if (t0 > lo) { lo = t0; ilo = i0; }
+            if (t1 < hi) { hi = t1; ihi = i1; }
+        } else if (r.oy < R(0) || r.oy > R(1)) return;
+        spans_push(L, lo, ilo, hi, ihi);
+    } else {                                             // cone: convex, min / max of the valid boundary candidates
+        R cand[3]; int cf[3]; int nc = 0;
+        const R a = r.dx * r.dx + r.dz * r.dz - r.dy * r.dy;
+        const R hb = r.ox * r.dx + r.oz * r.dz - r.oy * r.dy;
+        const R c0 = r.ox * r.ox + r.oz * r.oz - r.oy * r.oy;
+        if (gm<R>::abs(a) > R(1e-12)) {
+            const R disc = hb * hb - a * c0;
+            if (disc >= R(0)) {
+                const R sq = gm<R>::sqrt(disc);
+                const R ts[2] = {(-hb - sq) / a, (-hb + sq) / a};
+#pragma unroll
+                for (int k = 0; k < 2; k++) {
+                    const R y = r.oy + r.dy * ts[k];
+                    if (y >= R(0) && y <= R(1)) { cand[nc] = ts[k]; cf[nc++] = 0; }
+                }
+            }
+        } else if (gm<R>::abs(hb) > R(1e-12)) {
+            const R t = -c0 / (R(2) * hb);
+            const R y = r.oy + r.dy * t;
+            if (y >= R(0) && y <= R(1)) { cand[nc] = t; cf[nc++] = 0; }
+        }
+        if (gm<R>::abs(r.dy) > R(1e-12)) {
+            const R t = (R(1) - r.oy) / r.dy;
+            const R px = r.ox + r.dx * t, pz = r.oz + r.dz * t;
+            if (px * px + pz * pz <= R(1)) { cand[nc] = t; cf[nc++] = 1; }
+        }
+        if (nc < 2) return;
+        int imin = 0, imax = 0;
+        for (int k = 1; k < nc; k++) { if (cand[k] < cand[imin]) imin = k; if (cand[k] > cand[imax]) imax = k; }
+        spans_push(L, cand[imin], bound_info(leaf, cf[imin]), cand[imax], bound_info(leaf, cf[imax]));
+    }
+}
+
+#define HIT_FLIP_BIT (1 << 27)
+template <typename R> __device__ __noinline__ void spans_complement(const Spans<R>& A, Spans<R>& out) {
+    out.n = 0;
+    R pt = -gm<R>::inf(); int pi = HIT_NONE_LEAF;
+    for (int i = 0; i < A.n; i++) {
+        spans_push(out, pt, pi, A.t[2 * i], A.info[2 * i] ^ HIT_FLIP_BIT);
+        pt = A.t[2 * i + 1]; pi = A.info[2 * i + 1] ^ HIT_FLIP_BIT;
+    }
+    spans_push(out, pt, pi, gm<R>::inf(), HIT_NONE_LEAF);
+}
+
+template <typename R> __device__ __noinline__ void spans_intersect(const Spans<R>& A, const Spans<R>& B, Spans<R>& out) {
+    out.n = 0;
+    int i = 0, j = 0;
+    while (i < A.n && j < B.n) {
+        const bool ain = A.t[2 * i] >= B.t[2 * j], aout = A.t[2 * i + 1] <= B.t[2 * j + 1];
+        spans_push(out, ain ? A.t[2 * i] : B.t[2 * j], ain ? A.info[2 * i] : B.info[2 * j],
+                   aout ? A.t[2 * i + 1] : B.t[2 * j + 1], aout ? A.info[2 * i + 1] : B.info[2 * j + 1]);
+        if (aout) i++; else j++;
+    }
+}
+
+// csg_intersect: evaluate object `obj`'s postfix program for the world ray `w`; first surface with t > 0.
+// `mats` = WorldToObject of every leaf in the arithmetic type of this instantiation.
+template <typename R>
+__device__ __noinline__ bool csg_hit(const int* prog, int len, const int* kinds, const R* mats, const Ray<R>& w, R& t, int& code) {
+    Spans<R> st[GMLRT_CSG_MAX_STACK], t1, t2;
+    int sp = 0;
+    for (int k = 0; k < len; k++) {
+        const int op = prog[k];
+        if (op >= 0) {                                   // push a member leaf
+            if (sp >= GMLRT_CSG_MAX_STACK) return false;
+            Ray<R> o;
+            to_object(mats + (size_t)op * 12, w, o);
+            leaf_spans<R>(kinds[op], op, o, st[sp++]);
+        } else {
+            if (sp < 2) return false;
+            Spans<R>& a = st[sp - 2];
+            Spans<R>& b = st[sp - 1];
+            const int kind = -1 - op;
+            if (kind == GMLRT_NODE_INTERSECT) { spans_intersect(a, b, t1); a = t1; }
+            else if (kind == GMLRT_NODE_DIFFERENCE) { spans_complement(b, t1); spans_intersect(a, t1, t2); a = t2; }
+            else {                                       // union = complement(complement a  intersect  complement b)
+                spans_complement(a, t1); spans_complement(b, t2);
+                spans_intersect(t1, t2, a);
+                spans_complement(a, t1); a = t1;
+            }
+            sp--;
+        }
+    }
+    if (sp != 1) return false;
+    const Spans<R>& L = st[0];
+    for (int i = 0; i < L.n; i++) {
+        int b = -1;
+        if (L.t[2 * i] > R(0)) b = 2 * i;
+        else if (L.t[2 * i + 1] > R(0)) b = 2 * i + 1;
+        if (b < 0) continue;
+        if ((L.info[b] & HIT_LEAF_MASK) == HIT_NONE_LEAF) return false;   // the solid extends to infinity along the ray
+        t = L.t[b]; code = L.info[b];
+        return true;
+    }
+    return false;
+}
+
 // ------------------------------------------------------------------ TMA bulk copy + mbarrier (sm_90+/sm_100a)
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
@@ -355,7 +534,7 @@ __device__ __forceinline__ void cull_groups(const R* sm, int sm_base, int g0, in
 template <typename R> __device__ __forceinline__ void load_w2o(const R* w2o, int i, Mat34<R>& M) { load_mat(w2o, i, M); }   // global, same layout
 
 __device__ __forceinline__ int kind_of(const int* kind_begin, int i) {
-    return (i >= kind_begin[1]) + (i >= kind_begin[2]) + (i >= kind_begin[3]) + (i >= kind_begin[4]);
+    return (i >= kind_begin[1]) + (i >= kind_begin[2]) + (i >= kind_begin[3]) + (i >= kind_begin[4]) + (i >= kind_begin[5]);
 }
 
 template <typename R> __device__ __forceinline__ bool hit_any_kind(int kind, const Ray<R>& o, R& t, int& face) {
@@ -373,24 +552,41 @@ template <typename R> __device__ __forceinline__ bool hit_any_kind(int kind, con
 // discriminant is inside the rounding band |disc| < 2^-17 (hb^2 + |a c|) or the origin is that
 // close to the surface; then - and for the non-quadric kinds always - the test is redone in
 // double from the unrounded camera ray and the double matrices.
-static __device__ __noinline__ bool hit_f64(const double* w2o64, int kind, int i, const double* ray64, int cap, int ri, float& t, int& face) {
+template <typename R>
+__device__ __forceinline__ bool csg_object_hit(const DevScene<R>& sc, int i, const R* mats, const Ray<R>& w, R& t, int& code) {
+    const int2 rg = sc.csg_range[i - sc.kind_begin[K_CSG]];
+    return csg_hit<R>(sc.csg_prog + rg.x, rg.y, sc.kind, mats, w, t, code);
+}
+
+template <typename R>
+static __device__ __noinline__ bool hit_f64(const DevScene<R>& sc, int kind, int i, const double* ray64, int cap, int ri, float& t, int& code) {
     Ray<double> w, o;
     w.ox = ray64[ri]; w.oy = ray64[cap + ri]; w.oz = ray64[2 * (size_t)cap + ri];
     w.dx = ray64[3 * (size_t)cap + ri]; w.dy = ray64[4 * (size_t)cap + ri]; w.dz = ray64[5 * (size_t)cap + ri];
-    to_object(w2o64 + (size_t)i * 12, w, o);
     double td = 0.0;
-    const bool h = hit_any_kind<double>(kind, o, td, face);
+    bool h;
+    if (kind == K_CSG) {
+        const int2 rg = sc.csg_range[i - sc.kind_begin[K_CSG]];
+        h = csg_hit<double>(sc.csg_prog + rg.x, rg.y, sc.kind, sc.w2o64, w, td, code);
+    } else {
+        int face = 0;
+        to_object(sc.w2o64 + (size_t)i * 12, w, o);
+        h = hit_any_kind<double>(kind, o, td, face);
+        code = i | (face << 28);
+    }
     t = (float)td;
     return h;
 }
 
-// the exact test of ray `w` against object i, exactly as <Type>.Intersect would decide it
+// the exact test of ray `w` against object i, exactly as <Type>.Intersect would decide it; `code` is the hit
+// code stored in Level::hit: leaf | flip << 27 | face << 28 (for a CSG object the member leaf that was hit)
 template <typename R, bool ROBUST>
-__device__ __forceinline__ bool exact_hit(const DevScene<R>& sc, int i, const Ray<R>& w, const double* ray64, int cap, int ri, R& t, int& face) {
+__device__ __forceinline__ bool exact_hit(const DevScene<R>& sc, int i, const Ray<R>& w, const double* ray64, int cap, int ri, R& t, int& code) {
     const int kind = kind_of(sc.kind_begin, i);
     if constexpr (ROBUST) {
-        if (kind != K_SPHERE) { float tf; const bool h = hit_f64(sc.w2o64, kind, i, ray64, cap, ri, tf, face); t = (R)tf; return h; }
+        if (kind != K_SPHERE) { float tf; const bool h = hit_f64<R>(sc, kind, i, ray64, cap, ri, tf, code); t = (R)tf; return h; }
     }
+    if (kind == K_CSG) return csg_object_hit<R>(sc, i, sc.w2o, w, t, code);
     Mat34<R> M;
     load_w2o(sc.w2o, i, M);
     Ray<R> o;
@@ -404,15 +600,19 @@ __device__ __forceinline__ bool exact_hit(const DevScene<R>& sc, int i, const Ra
         const R disc = hb * hb - p;
         const R band = R(7.62939453125e-6) * (hb * hb + gm<R>::abs(p));     // 2^-17
         if (gm<R>::abs(disc) < band || gm<R>::abs(c) < R(7.62939453125e-6) * (oo + R(1))) {
-            float tf; const bool h = hit_f64(sc.w2o64, K_SPHERE, i, ray64, cap, ri, tf, face); t = (R)tf; return h;
+            float tf; const bool h = hit_f64<R>(sc, K_SPHERE, i, ray64, cap, ri, tf, code); t = (R)tf; return h;
         }
+        code = i;
         if (disc >= R(0)) {
             const R t0 = (-hb - gm<R>::sqrt(disc)) / a;
-            if (t0 > R(0)) { t = t0; face = 0; return true; }
+            if (t0 > R(0)) { t = t0; return true; }
         }
         return false;
     } else {
-        return hit_any_kind<R>(kind, o, t, face);
+        int face = 0;
+        const bool h = hit_any_kind<R>(kind, o, t, face);
+        code = i | (face << 28);
+        return h;
     }
 }
 
@@ -518,11 +718,11 @@ __device__ __forceinline__ void warp_add(unsigned long long* dst, unsigned long 
 template <typename R, bool ROBUST, bool COUNT> struct ClosestVisit {
     const DevScene<R>& sc; const Level<R>& lv;
     Ray<R> w[RPT]; int ri[RPT]; bool active[RPT];
-    R best_t[RPT]; int best_i[RPT], best_face[RPT];
-    unsigned long long n_exact;
-    __device__ ClosestVisit(const DevScene<R>& s, const Level<R>& l) : sc(s), lv(l), n_exact(0) {}
+    R best_t[RPT]; int best_code[RPT];
+    unsigned long long n_exact, n_flops;
+    __device__ ClosestVisit(const DevScene<R>& s, const Level<R>& l) : sc(s), lv(l), n_exact(0), n_flops(0) {}
     __device__ __forceinline__ bool setup(int r, int i, bool act, Ray<R>& out) {
-        ri[r] = i; active[r] = act; best_t[r] = R(0); best_i[r] = -1; best_face[r] = 0;
+        ri[r] = i; active[r] = act; best_t[r] = R(0); best_code[r] = -1;
         if (act) {
             const size_t cap = (size_t)lv.cap;
             out.ox = lv.ray[i]; out.oy = lv.ray[cap + i]; out.oz = lv.ray[2 * cap + i];
@@ -532,18 +732,18 @@ template <typename R, bool ROBUST, bool COUNT> struct ClosestVisit {
         return act;
     }
     __device__ __forceinline__ void exact(int r, int i) {
-        R t; int face;
-        if (COUNT) n_exact++;
-        if (!exact_hit<R, ROBUST>(sc, i, w[r], lv.ray64, lv.cap, ri[r], t, face)) return;
-        if (best_i[r] < 0 || t < best_t[r] || (t == best_t[r] && sc.scan_of[i] < sc.scan_of[best_i[r]])) {
-            best_t[r] = t; best_i[r] = i; best_face[r] = face;
+        R t; int code;
+        if (COUNT) { n_exact++; n_flops += (unsigned)sc.obj_flops[i]; }
+        if (!exact_hit<R, ROBUST>(sc, i, w[r], lv.ray64, lv.cap, ri[r], t, code)) return;
+        if (best_code[r] < 0 || t < best_t[r] || (t == best_t[r] && sc.scan_of[i] < sc.scan_of[best_code[r] & HIT_LEAF_MASK])) {
+            best_t[r] = t; best_code[r] = code;
         }
     }
     __device__ __forceinline__ bool done(int) const { return false; }
     __device__ __forceinline__ bool all_done() const { return false; }
     __device__ __forceinline__ void finish(int r) {
         if (active[r]) {
-            lv.hit[ri[r]] = best_i[r] < 0 ? -1 : (best_i[r] | (best_face[r] << 28));
+            lv.hit[ri[r]] = best_code[r];
             lv.t[ri[r]] = best_t[r];
         }
     }
@@ -556,6 +756,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_closest(const __grid_constant_
     scan_rays<R>(sc, ctr->count[level], chunk_objs, resident, V);
     if (COUNT) {
         warp_add(&ctr->exact_tests, V.n_exact);
+        warp_add(&ctr->exact_flops, V.n_flops);
     }
 }
 
@@ -567,9 +768,9 @@ template <typename R, bool COUNT> struct ShadowVisit {
     const DevScene<R>& sc; const ShadowQueue<R>& sq; unsigned char* occl;
     Ray<R> w[RPT]; int ri[RPT], skip[RPT]; bool active[RPT], occluded[RPT];
     R dist[RPT], in_len[RPT]; int first[RPT];
-    unsigned long long n_exact, n_occluded, cred_tests, cred_flops;
+    unsigned long long n_exact, n_flops, n_occluded, cred_tests, cred_flops;
     __device__ ShadowVisit(const DevScene<R>& s, const ShadowQueue<R>& q, unsigned char* o)
-        : sc(s), sq(q), occl(o), n_exact(0), n_occluded(0), cred_tests(0), cred_flops(0) {}
+        : sc(s), sq(q), occl(o), n_exact(0), n_flops(0), n_occluded(0), cred_tests(0), cred_flops(0) {}
     __device__ __forceinline__ bool setup(int r, int i, bool act, Ray<R>& out) {
         ri[r] = i; active[r] = act; occluded[r] = false; skip[r] = -1; dist[r] = R(0); in_len[r] = R(1); first[r] = 0x7fffffff;
         if (act) {
@@ -584,9 +785,9 @@ template <typename R, bool COUNT> struct ShadowVisit {
     }
     __device__ __forceinline__ void exact(int r, int i) {
         if (i == skip[r] || (!COUNT && occluded[r])) return;
-        R t; int face;
-        if (COUNT) n_exact++;
-        if (!exact_hit<R, false>(sc, i, w[r], nullptr, 0, 0, t, face)) return;
+        R t; int code;
+        if (COUNT) { n_exact++; n_flops += (unsigned)sc.obj_flops[i]; }
+        if (!exact_hit<R, false>(sc, i, w[r], nullptr, 0, 0, t, code)) return;
         if (t * in_len[r] < dist[r]) {
             occluded[r] = true;
             if (COUNT) first[r] = min(first[r], sc.scan_of[i]);
@@ -608,7 +809,7 @@ template <typename R, bool COUNT> struct ShadowVisit {
             if (last >= 0) {
                 unsigned long long tests = (unsigned long long)last + 1, flops = sc.cum_flops[last];
                 const int ss = skip[r] >= 0 ? sc.scan_of[skip[r]] : 0x7fffffff;
-                if (ss <= last) { tests--; flops -= (unsigned long long)sc.flops_of_kind[kind_of(sc.kind_begin, skip[r])]; }
+                if (ss <= last) { tests--; flops -= (unsigned long long)sc.obj_flops[skip[r]]; }
                 cred_tests += tests; cred_flops += flops;
             }
         }
@@ -625,6 +826,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_shadow(const __grid_constant__
     warp_add(&ctr->shadow_occluded, V.n_occluded);
     if (COUNT) {
         warp_add(&ctr->exact_tests, V.n_exact);
+        warp_add(&ctr->exact_flops, V.n_flops);
         warp_add(&ctr->shadow_tests, V.cred_tests);
         warp_add(&ctr->shadow_flops, V.cred_flops);
     }
@@ -824,7 +1026,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
     bool live = i < n;
     int h = live ? lv.hit[i] : -1;
     if (ids && live) {                                     // level 0 only: primary hit ids in (y, x, sample) order
-        ids[(size_t)y0 * sc.W * 4 + i] = h < 0 ? -1 : sc.scan_of[h & 0x0fffffff];
+        ids[(size_t)y0 * sc.W * 4 + i] = h < 0 ? -1 : sc.scan_of[h & HIT_LEAF_MASK];
     }
     live = live && h >= 0;
     Ray<R> w = {R(0), R(0), R(0), R(0), R(0), R(1)};
@@ -833,8 +1035,9 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
     for (int k = 0; k < 10; k++) mat[k] = R(0);
     int leaf = 0;
     if (live) {
-        leaf = h & 0x0fffffff;
+        leaf = h & HIT_LEAF_MASK;
         int face = h >> 28;
+        const bool flip = (h & HIT_FLIP_BIT) != 0;          // CSG: surface of a subtracted solid
         w.ox = lv.ray[i]; w.oy = lv.ray[cap + i]; w.oz = lv.ray[2 * cap + i];
         w.dx = lv.ray[3 * cap + i]; w.dy = lv.ray[4 * cap + i]; w.dz = lv.ray[5 * cap + i];
         const R t = lv.t[i];
@@ -884,6 +1087,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
             lv.hit[i] = -1;
         } else {
             P = mul_point(sc.o2w + (size_t)leaf * 12, p);
+            if (flip) N = neg(N);
         }
     }
     const R refl = mat[3], fuzz = mat[4], transp = mat[5], ior = mat[6];
@@ -917,7 +1121,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
             sq.q[slot] = so.x; sq.q[qc + slot] = so.y; sq.q[2 * qc + slot] = so.z;
             sq.q[3 * qc + slot] = ldir.x; sq.q[4 * qc + slot] = ldir.y; sq.q[5 * qc + slot] = ldir.z;
             sq.q[6 * qc + slot] = dist; sq.q[7 * qc + slot] = length(D);
-            sq.skip[slot] = leaf;
+            sq.skip[slot] = leaf < sc.n_leaves ? leaf : -1;      // a CSG object may shadow itself (oracle.c in_shadow)
             sq.target[slot] = i * sc.n_lights + li;
             occl[i * sc.n_lights + li] = 0;
         }
@@ -1112,16 +1316,24 @@ public:
 
     static constexpr bool kRobustPrimary = std::is_same<R, float>::value;   // f32: double re-test of borderline primary hits
 
-    void reset_totals() override { totals_ = TraceTotals(); need_ctr_reset_ = true; }
+    void reset_totals() override { totals_ = TraceTotals(); need_ctr_reset_ = true; ev_used_ = 0; ev_cls_.clear(); }
+    void set_profiling(bool on) override { profile_ = on; }
 
     int fetch_totals(TraceTotals& out, std::string& err) override {
         CU_TRY(cudaSetDevice(dev_));
         Counters c;
         CU_TRY(cudaMemcpy(&c, ctr_, sizeof c, cudaMemcpyDeviceToHost));
+        for (size_t k = 0; k + 1 < ev_used_; k++) {          // the stream has been synchronised by the caller
+            if (ev_cls_[k] < 0) continue;
+            float ms = 0;
+            CU_TRY(cudaEventElapsedTime(&ms, ev_pool_[k], ev_pool_[k + 1]));
+            totals_.ms_class[ev_cls_[k]] += ms; totals_.launches_class[ev_cls_[k]]++;
+        }
+        ev_used_ = 0; ev_cls_.clear();
         out = totals_;
         out.rays_reflect = c.rays_reflect; out.rays_refract = c.rays_refract;
         out.rays_shadow = c.rays_shadow; out.shadow_occluded = c.shadow_occluded;
-        out.shadow_tests = c.shadow_tests; out.shadow_flops = c.shadow_flops; out.exact_tests = c.exact_tests;
+        out.shadow_tests = c.shadow_tests; out.shadow_flops = c.shadow_flops; out.exact_tests = c.exact_tests; out.exact_flops = c.exact_flops;
         out.error = c.error;
         return GMLRT_OK;
     }
@@ -1154,6 +1366,8 @@ private:
         if (frame_) cudaFree(frame_);
         if (ids_) cudaFree(ids_);
         if (ctr_) cudaFree(ctr_);
+        for (cudaEvent_t e : ev_pool_) cudaEventDestroy(e);
+        ev_pool_.clear();
         if (stream_) cudaStreamDestroy(stream_);
         frame_ = nullptr; ids_ = nullptr; ctr_ = nullptr; stream_ = nullptr;
     }
@@ -1173,6 +1387,8 @@ private:
     uchar4* frame_ = nullptr; size_t frame_px_ = 0;
     int32_t* ids_ = nullptr; size_t ids_n_ = 0;
     Counters* ctr_ = nullptr;
+    bool profile_ = false;
+    std::vector<cudaEvent_t> ev_pool_; size_t ev_used_ = 0; std::vector<int> ev_cls_;
     TraceTotals totals_;
     bool need_ctr_reset_ = true;
     // scan kernel configuration
@@ -1184,52 +1400,85 @@ private:
 template <typename R>
 int Renderer<R>::upload(const HostScene& S, std::string& err) {
     CU_TRY(cudaSetDevice(dev_));
-    if (!S.csg.empty()) { err = "intersect/difference objects are not supported by this build"; return GMLRT_E_UNSUPPORTED; }
     if (S.depth > GMLRT_MAX_DEPTH) { err = "recursion depth above GMLRT_MAX_DEPTH"; return GMLRT_E_UNSUPPORTED; }
     CU_TRY(cudaStreamSynchronize(stream_));
     free_scene();
-    const int n = S.n_plain;
-    if (n >= (1 << 28)) { err = "too many leaves"; return GMLRT_E_UNSUPPORTED; }
-    // device order: stable sort by kind, so that equal kinds keep scan order
-    std::vector<int> order(n);
-    for (int i = 0; i < n; i++) order[i] = i;
+    // Device layout.  Objects (what closestHit / inShadow scan): the plain leaves, stably sorted by kind so that
+    // equal kinds keep scan order, then the CSG objects.  After them, the member leaves of the CSG objects.  Every
+    // per-leaf array has n_all entries (a CSG object's own entry is unused filler).
+    const int n_plain = S.n_plain, n_csg = (int)S.csg.size(), n = n_plain + n_csg;
+    const int n_members = (int)S.leaves.size() - n_plain, n_all = n + n_members;
+    if (n_all >= HIT_NONE_LEAF) { err = "too many leaves"; return GMLRT_E_UNSUPPORTED; }
+    if (n > 0xffff * GROUP) { err = "too many objects for the 16-bit group index of the scan kernels"; return GMLRT_E_UNSUPPORTED; }
+    std::vector<int> order(n_plain);
+    for (int i = 0; i < n_plain; i++) order[i] = i;
     std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return S.leaves[a].kind < S.leaves[b].kind; });
-    std::vector<R> w2o((size_t)n * 12), o2w((size_t)n * 12), fn((size_t)n * 18);
-    std::vector<double> w2o64(kRobustPrimary ? (size_t)n * 12 : 0);
-    std::vector<int> scan_of(n), surface(n), kind(n);
-    if (n > 0xffff * GROUP) { err = "too many leaves for the 16-bit group index of the scan kernels"; return GMLRT_E_UNSUPPORTED; }
+    std::vector<int> dev_of_host(S.leaves.size());                     // host leaf index -> device leaf index
+    for (int d = 0; d < n_plain; d++) dev_of_host[order[d]] = d;
+    for (int m = 0; m < n_members; m++) dev_of_host[n_plain + m] = n + m;
+    const size_t na = (size_t)std::max(n_all, 1);
+    std::vector<R> w2o(na * 12, R(0)), o2w(na * 12, R(0)), fn(na * 18, R(0));
+    std::vector<double> w2o64(kRobustPrimary ? na * 12 : 0, 0.0);
+    std::vector<int> scan_of(na, 0), surface(na, 0), kind(na, K_SPHERE), obj_flops(std::max(n, 1), 0);
     const int n_cull = (n + GROUP - 1) / GROUP * GROUP;
     std::vector<R> cull((size_t)std::max(n_cull, GROUP) * 4);
     std::vector<unsigned long long> cum_flops(std::max(n, 1), 0ull);
     DevScene<R> sc{};
-    sc.n_leaves = n; sc.n_cull = n_cull;
-    for (int k = 0; k < K_COUNT; k++) sc.flops_of_kind[k] = (int)kFlopsByKind[k];
-    for (int k = 0; k <= K_COUNT; k++) sc.kind_begin[k] = 0;
-    for (int d = 0; d < n; d++) {
-        const HostLeaf& L = S.leaves[order[d]];
-        for (int k = 0; k < 12; k++) { w2o[(size_t)d * 12 + k] = (R)L.w2o[k]; o2w[(size_t)d * 12 + k] = (R)L.o2w[k]; }
-        if (kRobustPrimary) for (int k = 0; k < 12; k++) w2o64[(size_t)d * 12 + k] = L.w2o[k];
-        for (int f = 0; f < 6; f++) for (int k = 0; k < 3; k++) fn[(size_t)d * 18 + 3 * f + k] = (R)L.face_normal[f][k];
-        scan_of[d] = L.scan_index; surface[d] = (int)L.surface; kind[d] = L.kind;
-        sc.kind_begin[L.kind + 1]++;
-        // cull record: bounding sphere, radius inflated so that a reject is always a true miss (see the scan section)
-        double C[3], Rw;
-        leaf_bound(L.kind, L.o2w, C, Rw);
+    sc.n_leaves = n; sc.n_cull = n_cull; sc.n_all = n_all;
+    for (int k = 0; k <= K_OBJ_KINDS; k++) sc.kind_begin[k] = 0;
+    auto put_cull = [&](int d, const double* C, double Rw) {
+        // bounding sphere, radius inflated so that a reject is always a true miss (see the scan section)
         const R cx = (R)C[0], cy = (R)C[1], cz = (R)C[2];
         const double cc = (double)cx * cx + (double)cy * cy + (double)cz * cz;
         const double Rm = Rw * (1.0 + CullMargin<R>::radius);
         double K = cc - Rm * Rm - CullMargin<R>::rel * cc;
         if (!(K == K) || std::isinf(Rw)) K = -INFINITY;                      // unbounded (plane) or degenerate: never rejected
-        cull[(size_t)d * 4 + 0] = cx; cull[(size_t)d * 4 + 1] = cy; cull[(size_t)d * 4 + 2] = cz; cull[(size_t)d * 4 + 3] = (R)K;
-        if ((double)cull[(size_t)d * 4 + 3] > K) cull[(size_t)d * 4 + 3] = std::nextafter(cull[(size_t)d * 4 + 3], (R)-INFINITY);
-        cum_flops[L.scan_index] = (unsigned long long)kFlopsByKind[L.kind];
+        R* rec = &cull[(size_t)d * 4];
+        rec[0] = std::isinf(Rw) ? R(0) : cx; rec[1] = std::isinf(Rw) ? R(0) : cy; rec[2] = std::isinf(Rw) ? R(0) : cz; rec[3] = (R)K;
+        if ((double)rec[3] > K) rec[3] = std::nextafter(rec[3], (R)-INFINITY);
+    };
+    auto put_leaf = [&](int d, const HostLeaf& L) {
+        for (int k = 0; k < 12; k++) { w2o[(size_t)d * 12 + k] = (R)L.w2o[k]; o2w[(size_t)d * 12 + k] = (R)L.o2w[k]; }
+        if (kRobustPrimary) for (int k = 0; k < 12; k++) w2o64[(size_t)d * 12 + k] = L.w2o[k];
+        for (int f = 0; f < 6; f++) for (int k = 0; k < 3; k++) fn[(size_t)d * 18 + 3 * f + k] = (R)L.face_normal[f][k];
+        surface[d] = (int)L.surface; kind[d] = L.kind;
+    };
+    for (int d = 0; d < n_plain; d++) {
+        const HostLeaf& L = S.leaves[order[d]];
+        put_leaf(d, L);
+        scan_of[d] = L.scan_index;
+        sc.kind_begin[L.kind + 1]++;
+        double C[3], Rw;
+        leaf_bound(L.kind, L.o2w, C, Rw);
+        put_cull(d, C, Rw);
+        obj_flops[d] = (int)kFlopsByKind[L.kind];
+        cum_flops[L.scan_index] = (unsigned long long)obj_flops[d];
+    }
+    std::vector<int> csg_prog; std::vector<int2> csg_range(std::max(n_csg, 1), make_int2(0, 0));
+    for (int c = 0; c < n_csg; c++) {
+        const HostCsgObject& obj = S.csg[c];
+        const int d = n_plain + c;
+        scan_of[d] = obj.scan_index; kind[d] = K_CSG;
+        sc.kind_begin[K_CSG + 1]++;
+        put_cull(d, obj.C, obj.R);
+        obj_flops[d] = (int)obj.flops;
+        cum_flops[obj.scan_index] = (unsigned long long)obj_flops[d];
+        csg_range[c] = make_int2((int)csg_prog.size(), (int)obj.postfix.size());
+        for (const HostCsgOp& op : obj.postfix) {
+            if (op.op < 0) {
+                const int dm = dev_of_host[op.leaf];
+                put_leaf(dm, S.leaves[op.leaf]);
+                scan_of[dm] = obj.scan_index;                     // ids and tie-breaks see the owning object
+                csg_prog.push_back(dm);
+            } else csg_prog.push_back(-1 - op.op);
+        }
     }
     for (int d = n; d < std::max(n_cull, GROUP); d++) {                      // padding: always rejected
         cull[(size_t)d * 4 + 0] = cull[(size_t)d * 4 + 1] = cull[(size_t)d * 4 + 2] = R(0);
         cull[(size_t)d * 4 + 3] = (R)INFINITY;
     }
     for (int i = 1; i < n; i++) cum_flops[i] += cum_flops[i - 1];
-    for (int k = 0; k < K_COUNT; k++) sc.kind_begin[k + 1] += sc.kind_begin[k];
+    for (int k = 0; k < K_OBJ_KINDS; k++) sc.kind_begin[k + 1] += sc.kind_begin[k];
     kind_host_ = kind;
     std::vector<DevLight<R>> lights(S.lights.size());
     for (size_t i = 0; i < S.lights.size(); i++) {
@@ -1257,9 +1506,10 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     int rc;
     double* d_w2o64 = nullptr;
     if ((rc = to_device(w2o64, &d_w2o64, err))) return rc;
-    R* d_cull; unsigned long long* d_cum;
-    if ((rc = to_device(cull, &d_cull, err)) || (rc = to_device(cum_flops, &d_cum, err))) return rc;
-    sc.cull = d_cull; sc.cum_flops = d_cum;
+    R* d_cull; unsigned long long* d_cum; int *d_prog, *d_oflops; int2* d_range;
+    if ((rc = to_device(cull, &d_cull, err)) || (rc = to_device(cum_flops, &d_cum, err)) || (rc = to_device(csg_prog, &d_prog, err)) ||
+        (rc = to_device(csg_range, &d_range, err)) || (rc = to_device(obj_flops, &d_oflops, err))) return rc;
+    sc.cull = d_cull; sc.cum_flops = d_cum; sc.csg_prog = d_prog; sc.csg_range = d_range; sc.obj_flops = d_oflops;
     R *d_w2o, *d_o2w, *d_fn, *d_fpool; int *d_scan, *d_surf, *d_kind, *d_itab; uint32_t* d_code;
     DevLight<R>* d_lights; DevSurface<R>* d_surfaces;
     if ((rc = to_device(w2o, &d_w2o, err)) || (rc = to_device(o2w, &d_o2w, err)) || (rc = to_device(fn, &d_fn, err)) ||
@@ -1381,9 +1631,20 @@ int Renderer<R>::trace_rows(int y0, int y1, bool counting, std::string& err) {
         ids_n_ = (size_t)W * sc_.H * 4;
     }
     const int wide = sms_ * 16;
+    // profiling: one event before every launch; launches on one stream serialise, so consecutive events bracket a kernel
+    auto mark = [&](int cls) -> int {
+        if (!profile_) return GMLRT_OK;
+        if (ev_used_ == ev_pool_.size()) { cudaEvent_t e; CU_TRY(cudaEventCreate(&e)); ev_pool_.push_back(e); }
+        CU_TRY(cudaEventRecord(ev_pool_[ev_used_++], stream_));
+        ev_cls_.push_back(cls);
+        return GMLRT_OK;
+    };
+    int mrc;
+#define MARK(cls) do { if ((mrc = mark(cls))) return mrc; } while (0)
     for (int ty = y0; ty < y1; ty += rows_per_tile_) {
         const int rows = std::min(rows_per_tile_, y1 - ty);
         const int S = rows * W * 4;
+        MARK(KC_GEN);
         k_gen<R><<<(S + 255) / 256, 256, 0, stream_>>>(sc_, levels_[0], ctr_, ty, rows);
         totals_.launches++;
         totals_.rays_primary += (unsigned long long)S;
@@ -1391,6 +1652,7 @@ int Renderer<R>::trace_rows(int y0, int y1, bool counting, std::string& err) {
             const int cap_blocks = (levels_[l].cap + SHADE_THREADS - 1) / SHADE_THREADS;
             const bool robust = (l == 0 && kRobustPrimary);
             const int gc = grid_closest_[robust][counting];
+            MARK(robust ? KC_CLOSEST_PRIMARY : KC_CLOSEST);
             if (robust) {
                 if (counting) k_closest<R, kRobustPrimary, true><<<gc, SCAN_THREADS, scan_smem_, stream_>>>(sc_, levels_[l], ctr_, l, chunk_objs_, resident_);
                 else k_closest<R, kRobustPrimary, false><<<gc, SCAN_THREADS, scan_smem_, stream_>>>(sc_, levels_[l], ctr_, l, chunk_objs_, resident_);
@@ -1399,11 +1661,13 @@ int Renderer<R>::trace_rows(int y0, int y1, bool counting, std::string& err) {
                 else k_closest<R, false, false><<<gc, SCAN_THREADS, scan_smem_, stream_>>>(sc_, levels_[l], ctr_, l, chunk_objs_, resident_);
             }
             const bool spawn = l + 1 < depth_eff_;
+            MARK(KC_SHADE);
             k_shade<R><<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
                 sc_, levels_[l], spawn ? levels_[l + 1] : levels_[l], sq_, occl_[l], ctr_, l, spawn ? 1 : 0,
                 (counting && l == 0) ? ids_ : nullptr, ty);
             totals_.launches += 2;
             if (sc_.n_lights > 0) {
+                MARK(KC_SHADOW);
                 if (counting) k_shadow<R, true><<<grid_shadow_[1], SCAN_THREADS, scan_smem_, stream_>>>(sc_, sq_, occl_[l], ctr_, chunk_objs_, resident_);
                 else k_shadow<R, false><<<grid_shadow_[0], SCAN_THREADS, scan_smem_, stream_>>>(sc_, sq_, occl_[l], ctr_, chunk_objs_, resident_);
                 CU_TRY(cudaMemsetAsync(&ctr_->shadow_count, 0, sizeof(int), stream_));
@@ -1412,13 +1676,17 @@ int Renderer<R>::trace_rows(int y0, int y1, bool counting, std::string& err) {
         }
         for (int l = depth_eff_ - 1; l >= 0; l--) {
             const int cap_blocks = (levels_[l].cap + SHADE_THREADS - 1) / SHADE_THREADS;
+            MARK(KC_RESOLVE);
             k_resolve<R><<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
                 sc_, levels_[l], l > 0 ? levels_[l - 1] : levels_[l], occl_[l], ctr_, l, samples_, sample_cap_);
             totals_.launches++;
         }
+        MARK(KC_PIXELS);
         k_pixels<R><<<(rows * W + 255) / 256, 256, 0, stream_>>>(sc_, samples_, sample_cap_, frame_, ty, rows);
         totals_.launches++;
     }
+    MARK(-1);
+#undef MARK
     CU_TRY(cudaGetLastError());
     return GMLRT_OK;
 }

@@ -11,10 +11,15 @@
 
 namespace gmlrt {
 
+// kernel classes for the profiling mode (gmlrt_set_profiling)
+enum KernelClass { KC_GEN = 0, KC_CLOSEST_PRIMARY = 1, KC_CLOSEST = 2, KC_SHADOW = 3, KC_SHADE = 4, KC_RESOLVE = 5, KC_PIXELS = 6, KC_COUNT = 7 };
+
 struct TraceTotals {                   // summed over the tiles a device rendered
     unsigned long long rays_primary = 0, rays_reflect = 0, rays_refract = 0, rays_shadow = 0, shadow_occluded = 0;
     unsigned long long shadow_tests = 0, shadow_flops = 0;   // credited (reference scan order), counting mode
-    unsigned long long cull_tests = 0, exact_tests = 0;      // executed: first-phase (all pairs) and second-phase tests
+    unsigned long long cull_tests = 0, exact_tests = 0, exact_flops = 0;   // executed: first-phase (all pairs) and second-phase tests
+    double ms_class[KC_COUNT] = {0, 0, 0, 0, 0, 0, 0};         // profiling mode: device time per kernel class
+    unsigned long long launches_class[KC_COUNT] = {0, 0, 0, 0, 0, 0, 0};
     unsigned long long launches = 0;
     int error = 0;
 };
@@ -29,6 +34,7 @@ public:
     // after the stream is synchronised: fetch counters accumulated since reset_totals()
     virtual int fetch_totals(TraceTotals& out, std::string& err) = 0;
     virtual void reset_totals() = 0;
+    virtual void set_profiling(bool on) = 0;   // record an event before every launch; per-class times land in TraceTotals
     virtual uint8_t* frame() = 0;          // device RGBA8 frame, full size (only own rows valid)
     virtual int32_t* primary_ids() = 0;    // device [H][W][4] scan-order ids (counting mode), may be null
     virtual cudaStream_t stream() = 0;

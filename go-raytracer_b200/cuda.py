@@ -24,7 +24,10 @@ class Stats(ctypes.Structure):
                 ("rays_refract", ctypes.c_uint64), ("rays_shadow", ctypes.c_uint64), ("shadow_occluded", ctypes.c_uint64),
                 ("leaf_tests", ctypes.c_uint64), ("flops_credited", ctypes.c_double), ("kernel_launches", ctypes.c_uint64),
                 ("n_devices", ctypes.c_uint32), ("n_leaves", ctypes.c_uint32),
-                ("cull_tests", ctypes.c_uint64), ("exact_tests", ctypes.c_uint64)]
+                ("cull_tests", ctypes.c_uint64), ("exact_tests", ctypes.c_uint64), ("flops_executed", ctypes.c_double),
+                ("ms_class", ctypes.c_double * 7), ("launches_class", ctypes.c_uint64 * 7)]
+
+    KERNEL_CLASSES = ("gen", "closest_primary", "closest", "shadow", "shade", "resolve", "pixels")
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -40,7 +43,7 @@ class GmlrtError(RuntimeError):
         self.code = code
 
 
-EXPORTS = ("gmlrt_set_partition", "gmlrt_frame_device", "gmlrt_create", "gmlrt_render", "gmlrt_upload", "gmlrt_trace", "gmlrt_download", "gmlrt_set_counting",
+EXPORTS = ("gmlrt_measure_fp32_tflops", "gmlrt_set_profiling", "gmlrt_set_partition", "gmlrt_frame_device", "gmlrt_create", "gmlrt_render", "gmlrt_upload", "gmlrt_trace", "gmlrt_download", "gmlrt_set_counting",
            "gmlrt_primary_hits", "gmlrt_stream", "gmlrt_last_error", "gmlrt_destroy", "gmlrt_blob_version", "gmlrt_build_info")
 
 _lib = None
@@ -61,6 +64,8 @@ def load():
         L.gmlrt_trace.restype, L.gmlrt_trace.argtypes = i, [p, ctypes.POINTER(Stats)]
         L.gmlrt_download.restype, L.gmlrt_download.argtypes = i, [p, p, sz]
         L.gmlrt_set_counting.restype, L.gmlrt_set_counting.argtypes = i, [p, i]
+        L.gmlrt_measure_fp32_tflops.restype, L.gmlrt_measure_fp32_tflops.argtypes = ctypes.c_double, [i]
+        L.gmlrt_set_profiling.restype, L.gmlrt_set_profiling.argtypes = i, [p, i]
         L.gmlrt_primary_hits.restype, L.gmlrt_primary_hits.argtypes = i, [p, p, sz]
         L.gmlrt_stream.restype, L.gmlrt_stream.argtypes = p, [p]
         L.gmlrt_set_partition.restype, L.gmlrt_set_partition.argtypes = i, [p, i, i]
@@ -71,6 +76,11 @@ def load():
         L.gmlrt_build_info.restype, L.gmlrt_build_info.argtypes = ctypes.c_char_p, []
         _lib = L
     return _lib
+
+
+def measure_fp32_tflops(device=0):
+    """FFMA-chain microbenchmark on `device` (TFLOP/s): the measured FP32 roofline denominator."""
+    return float(load().gmlrt_measure_fp32_tflops(int(device)))
 
 
 class Context:
@@ -133,6 +143,9 @@ class Context:
 
     def set_counting(self, enabled):
         self._check(self._L.gmlrt_set_counting(self._h, 1 if enabled else 0))
+
+    def set_profiling(self, enabled):
+        self._check(self._L.gmlrt_set_profiling(self._h, 1 if enabled else 0))
 
     def primary_hits(self):
         w, h = self._size

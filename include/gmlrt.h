@@ -188,6 +188,9 @@ typedef struct gmlrt_stats {
     uint32_t n_leaves;
     uint64_t cull_tests;        /* executed: first-phase bounding-sphere tests (every query x every object) */
     uint64_t exact_tests;       /* executed: second-phase <Type>.Intersect tests on the survivors (counting mode) */
+    double   flops_executed;    /* 14 per cull test (7 FFMA) + the per-leaf-type table per exact test (counting mode) */
+    double   ms_class[7];       /* profiling mode: device ms per kernel class: gen, closest(primary), closest, shadow, shade, resolve, pixels */
+    uint64_t launches_class[7]; /* ... and launches per class */
 } gmlrt_stats;
 
 /* Create a context on `n` devices (`devices` = CUDA ordinals; n >= 1).  With n > 1 the
@@ -222,6 +225,10 @@ void* gmlrt_frame_device(gmlrt_ctx*);
  * gmlrt_stats; counting costs a few percent, so timed runs leave it off.              */
 int gmlrt_set_counting(gmlrt_ctx*, int enabled);
 
+/* Enable (1) / disable (0) per-kernel-class timing: a CUDA event is recorded before every launch and
+ * gmlrt_stats.ms_class / launches_class are filled.  bench.py uses it for the roofline of the scan kernels. */
+int gmlrt_set_profiling(gmlrt_ctx*, int enabled);
+
 /* Per-sample id of the object hit by each primary ray (-1 = background), 4*W*H int32 in
  * (y, x, sample) order, from the last trace.  For the "zero primary hit/miss flips"
  * check of the north_star.  Requires gmlrt_set_counting(ctx, 1) before the trace.      */
@@ -230,6 +237,10 @@ int gmlrt_primary_hits(gmlrt_ctx*, int32_t* ids, size_t n_ids);
 /* CUDA stream of device 0 that gmlrt_trace launches on (a cudaStream_t), so a caller
  * can bracket it with its own events.                                                 */
 void* gmlrt_stream(gmlrt_ctx*);
+
+/* FP32 FFMA throughput of `device` in TFLOP/s from an 8-chain FFMA microbenchmark (about 50 ms): the
+ * measured denominator of the FP32 roofline (MEASURED_PEAKS.json holds no FP32 figure).  < 0 on error. */
+double gmlrt_measure_fp32_tflops(int device);
 
 const char* gmlrt_last_error(gmlrt_ctx*);   /* text for the last non-OK code; never NULL */
 void gmlrt_destroy(gmlrt_ctx*);

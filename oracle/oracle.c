@@ -83,6 +83,7 @@ typedef struct {
     double o2w[12], w2o[12];
     v3 face_normal_world[6];   /* plane: [0]; cube: per face (raytracer.go:764-774, 799-803) */
     uint32_t csg_root;         /* CSG objects: node index of the subtree root */
+    double flops;              /* credited flops of one test of this object */
 } object_t;
 
 typedef struct {
@@ -129,13 +130,18 @@ static void init_leaf(object_t* o, const gmlrt_node* n) {
 
 static int is_leaf_kind(uint32_t k) { return k >= 16 && k <= 20; }
 
-static int mark_csg_leaves(scene_t* s, uint32_t ni, int depth) {
+/* a CSG object is credited with its member leaves' table flops, +2 per quadric because both roots are needed */
+static int mark_csg_leaves(scene_t* s, uint32_t ni, int depth, double* flops) {
     if (ni >= s->h->n_nodes || depth > 4096) return -1;
     const gmlrt_node* n = &s->nodes[ni];
-    if (is_leaf_kind(n->kind)) { init_leaf(&s->leaves[ni], n); return 0; }
+    if (is_leaf_kind(n->kind)) {
+        init_leaf(&s->leaves[ni], n);
+        *flops += kind_flops((int)n->kind) + ((n->kind == GMLRT_NODE_SPHERE || n->kind == GMLRT_NODE_CYLINDER || n->kind == GMLRT_NODE_CONE) ? 2 : 0);
+        return 0;
+    }
     if (n->kind > 2) return -1;
-    if (mark_csg_leaves(s, n->a, depth + 1)) return -1;
-    return mark_csg_leaves(s, n->b, depth + 1);
+    if (mark_csg_leaves(s, n->a, depth + 1, flops)) return -1;
+    return mark_csg_leaves(s, n->b, depth + 1, flops);
 }
 
 /* returns 0 or a GMLRT_E_* code */
@@ -180,18 +186,20 @@ static int scene_init(scene_t* s, const void* blob, size_t nbytes) {
             if (n->a >= h->n_nodes || n->b >= h->n_nodes || qt + 2 > h->n_nodes + 1) { rc = GMLRT_E_BAD_BLOB; break; }
             q[qt++] = n->a; q[qt++] = n->b;
         } else if (is_leaf_kind(n->kind)) {
-            init_leaf(&s->objs[s->n_objs++], n);
+            init_leaf(&s->objs[s->n_objs], n);
+            s->objs[s->n_objs].flops = kind_flops((int)n->kind);
+            s->n_objs++;
         } else if (n->kind == GMLRT_NODE_INTERSECT || n->kind == GMLRT_NODE_DIFFERENCE) {
             /* extension: the reference rejects these (raytracer.go:825-826) */
             object_t* o = &s->objs[s->n_objs++];
             o->kind = -1; o->csg_root = ni;
-            if (mark_csg_leaves(s, ni, 0)) rc = GMLRT_E_BAD_BLOB;
+            if (mark_csg_leaves(s, ni, 0, &o->flops)) rc = GMLRT_E_BAD_BLOB;
         } else {
             rc = GMLRT_E_UNSUPPORTED;
         }
     }
     free(q);
-    for (int i = 0; i < s->n_objs; i++) s->flops_all += kind_flops(s->objs[i].kind);
+    for (int i = 0; i < s->n_objs; i++) s->flops_all += s->objs[i].flops;
     return rc;
 }
 
@@ -461,7 +469,7 @@ static int in_shadow(const scene_t* s, const hit_t* hit, const hitex_t* ex, v3 l
     c->rays_shadow++;
     for (int i = 0; i < s->n_objs; i++) {
         if (i == hit->obj && s->objs[i].kind >= 0) continue;   /* CSG objects may shadow themselves */
-        c->leaf_tests++; c->flops += kind_flops(s->objs[i].kind);
+        c->leaf_tests++; c->flops += s->objs[i].flops;
         hit_t sh;
         if (!object_intersect(s, i, sr, &sh)) continue;
         if (sh.t * in_len < dist) { c->shadow_occluded++; return 1; }

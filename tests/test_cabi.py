@@ -13,7 +13,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def test_library_exports_every_declared_symbol():
     hdr = open(os.path.join(ROOT, "include", "gmlrt.h")).read()
-    declared = set(re.findall(r"\b(gmlrt_[a-z_]+)\s*\(", hdr))
+    declared = set(re.findall(r"\b(gmlrt_[a-z0-9_]+)\s*\(", hdr))
     assert declared == set(cuda.EXPORTS)
     lib = cuda.load()
     for name in declared:
@@ -59,3 +59,22 @@ def test_synthetic_scene_generators_are_deterministic():
     assert sum(1 for n in d["nodes"] if n["kind"] == 16) == 16 and [l["kind"] for l in d["lights"]] == [0, 1]
     d = lowering.describe(scenes.to_blob(scenes.csg(64, 36, groups=(2, 2))))
     assert sum(1 for n in d["nodes"] if n["kind"] in (1, 2)) == 12 and all(l["kind"] == 2 for l in d["lights"])
+
+
+def test_stats_mirrors_match_header_size():
+    """gmlrt_stats is filled by C code through a pointer: both ctypes mirrors must be as large as the C struct."""
+    import ctypes
+    import oracle
+    hdr = open(os.path.join(ROOT, "include", "gmlrt.h")).read()
+    body = re.search(r"typedef struct gmlrt_stats \{(.*?)\} gmlrt_stats;", hdr, re.S).group(1)
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    size = 0
+    for decl in body.split(";"):
+        m = re.match(r"\s*(double|uint64_t|uint32_t)\s+(.*)", decl.strip(), re.S)
+        if not m:
+            continue
+        width = {"double": 8, "uint64_t": 8, "uint32_t": 4}[m.group(1)]
+        for name in m.group(2).split(","):
+            dim = re.search(r"\[(\d+)\]", name)
+            size += width * (int(dim.group(1)) if dim else 1)
+    assert ctypes.sizeof(cuda.Stats) == size == ctypes.sizeof(oracle.Stats)
