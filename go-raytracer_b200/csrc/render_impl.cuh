@@ -55,7 +55,6 @@ template <typename R> struct DevScene {
     const int2* csg_range;         // [n_csg] (offset, length) into csg_prog, indexed by object - kind_begin[K_CSG]
     const int* obj_flops;          // [n_leaves] credited flops of one test of the object
     int n_cull;                    // n_leaves rounded up to a multiple of GROUP
-    const R* cull;                 // [n_cull][4] bounding sphere centre xyz, K = |C|^2 - R^2 - margin   (hot: staged in smem)
     const unsigned long long* cum_flops;   // [n] credited flops of scan-order objects 0..s
     const R* w2o;                  // [n][12] rows 0..2 of WorldToObject
     const int* scan_of;            // device index -> scan-order index (tie-breaks, ids)
@@ -86,16 +85,16 @@ template <typename R> struct Level {
     int cap;
 };
 
-template <typename R> struct ShadowQueue {
+template <typename R> struct ShadowQueue {      // one segment of `per_light` slots per light: slot = light * per_light + k
     R* q;         // [8][cap] origin xyz, direction xyz, distance to light, |incoming direction|
     int* skip;    // [cap] device leaf index of the shaded object (inShadow skips it)
     int* target;  // [cap] node * n_lights + light
-    int cap;
+    int* count;   // [n_lights] queued rays per light
+    int cap, per_light;
 };
 
 struct Counters {                  // device-resident, zeroed per trace
     int count[GMLRT_MAX_DEPTH + 1];     // rays per level
-    int shadow_count;
     int error;
     unsigned long long rays_reflect, rays_refract, rays_shadow, shadow_occluded;
     unsigned long long shadow_tests, shadow_flops;   // credited: the reference's scan up to its first occluder (counting mode)
@@ -456,24 +455,27 @@ __device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem
 // closestHit / inShadow visit every object for every ray (raytracer.go:469-483, 411-429).  The scan
 // kernels keep that all-pairs structure (no hierarchy), but split each ray x object test in two:
 //
-//   cull   7 FFMA + 1 compare against the object's bounding sphere, from a 16-byte (f32) record in
-//          shared memory:  reject iff |C-o|^2 - ((C-o).d^)^2 > R^2  (+ a rounding margin, so a reject
-//          is always a true miss).  Expanded so that everything per-ray is hoisted:
-//              A = C.(-2o) + K          K = |C|^2 - R^2 - margin|C|^2   (per object)
-//              B = C.d^ - o.d^
-//              reject  <=>  A - B^2 > -|o|^2 + margin|o|^2
-//   exact  the reference's own test (<Type>.Intersect) - only for the survivors, which each ray
-//          collects as (group, 16-bit mask) entries in a private shared-memory list and processes
-//          every FLUSH_GROUPS groups, so that lanes run their exact tests side by side instead of
-//          one lane at a time.
+//   cull   a few FFMA + 1 compare against the object's bounding sphere (centre C, radius R), from a
+//          16-byte (f32) record in shared memory; the radius carries a rounding margin so that a reject
+//          is always a true miss.  Three record/ray "families", by what the rays of a launch share:
+//            GENERAL  any ray (o, d^):  reject iff |C-o|^2 - ((C-o).d^)^2 > R^2, expanded so that
+//                     everything per-ray is hoisted:  A = C.(-2o) + K,  K = |C|^2 - R^2 - margin,
+//                     B = C.d^ - o.d^,  reject <=> A - B^2 > -|o|^2 + margin          7 FFMA + compare
+//            PIVOT    rays whose LINE passes through one point V (camera rays: the eye; shadow rays of a
+//                     point / spot light: the light):  record p = C - V, K = |p|^2 - R^2 - margin,
+//                     B = p.d^,  reject <=> K - B^2 > 0                                 4 FP + compare
+//            AXIS     rays with one common direction (shadow rays of a directional light): project on
+//                     the plane orthogonal to it,  du = Cu - ou, dv = Cv - ov,
+//                     reject <=> du^2 + dv^2 - R^2 > 0                                  4 FP + compare
+//          The survivors of a window of GROUP = 64 objects are collected as one 64-bit mask per ray.
+//   exact  after each window every ray walks the set bits of its mask and runs the reference's own test
+//          (<Type>.Intersect, or the CSG span lists) on those objects.  Deferring to the end of the window
+//          makes the lanes of a warp run their k-th exact tests side by side instead of one lane at a time.
 //
 // Each thread carries RPT rays so that the record load and the loop overhead are shared.
 constexpr int SCAN_THREADS = 256;
-constexpr int RPT = 2;                      // rays per thread
-constexpr int GROUP = 16;                   // objects per survivor bitmask
-constexpr int FLUSH_GROUPS = 8;             // groups between two exact-test flushes = list capacity per ray
-constexpr int RAYS_PER_BLOCK = SCAN_THREADS * RPT;
-constexpr size_t LIST_BYTES = (size_t)FLUSH_GROUPS * RAYS_PER_BLOCK * sizeof(uint32_t);
+constexpr int GROUP = 64;                   // objects per window: one 64-bit survivor mask per ray, kept in two registers
+enum CullFamily { CULL_GENERAL = 0, CULL_PIVOT = 1, CULL_AXIS = 2 };
 
 __device__ __forceinline__ float fma_(float a, float b, float c) { return __fmaf_rn(a, b, c); }
 __device__ __forceinline__ double fma_(double a, double b, double c) { return __fma_rn(a, b, c); }
@@ -494,40 +496,72 @@ __device__ __forceinline__ Cull4<double> load_cull(const double* sm, int i) {
     return c;
 }
 
-template <typename R> struct CullRay { R o2x, o2y, o2z, dx, dy, dz, nod, cmp; };
+// What a launch's cull table was built for (host: Renderer::build_cull_table).
+template <typename R> struct CullFrame { int family; R e1[3], e2[3]; };   // AXIS: orthonormal basis of the plane orthogonal to the common direction
 
-template <typename R> __device__ __forceinline__ void make_cull_ray(const Ray<R>& w, bool active, CullRay<R>& c) {
-    const R inv = R(1) / gm<R>::sqrt(fma_(w.dx, w.dx, fma_(w.dy, w.dy, w.dz * w.dz)));
-    c.dx = w.dx * inv; c.dy = w.dy * inv; c.dz = w.dz * inv;
-    c.o2x = R(-2) * w.ox; c.o2y = R(-2) * w.oy; c.o2z = R(-2) * w.oz;
-    c.nod = -fma_(w.ox, c.dx, fma_(w.oy, c.dy, w.oz * c.dz));
-    const R oo = fma_(w.ox, w.ox, fma_(w.oy, w.oy, w.oz * w.oz));
-    c.cmp = active ? fma_(oo, R(CullMargin<R>::rel), -oo) : -gm<R>::inf();    // inactive: everything is rejected
-}
+template <typename R, int FAMILY> struct CullRay;
+template <typename R> struct CullRay<R, CULL_GENERAL> {
+    R o2x, o2y, o2z, dx, dy, dz, nod, cmp;
+    __device__ __forceinline__ void init(const Ray<R>& w, bool active, const CullFrame<R>&) {
+        const R inv = R(1) / gm<R>::sqrt(fma_(w.dx, w.dx, fma_(w.dy, w.dy, w.dz * w.dz)));
+        dx = w.dx * inv; dy = w.dy * inv; dz = w.dz * inv;
+        o2x = R(-2) * w.ox; o2y = R(-2) * w.oy; o2z = R(-2) * w.oz;
+        nod = -fma_(w.ox, dx, fma_(w.oy, dy, w.oz * dz));
+        const R oo = fma_(w.ox, w.ox, fma_(w.oy, w.oy, w.oz * w.oz));
+        cmp = active ? fma_(oo, R(CullMargin<R>::rel), -oo) : -gm<R>::inf();    // inactive: everything is rejected
+    }
+    __device__ __forceinline__ bool reject(const Cull4<R>& L) const {
+        const R A = fma_(L.x, o2x, fma_(L.y, o2y, fma_(L.z, o2z, L.k)));
+        const R B = fma_(L.x, dx, fma_(L.y, dy, fma_(L.z, dz, nod)));
+        return fma_(-B, B, A) > cmp;                                           // NaN survives
+    }
+    __device__ __forceinline__ void retire() { cmp = -gm<R>::inf(); }
+};
+template <typename R> struct CullRay<R, CULL_PIVOT> {
+    R dx, dy, dz, cmp;
+    __device__ __forceinline__ void init(const Ray<R>& w, bool active, const CullFrame<R>&) {
+        const R inv = R(1) / gm<R>::sqrt(fma_(w.dx, w.dx, fma_(w.dy, w.dy, w.dz * w.dz)));
+        dx = w.dx * inv; dy = w.dy * inv; dz = w.dz * inv;
+        cmp = active ? R(0) : -gm<R>::inf();
+    }
+    __device__ __forceinline__ bool reject(const Cull4<R>& L) const {
+        const R B = fma_(L.x, dx, fma_(L.y, dy, L.z * dz));
+        return fma_(-B, B, L.k) > cmp;
+    }
+    __device__ __forceinline__ void retire() { cmp = -gm<R>::inf(); }
+};
+template <typename R> struct CullRay<R, CULL_AXIS> {
+    R ou, ov, cmp;
+    __device__ __forceinline__ void init(const Ray<R>& w, bool active, const CullFrame<R>& fr) {
+        ou = fma_(w.ox, fr.e1[0], fma_(w.oy, fr.e1[1], w.oz * fr.e1[2]));
+        ov = fma_(w.ox, fr.e2[0], fma_(w.oy, fr.e2[1], w.oz * fr.e2[2]));
+        const R oo = fma_(w.ox, w.ox, fma_(w.oy, w.oy, w.oz * w.oz));
+        cmp = active ? R(CullMargin<R>::rel) * (oo + R(1)) : -gm<R>::inf();
+    }
+    __device__ __forceinline__ bool reject(const Cull4<R>& L) const {       // record: (Cu, Cv, -R^2 - margin, unused)
+        const R du = L.x - ou, dv = L.y - ov;
+        return fma_(dv, dv, fma_(du, du, L.z)) > cmp;
+    }
+    __device__ __forceinline__ void retire() { cmp = -gm<R>::inf(); }
+};
 
-// objects [g0, g1) * GROUP of the staged table `sm` (whose first record is object sm_base); survivors of
-// ray r go to list[slot][r * SCAN_THREADS + tid] as  (global group index) << 16 | mask
-template <typename R>
-__device__ __forceinline__ void cull_groups(const R* sm, int sm_base, int g0, int g1, const CullRay<R> (&cr)[RPT],
-                                            uint32_t* list, int (&cnt)[RPT]) {
-    for (int g = g0; g < g1; g++) {
-        uint32_t m[RPT];
+// one window: objects [w * GROUP, (w + 1) * GROUP) of the staged table `sm` (whose first record is object sm_base);
+// bit j of (lo, hi)[r] = object w * GROUP + j survives ray r
+template <typename R, int FAMILY, int RPT>
+__device__ __forceinline__ void cull_window(const R* sm, int first, const CullRay<R, FAMILY> (&cr)[RPT], uint32_t (&lo)[RPT], uint32_t (&hi)[RPT]) {
 #pragma unroll
-        for (int r = 0; r < RPT; r++) m[r] = 0;
+    for (int r = 0; r < RPT; r++) { lo[r] = 0; hi[r] = 0; }
 #pragma unroll
-        for (int j = 0; j < GROUP; j++) {
-            const Cull4<R> L = load_cull(sm, g * GROUP + j - sm_base);
+    for (int j = 0; j < 32; j++) {
+        const Cull4<R> L = load_cull(sm, first + j);
 #pragma unroll
-            for (int r = 0; r < RPT; r++) {
-                const R A = fma_(L.x, cr[r].o2x, fma_(L.y, cr[r].o2y, fma_(L.z, cr[r].o2z, L.k)));
-                const R B = fma_(L.x, cr[r].dx, fma_(L.y, cr[r].dy, fma_(L.z, cr[r].dz, cr[r].nod)));
-                const R f = fma_(-B, B, A);
-                if (!(f > cr[r].cmp)) m[r] |= 1u << j;          // NaN survives
-            }
-        }
+        for (int r = 0; r < RPT; r++) if (!cr[r].reject(L)) lo[r] |= 1u << j;
+    }
 #pragma unroll
-        for (int r = 0; r < RPT; r++)
-            if (m[r]) { list[cnt[r] * RAYS_PER_BLOCK + r * SCAN_THREADS + threadIdx.x] = ((uint32_t)g << 16) | m[r]; cnt[r]++; }
+    for (int j = 0; j < 32; j++) {
+        const Cull4<R> L = load_cull(sm, first + 32 + j);
+#pragma unroll
+        for (int r = 0; r < RPT; r++) if (!cr[r].reject(L)) hi[r] |= 1u << j;
     }
 }
 
@@ -581,7 +615,7 @@ static __device__ __noinline__ bool hit_f64(const DevScene<R>& sc, int kind, int
 // the exact test of ray `w` against object i, exactly as <Type>.Intersect would decide it; `code` is the hit
 // code stored in Level::hit: leaf | flip << 27 | face << 28 (for a CSG object the member leaf that was hit)
 template <typename R, bool ROBUST>
-__device__ __forceinline__ bool exact_hit(const DevScene<R>& sc, int i, const Ray<R>& w, const double* ray64, int cap, int ri, R& t, int& code) {
+__device__ __noinline__ bool exact_hit(const DevScene<R>& sc, int i, const Ray<R>& w, const double* ray64, int cap, int ri, R& t, int& code) {
     const int kind = kind_of(sc.kind_begin, i);
     if constexpr (ROBUST) {
         if (kind != K_SPHERE) { float tf; const bool h = hit_f64<R>(sc, kind, i, ray64, cap, ri, tf, code); t = (R)tf; return h; }
@@ -616,95 +650,127 @@ __device__ __forceinline__ bool exact_hit(const DevScene<R>& sc, int i, const Ra
     }
 }
 
-// Stage `cnt` cull records starting at object `base` into `dst` (one thread).
+// Stage `cnt` cull records of `table` starting at object `base` into `dst` (one thread).
 template <typename R>
-__device__ __forceinline__ void stage_cull(const DevScene<R>& sc, int base, int cnt, R* dst, uint64_t* bar) {
+__device__ __forceinline__ void stage_cull(const R* table, int base, int cnt, R* dst, uint64_t* bar) {
     const uint32_t bytes = (uint32_t)(cnt * 4 * sizeof(R));
     mbar_expect_tx(bar, bytes);
-    tma_load_1d(dst, sc.cull + (size_t)base * 4, bytes, bar);
+    tma_load_1d(dst, table + (size_t)base * 4, bytes, bar);
 }
 
-// Shared skeleton of the two scan kernels: persistent CTAs over blocks of RAYS_PER_BLOCK rays; the
-// cull table is staged once per CTA when it fits ("resident"), else streamed through two buffers
-// per block of rays.  `Visit` supplies setup(r, ray index) / exact(r, object) / finish(r).
-template <typename R, typename Visit>
-__device__ __forceinline__ void scan_rays(const DevScene<R>& sc, int n, int chunk_objs, int resident, Visit& V) {
+// Shared skeleton of the scan kernels.  Persistent CTAs over blocks of SCAN_THREADS * RPT rays; the cull table
+// is staged once per CTA when it fits ("resident"), else streamed through two buffers per block of rays.
+//
+// Phase 1 (per thread, RPT rays in registers): cull a window of GROUP objects -> survivor masks -> every set
+// bit is appended to the CTA's candidate list in shared memory as (object << 10 | ray slot).
+// Phase 2 (CTA-wide, dense): when the list fills up, and after the last window, the CTA's threads take one
+// candidate each and run the exact test - every lane busy, instead of the few lanes of a warp that happen to
+// have a survivor in the same window.  `Visit` owns the per-ray result state in shared memory and supplies
+// setup / dense / finish.
+constexpr int CAND_CAP = 4096;              // candidate list entries per CTA
+constexpr int CAND_DRAIN = 2048;            // run phase 2 once this many are queued
+constexpr int SLOT_BITS = 10;               // ray slot within the CTA (SCAN_THREADS * RPT <= 1024)
+
+template <typename R, int FAMILY, int RPT, typename Visit>
+__device__ __forceinline__ void scan_rays(const DevScene<R>& sc, const R* table, const CullFrame<R>& frame, int n, int chunk_objs,
+                                          int resident, Visit& V) {
+    constexpr int RAYS_PER_BLOCK = SCAN_THREADS * RPT;
+    static_assert(RAYS_PER_BLOCK <= (1 << SLOT_BITS), "ray slot does not fit the candidate entry");
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ __align__(8) uint64_t bar[2];
-    uint32_t* list = reinterpret_cast<uint32_t*>(smem_raw);
-    R* const tab = reinterpret_cast<R*>(smem_raw + LIST_BYTES);        // buffer b starts at tab + b * chunk_objs * 4
+    __shared__ int cand_count;
+    uint32_t* const list = reinterpret_cast<uint32_t*>(smem_raw);
+    unsigned char* const state = smem_raw + CAND_CAP * sizeof(uint32_t);
+    R* const tab = reinterpret_cast<R*>(state + Visit::state_bytes());       // buffer b starts at tab + b * chunk_objs * 4
     const int nblocks = (n + RAYS_PER_BLOCK - 1) / RAYS_PER_BLOCK;
     if ((int)blockIdx.x >= nblocks) return;
     const int tid = threadIdx.x;
     const int NP = sc.n_cull;                                  // padded to a multiple of GROUP
     const int nchunks = (NP + chunk_objs - 1) / chunk_objs;
-    if (tid == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_fence_init(); }
+    if (tid == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_fence_init(); cand_count = 0; }
     __syncthreads();
     uint32_t phase[2] = {0, 0};
     if (resident && NP > 0) {
-        if (tid == 0) stage_cull(sc, 0, NP, tab, &bar[0]);
+        if (tid == 0) stage_cull(table, 0, NP, tab, &bar[0]);
         mbar_wait(&bar[0], 0);
     }
     for (int blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
-        CullRay<R> cr[RPT];
-        int cnt[RPT];
+        const int ray0 = blk * RAYS_PER_BLOCK;
+        CullRay<R, FAMILY> cr[RPT];
+        bool active[RPT];
 #pragma unroll
         for (int r = 0; r < RPT; r++) {
-            const int ri = blk * RAYS_PER_BLOCK + r * SCAN_THREADS + tid;
+            const int slot = r * SCAN_THREADS + tid;
             Ray<R> w = {R(0), R(0), R(0), R(0), R(0), R(1)};
-            const bool active = V.setup(r, ri, ri < n, w);
-            make_cull_ray(w, active, cr[r]);
-            cnt[r] = 0;
+            active[r] = V.setup(state, slot, ray0 + slot, ray0 + slot < n, w);
+            cr[r].init(w, active[r], frame);
         }
-        auto flush = [&]() {
+        __syncthreads();                                       // per-ray state initialised before any phase 2
+        // one window of GROUP objects starting at object `first` (record sm[first - sm_base])
+        auto window = [&](const R* sm, int sm_base, int first) {
+            uint32_t lo[RPT], hi[RPT];
+            cull_window<R, FAMILY, RPT>(sm, first - sm_base, cr, lo, hi);
 #pragma unroll
-            for (int r = 0; r < RPT; r++) {
-                const int c = V.active[r] ? cnt[r] : 0;
-                for (int s = 0; s < c; s++) {
-                    const uint32_t e = list[s * RAYS_PER_BLOCK + r * SCAN_THREADS + tid];
-                    uint32_t m = e & 0xffffu;
-                    const int base = (int)(e >> 16) * GROUP;
-                    while (m) {
-                        const int j = __ffs(m) - 1;
-                        m &= m - 1;
-                        if (base + j < sc.n_leaves) V.exact(r, base + j);
+            for (int r = 0; r < RPT; r++) if (!active[r]) { lo[r] = 0; hi[r] = 0; }
+            bool more;
+            do {
+#pragma unroll
+                for (int r = 0; r < RPT; r++) {
+                    const uint32_t slot = (uint32_t)(r * SCAN_THREADS + tid);
+                    while (lo[r]) {
+                        const int k = atomicAdd(&cand_count, 1);
+                        if (k >= CAND_CAP) break;              // full: keep the bit, retry after the drain
+                        list[k] = ((uint32_t)(first + __ffs(lo[r]) - 1) << SLOT_BITS) | slot;
+                        lo[r] &= lo[r] - 1;
+                    }
+                    while (!lo[r] && hi[r]) {
+                        const int k = atomicAdd(&cand_count, 1);
+                        if (k >= CAND_CAP) break;
+                        list[k] = ((uint32_t)(first + 32 + __ffs(hi[r]) - 1) << SLOT_BITS) | slot;
+                        hi[r] &= hi[r] - 1;
                     }
                 }
-                cnt[r] = 0;
-                if (V.done(r)) cr[r].cmp = -gm<R>::inf();
-            }
+                __syncthreads();
+                const int c = cand_count;                      // uniform: read between two barriers
+                more = c > CAND_CAP;
+                if (c >= CAND_DRAIN) {
+                    V.dense(state, list, min(c, CAND_CAP), ray0);
+                    __syncthreads();
+                    if (tid == 0) cand_count = 0;
+                }
+                __syncthreads();
+            } while (more);
         };
         if (resident) {
-            const int ngroups = NP / GROUP;
-            for (int g0 = 0; g0 < ngroups; g0 += FLUSH_GROUPS) {
-                cull_groups<R>(tab, 0, g0, min(g0 + FLUSH_GROUPS, ngroups), cr, list, cnt);
-                flush();
-                if (V.all_done()) break;
-            }
+            for (int first = 0; first < NP; first += GROUP) window(tab, 0, first);
         } else {
             if (tid == 0) {
-                stage_cull(sc, 0, min(chunk_objs, NP), tab, &bar[0]);
-                if (nchunks > 1) stage_cull(sc, chunk_objs, min(chunk_objs, NP - chunk_objs), tab + (size_t)chunk_objs * 4, &bar[1]);
+                stage_cull(table, 0, min(chunk_objs, NP), tab, &bar[0]);
+                if (nchunks > 1) stage_cull(table, chunk_objs, min(chunk_objs, NP - chunk_objs), tab + (size_t)chunk_objs * 4, &bar[1]);
             }
             for (int c = 0; c < nchunks; c++) {
                 const int b = c & 1;
                 mbar_wait(&bar[b], phase[b]);
                 phase[b] ^= 1;
                 const int base = c * chunk_objs;
-                const int gbeg = base / GROUP, gend = (base + min(chunk_objs, NP - base)) / GROUP;
-                for (int g0 = gbeg; g0 < gend; g0 += FLUSH_GROUPS) {
-                    cull_groups<R>(tab + (size_t)b * chunk_objs * 4, base, g0, min(g0 + FLUSH_GROUPS, gend), cr, list, cnt);
-                    flush();
-                }
-                __syncthreads();                       // everyone is done reading buf[b]
+                const R* sm = tab + (size_t)b * chunk_objs * 4;
+                const int end = base + min(chunk_objs, NP - base);
+                for (int first = base; first < end; first += GROUP) window(sm, base, first);   // ends with a barrier: buffer b is free
                 if (tid == 0 && c + 2 < nchunks) {
                     const int nb = (c + 2) * chunk_objs;
-                    stage_cull(sc, nb, min(chunk_objs, NP - nb), tab + (size_t)b * chunk_objs * 4, &bar[b]);
+                    stage_cull(table, nb, min(chunk_objs, NP - nb), tab + (size_t)b * chunk_objs * 4, &bar[b]);
                 }
             }
         }
+        {   // last drain of this block of rays
+            const int c = cand_count;                          // every window ends with a barrier
+            if (c > 0) V.dense(state, list, c, ray0);
+            __syncthreads();
+            if (tid == 0) cand_count = 0;
+        }
 #pragma unroll
-        for (int r = 0; r < RPT; r++) V.finish(r);
+        for (int r = 0; r < RPT; r++) if (active[r]) V.finish(state, r * SCAN_THREADS + tid, ray0 + r * SCAN_THREADS + tid);
+        __syncthreads();                                       // state is re-initialised by the next block of rays
     }
 }
 
@@ -713,116 +779,157 @@ __device__ __forceinline__ void warp_add(unsigned long long* dst, unsigned long 
     if ((threadIdx.x & 31) == 0 && v) atomicAdd(dst, v);
 }
 
-// closestHit for one recursion level (raytracer.go:469-483): strictly smaller T wins, equal T keeps
-// the object that comes first in scan order.
-template <typename R, bool ROBUST, bool COUNT> struct ClosestVisit {
+template <typename R> struct BitsOf;
+template <> struct BitsOf<float> {
+    typedef unsigned int type;
+    static __device__ __forceinline__ unsigned int of(float t) { return __float_as_uint(t); }
+    static __device__ __forceinline__ float back(unsigned int b) { return __uint_as_float(b); }
+};
+template <> struct BitsOf<double> {
+    typedef unsigned long long type;
+    static __device__ __forceinline__ unsigned long long of(double t) { return (unsigned long long)__double_as_longlong(t); }
+    static __device__ __forceinline__ double back(unsigned long long b) { return __longlong_as_double((long long)b); }
+};
+
+// closestHit for one recursion level (raytracer.go:469-483): strictly smaller T wins, equal T keeps the object
+// that comes first in scan order.  Per ray in shared memory: the smallest T so far (hits have T > 0, so the bit
+// pattern orders like the value), the smallest scan index among the hits with that T, and that hit's code.
+template <typename R, bool ROBUST, bool COUNT, int RPT> struct ClosestVisit {
+    typedef typename BitsOf<R>::type UB;
+    static constexpr int NR = SCAN_THREADS * RPT;
     const DevScene<R>& sc; const Level<R>& lv;
-    Ray<R> w[RPT]; int ri[RPT]; bool active[RPT];
-    R best_t[RPT]; int best_code[RPT];
     unsigned long long n_exact, n_flops;
     __device__ ClosestVisit(const DevScene<R>& s, const Level<R>& l) : sc(s), lv(l), n_exact(0), n_flops(0) {}
-    __device__ __forceinline__ bool setup(int r, int i, bool act, Ray<R>& out) {
-        ri[r] = i; active[r] = act; best_t[r] = R(0); best_code[r] = -1;
-        if (act) {
-            const size_t cap = (size_t)lv.cap;
-            out.ox = lv.ray[i]; out.oy = lv.ray[cap + i]; out.oz = lv.ray[2 * cap + i];
-            out.dx = lv.ray[3 * cap + i]; out.dy = lv.ray[4 * cap + i]; out.dz = lv.ray[5 * cap + i];
-        }
-        w[r] = out;
+    static __host__ __device__ constexpr size_t state_bytes() { return (size_t)NR * (sizeof(UB) + 8); }
+    static __device__ __forceinline__ UB* tbest(unsigned char* st) { return reinterpret_cast<UB*>(st); }
+    static __device__ __forceinline__ int* order(unsigned char* st) { return reinterpret_cast<int*>(st + (size_t)NR * sizeof(UB)); }
+    static __device__ __forceinline__ int* codes(unsigned char* st) { return order(st) + NR; }
+    __device__ __forceinline__ void load_ray(int i, Ray<R>& out) const {
+        const size_t cap = (size_t)lv.cap;
+        out.ox = lv.ray[i]; out.oy = lv.ray[cap + i]; out.oz = lv.ray[2 * cap + i];
+        out.dx = lv.ray[3 * cap + i]; out.dy = lv.ray[4 * cap + i]; out.dz = lv.ray[5 * cap + i];
+    }
+    __device__ __forceinline__ bool setup(unsigned char* st, int slot, int i, bool act, Ray<R>& out) {
+        tbest(st)[slot] = ~(UB)0; order(st)[slot] = 0x7fffffff; codes(st)[slot] = -1;
+        if (act) load_ray(i, out);
         return act;
     }
-    __device__ __forceinline__ void exact(int r, int i) {
-        R t; int code;
-        if (COUNT) { n_exact++; n_flops += (unsigned)sc.obj_flops[i]; }
-        if (!exact_hit<R, ROBUST>(sc, i, w[r], lv.ray64, lv.cap, ri[r], t, code)) return;
-        if (best_code[r] < 0 || t < best_t[r] || (t == best_t[r] && sc.scan_of[i] < sc.scan_of[best_code[r] & HIT_LEAF_MASK])) {
-            best_t[r] = t; best_code[r] = code;
+    __device__ __forceinline__ void dense(unsigned char* st, const uint32_t* list, int count, int ray0) {
+        UB* tb = tbest(st); int* ord = order(st); int* cod = codes(st);
+        const int iters = (count + SCAN_THREADS - 1) / SCAN_THREADS;
+        for (int it = 0; it < iters; it++) {
+            const int k = it * SCAN_THREADS + threadIdx.x;
+            bool hit = false, lowered = false;
+            R t = R(0); int code = -1, slot = 0, scan = 0;
+            UB b = 0;
+            if (k < count) {
+                const uint32_t e = list[k];
+                slot = (int)(e & ((1u << SLOT_BITS) - 1));
+                const int obj = (int)(e >> SLOT_BITS);
+                if (obj < sc.n_leaves) {                     // a padding record can only be reached by a NaN ray
+                    if (COUNT) { n_exact++; n_flops += (unsigned)sc.obj_flops[obj]; }
+                    Ray<R> w;
+                    load_ray(ray0 + slot, w);
+                    hit = exact_hit<R, ROBUST>(sc, obj, w, lv.ray64, lv.cap, ray0 + slot, t, code);
+                    scan = sc.scan_of[obj];
+                }
+            }
+            if (hit) { b = BitsOf<R>::of(t); const UB old = atomicMin(&tb[slot], b); lowered = b < old; }
+            __syncthreads();
+            if (hit && lowered && tb[slot] == b) ord[slot] = 0x7fffffff;        // a new smallest T: forget the old tie-break
+            __syncthreads();
+            if (hit && tb[slot] == b) atomicMin(&ord[slot], scan);
+            __syncthreads();
+            if (hit && tb[slot] == b && ord[slot] == scan) cod[slot] = code;
         }
     }
-    __device__ __forceinline__ bool done(int) const { return false; }
-    __device__ __forceinline__ bool all_done() const { return false; }
-    __device__ __forceinline__ void finish(int r) {
-        if (active[r]) {
-            lv.hit[ri[r]] = best_code[r];
-            lv.t[ri[r]] = best_t[r];
-        }
+    __device__ __forceinline__ void finish(unsigned char* st, int slot, int i) {
+        const int code = codes(st)[slot];
+        lv.hit[i] = code;
+        lv.t[i] = code < 0 ? R(0) : BitsOf<R>::back(tbest(st)[slot]);
     }
 };
 
-template <typename R, bool ROBUST, bool COUNT>
-__global__ void __launch_bounds__(SCAN_THREADS) k_closest(const __grid_constant__ DevScene<R> sc, const __grid_constant__ Level<R> lv,
+template <typename R, int FAMILY, int RPT, bool ROBUST, bool COUNT>
+__global__ void __launch_bounds__(SCAN_THREADS, sizeof(R) == 4 ? 4 : 2) k_closest(const __grid_constant__ DevScene<R> sc, const __grid_constant__ Level<R> lv,
+                                                          const R* table, const __grid_constant__ CullFrame<R> frame,
                                                           Counters* ctr, int level, int chunk_objs, int resident) {
-    ClosestVisit<R, ROBUST, COUNT> V(sc, lv);
-    scan_rays<R>(sc, ctr->count[level], chunk_objs, resident, V);
+    ClosestVisit<R, ROBUST, COUNT, RPT> V(sc, lv);
+    scan_rays<R, FAMILY, RPT>(sc, table, frame, ctr->count[level], chunk_objs, resident, V);
     if (COUNT) {
         warp_add(&ctr->exact_tests, V.n_exact);
         warp_add(&ctr->exact_flops, V.n_flops);
     }
 }
 
-// inShadow for every queued (hit, light) pair (raytracer.go:411-429): writes occl[target] = 1 when some
-// object other than the shaded one has  shadowHit.T * |ray.Direction| < distToLight  (:424).  The answer
-// does not depend on the order objects are visited in; COUNT additionally finds the FIRST occluder in
-// the reference's scan order to credit the tests the reference itself would have run.
-template <typename R, bool COUNT> struct ShadowVisit {
-    const DevScene<R>& sc; const ShadowQueue<R>& sq; unsigned char* occl;
-    Ray<R> w[RPT]; int ri[RPT], skip[RPT]; bool active[RPT], occluded[RPT];
-    R dist[RPT], in_len[RPT]; int first[RPT];
+// inShadow for the queued (hit, light) pairs of ONE light (raytracer.go:411-429): writes occl[target] = 1 when
+// some object other than the shaded one has  shadowHit.T * |ray.Direction| < distToLight  (:424).  The answer
+// does not depend on the order objects are visited in; COUNT additionally finds the FIRST occluder in the
+// reference's scan order to credit the tests the reference itself would have run.
+template <typename R, bool COUNT, int RPT> struct ShadowVisit {
+    static constexpr int NR = SCAN_THREADS * RPT;
+    const DevScene<R>& sc; const ShadowQueue<R>& sq; unsigned char* occl; int qbase;
     unsigned long long n_exact, n_flops, n_occluded, cred_tests, cred_flops;
-    __device__ ShadowVisit(const DevScene<R>& s, const ShadowQueue<R>& q, unsigned char* o)
-        : sc(s), sq(q), occl(o), n_exact(0), n_flops(0), n_occluded(0), cred_tests(0), cred_flops(0) {}
-    __device__ __forceinline__ bool setup(int r, int i, bool act, Ray<R>& out) {
-        ri[r] = i; active[r] = act; occluded[r] = false; skip[r] = -1; dist[r] = R(0); in_len[r] = R(1); first[r] = 0x7fffffff;
-        if (act) {
-            const size_t cap = (size_t)sq.cap;
-            out.ox = sq.q[i]; out.oy = sq.q[cap + i]; out.oz = sq.q[2 * cap + i];
-            out.dx = sq.q[3 * cap + i]; out.dy = sq.q[4 * cap + i]; out.dz = sq.q[5 * cap + i];
-            dist[r] = sq.q[6 * cap + i]; in_len[r] = sq.q[7 * cap + i];
-            skip[r] = sq.skip[i];
-        }
-        w[r] = out;
+    __device__ ShadowVisit(const DevScene<R>& s, const ShadowQueue<R>& q, unsigned char* o, int base)
+        : sc(s), sq(q), occl(o), qbase(base), n_exact(0), n_flops(0), n_occluded(0), cred_tests(0), cred_flops(0) {}
+    static __host__ __device__ constexpr size_t state_bytes() { return (size_t)NR * 4; }
+    static __device__ __forceinline__ int* first(unsigned char* st) { return reinterpret_cast<int*>(st); }   // smallest scan index of an occluder
+    __device__ __forceinline__ void load_ray(int i, Ray<R>& out) const {
+        const size_t cap = (size_t)sq.cap;
+        out.ox = sq.q[i]; out.oy = sq.q[cap + i]; out.oz = sq.q[2 * cap + i];
+        out.dx = sq.q[3 * cap + i]; out.dy = sq.q[4 * cap + i]; out.dz = sq.q[5 * cap + i];
+    }
+    __device__ __forceinline__ bool setup(unsigned char* st, int slot, int i, bool act, Ray<R>& out) {
+        first(st)[slot] = 0x7fffffff;
+        if (act) load_ray(qbase + i, out);
         return act;
     }
-    __device__ __forceinline__ void exact(int r, int i) {
-        if (i == skip[r] || (!COUNT && occluded[r])) return;
-        R t; int code;
-        if (COUNT) { n_exact++; n_flops += (unsigned)sc.obj_flops[i]; }
-        if (!exact_hit<R, false>(sc, i, w[r], nullptr, 0, 0, t, code)) return;
-        if (t * in_len[r] < dist[r]) {
-            occluded[r] = true;
-            if (COUNT) first[r] = min(first[r], sc.scan_of[i]);
+    __device__ __forceinline__ void dense(unsigned char* st, const uint32_t* list, int count, int ray0) {
+        int* fo = first(st);
+        for (int k = threadIdx.x; k < count; k += SCAN_THREADS) {
+            const uint32_t e = list[k];
+            const int slot = (int)(e & ((1u << SLOT_BITS) - 1));
+            const int obj = (int)(e >> SLOT_BITS);
+            const int q = qbase + ray0 + slot;
+            if (obj >= sc.n_leaves || obj == sq.skip[q]) continue;
+            if (!COUNT && fo[slot] != 0x7fffffff) continue;    // already occluded (a stale read only costs a test)
+            if (COUNT) { n_exact++; n_flops += (unsigned)sc.obj_flops[obj]; }
+            Ray<R> w;
+            load_ray(q, w);
+            R t; int code;
+            if (!exact_hit<R, false>(sc, obj, w, nullptr, 0, 0, t, code)) continue;
+            const size_t cap = (size_t)sq.cap;
+            if (t * sq.q[7 * cap + q] < sq.q[6 * cap + q])     // T * |incoming direction| < distance to the light
+                atomicMin(&fo[slot], sc.scan_of[obj]);
         }
     }
-    __device__ __forceinline__ bool done(int r) const { return !COUNT && (occluded[r] || !active[r]); }
-    __device__ __forceinline__ bool all_done() const {
-        bool d = true;
-#pragma unroll
-        for (int r = 0; r < RPT; r++) d = d && done(r);
-        return __all_sync(0xffffffffu, d);
-    }
-    __device__ __forceinline__ void finish(int r) {
-        if (!active[r]) return;
-        if (occluded[r]) { occl[sq.target[ri[r]]] = 1; n_occluded++; }
+    __device__ __forceinline__ void finish(unsigned char* st, int slot, int i) {
+        const int q = qbase + i;
+        const int fs = first(st)[slot];
+        const bool occluded = fs != 0x7fffffff;
+        if (occluded) { occl[sq.target[q]] = 1; n_occluded++; }
         if (COUNT) {
             // objects 0..last of the scan order are tested, minus the shaded one (raytracer.go:416-427)
-            const int last = occluded[r] ? first[r] : sc.n_leaves - 1;
+            const int last = occluded ? fs : sc.n_leaves - 1;
             if (last >= 0) {
                 unsigned long long tests = (unsigned long long)last + 1, flops = sc.cum_flops[last];
-                const int ss = skip[r] >= 0 ? sc.scan_of[skip[r]] : 0x7fffffff;
-                if (ss <= last) { tests--; flops -= (unsigned long long)sc.obj_flops[skip[r]]; }
+                const int skip = sq.skip[q];
+                const int ss = skip >= 0 ? sc.scan_of[skip] : 0x7fffffff;
+                if (ss <= last) { tests--; flops -= (unsigned long long)sc.obj_flops[skip]; }
                 cred_tests += tests; cred_flops += flops;
             }
         }
     }
 };
 
-template <typename R, bool COUNT>
-__global__ void __launch_bounds__(SCAN_THREADS) k_shadow(const __grid_constant__ DevScene<R> sc, const __grid_constant__ ShadowQueue<R> sq,
-                                                         unsigned char* occl, Counters* ctr, int chunk_objs, int resident) {
-    const int n = ctr->shadow_count;
+template <typename R, int FAMILY, int RPT, bool COUNT>
+__global__ void __launch_bounds__(SCAN_THREADS, sizeof(R) == 4 ? 4 : 2) k_shadow(const __grid_constant__ DevScene<R> sc, const __grid_constant__ ShadowQueue<R> sq,
+                                                         const R* table, const __grid_constant__ CullFrame<R> frame,
+                                                         unsigned char* occl, Counters* ctr, int light, int chunk_objs, int resident) {
+    const int n = sq.count[light];
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ctr->rays_shadow, (unsigned long long)n);
-    ShadowVisit<R, COUNT> V(sc, sq, occl);
-    scan_rays<R>(sc, n, chunk_objs, resident, V);
+    ShadowVisit<R, COUNT, RPT> V(sc, sq, occl, light * sq.per_light);
+    scan_rays<R, FAMILY, RPT>(sc, table, frame, n, chunk_objs, resident, V);
     warp_add(&ctr->shadow_occluded, V.n_occluded);
     if (COUNT) {
         warp_add(&ctr->exact_tests, V.n_exact);
@@ -831,7 +938,6 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_shadow(const __grid_constant__
         warp_add(&ctr->shadow_flops, V.cred_flops);
     }
 }
-
 
 // ------------------------------------------------------------------ surface bytecode interpreter
 // EvalSurfaceFn (internal/gml/evaluator.go:672-727) after host-side partial evaluation: typed
@@ -983,7 +1089,6 @@ __global__ void __launch_bounds__(256) k_gen(DevScene<R> sc, Level<R> lv, Counte
     if (i == 0) {
         for (int l = 1; l <= GMLRT_MAX_DEPTH; l++) ctr->count[l] = 0;
         ctr->count[0] = S;
-        ctr->shadow_count = 0;
     }
     if (i >= S) return;
     const int s = i & 3, pix = i >> 2;
@@ -1052,9 +1157,11 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
         if (kind == K_SPHERE) {                                                      // :106-150
             face = 0;
             if (sf.kind != GMLRT_SURFACE_CONST) {
-                if (gm<R>::abs(p.y) > R(1)) ok = false;
-                v = (p.y + R(1)) / R(2);
-                R ca = p.z / gm<R>::sqrt(R(1) - p.y * p.y);
+                R py = p.y;
+                if (!GMLRT_PARITY_TU) py = fminf(fmaxf((float)py, -1.0f), 1.0f);      // float rounding can leave |y| = 1 + ulp at the poles: clamp instead of the reference's error
+                if (gm<R>::abs(py) > R(1)) ok = false;                                // raytracer.go:142-144
+                v = (py + R(1)) / R(2);
+                R ca = p.z / gm<R>::sqrt(R(1) - py * py);
                 if (!GMLRT_PARITY_TU) ca = fminf(fmaxf((float)ca, -1.0f), 1.0f);   // float rounding can leave |ca| = 1 + ulp on the x = 0 meridian
                 u = gm<R>::acos(ca) / (R(2) * R(GM_PI));
             }
@@ -1114,8 +1221,9 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
     for (int li = 0; li < sc.n_lights; li++) {
         V3<R> ldir = mk(R(0), R(0), R(1)), lcol; R dist = R(0);
         bool want = live && light_at(sc.lights[li], P, ldir, dist, lcol);
-        const int slot = warp_append(&ctr->shadow_count, want);
+        int slot = warp_append(&sq.count[li], want);
         if (want) {
+            slot += li * sq.per_light;
             const V3<R> so = P + N * R(1e-4);
             const int qc = sq.cap;
             sq.q[slot] = so.x; sq.q[qc + slot] = so.y; sq.q[2 * qc + slot] = so.z;
@@ -1303,18 +1411,18 @@ public:
         CU_TRY(cudaMalloc(&ctr_, sizeof(Counters)));
         CU_TRY(cudaMemset(ctr_, 0, sizeof(Counters)));
         const int smem_max = 200 * 1024;
-        CU_TRY(cudaFuncSetAttribute(k_closest<R, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
-        CU_TRY(cudaFuncSetAttribute(k_closest<R, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
-        if (kRobustPrimary) {
-            CU_TRY(cudaFuncSetAttribute(k_closest<R, kRobustPrimary, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
-            CU_TRY(cudaFuncSetAttribute(k_closest<R, kRobustPrimary, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
-        }
-        CU_TRY(cudaFuncSetAttribute(k_shadow<R, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
-        CU_TRY(cudaFuncSetAttribute(k_shadow<R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+        auto allow = [&](auto kernel) -> int { CU_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max)); return GMLRT_OK; };
+        int rc;
+        if ((rc = allow(k_closest<R, CULL_PIVOT, RPT_FAMILY, kRobustPrimary, false>)) || (rc = allow(k_closest<R, CULL_PIVOT, RPT_FAMILY, kRobustPrimary, true>)) ||
+            (rc = allow(k_closest<R, CULL_GENERAL, RPT_GENERAL, false, false>)) || (rc = allow(k_closest<R, CULL_GENERAL, RPT_GENERAL, false, true>)) ||
+            (rc = allow(k_shadow<R, CULL_PIVOT, RPT_FAMILY, false>)) || (rc = allow(k_shadow<R, CULL_PIVOT, RPT_FAMILY, true>)) ||
+            (rc = allow(k_shadow<R, CULL_AXIS, RPT_FAMILY, false>)) || (rc = allow(k_shadow<R, CULL_AXIS, RPT_FAMILY, true>)))
+            return rc;
         return GMLRT_OK;
     }
 
     static constexpr bool kRobustPrimary = std::is_same<R, float>::value;   // f32: double re-test of borderline primary hits
+    static constexpr int RPT_GENERAL = 2, RPT_FAMILY = 4;                   // rays per thread: 8 cull registers per ray vs 4
 
     void reset_totals() override { totals_ = TraceTotals(); need_ctr_reset_ = true; ev_used_ = 0; ev_cls_.clear(); }
     void set_profiling(bool on) override { profile_ = on; }
@@ -1392,8 +1500,15 @@ private:
     TraceTotals totals_;
     bool need_ctr_reset_ = true;
     // scan kernel configuration
-    int chunk_objs_ = GROUP, resident_ = 1; size_t scan_smem_ = 0;
-    int grid_closest_[2][2] = {{148, 148}, {148, 148}}, grid_shadow_[2] = {148, 148};   // [robust][counting], [counting]
+    int chunk_objs_ = GROUP, resident_ = 1; size_t table_smem_ = 0;
+    struct Launch { int grid = 148; size_t smem = 0; };
+    Launch l_primary_[2], l_closest_[2], l_shadow_pivot_[2], l_shadow_axis_[2];          // [counting]
+    // cull tables (device) and what they were built for: any ray, camera rays, one per light
+    std::vector<double> bound_;                                  // host: [n][4] bounding spheres (centre, radius) of the objects
+    R* cull_general_ = nullptr; R* cull_eye_ = nullptr; std::vector<R*> cull_light_;
+    CullFrame<R> frame_general_{}, frame_eye_{}; std::vector<CullFrame<R>> frame_light_;
+    int* shadow_counts_ = nullptr;
+    int build_cull_table(int family, const double* v, double offset_abs, R** out, CullFrame<R>& frame, std::string& err);
     std::vector<int> kind_host_;
 };
 
@@ -1409,7 +1524,6 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     const int n_plain = S.n_plain, n_csg = (int)S.csg.size(), n = n_plain + n_csg;
     const int n_members = (int)S.leaves.size() - n_plain, n_all = n + n_members;
     if (n_all >= HIT_NONE_LEAF) { err = "too many leaves"; return GMLRT_E_UNSUPPORTED; }
-    if (n > 0xffff * GROUP) { err = "too many objects for the 16-bit group index of the scan kernels"; return GMLRT_E_UNSUPPORTED; }
     std::vector<int> order(n_plain);
     for (int i = 0; i < n_plain; i++) order[i] = i;
     std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return S.leaves[a].kind < S.leaves[b].kind; });
@@ -1420,22 +1534,14 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     std::vector<R> w2o(na * 12, R(0)), o2w(na * 12, R(0)), fn(na * 18, R(0));
     std::vector<double> w2o64(kRobustPrimary ? na * 12 : 0, 0.0);
     std::vector<int> scan_of(na, 0), surface(na, 0), kind(na, K_SPHERE), obj_flops(std::max(n, 1), 0);
-    const int n_cull = (n + GROUP - 1) / GROUP * GROUP;
-    std::vector<R> cull((size_t)std::max(n_cull, GROUP) * 4);
+    const int n_cull = std::max((n + GROUP - 1) / GROUP * GROUP, GROUP);
     std::vector<unsigned long long> cum_flops(std::max(n, 1), 0ull);
     DevScene<R> sc{};
     sc.n_leaves = n; sc.n_cull = n_cull; sc.n_all = n_all;
     for (int k = 0; k <= K_OBJ_KINDS; k++) sc.kind_begin[k] = 0;
+    bound_.assign((size_t)std::max(n, 1) * 4, 0.0);
     auto put_cull = [&](int d, const double* C, double Rw) {
-        // bounding sphere, radius inflated so that a reject is always a true miss (see the scan section)
-        const R cx = (R)C[0], cy = (R)C[1], cz = (R)C[2];
-        const double cc = (double)cx * cx + (double)cy * cy + (double)cz * cz;
-        const double Rm = Rw * (1.0 + CullMargin<R>::radius);
-        double K = cc - Rm * Rm - CullMargin<R>::rel * cc;
-        if (!(K == K) || std::isinf(Rw)) K = -INFINITY;                      // unbounded (plane) or degenerate: never rejected
-        R* rec = &cull[(size_t)d * 4];
-        rec[0] = std::isinf(Rw) ? R(0) : cx; rec[1] = std::isinf(Rw) ? R(0) : cy; rec[2] = std::isinf(Rw) ? R(0) : cz; rec[3] = (R)K;
-        if ((double)rec[3] > K) rec[3] = std::nextafter(rec[3], (R)-INFINITY);
+        bound_[(size_t)d * 4] = C[0]; bound_[(size_t)d * 4 + 1] = C[1]; bound_[(size_t)d * 4 + 2] = C[2]; bound_[(size_t)d * 4 + 3] = Rw;
     };
     auto put_leaf = [&](int d, const HostLeaf& L) {
         for (int k = 0; k < 12; k++) { w2o[(size_t)d * 12 + k] = (R)L.w2o[k]; o2w[(size_t)d * 12 + k] = (R)L.o2w[k]; }
@@ -1473,10 +1579,6 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
             } else csg_prog.push_back(-1 - op.op);
         }
     }
-    for (int d = n; d < std::max(n_cull, GROUP); d++) {                      // padding: always rejected
-        cull[(size_t)d * 4 + 0] = cull[(size_t)d * 4 + 1] = cull[(size_t)d * 4 + 2] = R(0);
-        cull[(size_t)d * 4 + 3] = (R)INFINITY;
-    }
     for (int i = 1; i < n; i++) cum_flops[i] += cum_flops[i - 1];
     for (int k = 0; k < K_OBJ_KINDS; k++) sc.kind_begin[k + 1] += sc.kind_begin[k];
     kind_host_ = kind;
@@ -1506,10 +1608,10 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     int rc;
     double* d_w2o64 = nullptr;
     if ((rc = to_device(w2o64, &d_w2o64, err))) return rc;
-    R* d_cull; unsigned long long* d_cum; int *d_prog, *d_oflops; int2* d_range;
-    if ((rc = to_device(cull, &d_cull, err)) || (rc = to_device(cum_flops, &d_cum, err)) || (rc = to_device(csg_prog, &d_prog, err)) ||
+    unsigned long long* d_cum; int *d_prog, *d_oflops; int2* d_range;
+    if ((rc = to_device(cum_flops, &d_cum, err)) || (rc = to_device(csg_prog, &d_prog, err)) ||
         (rc = to_device(csg_range, &d_range, err)) || (rc = to_device(obj_flops, &d_oflops, err))) return rc;
-    sc.cull = d_cull; sc.cum_flops = d_cum; sc.csg_prog = d_prog; sc.csg_range = d_range; sc.obj_flops = d_oflops;
+    sc.cum_flops = d_cum; sc.csg_prog = d_prog; sc.csg_range = d_range; sc.obj_flops = d_oflops;
     R *d_w2o, *d_o2w, *d_fn, *d_fpool; int *d_scan, *d_surf, *d_kind, *d_itab; uint32_t* d_code;
     DevLight<R>* d_lights; DevSurface<R>* d_surfaces;
     if ((rc = to_device(w2o, &d_w2o, err)) || (rc = to_device(o2w, &d_o2w, err)) || (rc = to_device(fn, &d_fn, err)) ||
@@ -1525,6 +1627,32 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     sc.W = S.width; sc.H = S.height; sc.depth = S.depth; sc.vw = S.vw; sc.vh = S.vh;
     for (int k = 0; k < 3; k++) { sc.ambient[k] = (R)S.h.ambient[k]; sc.bg0[k] = (R)S.h.bg_start[k]; sc.bg1[k] = (R)S.h.bg_end[k]; }
     sc_ = sc;
+    // cull tables: any ray; camera rays (their lines pass through the eye, raytracer.go:605-609); one per light
+    const double eye[3] = {0.0, 0.0, -1.0};
+    if ((rc = build_cull_table(CULL_GENERAL, nullptr, 0.0, &cull_general_, frame_general_, err)) ||
+        (rc = build_cull_table(CULL_PIVOT, eye, 1e-5, &cull_eye_, frame_eye_, err))) return rc;
+    cull_light_.assign(S.lights.size(), nullptr);
+    frame_light_.assign(S.lights.size(), CullFrame<R>{});
+    for (size_t i = 0; i < S.lights.size(); i++) {
+        const gmlrt_light& l = S.lights[i];
+        if (l.kind == GMLRT_LIGHT_DIRECTIONAL) {
+            double a[3] = {-l.pos[0], -l.pos[1], -l.pos[2]};                 // towards the light (light_at)
+            normalize3(a);
+            rc = build_cull_table(CULL_AXIS, a, 1e-5, &cull_light_[i], frame_light_[i], err);
+        } else {
+            // a shadow ray starts at P + N*1e-4 but points along normalize(Lpos - P) (raytracer.go:412-413), so its
+            // line misses the light by up to 1e-4 |N|: widen every sphere by that much
+            rc = build_cull_table(CULL_PIVOT, l.pos, 1.5e-4, &cull_light_[i], frame_light_[i], err);
+        }
+        if (rc) return rc;
+    }
+    {
+        void* p = nullptr;
+        CU_TRY(cudaMalloc(&p, std::max<size_t>(S.lights.size(), 1) * sizeof(int)));
+        scene_allocs_.push_back(p);
+        shadow_counts_ = reinterpret_cast<int*>(p);
+        CU_TRY(cudaMemsetAsync(shadow_counts_, 0, std::max<size_t>(S.lights.size(), 1) * sizeof(int), stream_));
+    }
     CU_TRY(cudaStreamSynchronize(stream_));      // host vectors go out of scope
 
     // frame + ids
@@ -1536,6 +1664,59 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
         frame_px_ = px;
     }
     return plan_tiles(S, err);
+}
+
+// One 4-value record per object for the cull phase of the scan kernels (see "two-phase scan"): the bounding
+// sphere (centre C, radius Rw) in the form the family's reject() test reads, with every margin folded in so that
+// a reject is always a true miss: relative radius inflation, an absolute widening `offset_abs` (rays that only
+// nearly pass through the pivot / along the axis) and a rounding allowance relative to the squared magnitudes.
+template <typename R>
+int Renderer<R>::build_cull_table(int family, const double* v, double offset_abs, R** out, CullFrame<R>& frame, std::string& err) {
+    const int n = sc_.n_leaves, n_cull = sc_.n_cull;
+    std::vector<R> tab((size_t)n_cull * 4);
+    frame = CullFrame<R>{};
+    frame.family = family;
+    double e1[3] = {1, 0, 0}, e2[3] = {0, 1, 0};
+    if (family == CULL_AXIS) {                       // orthonormal basis of the plane orthogonal to the unit axis v
+        const int k = std::fabs(v[0]) < std::fabs(v[1]) ? (std::fabs(v[0]) < std::fabs(v[2]) ? 0 : 2) : (std::fabs(v[1]) < std::fabs(v[2]) ? 1 : 2);
+        double u[3] = {0, 0, 0};
+        u[k] = 1.0;
+        const double d = u[0] * v[0] + u[1] * v[1] + u[2] * v[2];
+        for (int i = 0; i < 3; i++) e1[i] = u[i] - d * v[i];
+        normalize3(e1);
+        e2[0] = v[1] * e1[2] - v[2] * e1[1]; e2[1] = v[2] * e1[0] - v[0] * e1[2]; e2[2] = v[0] * e1[1] - v[1] * e1[0];
+        normalize3(e2);
+        for (int i = 0; i < 3; i++) { frame.e1[i] = (R)e1[i]; frame.e2[i] = (R)e2[i]; }
+        for (int i = 0; i < 3; i++) { e1[i] = (double)frame.e1[i]; e2[i] = (double)frame.e2[i]; }      // what the device projects rays with
+    }
+    const double rel = CullMargin<R>::rel;
+    for (int d = 0; d < n_cull; d++) {
+        R* rec = &tab[(size_t)d * 4];
+        if (d >= n) { rec[0] = rec[1] = rec[2] = R(0); rec[3] = (R)INFINITY; if (family == CULL_AXIS) rec[2] = (R)INFINITY; continue; }   // padding: always rejected
+        const double* C = &bound_[(size_t)d * 4];
+        const double Rw = bound_[(size_t)d * 4 + 3];
+        const bool unbounded = std::isinf(Rw) || !(Rw == Rw);
+        const double Rm = Rw * (1.0 + CullMargin<R>::radius) + offset_abs;
+        double K;
+        if (family == CULL_AXIS) {
+            const R cu = (R)(C[0] * e1[0] + C[1] * e1[1] + C[2] * e1[2]), cv = (R)(C[0] * e2[0] + C[1] * e2[1] + C[2] * e2[2]);
+            const double cc = C[0] * C[0] + C[1] * C[1] + C[2] * C[2];
+            K = -(Rm * Rm) - rel * (cc + 1.0);
+            rec[0] = unbounded ? R(0) : cu; rec[1] = unbounded ? R(0) : cv; rec[3] = R(0);
+            if (unbounded || !(K == K)) K = -INFINITY;
+            rec[2] = (R)K;
+            if ((double)rec[2] > K) rec[2] = std::nextafter(rec[2], (R)-INFINITY);
+        } else {
+            const double px = C[0] - (v ? v[0] : 0.0), py = C[1] - (v ? v[1] : 0.0), pz = C[2] - (v ? v[2] : 0.0);
+            const R cx = (R)px, cy = (R)py, cz = (R)pz;
+            const double cc = (double)cx * cx + (double)cy * cy + (double)cz * cz;
+            K = cc - Rm * Rm - rel * (cc + 1.0);
+            if (unbounded || !(K == K)) K = -INFINITY;                       // plane or degenerate: never rejected
+            rec[0] = unbounded ? R(0) : cx; rec[1] = unbounded ? R(0) : cy; rec[2] = unbounded ? R(0) : cz; rec[3] = (R)K;
+            if ((double)rec[3] > K) rec[3] = std::nextafter(rec[3], (R)-INFINITY);
+        }
+    }
+    return to_device(tab, out, err);
 }
 
 template <typename R>
@@ -1596,25 +1777,32 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
         L.ray64 = (kRobustPrimary && l == 0) ? (double*)(base + o_ray64) : nullptr;
     }
     sq_.q = (R*)(base + o_sq); sq_.skip = (int*)(base + o_skip); sq_.target = (int*)(base + o_tgt); sq_.cap = (int)sq_cap;
+    sq_.per_light = (int)max_cap; sq_.count = shadow_counts_;
     samples_ = (R*)(base + o_samples); sample_cap_ = (int)S0;
 
     // scan kernels: resident cull table when it fits, else two streaming buffers (chunks of whole groups)
     const size_t rec_bytes = 4 * sizeof(R);
     const size_t resident_max = env_size("GMLRT_RESIDENT_KB", 128) * 1024;
     const size_t chunk_bytes = std::max<size_t>(env_size("GMLRT_CHUNK_KB", 32) * 1024, GROUP * rec_bytes);
-    const size_t all = (size_t)std::max(sc_.n_cull, GROUP) * rec_bytes;
-    if (all <= resident_max) { resident_ = 1; chunk_objs_ = std::max(sc_.n_cull, GROUP); scan_smem_ = LIST_BYTES + all; }
-    else { resident_ = 0; chunk_objs_ = (int)(chunk_bytes / rec_bytes) / GROUP * GROUP; scan_smem_ = LIST_BYTES + 2 * (size_t)chunk_objs_ * rec_bytes; }
-    auto grid_for = [&](auto kernel, int& grid) -> int {
+    const size_t all = (size_t)sc_.n_cull * rec_bytes;
+    if (all <= resident_max) { resident_ = 1; chunk_objs_ = sc_.n_cull; table_smem_ = all; }
+    else { resident_ = 0; chunk_objs_ = (int)(chunk_bytes / rec_bytes) / GROUP * GROUP; table_smem_ = 2 * (size_t)chunk_objs_ * rec_bytes; }
+    auto cfg = [&](auto kernel, size_t state, Launch& L) -> int {
         int occ = 1;
-        CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, SCAN_THREADS, scan_smem_));
-        grid = sms_ * std::max(occ, 1);
+        L.smem = CAND_CAP * sizeof(uint32_t) + state + table_smem_;
+        CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, SCAN_THREADS, L.smem));
+        L.grid = sms_ * std::max(occ, 1);
         return GMLRT_OK;
     };
     int rc;
-    if ((rc = grid_for(k_closest<R, false, false>, grid_closest_[0][0])) || (rc = grid_for(k_closest<R, false, true>, grid_closest_[0][1])) ||
-        (rc = grid_for(k_closest<R, kRobustPrimary, false>, grid_closest_[1][0])) || (rc = grid_for(k_closest<R, kRobustPrimary, true>, grid_closest_[1][1])) ||
-        (rc = grid_for(k_shadow<R, false>, grid_shadow_[0])) || (rc = grid_for(k_shadow<R, true>, grid_shadow_[1])))
+    const size_t lf = ClosestVisit<R, kRobustPrimary, false, RPT_FAMILY>::state_bytes(), lg = ClosestVisit<R, false, false, RPT_GENERAL>::state_bytes();
+    const size_t ls = ShadowVisit<R, false, RPT_FAMILY>::state_bytes();
+    if ((rc = cfg(k_closest<R, CULL_PIVOT, RPT_FAMILY, kRobustPrimary, false>, lf, l_primary_[0])) ||
+        (rc = cfg(k_closest<R, CULL_PIVOT, RPT_FAMILY, kRobustPrimary, true>, lf, l_primary_[1])) ||
+        (rc = cfg(k_closest<R, CULL_GENERAL, RPT_GENERAL, false, false>, lg, l_closest_[0])) ||
+        (rc = cfg(k_closest<R, CULL_GENERAL, RPT_GENERAL, false, true>, lg, l_closest_[1])) ||
+        (rc = cfg(k_shadow<R, CULL_PIVOT, RPT_FAMILY, false>, ls, l_shadow_pivot_[0])) || (rc = cfg(k_shadow<R, CULL_PIVOT, RPT_FAMILY, true>, ls, l_shadow_pivot_[1])) ||
+        (rc = cfg(k_shadow<R, CULL_AXIS, RPT_FAMILY, false>, ls, l_shadow_axis_[0])) || (rc = cfg(k_shadow<R, CULL_AXIS, RPT_FAMILY, true>, ls, l_shadow_axis_[1])))
         return rc;
     return GMLRT_OK;
 }
@@ -1650,15 +1838,17 @@ int Renderer<R>::trace_rows(int y0, int y1, bool counting, std::string& err) {
         totals_.rays_primary += (unsigned long long)S;
         for (int l = 0; l < depth_eff_; l++) {
             const int cap_blocks = (levels_[l].cap + SHADE_THREADS - 1) / SHADE_THREADS;
-            const bool robust = (l == 0 && kRobustPrimary);
-            const int gc = grid_closest_[robust][counting];
-            MARK(robust ? KC_CLOSEST_PRIMARY : KC_CLOSEST);
-            if (robust) {
-                if (counting) k_closest<R, kRobustPrimary, true><<<gc, SCAN_THREADS, scan_smem_, stream_>>>(sc_, levels_[l], ctr_, l, chunk_objs_, resident_);
-                else k_closest<R, kRobustPrimary, false><<<gc, SCAN_THREADS, scan_smem_, stream_>>>(sc_, levels_[l], ctr_, l, chunk_objs_, resident_);
+            const int ci = counting ? 1 : 0;
+            if (l == 0) {                                  // camera rays: PIVOT family through the eye, robust re-tests in f32
+                MARK(KC_CLOSEST_PRIMARY);
+                const Launch& L = l_primary_[ci];
+                if (counting) k_closest<R, CULL_PIVOT, RPT_FAMILY, kRobustPrimary, true><<<L.grid, SCAN_THREADS, L.smem, stream_>>>(sc_, levels_[l], cull_eye_, frame_eye_, ctr_, l, chunk_objs_, resident_);
+                else k_closest<R, CULL_PIVOT, RPT_FAMILY, kRobustPrimary, false><<<L.grid, SCAN_THREADS, L.smem, stream_>>>(sc_, levels_[l], cull_eye_, frame_eye_, ctr_, l, chunk_objs_, resident_);
             } else {
-                if (counting) k_closest<R, false, true><<<gc, SCAN_THREADS, scan_smem_, stream_>>>(sc_, levels_[l], ctr_, l, chunk_objs_, resident_);
-                else k_closest<R, false, false><<<gc, SCAN_THREADS, scan_smem_, stream_>>>(sc_, levels_[l], ctr_, l, chunk_objs_, resident_);
+                MARK(KC_CLOSEST);
+                const Launch& L = l_closest_[ci];
+                if (counting) k_closest<R, CULL_GENERAL, RPT_GENERAL, false, true><<<L.grid, SCAN_THREADS, L.smem, stream_>>>(sc_, levels_[l], cull_general_, frame_general_, ctr_, l, chunk_objs_, resident_);
+                else k_closest<R, CULL_GENERAL, RPT_GENERAL, false, false><<<L.grid, SCAN_THREADS, L.smem, stream_>>>(sc_, levels_[l], cull_general_, frame_general_, ctr_, l, chunk_objs_, resident_);
             }
             const bool spawn = l + 1 < depth_eff_;
             MARK(KC_SHADE);
@@ -1666,13 +1856,20 @@ int Renderer<R>::trace_rows(int y0, int y1, bool counting, std::string& err) {
                 sc_, levels_[l], spawn ? levels_[l + 1] : levels_[l], sq_, occl_[l], ctr_, l, spawn ? 1 : 0,
                 (counting && l == 0) ? ids_ : nullptr, ty);
             totals_.launches += 2;
-            if (sc_.n_lights > 0) {
+            for (int li = 0; li < sc_.n_lights; li++) {    // one launch per light: its shadow rays share a pivot (or an axis)
                 MARK(KC_SHADOW);
-                if (counting) k_shadow<R, true><<<grid_shadow_[1], SCAN_THREADS, scan_smem_, stream_>>>(sc_, sq_, occl_[l], ctr_, chunk_objs_, resident_);
-                else k_shadow<R, false><<<grid_shadow_[0], SCAN_THREADS, scan_smem_, stream_>>>(sc_, sq_, occl_[l], ctr_, chunk_objs_, resident_);
-                CU_TRY(cudaMemsetAsync(&ctr_->shadow_count, 0, sizeof(int), stream_));
+                const bool axis = frame_light_[li].family == CULL_AXIS;
+                const Launch& L = axis ? l_shadow_axis_[counting ? 1 : 0] : l_shadow_pivot_[counting ? 1 : 0];
+                if (axis) {
+                    if (counting) k_shadow<R, CULL_AXIS, RPT_FAMILY, true><<<L.grid, SCAN_THREADS, L.smem, stream_>>>(sc_, sq_, cull_light_[li], frame_light_[li], occl_[l], ctr_, li, chunk_objs_, resident_);
+                    else k_shadow<R, CULL_AXIS, RPT_FAMILY, false><<<L.grid, SCAN_THREADS, L.smem, stream_>>>(sc_, sq_, cull_light_[li], frame_light_[li], occl_[l], ctr_, li, chunk_objs_, resident_);
+                } else {
+                    if (counting) k_shadow<R, CULL_PIVOT, RPT_FAMILY, true><<<L.grid, SCAN_THREADS, L.smem, stream_>>>(sc_, sq_, cull_light_[li], frame_light_[li], occl_[l], ctr_, li, chunk_objs_, resident_);
+                    else k_shadow<R, CULL_PIVOT, RPT_FAMILY, false><<<L.grid, SCAN_THREADS, L.smem, stream_>>>(sc_, sq_, cull_light_[li], frame_light_[li], occl_[l], ctr_, li, chunk_objs_, resident_);
+                }
                 totals_.launches++;
             }
+            if (sc_.n_lights > 0) CU_TRY(cudaMemsetAsync(shadow_counts_, 0, sizeof(int) * sc_.n_lights, stream_));
         }
         for (int l = depth_eff_ - 1; l >= 0; l--) {
             const int cap_blocks = (levels_[l].cap + SHADE_THREADS - 1) / SHADE_THREADS;
