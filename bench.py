@@ -204,15 +204,15 @@ def main():
     sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches, kernel_ms = 0, 0.0
-    class_ms = [0.0] * 7
-    class_launches = [0] * 7
+    class_ms = [0.0] * 8
+    class_launches = [0] * 8
     with torch.cuda.stream(ext):
         e0.record()
     for _ in range(args.steps):
         st = step()
         launches += st.kernel_launches
         kernel_ms += st.ms_kernels
-        for k in range(7):
+        for k in range(8):
             class_ms[k] += st.ms_class[k]
             class_launches[k] += st.launches_class[k]
     with torch.cuda.stream(ext):
@@ -228,8 +228,8 @@ def main():
         tsum = t.clone()
         dist.all_reduce(tsum)
         ms_total, kernel_ms, launches = float(tmax[0]), float(tmax[1]), int(tsum[2])
-        class_ms = [float(x) for x in tmax[3:10]]
-        class_launches = [int(x) for x in tsum[10:17]]
+        class_ms = [float(x) for x in tmax[3:11]]
+        class_launches = [int(x) for x in tsum[11:19]]
     ctx.set_profiling(False)
     ms_step = ms_total / args.steps
     value = rays_frame / (ms_step * 1e-3) / 1e6
@@ -238,9 +238,16 @@ def main():
     host = np.empty((H, W, 4), dtype=np.uint8)
     pinned = torch.empty((H, W, 4), dtype=torch.uint8, pin_memory=True) if rank == 0 else None
 
+    phase_ms = {"upload": 0.0, "trace": 0.0, "download": 0.0}
+
     def e2e_step():
+        ta = time.perf_counter()
         ctx.upload(blob)                                    # H2D of this step's input
+        tb = time.perf_counter()
         step()
+        tc = time.perf_counter()
+        phase_ms["upload"] += (tb - ta) * 1e3
+        phase_ms["trace"] += (tc - tb) * 1e3
         if rank == 0:                                       # D2H of the step's result
             if dist is None:
                 ctx.download(pinned.numpy())
@@ -248,9 +255,12 @@ def main():
                 with torch.cuda.stream(ext):
                     pinned.copy_(gathered[0], non_blocking=True)
                 ext.synchronize()
+        phase_ms["download"] += (time.perf_counter() - tc) * 1e3
     for _ in range(2):
         e2e_step()
     barrier()
+    for k in phase_ms:
+        phase_ms[k] = 0.0
     t0 = time.perf_counter()
     e2e_steps = max(3, min(args.steps, 10))
     for _ in range(e2e_steps):
@@ -280,8 +290,8 @@ def main():
     fp32_peak = (fp32_measured if fp32_measured > 0 else fp32_derived) * world
     # dominant kernels: the scan kernels (closest-hit + shadow instantiations of one skeleton)
     names = cuda.Stats.KERNEL_CLASSES
-    scan_ms = sum(class_ms[k] for k in (1, 2, 3))
-    scan_launches = sum(class_launches[k] for k in (1, 2, 3))
+    scan_ms = sum(class_ms[k] for k in (1, 2, 3, 7))
+    scan_launches = sum(class_launches[k] for k in (1, 2, 3, 7))
     achieved = flops_frame * args.steps / (scan_ms * 1e-3) / 1e12 if scan_ms > 0 else 0.0
     traffic = None
     try:
@@ -299,11 +309,12 @@ def main():
                            "shadow_occluded": int(counts[4])},
         "gpu_launches": launches,
         "clocks": clocks,
-        "e2e": {"value": e2e_value, "unit": "Mrays/s", "frame_ms": e2e_ms, "h2d_bytes_per_step": len(blob), "d2h_bytes_per_step": W * H * 4},
-        "kernel_ms_per_frame": {names[k]: class_ms[k] / args.steps for k in range(7)},
+        "e2e": {"value": e2e_value, "unit": "Mrays/s", "frame_ms": e2e_ms, "h2d_bytes_per_step": len(blob), "d2h_bytes_per_step": W * H * 4,
+                "phase_ms": {k: v / e2e_steps for k, v in phase_ms.items()}},
+        "kernel_ms_per_frame": {names[k]: class_ms[k] / args.steps for k in range(8)},
         "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak if fp32_peak else None,
                      "traffic": traffic,
-                     "kernel": "scan kernels k_closest + k_shadow (one skeleton): %d launches, %.3f ms per frame" % (scan_launches, scan_ms / args.steps),
+                     "kernel": "scan kernels (k_cull x 4 instantiations + k_exact_*): %d event intervals, %.3f ms per frame" % (scan_launches, scan_ms / args.steps),
                      "peak_kind": "measured: FFMA-chain microbenchmark on this GPU (gmlrt_measure_fp32_tflops)" if fp32_measured > 0 else "derived",
                      "peak_derived": fp32_derived * world,
                      "note": "achieved = flops the scan kernels EXECUTE (14 per first-phase cull test = 7 FFMA, every query x every object; "

@@ -209,7 +209,8 @@ int gmlrt_set_partition(gmlrt_ctx* c, int part, int n_parts) {
 
 void* gmlrt_frame_device(gmlrt_ctx* c) { return c && !c->r.empty() ? (void*)c->r[0]->frame() : nullptr; }
 
-int gmlrt_trace(gmlrt_ctx* c, gmlrt_stats* stats) {
+static int trace_once(gmlrt_ctx* c, gmlrt_stats* stats, bool& overflow) {
+    overflow = false;
     if (!c) return fail(nullptr, GMLRT_E_BAD_ARG, "ctx is null");
     if (!c->have_scene) return fail(c, GMLRT_E_BAD_ARG, "gmlrt_trace before a successful gmlrt_upload");
     std::string err;
@@ -260,7 +261,7 @@ int gmlrt_trace(gmlrt_ctx* c, gmlrt_stats* stats) {
         sum.rays_shadow += t.rays_shadow; sum.shadow_occluded += t.shadow_occluded; sum.launches += t.launches;
         sum.shadow_tests += t.shadow_tests; sum.shadow_flops += t.shadow_flops; sum.exact_tests += t.exact_tests; sum.exact_flops += t.exact_flops;
         for (int k = 0; k < KC_COUNT; k++) { sum.ms_class[k] = std::max(sum.ms_class[k], t.ms_class[k]); sum.launches_class[k] += t.launches_class[k]; }
-        sum.error |= t.error;
+        sum.error |= t.error; overflow = overflow || t.overflow;
     }
     if (stats) {
         std::memset(stats, 0, sizeof *stats);
@@ -284,8 +285,29 @@ int gmlrt_trace(gmlrt_ctx* c, gmlrt_stats* stats) {
         stats->flops_executed = 14.0 * (double)stats->cull_tests + (double)sum.exact_flops;   // cull = 7 FFMA
         for (int k = 0; k < KC_COUNT; k++) { stats->ms_class[k] = sum.ms_class[k]; stats->launches_class[k] = sum.launches_class[k]; }
     }
+    if (overflow) return GMLRT_OK;      // the caller shrinks the tiles and traces again
     if (sum.error) return fail(c, GMLRT_E_SURFACE, "a surface function faulted at render time (the reference panics here, raytracer.go:499-501)");
     return GMLRT_OK;
+}
+
+int gmlrt_trace(gmlrt_ctx* c, gmlrt_stats* stats) {
+    if (!c) return fail(nullptr, GMLRT_E_BAD_ARG, "ctx is null");
+    // a cull launch that runs out of candidate queue raises Counters::overflow: that frame is discarded, the tiles are
+    // halved (same buffers, so twice the queue per ray) and the frame is traced again
+    for (int attempt = 0; attempt < 12; attempt++) {
+        bool overflow = false;
+        int rc = trace_once(c, stats, overflow);
+        if (rc != GMLRT_OK || !overflow) return rc;
+        c->have_frame = false;
+        std::string err;
+        int min_rows = c->scene.height;
+        for (auto& r : c->r) {
+            if (!r->shrink_tiles(c->scene, err)) return fail(c, GMLRT_E_OOM, "candidate queue overflow: " + err);
+            min_rows = std::min(min_rows, r->max_rows_per_tile());
+        }
+        c->band_rows = std::max(1, std::min(c->band_rows, min_rows));
+    }
+    return fail(c, GMLRT_E_OOM, "candidate queue overflow persists after shrinking the tiles");
 }
 
 int gmlrt_download(gmlrt_ctx* c, uint8_t* rgba, size_t rgba_bytes) {

@@ -78,7 +78,8 @@ template <typename R> struct Level {
     R* ray;       // [6][cap] origin xyz, direction xyz
     int* parent;  // [cap] index in the previous level | (1<<31 for the refraction slot)
     int* hit;     // [cap] device leaf index | face << 28, or -1
-    R* t;         // [cap]
+    R* t;         // [cap] T of the hit; during the scan: bit pattern of the smallest T so far (all ones = none)
+    int* order;   // [cap] scan scratch: smallest scan index among the hits that have the smallest T
     R* rec;       // [NREC][cap]
     R* child;     // [6][cap] colour returned by the reflection / refraction child
     double* ray64; // [6][cap] level 0 in f32 mode only: the camera ray before rounding to float
@@ -89,6 +90,7 @@ template <typename R> struct ShadowQueue {      // one segment of `per_light` sl
     R* q;         // [8][cap] origin xyz, direction xyz, distance to light, |incoming direction|
     int* skip;    // [cap] device leaf index of the shaded object (inShadow skips it)
     int* target;  // [cap] node * n_lights + light
+    int* first;   // [cap] scan result: smallest scan index of an occluder, 0x7fffffff = none
     int* count;   // [n_lights] queued rays per light
     int cap, per_light;
 };
@@ -96,6 +98,7 @@ template <typename R> struct ShadowQueue {      // one segment of `per_light` sl
 struct Counters {                  // device-resident, zeroed per trace
     int count[GMLRT_MAX_DEPTH + 1];     // rays per level
     int error;
+    int overflow;                       // a cull launch ran out of candidate queue: retrace with smaller tiles
     unsigned long long rays_reflect, rays_refract, rays_shadow, shadow_occluded;
     unsigned long long shadow_tests, shadow_flops;   // credited: the reference's scan up to its first occluder (counting mode)
     unsigned long long exact_tests, exact_flops;     // executed second-phase tests and their table flops (counting mode)
@@ -475,6 +478,7 @@ __device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem
 // Each thread carries RPT rays so that the record load and the loop overhead are shared.
 constexpr int SCAN_THREADS = 256;
 constexpr int GROUP = 64;                   // objects per window: one 64-bit survivor mask per ray, kept in two registers
+constexpr int CULL_UNROLL = 8;              // objects per unrolled body of the cull loop
 enum CullFamily { CULL_GENERAL = 0, CULL_PIVOT = 1, CULL_AXIS = 2 };
 
 __device__ __forceinline__ float fma_(float a, float b, float c) { return __fmaf_rn(a, b, c); }
@@ -500,68 +504,77 @@ __device__ __forceinline__ Cull4<double> load_cull(const double* sm, int i) {
 template <typename R> struct CullFrame { int family; R e1[3], e2[3]; };   // AXIS: orthonormal basis of the plane orthogonal to the common direction
 
 template <typename R, int FAMILY> struct CullRay;
+// slack(L) < 0 (sign bit set)  <=>  the object may be hit; > 0  <=>  certainly missed
 template <typename R> struct CullRay<R, CULL_GENERAL> {
-    R o2x, o2y, o2z, dx, dy, dz, nod, cmp;
-    __device__ __forceinline__ void init(const Ray<R>& w, bool active, const CullFrame<R>&) {
+    R o2x, o2y, o2z, dx, dy, dz, nod, ncmp;
+    __device__ __forceinline__ void init(const Ray<R>& w, const CullFrame<R>&) {
         const R inv = R(1) / gm<R>::sqrt(fma_(w.dx, w.dx, fma_(w.dy, w.dy, w.dz * w.dz)));
         dx = w.dx * inv; dy = w.dy * inv; dz = w.dz * inv;
         o2x = R(-2) * w.ox; o2y = R(-2) * w.oy; o2z = R(-2) * w.oz;
         nod = -fma_(w.ox, dx, fma_(w.oy, dy, w.oz * dz));
         const R oo = fma_(w.ox, w.ox, fma_(w.oy, w.oy, w.oz * w.oz));
-        cmp = active ? fma_(oo, R(CullMargin<R>::rel), -oo) : -gm<R>::inf();    // inactive: everything is rejected
+        ncmp = fma_(oo, R(-CullMargin<R>::rel), oo);                           // |o|^2 (1 - margin)
     }
-    __device__ __forceinline__ bool reject(const Cull4<R>& L) const {
+    __device__ __forceinline__ R slack(const Cull4<R>& L) const {
         const R A = fma_(L.x, o2x, fma_(L.y, o2y, fma_(L.z, o2z, L.k)));
         const R B = fma_(L.x, dx, fma_(L.y, dy, fma_(L.z, dz, nod)));
-        return fma_(-B, B, A) > cmp;                                           // NaN survives
+        return fma_(-B, B, A) + ncmp;
     }
-    __device__ __forceinline__ void retire() { cmp = -gm<R>::inf(); }
 };
 template <typename R> struct CullRay<R, CULL_PIVOT> {
-    R dx, dy, dz, cmp;
-    __device__ __forceinline__ void init(const Ray<R>& w, bool active, const CullFrame<R>&) {
+    R dx, dy, dz;
+    __device__ __forceinline__ void init(const Ray<R>& w, const CullFrame<R>&) {
         const R inv = R(1) / gm<R>::sqrt(fma_(w.dx, w.dx, fma_(w.dy, w.dy, w.dz * w.dz)));
         dx = w.dx * inv; dy = w.dy * inv; dz = w.dz * inv;
-        cmp = active ? R(0) : -gm<R>::inf();
     }
-    __device__ __forceinline__ bool reject(const Cull4<R>& L) const {
+    __device__ __forceinline__ R slack(const Cull4<R>& L) const {
         const R B = fma_(L.x, dx, fma_(L.y, dy, L.z * dz));
-        return fma_(-B, B, L.k) > cmp;
+        return fma_(-B, B, L.k);
     }
-    __device__ __forceinline__ void retire() { cmp = -gm<R>::inf(); }
 };
 template <typename R> struct CullRay<R, CULL_AXIS> {
-    R ou, ov, cmp;
-    __device__ __forceinline__ void init(const Ray<R>& w, bool active, const CullFrame<R>& fr) {
+    R ou, ov, ncmp;
+    __device__ __forceinline__ void init(const Ray<R>& w, const CullFrame<R>& fr) {
         ou = fma_(w.ox, fr.e1[0], fma_(w.oy, fr.e1[1], w.oz * fr.e1[2]));
         ov = fma_(w.ox, fr.e2[0], fma_(w.oy, fr.e2[1], w.oz * fr.e2[2]));
         const R oo = fma_(w.ox, w.ox, fma_(w.oy, w.oy, w.oz * w.oz));
-        cmp = active ? R(CullMargin<R>::rel) * (oo + R(1)) : -gm<R>::inf();
+        ncmp = -R(CullMargin<R>::rel) * (oo + R(1));
     }
-    __device__ __forceinline__ bool reject(const Cull4<R>& L) const {       // record: (Cu, Cv, -R^2 - margin, unused)
+    __device__ __forceinline__ R slack(const Cull4<R>& L) const {          // record: (Cu, Cv, -R^2 - margin, unused)
         const R du = L.x - ou, dv = L.y - ov;
-        return fma_(dv, dv, fma_(du, du, L.z)) > cmp;
+        return fma_(dv, dv, fma_(du, du, L.z)) + ncmp;
     }
-    __device__ __forceinline__ void retire() { cmp = -gm<R>::inf(); }
 };
 
-// one window: objects [w * GROUP, (w + 1) * GROUP) of the staged table `sm` (whose first record is object sm_base);
-// bit j of (lo, hi)[r] = object w * GROUP + j survives ray r
+// shift the sign bit of `s` into the low end of a 32-bit mask: one funnel shift per test
+__device__ __forceinline__ uint32_t push_sign(uint32_t mask, float s) { return __funnelshift_l(__float_as_uint(s), mask, 1); }
+__device__ __forceinline__ uint32_t push_sign(uint32_t mask, double s) { return __funnelshift_l((uint32_t)__double2hiint(s), mask, 1); }
+
+// one window: objects first .. first + GROUP - 1 of the staged table `sm`; test j of each half lands in bit 31 - j
+// of lo / hi (the masks are shifted left once per test), set = object survives ray r
 template <typename R, int FAMILY, int RPT>
 __device__ __forceinline__ void cull_window(const R* sm, int first, const CullRay<R, FAMILY> (&cr)[RPT], uint32_t (&lo)[RPT], uint32_t (&hi)[RPT]) {
 #pragma unroll
     for (int r = 0; r < RPT; r++) { lo[r] = 0; hi[r] = 0; }
+    // unrolled by CULL_UNROLL only: the fully unrolled window (1300+ instructions) missed the instruction cache
+    // ("no_instruction" was the top stall); the masks are built by shifting, so the body needs no immediates
+#pragma unroll 1
+    for (int j0 = 0; j0 < 32; j0 += CULL_UNROLL) {
 #pragma unroll
-    for (int j = 0; j < 32; j++) {
-        const Cull4<R> L = load_cull(sm, first + j);
+        for (int j = 0; j < CULL_UNROLL; j++) {
+            const Cull4<R> L = load_cull(sm, first + j0 + j);
 #pragma unroll
-        for (int r = 0; r < RPT; r++) if (!cr[r].reject(L)) lo[r] |= 1u << j;
+            for (int r = 0; r < RPT; r++) lo[r] = push_sign(lo[r], cr[r].slack(L));
+        }
     }
+#pragma unroll 1
+    for (int j0 = 32; j0 < 64; j0 += CULL_UNROLL) {
 #pragma unroll
-    for (int j = 0; j < 32; j++) {
-        const Cull4<R> L = load_cull(sm, first + 32 + j);
+        for (int j = 0; j < CULL_UNROLL; j++) {
+            const Cull4<R> L = load_cull(sm, first + j0 + j);
 #pragma unroll
-        for (int r = 0; r < RPT; r++) if (!cr[r].reject(L)) hi[r] |= 1u << j;
+            for (int r = 0; r < RPT; r++) hi[r] = push_sign(hi[r], cr[r].slack(L));
+        }
     }
 }
 
@@ -658,127 +671,6 @@ __device__ __forceinline__ void stage_cull(const R* table, int base, int cnt, R*
     tma_load_1d(dst, table + (size_t)base * 4, bytes, bar);
 }
 
-// Shared skeleton of the scan kernels.  Persistent CTAs over blocks of SCAN_THREADS * RPT rays; the cull table
-// is staged once per CTA when it fits ("resident"), else streamed through two buffers per block of rays.
-//
-// Phase 1 (per thread, RPT rays in registers): cull a window of GROUP objects -> survivor masks -> every set
-// bit is appended to the CTA's candidate list in shared memory as (object << 10 | ray slot).
-// Phase 2 (CTA-wide, dense): when the list fills up, and after the last window, the CTA's threads take one
-// candidate each and run the exact test - every lane busy, instead of the few lanes of a warp that happen to
-// have a survivor in the same window.  `Visit` owns the per-ray result state in shared memory and supplies
-// setup / dense / finish.
-constexpr int CAND_CAP = 4096;              // candidate list entries per CTA
-constexpr int CAND_DRAIN = 2048;            // run phase 2 once this many are queued
-constexpr int SLOT_BITS = 10;               // ray slot within the CTA (SCAN_THREADS * RPT <= 1024)
-
-template <typename R, int FAMILY, int RPT, typename Visit>
-__device__ __forceinline__ void scan_rays(const DevScene<R>& sc, const R* table, const CullFrame<R>& frame, int n, int chunk_objs,
-                                          int resident, Visit& V) {
-    constexpr int RAYS_PER_BLOCK = SCAN_THREADS * RPT;
-    static_assert(RAYS_PER_BLOCK <= (1 << SLOT_BITS), "ray slot does not fit the candidate entry");
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    __shared__ __align__(8) uint64_t bar[2];
-    __shared__ int cand_count;
-    uint32_t* const list = reinterpret_cast<uint32_t*>(smem_raw);
-    unsigned char* const state = smem_raw + CAND_CAP * sizeof(uint32_t);
-    R* const tab = reinterpret_cast<R*>(state + Visit::state_bytes());       // buffer b starts at tab + b * chunk_objs * 4
-    const int nblocks = (n + RAYS_PER_BLOCK - 1) / RAYS_PER_BLOCK;
-    if ((int)blockIdx.x >= nblocks) return;
-    const int tid = threadIdx.x;
-    const int NP = sc.n_cull;                                  // padded to a multiple of GROUP
-    const int nchunks = (NP + chunk_objs - 1) / chunk_objs;
-    if (tid == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_fence_init(); cand_count = 0; }
-    __syncthreads();
-    uint32_t phase[2] = {0, 0};
-    if (resident && NP > 0) {
-        if (tid == 0) stage_cull(table, 0, NP, tab, &bar[0]);
-        mbar_wait(&bar[0], 0);
-    }
-    for (int blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
-        const int ray0 = blk * RAYS_PER_BLOCK;
-        CullRay<R, FAMILY> cr[RPT];
-        bool active[RPT];
-#pragma unroll
-        for (int r = 0; r < RPT; r++) {
-            const int slot = r * SCAN_THREADS + tid;
-            Ray<R> w = {R(0), R(0), R(0), R(0), R(0), R(1)};
-            active[r] = V.setup(state, slot, ray0 + slot, ray0 + slot < n, w);
-            cr[r].init(w, active[r], frame);
-        }
-        __syncthreads();                                       // per-ray state initialised before any phase 2
-        // one window of GROUP objects starting at object `first` (record sm[first - sm_base])
-        auto window = [&](const R* sm, int sm_base, int first) {
-            uint32_t lo[RPT], hi[RPT];
-            cull_window<R, FAMILY, RPT>(sm, first - sm_base, cr, lo, hi);
-#pragma unroll
-            for (int r = 0; r < RPT; r++) if (!active[r]) { lo[r] = 0; hi[r] = 0; }
-            bool more;
-            do {
-#pragma unroll
-                for (int r = 0; r < RPT; r++) {
-                    const uint32_t slot = (uint32_t)(r * SCAN_THREADS + tid);
-                    while (lo[r]) {
-                        const int k = atomicAdd(&cand_count, 1);
-                        if (k >= CAND_CAP) break;              // full: keep the bit, retry after the drain
-                        list[k] = ((uint32_t)(first + __ffs(lo[r]) - 1) << SLOT_BITS) | slot;
-                        lo[r] &= lo[r] - 1;
-                    }
-                    while (!lo[r] && hi[r]) {
-                        const int k = atomicAdd(&cand_count, 1);
-                        if (k >= CAND_CAP) break;
-                        list[k] = ((uint32_t)(first + 32 + __ffs(hi[r]) - 1) << SLOT_BITS) | slot;
-                        hi[r] &= hi[r] - 1;
-                    }
-                }
-                __syncthreads();
-                const int c = cand_count;                      // uniform: read between two barriers
-                more = c > CAND_CAP;
-                if (c >= CAND_DRAIN) {
-                    V.dense(state, list, min(c, CAND_CAP), ray0);
-                    __syncthreads();
-                    if (tid == 0) cand_count = 0;
-                }
-                __syncthreads();
-            } while (more);
-        };
-        if (resident) {
-            for (int first = 0; first < NP; first += GROUP) window(tab, 0, first);
-        } else {
-            if (tid == 0) {
-                stage_cull(table, 0, min(chunk_objs, NP), tab, &bar[0]);
-                if (nchunks > 1) stage_cull(table, chunk_objs, min(chunk_objs, NP - chunk_objs), tab + (size_t)chunk_objs * 4, &bar[1]);
-            }
-            for (int c = 0; c < nchunks; c++) {
-                const int b = c & 1;
-                mbar_wait(&bar[b], phase[b]);
-                phase[b] ^= 1;
-                const int base = c * chunk_objs;
-                const R* sm = tab + (size_t)b * chunk_objs * 4;
-                const int end = base + min(chunk_objs, NP - base);
-                for (int first = base; first < end; first += GROUP) window(sm, base, first);   // ends with a barrier: buffer b is free
-                if (tid == 0 && c + 2 < nchunks) {
-                    const int nb = (c + 2) * chunk_objs;
-                    stage_cull(table, nb, min(chunk_objs, NP - nb), tab + (size_t)b * chunk_objs * 4, &bar[b]);
-                }
-            }
-        }
-        {   // last drain of this block of rays
-            const int c = cand_count;                          // every window ends with a barrier
-            if (c > 0) V.dense(state, list, c, ray0);
-            __syncthreads();
-            if (tid == 0) cand_count = 0;
-        }
-#pragma unroll
-        for (int r = 0; r < RPT; r++) if (active[r]) V.finish(state, r * SCAN_THREADS + tid, ray0 + r * SCAN_THREADS + tid);
-        __syncthreads();                                       // state is re-initialised by the next block of rays
-    }
-}
-
-__device__ __forceinline__ void warp_add(unsigned long long* dst, unsigned long long v) {
-    for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
-    if ((threadIdx.x & 31) == 0 && v) atomicAdd(dst, v);
-}
-
 template <typename R> struct BitsOf;
 template <> struct BitsOf<float> {
     typedef unsigned int type;
@@ -791,121 +683,243 @@ template <> struct BitsOf<double> {
     static __device__ __forceinline__ double back(unsigned long long b) { return __longlong_as_double((long long)b); }
 };
 
-// closestHit for one recursion level (raytracer.go:469-483): strictly smaller T wins, equal T keeps the object
-// that comes first in scan order.  Per ray in shared memory: the smallest T so far (hits have T > 0, so the bit
-// pattern orders like the value), the smallest scan index among the hits with that T, and that hit's code.
-template <typename R, bool ROBUST, bool COUNT, int RPT> struct ClosestVisit {
-    typedef typename BitsOf<R>::type UB;
-    static constexpr int NR = SCAN_THREADS * RPT;
-    const DevScene<R>& sc; const Level<R>& lv;
-    unsigned long long n_exact, n_flops;
-    __device__ ClosestVisit(const DevScene<R>& s, const Level<R>& l) : sc(s), lv(l), n_exact(0), n_flops(0) {}
-    static __host__ __device__ constexpr size_t state_bytes() { return (size_t)NR * (sizeof(UB) + 8); }
-    static __device__ __forceinline__ UB* tbest(unsigned char* st) { return reinterpret_cast<UB*>(st); }
-    static __device__ __forceinline__ int* order(unsigned char* st) { return reinterpret_cast<int*>(st + (size_t)NR * sizeof(UB)); }
-    static __device__ __forceinline__ int* codes(unsigned char* st) { return order(st) + NR; }
-    __device__ __forceinline__ void load_ray(int i, Ray<R>& out) const {
+// ------------------------------------------------------------------ scan = cull kernel + exact kernels
+// Phase 1, k_cull: persistent CTAs over blocks of SCAN_THREADS * RPT rays; the cull table is staged once per
+// CTA when it fits ("resident"), else streamed through two buffers per block of rays.  Each thread carries RPT
+// rays in registers, culls a window of GROUP objects into survivor masks, and the warp appends every set bit to
+// the launch's candidate queue in HBM as a (ray, object) pair - one atomic per warp and window.
+// Phase 2, k_exact_*: one thread per candidate runs the reference's own test - every lane busy, instead of the
+// few lanes of a warp that happen to have a survivor in the same window - and folds the result into the ray's
+// record with atomics.
+//
+// The queue is sized from the scene (Renderer::plan_tiles); if a launch overflows it, `Counters::overflow`
+// is raised, the frame is discarded and traced again with smaller tiles (gmlrt_trace).
+struct CandQueue {
+    int* ray;        // [cap] ray index within the launch's ray source
+    int* obj;        // [cap] object index; k_exact_closest overwrites it with the hit code (or -1)
+    void* t;         // [cap] R: T of the hit (closest only)
+    int* count;      // entries appended by the current launch
+    int cap;
+};
+
+template <typename R> struct ClosestSource {                 // rays of one recursion level
+    Level<R> lv;
+    __device__ __forceinline__ void load(int i, Ray<R>& out) const {
         const size_t cap = (size_t)lv.cap;
         out.ox = lv.ray[i]; out.oy = lv.ray[cap + i]; out.oz = lv.ray[2 * cap + i];
         out.dx = lv.ray[3 * cap + i]; out.dy = lv.ray[4 * cap + i]; out.dz = lv.ray[5 * cap + i];
     }
-    __device__ __forceinline__ bool setup(unsigned char* st, int slot, int i, bool act, Ray<R>& out) {
-        tbest(st)[slot] = ~(UB)0; order(st)[slot] = 0x7fffffff; codes(st)[slot] = -1;
-        if (act) load_ray(i, out);
-        return act;
-    }
-    __device__ __forceinline__ void dense(unsigned char* st, const uint32_t* list, int count, int ray0) {
-        UB* tb = tbest(st); int* ord = order(st); int* cod = codes(st);
-        const int iters = (count + SCAN_THREADS - 1) / SCAN_THREADS;
-        for (int it = 0; it < iters; it++) {
-            const int k = it * SCAN_THREADS + threadIdx.x;
-            bool hit = false, lowered = false;
-            R t = R(0); int code = -1, slot = 0, scan = 0;
-            UB b = 0;
-            if (k < count) {
-                const uint32_t e = list[k];
-                slot = (int)(e & ((1u << SLOT_BITS) - 1));
-                const int obj = (int)(e >> SLOT_BITS);
-                if (obj < sc.n_leaves) {                     // a padding record can only be reached by a NaN ray
-                    if (COUNT) { n_exact++; n_flops += (unsigned)sc.obj_flops[obj]; }
-                    Ray<R> w;
-                    load_ray(ray0 + slot, w);
-                    hit = exact_hit<R, ROBUST>(sc, obj, w, lv.ray64, lv.cap, ray0 + slot, t, code);
-                    scan = sc.scan_of[obj];
-                }
-            }
-            if (hit) { b = BitsOf<R>::of(t); const UB old = atomicMin(&tb[slot], b); lowered = b < old; }
-            __syncthreads();
-            if (hit && lowered && tb[slot] == b) ord[slot] = 0x7fffffff;        // a new smallest T: forget the old tie-break
-            __syncthreads();
-            if (hit && tb[slot] == b) atomicMin(&ord[slot], scan);
-            __syncthreads();
-            if (hit && tb[slot] == b && ord[slot] == scan) cod[slot] = code;
-        }
-    }
-    __device__ __forceinline__ void finish(unsigned char* st, int slot, int i) {
-        const int code = codes(st)[slot];
-        lv.hit[i] = code;
-        lv.t[i] = code < 0 ? R(0) : BitsOf<R>::back(tbest(st)[slot]);
+    __device__ __forceinline__ void init(int i) const {       // no hit yet
+        lv.hit[i] = -1;
+        reinterpret_cast<typename BitsOf<R>::type*>(lv.t)[i] = ~(typename BitsOf<R>::type)0;
+        lv.order[i] = 0x7fffffff;
     }
 };
 
-template <typename R, int FAMILY, int RPT, bool ROBUST, bool COUNT>
-__global__ void __launch_bounds__(SCAN_THREADS, sizeof(R) == 4 ? 4 : 2) k_closest(const __grid_constant__ DevScene<R> sc, const __grid_constant__ Level<R> lv,
-                                                          const R* table, const __grid_constant__ CullFrame<R> frame,
-                                                          Counters* ctr, int level, int chunk_objs, int resident) {
-    ClosestVisit<R, ROBUST, COUNT, RPT> V(sc, lv);
-    scan_rays<R, FAMILY, RPT>(sc, table, frame, ctr->count[level], chunk_objs, resident, V);
-    if (COUNT) {
-        warp_add(&ctr->exact_tests, V.n_exact);
-        warp_add(&ctr->exact_flops, V.n_flops);
+template <typename R> struct ShadowSource {                  // shadow rays of one light: slots [base, base + n)
+    ShadowQueue<R> sq; int base;
+    __device__ __forceinline__ void load(int i, Ray<R>& out) const {
+        const size_t cap = (size_t)sq.cap; const int q = base + i;
+        out.ox = sq.q[q]; out.oy = sq.q[cap + q]; out.oz = sq.q[2 * cap + q];
+        out.dx = sq.q[3 * cap + q]; out.dy = sq.q[4 * cap + q]; out.dz = sq.q[5 * cap + q];
+    }
+    __device__ __forceinline__ void init(int i) const { sq.first[base + i] = 0x7fffffff; }
+};
+
+template <typename R, int FAMILY, int RPT, typename Source>
+__global__ void __launch_bounds__(SCAN_THREADS, sizeof(R) == 4 ? 3 : 2)
+k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, const __grid_constant__ CullFrame<R> frame,
+       int n_cull, const __grid_constant__ CandQueue cq, Counters* ctr, int chunk_objs, int resident) {
+    constexpr int RAYS_PER_BLOCK = SCAN_THREADS * RPT;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ __align__(8) uint64_t bar[2];
+    const int tid = threadIdx.x, lane = tid & 31;
+    R* const tab = reinterpret_cast<R*>(smem_raw);             // buffer b starts at tab + b * chunk_objs * 4
+    const int n = *n_ptr;
+    const int nblocks = (n + RAYS_PER_BLOCK - 1) / RAYS_PER_BLOCK;
+    if ((int)blockIdx.x >= nblocks) return;
+    const int NP = n_cull;                                     // padded to a multiple of GROUP
+    const int nchunks = (NP + chunk_objs - 1) / chunk_objs;
+    if (tid == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_fence_init(); }
+    __syncthreads();
+    uint32_t phase[2] = {0, 0};
+    if (resident && NP > 0) {
+        if (tid == 0) stage_cull(table, 0, NP, tab, &bar[0]);
+        mbar_wait(&bar[0], 0);
+    }
+    for (int blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
+        const int ray0 = blk * RAYS_PER_BLOCK;
+        CullRay<R, FAMILY> cr[RPT];
+        bool active[RPT];
+#pragma unroll
+        for (int r = 0; r < RPT; r++) {
+            const int i = ray0 + r * SCAN_THREADS + tid;
+            Ray<R> w = {R(0), R(0), R(0), R(0), R(0), R(1)};
+            active[r] = i < n;
+            if (active[r]) { src.load(i, w); src.init(i); }
+            cr[r].init(w, frame);
+        }
+        if (!resident) {
+            __syncthreads();                                   // (re)staging must not overtake readers of the previous block of rays
+            if (tid == 0) {
+                stage_cull(table, 0, min(chunk_objs, NP), tab, &bar[0]);
+                if (nchunks > 1) stage_cull(table, chunk_objs, min(chunk_objs, NP - chunk_objs), tab + (size_t)chunk_objs * 4, &bar[1]);
+            }
+        }
+        for (int c = 0; c < (resident ? 1 : nchunks); c++) {   // a resident table is one chunk that is already staged
+            const int b = c & 1;
+            if (!resident) { mbar_wait(&bar[b], phase[b]); phase[b] ^= 1; }
+            const int base = resident ? 0 : c * chunk_objs;
+            const R* sm = resident ? tab : tab + (size_t)b * chunk_objs * 4;
+            const int end = resident ? NP : base + min(chunk_objs, NP - base);
+            for (int first = base; first < end; first += GROUP) {          // one window of GROUP objects
+                uint32_t lo[RPT], hi[RPT];
+                cull_window<R, FAMILY, RPT>(sm, first - base, cr, lo, hi);
+                int mine = 0;
+#pragma unroll
+                for (int r = 0; r < RPT; r++) {
+                    if (!active[r]) { lo[r] = 0; hi[r] = 0; }
+                    mine += __popc(lo[r]) + __popc(hi[r]);
+                }
+                if (!__any_sync(0xffffffffu, mine != 0)) continue;         // nothing survived in this warp
+                // warp-aggregated append: inclusive scan of the lanes' counts, one atomic for the warp
+                int incl = mine;
+#pragma unroll
+                for (int off = 1; off < 32; off <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, off); if (lane >= off) incl += v; }
+                const int total = __shfl_sync(0xffffffffu, incl, 31);
+                int at = 0;
+                if (lane == 31) at = atomicAdd(cq.count, total);
+                at = __shfl_sync(0xffffffffu, at, 31) + incl - mine;
+                if (at + mine > cq.cap) { if (mine) ctr->overflow = 1; continue; }   // queue full: the host retries with smaller tiles
+#pragma unroll
+                for (int r = 0; r < RPT; r++) {
+                    const int i = ray0 + r * SCAN_THREADS + tid;
+                    uint32_t m = lo[r];
+                    while (m) {                                // test j of the first half sits in bit 31 - j
+                        const int j = __clz(m);
+                        m &= ~(0x80000000u >> j);
+                        cq.ray[at] = i; cq.obj[at] = first + j; at++;
+                    }
+                    m = hi[r];
+                    while (m) {
+                        const int j = __clz(m);
+                        m &= ~(0x80000000u >> j);
+                        cq.ray[at] = i; cq.obj[at] = first + 32 + j; at++;
+                    }
+                }
+            }
+            if (!resident) {
+                __syncthreads();                               // everyone is done reading buffer b
+                if (tid == 0 && c + 2 < nchunks) {
+                    const int nb = (c + 2) * chunk_objs;
+                    stage_cull(table, nb, min(chunk_objs, NP - nb), tab + (size_t)b * chunk_objs * 4, &bar[b]);
+                }
+            }
+        }
     }
 }
 
-// inShadow for the queued (hit, light) pairs of ONE light (raytracer.go:411-429): writes occl[target] = 1 when
-// some object other than the shaded one has  shadowHit.T * |ray.Direction| < distToLight  (:424).  The answer
-// does not depend on the order objects are visited in; COUNT additionally finds the FIRST occluder in the
-// reference's scan order to credit the tests the reference itself would have run.
-template <typename R, bool COUNT, int RPT> struct ShadowVisit {
-    static constexpr int NR = SCAN_THREADS * RPT;
-    const DevScene<R>& sc; const ShadowQueue<R>& sq; unsigned char* occl; int qbase;
-    unsigned long long n_exact, n_flops, n_occluded, cred_tests, cred_flops;
-    __device__ ShadowVisit(const DevScene<R>& s, const ShadowQueue<R>& q, unsigned char* o, int base)
-        : sc(s), sq(q), occl(o), qbase(base), n_exact(0), n_flops(0), n_occluded(0), cred_tests(0), cred_flops(0) {}
-    static __host__ __device__ constexpr size_t state_bytes() { return (size_t)NR * 4; }
-    static __device__ __forceinline__ int* first(unsigned char* st) { return reinterpret_cast<int*>(st); }   // smallest scan index of an occluder
-    __device__ __forceinline__ void load_ray(int i, Ray<R>& out) const {
-        const size_t cap = (size_t)sq.cap;
-        out.ox = sq.q[i]; out.oy = sq.q[cap + i]; out.oz = sq.q[2 * cap + i];
-        out.dx = sq.q[3 * cap + i]; out.dy = sq.q[4 * cap + i]; out.dz = sq.q[5 * cap + i];
-    }
-    __device__ __forceinline__ bool setup(unsigned char* st, int slot, int i, bool act, Ray<R>& out) {
-        first(st)[slot] = 0x7fffffff;
-        if (act) load_ray(qbase + i, out);
-        return act;
-    }
-    __device__ __forceinline__ void dense(unsigned char* st, const uint32_t* list, int count, int ray0) {
-        int* fo = first(st);
-        for (int k = threadIdx.x; k < count; k += SCAN_THREADS) {
-            const uint32_t e = list[k];
-            const int slot = (int)(e & ((1u << SLOT_BITS) - 1));
-            const int obj = (int)(e >> SLOT_BITS);
-            const int q = qbase + ray0 + slot;
-            if (obj >= sc.n_leaves || obj == sq.skip[q]) continue;
-            if (!COUNT && fo[slot] != 0x7fffffff) continue;    // already occluded (a stale read only costs a test)
+__device__ __forceinline__ void warp_add(unsigned long long* dst, unsigned long long v) {
+    for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
+    if ((threadIdx.x & 31) == 0 && v) atomicAdd(dst, v);
+}
+
+constexpr int EXACT_THREADS = 128;
+
+// closestHit (raytracer.go:469-483): strictly smaller T wins, equal T keeps the object that comes first in scan
+// order.  Three passes over the candidates: (1) exact test, T of a hit into the queue and atomicMin into the ray's
+// record (hits have T > 0, so the bit pattern orders like the value); (2) among the hits that have the ray's
+// smallest T, atomicMin of the scan index; (3) the winner writes its hit code.
+template <typename R, bool ROBUST, bool COUNT>
+__global__ void __launch_bounds__(EXACT_THREADS) k_exact_closest(const __grid_constant__ DevScene<R> sc, const __grid_constant__ Level<R> lv,
+                                                                const __grid_constant__ CandQueue cq, Counters* ctr) {
+    typedef typename BitsOf<R>::type UB;
+    const int count = min(*cq.count, cq.cap);
+    UB* tbest = reinterpret_cast<UB*>(lv.t);
+    R* ct = reinterpret_cast<R*>(cq.t);
+    unsigned long long n_exact = 0, n_flops = 0;
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
+        const int ri = cq.ray[k], obj = cq.obj[k];
+        int code = -1; R t = R(0);
+        if (obj < sc.n_leaves) {                               // a padding record can only be reached by a NaN ray
             if (COUNT) { n_exact++; n_flops += (unsigned)sc.obj_flops[obj]; }
             Ray<R> w;
-            load_ray(q, w);
-            R t; int code;
-            if (!exact_hit<R, false>(sc, obj, w, nullptr, 0, 0, t, code)) continue;
-            const size_t cap = (size_t)sq.cap;
-            if (t * sq.q[7 * cap + q] < sq.q[6 * cap + q])     // T * |incoming direction| < distance to the light
-                atomicMin(&fo[slot], sc.scan_of[obj]);
+            const size_t cap = (size_t)lv.cap;
+            w.ox = lv.ray[ri]; w.oy = lv.ray[cap + ri]; w.oz = lv.ray[2 * cap + ri];
+            w.dx = lv.ray[3 * cap + ri]; w.dy = lv.ray[4 * cap + ri]; w.dz = lv.ray[5 * cap + ri];
+            if (exact_hit<R, ROBUST>(sc, obj, w, lv.ray64, lv.cap, ri, t, code)) atomicMin(&tbest[ri], BitsOf<R>::of(t));
+            else code = -1;
         }
+        cq.obj[k] = code; ct[k] = t;
     }
-    __device__ __forceinline__ void finish(unsigned char* st, int slot, int i) {
-        const int q = qbase + i;
-        const int fs = first(st)[slot];
+    if (COUNT) { warp_add(&ctr->exact_tests, n_exact); warp_add(&ctr->exact_flops, n_flops); }
+}
+
+template <typename R>
+__global__ void __launch_bounds__(256) k_closest_order(const __grid_constant__ DevScene<R> sc, const __grid_constant__ Level<R> lv,
+                                                      const __grid_constant__ CandQueue cq) {
+    typedef typename BitsOf<R>::type UB;
+    const int count = min(*cq.count, cq.cap);
+    const UB* tbest = reinterpret_cast<const UB*>(lv.t);
+    const R* ct = reinterpret_cast<const R*>(cq.t);
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
+        const int code = cq.obj[k];
+        if (code < 0) continue;
+        const int ri = cq.ray[k];
+        if (BitsOf<R>::of(ct[k]) == tbest[ri]) atomicMin(&lv.order[ri], sc.scan_of[code & HIT_LEAF_MASK]);
+    }
+}
+
+template <typename R>
+__global__ void __launch_bounds__(256) k_closest_pick(const __grid_constant__ DevScene<R> sc, const __grid_constant__ Level<R> lv,
+                                                     const __grid_constant__ CandQueue cq) {
+    typedef typename BitsOf<R>::type UB;
+    const int count = min(*cq.count, cq.cap);
+    const UB* tbest = reinterpret_cast<const UB*>(lv.t);
+    const R* ct = reinterpret_cast<const R*>(cq.t);
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
+        const int code = cq.obj[k];
+        if (code < 0) continue;
+        const int ri = cq.ray[k];
+        if (BitsOf<R>::of(ct[k]) == tbest[ri] && lv.order[ri] == sc.scan_of[code & HIT_LEAF_MASK]) lv.hit[ri] = code;
+    }
+}
+
+// inShadow for the queued (hit, light) pairs of ONE light (raytracer.go:411-429): an object other than the shaded
+// one occludes when  shadowHit.T * |ray.Direction| < distToLight  (:424).  The answer does not depend on the
+// order objects are visited in; `first` keeps the smallest scan index of an occluder so that COUNT can credit the
+// tests the reference itself would have run up to its first occluder.
+template <typename R, bool COUNT>
+__global__ void __launch_bounds__(EXACT_THREADS) k_exact_shadow(const __grid_constant__ DevScene<R> sc, const __grid_constant__ ShadowQueue<R> sq,
+                                                               int base, const __grid_constant__ CandQueue cq, Counters* ctr) {
+    const int count = min(*cq.count, cq.cap);
+    unsigned long long n_exact = 0, n_flops = 0;
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
+        const int q = base + cq.ray[k], obj = cq.obj[k];
+        if (obj >= sc.n_leaves || obj == sq.skip[q]) continue;
+        if (!COUNT && sq.first[q] != 0x7fffffff) continue;     // already occluded (a stale read only costs a test)
+        if (COUNT) { n_exact++; n_flops += (unsigned)sc.obj_flops[obj]; }
+        Ray<R> w;
+        const size_t cap = (size_t)sq.cap;
+        w.ox = sq.q[q]; w.oy = sq.q[cap + q]; w.oz = sq.q[2 * cap + q];
+        w.dx = sq.q[3 * cap + q]; w.dy = sq.q[4 * cap + q]; w.dz = sq.q[5 * cap + q];
+        R t; int code;
+        if (!exact_hit<R, false>(sc, obj, w, nullptr, 0, 0, t, code)) continue;
+        if (t * sq.q[7 * cap + q] < sq.q[6 * cap + q]) atomicMin(&sq.first[q], sc.scan_of[obj]);
+    }
+    if (COUNT) { warp_add(&ctr->exact_tests, n_exact); warp_add(&ctr->exact_flops, n_flops); }
+}
+
+// occlusion flags for the resolve pass (+ the credited-work counters)
+template <typename R, bool COUNT>
+__global__ void __launch_bounds__(256) k_shadow_finish(const __grid_constant__ DevScene<R> sc, const __grid_constant__ ShadowQueue<R> sq,
+                                                      int light, unsigned char* occl, Counters* ctr) {
+    const int n = sq.count[light], base = light * sq.per_light;
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ctr->rays_shadow, (unsigned long long)n);
+    unsigned long long n_occluded = 0, cred_tests = 0, cred_flops = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int q = base + i;
+        const int fs = sq.first[q];
         const bool occluded = fs != 0x7fffffff;
         if (occluded) { occl[sq.target[q]] = 1; n_occluded++; }
         if (COUNT) {
@@ -920,23 +934,8 @@ template <typename R, bool COUNT, int RPT> struct ShadowVisit {
             }
         }
     }
-};
-
-template <typename R, int FAMILY, int RPT, bool COUNT>
-__global__ void __launch_bounds__(SCAN_THREADS, sizeof(R) == 4 ? 4 : 2) k_shadow(const __grid_constant__ DevScene<R> sc, const __grid_constant__ ShadowQueue<R> sq,
-                                                         const R* table, const __grid_constant__ CullFrame<R> frame,
-                                                         unsigned char* occl, Counters* ctr, int light, int chunk_objs, int resident) {
-    const int n = sq.count[light];
-    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ctr->rays_shadow, (unsigned long long)n);
-    ShadowVisit<R, COUNT, RPT> V(sc, sq, occl, light * sq.per_light);
-    scan_rays<R, FAMILY, RPT>(sc, table, frame, n, chunk_objs, resident, V);
-    warp_add(&ctr->shadow_occluded, V.n_occluded);
-    if (COUNT) {
-        warp_add(&ctr->exact_tests, V.n_exact);
-        warp_add(&ctr->exact_flops, V.n_flops);
-        warp_add(&ctr->shadow_tests, V.cred_tests);
-        warp_add(&ctr->shadow_flops, V.cred_flops);
-    }
+    warp_add(&ctr->shadow_occluded, n_occluded);
+    if (COUNT) { warp_add(&ctr->shadow_tests, cred_tests); warp_add(&ctr->shadow_flops, cred_flops); }
 }
 
 // ------------------------------------------------------------------ surface bytecode interpreter
@@ -1413,10 +1412,8 @@ public:
         const int smem_max = 200 * 1024;
         auto allow = [&](auto kernel) -> int { CU_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max)); return GMLRT_OK; };
         int rc;
-        if ((rc = allow(k_closest<R, CULL_PIVOT, RPT_FAMILY, kRobustPrimary, false>)) || (rc = allow(k_closest<R, CULL_PIVOT, RPT_FAMILY, kRobustPrimary, true>)) ||
-            (rc = allow(k_closest<R, CULL_GENERAL, RPT_GENERAL, false, false>)) || (rc = allow(k_closest<R, CULL_GENERAL, RPT_GENERAL, false, true>)) ||
-            (rc = allow(k_shadow<R, CULL_PIVOT, RPT_FAMILY, false>)) || (rc = allow(k_shadow<R, CULL_PIVOT, RPT_FAMILY, true>)) ||
-            (rc = allow(k_shadow<R, CULL_AXIS, RPT_FAMILY, false>)) || (rc = allow(k_shadow<R, CULL_AXIS, RPT_FAMILY, true>)))
+        if ((rc = allow(k_cull<R, CULL_PIVOT, RPT_FAMILY, ClosestSource<R>>)) || (rc = allow(k_cull<R, CULL_GENERAL, RPT_GENERAL, ClosestSource<R>>)) ||
+            (rc = allow(k_cull<R, CULL_PIVOT, RPT_FAMILY, ShadowSource<R>>)) || (rc = allow(k_cull<R, CULL_AXIS, RPT_FAMILY, ShadowSource<R>>)))
             return rc;
         return GMLRT_OK;
     }
@@ -1442,7 +1439,7 @@ public:
         out.rays_reflect = c.rays_reflect; out.rays_refract = c.rays_refract;
         out.rays_shadow = c.rays_shadow; out.shadow_occluded = c.shadow_occluded;
         out.shadow_tests = c.shadow_tests; out.shadow_flops = c.shadow_flops; out.exact_tests = c.exact_tests; out.exact_flops = c.exact_flops;
-        out.error = c.error;
+        out.error = c.error; out.overflow = c.overflow;
         return GMLRT_OK;
     }
 
@@ -1450,19 +1447,37 @@ public:
     int trace_rows(int y0, int y1, bool counting, std::string& err) override;
 
 private:
+    // Scene arrays are bump-allocated from one arena that survives across uploads (cudaMalloc / cudaFree cost more than
+    // the whole upload of a 1024-leaf scene); what does not fit is allocated separately and the arena grows next time.
+    int scene_alloc(size_t bytes, void** out, std::string& err) {
+        bytes = (std::max<size_t>(bytes, 256) + 255) & ~(size_t)255;
+        arena_need_ += bytes;
+        if (arena_used_ + bytes <= arena_bytes_) { *out = arena_ + arena_used_; arena_used_ += bytes; return GMLRT_OK; }
+        CU_TRY(cudaMalloc(out, bytes));
+        scene_allocs_.push_back(*out);
+        return GMLRT_OK;
+    }
     template <typename T> int to_device(const std::vector<T>& v, T** out, std::string& err) {
         *out = nullptr;
-        size_t bytes = std::max<size_t>(v.size() * sizeof(T), 256);
         void* p = nullptr;
-        CU_TRY(cudaMalloc(&p, bytes));
-        scene_allocs_.push_back(p);
+        int rc = scene_alloc(v.size() * sizeof(T), &p, err);
+        if (rc) return rc;
         if (!v.empty()) CU_TRY(cudaMemcpyAsync(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, stream_));
         *out = reinterpret_cast<T*>(p);
         return GMLRT_OK;
     }
-    void free_scene() {
+    void free_scene() {                                  // start of an upload: recycle the arena (grown if the last scene spilled)
         for (void* p : scene_allocs_) cudaFree(p);
         scene_allocs_.clear();
+        if (arena_need_ > arena_bytes_) {
+            if (arena_) cudaFree(arena_);
+            arena_ = nullptr; arena_bytes_ = 0;
+            const size_t want = std::max<size_t>(arena_need_ + arena_need_ / 2, (size_t)1 << 20);
+            void* p = nullptr;
+            if (cudaMalloc(&p, want) == cudaSuccess) { arena_ = reinterpret_cast<char*>(p); arena_bytes_ = want; }
+            else cudaGetLastError();
+        }
+        arena_used_ = 0; arena_need_ = 0;
     }
     void free_tiles() {
         if (pool_) cudaFree(pool_);
@@ -1471,6 +1486,8 @@ private:
     void release() {
         cudaSetDevice(dev_);
         free_scene(); free_tiles();
+        if (arena_) cudaFree(arena_);
+        arena_ = nullptr; arena_bytes_ = 0;
         if (frame_) cudaFree(frame_);
         if (ids_) cudaFree(ids_);
         if (ctr_) cudaFree(ctr_);
@@ -1480,11 +1497,19 @@ private:
         frame_ = nullptr; ids_ = nullptr; ctr_ = nullptr; stream_ = nullptr;
     }
     int plan_tiles(const HostScene& S, std::string& err);
+public:
+    bool shrink_tiles(const HostScene& S, std::string& err) override {
+        if (rows_per_tile_ <= 1) { err = "candidate queue overflow with one-row tiles"; return false; }
+        tile_shrink_++;
+        return plan_tiles(S, err) == GMLRT_OK;
+    }
+private:
 
     int dev_, sms_ = 148;
     cudaStream_t stream_ = nullptr;
     DevScene<R> sc_{};
     std::vector<void*> scene_allocs_;
+    char* arena_ = nullptr; size_t arena_bytes_ = 0, arena_used_ = 0, arena_need_ = 1 << 20;
     // tile buffers
     void* pool_ = nullptr; size_t pool_bytes_ = 0;
     std::vector<Level<R>> levels_;
@@ -1502,7 +1527,8 @@ private:
     // scan kernel configuration
     int chunk_objs_ = GROUP, resident_ = 1; size_t table_smem_ = 0;
     struct Launch { int grid = 148; size_t smem = 0; };
-    Launch l_primary_[2], l_closest_[2], l_shadow_pivot_[2], l_shadow_axis_[2];          // [counting]
+    Launch l_primary_, l_closest_, l_shadow_pivot_, l_shadow_axis_;                      // the four k_cull instantiations
+    CandQueue cq_{}; int cand_per_ray_ = 4, tile_shrink_ = 0;
     // cull tables (device) and what they were built for: any ray, camera rays, one per light
     std::vector<double> bound_;                                  // host: [n][4] bounding spheres (centre, radius) of the objects
     R* cull_general_ = nullptr; R* cull_eye_ = nullptr; std::vector<R*> cull_light_;
@@ -1518,6 +1544,7 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     if (S.depth > GMLRT_MAX_DEPTH) { err = "recursion depth above GMLRT_MAX_DEPTH"; return GMLRT_E_UNSUPPORTED; }
     CU_TRY(cudaStreamSynchronize(stream_));
     free_scene();
+    tile_shrink_ = 0;
     // Device layout.  Objects (what closestHit / inShadow scan): the plain leaves, stably sorted by kind so that
     // equal kinds keep scan order, then the CSG objects.  After them, the member leaves of the CSG objects.  Every
     // per-leaf array has n_all entries (a CSG object's own entry is unused filler).
@@ -1648,8 +1675,7 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     }
     {
         void* p = nullptr;
-        CU_TRY(cudaMalloc(&p, std::max<size_t>(S.lights.size(), 1) * sizeof(int)));
-        scene_allocs_.push_back(p);
+        if ((rc = scene_alloc(std::max<size_t>(S.lights.size(), 1) * sizeof(int), &p, err))) return rc;
         shadow_counts_ = reinterpret_cast<int*>(p);
         CU_TRY(cudaMemsetAsync(shadow_counts_, 0, std::max<size_t>(S.lights.size(), 1) * sizeof(int), stream_));
     }
@@ -1729,9 +1755,15 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
         mult[l] = S.may_branch ? std::ldexp(1.0, std::min(l, 30)) : 1.0;     // binary ray tree only when a material asks for it
         sum_mult += mult[l]; max_mult = std::max(max_mult, mult[l]);
     }
-    const double node_bytes = (6 + 1 + NREC + 6) * sizeof(R) + 8 + nl;
-    const double shadow_bytes = nl * (8.0 * sizeof(R) + 8);
-    const double per_sample = sum_mult * node_bytes + max_mult * shadow_bytes + 3 * sizeof(R) + (kRobustPrimary ? 48 : 0);
+    // candidate queue: (ray, object, T) per survivor of the cull phase.  Unbounded objects (planes) survive every ray;
+    // beyond them a handful per ray is typical (about 1 at 1024 spheres); an overflow retraces with smaller tiles.
+    int n_unbounded = 0;
+    for (int d = 0; d < sc_.n_leaves; d++) n_unbounded += std::isinf(bound_[(size_t)d * 4 + 3]) ? 1 : 0;
+    cand_per_ray_ = std::min<int>(std::max(sc_.n_leaves, 1), (int)env_size("GMLRT_CAND_PER_RAY", 4) + n_unbounded);
+    const double cand_bytes = cand_per_ray_ * (8.0 + sizeof(R));
+    const double node_bytes = (6 + 1 + NREC + 6) * sizeof(R) + 12 + nl;
+    const double shadow_bytes = nl * (8.0 * sizeof(R) + 12);
+    const double per_sample = sum_mult * node_bytes + max_mult * (shadow_bytes + cand_bytes) + 3 * sizeof(R) + (kRobustPrimary ? 48 : 0);
     size_t free_b = 0, total_b = 0;
     CU_TRY(cudaMemGetInfo(&free_b, &total_b));
     free_b += pool_bytes_;
@@ -1740,24 +1772,27 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     max_samples = std::min(max_samples, 2.0e9 / (max_mult * std::max(nl, 1)));       // int32 indexing of node*n_lights
     int rows = (int)std::min<double>(H, std::floor(max_samples / (4.0 * W)));
     if (rows < 1) { err = "image row does not fit the device queue budget"; return GMLRT_E_OOM; }
+    rows = std::max(1, rows >> tile_shrink_);                   // after a candidate-queue overflow: same buffers, fewer rays
     rows_per_tile_ = rows;
     const size_t S0 = (size_t)rows * W * 4;
     // carve one pool
     auto align = [](size_t x) { return (x + 255) & ~(size_t)255; };
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off = align(off + bytes); return o; };
-    struct LvOff { size_t ray, parent, hit, t, rec, child, occl; size_t cap; };
+    struct LvOff { size_t ray, parent, hit, t, order, rec, child, occl; size_t cap; };
     std::vector<LvOff> lo(depth_eff_);
     size_t max_cap = 0;
     for (int l = 0; l < depth_eff_; l++) {
         size_t cap = (size_t)std::min((double)S0 * mult[l], 2.0e9);
         lo[l].cap = cap; max_cap = std::max(max_cap, cap);
         lo[l].ray = take(6 * cap * sizeof(R)); lo[l].parent = take(cap * 4); lo[l].hit = take(cap * 4);
-        lo[l].t = take(cap * sizeof(R)); lo[l].rec = take(NREC * cap * sizeof(R)); lo[l].child = take(6 * cap * sizeof(R));
+        lo[l].t = take(cap * sizeof(R)); lo[l].order = take(cap * 4); lo[l].rec = take(NREC * cap * sizeof(R)); lo[l].child = take(6 * cap * sizeof(R));
         lo[l].occl = take(cap * std::max(nl, 1));
     }
     const size_t sq_cap = max_cap * std::max(nl, 1);
-    size_t o_sq = take(8 * sq_cap * sizeof(R)), o_skip = take(sq_cap * 4), o_tgt = take(sq_cap * 4);
+    size_t o_sq = take(8 * sq_cap * sizeof(R)), o_skip = take(sq_cap * 4), o_tgt = take(sq_cap * 4), o_first = take(sq_cap * 4);
+    const size_t cand_cap = std::min<size_t>((size_t)((double)max_cap * cand_per_ray_ * (double)(1 << tile_shrink_)), (size_t)2000000000);
+    size_t o_cray = take(cand_cap * 4), o_cobj = take(cand_cap * 4), o_ct = take(cand_cap * sizeof(R)), o_ccount = take(256);
     size_t o_samples = take(3 * S0 * sizeof(R));
     size_t o_ray64 = kRobustPrimary ? take(6 * S0 * sizeof(double)) : 0;
     if (off > pool_bytes_) {
@@ -1772,12 +1807,14 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
         Level<R>& L = levels_[l];
         L.cap = (int)lo[l].cap;
         L.ray = (R*)(base + lo[l].ray); L.parent = (int*)(base + lo[l].parent); L.hit = (int*)(base + lo[l].hit);
-        L.t = (R*)(base + lo[l].t); L.rec = (R*)(base + lo[l].rec); L.child = (R*)(base + lo[l].child);
+        L.t = (R*)(base + lo[l].t); L.order = (int*)(base + lo[l].order); L.rec = (R*)(base + lo[l].rec); L.child = (R*)(base + lo[l].child);
         occl_[l] = (unsigned char*)(base + lo[l].occl);
         L.ray64 = (kRobustPrimary && l == 0) ? (double*)(base + o_ray64) : nullptr;
     }
     sq_.q = (R*)(base + o_sq); sq_.skip = (int*)(base + o_skip); sq_.target = (int*)(base + o_tgt); sq_.cap = (int)sq_cap;
-    sq_.per_light = (int)max_cap; sq_.count = shadow_counts_;
+    sq_.per_light = (int)max_cap; sq_.count = shadow_counts_; sq_.first = (int*)(base + o_first);
+    cq_.ray = (int*)(base + o_cray); cq_.obj = (int*)(base + o_cobj); cq_.t = (void*)(base + o_ct); cq_.count = (int*)(base + o_ccount);
+    cq_.cap = (int)cand_cap;
     samples_ = (R*)(base + o_samples); sample_cap_ = (int)S0;
 
     // scan kernels: resident cull table when it fits, else two streaming buffers (chunks of whole groups)
@@ -1787,22 +1824,18 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     const size_t all = (size_t)sc_.n_cull * rec_bytes;
     if (all <= resident_max) { resident_ = 1; chunk_objs_ = sc_.n_cull; table_smem_ = all; }
     else { resident_ = 0; chunk_objs_ = (int)(chunk_bytes / rec_bytes) / GROUP * GROUP; table_smem_ = 2 * (size_t)chunk_objs_ * rec_bytes; }
-    auto cfg = [&](auto kernel, size_t state, Launch& L) -> int {
+    auto cfg = [&](auto kernel, Launch& L) -> int {
         int occ = 1;
-        L.smem = CAND_CAP * sizeof(uint32_t) + state + table_smem_;
+        L.smem = table_smem_;
         CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, SCAN_THREADS, L.smem));
         L.grid = sms_ * std::max(occ, 1);
         return GMLRT_OK;
     };
     int rc;
-    const size_t lf = ClosestVisit<R, kRobustPrimary, false, RPT_FAMILY>::state_bytes(), lg = ClosestVisit<R, false, false, RPT_GENERAL>::state_bytes();
-    const size_t ls = ShadowVisit<R, false, RPT_FAMILY>::state_bytes();
-    if ((rc = cfg(k_closest<R, CULL_PIVOT, RPT_FAMILY, kRobustPrimary, false>, lf, l_primary_[0])) ||
-        (rc = cfg(k_closest<R, CULL_PIVOT, RPT_FAMILY, kRobustPrimary, true>, lf, l_primary_[1])) ||
-        (rc = cfg(k_closest<R, CULL_GENERAL, RPT_GENERAL, false, false>, lg, l_closest_[0])) ||
-        (rc = cfg(k_closest<R, CULL_GENERAL, RPT_GENERAL, false, true>, lg, l_closest_[1])) ||
-        (rc = cfg(k_shadow<R, CULL_PIVOT, RPT_FAMILY, false>, ls, l_shadow_pivot_[0])) || (rc = cfg(k_shadow<R, CULL_PIVOT, RPT_FAMILY, true>, ls, l_shadow_pivot_[1])) ||
-        (rc = cfg(k_shadow<R, CULL_AXIS, RPT_FAMILY, false>, ls, l_shadow_axis_[0])) || (rc = cfg(k_shadow<R, CULL_AXIS, RPT_FAMILY, true>, ls, l_shadow_axis_[1])))
+    if ((rc = cfg(k_cull<R, CULL_PIVOT, RPT_FAMILY, ClosestSource<R>>, l_primary_)) ||
+        (rc = cfg(k_cull<R, CULL_GENERAL, RPT_GENERAL, ClosestSource<R>>, l_closest_)) ||
+        (rc = cfg(k_cull<R, CULL_PIVOT, RPT_FAMILY, ShadowSource<R>>, l_shadow_pivot_)) ||
+        (rc = cfg(k_cull<R, CULL_AXIS, RPT_FAMILY, ShadowSource<R>>, l_shadow_axis_)))
         return rc;
     return GMLRT_OK;
 }
@@ -1838,36 +1871,51 @@ int Renderer<R>::trace_rows(int y0, int y1, bool counting, std::string& err) {
         totals_.rays_primary += (unsigned long long)S;
         for (int l = 0; l < depth_eff_; l++) {
             const int cap_blocks = (levels_[l].cap + SHADE_THREADS - 1) / SHADE_THREADS;
-            const int ci = counting ? 1 : 0;
+            const int exact_grid = sms_ * 16;
+            CU_TRY(cudaMemsetAsync(cq_.count, 0, sizeof(int), stream_));
+            ClosestSource<R> csrc{levels_[l]};
             if (l == 0) {                                  // camera rays: PIVOT family through the eye, robust re-tests in f32
                 MARK(KC_CLOSEST_PRIMARY);
-                const Launch& L = l_primary_[ci];
-                if (counting) k_closest<R, CULL_PIVOT, RPT_FAMILY, kRobustPrimary, true><<<L.grid, SCAN_THREADS, L.smem, stream_>>>(sc_, levels_[l], cull_eye_, frame_eye_, ctr_, l, chunk_objs_, resident_);
-                else k_closest<R, CULL_PIVOT, RPT_FAMILY, kRobustPrimary, false><<<L.grid, SCAN_THREADS, L.smem, stream_>>>(sc_, levels_[l], cull_eye_, frame_eye_, ctr_, l, chunk_objs_, resident_);
+                k_cull<R, CULL_PIVOT, RPT_FAMILY, ClosestSource<R>><<<l_primary_.grid, SCAN_THREADS, l_primary_.smem, stream_>>>(
+                    csrc, &ctr_->count[l], cull_eye_, frame_eye_, sc_.n_cull, cq_, ctr_, chunk_objs_, resident_);
+                MARK(KC_EXACT);
+                if (counting) k_exact_closest<R, kRobustPrimary, true><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
+                else k_exact_closest<R, kRobustPrimary, false><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
             } else {
                 MARK(KC_CLOSEST);
-                const Launch& L = l_closest_[ci];
-                if (counting) k_closest<R, CULL_GENERAL, RPT_GENERAL, false, true><<<L.grid, SCAN_THREADS, L.smem, stream_>>>(sc_, levels_[l], cull_general_, frame_general_, ctr_, l, chunk_objs_, resident_);
-                else k_closest<R, CULL_GENERAL, RPT_GENERAL, false, false><<<L.grid, SCAN_THREADS, L.smem, stream_>>>(sc_, levels_[l], cull_general_, frame_general_, ctr_, l, chunk_objs_, resident_);
+                k_cull<R, CULL_GENERAL, RPT_GENERAL, ClosestSource<R>><<<l_closest_.grid, SCAN_THREADS, l_closest_.smem, stream_>>>(
+                    csrc, &ctr_->count[l], cull_general_, frame_general_, sc_.n_cull, cq_, ctr_, chunk_objs_, resident_);
+                MARK(KC_EXACT);
+                if (counting) k_exact_closest<R, false, true><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
+                else k_exact_closest<R, false, false><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
             }
+            k_closest_order<R><<<exact_grid, 256, 0, stream_>>>(sc_, levels_[l], cq_);
+            k_closest_pick<R><<<exact_grid, 256, 0, stream_>>>(sc_, levels_[l], cq_);
+            totals_.launches += 3;
             const bool spawn = l + 1 < depth_eff_;
             MARK(KC_SHADE);
             k_shade<R><<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
                 sc_, levels_[l], spawn ? levels_[l + 1] : levels_[l], sq_, occl_[l], ctr_, l, spawn ? 1 : 0,
                 (counting && l == 0) ? ids_ : nullptr, ty);
             totals_.launches += 2;
-            for (int li = 0; li < sc_.n_lights; li++) {    // one launch per light: its shadow rays share a pivot (or an axis)
-                MARK(KC_SHADOW);
+            for (int li = 0; li < sc_.n_lights; li++) {    // per light: its shadow rays share a pivot (or an axis)
                 const bool axis = frame_light_[li].family == CULL_AXIS;
-                const Launch& L = axis ? l_shadow_axis_[counting ? 1 : 0] : l_shadow_pivot_[counting ? 1 : 0];
-                if (axis) {
-                    if (counting) k_shadow<R, CULL_AXIS, RPT_FAMILY, true><<<L.grid, SCAN_THREADS, L.smem, stream_>>>(sc_, sq_, cull_light_[li], frame_light_[li], occl_[l], ctr_, li, chunk_objs_, resident_);
-                    else k_shadow<R, CULL_AXIS, RPT_FAMILY, false><<<L.grid, SCAN_THREADS, L.smem, stream_>>>(sc_, sq_, cull_light_[li], frame_light_[li], occl_[l], ctr_, li, chunk_objs_, resident_);
+                ShadowSource<R> ssrc{sq_, li * sq_.per_light};
+                CU_TRY(cudaMemsetAsync(cq_.count, 0, sizeof(int), stream_));
+                MARK(KC_SHADOW);
+                if (axis) k_cull<R, CULL_AXIS, RPT_FAMILY, ShadowSource<R>><<<l_shadow_axis_.grid, SCAN_THREADS, l_shadow_axis_.smem, stream_>>>(
+                    ssrc, &shadow_counts_[li], cull_light_[li], frame_light_[li], sc_.n_cull, cq_, ctr_, chunk_objs_, resident_);
+                else k_cull<R, CULL_PIVOT, RPT_FAMILY, ShadowSource<R>><<<l_shadow_pivot_.grid, SCAN_THREADS, l_shadow_pivot_.smem, stream_>>>(
+                    ssrc, &shadow_counts_[li], cull_light_[li], frame_light_[li], sc_.n_cull, cq_, ctr_, chunk_objs_, resident_);
+                MARK(KC_EXACT);
+                if (counting) {
+                    k_exact_shadow<R, true><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, sq_, li * sq_.per_light, cq_, ctr_);
+                    k_shadow_finish<R, true><<<wide, 256, 0, stream_>>>(sc_, sq_, li, occl_[l], ctr_);
                 } else {
-                    if (counting) k_shadow<R, CULL_PIVOT, RPT_FAMILY, true><<<L.grid, SCAN_THREADS, L.smem, stream_>>>(sc_, sq_, cull_light_[li], frame_light_[li], occl_[l], ctr_, li, chunk_objs_, resident_);
-                    else k_shadow<R, CULL_PIVOT, RPT_FAMILY, false><<<L.grid, SCAN_THREADS, L.smem, stream_>>>(sc_, sq_, cull_light_[li], frame_light_[li], occl_[l], ctr_, li, chunk_objs_, resident_);
+                    k_exact_shadow<R, false><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, sq_, li * sq_.per_light, cq_, ctr_);
+                    k_shadow_finish<R, false><<<wide, 256, 0, stream_>>>(sc_, sq_, li, occl_[l], ctr_);
                 }
-                totals_.launches++;
+                totals_.launches += 3;
             }
             if (sc_.n_lights > 0) CU_TRY(cudaMemsetAsync(shadow_counts_, 0, sizeof(int) * sc_.n_lights, stream_));
         }

@@ -189,8 +189,9 @@ typedef struct gmlrt_stats {
     uint64_t cull_tests;        /* executed: first-phase bounding-sphere tests (every query x every object) */
     uint64_t exact_tests;       /* executed: second-phase <Type>.Intersect tests on the survivors (counting mode) */
     double   flops_executed;    /* 14 per cull test (7 FFMA) + the per-leaf-type table per exact test (counting mode) */
-    double   ms_class[7];       /* profiling mode: device ms per kernel class: gen, closest(primary), closest, shadow, shade, resolve, pixels */
-    uint64_t launches_class[7]; /* ... and launches per class */
+    double   ms_class[8];       /* profiling mode: device ms per kernel class: gen, cull of camera rays, cull of reflection/refraction
+                                   rays, cull of shadow rays, shade, resolve, pixels, exact tests */
+    uint64_t launches_class[8]; /* ... and launches per class */
 } gmlrt_stats;
 
 /* Create a context on `n` devices (`devices` = CUDA ordinals; n >= 1).  With n > 1 the
