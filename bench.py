@@ -188,7 +188,7 @@ def main():
     cst = ctx.trace()
     ctx.set_counting(False)
     counts = torch.tensor([cst.rays_primary, cst.rays_reflect, cst.rays_refract, cst.rays_shadow, cst.shadow_occluded,
-                           cst.leaf_tests, int(cst.flops_credited / 1e3), cst.cull_tests, cst.exact_tests, int(cst.flops_executed / 1e3)],
+                           cst.leaf_tests, int(cst.flops_credited / 1e3), cst.cull_tests, cst.exact_tests, int(cst.flops_executed / 1e3), cst.packet_tests],
                           dtype=torch.int64, device=f"cuda:{local_rank}")
     if dist is not None:
         dist.all_reduce(counts)
@@ -204,15 +204,15 @@ def main():
     sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches, kernel_ms = 0, 0.0
-    class_ms = [0.0] * 8
-    class_launches = [0] * 8
+    class_ms = [0.0] * 9
+    class_launches = [0] * 9
     with torch.cuda.stream(ext):
         e0.record()
     for _ in range(args.steps):
         st = step()
         launches += st.kernel_launches
         kernel_ms += st.ms_kernels
-        for k in range(8):
+        for k in range(9):
             class_ms[k] += st.ms_class[k]
             class_launches[k] += st.launches_class[k]
     with torch.cuda.stream(ext):
@@ -228,8 +228,8 @@ def main():
         tsum = t.clone()
         dist.all_reduce(tsum)
         ms_total, kernel_ms, launches = float(tmax[0]), float(tmax[1]), int(tsum[2])
-        class_ms = [float(x) for x in tmax[3:11]]
-        class_launches = [int(x) for x in tsum[11:19]]
+        class_ms = [float(x) for x in tmax[3:12]]
+        class_launches = [int(x) for x in tsum[12:21]]
     ctx.set_profiling(False)
     ms_step = ms_total / args.steps
     value = rays_frame / (ms_step * 1e-3) / 1e6
@@ -290,8 +290,8 @@ def main():
     fp32_peak = (fp32_measured if fp32_measured > 0 else fp32_derived) * world
     # dominant kernels: the scan kernels (closest-hit + shadow instantiations of one skeleton)
     names = cuda.Stats.KERNEL_CLASSES
-    scan_ms = sum(class_ms[k] for k in (1, 2, 3, 7))
-    scan_launches = sum(class_launches[k] for k in (1, 2, 3, 7))
+    scan_ms = sum(class_ms[k] for k in (1, 2, 3, 7, 8))
+    scan_launches = sum(class_launches[k] for k in (1, 2, 3, 7, 8))
     achieved = flops_frame * args.steps / (scan_ms * 1e-3) / 1e12 if scan_ms > 0 else 0.0
     traffic = None
     try:
@@ -311,18 +311,18 @@ def main():
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "frame_ms": e2e_ms, "h2d_bytes_per_step": len(blob), "d2h_bytes_per_step": W * H * 4,
                 "phase_ms": {k: v / e2e_steps for k, v in phase_ms.items()}},
-        "kernel_ms_per_frame": {names[k]: class_ms[k] / args.steps for k in range(8)},
+        "kernel_ms_per_frame": {names[k]: class_ms[k] / args.steps for k in range(9)},
         "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak if fp32_peak else None,
                      "traffic": traffic,
                      "kernel": "scan kernels (k_cull x 4 instantiations + k_exact_*): %d event intervals, %.3f ms per frame" % (scan_launches, scan_ms / args.steps),
                      "peak_kind": "measured: FFMA-chain microbenchmark on this GPU (gmlrt_measure_fp32_tflops)" if fp32_measured > 0 else "derived",
                      "peak_derived": fp32_derived * world,
-                     "note": "achieved = flops the scan kernels EXECUTE (14 per first-phase cull test = 7 FFMA, every query x every object; "
-                             "SURVEY 8(d) table - sphere 56, plane 47, cube 81, cylinder 74, cone 70 - per second-phase exact test on the "
-                             "survivors) over their CUDA-event time in the timed region.  The reference's all-pairs scan would execute "
-                             "flops_bruteforce_equivalent for the same queries; the cull phase removes most of it, so that figure over "
-                             "the same time is reported separately and is NOT a roofline fraction.",
-                     "flops_per_frame": flops_frame, "cull_tests_per_frame": int(counts[7]), "exact_tests_per_frame": int(counts[8]),
+                     "note": "achieved = flops the scan kernels EXECUTE, from device counters (per-ray cull tests: 15 flops GENERAL, 7 PIVOT, 7 AXIS; "
+                             "per-warp packet tests: 20; SURVEY 8(d) table - sphere 56, plane 47, cube 81, cylinder 74, cone 70 - per exact "
+                             "test on the survivors) over their CUDA-event time in the timed region.  The reference's all-pairs scan would "
+                             "execute flops_bruteforce_equivalent for the same queries; culling removes most of it, so that figure over the "
+                             "same time is reported separately and is NOT a roofline fraction.",
+                     "flops_per_frame": flops_frame, "cull_tests_per_frame": int(counts[7]), "packet_tests_per_frame": int(counts[10]), "exact_tests_per_frame": int(counts[8]),
                      "flops_bruteforce_equivalent": flops_credited_frame, "leaf_tests_bruteforce_equivalent": int(counts[5]),
                      "bruteforce_equivalent_tflops": flops_credited_frame * args.steps / (scan_ms * 1e-3) / 1e12 if scan_ms > 0 else None},
     }

@@ -259,7 +259,8 @@ static int trace_once(gmlrt_ctx* c, gmlrt_stats* stats, bool& overflow) {
         if (rc != GMLRT_OK) return fail(c, rc, err);
         sum.rays_primary += t.rays_primary; sum.rays_reflect += t.rays_reflect; sum.rays_refract += t.rays_refract;
         sum.rays_shadow += t.rays_shadow; sum.shadow_occluded += t.shadow_occluded; sum.launches += t.launches;
-        sum.shadow_tests += t.shadow_tests; sum.shadow_flops += t.shadow_flops; sum.exact_tests += t.exact_tests; sum.exact_flops += t.exact_flops;
+        sum.shadow_tests += t.shadow_tests; sum.shadow_flops += t.shadow_flops; sum.exact_tests += t.exact_tests; sum.exact_flops += t.exact_flops; sum.packet_tests += t.packet_tests;
+        for (int k = 0; k < 3; k++) sum.cull_by_family[k] += t.cull_by_family[k];
         for (int k = 0; k < KC_COUNT; k++) { sum.ms_class[k] = std::max(sum.ms_class[k], t.ms_class[k]); sum.launches_class[k] += t.launches_class[k]; }
         sum.error |= t.error; overflow = overflow || t.overflow;
     }
@@ -279,10 +280,14 @@ static int trace_once(gmlrt_ctx* c, gmlrt_stats* stats, bool& overflow) {
         stats->flops_credited = (double)closest * all;
         stats->leaf_tests += sum.shadow_tests;
         stats->flops_credited += (double)sum.shadow_flops;
-        // executed work: every query runs the 7-FFMA cull test against every object, the exact test only on survivors
-        stats->cull_tests = (closest + sum.rays_shadow) * nleaf;
+        // executed work, from device counters: per-ray cull tests by family (GENERAL: 7 FFMA + 1 FADD = 15 flops; PIVOT:
+        // FMUL + 3 FFMA = 7; AXIS: 3 FADD + 2 FFMA = 7), per-warp packet tests (about 20 flops: two dot products, a
+        // reciprocal, three square roots, the angle inequality) and the exact tests on the survivors (counting mode)
+        stats->cull_tests = sum.cull_by_family[0] + sum.cull_by_family[1] + sum.cull_by_family[2];
+        stats->packet_tests = sum.packet_tests;
         stats->exact_tests = sum.exact_tests;
-        stats->flops_executed = 14.0 * (double)stats->cull_tests + (double)sum.exact_flops;   // cull = 7 FFMA
+        stats->flops_executed = 15.0 * (double)sum.cull_by_family[0] + 7.0 * (double)(sum.cull_by_family[1] + sum.cull_by_family[2]) +
+                                20.0 * (double)sum.packet_tests + (double)sum.exact_flops;
         for (int k = 0; k < KC_COUNT; k++) { stats->ms_class[k] = sum.ms_class[k]; stats->launches_class[k] = sum.launches_class[k]; }
     }
     if (overflow) return GMLRT_OK;      // the caller shrinks the tiles and traces again

@@ -87,7 +87,9 @@ template <typename R> struct Level {
 };
 
 template <typename R> struct ShadowQueue {      // one segment of `per_light` slots per light: slot = light * per_light + k
-    R* q;         // [8][cap] origin xyz, direction xyz, distance to light, |incoming direction|
+    R* q;         // [cap][8] origin xyz, direction xyz, distance to light, |incoming direction| (one 32-byte record in f32:
+                  //          the cull kernel reads the rays through the by-object permutation, one sector per ray)
+    int* perm;    // [cap] per light segment: slots (relative to the segment) ordered by the shaded object
     int* skip;    // [cap] device leaf index of the shaded object (inShadow skips it)
     int* target;  // [cap] node * n_lights + light
     int* first;   // [cap] scan result: smallest scan index of an occluder, 0x7fffffff = none
@@ -99,6 +101,9 @@ struct Counters {                  // device-resident, zeroed per trace
     int count[GMLRT_MAX_DEPTH + 1];     // rays per level
     int error;
     int overflow;                       // a cull launch ran out of candidate queue: retrace with smaller tiles
+    unsigned long long cull_tests[3];   // executed per-ray cull tests by family (GENERAL, PIVOT, AXIS)
+    unsigned long long packet_tests;    // executed per-warp packet tests (one lane x one object)
+    unsigned long long dbg[8];          // GMLRT_DEBUG_PACKETS: warp blocks, usable, objects offered, survivors
     unsigned long long rays_reflect, rays_refract, rays_shadow, shadow_occluded;
     unsigned long long shadow_tests, shadow_flops;   // credited: the reference's scan up to its first occluder (counting mode)
     unsigned long long exact_tests, exact_flops;     // executed second-phase tests and their table flops (counting mode)
@@ -683,6 +688,111 @@ template <> struct BitsOf<double> {
     static __device__ __forceinline__ double back(unsigned long long b) { return __longlong_as_double((long long)b); }
 };
 
+// the same window over an index list: objects idx[k0 .. k0 + GROUP - 1] (indices into `sm`), 8 indices per 16-byte load
+template <typename R, int FAMILY, int RPT>
+__device__ __forceinline__ void cull_window_indirect(const R* sm, const uint16_t* idx, int k0, const CullRay<R, FAMILY> (&cr)[RPT],
+                                                     uint32_t (&lo)[RPT], uint32_t (&hi)[RPT]) {
+#pragma unroll
+    for (int r = 0; r < RPT; r++) { lo[r] = 0; hi[r] = 0; }
+#pragma unroll 1
+    for (int j0 = 0; j0 < 32; j0 += 8) {
+        const uint4 pk = *reinterpret_cast<const uint4*>(idx + k0 + j0);
+        const uint32_t w[4] = {pk.x, pk.y, pk.z, pk.w};
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const Cull4<R> L = load_cull(sm, (int)((w[j >> 1] >> (16 * (j & 1))) & 0xffffu));
+#pragma unroll
+            for (int r = 0; r < RPT; r++) lo[r] = push_sign(lo[r], cr[r].slack(L));
+        }
+    }
+#pragma unroll 1
+    for (int j0 = 32; j0 < 64; j0 += 8) {
+        const uint4 pk = *reinterpret_cast<const uint4*>(idx + k0 + j0);
+        const uint32_t w[4] = {pk.x, pk.y, pk.z, pk.w};
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const Cull4<R> L = load_cull(sm, (int)((w[j >> 1] >> (16 * (j & 1))) & 0xffffu));
+#pragma unroll
+            for (int r = 0; r < RPT; r++) hi[r] = push_sign(hi[r], cr[r].slack(L));
+        }
+    }
+}
+
+// What the rays of one warp (RPT per lane) have in common, for the packet stage of the PIVOT / AXIS families:
+//   PIVOT  a double cone around `axis` (unit) with half-angle theta that contains every ray's line through the pivot
+//   AXIS   a disc (centre mu, mv; radius rho) in the plane orthogonal to the common direction that contains every ray
+template <typename R> struct WarpBound { R ax, ay, az, cos_t, sin_t; bool usable; };
+
+template <typename R>
+__device__ __forceinline__ R warp_sum(R v) { for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o); return v; }
+template <typename R>
+__device__ __forceinline__ R warp_min(R v) { for (int o = 16; o > 0; o >>= 1) { const R u = __shfl_xor_sync(0xffffffffu, v, o); v = u < v ? u : v; } return v; }
+template <typename R>
+__device__ __forceinline__ R warp_max(R v) { for (int o = 16; o > 0; o >>= 1) { const R u = __shfl_xor_sync(0xffffffffu, v, o); v = u > v ? u : v; } return v; }
+
+__device__ __forceinline__ unsigned long long warp_sum_u64(unsigned long long v) { for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o); return v; }
+
+template <typename R, int RPT>
+__device__ __forceinline__ WarpBound<R> warp_bound(const CullRay<R, CULL_PIVOT> (&cr)[RPT], const bool (&active)[RPT]) {
+    R sx = R(0), sy = R(0), sz = R(0);
+#pragma unroll
+    for (int r = 0; r < RPT; r++) if (active[r]) { sx += cr[r].dx; sy += cr[r].dy; sz += cr[r].dz; }
+    sx = warp_sum(sx); sy = warp_sum(sy); sz = warp_sum(sz);
+    const R len = gm<R>::sqrt(fma_(sx, sx, fma_(sy, sy, sz * sz)));
+    WarpBound<R> b;
+    b.usable = len > R(0);
+    const R inv = b.usable ? R(1) / len : R(0);
+    b.ax = sx * inv; b.ay = sy * inv; b.az = sz * inv;
+    R c = R(1);
+#pragma unroll
+    for (int r = 0; r < RPT; r++) if (active[r]) { const R d = fma_(cr[r].dx, b.ax, fma_(cr[r].dy, b.ay, cr[r].dz * b.az)); c = d < c ? d : c; }
+    c = warp_min(c) - R(1e-5);                          // a slightly wider cone absorbs the rounding of axis and dot products
+    b.cos_t = c;
+    b.sin_t = gm<R>::sqrt(R(1) - (c < R(1) ? c * c : R(1))) + R(1e-5);
+    b.usable = b.usable && c > R(0.5);                   // a wide cone culls little: use the plain scan
+    return b;
+}
+template <typename R, int RPT>
+__device__ __forceinline__ WarpBound<R> warp_bound(const CullRay<R, CULL_AXIS> (&cr)[RPT], const bool (&active)[RPT]) {
+    R su = R(0), sv = R(0), cnt = R(0);
+#pragma unroll
+    for (int r = 0; r < RPT; r++) if (active[r]) { su += cr[r].ou; sv += cr[r].ov; cnt += R(1); }
+    su = warp_sum(su); sv = warp_sum(sv); cnt = warp_sum(cnt);
+    WarpBound<R> b;
+    b.usable = cnt > R(0);
+    b.ax = b.usable ? su / cnt : R(0); b.ay = b.usable ? sv / cnt : R(0); b.az = R(0);
+    R d2 = R(0);
+#pragma unroll
+    for (int r = 0; r < RPT; r++) if (active[r]) { const R du = cr[r].ou - b.ax, dv = cr[r].ov - b.ay; const R d = fma_(du, du, dv * dv); d2 = d > d2 ? d : d2; }
+    d2 = warp_max(d2);
+    b.cos_t = gm<R>::sqrt(d2) * R(1.0001) + R(1e-6) * (gm<R>::abs(b.ax) + gm<R>::abs(b.ay) + R(1));      // rho, widened for rounding
+    b.sin_t = R(0);
+    return b;
+}
+template <typename R, int RPT>
+__device__ __forceinline__ WarpBound<R> warp_bound(const CullRay<R, CULL_GENERAL> (&)[RPT], const bool (&)[RPT]) { WarpBound<R> b = {}; b.usable = false; return b; }
+
+// may object record L be hit by ANY ray inside the warp's bound?  (conservative)
+template <typename R> __device__ __forceinline__ bool packet_survives(const Cull4<R>& L, const WarpBound<R>& b, CullRay<R, CULL_PIVOT>*) {
+    const R pp = fma_(L.x, L.x, fma_(L.y, L.y, L.z * L.z));
+    const R r2 = pp - L.k;                               // >= R^2 (the record's K carries the margins)
+    if (!(r2 < pp)) return true;                         // pivot inside the sphere, unbounded object (K = -inf), NaN
+    const R inv = R(1) / pp;
+    const R s2 = r2 * inv;                               // sin^2 of the sphere's angular radius alpha seen from the pivot
+    const R sa = gm<R>::sqrt(s2) * R(1.0001), ca = gm<R>::sqrt(R(1) - s2);
+    const R c = gm<R>::abs(fma_(L.x, b.ax, fma_(L.y, b.ay, L.z * b.az))) * gm<R>::sqrt(inv);     // |cos| of the angle to the axis
+    return !(c < b.cos_t * ca - b.sin_t * sa - R(1e-5));      // angle <= theta + alpha
+}
+template <typename R> __device__ __forceinline__ bool packet_survives(const Cull4<R>& L, const WarpBound<R>& b, CullRay<R, CULL_AXIS>*) {
+    const R du = L.x - b.ax, dv = L.y - b.ay;
+    const R rr = gm<R>::sqrt(-L.z) * R(1.0001) + b.cos_t;      // sqrt(R^2 + margin) + rho; -L.z = +inf for unbounded objects
+    return !(fma_(du, du, dv * dv) > rr * rr);
+}
+template <typename R> __device__ __forceinline__ bool packet_survives(const Cull4<R>&, const WarpBound<R>&, CullRay<R, CULL_GENERAL>*) { return true; }
+
+constexpr int PCHUNK = 1024;                // objects per packet pass = survivor list capacity per warp (uint16 indices)
+constexpr size_t SURV_BYTES = (size_t)(SCAN_THREADS / 32) * PCHUNK * sizeof(uint16_t);
+
 // ------------------------------------------------------------------ scan = cull kernel + exact kernels
 // Phase 1, k_cull: persistent CTAs over blocks of SCAN_THREADS * RPT rays; the cull table is staged once per
 // CTA when it fits ("resident"), else streamed through two buffers per block of rays.  Each thread carries RPT
@@ -709,6 +819,7 @@ template <typename R> struct ClosestSource {                 // rays of one recu
         out.ox = lv.ray[i]; out.oy = lv.ray[cap + i]; out.oz = lv.ray[2 * cap + i];
         out.dx = lv.ray[3 * cap + i]; out.dy = lv.ray[4 * cap + i]; out.dz = lv.ray[5 * cap + i];
     }
+    __device__ __forceinline__ int id(int i) const { return i; }
     __device__ __forceinline__ void init(int i) const {       // no hit yet
         lv.hit[i] = -1;
         reinterpret_cast<typename BitsOf<R>::type*>(lv.t)[i] = ~(typename BitsOf<R>::type)0;
@@ -718,12 +829,12 @@ template <typename R> struct ClosestSource {                 // rays of one recu
 
 template <typename R> struct ShadowSource {                  // shadow rays of one light: slots [base, base + n)
     ShadowQueue<R> sq; int base;
+    __device__ __forceinline__ int id(int i) const { return sq.perm[base + i]; }          // i-th ray in by-object order -> slot in the segment
     __device__ __forceinline__ void load(int i, Ray<R>& out) const {
-        const size_t cap = (size_t)sq.cap; const int q = base + i;
-        out.ox = sq.q[q]; out.oy = sq.q[cap + q]; out.oz = sq.q[2 * cap + q];
-        out.dx = sq.q[3 * cap + q]; out.dy = sq.q[4 * cap + q]; out.dz = sq.q[5 * cap + q];
+        const R* rec = sq.q + (size_t)(base + id(i)) * 8;
+        out.ox = rec[0]; out.oy = rec[1]; out.oz = rec[2]; out.dx = rec[3]; out.dy = rec[4]; out.dz = rec[5];
     }
-    __device__ __forceinline__ void init(int i) const { sq.first[base + i] = 0x7fffffff; }
+    __device__ __forceinline__ void init(int i) const { sq.first[base + id(i)] = 0x7fffffff; }
 };
 
 template <typename R, int FAMILY, int RPT, typename Source>
@@ -734,7 +845,8 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ __align__(8) uint64_t bar[2];
     const int tid = threadIdx.x, lane = tid & 31;
-    R* const tab = reinterpret_cast<R*>(smem_raw);             // buffer b starts at tab + b * chunk_objs * 4
+    uint16_t* const surv = reinterpret_cast<uint16_t*>(smem_raw) + (tid >> 5) * PCHUNK;    // this warp's survivor list (packet stage)
+    R* const tab = reinterpret_cast<R*>(smem_raw + SURV_BYTES);   // buffer b starts at tab + b * chunk_objs * 4
     const int n = *n_ptr;
     const int nblocks = (n + RAYS_PER_BLOCK - 1) / RAYS_PER_BLOCK;
     if ((int)blockIdx.x >= nblocks) return;
@@ -751,14 +863,24 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
         const int ray0 = blk * RAYS_PER_BLOCK;
         CullRay<R, FAMILY> cr[RPT];
         bool active[RPT];
+        int rid[RPT];                                          // what the exact kernels index the ray source with
 #pragma unroll
         for (int r = 0; r < RPT; r++) {
-            const int i = ray0 + r * SCAN_THREADS + tid;
+            const int i = ray0 + ((tid >> 5) * RPT + r) * 32 + lane;      // a warp owns 32 * RPT consecutive rays: a narrow packet
             Ray<R> w = {R(0), R(0), R(0), R(0), R(0), R(1)};
             active[r] = i < n;
+            rid[r] = active[r] ? src.id(i) : 0;
             if (active[r]) { src.load(i, w); src.init(i); }
             cr[r].init(w, frame);
         }
+        const WarpBound<R> wb = warp_bound<R, RPT>(cr, active);
+        int n_active = 0;
+#pragma unroll
+        for (int r = 0; r < RPT; r++) n_active += active[r] ? 1 : 0;
+        unsigned long long fine = 0, packet = 0;           // this lane's executed tests
+#ifdef GMLRT_DEBUG_PACKETS
+        if (lane == 0 && FAMILY != CULL_GENERAL) { atomicAdd(&ctr->dbg[0 + 4 * (FAMILY == CULL_AXIS)], 1ull); if (wb.usable) atomicAdd(&ctr->dbg[1 + 4 * (FAMILY == CULL_AXIS)], 1ull); }
+#endif
         if (!resident) {
             __syncthreads();                                   // (re)staging must not overtake readers of the previous block of rays
             if (tid == 0) {
@@ -772,16 +894,15 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
             const int base = resident ? 0 : c * chunk_objs;
             const R* sm = resident ? tab : tab + (size_t)b * chunk_objs * 4;
             const int end = resident ? NP : base + min(chunk_objs, NP - base);
-            for (int first = base; first < end; first += GROUP) {          // one window of GROUP objects
-                uint32_t lo[RPT], hi[RPT];
-                cull_window<R, FAMILY, RPT>(sm, first - base, cr, lo, hi);
+            // append the survivors in (lo, hi)[r] to the candidate queue; bit 31 - j of lo = object id_of(j), of hi = id_of(32 + j)
+            auto append = [&](uint32_t (&lo)[RPT], uint32_t (&hi)[RPT], auto id_of) __attribute__((always_inline)) {
                 int mine = 0;
 #pragma unroll
                 for (int r = 0; r < RPT; r++) {
                     if (!active[r]) { lo[r] = 0; hi[r] = 0; }
                     mine += __popc(lo[r]) + __popc(hi[r]);
                 }
-                if (!__any_sync(0xffffffffu, mine != 0)) continue;         // nothing survived in this warp
+                if (!__any_sync(0xffffffffu, mine != 0)) return;            // nothing survived in this warp
                 // warp-aggregated append: inclusive scan of the lanes' counts, one atomic for the warp
                 int incl = mine;
 #pragma unroll
@@ -790,22 +911,63 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
                 int at = 0;
                 if (lane == 31) at = atomicAdd(cq.count, total);
                 at = __shfl_sync(0xffffffffu, at, 31) + incl - mine;
-                if (at + mine > cq.cap) { if (mine) ctr->overflow = 1; continue; }   // queue full: the host retries with smaller tiles
+                if (at + mine > cq.cap) { if (mine) ctr->overflow = 1; return; }     // queue full: the host retries with smaller tiles
 #pragma unroll
                 for (int r = 0; r < RPT; r++) {
-                    const int i = ray0 + r * SCAN_THREADS + tid;
+                    const int i = rid[r];
                     uint32_t m = lo[r];
-                    while (m) {                                // test j of the first half sits in bit 31 - j
+                    while (m) {
                         const int j = __clz(m);
                         m &= ~(0x80000000u >> j);
-                        cq.ray[at] = i; cq.obj[at] = first + j; at++;
+                        cq.ray[at] = i; cq.obj[at] = id_of(j); at++;
                     }
                     m = hi[r];
                     while (m) {
                         const int j = __clz(m);
                         m &= ~(0x80000000u >> j);
-                        cq.ray[at] = i; cq.obj[at] = first + 32 + j; at++;
+                        cq.ray[at] = i; cq.obj[at] = id_of(32 + j); at++;
                     }
+                }
+            };
+            if (FAMILY != CULL_GENERAL && wb.usable) {
+                // packet stage: the lanes test 32 objects at a time against the warp's bound; the survivors' indices
+                // (relative to this chunk) are compacted into the warp's list, then only those are tested per ray
+                for (int p0 = base; p0 < end; p0 += PCHUNK) {
+                    const int pn = min(PCHUNK, end - p0);
+                    int ns = 0;
+                    for (int o = 0; o < pn; o += 32) {
+                        const int k = p0 - base + o + lane;
+                        packet += (o + lane < pn) ? 1 : 0;
+                        const bool sv = (o + lane < pn) && packet_survives<R>(load_cull(sm, k), wb, (CullRay<R, FAMILY>*)nullptr);
+                        const unsigned bal = __ballot_sync(0xffffffffu, sv);
+                        if (sv) surv[ns + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)k;
+                        ns += __popc(bal);
+                    }
+#ifdef GMLRT_DEBUG_PACKETS
+                    if (lane == 0) { atomicAdd(&ctr->dbg[2 + 4 * (FAMILY == CULL_AXIS)], (unsigned long long)pn); atomicAdd(&ctr->dbg[3 + 4 * (FAMILY == CULL_AXIS)], (unsigned long long)ns); }
+#endif
+                    const int padded = (ns + GROUP - 1) / GROUP * GROUP;
+                    for (int k = ns + lane; k < padded; k += 32) surv[k] = (uint16_t)(p0 - base);      // any valid record; masked off below
+                    __syncwarp();
+                    for (int k0 = 0; k0 < padded; k0 += GROUP) {
+                        uint32_t lo[RPT], hi[RPT];
+                        cull_window_indirect<R, FAMILY, RPT>(sm, surv, k0, cr, lo, hi);
+                        const int valid = ns - k0;                                 // entries of this window that are real
+                        fine += (unsigned long long)(n_active * min(valid, GROUP));
+                        const uint32_t mlo = valid >= 32 ? 0xffffffffu : ~(0xffffffffu >> valid);
+                        const uint32_t mhi = valid >= 64 ? 0xffffffffu : (valid <= 32 ? 0u : ~(0xffffffffu >> (valid - 32)));
+#pragma unroll
+                        for (int r = 0; r < RPT; r++) { lo[r] &= mlo; hi[r] &= mhi; }
+                        append(lo, hi, [&](int j) { return base + (int)surv[k0 + j]; });
+                    }
+                    __syncwarp();                                                   // the list is rewritten by the next pass
+                }
+            } else {
+                for (int first = base; first < end; first += GROUP) {      // one window of GROUP objects
+                    uint32_t lo[RPT], hi[RPT];
+                    cull_window<R, FAMILY, RPT>(sm, first - base, cr, lo, hi);
+                    fine += (unsigned long long)(n_active * GROUP);
+                    append(lo, hi, [&](int j) { return first + j; });
                 }
             }
             if (!resident) {
@@ -816,6 +978,8 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
                 }
             }
         }
+        fine = warp_sum_u64(fine); packet = warp_sum_u64(packet);
+        if (lane == 0) { atomicAdd(&ctr->cull_tests[FAMILY], fine); if (packet) atomicAdd(&ctr->packet_tests, packet); }
     }
 }
 
@@ -900,14 +1064,75 @@ __global__ void __launch_bounds__(EXACT_THREADS) k_exact_shadow(const __grid_con
         if (!COUNT && sq.first[q] != 0x7fffffff) continue;     // already occluded (a stale read only costs a test)
         if (COUNT) { n_exact++; n_flops += (unsigned)sc.obj_flops[obj]; }
         Ray<R> w;
-        const size_t cap = (size_t)sq.cap;
-        w.ox = sq.q[q]; w.oy = sq.q[cap + q]; w.oz = sq.q[2 * cap + q];
-        w.dx = sq.q[3 * cap + q]; w.dy = sq.q[4 * cap + q]; w.dz = sq.q[5 * cap + q];
+        const R* rec = sq.q + (size_t)q * 8;
+        w.ox = rec[0]; w.oy = rec[1]; w.oz = rec[2]; w.dx = rec[3]; w.dy = rec[4]; w.dz = rec[5];
         R t; int code;
         if (!exact_hit<R, false>(sc, obj, w, nullptr, 0, 0, t, code)) continue;
-        if (t * sq.q[7 * cap + q] < sq.q[6 * cap + q]) atomicMin(&sq.first[q], sc.scan_of[obj]);
+        if (t * rec[7] < rec[6]) atomicMin(&sq.first[q], sc.scan_of[obj]);   // T * |incoming direction| < distance to the light
     }
     if (COUNT) { warp_add(&ctr->exact_tests, n_exact); warp_add(&ctr->exact_flops, n_flops); }
+}
+
+// ------------------------------------------------------------------ shadow rays by shaded object
+// The packet stage of k_cull only pays off when the 32 * RPT rays of a warp form a narrow beam.  In queue order
+// (= screen order of the rays that spawned them) a warp's shadow rays start on whatever objects a strip of pixels
+// happens to cross, at any depth; ordered by the SHADED OBJECT they start within one bounding sphere (small objects)
+// or stay in screen order within it (a ground plane).  Counting sort of slot indices, keys = sq.skip (the shaded
+// leaf; -1 for CSG members): block-private histograms, one scan, block-wise scatter.  Only the 4-byte permutation
+// is written; the 32-byte ray records stay where k_shade put them.
+constexpr int SORT_BINS_MAX = 4096, SORT_CHUNK = 4096, SORT_THREADS = 256;
+
+__device__ __forceinline__ int sort_bin(int key, int shift, int nb) { return key < 0 ? nb - 1 : min(key >> shift, nb - 2); }
+
+template <typename R>
+__global__ void __launch_bounds__(SORT_THREADS) k_sort_hist(const __grid_constant__ ShadowQueue<R> sq, int light, int shift, int nb, int* hist) {
+    __shared__ int h[SORT_BINS_MAX];
+    const int n = sq.count[light], base = light * sq.per_light;
+    const int nchunks = (n + SORT_CHUNK - 1) / SORT_CHUNK;
+    for (int b = threadIdx.x; b < nb; b += SORT_THREADS) h[b] = 0;
+    __syncthreads();
+    for (int c = blockIdx.x; c < nchunks; c += gridDim.x)
+        for (int i = c * SORT_CHUNK + threadIdx.x; i < min(n, (c + 1) * SORT_CHUNK); i += SORT_THREADS)
+            atomicAdd(&h[sort_bin(sq.skip[base + i], shift, nb)], 1);
+    __syncthreads();
+    for (int b = threadIdx.x; b < nb; b += SORT_THREADS) if (h[b]) atomicAdd(&hist[b], h[b]);
+}
+
+// exclusive prefix of hist[0..nb) into cursor[0..nb); hist is cleared for the next use (one block)
+static __global__ void __launch_bounds__(1024) k_sort_scan(int nb, int* hist, int* cursor) {
+    __shared__ int part[1024];
+    const int per = (nb + 1023) / 1024, b0 = threadIdx.x * per;
+    int sum = 0;
+    for (int b = b0; b < min(nb, b0 + per); b++) sum += hist[b];
+    part[threadIdx.x] = sum;
+    __syncthreads();
+    for (int off = 1; off < 1024; off <<= 1) {
+        const int v = threadIdx.x >= off ? part[threadIdx.x - off] : 0;
+        __syncthreads();
+        part[threadIdx.x] += v;
+        __syncthreads();
+    }
+    int run = part[threadIdx.x] - sum;
+    for (int b = b0; b < min(nb, b0 + per); b++) { cursor[b] = run; run += hist[b]; hist[b] = 0; }
+}
+
+template <typename R>
+__global__ void __launch_bounds__(SORT_THREADS) k_sort_scatter(const __grid_constant__ ShadowQueue<R> sq, int light, int shift, int nb, int* cursor) {
+    __shared__ int h[SORT_BINS_MAX], at[SORT_BINS_MAX];
+    const int n = sq.count[light], base = light * sq.per_light;
+    const int nchunks = (n + SORT_CHUNK - 1) / SORT_CHUNK;
+    for (int c = blockIdx.x; c < nchunks; c += gridDim.x) {
+        for (int b = threadIdx.x; b < nb; b += SORT_THREADS) h[b] = 0;
+        __syncthreads();
+        const int i1 = min(n, (c + 1) * SORT_CHUNK);
+        for (int i = c * SORT_CHUNK + threadIdx.x; i < i1; i += SORT_THREADS) atomicAdd(&h[sort_bin(sq.skip[base + i], shift, nb)], 1);
+        __syncthreads();
+        for (int b = threadIdx.x; b < nb; b += SORT_THREADS) at[b] = h[b] ? atomicAdd(&cursor[b], h[b]) : 0;   // this chunk's range in bin b
+        __syncthreads();
+        for (int i = c * SORT_CHUNK + threadIdx.x; i < i1; i += SORT_THREADS)
+            sq.perm[base + atomicAdd(&at[sort_bin(sq.skip[base + i], shift, nb)], 1)] = i;
+        __syncthreads();
+    }
 }
 
 // occlusion flags for the resolve pass (+ the credited-work counters)
@@ -1225,9 +1450,9 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
             slot += li * sq.per_light;
             const V3<R> so = P + N * R(1e-4);
             const int qc = sq.cap;
-            sq.q[slot] = so.x; sq.q[qc + slot] = so.y; sq.q[2 * qc + slot] = so.z;
-            sq.q[3 * qc + slot] = ldir.x; sq.q[4 * qc + slot] = ldir.y; sq.q[5 * qc + slot] = ldir.z;
-            sq.q[6 * qc + slot] = dist; sq.q[7 * qc + slot] = length(D);
+            R* rec = sq.q + (size_t)slot * 8;
+            rec[0] = so.x; rec[1] = so.y; rec[2] = so.z; rec[3] = ldir.x; rec[4] = ldir.y; rec[5] = ldir.z;
+            rec[6] = dist; rec[7] = length(D);
             sq.skip[slot] = leaf < sc.n_leaves ? leaf : -1;      // a CSG object may shadow itself (oracle.c in_shadow)
             sq.target[slot] = i * sc.n_lights + li;
             occl[i * sc.n_lights + li] = 0;
@@ -1439,7 +1664,13 @@ public:
         out.rays_reflect = c.rays_reflect; out.rays_refract = c.rays_refract;
         out.rays_shadow = c.rays_shadow; out.shadow_occluded = c.shadow_occluded;
         out.shadow_tests = c.shadow_tests; out.shadow_flops = c.shadow_flops; out.exact_tests = c.exact_tests; out.exact_flops = c.exact_flops;
+        for (int k = 0; k < 3; k++) out.cull_by_family[k] = c.cull_tests[k];
+        out.packet_tests = c.packet_tests;
         out.error = c.error; out.overflow = c.overflow;
+#ifdef GMLRT_DEBUG_PACKETS
+        std::fprintf(stderr, "packets pivot: blocks %llu usable %llu offered %llu survivors %llu | axis: blocks %llu usable %llu offered %llu survivors %llu\n",
+                     c.dbg[0], c.dbg[1], c.dbg[2], c.dbg[3], c.dbg[4], c.dbg[5], c.dbg[6], c.dbg[7]);
+#endif
         return GMLRT_OK;
     }
 
@@ -1529,6 +1760,7 @@ private:
     struct Launch { int grid = 148; size_t smem = 0; };
     Launch l_primary_, l_closest_, l_shadow_pivot_, l_shadow_axis_;                      // the four k_cull instantiations
     CandQueue cq_{}; int cand_per_ray_ = 4, tile_shrink_ = 0;
+    int* sort_hist_ = nullptr; int* sort_cursor_ = nullptr; int sort_nb_ = 2, sort_shift_ = 0; bool sort_clear_ = true;
     // cull tables (device) and what they were built for: any ray, camera rays, one per light
     std::vector<double> bound_;                                  // host: [n][4] bounding spheres (centre, radius) of the objects
     R* cull_general_ = nullptr; R* cull_eye_ = nullptr; std::vector<R*> cull_light_;
@@ -1762,7 +1994,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     cand_per_ray_ = std::min<int>(std::max(sc_.n_leaves, 1), (int)env_size("GMLRT_CAND_PER_RAY", 4) + n_unbounded);
     const double cand_bytes = cand_per_ray_ * (8.0 + sizeof(R));
     const double node_bytes = (6 + 1 + NREC + 6) * sizeof(R) + 12 + nl;
-    const double shadow_bytes = nl * (8.0 * sizeof(R) + 12);
+    const double shadow_bytes = nl * (8.0 * sizeof(R) + 16);
     const double per_sample = sum_mult * node_bytes + max_mult * (shadow_bytes + cand_bytes) + 3 * sizeof(R) + (kRobustPrimary ? 48 : 0);
     size_t free_b = 0, total_b = 0;
     CU_TRY(cudaMemGetInfo(&free_b, &total_b));
@@ -1790,7 +2022,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
         lo[l].occl = take(cap * std::max(nl, 1));
     }
     const size_t sq_cap = max_cap * std::max(nl, 1);
-    size_t o_sq = take(8 * sq_cap * sizeof(R)), o_skip = take(sq_cap * 4), o_tgt = take(sq_cap * 4), o_first = take(sq_cap * 4);
+    size_t o_sq = take(8 * sq_cap * sizeof(R)), o_skip = take(sq_cap * 4), o_tgt = take(sq_cap * 4), o_first = take(sq_cap * 4), o_perm = take(sq_cap * 4), o_sort = take(2 * SORT_BINS_MAX * sizeof(int));
     const size_t cand_cap = std::min<size_t>((size_t)((double)max_cap * cand_per_ray_ * (double)(1 << tile_shrink_)), (size_t)2000000000);
     size_t o_cray = take(cand_cap * 4), o_cobj = take(cand_cap * 4), o_ct = take(cand_cap * sizeof(R)), o_ccount = take(256);
     size_t o_samples = take(3 * S0 * sizeof(R));
@@ -1812,7 +2044,10 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
         L.ray64 = (kRobustPrimary && l == 0) ? (double*)(base + o_ray64) : nullptr;
     }
     sq_.q = (R*)(base + o_sq); sq_.skip = (int*)(base + o_skip); sq_.target = (int*)(base + o_tgt); sq_.cap = (int)sq_cap;
-    sq_.per_light = (int)max_cap; sq_.count = shadow_counts_; sq_.first = (int*)(base + o_first);
+    sq_.per_light = (int)max_cap; sq_.count = shadow_counts_; sq_.first = (int*)(base + o_first); sq_.perm = (int*)(base + o_perm);
+    sort_hist_ = (int*)(base + o_sort); sort_cursor_ = sort_hist_ + SORT_BINS_MAX; sort_clear_ = true;
+    sort_nb_ = std::min(sc_.n_leaves + 1, SORT_BINS_MAX); sort_shift_ = 0;
+    while (((std::max(sc_.n_leaves, 1) - 1) >> sort_shift_) + 2 > sort_nb_) sort_shift_++;
     cq_.ray = (int*)(base + o_cray); cq_.obj = (int*)(base + o_cobj); cq_.t = (void*)(base + o_ct); cq_.count = (int*)(base + o_ccount);
     cq_.cap = (int)cand_cap;
     samples_ = (R*)(base + o_samples); sample_cap_ = (int)S0;
@@ -1826,7 +2061,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     else { resident_ = 0; chunk_objs_ = (int)(chunk_bytes / rec_bytes) / GROUP * GROUP; table_smem_ = 2 * (size_t)chunk_objs_ * rec_bytes; }
     auto cfg = [&](auto kernel, Launch& L) -> int {
         int occ = 1;
-        L.smem = table_smem_;
+        L.smem = SURV_BYTES + table_smem_;
         CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, SCAN_THREADS, L.smem));
         L.grid = sms_ * std::max(occ, 1);
         return GMLRT_OK;
@@ -1902,6 +2137,12 @@ int Renderer<R>::trace_rows(int y0, int y1, bool counting, std::string& err) {
                 const bool axis = frame_light_[li].family == CULL_AXIS;
                 ShadowSource<R> ssrc{sq_, li * sq_.per_light};
                 CU_TRY(cudaMemsetAsync(cq_.count, 0, sizeof(int), stream_));
+                MARK(KC_SORT);
+                if (sort_clear_) { CU_TRY(cudaMemsetAsync(sort_hist_, 0, SORT_BINS_MAX * sizeof(int), stream_)); sort_clear_ = false; }
+                k_sort_hist<R><<<sms_ * 4, SORT_THREADS, 0, stream_>>>(sq_, li, sort_shift_, sort_nb_, sort_hist_);
+                k_sort_scan<<<1, 1024, 0, stream_>>>(sort_nb_, sort_hist_, sort_cursor_);
+                k_sort_scatter<R><<<sms_ * 4, SORT_THREADS, 0, stream_>>>(sq_, li, sort_shift_, sort_nb_, sort_cursor_);
+                totals_.launches += 3;
                 MARK(KC_SHADOW);
                 if (axis) k_cull<R, CULL_AXIS, RPT_FAMILY, ShadowSource<R>><<<l_shadow_axis_.grid, SCAN_THREADS, l_shadow_axis_.smem, stream_>>>(
                     ssrc, &shadow_counts_[li], cull_light_[li], frame_light_[li], sc_.n_cull, cq_, ctr_, chunk_objs_, resident_);

@@ -186,12 +186,14 @@ typedef struct gmlrt_stats {
     uint64_t kernel_launches;   /* kernels launched by this call */
     uint32_t n_devices;
     uint32_t n_leaves;
-    uint64_t cull_tests;        /* executed: first-phase bounding-sphere tests (every query x every object) */
+    uint64_t cull_tests;        /* executed: per-ray bounding-sphere tests (after the per-warp packet stage) */
     uint64_t exact_tests;       /* executed: second-phase <Type>.Intersect tests on the survivors (counting mode) */
-    double   flops_executed;    /* 14 per cull test (7 FFMA) + the per-leaf-type table per exact test (counting mode) */
-    double   ms_class[8];       /* profiling mode: device ms per kernel class: gen, cull of camera rays, cull of reflection/refraction
-                                   rays, cull of shadow rays, shade, resolve, pixels, exact tests */
-    uint64_t launches_class[8]; /* ... and launches per class */
+    double   flops_executed;    /* 15 / 7 / 7 per cull test (GENERAL / PIVOT / AXIS), 20 per packet test, the per-leaf-type
+                                   table per exact test (the last term needs counting mode) */
+    double   ms_class[9];       /* profiling mode: device ms per kernel class: gen, cull of camera rays, cull of reflection/refraction
+                                   rays, cull of shadow rays, shade, resolve, pixels, exact tests, shadow-ray sort */
+    uint64_t launches_class[9]; /* ... and launches per class */
+    uint64_t packet_tests;      /* executed: per-warp packet tests (one lane x one object) */
 } gmlrt_stats;
 
 /* Create a context on `n` devices (`devices` = CUDA ordinals; n >= 1).  With n > 1 the

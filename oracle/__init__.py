@@ -18,7 +18,8 @@ class Stats(ctypes.Structure):
                 ("leaf_tests", ctypes.c_uint64), ("flops_credited", ctypes.c_double), ("kernel_launches", ctypes.c_uint64),
                 ("n_devices", ctypes.c_uint32), ("n_leaves", ctypes.c_uint32),
                 ("cull_tests", ctypes.c_uint64), ("exact_tests", ctypes.c_uint64), ("flops_executed", ctypes.c_double),
-                ("ms_class", ctypes.c_double * 8), ("launches_class", ctypes.c_uint64 * 8)]     # = gmlrt_stats, include/gmlrt.h
+                ("ms_class", ctypes.c_double * 9), ("launches_class", ctypes.c_uint64 * 9),
+                ("packet_tests", ctypes.c_uint64)]     # = gmlrt_stats, include/gmlrt.h
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
