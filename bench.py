@@ -188,7 +188,7 @@ def main():
     cst = ctx.trace()
     ctx.set_counting(False)
     counts = torch.tensor([cst.rays_primary, cst.rays_reflect, cst.rays_refract, cst.rays_shadow, cst.shadow_occluded,
-                           cst.leaf_tests, int(cst.flops_credited / 1e3), cst.cull_tests, cst.exact_tests, int(cst.flops_executed / 1e3), cst.packet_tests],
+                           cst.leaf_tests, int(cst.flops_credited / 1e3), cst.cull_tests, cst.exact_tests, int(cst.flops_executed / 1e3), cst.packet_tests, cst.cull_tests_family[0], cst.cull_tests_family[1], cst.cull_tests_family[2]],
                           dtype=torch.int64, device=f"cuda:{local_rank}")
     if dist is not None:
         dist.all_reduce(counts)
@@ -288,11 +288,23 @@ def main():
     fp32_derived = props.multi_processor_count * 128 * 2 * sm_max_mhz * 1e6 / 1e12                  # TFLOP/s per GPU
     fp32_measured = cuda.measure_fp32_tflops(local_rank)                                           # FFMA-chain microbenchmark, this box
     fp32_peak = (fp32_measured if fp32_measured > 0 else fp32_derived) * world
-    # dominant kernels: the scan kernels (closest-hit + shadow instantiations of one skeleton)
+    # every scan kernel class (cull x3, exact, sort) and, for the roofline, the dominant single kernel
     names = cuda.Stats.KERNEL_CLASSES
     scan_ms = sum(class_ms[k] for k in (1, 2, 3, 7, 8))
     scan_launches = sum(class_launches[k] for k in (1, 2, 3, 7, 8))
-    achieved = flops_frame * args.steps / (scan_ms * 1e-3) / 1e12 if scan_ms > 0 else 0.0
+    scan_tflops = flops_frame * args.steps / (scan_ms * 1e-3) / 1e12 if scan_ms > 0 else 0.0
+    # per-ray cull kernels: flops per test 15 (GENERAL), 7 (PIVOT / AXIS); camera rays are all PIVOT, reflection /
+    # refraction rays all GENERAL; the shadow class mixes PIVOT and AXIS launches
+    cull_flops = {1: 7.0 * float(counts[12]) * (class_ms[1] / max(class_ms[1] + class_ms[3], 1e-9)), 2: 15.0 * float(counts[11])}
+    dom = max((1, 2, 3, 4, 5, 7, 8), key=lambda k: class_ms[k])
+    dom_kernel = {1: "k_cull<PIVOT> over camera rays", 2: "k_cull<GENERAL> over reflection / refraction rays", 3: "k_cull<PIVOT|AXIS> over shadow rays",
+                  4: "k_shade", 5: "k_resolve", 7: "k_exact_* (exact tests on the cull survivors)", 8: "k_sort_*"}[dom]
+    if dom == 2 and class_ms[2] > 0:
+        achieved = cull_flops[2] * args.steps / (class_ms[2] * 1e-3) / 1e12
+        dom_launch_ms = class_ms[2] / max(class_launches[2], 1)
+        dom_flops_launch = cull_flops[2] * args.steps / max(class_launches[2], 1)
+    else:                                   # no single FP32-bound kernel dominates: quote the whole scan
+        achieved, dom_launch_ms, dom_flops_launch = scan_tflops, scan_ms / max(scan_launches, 1), flops_frame * args.steps / max(scan_launches, 1)
     traffic = None
     try:
         traffic = json.load(open(os.path.join(ROOT, "profiles", "scan_traffic.json"))).get("dram_bytes_per_launch")
@@ -314,15 +326,20 @@ def main():
         "kernel_ms_per_frame": {names[k]: class_ms[k] / args.steps for k in range(9)},
         "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak if fp32_peak else None,
                      "traffic": traffic,
-                     "kernel": "scan kernels (k_cull x 4 instantiations + k_exact_*): %d event intervals, %.3f ms per frame" % (scan_launches, scan_ms / args.steps),
+                     "kernel": dom_kernel, "kernel_ms_per_launch": dom_launch_ms, "kernel_flops_per_launch": dom_flops_launch,
+                     "kernel_share_of_step": class_ms[dom] / max(sum(class_ms), 1e-9),
                      "peak_kind": "measured: FFMA-chain microbenchmark on this GPU (gmlrt_measure_fp32_tflops)" if fp32_measured > 0 else "derived",
                      "peak_derived": fp32_derived * world,
-                     "note": "achieved = flops the scan kernels EXECUTE, from device counters (per-ray cull tests: 15 flops GENERAL, 7 PIVOT, 7 AXIS; "
-                             "per-warp packet tests: 20; SURVEY 8(d) table - sphere 56, plane 47, cube 81, cylinder 74, cone 70 - per exact "
-                             "test on the survivors) over their CUDA-event time in the timed region.  The reference's all-pairs scan would "
-                             "execute flops_bruteforce_equivalent for the same queries; culling removes most of it, so that figure over the "
-                             "same time is reported separately and is NOT a roofline fraction.",
-                     "flops_per_frame": flops_frame, "cull_tests_per_frame": int(counts[7]), "packet_tests_per_frame": int(counts[10]), "exact_tests_per_frame": int(counts[8]),
+                     "note": "dominant kernel by CUDA-event time in the timed region.  achieved = flops it EXECUTES (device counters: "
+                             "per-ray cull tests x 15 flops for the GENERAL family = 7 FFMA + 1 FADD) / its event time.  whole_scan gives "
+                             "the same for all scan kernels together (cull: 15 / 7 / 7 flops per test GENERAL / PIVOT / AXIS; packet tests "
+                             "20; exact tests: SURVEY 8(d) table - sphere 56, plane 47, cube 81, cylinder 74, cone 70).  The reference's "
+                             "all-pairs scan would execute flops_bruteforce_equivalent for the same queries; the cull and packet stages "
+                             "remove most of it, so bruteforce_equivalent_tflops is a speed-up figure, NOT a roofline fraction.",
+                     "whole_scan": {"tflops": scan_tflops, "frac": scan_tflops / fp32_peak if fp32_peak else None, "ms_per_frame": scan_ms / args.steps,
+                                    "flops_per_frame": flops_frame, "cull_tests_per_frame": int(counts[7]),
+                                    "cull_tests_by_family": {"general": int(counts[11]), "pivot": int(counts[12]), "axis": int(counts[13])},
+                                    "packet_tests_per_frame": int(counts[10]), "exact_tests_per_frame": int(counts[8])},
                      "flops_bruteforce_equivalent": flops_credited_frame, "leaf_tests_bruteforce_equivalent": int(counts[5]),
                      "bruteforce_equivalent_tflops": flops_credited_frame * args.steps / (scan_ms * 1e-3) / 1e12 if scan_ms > 0 else None},
     }

@@ -285,6 +285,7 @@ static int trace_once(gmlrt_ctx* c, gmlrt_stats* stats, bool& overflow) {
         // reciprocal, three square roots, the angle inequality) and the exact tests on the survivors (counting mode)
         stats->cull_tests = sum.cull_by_family[0] + sum.cull_by_family[1] + sum.cull_by_family[2];
         stats->packet_tests = sum.packet_tests;
+        for (int k = 0; k < 3; k++) stats->cull_tests_family[k] = sum.cull_by_family[k];
         stats->exact_tests = sum.exact_tests;
         stats->flops_executed = 15.0 * (double)sum.cull_by_family[0] + 7.0 * (double)(sum.cull_by_family[1] + sum.cull_by_family[2]) +
                                 20.0 * (double)sum.packet_tests + (double)sum.exact_flops;

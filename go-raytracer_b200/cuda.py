@@ -26,7 +26,7 @@ class Stats(ctypes.Structure):
                 ("n_devices", ctypes.c_uint32), ("n_leaves", ctypes.c_uint32),
                 ("cull_tests", ctypes.c_uint64), ("exact_tests", ctypes.c_uint64), ("flops_executed", ctypes.c_double),
                 ("ms_class", ctypes.c_double * 9), ("launches_class", ctypes.c_uint64 * 9),
-                ("packet_tests", ctypes.c_uint64)]
+                ("packet_tests", ctypes.c_uint64), ("cull_tests_family", ctypes.c_uint64 * 3)]
 
     KERNEL_CLASSES = ("gen", "cull_primary", "cull_secondary", "cull_shadow", "shade", "resolve", "pixels", "exact", "sort")
 

@@ -194,6 +194,7 @@ typedef struct gmlrt_stats {
                                    rays, cull of shadow rays, shade, resolve, pixels, exact tests, shadow-ray sort */
     uint64_t launches_class[9]; /* ... and launches per class */
     uint64_t packet_tests;      /* executed: per-warp packet tests (one lane x one object) */
+    uint64_t cull_tests_family[3]; /* cull_tests split by family: GENERAL (reflection / refraction rays), PIVOT, AXIS */
 } gmlrt_stats;
 
 /* Create a context on `n` devices (`devices` = CUDA ordinals; n >= 1).  With n > 1 the
