@@ -127,6 +127,9 @@ def main():
     ap.add_argument("--ref-crop", type=int, nargs=2, default=[240, 140])
     ap.add_argument("--cpu-crop", type=int, nargs=2, default=[480, 260])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--gather", default="ipc", choices=["ipc", "nccl"],
+                    help="N > 1: ipc = every rank's pixel kernel stores into rank 0's frame over NVLink (CUDA IPC peer mapping); "
+                         "nccl = reduce(SUM) of the disjoint bands")
     args = ap.parse_args()
     if args.depth is None:
         args.depth = {"mixed4096": 5, "proctex": 2, "csg256": 2}.get(args.config, 3)
@@ -166,6 +169,15 @@ def main():
     class _Frame:   # the library's device frame as a torch tensor (no copy)
         __cuda_array_interface__ = {"shape": (H, W, 4), "typestr": "|u1", "data": (ctx.frame_device_ptr, False), "version": 2}
     frame = torch.as_tensor(_Frame(), device=f"cuda:{local_rank}") if world > 1 else None
+    use_ipc = world > 1 and args.gather == "ipc"
+    if use_ipc:     # rank 0 exports its frame once; the others map it and store their rows there from k_pixels
+        handle = torch.zeros(cuda.IPC_HANDLE_BYTES, dtype=torch.uint8, device=f"cuda:{local_rank}")
+        if rank == 0:
+            handle.copy_(torch.frombuffer(bytearray(ctx.frame_ipc_export()), dtype=torch.uint8))
+        dist.broadcast(handle, src=0)
+        if rank != 0:
+            ctx.frame_ipc_attach(bytes(handle.cpu().numpy().tobytes()))
+        dist.barrier()
 
     def barrier():
         if dist is not None:
@@ -176,7 +188,9 @@ def main():
 
     def step():
         st = ctx.trace()
-        if dist is not None:
+        if use_ipc:
+            gathered[0] = frame              # rank 0's frame; complete once every rank's trace has returned (barrier below)
+        elif dist is not None:
             with torch.cuda.stream(ext):
                 buf = frame.clone()                                  # rank frames are zero outside their own bands
                 dist.reduce(buf, dst=0, op=dist.ReduceOp.SUM)        # => SUM gathers the disjoint bands onto rank 0
@@ -245,6 +259,8 @@ def main():
         ctx.upload(blob)                                    # H2D of this step's input
         tb = time.perf_counter()
         step()
+        if use_ipc:
+            dist.barrier()                                  # every producer's stores have landed in rank 0's frame
         tc = time.perf_counter()
         phase_ms["upload"] += (tb - ta) * 1e3
         phase_ms["trace"] += (tc - tb) * 1e3
@@ -307,7 +323,8 @@ def main():
         achieved, dom_launch_ms, dom_flops_launch = scan_tflops, scan_ms / max(scan_launches, 1), flops_frame * args.steps / max(scan_launches, 1)
     traffic = None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "scan_traffic.json"))).get("dram_bytes_per_launch")
+        if dom == 2 and args.config == "spheres1024" and (W, H, args.depth, world) == (3840, 2160, 3, 1):   # the captured workload
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "scan_traffic.json"))).get("dram_bytes_per_launch")
     except Exception:
         pass
     line = {
@@ -316,7 +333,9 @@ def main():
         "dtype": args.precision, "data": "synthetic",
         "config": {"workload": f"{args.config} {W}x{H} depth {args.depth}, 4 spp, {cst.n_leaves} leaves", "precision": args.precision,
                    "l2": "inputs larger than L2: the per-level ray queues of one frame are GBs, no flush needed",
-                   "parallelism": f"row bands over {world} GPU(s), scene replicated, NCCL reduce of disjoint bands to rank 0" if world > 1 else "1 GPU"},
+                   "parallelism": (f"8-row bands dealt round-robin over {world} GPU(s), scene replicated, " +
+                                   ("finished rows stored by k_pixels into GPU 0's frame over NVLink (CUDA IPC), no collective" if use_ipc
+                                    else "NCCL reduce of disjoint bands to rank 0")) if world > 1 else "1 GPU"},
         "rays_per_frame": {"primary": int(counts[0]), "reflect": int(counts[1]), "refract": int(counts[2]), "shadow": int(counts[3]),
                            "shadow_occluded": int(counts[4])},
         "gpu_launches": launches,

@@ -34,6 +34,8 @@ struct gmlrt_ctx {
     std::vector<cudaEvent_t> ev_done;                        // per device: its bands are in device 0's frame
     int band_rows = 0;
     int part = 0, n_parts = 1;                               // multi-process sharding: this context renders bands part, part+n_parts, ...
+    std::vector<char> peer_ok;                               // per device: it can store straight into devices[0]'s frame
+    uint8_t* remote_frame = nullptr;                         // another process's frame opened over CUDA IPC (gmlrt_frame_ipc_attach)
 };
 
 static thread_local std::string g_last_error = "";
@@ -123,11 +125,13 @@ int gmlrt_create(gmlrt_ctx** out, const int* devices, int n, unsigned flags) {
         c->r.emplace_back(r);
     }
     // peer access to device 0 for the band gather (ignored when unsupported: cudaMemcpyPeer still works, staged)
+    c->peer_ok.assign(devs.size(), 0);
     for (size_t i = 1; i < devs.size(); i++) {
         int can = 0;
         if (cudaDeviceCanAccessPeer(&can, devs[i], devs[0]) == cudaSuccess && can) {
             cudaSetDevice(devs[i]);
             cudaError_t pe = cudaDeviceEnablePeerAccess(devs[0], 0);
+            if (pe == cudaSuccess || pe == cudaErrorPeerAccessAlreadyEnabled) c->peer_ok[i] = 1;
             if (pe != cudaSuccess) cudaGetLastError();
         }
     }
@@ -148,6 +152,7 @@ int gmlrt_create(gmlrt_ctx** out, const int* devices, int n, unsigned flags) {
 void gmlrt_destroy(gmlrt_ctx* c) {
     if (!c) return;
     for (auto& r : c->r) { cudaSetDevice(r->device()); cudaStreamSynchronize(r->stream()); }
+    if (c->remote_frame) { cudaSetDevice(c->r[0]->device()); cudaIpcCloseMemHandle(c->remote_frame); }
     if (c->pinned) cudaFreeHost(c->pinned);
     if (c->ev_a) cudaEventDestroy(c->ev_a);
     if (c->ev_b) cudaEventDestroy(c->ev_b);
@@ -184,16 +189,22 @@ int gmlrt_upload(gmlrt_ctx* c, const void* blob, size_t blob_bytes) {
         if (rc != GMLRT_OK) return fail(c, rc, err);
         min_rows = std::min(min_rows, r->max_rows_per_tile());
     }
-    // band height: whole tiles on one device; with several devices at least ~8 bands each (tail balance)
+    (void)min_rows;
+    // rows are dealt to the devices of all processes in bands of 8 (round-robin: every device sees every part of the
+    // image, so the load balances); a device renders its bands as one run of virtual rows (RowMap), i.e. the same few
+    // large launches however many devices share the frame
     const int nd = (int)c->r.size() * c->n_parts;
-    int rows = min_rows;
-    if (nd > 1) rows = std::max(1, std::min(rows, (c->scene.height + 8 * nd - 1) / (8 * nd)));
-    c->band_rows = rows;
-    if (c->n_parts > 1) {   // rows owned by other processes stay zero, so the rank frames can be summed
-        for (auto& r : c->r) {
-            API_CU(cudaSetDevice(r->device()));
-            API_CU(cudaMemsetAsync(r->frame(), 0, (size_t)c->scene.width * c->scene.height * 4, r->stream()));
-        }
+    c->band_rows = nd > 1 ? 8 : c->scene.height;
+    IRenderer* r0 = c->r[0].get();
+    for (size_t i = 0; i < c->r.size(); i++) {
+        uint8_t* target = nullptr;
+        if (c->remote_frame) target = c->remote_frame;                 // every device of this process stores into the remote frame
+        else if (i > 0 && c->peer_ok[i]) target = r0->frame();         // NVLink stores from k_pixels: the gather is fused
+        c->r[i]->set_frame_target(target);
+    }
+    if (c->n_parts > 1 && !c->remote_frame) {   // rows owned by other processes stay zero, so the rank frames can be summed
+        API_CU(cudaSetDevice(r0->device()));
+        API_CU(cudaMemsetAsync(r0->frame(), 0, (size_t)c->scene.width * c->scene.height * 4, r0->stream()));
     }
     c->have_scene = true;
     return GMLRT_OK;
@@ -209,6 +220,35 @@ int gmlrt_set_partition(gmlrt_ctx* c, int part, int n_parts) {
 
 void* gmlrt_frame_device(gmlrt_ctx* c) { return c && !c->r.empty() ? (void*)c->r[0]->frame() : nullptr; }
 
+int gmlrt_frame_ipc_export(gmlrt_ctx* c, void* handle, size_t handle_bytes) {
+    if (!c) return fail(nullptr, GMLRT_E_BAD_ARG, "ctx is null");
+    if (!handle || handle_bytes < sizeof(cudaIpcMemHandle_t)) return fail(c, GMLRT_E_BAD_ARG, "handle buffer must hold GMLRT_IPC_HANDLE_BYTES");
+    if (!c->have_scene) return fail(c, GMLRT_E_BAD_ARG, "gmlrt_frame_ipc_export before a successful gmlrt_upload");
+    API_CU(cudaSetDevice(c->r[0]->device()));
+    cudaIpcMemHandle_t h;
+    API_CU(cudaIpcGetMemHandle(&h, c->r[0]->frame()));
+    std::memcpy(handle, &h, sizeof h);
+    return GMLRT_OK;
+}
+
+int gmlrt_frame_ipc_attach(gmlrt_ctx* c, const void* handle, size_t handle_bytes) {
+    if (!c) return fail(nullptr, GMLRT_E_BAD_ARG, "ctx is null");
+    API_CU(cudaSetDevice(c->r[0]->device()));
+    if (c->remote_frame) { cudaIpcCloseMemHandle(c->remote_frame); c->remote_frame = nullptr; }
+    if (handle) {
+        if (handle_bytes < sizeof(cudaIpcMemHandle_t)) return fail(c, GMLRT_E_BAD_ARG, "handle buffer must hold GMLRT_IPC_HANDLE_BYTES");
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, handle, sizeof h);
+        void* p = nullptr;
+        API_CU(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        c->remote_frame = (uint8_t*)p;
+    }
+    for (auto& r : c->r) r->set_frame_target(c->remote_frame);
+    if (!c->remote_frame)
+        for (size_t i = 1; i < c->r.size(); i++) c->r[i]->set_frame_target(c->peer_ok[i] ? c->r[0]->frame() : nullptr);
+    return GMLRT_OK;
+}
+
 static int trace_once(gmlrt_ctx* c, gmlrt_stats* stats, bool& overflow) {
     overflow = false;
     if (!c) return fail(nullptr, GMLRT_E_BAD_ARG, "ctx is null");
@@ -222,20 +262,28 @@ static int trace_once(gmlrt_ctx* c, gmlrt_stats* stats, bool& overflow) {
     API_CU(cudaEventRecord(c->ev_a, r0->stream()));
     // the other devices start after ev_a so that ev_a..ev_b on device 0 brackets the whole job
     for (int i = 1; i < nd; i++) { API_CU(cudaSetDevice(c->r[i]->device())); API_CU(cudaStreamWaitEvent(c->r[i]->stream(), c->ev_a, 0)); }
-    int band = 0;
-    for (int y0 = 0; y0 < H; y0 += c->band_rows, band++) {
-        const int y1 = std::min(H, y0 + c->band_rows);
-        if (band % c->n_parts != c->part) continue;
-        const int di = (band / c->n_parts) % nd;
+    for (int di = 0; di < nd; di++) {
         IRenderer* r = c->r[di].get();
-        int rc = r->trace_rows(y0, y1, c->counting, err);
+        RowMap map;
+        map.band_rows = c->band_rows; map.n_parts = nd * c->n_parts; map.part = c->part * nd + di;
+        const int vrows = map.count(H);
+        if (vrows == 0) continue;
+        int rc = r->trace_rows(0, vrows, map, c->counting, err);
         if (rc != GMLRT_OK) return fail(c, rc, err);
-        if (di != 0) {   // gather: finished band -> device 0's frame, on the producing device's stream
+        if (di != 0) {   // gather on the producing device's stream: frame rows only when k_pixels could not store them itself
             API_CU(cudaSetDevice(r->device()));
-            const size_t off = (size_t)y0 * W * 4, bytes = (size_t)(y1 - y0) * W * 4;
-            API_CU(cudaMemcpyPeerAsync(r0->frame() + off, r0->device(), r->frame() + off, r->device(), bytes, r->stream()));
+            const size_t band = (size_t)c->band_rows * W * 4, pitch = band * map.n_parts, first = band * map.part;
+            const int full = vrows / c->band_rows, rest = vrows % c->band_rows;
+            auto gather = [&](uint8_t* dst, const uint8_t* src, size_t scale) -> cudaError_t {
+                cudaError_t e = cudaSuccess;
+                if (full) e = cudaMemcpy2DAsync(dst + first * scale, pitch * scale, src + first * scale, pitch * scale, band * scale, full, cudaMemcpyDefault, r->stream());
+                if (e == cudaSuccess && rest)
+                    e = cudaMemcpyAsync(dst + (first + pitch * full) * scale, src + (first + pitch * full) * scale, (size_t)rest * W * 4 * scale, cudaMemcpyDefault, r->stream());
+                return e;
+            };
+            if (!c->peer_ok[di] && !c->remote_frame) API_CU(gather(r0->frame(), r->frame(), 1));
             if (c->counting && r->primary_ids() && r0->primary_ids())
-                API_CU(cudaMemcpyPeerAsync(r0->primary_ids() + off, r0->device(), r->primary_ids() + off, r->device(), bytes * 4, r->stream()));
+                API_CU(gather((uint8_t*)r0->primary_ids(), (const uint8_t*)r->primary_ids(), 4));
         }
     }
     for (int i = 1; i < nd; i++) {
@@ -306,12 +354,8 @@ int gmlrt_trace(gmlrt_ctx* c, gmlrt_stats* stats) {
         if (rc != GMLRT_OK || !overflow) return rc;
         c->have_frame = false;
         std::string err;
-        int min_rows = c->scene.height;
-        for (auto& r : c->r) {
+        for (auto& r : c->r)
             if (!r->shrink_tiles(c->scene, err)) return fail(c, GMLRT_E_OOM, "candidate queue overflow: " + err);
-            min_rows = std::min(min_rows, r->max_rows_per_tile());
-        }
-        c->band_rows = std::max(1, std::min(c->band_rows, min_rows));
     }
     return fail(c, GMLRT_E_OOM, "candidate queue overflow persists after shrinking the tiles");
 }

@@ -1307,7 +1307,7 @@ __constant__ gomath::PcgJump c_pcg_jump[160];   // affine maps advancing the PCG
 constexpr int SHADE_THREADS = 128;
 
 template <typename R>
-__global__ void __launch_bounds__(256) k_gen(DevScene<R> sc, Level<R> lv, Counters* ctr, int y0, int rows) {
+__global__ void __launch_bounds__(256) k_gen(DevScene<R> sc, Level<R> lv, Counters* ctr, int y0, int rows, RowMap map) {
     const int S = rows * sc.W * 4;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i == 0) {
@@ -1316,7 +1316,7 @@ __global__ void __launch_bounds__(256) k_gen(DevScene<R> sc, Level<R> lv, Counte
     }
     if (i >= S) return;
     const int s = i & 3, pix = i >> 2;
-    const int x = pix % sc.W, y = y0 + pix / sc.W;
+    const int x = pix % sc.W, y = map.actual(y0 + pix / sc.W);
     const int ymin = (y / 20) * 20;                       // work item = (column, 20-row batch), :663-672
     const int q = 8 * (y - ymin) + 2 * s;                 // draws consumed before this sample
     gomath::Pcg rng;
@@ -1347,7 +1347,7 @@ enum { REC_P = 0, REC_N = 3, REC_COL = 6, REC_REFL = 9, REC_TRANSP = 10, REC_KR 
 template <typename R>
 __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R> lv, Level<R> next, ShadowQueue<R> sq,
                                                          unsigned char* occl, Counters* ctr, int level, int spawn,
-                                                         int32_t* ids, int y0) {
+                                                         int32_t* ids, int y0, RowMap map) {
     const int n = ctr->count[level];
     for (int blk0 = blockIdx.x * blockDim.x; blk0 < n; blk0 += gridDim.x * blockDim.x) {   // uniform per block
     const int i = blk0 + threadIdx.x;
@@ -1355,7 +1355,8 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
     bool live = i < n;
     int h = live ? lv.hit[i] : -1;
     if (ids && live) {                                     // level 0 only: primary hit ids in (y, x, sample) order
-        ids[(size_t)y0 * sc.W * 4 + i] = h < 0 ? -1 : sc.scan_of[h & HIT_LEAF_MASK];
+        const int pix = i >> 2;
+        ids[((size_t)map.actual(y0 + pix / sc.W) * sc.W + pix % sc.W) * 4 + (i & 3)] = h < 0 ? -1 : sc.scan_of[h & HIT_LEAF_MASK];
     }
     live = live && h >= 0;
     Ray<R> w = {R(0), R(0), R(0), R(0), R(0), R(1)};
@@ -1570,7 +1571,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_resolve(DevScene<R> sc, Level
 // mean of the 4 samples and quantisation: img.Set(x, y, total*0.25) -> Vec3.RGBA -> RGBAModel
 // (raytracer.go:656, vec.go:104-107): uint8(uint32(c*65535) >> 8), alpha 0xFF.
 template <typename R>
-__global__ void __launch_bounds__(256) k_pixels(DevScene<R> sc, const R* samples, int sample_cap, uchar4* frame, int y0, int rows) {
+__global__ void __launch_bounds__(256) k_pixels(DevScene<R> sc, const R* samples, int sample_cap, uchar4* frame, int y0, int rows, RowMap map) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= rows * sc.W) return;
     R c[3];
@@ -1585,7 +1586,7 @@ __global__ void __launch_bounds__(256) k_pixels(DevScene<R> sc, const R* samples
     px.y = (unsigned char)((unsigned)(c[1] * R(65535)) >> 8);
     px.z = (unsigned char)((unsigned)(c[2] * R(65535)) >> 8);
     px.w = 0xFF;
-    frame[(size_t)y0 * sc.W + p] = px;
+    frame[(size_t)map.actual(y0 + p / sc.W) * sc.W + p % sc.W] = px;      // may be a peer device's frame (NVLink stores)
 }
 
 // ------------------------------------------------------------------ host side: one renderer per device
@@ -1675,7 +1676,8 @@ public:
     }
 
     int upload(const HostScene& S, std::string& err) override;
-    int trace_rows(int y0, int y1, bool counting, std::string& err) override;
+    int trace_rows(int v0, int v1, const RowMap& map, bool counting, std::string& err) override;
+    void set_frame_target(uint8_t* target) override { frame_target_ = target; }
 
 private:
     // Scene arrays are bump-allocated from one arena that survives across uploads (cudaMalloc / cudaFree cost more than
@@ -1749,6 +1751,7 @@ private:
     R* samples_ = nullptr; int sample_cap_ = 0;
     int rows_per_tile_ = 0, depth_eff_ = 1;
     uchar4* frame_ = nullptr; size_t frame_px_ = 0;
+    uint8_t* frame_target_ = nullptr;       // where k_pixels stores instead of frame_ (a peer device's frame), or null
     int32_t* ids_ = nullptr; size_t ids_n_ = 0;
     Counters* ctr_ = nullptr;
     bool profile_ = false;
@@ -2076,7 +2079,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
 }
 
 template <typename R>
-int Renderer<R>::trace_rows(int y0, int y1, bool counting, std::string& err) {
+int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, std::string& err) {
     CU_TRY(cudaSetDevice(dev_));
     const int W = sc_.W;
     if (need_ctr_reset_) { CU_TRY(cudaMemsetAsync(ctr_, 0, sizeof(Counters), stream_)); need_ctr_reset_ = false; }
@@ -2101,7 +2104,7 @@ int Renderer<R>::trace_rows(int y0, int y1, bool counting, std::string& err) {
         const int rows = std::min(rows_per_tile_, y1 - ty);
         const int S = rows * W * 4;
         MARK(KC_GEN);
-        k_gen<R><<<(S + 255) / 256, 256, 0, stream_>>>(sc_, levels_[0], ctr_, ty, rows);
+        k_gen<R><<<(S + 255) / 256, 256, 0, stream_>>>(sc_, levels_[0], ctr_, ty, rows, map);
         totals_.launches++;
         totals_.rays_primary += (unsigned long long)S;
         for (int l = 0; l < depth_eff_; l++) {
@@ -2131,7 +2134,7 @@ int Renderer<R>::trace_rows(int y0, int y1, bool counting, std::string& err) {
             MARK(KC_SHADE);
             k_shade<R><<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
                 sc_, levels_[l], spawn ? levels_[l + 1] : levels_[l], sq_, occl_[l], ctr_, l, spawn ? 1 : 0,
-                (counting && l == 0) ? ids_ : nullptr, ty);
+                (counting && l == 0) ? ids_ : nullptr, ty, map);
             totals_.launches += 2;
             for (int li = 0; li < sc_.n_lights; li++) {    // per light: its shadow rays share a pivot (or an axis)
                 const bool axis = frame_light_[li].family == CULL_AXIS;
@@ -2168,7 +2171,7 @@ int Renderer<R>::trace_rows(int y0, int y1, bool counting, std::string& err) {
             totals_.launches++;
         }
         MARK(KC_PIXELS);
-        k_pixels<R><<<(rows * W + 255) / 256, 256, 0, stream_>>>(sc_, samples_, sample_cap_, frame_, ty, rows);
+        k_pixels<R><<<(rows * W + 255) / 256, 256, 0, stream_>>>(sc_, samples_, sample_cap_, frame_target_ ? (uchar4*)frame_target_ : frame_, ty, rows, map);
         totals_.launches++;
     }
     MARK(-1);

@@ -25,13 +25,33 @@ struct TraceTotals {                   // summed over the tiles a device rendere
     int error = 0, overflow = 0;
 };
 
+// Which image rows a device renders.  The image is cut into bands of `band_rows` rows dealt round-robin to `n_parts`
+// devices; device `part` sees its own bands as one contiguous run of VIRTUAL rows, so a frame is a few large launches
+// per device however fine the interleave is.  n_parts == 1 is the identity.
+struct RowMap {
+    int band_rows = 1, n_parts = 1, part = 0;
+    __host__ __device__ int actual(int v) const {
+        return n_parts == 1 ? v : ((v / band_rows) * n_parts + part) * band_rows + v % band_rows;
+    }
+    // number of virtual rows of this part for an image of H rows
+    int count(int H) const {
+        if (n_parts == 1) return H;
+        const int full = H / band_rows, rest = H % band_rows;      // full bands + one partial band (index `full`)
+        int rows = (full / n_parts + (full % n_parts > part ? 1 : 0)) * band_rows;
+        if (rest && full % n_parts == part) rows += rest;
+        return rows;
+    }
+};
+
 class IRenderer {
 public:
     virtual ~IRenderer() {}
     // copy the converted scene to this device; (re)allocate queues for rows_per_tile rows
     virtual int upload(const HostScene& S, std::string& err) = 0;
-    // enqueue the kernels for image rows [y0, y1) on this device's stream (no host sync)
-    virtual int trace_rows(int y0, int y1, bool counting, std::string& err) = 0;
+    // enqueue the kernels for virtual rows [v0, v1) of `map` on this device's stream (no host sync)
+    virtual int trace_rows(int v0, int v1, const RowMap& map, bool counting, std::string& err) = 0;
+    // where k_pixels stores: this device's own frame (default) or a peer-mapped frame of the gathering device
+    virtual void set_frame_target(uint8_t* target) = 0;
     // after the stream is synchronised: fetch counters accumulated since reset_totals()
     virtual int fetch_totals(TraceTotals& out, std::string& err) = 0;
     virtual void reset_totals() = 0;

@@ -11,6 +11,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libgmlrt.so")
 
+IPC_HANDLE_BYTES = 64
 PRECISION_F32 = 0
 PRECISION_F64_PARITY = 1
 
@@ -44,7 +45,7 @@ class GmlrtError(RuntimeError):
         self.code = code
 
 
-EXPORTS = ("gmlrt_measure_fp32_tflops", "gmlrt_set_profiling", "gmlrt_set_partition", "gmlrt_frame_device", "gmlrt_create", "gmlrt_render", "gmlrt_upload", "gmlrt_trace", "gmlrt_download", "gmlrt_set_counting",
+EXPORTS = ("gmlrt_frame_ipc_export", "gmlrt_frame_ipc_attach", "gmlrt_measure_fp32_tflops", "gmlrt_set_profiling", "gmlrt_set_partition", "gmlrt_frame_device", "gmlrt_create", "gmlrt_render", "gmlrt_upload", "gmlrt_trace", "gmlrt_download", "gmlrt_set_counting",
            "gmlrt_primary_hits", "gmlrt_stream", "gmlrt_last_error", "gmlrt_destroy", "gmlrt_blob_version", "gmlrt_build_info")
 
 _lib = None
@@ -71,6 +72,8 @@ def load():
         L.gmlrt_stream.restype, L.gmlrt_stream.argtypes = p, [p]
         L.gmlrt_set_partition.restype, L.gmlrt_set_partition.argtypes = i, [p, i, i]
         L.gmlrt_frame_device.restype, L.gmlrt_frame_device.argtypes = p, [p]
+        L.gmlrt_frame_ipc_export.restype, L.gmlrt_frame_ipc_export.argtypes = i, [p, p, sz]
+        L.gmlrt_frame_ipc_attach.restype, L.gmlrt_frame_ipc_attach.argtypes = i, [p, p, sz]
         L.gmlrt_last_error.restype, L.gmlrt_last_error.argtypes = ctypes.c_char_p, [p]
         L.gmlrt_destroy.restype, L.gmlrt_destroy.argtypes = None, [p]
         L.gmlrt_blob_version.restype, L.gmlrt_blob_version.argtypes = i, []
@@ -156,6 +159,20 @@ class Context:
 
     def set_partition(self, part, n_parts):
         self._check(self._L.gmlrt_set_partition(self._h, part, n_parts))
+
+    def frame_ipc_export(self):
+        """-> 64-byte CUDA IPC handle of this context's frame (after upload)."""
+        buf = ctypes.create_string_buffer(IPC_HANDLE_BYTES)
+        self._check(self._L.gmlrt_frame_ipc_export(self._h, buf, IPC_HANDLE_BYTES))
+        return buf.raw
+
+    def frame_ipc_attach(self, handle):
+        """Store finished rows straight into another process's frame (NVLink peer mapping); None detaches."""
+        if handle is None:
+            self._check(self._L.gmlrt_frame_ipc_attach(self._h, None, 0))
+        else:
+            buf = ctypes.create_string_buffer(bytes(handle), IPC_HANDLE_BYTES)
+            self._check(self._L.gmlrt_frame_ipc_attach(self._h, buf, IPC_HANDLE_BYTES))
 
     @property
     def frame_device_ptr(self):

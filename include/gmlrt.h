@@ -216,14 +216,22 @@ int gmlrt_trace(gmlrt_ctx*, gmlrt_stats* stats /* nullable */);
 int gmlrt_download(gmlrt_ctx*, uint8_t* rgba, size_t rgba_bytes);
 
 /* Multi-process sharding (one process per GPU, e.g. under torchrun): this context renders only the
- * row bands  part, part + n_parts, ...  of the frame and leaves the other rows zero, so that the
- * per-process frames can be summed / gathered by the caller (NCCL, or peer copies).  Call before
+ * row bands (8 rows each)  part, part + n_parts, ...  of the frame and leaves the other rows zero, so that the
+ * per-process frames can be summed / gathered by the caller (NCCL), or stored into one frame (gmlrt_frame_ipc_*).  Call before
  * gmlrt_upload.  The default (0, 1) renders the whole frame.                                     */
 int gmlrt_set_partition(gmlrt_ctx*, int part, int n_parts);
 
 /* Device pointer of the RGBA8 frame on devices[0] (valid after gmlrt_upload), for callers that
  * keep the raster on the GPU.                                                                    */
 void* gmlrt_frame_device(gmlrt_ctx*);
+
+/* One process per GPU without a collective: the gathering process exports its frame (after gmlrt_upload; the frame
+ * keeps its address while width x height is unchanged), the others attach it, and from then on their pixel kernel
+ * stores finished rows straight into that frame over NVLink (CUDA IPC peer mapping).  The caller orders "all
+ * producers finished" before it reads the frame (a barrier).  attach(NULL, 0) detaches.                           */
+#define GMLRT_IPC_HANDLE_BYTES 64
+int gmlrt_frame_ipc_export(gmlrt_ctx*, void* handle, size_t handle_bytes);
+int gmlrt_frame_ipc_attach(gmlrt_ctx*, const void* handle, size_t handle_bytes);
 
 /* Enable (1) / disable (0) the counting kernels that fill the ray and flop fields of
  * gmlrt_stats; counting costs a few percent, so timed runs leave it off.              */

@@ -110,6 +110,36 @@ def test_tiling_does_not_change_the_raster(ctx64):
     assert np.array_equal(whole, tiled)
 
 
+@pytest.mark.parametrize("n_parts", [2, 3, 8])
+def test_row_band_partitions_tile_the_frame(ctx64, n_parts):
+    """gmlrt_set_partition: part k renders the 8-row bands k, k + n, ... as one run of virtual rows and leaves the
+    other rows zero; the parts are disjoint and their sum is the unpartitioned raster, byte for byte (the height
+    is not a multiple of the band so the last band is partial).  Primary ids gather the same way."""
+    from go_raytracer_b200 import bands
+    blob = scenes.to_blob(scenes.mixed(96, 77, grid=(3, 3, 3), depth=3))
+    whole, _ = ctx64.render(blob)
+    ids_whole = ctx64.primary_hits()
+    total = np.zeros_like(whole, dtype=np.int32)
+    ids = np.full_like(ids_whole, -7)
+    c = cuda.Context((0,), cuda.PRECISION_F64_PARITY)
+    c.set_counting(True)
+    try:
+        for part in range(n_parts):
+            c.set_partition(part, n_parts)
+            img, st = c.render(blob)
+            rows = bands.rows_of(part, n_parts, 77)
+            assert st.rays_primary == 4 * 96 * len(rows)
+            mine = np.zeros(77, bool)
+            mine[rows] = True
+            assert not img[~mine].any()
+            total += img
+            ids[mine] = c.primary_hits()[mine]
+    finally:
+        c.close()
+    assert np.array_equal(total.astype(np.uint8), whole)
+    assert np.array_equal(ids, ids_whole)
+
+
 def test_streaming_scene_path_equals_resident(ctx64):
     blob = scenes.to_blob(scenes.mixed(160, 100, grid=(8, 8, 4), depth=3))
     resident, _ = ctx64.render(blob)
