@@ -46,24 +46,56 @@ def build_blob(args):
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    """SM clock + throttle reasons sampled DURING the timed region (NVML in-process: a sample is well under a
+    millisecond, so even a 50 ms region gets several; falls back to spawning nvidia-smi)."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.rows, self.stop_flag = index, [], False
+        self.nvml = self.handle = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            # torch's device ordinal -> NVML handle (CUDA_VISIBLE_DEVICES may renumber): match by PCI bus id
+            import torch
+            bus = torch.cuda.get_device_properties(index).pci_bus_id if hasattr(torch.cuda.get_device_properties(index), "pci_bus_id") else None
+            handle = None
+            if bus is not None:
+                for k in range(pynvml.nvmlDeviceGetCount()):
+                    hk = pynvml.nvmlDeviceGetHandleByIndex(k)
+                    if pynvml.nvmlDeviceGetPciInfo(hk).bus == bus:
+                        handle = hk
+                        break
+            self.handle = handle or pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.nvml = pynvml
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.nvml = None
+
+    def sample(self):
+        if self.nvml is not None:
+            n = self.nvml
+            mhz = float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM))
+            r = int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle))
+            flag = lambda bit: "Active" if r & bit else "Not Active"
+            self.rows.append([str(mhz), str(self.max_mhz), "", flag(n.nvmlClocksThrottleReasonHwSlowdown),
+                              flag(n.nvmlClocksThrottleReasonHwThermalSlowdown), flag(n.nvmlClocksThrottleReasonSwThermalSlowdown),
+                              flag(n.nvmlClocksThrottleReasonSwPowerCap)])
+        else:
+            out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                                 capture_output=True, text=True, timeout=5).stdout.strip()
+            if out:
+                self.rows.append([x.strip() for x in out.split(",")])
 
     def run(self):
         while not self.stop_flag:
             try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([x.strip() for x in out.split(",")])
+                self.sample()
             except Exception:
                 pass
-            time.sleep(0.2)
+            time.sleep(0.005 if self.nvml is not None else 0.2)
 
     def summary(self):
         self.stop_flag = True
@@ -73,7 +105,7 @@ class ClockSampler(threading.Thread):
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for k, n in enumerate(names) if any(r[3 + k].lower().startswith("active") for r in self.rows if len(r) > 3 + k)]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
-                "samples": len(self.rows)}
+                "samples": len(self.rows), "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
 def central_crop(w, h, cw, ch):
@@ -127,6 +159,7 @@ def main():
     ap.add_argument("--ref-crop", type=int, nargs=2, default=[240, 140])
     ap.add_argument("--cpu-crop", type=int, nargs=2, default=[480, 260])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--parts", type=int, default=1, help="diagnostic (1 GPU): render only part 0 of PARTS row-band parts, i.e. one rank's share of an N-GPU frame")
     ap.add_argument("--gather", default="ipc", choices=["ipc", "nccl"],
                     help="N > 1: ipc = every rank's pixel kernel stores into rank 0's frame over NVLink (CUDA IPC peer mapping); "
                          "nccl = reduce(SUM) of the disjoint bands")
@@ -162,7 +195,7 @@ def main():
     W, H = args.width, args.height
     prec = cuda.PRECISION_F32 if args.precision == "f32" else cuda.PRECISION_F64_PARITY
     ctx = cuda.Context((local_rank,), prec)
-    ctx.set_partition(rank, world)
+    ctx.set_partition(rank, world) if args.parts <= 1 or world > 1 else ctx.set_partition(0, args.parts)
     ctx.upload(blob)
     ext = torch.cuda.ExternalStream(ctx.stream, device=local_rank)
 
@@ -209,7 +242,7 @@ def main():
     rays_frame = int(counts[:4].sum())
     flops_credited_frame = float(counts[6]) * 1e3       # what the reference's all-pairs scan would execute
     flops_frame = float(counts[9]) * 1e3                # what the scan kernels execute: 14 per cull test + table flops per exact test
-    ctx.set_profiling(True)                             # an event before every launch: per-kernel-class device time, live
+    ctx.set_profiling(world == 1)                       # an event before every launch: per-kernel-class device time, live (the roofline is an N = 1 figure)
 
     for _ in range(max(args.warmup, 3)):
         step()
@@ -253,6 +286,7 @@ def main():
     pinned = torch.empty((H, W, 4), dtype=torch.uint8, pin_memory=True) if rank == 0 else None
 
     phase_ms = {"upload": 0.0, "trace": 0.0, "download": 0.0}
+    upload_each = []
 
     def e2e_step():
         ta = time.perf_counter()
@@ -263,6 +297,7 @@ def main():
             dist.barrier()                                  # every producer's stores have landed in rank 0's frame
         tc = time.perf_counter()
         phase_ms["upload"] += (tb - ta) * 1e3
+        upload_each.append((tb - ta) * 1e3)
         phase_ms["trace"] += (tc - tb) * 1e3
         if rank == 0:                                       # D2H of the step's result
             if dist is None:
@@ -277,6 +312,7 @@ def main():
     barrier()
     for k in phase_ms:
         phase_ms[k] = 0.0
+    upload_each.clear()
     t0 = time.perf_counter()
     e2e_steps = max(3, min(args.steps, 10))
     for _ in range(e2e_steps):
@@ -319,6 +355,9 @@ def main():
         achieved = cull_flops[2] * args.steps / (class_ms[2] * 1e-3) / 1e12
         dom_launch_ms = class_ms[2] / max(class_launches[2], 1)
         dom_flops_launch = cull_flops[2] * args.steps / max(class_launches[2], 1)
+    elif world > 1:                         # per-kernel events are an N = 1 tool: quote the executed flops of the whole frame over N GPUs
+        dom_kernel = f"whole frame on {world} GPUs (per-kernel timing is off at N > 1; see the N = 1 line)"
+        achieved, dom_launch_ms, dom_flops_launch = flops_frame / (ms_step * 1e-3) / 1e12, ms_step, flops_frame
     else:                                   # no single FP32-bound kernel dominates: quote the whole scan
         achieved, dom_launch_ms, dom_flops_launch = scan_tflops, scan_ms / max(scan_launches, 1), flops_frame * args.steps / max(scan_launches, 1)
     traffic = None
@@ -331,7 +370,8 @@ def main():
         "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_step, "frame_ms": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": args.precision, "data": "synthetic",
-        "config": {"workload": f"{args.config} {W}x{H} depth {args.depth}, 4 spp, {cst.n_leaves} leaves", "precision": args.precision,
+        "config": {"workload": f"{args.config} {W}x{H} depth {args.depth}, 4 spp, {cst.n_leaves} leaves" +
+                               (f" - DIAGNOSTIC: part 0 of {args.parts} only" if world == 1 and args.parts > 1 else ""), "precision": args.precision,
                    "l2": "inputs larger than L2: the per-level ray queues of one frame are GBs, no flush needed",
                    "parallelism": (f"8-row bands dealt round-robin over {world} GPU(s), scene replicated, " +
                                    ("finished rows stored by k_pixels into GPU 0's frame over NVLink (CUDA IPC), no collective" if use_ipc
@@ -341,7 +381,7 @@ def main():
         "gpu_launches": launches,
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "frame_ms": e2e_ms, "h2d_bytes_per_step": len(blob), "d2h_bytes_per_step": W * H * 4,
-                "phase_ms": {k: v / e2e_steps for k, v in phase_ms.items()}},
+                "phase_ms": {k: v / e2e_steps for k, v in phase_ms.items()}, "upload_ms_each": [round(x, 3) for x in upload_each]},
         "kernel_ms_per_frame": {names[k]: class_ms[k] / args.steps for k in range(9)},
         "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak if fp32_peak else None,
                      "traffic": traffic,

@@ -19,6 +19,7 @@
 // This header is compiled twice: render_f64.cu (R = double, -fmad=false: reference operation
 // order, bit-parity mode) and render_f32.cu (R = float, FMA contraction: throughput mode).
 #pragma once
+#include <chrono>
 #include <cstdint>
 #include <cstdio>
 #include <algorithm>
@@ -808,7 +809,7 @@ struct CandQueue {
     int* ray;        // [cap] ray index within the launch's ray source
     int* obj;        // [cap] object index; k_exact_closest overwrites it with the hit code (or -1)
     void* t;         // [cap] R: T of the hit (closest only)
-    int* count;      // entries appended by the current launch
+    int* count;      // [0] entries appended by the current launch, [1] blocks of rays handed out beyond the first wave
     int cap;
 };
 
@@ -859,7 +860,12 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
         if (tid == 0) stage_cull(table, 0, NP, tab, &bar[0]);
         mbar_wait(&bar[0], 0);
     }
-    for (int blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
+    // blocks of rays are handed out dynamically (their cost varies with what survives the packet stage): a CTA starts
+    // on block blockIdx.x and fetches the following ones from a device counter, one iteration ahead
+    __shared__ int next_blk[2];
+    int iter = 0;
+    for (int blk = blockIdx.x; blk < nblocks; blk = next_blk[iter++ & 1]) {
+        if (tid == 0) next_blk[iter & 1] = (int)gridDim.x + atomicAdd(cq.count + 1, 1);
         const int ray0 = blk * RAYS_PER_BLOCK;
         CullRay<R, FAMILY> cr[RPT];
         bool active[RPT];
@@ -980,6 +986,7 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
         }
         fine = warp_sum_u64(fine); packet = warp_sum_u64(packet);
         if (lane == 0) { atomicAdd(&ctr->cull_tests[FAMILY], fine); if (packet) atomicAdd(&ctr->packet_tests, packet); }
+        __syncthreads();                                       // next_blk[iter & 1] is visible; slot (iter + 1) & 1 is free again
     }
 }
 
@@ -1777,8 +1784,12 @@ template <typename R>
 int Renderer<R>::upload(const HostScene& S, std::string& err) {
     CU_TRY(cudaSetDevice(dev_));
     if (S.depth > GMLRT_MAX_DEPTH) { err = "recursion depth above GMLRT_MAX_DEPTH"; return GMLRT_E_UNSUPPORTED; }
+    const bool dbg_t = getenv("GMLRT_DEBUG_UPLOAD") != nullptr;
+    auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t_a = now();
     CU_TRY(cudaStreamSynchronize(stream_));
     free_scene();
+    const double t_b = now();
     tile_shrink_ = 0;
     // Device layout.  Objects (what closestHit / inShadow scan): the plain leaves, stably sorted by kind so that
     // equal kinds keep scan order, then the CSG objects.  After them, the member leaves of the CSG objects.  Every
@@ -1914,7 +1925,9 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
         shadow_counts_ = reinterpret_cast<int*>(p);
         CU_TRY(cudaMemsetAsync(shadow_counts_, 0, std::max<size_t>(S.lights.size(), 1) * sizeof(int), stream_));
     }
+    const double t_c = now();
     CU_TRY(cudaStreamSynchronize(stream_));      // host vectors go out of scope
+    const double t_d = now();
 
     // frame + ids
     const size_t px = (size_t)S.width * S.height;
@@ -1924,7 +1937,10 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
         CU_TRY(cudaMalloc(&frame_, px * sizeof(uchar4)));
         frame_px_ = px;
     }
-    return plan_tiles(S, err);
+    const int prc = plan_tiles(S, err);
+    if (dbg_t) fprintf(stderr, "[gmlrt upload dev %d] sync+free %.3f  host build + enqueue copies %.3f  copy sync %.3f  frame+plan_tiles %.3f ms\n",
+                       dev_, t_b - t_a, t_c - t_b, t_d - t_c, now() - t_d);
+    return prc;
 }
 
 // One 4-value record per object for the cull phase of the scan kernels (see "two-phase scan"): the bounding
@@ -2110,7 +2126,7 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
         for (int l = 0; l < depth_eff_; l++) {
             const int cap_blocks = (levels_[l].cap + SHADE_THREADS - 1) / SHADE_THREADS;
             const int exact_grid = sms_ * 16;
-            CU_TRY(cudaMemsetAsync(cq_.count, 0, sizeof(int), stream_));
+            CU_TRY(cudaMemsetAsync(cq_.count, 0, 2 * sizeof(int), stream_));
             ClosestSource<R> csrc{levels_[l]};
             if (l == 0) {                                  // camera rays: PIVOT family through the eye, robust re-tests in f32
                 MARK(KC_CLOSEST_PRIMARY);
@@ -2139,7 +2155,7 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             for (int li = 0; li < sc_.n_lights; li++) {    // per light: its shadow rays share a pivot (or an axis)
                 const bool axis = frame_light_[li].family == CULL_AXIS;
                 ShadowSource<R> ssrc{sq_, li * sq_.per_light};
-                CU_TRY(cudaMemsetAsync(cq_.count, 0, sizeof(int), stream_));
+                CU_TRY(cudaMemsetAsync(cq_.count, 0, 2 * sizeof(int), stream_));
                 MARK(KC_SORT);
                 if (sort_clear_) { CU_TRY(cudaMemsetAsync(sort_hist_, 0, SORT_BINS_MAX * sizeof(int), stream_)); sort_clear_ = false; }
                 k_sort_hist<R><<<sms_ * 4, SORT_THREADS, 0, stream_>>>(sq_, li, sort_shift_, sort_nb_, sort_hist_);
