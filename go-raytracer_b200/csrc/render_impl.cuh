@@ -70,6 +70,7 @@ template <typename R> struct DevScene {
     const R* fpool; const int* itab; const uint32_t* code;
     int n_fpool, n_itab;
     int W, H, depth;
+    int key_shift, key_k;          // sort key of a spawned ray: (leaf >> key_shift) * 6 k^2 + cube-map cell of its direction
     double vw, vh;
     R ambient[3], bg0[3], bg1[3];
 };
@@ -722,7 +723,9 @@ __device__ __forceinline__ void cull_window_indirect(const R* sm, const uint16_t
 // What the rays of one warp (RPT per lane) have in common, for the packet stage of the PIVOT / AXIS families:
 //   PIVOT  a double cone around `axis` (unit) with half-angle theta that contains every ray's line through the pivot
 //   AXIS   a disc (centre mu, mv; radius rho) in the plane orthogonal to the common direction that contains every ray
-template <typename R> struct WarpBound { R ax, ay, az, cos_t, sin_t; bool usable; };
+//   GENERAL (rays sorted by origin object and direction cell) a sphere (centre o, radius rho) that holds every origin
+//          and a cone around `axis` with half-angle theta that holds every direction
+template <typename R> struct WarpBound { R ax, ay, az, cos_t, sin_t; bool usable; R ox, oy, oz, rho; };
 
 template <typename R>
 __device__ __forceinline__ R warp_sum(R v) { for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o); return v; }
@@ -771,7 +774,38 @@ __device__ __forceinline__ WarpBound<R> warp_bound(const CullRay<R, CULL_AXIS> (
     return b;
 }
 template <typename R, int RPT>
-__device__ __forceinline__ WarpBound<R> warp_bound(const CullRay<R, CULL_GENERAL> (&)[RPT], const bool (&)[RPT]) { WarpBound<R> b = {}; b.usable = false; return b; }
+__device__ __forceinline__ WarpBound<R> warp_bound(const CullRay<R, CULL_GENERAL> (&cr)[RPT], const bool (&active)[RPT]) {
+    R sx = R(0), sy = R(0), sz = R(0), qx = R(0), qy = R(0), qz = R(0), cnt = R(0);
+#pragma unroll
+    for (int r = 0; r < RPT; r++) if (active[r]) {
+        sx += cr[r].dx; sy += cr[r].dy; sz += cr[r].dz;
+        qx += cr[r].o2x; qy += cr[r].o2y; qz += cr[r].o2z; cnt += R(1);          // o2 = -2 o
+    }
+    sx = warp_sum(sx); sy = warp_sum(sy); sz = warp_sum(sz);
+    qx = warp_sum(qx); qy = warp_sum(qy); qz = warp_sum(qz); cnt = warp_sum(cnt);
+    const R len = gm<R>::sqrt(fma_(sx, sx, fma_(sy, sy, sz * sz)));
+    WarpBound<R> b;
+    b.usable = len > R(0) && cnt > R(0);
+    const R inv = b.usable ? R(1) / len : R(0), icnt = b.usable ? R(-0.5) / cnt : R(0);
+    b.ax = sx * inv; b.ay = sy * inv; b.az = sz * inv;
+    b.ox = qx * icnt; b.oy = qy * icnt; b.oz = qz * icnt;
+    R c = R(1), d2 = R(0);
+#pragma unroll
+    for (int r = 0; r < RPT; r++) if (active[r]) {
+        const R d = fma_(cr[r].dx, b.ax, fma_(cr[r].dy, b.ay, cr[r].dz * b.az));
+        c = d < c ? d : c;
+        const R ex = fma_(R(-0.5), cr[r].o2x, -b.ox), ey = fma_(R(-0.5), cr[r].o2y, -b.oy), ez = fma_(R(-0.5), cr[r].o2z, -b.oz);
+        const R e = fma_(ex, ex, fma_(ey, ey, ez * ez));
+        d2 = e > d2 ? e : d2;
+    }
+    c = warp_min(c) - R(1e-5);
+    d2 = warp_max(d2);
+    b.cos_t = c;
+    b.sin_t = gm<R>::sqrt(R(1) - (c < R(1) ? c * c : R(1))) + R(1e-5);
+    b.rho = gm<R>::sqrt(d2) * R(1.0001) + R(1e-6) * (gm<R>::abs(b.ox) + gm<R>::abs(b.oy) + gm<R>::abs(b.oz) + R(1));
+    b.usable = b.usable && c > R(0.2);                   // NaN rays make c NaN: not usable, the plain scan handles them
+    return b;
+}
 
 // may object record L be hit by ANY ray inside the warp's bound?  (conservative)
 template <typename R> __device__ __forceinline__ bool packet_survives(const Cull4<R>& L, const WarpBound<R>& b, CullRay<R, CULL_PIVOT>*) {
@@ -789,7 +823,23 @@ template <typename R> __device__ __forceinline__ bool packet_survives(const Cull
     const R rr = gm<R>::sqrt(-L.z) * R(1.0001) + b.cos_t;      // sqrt(R^2 + margin) + rho; -L.z = +inf for unbounded objects
     return !(fma_(du, du, dv * dv) > rr * rr);
 }
-template <typename R> __device__ __forceinline__ bool packet_survives(const Cull4<R>&, const WarpBound<R>&, CullRay<R, CULL_GENERAL>*) { return true; }
+// GENERAL record (C, K = |C|^2 - R^2 - margin).  A ray from o (|o - oc| <= rho) that hits the sphere (C, R) at T > 0 is,
+// moved to oc, a ray that hits a sphere of the same radius whose centre is within rho of C: so test the sphere
+// (C, R + rho) against the cone of directions from oc - forward only, the reference accepts T > 0 alone.
+template <typename R> __device__ __forceinline__ bool packet_survives(const Cull4<R>& L, const WarpBound<R>& b, CullRay<R, CULL_GENERAL>*) {
+    const R cc = fma_(L.x, L.x, fma_(L.y, L.y, L.z * L.z));
+    const R r2 = fma_(cc, R(9.5367431640625e-7), cc - L.k);       // R^2 + margins + 2^-20 |C|^2 for the cancellation in |C|^2 - K
+    const R rr = gm<R>::sqrt(r2) * R(1.0001) + b.rho;
+    const R rr2 = rr * rr;
+    const R px = L.x - b.ox, py = L.y - b.oy, pz = L.z - b.oz;
+    const R pp = fma_(px, px, fma_(py, py, pz * pz));
+    if (!(rr2 < pp)) return true;                        // an origin may be inside the sphere; unbounded object; NaN / padding
+    const R inv = R(1) / pp;
+    const R s2 = rr2 * inv;
+    const R sa = gm<R>::sqrt(s2) * R(1.0001), ca = gm<R>::sqrt(R(1) - s2);
+    const R c = fma_(px, b.ax, fma_(py, b.ay, pz * b.az)) * gm<R>::sqrt(inv);      // signed: behind the packet = miss
+    return !(c < b.cos_t * ca - b.sin_t * sa - R(1e-5));      // angle(C - oc, axis) <= theta + alpha
+}
 
 constexpr int PCHUNK = 1024;                // objects per packet pass = survivor list capacity per warp (uint16 indices)
 constexpr size_t SURV_BYTES = (size_t)(SCAN_THREADS / 32) * PCHUNK * sizeof(uint16_t);
@@ -815,16 +865,19 @@ struct CandQueue {
 
 template <typename R> struct ClosestSource {                 // rays of one recursion level
     Level<R> lv;
+    const int* perm;                                          // levels >= 1: rays by (origin object, direction cell); null = queue order
+    __device__ __forceinline__ int id(int i) const { return perm ? perm[i] : i; }
     __device__ __forceinline__ void load(int i, Ray<R>& out) const {
         const size_t cap = (size_t)lv.cap;
-        out.ox = lv.ray[i]; out.oy = lv.ray[cap + i]; out.oz = lv.ray[2 * cap + i];
-        out.dx = lv.ray[3 * cap + i]; out.dy = lv.ray[4 * cap + i]; out.dz = lv.ray[5 * cap + i];
+        const int k = id(i);
+        out.ox = lv.ray[k]; out.oy = lv.ray[cap + k]; out.oz = lv.ray[2 * cap + k];
+        out.dx = lv.ray[3 * cap + k]; out.dy = lv.ray[4 * cap + k]; out.dz = lv.ray[5 * cap + k];
     }
-    __device__ __forceinline__ int id(int i) const { return i; }
     __device__ __forceinline__ void init(int i) const {       // no hit yet
-        lv.hit[i] = -1;
-        reinterpret_cast<typename BitsOf<R>::type*>(lv.t)[i] = ~(typename BitsOf<R>::type)0;
-        lv.order[i] = 0x7fffffff;
+        const int k = id(i);
+        lv.hit[k] = -1;
+        reinterpret_cast<typename BitsOf<R>::type*>(lv.t)[k] = ~(typename BitsOf<R>::type)0;
+        lv.order[k] = 0x7fffffff;
     }
 };
 
@@ -935,7 +988,7 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
                     }
                 }
             };
-            if (FAMILY != CULL_GENERAL && wb.usable) {
+            if (wb.usable) {
                 // packet stage: the lanes test 32 objects at a time against the warp's bound; the survivors' indices
                 // (relative to this chunk) are compacted into the warp's list, then only those are tested per ray
                 for (int p0 = base; p0 < end; p0 += PCHUNK) {
@@ -997,13 +1050,39 @@ __device__ __forceinline__ void warp_add(unsigned long long* dst, unsigned long 
 
 constexpr int EXACT_THREADS = 128;
 
+// The exact kernels come in three flavours so that the common case runs at full occupancy: ALL kinds through
+// exact_hit (a call; 96-128 registers because of the CSG span lists), SPHERES only with the test inlined (the
+// candidates of other kinds are skipped) and REST = every kind but spheres, through exact_hit.  A scene of spheres
+// launches SPHERES alone, a mixed scene SPHERES then REST over the same candidate list.
+enum ExactKinds { EXACT_ALL = 0, EXACT_SPHERES = 1, EXACT_REST = 2 };
+
+template <typename R, int KINDS>
+__device__ __forceinline__ bool exact_hit_kinds(const DevScene<R>& sc, int obj, const Ray<R>& w, R& t, int& code) {
+    if constexpr (KINDS == EXACT_SPHERES) {
+        Mat34<R> M;
+        load_w2o(sc.w2o, obj, M);
+        Ray<R> o;
+        to_object(M.m, w, o);
+        int face = 0;
+        code = obj;
+        return hit_sphere<R>(o, t, face);
+    } else {
+        return exact_hit<R, false>(sc, obj, w, nullptr, 0, 0, t, code);
+    }
+}
+// does this flavour own candidate object `obj`?  (objects are sorted by kind: spheres first)
+template <int KINDS> __device__ __forceinline__ bool exact_owns(int obj, int n_spheres) {
+    return KINDS == EXACT_ALL || (KINDS == EXACT_SPHERES ? obj < n_spheres : obj >= n_spheres);
+}
+
 // closestHit (raytracer.go:469-483): strictly smaller T wins, equal T keeps the object that comes first in scan
 // order.  Three passes over the candidates: (1) exact test, T of a hit into the queue and atomicMin into the ray's
 // record (hits have T > 0, so the bit pattern orders like the value); (2) among the hits that have the ray's
 // smallest T, atomicMin of the scan index; (3) the winner writes its hit code.
-template <typename R, bool ROBUST, bool COUNT>
+template <typename R, bool ROBUST, bool COUNT, int KINDS>
 __global__ void __launch_bounds__(EXACT_THREADS) k_exact_closest(const __grid_constant__ DevScene<R> sc, const __grid_constant__ Level<R> lv,
                                                                 const __grid_constant__ CandQueue cq, Counters* ctr) {
+    static_assert(!ROBUST || KINDS == EXACT_ALL, "the robust camera-ray test has one flavour");
     typedef typename BitsOf<R>::type UB;
     const int count = min(*cq.count, cq.cap);
     UB* tbest = reinterpret_cast<UB*>(lv.t);
@@ -1011,6 +1090,8 @@ __global__ void __launch_bounds__(EXACT_THREADS) k_exact_closest(const __grid_co
     unsigned long long n_exact = 0, n_flops = 0;
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
         const int ri = cq.ray[k], obj = cq.obj[k];
+        if (KINDS == EXACT_REST && obj < 0) continue;          // a sphere candidate the SPHERES pass has already resolved to a miss
+        if (KINDS != EXACT_ALL && obj < sc.n_leaves && !exact_owns<KINDS>(obj, sc.kind_begin[K_SPHERE + 1])) continue;
         int code = -1; R t = R(0);
         if (obj < sc.n_leaves) {                               // a padding record can only be reached by a NaN ray
             if (COUNT) { n_exact++; n_flops += (unsigned)sc.obj_flops[obj]; }
@@ -1018,7 +1099,10 @@ __global__ void __launch_bounds__(EXACT_THREADS) k_exact_closest(const __grid_co
             const size_t cap = (size_t)lv.cap;
             w.ox = lv.ray[ri]; w.oy = lv.ray[cap + ri]; w.oz = lv.ray[2 * cap + ri];
             w.dx = lv.ray[3 * cap + ri]; w.dy = lv.ray[4 * cap + ri]; w.dz = lv.ray[5 * cap + ri];
-            if (exact_hit<R, ROBUST>(sc, obj, w, lv.ray64, lv.cap, ri, t, code)) atomicMin(&tbest[ri], BitsOf<R>::of(t));
+            bool h;
+            if constexpr (ROBUST) h = exact_hit<R, true>(sc, obj, w, lv.ray64, lv.cap, ri, t, code);
+            else h = exact_hit_kinds<R, KINDS>(sc, obj, w, t, code);
+            if (h) atomicMin(&tbest[ri], BitsOf<R>::of(t));
             else code = -1;
         }
         cq.obj[k] = code; ct[k] = t;
@@ -1060,21 +1144,21 @@ __global__ void __launch_bounds__(256) k_closest_pick(const __grid_constant__ De
 // one occludes when  shadowHit.T * |ray.Direction| < distToLight  (:424).  The answer does not depend on the
 // order objects are visited in; `first` keeps the smallest scan index of an occluder so that COUNT can credit the
 // tests the reference itself would have run up to its first occluder.
-template <typename R, bool COUNT>
+template <typename R, bool COUNT, int KINDS>
 __global__ void __launch_bounds__(EXACT_THREADS) k_exact_shadow(const __grid_constant__ DevScene<R> sc, const __grid_constant__ ShadowQueue<R> sq,
                                                                int base, const __grid_constant__ CandQueue cq, Counters* ctr) {
     const int count = min(*cq.count, cq.cap);
     unsigned long long n_exact = 0, n_flops = 0;
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
         const int q = base + cq.ray[k], obj = cq.obj[k];
-        if (obj >= sc.n_leaves || obj == sq.skip[q]) continue;
+        if (obj >= sc.n_leaves || !exact_owns<KINDS>(obj, sc.kind_begin[K_SPHERE + 1]) || obj == sq.skip[q]) continue;
         if (!COUNT && sq.first[q] != 0x7fffffff) continue;     // already occluded (a stale read only costs a test)
         if (COUNT) { n_exact++; n_flops += (unsigned)sc.obj_flops[obj]; }
         Ray<R> w;
         const R* rec = sq.q + (size_t)q * 8;
         w.ox = rec[0]; w.oy = rec[1]; w.oz = rec[2]; w.dx = rec[3]; w.dy = rec[4]; w.dz = rec[5];
         R t; int code;
-        if (!exact_hit<R, false>(sc, obj, w, nullptr, 0, 0, t, code)) continue;
+        if (!exact_hit_kinds<R, KINDS>(sc, obj, w, t, code)) continue;
         if (t * rec[7] < rec[6]) atomicMin(&sq.first[q], sc.scan_of[obj]);   // T * |incoming direction| < distance to the light
     }
     if (COUNT) { warp_add(&ctr->exact_tests, n_exact); warp_add(&ctr->exact_flops, n_flops); }
@@ -1105,22 +1189,42 @@ __global__ void __launch_bounds__(SORT_THREADS) k_sort_hist(const __grid_constan
     for (int b = threadIdx.x; b < nb; b += SORT_THREADS) if (h[b]) atomicAdd(&hist[b], h[b]);
 }
 
-// exclusive prefix of hist[0..nb) into cursor[0..nb); hist is cleared for the next use (one block)
+// exclusive prefix of hist[0..nb) into cursor[0..nb); hist is cleared for the next use (one block; tiles of 4096
+// bins read as int4, so the 55k bins of the key sort are 14 coalesced rounds)
 static __global__ void __launch_bounds__(1024) k_sort_scan(int nb, int* hist, int* cursor) {
-    __shared__ int part[1024];
-    const int per = (nb + 1023) / 1024, b0 = threadIdx.x * per;
-    int sum = 0;
-    for (int b = b0; b < min(nb, b0 + per); b++) sum += hist[b];
-    part[threadIdx.x] = sum;
+    __shared__ int warp_tot[32];
+    __shared__ int carry_s;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (tid == 0) carry_s = 0;
     __syncthreads();
-    for (int off = 1; off < 1024; off <<= 1) {
-        const int v = threadIdx.x >= off ? part[threadIdx.x - off] : 0;
+    for (int tile = 0; tile < nb; tile += 4096) {
+        const int b = tile + 4 * tid;
+        int4 v = make_int4(0, 0, 0, 0);
+        if (b + 3 < nb) v = *reinterpret_cast<const int4*>(hist + b);
+        else { if (b < nb) v.x = hist[b]; if (b + 1 < nb) v.y = hist[b + 1]; if (b + 2 < nb) v.z = hist[b + 2]; }
+        const int mine = v.x + v.y + v.z + v.w;
+        int incl = mine;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) { const int u = __shfl_up_sync(0xffffffffu, incl, off); if (lane >= off) incl += u; }
+        if (lane == 31) warp_tot[wid] = incl;
         __syncthreads();
-        part[threadIdx.x] += v;
+        if (wid == 0) {
+            int t = warp_tot[lane], ti = t;
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) { const int u = __shfl_up_sync(0xffffffffu, ti, off); if (lane >= off) ti += u; }
+            warp_tot[lane] = ti - t;                       // exclusive prefix of the warp totals
+        }
+        __syncthreads();
+        const int carry = carry_s;
+        int run = carry + warp_tot[wid] + incl - mine;
+        if (b < nb) { cursor[b] = run; hist[b] = 0; } run += v.x;
+        if (b + 1 < nb) { cursor[b + 1] = run; hist[b + 1] = 0; } run += v.y;
+        if (b + 2 < nb) { cursor[b + 2] = run; hist[b + 2] = 0; } run += v.z;
+        if (b + 3 < nb) { cursor[b + 3] = run; hist[b + 3] = 0; } run += v.w;
+        __syncthreads();
+        if (tid == 1023) carry_s = run;                    // inclusive total through this tile
         __syncthreads();
     }
-    int run = part[threadIdx.x] - sum;
-    for (int b = b0; b < min(nb, b0 + per); b++) { cursor[b] = run; run += hist[b]; hist[b] = 0; }
 }
 
 template <typename R>
@@ -1139,6 +1243,53 @@ __global__ void __launch_bounds__(SORT_THREADS) k_sort_scatter(const __grid_cons
         for (int i = c * SORT_CHUNK + threadIdx.x; i < i1; i += SORT_THREADS)
             sq.perm[base + atomicAdd(&at[sort_bin(sq.skip[base + i], shift, nb)], 1)] = i;
         __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------ reflection / refraction rays by (origin object, direction cell)
+// Same idea for the rays k_shade spawns: in queue order a warp's rays leave whatever objects a strip of pixels shows, in
+// every direction; keyed by the object they leave and the cube-map cell of their direction (k_shade leaves the key in
+// the child's `hit` slot, which the cull kernel re-initialises anyway) a warp's rays start in one small region and
+// point into one cone, so the packet stage applies to them too.  Up to 2^17 bins: histogram and cursors in global
+// memory, one warp-aggregated atomic per distinct key of a warp.  The order inside a bin is not deterministic; the
+// result of a ray does not depend on which warp tests it.
+constexpr int KEY_BINS_MAX = 1 << 17;
+
+__device__ __forceinline__ void key_peers(int key, bool valid, unsigned& peers, int& rank, int& leader) {
+    const unsigned act = __ballot_sync(0xffffffffu, valid);
+    peers = 0; rank = 0; leader = 0;
+    if (!valid) return;
+    peers = __match_any_sync(act, key);
+    rank = __popc(peers & ((1u << (threadIdx.x & 31)) - 1u));
+    leader = __ffs(peers) - 1;
+}
+
+static __global__ void __launch_bounds__(256) k_keysort_hist(const int* keys, const int* n_ptr, int nb, int* hist) {
+    const int n = *n_ptr;
+    const int rounds = (n + gridDim.x * blockDim.x - 1) / (gridDim.x * blockDim.x);
+    for (int r = 0; r < rounds; r++) {                     // whole warps stay in the loop: match / ballot need them
+        const int i = (r * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
+        const bool valid = i < n;
+        const int key = valid ? min(max(keys[i], 0), nb - 1) : 0;
+        unsigned peers; int rank, leader;
+        key_peers(key, valid, peers, rank, leader);
+        if (valid && rank == 0) atomicAdd(&hist[key], __popc(peers));
+    }
+}
+
+static __global__ void __launch_bounds__(256) k_keysort_scatter(const int* keys, const int* n_ptr, int nb, int* cursor, int* perm) {
+    const int n = *n_ptr;
+    const int rounds = (n + gridDim.x * blockDim.x - 1) / (gridDim.x * blockDim.x);
+    for (int r = 0; r < rounds; r++) {
+        const int i = (r * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
+        const bool valid = i < n;
+        const int key = valid ? min(max(keys[i], 0), nb - 1) : 0;
+        unsigned peers; int rank, leader;
+        key_peers(key, valid, peers, rank, leader);
+        int at = 0;
+        if (valid && rank == 0) at = atomicAdd(&cursor[key], __popc(peers));
+        at = __shfl_sync(0xffffffffu, at, leader);
+        if (valid) perm[at + rank] = i;
     }
 }
 
@@ -1251,6 +1402,21 @@ __device__ __noinline__ bool run_surface(const DevScene<R>& sc, const DevSurface
 
 // ------------------------------------------------------------------ small vector helpers (Vec3, vec.go:23-116)
 template <typename R> struct V3 { R x, y, z; };
+// sort key of a spawned ray (see k_keysort_*)
+template <typename R> __device__ __forceinline__ int ray_sort_key(const DevScene<R>& sc, int leaf, const V3<R>& d) {
+    const R ax = gm<R>::abs(d.x), ay = gm<R>::abs(d.y), az = gm<R>::abs(d.z);
+    int face; R m, u, v;
+    if (ax >= ay && ax >= az) { face = d.x < R(0) ? 1 : 0; m = ax; u = d.y; v = d.z; }
+    else if (ay >= az) { face = d.y < R(0) ? 3 : 2; m = ay; u = d.x; v = d.z; }
+    else { face = d.z < R(0) ? 5 : 4; m = az; u = d.x; v = d.y; }
+    const int k = sc.key_k;
+    const R half = R(0.5) * (R)k, s = half / m;
+    int cu = (int)fma_(u, s, half), cv = (int)fma_(v, s, half);
+    cu = min(k - 1, max(0, cu)); cv = min(k - 1, max(0, cv));
+    if (cu & 1) cv = k - 1 - cv;                           // boustrophedon: consecutive cells of a face are neighbours
+    return (leaf >> sc.key_shift) * (6 * k * k) + (face * k + cu) * k + cv;
+}
+
 template <typename R> __device__ __forceinline__ V3<R> mk(R x, R y, R z) { V3<R> v = {x, y, z}; return v; }
 template <typename R> __device__ __forceinline__ V3<R> operator+(V3<R> a, V3<R> b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
 template <typename R> __device__ __forceinline__ V3<R> operator-(V3<R> a, V3<R> b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
@@ -1288,6 +1454,33 @@ __device__ __forceinline__ int warp_append(int* counter, bool want) {
     return want ? base + __popc(m & ((1u << lane) - 1u)) : -1;
 }
 
+// queue append with one atomic per CTA: every thread of the block must call it (block-uniform control flow).  All CTAs
+// of a launch append to the same counter; with one atomic per warp the wait for its return was 40% of k_shade's
+// stall samples (ncu r01c), a 256-thread CTA issues 8x fewer.  `scratch` = int[2][SHADE_WARPS + 1], toggled by `phase`.
+constexpr int SHADE_THREADS = 256, SHADE_WARPS = SHADE_THREADS / 32;
+constexpr int SHADE_LIGHTS_PER_ROUND = 6, SHADE_Q_REFL = 6, SHADE_Q_REFR = 7, SHADE_QUEUES = 8;   // queues reserved per round trip in k_shade
+__device__ __forceinline__ int block_append(int* counter, bool want, int (*scratch)[SHADE_WARPS + 1], int& phase, unsigned long long* tally = nullptr) {
+    int* s = scratch[phase & 1];
+    phase++;
+    const unsigned m = __ballot_sync(0xffffffffu, want);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (lane == 0) s[wid] = __popc(m);
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        const int c = lane < SHADE_WARPS ? s[lane] : 0;
+        int incl = c;
+#pragma unroll
+        for (int off = 1; off < SHADE_WARPS; off <<= 1) { const int u = __shfl_up_sync(0xffffffffu, incl, off); if (lane >= off) incl += u; }
+        const int total = __shfl_sync(0xffffffffu, incl, SHADE_WARPS - 1);
+        int base = 0;
+        if (lane == 0 && total) { base = atomicAdd(counter, total); if (tally) atomicAdd(tally, (unsigned long long)total); }
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (lane < SHADE_WARPS) s[lane] = base + incl - c;
+    }
+    __syncthreads();
+    return want ? s[wid] + __popc(m & ((1u << lane) - 1u)) : -1;
+}
+
 // direction to a light, distance, and its colour at P (spot falloff is an EXTENSION); false = unlit
 template <typename R>
 __device__ __forceinline__ bool light_at(const DevLight<R>& L, V3<R> P, V3<R>& ldir, R& dist, V3<R>& lcol) {
@@ -1311,7 +1504,6 @@ __device__ __forceinline__ bool light_at(const DevLight<R>& L, V3<R> P, V3<R>& l
 // ------------------------------------------------------------------ gen: camera rays (Render, raytracer.go:632-652)
 __constant__ gomath::PcgJump c_pcg_jump[160];   // affine maps advancing the PCG stream by 0..159 draws
 
-constexpr int SHADE_THREADS = 128;
 
 template <typename R>
 __global__ void __launch_bounds__(256) k_gen(DevScene<R> sc, Level<R> lv, Counters* ctr, int y0, int rows, RowMap map) {
@@ -1356,6 +1548,8 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
                                                          unsigned char* occl, Counters* ctr, int level, int spawn,
                                                          int32_t* ids, int y0, RowMap map) {
     const int n = ctr->count[level];
+    __shared__ int s_append[2][SHADE_QUEUES][SHADE_WARPS];
+    int append_phase = 0;
     for (int blk0 = blockIdx.x * blockDim.x; blk0 < n; blk0 += gridDim.x * blockDim.x) {   // uniform per block
     const int i = blk0 + threadIdx.x;
     const int cap = lv.cap;
@@ -1449,15 +1643,78 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
         rec[REC_INLEN * cap] = length(D);
         for (int k = 0; k < 6; k++) lv.child[k * cap + i] = R(0);
     }
-    // shadow queries, one per light that can reach P (inShadow :411-414)
-    for (int li = 0; li < sc.n_lights; li++) {
-        V3<R> ldir = mk(R(0), R(0), R(1)), lcol; R dist = R(0);
-        bool want = live && light_at(sc.lights[li], P, ldir, dist, lcol);
-        int slot = warp_append(&sq.count[li], want);
-        if (want) {
-            slot += li * sq.per_light;
+    // Children.  Every ray may append one shadow query per light that can reach P (inShadow :411-414), a reflection
+    // child (:512-529) and a refraction child (:532-556).  All queues of a block iteration are reserved in ONE round
+    // trip: per-warp counts go to shared memory, lane q of warp 0 scans queue q over the warps and issues its
+    // atomicAdd, so the atomics of the (up to 6 lights + 2 child kinds) queues are in flight together.
+    bool want_refl = false, want_refr = false;
+    V3<R> refr_d = mk(R(0), R(0), R(0)), refr_n = N;
+    if (spawn) {
+        want_refl = live && refl > R(0);
+        want_refr = live && transp > R(0);
+        if (want_refr) {                                                             // refract :438-450
+            R n1 = R(1), n2 = ior;
+            if (dot(D, refr_n) > R(0)) { R tmp = n1; n1 = n2; n2 = tmp; refr_n = refr_n * R(-1); }
+            const R ratio = n1 / n2;
+            const R cosI = -dot(refr_n, D);
+            const R sinT2 = ratio * ratio * (R(1) - cosI * cosI);
+            if (sinT2 > R(1)) want_refr = false;                                     // total internal reflection
+            else {
+                const R cosT = gm<R>::sqrt(R(1) - sinT2);
+                refr_d = D * ratio + refr_n * (ratio * cosI - cosT);                 // not re-normalised
+                if (refr_d.x == R(0) && refr_d.y == R(0) && refr_d.z == R(0)) want_refr = false;
+            }
+        }
+    }
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const unsigned lt = (1u << lane) - 1u;
+    for (int l0 = 0; l0 == 0 || l0 < sc.n_lights; l0 += SHADE_LIGHTS_PER_ROUND) {       // uniform
+        int (*s)[SHADE_WARPS] = s_append[append_phase & 1];
+        append_phase++;
+        unsigned wmask = 0;
+        for (int q = 0; q < SHADE_LIGHTS_PER_ROUND && l0 + q < sc.n_lights; q++) {
+            V3<R> ldir = mk(R(0), R(0), R(1)), lcol; R dist = R(0);
+            if (live && light_at(sc.lights[l0 + q], P, ldir, dist, lcol)) wmask |= 1u << q;
+        }
+        if (l0 == 0) wmask |= (want_refl ? 1u << SHADE_Q_REFL : 0u) | (want_refr ? 1u << SHADE_Q_REFR : 0u);
+#pragma unroll
+        for (int q = 0; q < SHADE_QUEUES; q++) {
+            const unsigned m = __ballot_sync(0xffffffffu, (wmask >> q) & 1u);
+            if (lane == 0) s[q][wid] = __popc(m);
+        }
+        __syncthreads();
+        if (wid == 0) {
+            const int q = lane;
+            int excl[SHADE_WARPS], total = 0;
+            if (q < SHADE_QUEUES) {
+#pragma unroll
+                for (int w = 0; w < SHADE_WARPS; w++) { excl[w] = total; total += s[q][w]; }
+            }
+            // the two child kinds share the next level's queue: reflection children first, then refraction children
+            const int t_refr = __shfl_sync(0xffffffffu, total, SHADE_Q_REFR);
+            int base = 0;
+            if (q < SHADE_LIGHTS_PER_ROUND) { if (total) base = atomicAdd(&sq.count[l0 + q], total); }
+            else if (q == SHADE_Q_REFL) {
+                if (total + t_refr) base = atomicAdd(&ctr->count[level + 1], total + t_refr);
+                if (total) atomicAdd(&ctr->rays_reflect, (unsigned long long)total);
+                if (t_refr) atomicAdd(&ctr->rays_refract, (unsigned long long)t_refr);
+            }
+            const int b_refl = __shfl_sync(0xffffffffu, base, SHADE_Q_REFL), t_refl = __shfl_sync(0xffffffffu, total, SHADE_Q_REFL);
+            if (q == SHADE_Q_REFR) base = b_refl + t_refl;
+            if (q < SHADE_QUEUES) {
+#pragma unroll
+                for (int w = 0; w < SHADE_WARPS; w++) s[q][w] = base + excl[w];
+            }
+        }
+        __syncthreads();
+        for (int q = 0; q < SHADE_LIGHTS_PER_ROUND && l0 + q < sc.n_lights; q++) {
+            const unsigned m = __ballot_sync(0xffffffffu, (wmask >> q) & 1u);
+            if (!((wmask >> q) & 1u)) continue;
+            const int li = l0 + q;
+            V3<R> ldir = mk(R(0), R(0), R(1)), lcol; R dist = R(0);
+            light_at(sc.lights[li], P, ldir, dist, lcol);
+            const int slot = li * sq.per_light + s[q][wid] + __popc(m & lt);
             const V3<R> so = P + N * R(1e-4);
-            const int qc = sq.cap;
             R* rec = sq.q + (size_t)slot * 8;
             rec[0] = so.x; rec[1] = so.y; rec[2] = so.z; rec[3] = ldir.x; rec[4] = ldir.y; rec[5] = ldir.z;
             rec[6] = dist; rec[7] = length(D);
@@ -1465,52 +1722,29 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
             sq.target[slot] = i * sc.n_lights + li;
             occl[i * sc.n_lights + li] = 0;
         }
-    }
-    if (!spawn) continue;                                  // uniform
-    // reflection child (:512-529)
-    {
-        const bool want = live && refl > R(0);
-        const int slot = warp_append(&ctr->count[level + 1], want);
-        if (want) {
-            V3<R> rd = D - N * (R(2) * dot(D, N));
-            if (fuzz >= R(0)) rd = rd + mk(fuzz * gm<R>::cos(fuzz) * gm<R>::cos(fuzz), fuzz * gm<R>::sin(fuzz) * gm<R>::sin(fuzz), R(0));
-            const V3<R> ro = P + N * R(1e-4);
-            rd = normalize(rd);
+        if (l0 == 0 && spawn) {
+            const unsigned m_refl = __ballot_sync(0xffffffffu, want_refl), m_refr = __ballot_sync(0xffffffffu, want_refr);
             const int nc = next.cap;
-            next.ray[slot] = ro.x; next.ray[nc + slot] = ro.y; next.ray[2 * nc + slot] = ro.z;
-            next.ray[3 * nc + slot] = rd.x; next.ray[4 * nc + slot] = rd.y; next.ray[5 * nc + slot] = rd.z;
-            next.parent[slot] = i;
-        }
-        const unsigned m = __ballot_sync(0xffffffffu, want);
-        if ((threadIdx.x & 31) == 0 && m) atomicAdd(&ctr->rays_reflect, (unsigned long long)__popc(m));
-    }
-    // refraction child (:532-556); direction is not re-normalised, zero vector = total internal reflection
-    {
-        bool want = live && transp > R(0);
-        V3<R> rd = mk(R(0), R(0), R(0)), nn = N;
-        if (want) {
-            R n1 = R(1), n2 = ior;
-            if (dot(D, nn) > R(0)) { R tmp = n1; n1 = n2; n2 = tmp; nn = nn * R(-1); }
-            const R ratio = n1 / n2;                                                 // refract :438-450
-            const R cosI = -dot(nn, D);
-            const R sinT2 = ratio * ratio * (R(1) - cosI * cosI);
-            if (sinT2 > R(1)) want = false;
-            else {
-                const R cosT = gm<R>::sqrt(R(1) - sinT2);
-                rd = D * ratio + nn * (ratio * cosI - cosT);
-                if (rd.x == R(0) && rd.y == R(0) && rd.z == R(0)) want = false;
+            if (want_refl) {                                                         // reflection child (:512-529)
+                const int slot = s[SHADE_Q_REFL][wid] + __popc(m_refl & lt);
+                V3<R> rd = D - N * (R(2) * dot(D, N));
+                if (fuzz >= R(0)) rd = rd + mk(fuzz * gm<R>::cos(fuzz) * gm<R>::cos(fuzz), fuzz * gm<R>::sin(fuzz) * gm<R>::sin(fuzz), R(0));
+                const V3<R> ro = P + N * R(1e-4);
+                rd = normalize(rd);
+                next.ray[slot] = ro.x; next.ray[nc + slot] = ro.y; next.ray[2 * nc + slot] = ro.z;
+                next.ray[3 * nc + slot] = rd.x; next.ray[4 * nc + slot] = rd.y; next.ray[5 * nc + slot] = rd.z;
+                next.parent[slot] = i;
+                next.hit[slot] = ray_sort_key(sc, leaf, rd);
+            }
+            if (want_refr) {                                                         // refraction child (:532-556)
+                const int slot = s[SHADE_Q_REFR][wid] + __popc(m_refr & lt);
+                const V3<R> ro = P - refr_n * R(1e-4);
+                next.ray[slot] = ro.x; next.ray[nc + slot] = ro.y; next.ray[2 * nc + slot] = ro.z;
+                next.ray[3 * nc + slot] = refr_d.x; next.ray[4 * nc + slot] = refr_d.y; next.ray[5 * nc + slot] = refr_d.z;
+                next.parent[slot] = i | 0x80000000;
+                next.hit[slot] = ray_sort_key(sc, leaf, refr_d);
             }
         }
-        const int slot = warp_append(&ctr->count[level + 1], want);
-        if (want) {
-            const V3<R> ro = P - nn * R(1e-4);
-            const int nc = next.cap;
-            next.ray[slot] = ro.x; next.ray[nc + slot] = ro.y; next.ray[2 * nc + slot] = ro.z;
-            next.ray[3 * nc + slot] = rd.x; next.ray[4 * nc + slot] = rd.y; next.ray[5 * nc + slot] = rd.z;
-            next.parent[slot] = i | 0x80000000;
-        }
-        const unsigned m = __ballot_sync(0xffffffffu, want);
-        if ((threadIdx.x & 31) == 0 && m) atomicAdd(&ctr->rays_refract, (unsigned long long)__popc(m));
     }
     }  // grid-stride loop
 }
@@ -1771,6 +2005,8 @@ private:
     Launch l_primary_, l_closest_, l_shadow_pivot_, l_shadow_axis_;                      // the four k_cull instantiations
     CandQueue cq_{}; int cand_per_ray_ = 4, tile_shrink_ = 0;
     int* sort_hist_ = nullptr; int* sort_cursor_ = nullptr; int sort_nb_ = 2, sort_shift_ = 0; bool sort_clear_ = true;
+    int* key_hist_ = nullptr; int* key_cursor_ = nullptr; int key_nb_ = 6;      // spawned rays by (origin leaf, direction cell); cleared with sort_hist_
+    bool sort_spawned_ = true;
     // cull tables (device) and what they were built for: any ray, camera rays, one per light
     std::vector<double> bound_;                                  // host: [n][4] bounding spheres (centre, radius) of the objects
     R* cull_general_ = nullptr; R* cull_eye_ = nullptr; std::vector<R*> cull_light_;
@@ -1898,6 +2134,12 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     sc.fpool = d_fpool; sc.itab = d_itab; sc.code = d_code;
     sc.n_fpool = (int)fpool.size(); sc.n_itab = (int)S.itab.size();
     sc.W = S.width; sc.H = S.height; sc.depth = S.depth; sc.vw = S.vw; sc.vh = S.vh;
+    // sort key of spawned rays: 6 k^2 direction cells per origin leaf, at most KEY_BINS_MAX bins in all
+    sc.key_k = (int)env_size("GMLRT_KEY_K", 3); sc.key_k = std::max(1, std::min(sc.key_k, 8));
+    sc.key_shift = 0;
+    while ((size_t)(((std::max(n_all, 1) - 1) >> sc.key_shift) + 1) * 6 * sc.key_k * sc.key_k > (size_t)KEY_BINS_MAX) sc.key_shift++;
+    key_nb_ = (((std::max(n_all, 1) - 1) >> sc.key_shift) + 1) * 6 * sc.key_k * sc.key_k;
+    sort_spawned_ = env_size("GMLRT_SORT_SPAWNED", 1) != 0;
     for (int k = 0; k < 3; k++) { sc.ambient[k] = (R)S.h.ambient[k]; sc.bg0[k] = (R)S.h.bg_start[k]; sc.bg1[k] = (R)S.h.bg_end[k]; }
     sc_ = sc;
     // cull tables: any ray; camera rays (their lines pass through the eye, raytracer.go:605-609); one per light
@@ -2042,6 +2284,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     }
     const size_t sq_cap = max_cap * std::max(nl, 1);
     size_t o_sq = take(8 * sq_cap * sizeof(R)), o_skip = take(sq_cap * 4), o_tgt = take(sq_cap * 4), o_first = take(sq_cap * 4), o_perm = take(sq_cap * 4), o_sort = take(2 * SORT_BINS_MAX * sizeof(int));
+    size_t o_keysort = take(2 * (size_t)KEY_BINS_MAX * sizeof(int));
     const size_t cand_cap = std::min<size_t>((size_t)((double)max_cap * cand_per_ray_ * (double)(1 << tile_shrink_)), (size_t)2000000000);
     size_t o_cray = take(cand_cap * 4), o_cobj = take(cand_cap * 4), o_ct = take(cand_cap * sizeof(R)), o_ccount = take(256);
     size_t o_samples = take(3 * S0 * sizeof(R));
@@ -2065,6 +2308,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     sq_.q = (R*)(base + o_sq); sq_.skip = (int*)(base + o_skip); sq_.target = (int*)(base + o_tgt); sq_.cap = (int)sq_cap;
     sq_.per_light = (int)max_cap; sq_.count = shadow_counts_; sq_.first = (int*)(base + o_first); sq_.perm = (int*)(base + o_perm);
     sort_hist_ = (int*)(base + o_sort); sort_cursor_ = sort_hist_ + SORT_BINS_MAX; sort_clear_ = true;
+    key_hist_ = (int*)(base + o_keysort); key_cursor_ = key_hist_ + KEY_BINS_MAX;
     sort_nb_ = std::min(sc_.n_leaves + 1, SORT_BINS_MAX); sort_shift_ = 0;
     while (((std::max(sc_.n_leaves, 1) - 1) >> sort_shift_) + 2 > sort_nb_) sort_shift_++;
     cq_.ray = (int*)(base + o_cray); cq_.obj = (int*)(base + o_cobj); cq_.t = (void*)(base + o_ct); cq_.count = (int*)(base + o_ccount);
@@ -2106,6 +2350,21 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
         ids_n_ = (size_t)W * sc_.H * 4;
     }
     const int wide = sms_ * 16;
+    // exact kernels by kind (see ExactKinds): spheres inline at full occupancy, every other kind through exact_hit
+    const bool have_spheres = sc_.kind_begin[K_SPHERE + 1] > 0, have_rest = sc_.kind_begin[K_SPHERE + 1] < sc_.n_leaves || sc_.n_leaves == 0;
+    auto exact_closest = [&](int l, bool count) -> int {
+        const int grid = sms_ * 16;
+        if (have_spheres) {
+            if (count) k_exact_closest<R, false, true, EXACT_SPHERES><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
+            else k_exact_closest<R, false, false, EXACT_SPHERES><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
+        }
+        if (have_rest) {
+            if (count) k_exact_closest<R, false, true, EXACT_REST><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
+            else k_exact_closest<R, false, false, EXACT_REST><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
+        }
+        totals_.launches += (have_spheres && have_rest) ? 1 : 0;
+        return GMLRT_OK;
+    };
     // profiling: one event before every launch; launches on one stream serialise, so consecutive events bracket a kernel
     auto mark = [&](int cls) -> int {
         if (!profile_) return GMLRT_OK;
@@ -2127,21 +2386,39 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             const int cap_blocks = (levels_[l].cap + SHADE_THREADS - 1) / SHADE_THREADS;
             const int exact_grid = sms_ * 16;
             CU_TRY(cudaMemsetAsync(cq_.count, 0, 2 * sizeof(int), stream_));
-            ClosestSource<R> csrc{levels_[l]};
+            ClosestSource<R> csrc{levels_[l], nullptr};
+            if (sort_clear_) {
+                CU_TRY(cudaMemsetAsync(sort_hist_, 0, SORT_BINS_MAX * sizeof(int), stream_));
+                CU_TRY(cudaMemsetAsync(key_hist_, 0, KEY_BINS_MAX * sizeof(int), stream_));
+                sort_clear_ = false;
+            }
+            if (l > 0 && sort_spawned_) {                  // rays by (origin leaf, direction cell); the keys are in lv.hit, the permutation borrows
+                MARK(KC_SORT);                             // the shadow queue's (free until this level is shaded)
+                k_keysort_hist<<<sms_ * 8, 256, 0, stream_>>>(levels_[l].hit, &ctr_->count[l], key_nb_, key_hist_);
+                k_sort_scan<<<1, 1024, 0, stream_>>>(key_nb_, key_hist_, key_cursor_);
+                k_keysort_scatter<<<sms_ * 8, 256, 0, stream_>>>(levels_[l].hit, &ctr_->count[l], key_nb_, key_cursor_, sq_.perm);
+                totals_.launches += 3;
+                csrc.perm = sq_.perm;
+            }
             if (l == 0) {                                  // camera rays: PIVOT family through the eye, robust re-tests in f32
                 MARK(KC_CLOSEST_PRIMARY);
                 k_cull<R, CULL_PIVOT, RPT_FAMILY, ClosestSource<R>><<<l_primary_.grid, SCAN_THREADS, l_primary_.smem, stream_>>>(
                     csrc, &ctr_->count[l], cull_eye_, frame_eye_, sc_.n_cull, cq_, ctr_, chunk_objs_, resident_);
                 MARK(KC_EXACT);
-                if (counting) k_exact_closest<R, kRobustPrimary, true><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
-                else k_exact_closest<R, kRobustPrimary, false><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
+                if (kRobustPrimary) {
+                    if (counting) k_exact_closest<R, kRobustPrimary, true, EXACT_ALL><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
+                    else k_exact_closest<R, kRobustPrimary, false, EXACT_ALL><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
+                } else {
+                    int erc = exact_closest(l, counting);
+                    if (erc) return erc;
+                }
             } else {
                 MARK(KC_CLOSEST);
                 k_cull<R, CULL_GENERAL, RPT_GENERAL, ClosestSource<R>><<<l_closest_.grid, SCAN_THREADS, l_closest_.smem, stream_>>>(
                     csrc, &ctr_->count[l], cull_general_, frame_general_, sc_.n_cull, cq_, ctr_, chunk_objs_, resident_);
                 MARK(KC_EXACT);
-                if (counting) k_exact_closest<R, false, true><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
-                else k_exact_closest<R, false, false><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
+                int erc = exact_closest(l, counting);
+                if (erc) return erc;
             }
             k_closest_order<R><<<exact_grid, 256, 0, stream_>>>(sc_, levels_[l], cq_);
             k_closest_pick<R><<<exact_grid, 256, 0, stream_>>>(sc_, levels_[l], cq_);
@@ -2157,7 +2434,6 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
                 ShadowSource<R> ssrc{sq_, li * sq_.per_light};
                 CU_TRY(cudaMemsetAsync(cq_.count, 0, 2 * sizeof(int), stream_));
                 MARK(KC_SORT);
-                if (sort_clear_) { CU_TRY(cudaMemsetAsync(sort_hist_, 0, SORT_BINS_MAX * sizeof(int), stream_)); sort_clear_ = false; }
                 k_sort_hist<R><<<sms_ * 4, SORT_THREADS, 0, stream_>>>(sq_, li, sort_shift_, sort_nb_, sort_hist_);
                 k_sort_scan<<<1, 1024, 0, stream_>>>(sort_nb_, sort_hist_, sort_cursor_);
                 k_sort_scatter<R><<<sms_ * 4, SORT_THREADS, 0, stream_>>>(sq_, li, sort_shift_, sort_nb_, sort_cursor_);
@@ -2168,13 +2444,17 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
                 else k_cull<R, CULL_PIVOT, RPT_FAMILY, ShadowSource<R>><<<l_shadow_pivot_.grid, SCAN_THREADS, l_shadow_pivot_.smem, stream_>>>(
                     ssrc, &shadow_counts_[li], cull_light_[li], frame_light_[li], sc_.n_cull, cq_, ctr_, chunk_objs_, resident_);
                 MARK(KC_EXACT);
+                const int sbase = li * sq_.per_light;
                 if (counting) {
-                    k_exact_shadow<R, true><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, sq_, li * sq_.per_light, cq_, ctr_);
+                    if (have_spheres) k_exact_shadow<R, true, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, sq_, sbase, cq_, ctr_);
+                    if (have_rest) k_exact_shadow<R, true, EXACT_REST><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, sq_, sbase, cq_, ctr_);
                     k_shadow_finish<R, true><<<wide, 256, 0, stream_>>>(sc_, sq_, li, occl_[l], ctr_);
                 } else {
-                    k_exact_shadow<R, false><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, sq_, li * sq_.per_light, cq_, ctr_);
+                    if (have_spheres) k_exact_shadow<R, false, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, sq_, sbase, cq_, ctr_);
+                    if (have_rest) k_exact_shadow<R, false, EXACT_REST><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, sq_, sbase, cq_, ctr_);
                     k_shadow_finish<R, false><<<wide, 256, 0, stream_>>>(sc_, sq_, li, occl_[l], ctr_);
                 }
+                totals_.launches += (have_spheres && have_rest) ? 1 : 0;
                 totals_.launches += 3;
             }
             if (sc_.n_lights > 0) CU_TRY(cudaMemsetAsync(shadow_counts_, 0, sizeof(int) * sc_.n_lights, stream_));
