@@ -690,14 +690,17 @@ template <> struct BitsOf<double> {
     static __device__ __forceinline__ double back(unsigned long long b) { return __longlong_as_double((long long)b); }
 };
 
-// the same window over an index list: objects idx[k0 .. k0 + GROUP - 1] (indices into `sm`), 8 indices per 16-byte load
+// the same window over an index list: objects idx[k0 .. k0 + cnt - 1] (indices into `sm`; cnt a multiple of 8, at most
+// GROUP), 8 indices per 16-byte load.  A short list costs what it holds, not a whole window: the masks are shifted
+// up afterwards so that test j still sits in bit 31 - j.
 template <typename R, int FAMILY, int RPT>
-__device__ __forceinline__ void cull_window_indirect(const R* sm, const uint16_t* idx, int k0, const CullRay<R, FAMILY> (&cr)[RPT],
+__device__ __forceinline__ void cull_window_indirect(const R* sm, const uint16_t* idx, int k0, int cnt, const CullRay<R, FAMILY> (&cr)[RPT],
                                                      uint32_t (&lo)[RPT], uint32_t (&hi)[RPT]) {
 #pragma unroll
     for (int r = 0; r < RPT; r++) { lo[r] = 0; hi[r] = 0; }
+    const int n_lo = min(cnt, 32);
 #pragma unroll 1
-    for (int j0 = 0; j0 < 32; j0 += 8) {
+    for (int j0 = 0; j0 < n_lo; j0 += 8) {
         const uint4 pk = *reinterpret_cast<const uint4*>(idx + k0 + j0);
         const uint32_t w[4] = {pk.x, pk.y, pk.z, pk.w};
 #pragma unroll
@@ -707,8 +710,13 @@ __device__ __forceinline__ void cull_window_indirect(const R* sm, const uint16_t
             for (int r = 0; r < RPT; r++) lo[r] = push_sign(lo[r], cr[r].slack(L));
         }
     }
+    if (n_lo < 32) {
+#pragma unroll
+        for (int r = 0; r < RPT; r++) lo[r] <<= 32 - n_lo;
+        return;
+    }
 #pragma unroll 1
-    for (int j0 = 32; j0 < 64; j0 += 8) {
+    for (int j0 = 32; j0 < cnt; j0 += 8) {
         const uint4 pk = *reinterpret_cast<const uint4*>(idx + k0 + j0);
         const uint32_t w[4] = {pk.x, pk.y, pk.z, pk.w};
 #pragma unroll
@@ -717,6 +725,10 @@ __device__ __forceinline__ void cull_window_indirect(const R* sm, const uint16_t
 #pragma unroll
             for (int r = 0; r < RPT; r++) hi[r] = push_sign(hi[r], cr[r].slack(L));
         }
+    }
+    if (cnt > 32 && cnt < 64) {
+#pragma unroll
+        for (int r = 0; r < RPT; r++) hi[r] <<= 64 - cnt;
     }
 }
 
@@ -1005,12 +1017,12 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
 #ifdef GMLRT_DEBUG_PACKETS
                     if (lane == 0) { atomicAdd(&ctr->dbg[2 + 4 * (FAMILY == CULL_AXIS)], (unsigned long long)pn); atomicAdd(&ctr->dbg[3 + 4 * (FAMILY == CULL_AXIS)], (unsigned long long)ns); }
 #endif
-                    const int padded = (ns + GROUP - 1) / GROUP * GROUP;
-                    for (int k = ns + lane; k < padded; k += 32) surv[k] = (uint16_t)(p0 - base);      // any valid record; masked off below
+                    const int padded = (ns + 7) & ~7;                                   // whole 16-byte loads of 8 indices
+                    if (ns + lane < padded) surv[ns + lane] = (uint16_t)(p0 - base);     // any valid record; masked off below
                     __syncwarp();
                     for (int k0 = 0; k0 < padded; k0 += GROUP) {
                         uint32_t lo[RPT], hi[RPT];
-                        cull_window_indirect<R, FAMILY, RPT>(sm, surv, k0, cr, lo, hi);
+                        cull_window_indirect<R, FAMILY, RPT>(sm, surv, k0, min(GROUP, padded - k0), cr, lo, hi);
                         const int valid = ns - k0;                                 // entries of this window that are real
                         fine += (unsigned long long)(n_active * min(valid, GROUP));
                         const uint32_t mlo = valid >= 32 ? 0xffffffffu : ~(0xffffffffu >> valid);
