@@ -755,7 +755,7 @@ __device__ __forceinline__ WarpBound<R> warp_bound(const CullRay<R, CULL_PIVOT> 
     for (int r = 0; r < RPT; r++) if (active[r]) { sx += cr[r].dx; sy += cr[r].dy; sz += cr[r].dz; }
     sx = warp_sum(sx); sy = warp_sum(sy); sz = warp_sum(sz);
     const R len = gm<R>::sqrt(fma_(sx, sx, fma_(sy, sy, sz * sz)));
-    WarpBound<R> b;
+    WarpBound<R> b = {};
     b.usable = len > R(0);
     const R inv = b.usable ? R(1) / len : R(0);
     b.ax = sx * inv; b.ay = sy * inv; b.az = sz * inv;
@@ -774,7 +774,7 @@ __device__ __forceinline__ WarpBound<R> warp_bound(const CullRay<R, CULL_AXIS> (
 #pragma unroll
     for (int r = 0; r < RPT; r++) if (active[r]) { su += cr[r].ou; sv += cr[r].ov; cnt += R(1); }
     su = warp_sum(su); sv = warp_sum(sv); cnt = warp_sum(cnt);
-    WarpBound<R> b;
+    WarpBound<R> b = {};
     b.usable = cnt > R(0);
     b.ax = b.usable ? su / cnt : R(0); b.ay = b.usable ? sv / cnt : R(0); b.az = R(0);
     R d2 = R(0);
@@ -854,7 +854,73 @@ template <typename R> __device__ __forceinline__ bool packet_survives(const Cull
 }
 
 constexpr int PCHUNK = 1024;                // objects per packet pass = survivor list capacity per warp (uint16 indices)
-constexpr size_t SURV_BYTES = (size_t)(SCAN_THREADS / 32) * PCHUNK * sizeof(uint16_t);
+constexpr size_t SURV_BYTES = (size_t)(SCAN_THREADS / 32 + 1) * PCHUNK * sizeof(uint16_t);    // one list per warp + the CTA's
+
+// The bound of a whole CTA's rays = the union of its warps' bounds (published in shared memory by lane 0 of each warp;
+// every thread evaluates the same union).  Used for a first packet pass shared by the CTA: 256 threads x 4 objects
+// instead of 32 lanes x 32, after which a warp only looks at what the CTA kept.
+constexpr int WB_WORDS = 12;      // ax ay az cos sin ox oy oz rho usable active
+template <typename R> __device__ __forceinline__ void publish_bound(R* slot, const WarpBound<R>& b, bool any_active) {
+    slot[0] = b.ax; slot[1] = b.ay; slot[2] = b.az; slot[3] = b.cos_t; slot[4] = b.sin_t;
+    slot[5] = b.ox; slot[6] = b.oy; slot[7] = b.oz; slot[8] = b.rho;
+    slot[9] = b.usable ? R(1) : R(0); slot[10] = any_active ? R(1) : R(0);
+}
+template <typename R, int FAMILY>
+__device__ __forceinline__ WarpBound<R> cta_bound(const R (*wbs)[WB_WORDS]) {
+    constexpr int NW = SCAN_THREADS / 32;
+    WarpBound<R> c = {};
+    c.usable = true;
+    R sx = R(0), sy = R(0), sz = R(0), qx = R(0), qy = R(0), qz = R(0), cnt = R(0);
+#pragma unroll
+    for (int w = 0; w < NW; w++) {
+        const R* b = wbs[w];
+        if (b[10] == R(0)) continue;                         // a warp past the end of the queue
+        if (b[9] == R(0)) c.usable = false;
+        sx += b[0]; sy += b[1]; sz += b[2]; qx += b[5]; qy += b[6]; qz += b[7]; cnt += R(1);
+    }
+    if (!(cnt > R(0))) c.usable = false;
+    if (!c.usable) return c;
+    if (FAMILY == CULL_AXIS) {                               // discs in the plane orthogonal to the common direction
+        c.ax = sx / cnt; c.ay = sy / cnt;
+        R rho = R(0);
+#pragma unroll
+        for (int w = 0; w < NW; w++) {
+            const R* b = wbs[w];
+            if (b[10] == R(0)) continue;
+            const R du = b[0] - c.ax, dv = b[1] - c.ay;
+            const R d = gm<R>::sqrt(fma_(du, du, dv * dv)) * R(1.0001) + b[3];
+            rho = d > rho ? d : rho;
+        }
+        c.cos_t = rho * R(1.0001) + R(1e-6) * (gm<R>::abs(c.ax) + gm<R>::abs(c.ay) + R(1));
+        return c;
+    }
+    const R len = gm<R>::sqrt(fma_(sx, sx, fma_(sy, sy, sz * sz)));
+    if (!(len > R(0))) { c.usable = false; return c; }
+    const R inv = R(1) / len;
+    c.ax = sx * inv; c.ay = sy * inv; c.az = sz * inv;
+    c.ox = qx / cnt; c.oy = qy / cnt; c.oz = qz / cnt;
+    R cmin = R(1), rho = R(0);
+#pragma unroll
+    for (int w = 0; w < NW; w++) {
+        const R* b = wbs[w];
+        if (b[10] == R(0)) continue;
+        R cw = fma_(b[0], c.ax, fma_(b[1], c.ay, b[2] * c.az));      // cos of the angle phi between the warp's axis and the CTA's
+        if (!(cw > R(0))) c.usable = false;                           // phi + theta must stay below pi for the sum formula
+        cw = cw < R(1) ? cw : R(1);
+        const R sw = gm<R>::sqrt(R(1) - cw * cw) + R(1e-5);
+        const R cs = cw * b[3] - sw * b[4];                           // cos(phi + theta_w)
+        cmin = cs < cmin ? cs : cmin;
+        const R ex = b[5] - c.ox, ey = b[6] - c.oy, ez = b[7] - c.oz;
+        const R d = gm<R>::sqrt(fma_(ex, ex, fma_(ey, ey, ez * ez))) * R(1.0001) + b[8];
+        rho = d > rho ? d : rho;
+    }
+    cmin -= R(1e-5);
+    c.cos_t = cmin;
+    c.sin_t = gm<R>::sqrt(R(1) - (cmin < R(1) ? cmin * cmin : R(1))) + R(1e-5);
+    c.rho = rho * R(1.0001) + R(1e-6) * (gm<R>::abs(c.ox) + gm<R>::abs(c.oy) + gm<R>::abs(c.oz) + R(1));
+    c.usable = c.usable && cmin > R(0.2);
+    return c;
+}
 
 // ------------------------------------------------------------------ scan = cull kernel + exact kernels
 // Phase 1, k_cull: persistent CTAs over blocks of SCAN_THREADS * RPT rays; the cull table is staged once per
@@ -911,14 +977,18 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ __align__(8) uint64_t bar[2];
     const int tid = threadIdx.x, lane = tid & 31;
-    uint16_t* const surv = reinterpret_cast<uint16_t*>(smem_raw) + (tid >> 5) * PCHUNK;    // this warp's survivor list (packet stage)
+    uint16_t* const csurv = reinterpret_cast<uint16_t*>(smem_raw);                              // what the CTA's bound keeps (packet stage, first pass)
+    uint16_t* const surv = csurv + ((tid >> 5) + 1) * PCHUNK;                                  // what this warp's bound keeps of it
+    __shared__ R s_wb[SCAN_THREADS / 32][WB_WORDS];
+    __shared__ int s_cn[2];                                                                    // entries of the CTA's list, by pass parity
+    int pass_no = 0;
     R* const tab = reinterpret_cast<R*>(smem_raw + SURV_BYTES);   // buffer b starts at tab + b * chunk_objs * 4
     const int n = *n_ptr;
     const int nblocks = (n + RAYS_PER_BLOCK - 1) / RAYS_PER_BLOCK;
     if ((int)blockIdx.x >= nblocks) return;
     const int NP = n_cull;                                     // padded to a multiple of GROUP
     const int nchunks = (NP + chunk_objs - 1) / chunk_objs;
-    if (tid == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_fence_init(); }
+    if (tid == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_fence_init(); s_cn[0] = 0; s_cn[1] = 0; }
     __syncthreads();
     uint32_t phase[2] = {0, 0};
     if (resident && NP > 0) {
@@ -948,6 +1018,9 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
         int n_active = 0;
 #pragma unroll
         for (int r = 0; r < RPT; r++) n_active += active[r] ? 1 : 0;
+        if (lane == 0) publish_bound<R>(s_wb[tid >> 5], wb, ray0 + (tid >> 5) * RPT * 32 < n);
+        __syncthreads();
+        const WarpBound<R> cb = cta_bound<R, FAMILY>(s_wb);
         unsigned long long fine = 0, packet = 0;           // this lane's executed tests
 #ifdef GMLRT_DEBUG_PACKETS
         if (lane == 0 && FAMILY != CULL_GENERAL) { atomicAdd(&ctr->dbg[0 + 4 * (FAMILY == CULL_AXIS)], 1ull); if (wb.usable) atomicAdd(&ctr->dbg[1 + 4 * (FAMILY == CULL_AXIS)], 1ull); }
@@ -1000,19 +1073,48 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
                     }
                 }
             };
-            if (wb.usable) {
-                // packet stage: the lanes test 32 objects at a time against the warp's bound; the survivors' indices
-                // (relative to this chunk) are compacted into the warp's list, then only those are tested per ray
+            if (cb.usable || wb.usable) {
+                // packet stage.  First pass (when the CTA's rays are coherent as a whole): the 256 threads test the pass's
+                // objects against the CTA's bound, 32 per warp and step, and compact what it keeps into the CTA's list.
+                // Second pass: the lanes of each warp test that list (or, without a CTA bound, every object) against the
+                // warp's own bound and compact into the warp's list; only those objects are tested per ray.
+                const bool warp_has_rays = __any_sync(0xffffffffu, n_active != 0);
+                const unsigned lt = (1u << lane) - 1u;
                 for (int p0 = base; p0 < end; p0 += PCHUNK) {
                     const int pn = min(PCHUNK, end - p0);
+                    int cn = pn;
+                    if (cb.usable) {                                                 // uniform across the CTA
+                        int* const cnt = &s_cn[pass_no & 1];
+                        for (int o = tid & ~31; o < pn; o += SCAN_THREADS) {
+                            const int k = p0 - base + o + lane;
+                            const bool in = o + lane < pn;
+                            packet += in ? 1 : 0;
+                            const bool sv = in && packet_survives<R>(load_cull(sm, k), cb, (CullRay<R, FAMILY>*)nullptr);
+                            const unsigned bal = __ballot_sync(0xffffffffu, sv);
+                            int at = 0;
+                            if (lane == 0 && bal) at = atomicAdd(cnt, __popc(bal));
+                            at = __shfl_sync(0xffffffffu, at, 0);
+                            if (sv) csurv[at + __popc(bal & lt)] = (uint16_t)k;
+                        }
+                        __syncthreads();
+                        cn = *cnt;
+                        if (tid == 0) s_cn[(pass_no + 1) & 1] = 0;                    // free since the end of the previous pass
+                        pass_no++;
+                    }
                     int ns = 0;
-                    for (int o = 0; o < pn; o += 32) {
-                        const int k = p0 - base + o + lane;
-                        packet += (o + lane < pn) ? 1 : 0;
-                        const bool sv = (o + lane < pn) && packet_survives<R>(load_cull(sm, k), wb, (CullRay<R, FAMILY>*)nullptr);
-                        const unsigned bal = __ballot_sync(0xffffffffu, sv);
-                        if (sv) surv[ns + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)k;
-                        ns += __popc(bal);
+                    if (warp_has_rays && wb.usable) {
+                        for (int o = 0; o < cn; o += 32) {
+                            const bool in = o + lane < cn;
+                            const int k = cb.usable ? (in ? (int)csurv[o + lane] : 0) : p0 - base + o + lane;
+                            packet += in ? 1 : 0;
+                            const bool sv = in && packet_survives<R>(load_cull(sm, k), wb, (CullRay<R, FAMILY>*)nullptr);
+                            const unsigned bal = __ballot_sync(0xffffffffu, sv);
+                            if (sv) surv[ns + __popc(bal & lt)] = (uint16_t)k;
+                            ns += __popc(bal);
+                        }
+                    } else if (warp_has_rays) {                                      // (a warp bound can only be unusable here if the CTA's is)
+                        for (int o = lane; o < cn; o += 32) surv[o] = cb.usable ? csurv[o] : (uint16_t)(p0 - base + o);
+                        ns = cn;
                     }
 #ifdef GMLRT_DEBUG_PACKETS
                     if (lane == 0) { atomicAdd(&ctr->dbg[2 + 4 * (FAMILY == CULL_AXIS)], (unsigned long long)pn); atomicAdd(&ctr->dbg[3 + 4 * (FAMILY == CULL_AXIS)], (unsigned long long)ns); }
@@ -1031,7 +1133,8 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
                         for (int r = 0; r < RPT; r++) { lo[r] &= mlo; hi[r] &= mhi; }
                         append(lo, hi, [&](int j) { return base + (int)surv[k0 + j]; });
                     }
-                    __syncwarp();                                                   // the list is rewritten by the next pass
+                    if (cb.usable) __syncthreads();                                  // the CTA's list is rewritten by the next pass
+                    else __syncwarp();                                               // the warp's list likewise
                 }
             } else {
                 for (int first = base; first < end; first += GROUP) {      // one window of GROUP objects
