@@ -77,8 +77,8 @@ template <typename R> struct DevScene {
 
 // One recursion level of the wavefront (SoA, `cap` entries each).
 template <typename R> struct Level {
-    R* ray;       // [6][cap] origin xyz, direction xyz
-    int* parent;  // [cap] index in the previous level | (1<<31 for the refraction slot)
+    R* ray;       // [cap][8] one record per ray: origin xyz, direction xyz, then (as raw bits of word 6) the parent: index in
+                  //          the previous level | (1<<31 for the refraction slot).  32 bytes in f32: one sector per random read
     int* hit;     // [cap] device leaf index | face << 28, or -1
     R* t;         // [cap] T of the hit; during the scan: bit pattern of the smallest T so far (all ones = none)
     int* order;   // [cap] scan scratch: smallest scan index among the hits that have the smallest T
@@ -112,6 +112,33 @@ struct Counters {                  // device-resident, zeroed per trace
 };
 
 template <typename R> struct Ray { R ox, oy, oz, dx, dy, dz; };
+
+// ray records (Level::ray, and the staging buffer spawned rays wait in until they are sorted)
+constexpr int RAY_WORDS = 8;
+__device__ __forceinline__ void load_ray(const float* rays, int i, Ray<float>& w) {
+    const float4* p = reinterpret_cast<const float4*>(rays + (size_t)i * RAY_WORDS);
+    const float4 a = p[0], b = p[1];
+    w.ox = a.x; w.oy = a.y; w.oz = a.z; w.dx = a.w; w.dy = b.x; w.dz = b.y;
+}
+__device__ __forceinline__ void load_ray(const double* rays, int i, Ray<double>& w) {
+    const double2* p = reinterpret_cast<const double2*>(rays + (size_t)i * RAY_WORDS);
+    const double2 a = p[0], b = p[1], c = p[2];
+    w.ox = a.x; w.oy = a.y; w.oz = b.x; w.dx = b.y; w.dy = c.x; w.dz = c.y;
+}
+__device__ __forceinline__ void store_ray(float* rays, int i, float ox, float oy, float oz, float dx, float dy, float dz, int parent) {
+    float4* p = reinterpret_cast<float4*>(rays + (size_t)i * RAY_WORDS);
+    p[0] = make_float4(ox, oy, oz, dx);
+    p[1] = make_float4(dy, dz, __int_as_float(parent), 0.f);
+}
+__device__ __forceinline__ void store_ray(double* rays, int i, double ox, double oy, double oz, double dx, double dy, double dz, int parent) {
+    double2* p = reinterpret_cast<double2*>(rays + (size_t)i * RAY_WORDS);
+    p[0] = make_double2(ox, oy); p[1] = make_double2(oz, dx); p[2] = make_double2(dy, dz);
+    p[3] = make_double2(__longlong_as_double((long long)(unsigned)parent), 0.0);
+}
+template <typename R> __device__ __forceinline__ int ray_parent(const R* rays, int i) {
+    return reinterpret_cast<const int*>(rays + (size_t)i * RAY_WORDS + 6)[0];      // little-endian: the low word of word 6
+}
+
 
 // ------------------------------------------------------------------ leaf matrix in shared memory
 template <typename R> struct Mat34 { R m[12]; };
@@ -942,20 +969,13 @@ struct CandQueue {
 };
 
 template <typename R> struct ClosestSource {                 // rays of one recursion level
-    Level<R> lv;
-    const int* perm;                                          // levels >= 1: rays by (origin object, direction cell); null = queue order
-    __device__ __forceinline__ int id(int i) const { return perm ? perm[i] : i; }
-    __device__ __forceinline__ void load(int i, Ray<R>& out) const {
-        const size_t cap = (size_t)lv.cap;
-        const int k = id(i);
-        out.ox = lv.ray[k]; out.oy = lv.ray[cap + k]; out.oz = lv.ray[2 * cap + k];
-        out.dx = lv.ray[3 * cap + k]; out.dy = lv.ray[4 * cap + k]; out.dz = lv.ray[5 * cap + k];
-    }
+    Level<R> lv;                                              // (levels >= 1 are stored sorted by origin object and direction cell)
+    __device__ __forceinline__ int id(int i) const { return i; }
+    __device__ __forceinline__ void load(int i, Ray<R>& out) const { load_ray(lv.ray, i, out); }
     __device__ __forceinline__ void init(int i) const {       // no hit yet
-        const int k = id(i);
-        lv.hit[k] = -1;
-        reinterpret_cast<typename BitsOf<R>::type*>(lv.t)[k] = ~(typename BitsOf<R>::type)0;
-        lv.order[k] = 0x7fffffff;
+        lv.hit[i] = -1;
+        reinterpret_cast<typename BitsOf<R>::type*>(lv.t)[i] = ~(typename BitsOf<R>::type)0;
+        lv.order[i] = 0x7fffffff;
     }
 };
 
@@ -1211,9 +1231,7 @@ __global__ void __launch_bounds__(EXACT_THREADS) k_exact_closest(const __grid_co
         if (obj < sc.n_leaves) {                               // a padding record can only be reached by a NaN ray
             if (COUNT) { n_exact++; n_flops += (unsigned)sc.obj_flops[obj]; }
             Ray<R> w;
-            const size_t cap = (size_t)lv.cap;
-            w.ox = lv.ray[ri]; w.oy = lv.ray[cap + ri]; w.oz = lv.ray[2 * cap + ri];
-            w.dx = lv.ray[3 * cap + ri]; w.dy = lv.ray[4 * cap + ri]; w.dz = lv.ray[5 * cap + ri];
+            load_ray(lv.ray, ri, w);
             bool h;
             if constexpr (ROBUST) h = exact_hit<R, true>(sc, obj, w, lv.ray64, lv.cap, ri, t, code);
             else h = exact_hit_kinds<R, KINDS>(sc, obj, w, t, code);
@@ -1392,7 +1410,8 @@ static __global__ void __launch_bounds__(256) k_keysort_hist(const int* keys, co
     }
 }
 
-static __global__ void __launch_bounds__(256) k_keysort_scatter(const int* keys, const int* n_ptr, int nb, int* cursor, int* perm) {
+template <typename R>
+__global__ void __launch_bounds__(256) k_keysort_scatter(const int* keys, const int* n_ptr, int nb, int* cursor, const R* stage, R* out) {
     const int n = *n_ptr;
     const int rounds = (n + gridDim.x * blockDim.x - 1) / (gridDim.x * blockDim.x);
     for (int r = 0; r < rounds; r++) {
@@ -1404,7 +1423,12 @@ static __global__ void __launch_bounds__(256) k_keysort_scatter(const int* keys,
         int at = 0;
         if (valid && rank == 0) at = atomicAdd(&cursor[key], __popc(peers));
         at = __shfl_sync(0xffffffffu, at, leader);
-        if (valid) perm[at + rank] = i;
+        if (valid) {                                       // move the whole record: the level is STORED in sorted order
+            const uint4* src = reinterpret_cast<const uint4*>(stage + (size_t)i * RAY_WORDS);
+            uint4* dst = reinterpret_cast<uint4*>(out + (size_t)(at + rank) * RAY_WORDS);
+#pragma unroll
+            for (int k = 0; k < (int)(RAY_WORDS * sizeof(R) / 16); k++) dst[k] = src[k];
+        }
     }
 }
 
@@ -1646,8 +1670,7 @@ __global__ void __launch_bounds__(256) k_gen(DevScene<R> sc, Level<R> lv, Counte
     const double ex = ox - 0.0, ey = oy - 0.0, ez = oz - (-1.0);
     const double m = sqrt(ex * ex + ey * ey + ez * ez);
     const int cap = lv.cap;
-    lv.ray[i] = (R)ox; lv.ray[cap + i] = (R)oy; lv.ray[2 * cap + i] = (R)oz;
-    lv.ray[3 * cap + i] = (R)(ex / m); lv.ray[4 * cap + i] = (R)(ey / m); lv.ray[5 * cap + i] = (R)(ez / m);
+    store_ray(lv.ray, i, (R)ox, (R)oy, (R)oz, (R)(ex / m), (R)(ey / m), (R)(ez / m), 0);
     if (lv.ray64) {
         lv.ray64[i] = ox; lv.ray64[cap + i] = oy; lv.ray64[2 * cap + i] = oz;
         lv.ray64[3 * cap + i] = ex / m; lv.ray64[4 * cap + i] = ey / m; lv.ray64[5 * cap + i] = ez / m;
@@ -1661,7 +1684,7 @@ enum { REC_P = 0, REC_N = 3, REC_COL = 6, REC_REFL = 9, REC_TRANSP = 10, REC_KR 
 template <typename R>
 __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R> lv, Level<R> next, ShadowQueue<R> sq,
                                                          unsigned char* occl, Counters* ctr, int level, int spawn,
-                                                         int32_t* ids, int y0, RowMap map) {
+                                                         int32_t* ids, int y0, RowMap map, R* spawn_to) {
     const int n = ctr->count[level];
     __shared__ int s_append[2][SHADE_QUEUES][SHADE_WARPS];
     int append_phase = 0;
@@ -1684,8 +1707,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
         leaf = h & HIT_LEAF_MASK;
         int face = h >> 28;
         const bool flip = (h & HIT_FLIP_BIT) != 0;          // CSG: surface of a subtracted solid
-        w.ox = lv.ray[i]; w.oy = lv.ray[cap + i]; w.oz = lv.ray[2 * cap + i];
-        w.dx = lv.ray[3 * cap + i]; w.dy = lv.ray[4 * cap + i]; w.dz = lv.ray[5 * cap + i];
+        load_ray(lv.ray, i, w);
         const R t = lv.t[i];
         const R* Mw = sc.w2o + (size_t)leaf * 12;
         Ray<R> o;
@@ -1839,24 +1861,19 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
         }
         if (l0 == 0 && spawn) {
             const unsigned m_refl = __ballot_sync(0xffffffffu, want_refl), m_refr = __ballot_sync(0xffffffffu, want_refr);
-            const int nc = next.cap;
             if (want_refl) {                                                         // reflection child (:512-529)
                 const int slot = s[SHADE_Q_REFL][wid] + __popc(m_refl & lt);
                 V3<R> rd = D - N * (R(2) * dot(D, N));
                 if (fuzz >= R(0)) rd = rd + mk(fuzz * gm<R>::cos(fuzz) * gm<R>::cos(fuzz), fuzz * gm<R>::sin(fuzz) * gm<R>::sin(fuzz), R(0));
                 const V3<R> ro = P + N * R(1e-4);
                 rd = normalize(rd);
-                next.ray[slot] = ro.x; next.ray[nc + slot] = ro.y; next.ray[2 * nc + slot] = ro.z;
-                next.ray[3 * nc + slot] = rd.x; next.ray[4 * nc + slot] = rd.y; next.ray[5 * nc + slot] = rd.z;
-                next.parent[slot] = i;
+                store_ray(spawn_to, slot, ro.x, ro.y, ro.z, rd.x, rd.y, rd.z, i);
                 next.hit[slot] = ray_sort_key(sc, leaf, rd);
             }
             if (want_refr) {                                                         // refraction child (:532-556)
                 const int slot = s[SHADE_Q_REFR][wid] + __popc(m_refr & lt);
                 const V3<R> ro = P - refr_n * R(1e-4);
-                next.ray[slot] = ro.x; next.ray[nc + slot] = ro.y; next.ray[2 * nc + slot] = ro.z;
-                next.ray[3 * nc + slot] = refr_d.x; next.ray[4 * nc + slot] = refr_d.y; next.ray[5 * nc + slot] = refr_d.z;
-                next.parent[slot] = i | 0x80000000;
+                store_ray(spawn_to, slot, ro.x, ro.y, ro.z, refr_d.x, refr_d.y, refr_d.z, (int)((unsigned)i | 0x80000000u));
                 next.hit[slot] = ray_sort_key(sc, leaf, refr_d);
             }
         }
@@ -1874,7 +1891,9 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_resolve(DevScene<R> sc, Level
     const int n = ctr->count[level];
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const int cap = lv.cap;
-    const V3<R> D = mk(lv.ray[3 * cap + i], lv.ray[4 * cap + i], lv.ray[5 * cap + i]);
+    Ray<R> wr;
+    load_ray(lv.ray, i, wr);
+    const V3<R> D = mk(wr.dx, wr.dy, wr.dz);
     V3<R> out;
     if (lv.hit[i] < 0) {
         const R t = R(0.5) * (D.y + R(1));                                           // :495-496
@@ -1915,7 +1934,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_resolve(DevScene<R> sc, Level
     if (level == 0) {
         samples[i] = out.x; samples[sample_cap + i] = out.y; samples[2 * sample_cap + i] = out.z;
     } else {
-        const int p = lv.parent[i];
+        const int p = ray_parent(lv.ray, i);
         const int pi = p & 0x7fffffff;
         const int base = (p < 0) ? 3 : 0;
         const int pc = prev.cap;
@@ -2122,6 +2141,7 @@ private:
     int* sort_hist_ = nullptr; int* sort_cursor_ = nullptr; int sort_nb_ = 2, sort_shift_ = 0; bool sort_clear_ = true;
     int* key_hist_ = nullptr; int* key_cursor_ = nullptr; int key_nb_ = 6;      // spawned rays by (origin leaf, direction cell); cleared with sort_hist_
     bool sort_spawned_ = true;
+    R* spawn_stage_ = nullptr;
     // cull tables (device) and what they were built for: any ray, camera rays, one per light
     std::vector<double> bound_;                                  // host: [n][4] bounding spheres (centre, radius) of the objects
     R* cull_general_ = nullptr; R* cull_eye_ = nullptr; std::vector<R*> cull_light_;
@@ -2369,7 +2389,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     for (int d = 0; d < sc_.n_leaves; d++) n_unbounded += std::isinf(bound_[(size_t)d * 4 + 3]) ? 1 : 0;
     cand_per_ray_ = std::min<int>(std::max(sc_.n_leaves, 1), (int)env_size("GMLRT_CAND_PER_RAY", 4) + n_unbounded);
     const double cand_bytes = cand_per_ray_ * (8.0 + sizeof(R));
-    const double node_bytes = (6 + 1 + NREC + 6) * sizeof(R) + 12 + nl;
+    const double node_bytes = (2 * RAY_WORDS + NREC + 6) * sizeof(R) + 8 + nl;      // ray record (+ its staging copy), rec, child, hit, order, occl
     const double shadow_bytes = nl * (8.0 * sizeof(R) + 16);
     const double per_sample = sum_mult * node_bytes + max_mult * (shadow_bytes + cand_bytes) + 3 * sizeof(R) + (kRobustPrimary ? 48 : 0);
     size_t free_b = 0, total_b = 0;
@@ -2389,17 +2409,19 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     auto take = [&](size_t bytes) { size_t o = off; off = align(off + bytes); return o; };
     struct LvOff { size_t ray, parent, hit, t, order, rec, child, occl; size_t cap; };
     std::vector<LvOff> lo(depth_eff_);
-    size_t max_cap = 0;
+    size_t max_cap = 0, stage_cap = 0;
     for (int l = 0; l < depth_eff_; l++) {
         size_t cap = (size_t)std::min((double)S0 * mult[l], 2.0e9);
         lo[l].cap = cap; max_cap = std::max(max_cap, cap);
-        lo[l].ray = take(6 * cap * sizeof(R)); lo[l].parent = take(cap * 4); lo[l].hit = take(cap * 4);
+        lo[l].ray = take(RAY_WORDS * cap * sizeof(R)); lo[l].parent = 0; lo[l].hit = take(cap * 4);
+        if (l > 0) stage_cap = std::max(stage_cap, cap);
         lo[l].t = take(cap * sizeof(R)); lo[l].order = take(cap * 4); lo[l].rec = take(NREC * cap * sizeof(R)); lo[l].child = take(6 * cap * sizeof(R));
         lo[l].occl = take(cap * std::max(nl, 1));
     }
     const size_t sq_cap = max_cap * std::max(nl, 1);
     size_t o_sq = take(8 * sq_cap * sizeof(R)), o_skip = take(sq_cap * 4), o_tgt = take(sq_cap * 4), o_first = take(sq_cap * 4), o_perm = take(sq_cap * 4), o_sort = take(2 * SORT_BINS_MAX * sizeof(int));
     size_t o_keysort = take(2 * (size_t)KEY_BINS_MAX * sizeof(int));
+    size_t o_stage = take(RAY_WORDS * stage_cap * sizeof(R));         // spawned rays wait here until k_keysort_scatter stores them sorted
     const size_t cand_cap = std::min<size_t>((size_t)((double)max_cap * cand_per_ray_ * (double)(1 << tile_shrink_)), (size_t)2000000000);
     size_t o_cray = take(cand_cap * 4), o_cobj = take(cand_cap * 4), o_ct = take(cand_cap * sizeof(R)), o_ccount = take(256);
     size_t o_samples = take(3 * S0 * sizeof(R));
@@ -2415,7 +2437,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     for (int l = 0; l < depth_eff_; l++) {
         Level<R>& L = levels_[l];
         L.cap = (int)lo[l].cap;
-        L.ray = (R*)(base + lo[l].ray); L.parent = (int*)(base + lo[l].parent); L.hit = (int*)(base + lo[l].hit);
+        L.ray = (R*)(base + lo[l].ray); L.hit = (int*)(base + lo[l].hit);
         L.t = (R*)(base + lo[l].t); L.order = (int*)(base + lo[l].order); L.rec = (R*)(base + lo[l].rec); L.child = (R*)(base + lo[l].child);
         occl_[l] = (unsigned char*)(base + lo[l].occl);
         L.ray64 = (kRobustPrimary && l == 0) ? (double*)(base + o_ray64) : nullptr;
@@ -2424,6 +2446,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     sq_.per_light = (int)max_cap; sq_.count = shadow_counts_; sq_.first = (int*)(base + o_first); sq_.perm = (int*)(base + o_perm);
     sort_hist_ = (int*)(base + o_sort); sort_cursor_ = sort_hist_ + SORT_BINS_MAX; sort_clear_ = true;
     key_hist_ = (int*)(base + o_keysort); key_cursor_ = key_hist_ + KEY_BINS_MAX;
+    spawn_stage_ = (R*)(base + o_stage);
     sort_nb_ = std::min(sc_.n_leaves + 1, SORT_BINS_MAX); sort_shift_ = 0;
     while (((std::max(sc_.n_leaves, 1) - 1) >> sort_shift_) + 2 > sort_nb_) sort_shift_++;
     cq_.ray = (int*)(base + o_cray); cq_.obj = (int*)(base + o_cobj); cq_.t = (void*)(base + o_ct); cq_.count = (int*)(base + o_ccount);
@@ -2501,19 +2524,18 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             const int cap_blocks = (levels_[l].cap + SHADE_THREADS - 1) / SHADE_THREADS;
             const int exact_grid = sms_ * 16;
             CU_TRY(cudaMemsetAsync(cq_.count, 0, 2 * sizeof(int), stream_));
-            ClosestSource<R> csrc{levels_[l], nullptr};
+            ClosestSource<R> csrc{levels_[l]};
             if (sort_clear_) {
                 CU_TRY(cudaMemsetAsync(sort_hist_, 0, SORT_BINS_MAX * sizeof(int), stream_));
                 CU_TRY(cudaMemsetAsync(key_hist_, 0, KEY_BINS_MAX * sizeof(int), stream_));
                 sort_clear_ = false;
             }
-            if (l > 0 && sort_spawned_) {                  // rays by (origin leaf, direction cell); the keys are in lv.hit, the permutation borrows
-                MARK(KC_SORT);                             // the shadow queue's (free until this level is shaded)
+            if (l > 0 && sort_spawned_) {                  // rays by (origin leaf, direction cell): keys in lv.hit, records in the staging buffer
+                MARK(KC_SORT);
                 k_keysort_hist<<<sms_ * 8, 256, 0, stream_>>>(levels_[l].hit, &ctr_->count[l], key_nb_, key_hist_);
                 k_sort_scan<<<1, 1024, 0, stream_>>>(key_nb_, key_hist_, key_cursor_);
-                k_keysort_scatter<<<sms_ * 8, 256, 0, stream_>>>(levels_[l].hit, &ctr_->count[l], key_nb_, key_cursor_, sq_.perm);
+                k_keysort_scatter<R><<<sms_ * 8, 256, 0, stream_>>>(levels_[l].hit, &ctr_->count[l], key_nb_, key_cursor_, spawn_stage_, levels_[l].ray);
                 totals_.launches += 3;
-                csrc.perm = sq_.perm;
             }
             if (l == 0) {                                  // camera rays: PIVOT family through the eye, robust re-tests in f32
                 MARK(KC_CLOSEST_PRIMARY);
@@ -2542,7 +2564,8 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             MARK(KC_SHADE);
             k_shade<R><<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
                 sc_, levels_[l], spawn ? levels_[l + 1] : levels_[l], sq_, occl_[l], ctr_, l, spawn ? 1 : 0,
-                (counting && l == 0) ? ids_ : nullptr, ty, map);
+                (counting && l == 0) ? ids_ : nullptr, ty, map,
+                spawn ? (sort_spawned_ ? spawn_stage_ : levels_[l + 1].ray) : nullptr);
             totals_.launches += 2;
             for (int li = 0; li < sc_.n_lights; li++) {    // per light: its shadow rays share a pivot (or an axis)
                 const bool axis = frame_light_[li].family == CULL_AXIS;
