@@ -81,7 +81,8 @@ template <typename R> struct Level {
                   //          the previous level | (1<<31 for the refraction slot).  32 bytes in f32: one sector per random read
     int* hit;     // [cap] device leaf index | face << 28, or -1
     R* t;         // [cap] T of the hit; during the scan: bit pattern of the smallest T so far (all ones = none)
-    int* order;   // [cap] scan scratch: smallest scan index among the hits that have the smallest T
+    int* order;   // scan scratch.  f64: [cap] smallest scan index among the hits that have the smallest T; f32: [cap] 64-bit keys
+                  //               (bits of T) << 32 | scan index, folded by one atomicMin (fold_hit)
     R* rec;       // [NREC][cap]
     R* child;     // [6][cap] colour returned by the reflection / refraction child
     double* ray64; // [6][cap] level 0 in f32 mode only: the camera ray before rounding to float
@@ -972,10 +973,13 @@ template <typename R> struct ClosestSource {                 // rays of one recu
     Level<R> lv;                                              // (levels >= 1 are stored sorted by origin object and direction cell)
     __device__ __forceinline__ int id(int i) const { return i; }
     __device__ __forceinline__ void load(int i, Ray<R>& out) const { load_ray(lv.ray, i, out); }
-    __device__ __forceinline__ void init(int i) const {       // no hit yet
+    __device__ __forceinline__ void init(int i) const {       // no hit yet (see fold_hit)
         lv.hit[i] = -1;
-        reinterpret_cast<typename BitsOf<R>::type*>(lv.t)[i] = ~(typename BitsOf<R>::type)0;
-        lv.order[i] = 0x7fffffff;
+        if constexpr (sizeof(R) == 4) reinterpret_cast<unsigned long long*>(lv.order)[i] = ~0ull;
+        else {
+            reinterpret_cast<unsigned long long*>(lv.t)[i] = ~0ull;
+            lv.order[i] = 0x7fffffff;
+        }
     }
 };
 
@@ -1214,28 +1218,66 @@ template <int KINDS> __device__ __forceinline__ bool exact_owns(int obj, int n_s
 // order.  Three passes over the candidates: (1) exact test, T of a hit into the queue and atomicMin into the ray's
 // record (hits have T > 0, so the bit pattern orders like the value); (2) among the hits that have the ray's
 // smallest T, atomicMin of the scan index; (3) the winner writes its hit code.
+// Folding a hit into the ray's record.  float32: one 64-bit atomicMin of (bits of T) << 32 | scan index does the
+// whole rule at once - smaller T first, then the smaller scan index - so a single pick pass follows.  float64: T alone
+// fills the 64 bits, so the scan index is folded by a second pass over the candidates (k_closest_order).
+template <typename R> __device__ __forceinline__ unsigned long long hit_key32(const DevScene<R>& sc, float t, int code) {
+    return ((unsigned long long)__float_as_uint(t) << 32) | (unsigned)sc.scan_of[code & HIT_LEAF_MASK];
+}
+template <typename R> __device__ __forceinline__ void fold_hit(const DevScene<R>& sc, const Level<R>& lv, int ri, R t, int code) {
+    if constexpr (sizeof(R) == 4) atomicMin(&reinterpret_cast<unsigned long long*>(lv.order)[ri], hit_key32(sc, t, code));
+    else atomicMin(&reinterpret_cast<unsigned long long*>(lv.t)[ri], BitsOf<R>::of(t));
+}
+
+constexpr int CAND_DEFER = 0x40000000;   // robust camera-ray pass: a sphere candidate left to the double-precision pass
+
 template <typename R, bool ROBUST, bool COUNT, int KINDS>
 __global__ void __launch_bounds__(EXACT_THREADS) k_exact_closest(const __grid_constant__ DevScene<R> sc, const __grid_constant__ Level<R> lv,
                                                                 const __grid_constant__ CandQueue cq, Counters* ctr) {
-    static_assert(!ROBUST || KINDS == EXACT_ALL, "the robust camera-ray test has one flavour");
-    typedef typename BitsOf<R>::type UB;
+    static_assert(!ROBUST || KINDS != EXACT_ALL, "the robust camera-ray test runs as SPHERES (float32, inline) then REST (double)");
     const int count = min(*cq.count, cq.cap);
-    UB* tbest = reinterpret_cast<UB*>(lv.t);
+    const int n_spheres = sc.kind_begin[K_SPHERE + 1];
     R* ct = reinterpret_cast<R*>(cq.t);
     unsigned long long n_exact = 0, n_flops = 0;
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
-        const int ri = cq.ray[k], obj = cq.obj[k];
+        const int ri = cq.ray[k];
+        int obj = cq.obj[k];
         if (KINDS == EXACT_REST && obj < 0) continue;          // a sphere candidate the SPHERES pass has already resolved to a miss
-        if (KINDS != EXACT_ALL && obj < sc.n_leaves && !exact_owns<KINDS>(obj, sc.kind_begin[K_SPHERE + 1])) continue;
+        bool deferred = false;
+        if (ROBUST && KINDS == EXACT_REST) { deferred = (obj & CAND_DEFER) != 0; obj &= ~CAND_DEFER; }
+        if (KINDS != EXACT_ALL && obj < sc.n_leaves && !deferred && !exact_owns<KINDS>(obj, n_spheres)) continue;
         int code = -1; R t = R(0);
         if (obj < sc.n_leaves) {                               // a padding record can only be reached by a NaN ray
-            if (COUNT) { n_exact++; n_flops += (unsigned)sc.obj_flops[obj]; }
-            Ray<R> w;
-            load_ray(lv.ray, ri, w);
+            if (COUNT && !deferred) { n_exact++; n_flops += (unsigned)sc.obj_flops[obj]; }
             bool h;
-            if constexpr (ROBUST) h = exact_hit<R, true>(sc, obj, w, lv.ray64, lv.cap, ri, t, code);
-            else h = exact_hit_kinds<R, KINDS>(sc, obj, w, t, code);
-            if (h) atomicMin(&tbest[ri], BitsOf<R>::of(t));
+            if constexpr (ROBUST && KINDS == EXACT_SPHERES) {
+                // float32 sphere test, trusted unless the discriminant is inside its rounding band or the origin is that
+                // close to the surface (see exact_hit<ROBUST>); those candidates go to the REST pass, in double
+                Ray<R> w, o;
+                load_ray(lv.ray, ri, w);
+                Mat34<R> M;
+                load_w2o(sc.w2o, obj, M);
+                to_object(M.m, w, o);
+                const R a = o.dx * o.dx + o.dy * o.dy + o.dz * o.dz;
+                const R hb = o.ox * o.dx + o.oy * o.dy + o.oz * o.dz;
+                const R oo = o.ox * o.ox + o.oy * o.oy + o.oz * o.oz;
+                const R c = oo - R(1);
+                const R pr = a * c;
+                const R disc = hb * hb - pr;
+                const R band = R(7.62939453125e-6) * (hb * hb + gm<R>::abs(pr));     // 2^-17
+                if (gm<R>::abs(disc) < band || gm<R>::abs(c) < R(7.62939453125e-6) * (oo + R(1))) { cq.obj[k] = obj | CAND_DEFER; continue; }
+                code = obj; h = false;
+                if (disc >= R(0)) { const R t0 = (-hb - gm<R>::sqrt(disc)) / a; if (t0 > R(0)) { t = t0; h = true; } }
+            } else if constexpr (ROBUST) {                     // REST: every non-sphere kind, and the deferred spheres, in double
+                float tf = 0.f;
+                h = hit_f64<R>(sc, deferred ? (int)K_SPHERE : kind_of(sc.kind_begin, obj), obj, lv.ray64, lv.cap, ri, tf, code);
+                t = (R)tf;
+            } else {
+                Ray<R> w;
+                load_ray(lv.ray, ri, w);
+                h = exact_hit_kinds<R, KINDS>(sc, obj, w, t, code);
+            }
+            if (h) fold_hit<R>(sc, lv, ri, t, code);
             else code = -1;
         }
         cq.obj[k] = code; ct[k] = t;
@@ -1243,6 +1285,7 @@ __global__ void __launch_bounds__(EXACT_THREADS) k_exact_closest(const __grid_co
     if (COUNT) { warp_add(&ctr->exact_tests, n_exact); warp_add(&ctr->exact_flops, n_flops); }
 }
 
+// float64 only: among the hits that have the ray's smallest T, the smallest scan index
 template <typename R>
 __global__ void __launch_bounds__(256) k_closest_order(const __grid_constant__ DevScene<R> sc, const __grid_constant__ Level<R> lv,
                                                       const __grid_constant__ CandQueue cq) {
@@ -1258,18 +1301,23 @@ __global__ void __launch_bounds__(256) k_closest_order(const __grid_constant__ D
     }
 }
 
+// the winner writes its hit code (float32: and its T, which the key held until now)
 template <typename R>
 __global__ void __launch_bounds__(256) k_closest_pick(const __grid_constant__ DevScene<R> sc, const __grid_constant__ Level<R> lv,
                                                      const __grid_constant__ CandQueue cq) {
     typedef typename BitsOf<R>::type UB;
     const int count = min(*cq.count, cq.cap);
-    const UB* tbest = reinterpret_cast<const UB*>(lv.t);
     const R* ct = reinterpret_cast<const R*>(cq.t);
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
         const int code = cq.obj[k];
         if (code < 0) continue;
         const int ri = cq.ray[k];
-        if (BitsOf<R>::of(ct[k]) == tbest[ri] && lv.order[ri] == sc.scan_of[code & HIT_LEAF_MASK]) lv.hit[ri] = code;
+        if constexpr (sizeof(R) == 4) {
+            if (hit_key32(sc, ct[k], code) == reinterpret_cast<const unsigned long long*>(lv.order)[ri]) { lv.hit[ri] = code; lv.t[ri] = ct[k]; }
+        } else {
+            const UB* tbest = reinterpret_cast<const UB*>(lv.t);
+            if (BitsOf<R>::of(ct[k]) == tbest[ri] && lv.order[ri] == sc.scan_of[code & HIT_LEAF_MASK]) lv.hit[ri] = code;
+        }
     }
 }
 
@@ -1279,9 +1327,9 @@ __global__ void __launch_bounds__(256) k_closest_pick(const __grid_constant__ De
 // tests the reference itself would have run up to its first occluder.
 template <typename R, bool COUNT, int KINDS>
 __global__ void __launch_bounds__(EXACT_THREADS) k_exact_shadow(const __grid_constant__ DevScene<R> sc, const __grid_constant__ ShadowQueue<R> sq,
-                                                               int base, const __grid_constant__ CandQueue cq, Counters* ctr) {
+                                                               int base, const __grid_constant__ CandQueue cq, Counters* ctr, unsigned char* occl) {
     const int count = min(*cq.count, cq.cap);
-    unsigned long long n_exact = 0, n_flops = 0;
+    unsigned long long n_exact = 0, n_flops = 0, n_occluded = 0;
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
         const int q = base + cq.ray[k], obj = cq.obj[k];
         if (obj >= sc.n_leaves || !exact_owns<KINDS>(obj, sc.kind_begin[K_SPHERE + 1]) || obj == sq.skip[q]) continue;
@@ -1292,9 +1340,13 @@ __global__ void __launch_bounds__(EXACT_THREADS) k_exact_shadow(const __grid_con
         w.ox = rec[0]; w.oy = rec[1]; w.oz = rec[2]; w.dx = rec[3]; w.dy = rec[4]; w.dz = rec[5];
         R t; int code;
         if (!exact_hit_kinds<R, KINDS>(sc, obj, w, t, code)) continue;
-        if (t * rec[7] < rec[6]) atomicMin(&sq.first[q], sc.scan_of[obj]);   // T * |incoming direction| < distance to the light
+        if (t * rec[7] < rec[6]) {                             // T * |incoming direction| < distance to the light
+            if (COUNT) atomicMin(&sq.first[q], sc.scan_of[obj]);   // k_shadow_finish sets the flag and credits the reference's tests
+            else if (atomicExch(&sq.first[q], 0) == 0x7fffffff) { occl[sq.target[q]] = 1; n_occluded++; }   // first occluder found: flag it here
+        }
     }
     if (COUNT) { warp_add(&ctr->exact_tests, n_exact); warp_add(&ctr->exact_flops, n_flops); }
+    else warp_add(&ctr->shadow_occluded, n_occluded);
 }
 
 // ------------------------------------------------------------------ shadow rays by shaded object
@@ -1309,9 +1361,10 @@ constexpr int SORT_BINS_MAX = 4096, SORT_CHUNK = 4096, SORT_THREADS = 256;
 __device__ __forceinline__ int sort_bin(int key, int shift, int nb) { return key < 0 ? nb - 1 : min(key >> shift, nb - 2); }
 
 template <typename R>
-__global__ void __launch_bounds__(SORT_THREADS) k_sort_hist(const __grid_constant__ ShadowQueue<R> sq, int light, int shift, int nb, int* hist) {
+__global__ void __launch_bounds__(SORT_THREADS) k_sort_hist(const __grid_constant__ ShadowQueue<R> sq, int light, int shift, int nb, int* hist, Counters* ctr) {
     __shared__ int h[SORT_BINS_MAX];
     const int n = sq.count[light], base = light * sq.per_light;
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ctr->rays_shadow, (unsigned long long)n);
     const int nchunks = (n + SORT_CHUNK - 1) / SORT_CHUNK;
     for (int b = threadIdx.x; b < nb; b += SORT_THREADS) h[b] = 0;
     __syncthreads();
@@ -1386,7 +1439,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k_sort_scatter(const __grid_cons
 // point into one cone, so the packet stage applies to them too.  Up to 2^17 bins: histogram and cursors in global
 // memory, one warp-aggregated atomic per distinct key of a warp.  The order inside a bin is not deterministic; the
 // result of a ray does not depend on which warp tests it.
-constexpr int KEY_BINS_MAX = 1 << 17;
+constexpr int KEY_BINS_MAX = 1 << 19;
 
 __device__ __forceinline__ void key_peers(int key, bool valid, unsigned& peers, int& rank, int& leader) {
     const unsigned act = __ballot_sync(0xffffffffu, valid);
@@ -1437,7 +1490,6 @@ template <typename R, bool COUNT>
 __global__ void __launch_bounds__(256) k_shadow_finish(const __grid_constant__ DevScene<R> sc, const __grid_constant__ ShadowQueue<R> sq,
                                                       int light, unsigned char* occl, Counters* ctr) {
     const int n = sq.count[light], base = light * sq.per_light;
-    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ctr->rays_shadow, (unsigned long long)n);
     unsigned long long n_occluded = 0, cred_tests = 0, cred_flops = 0;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const int q = base + i;
@@ -2389,7 +2441,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     for (int d = 0; d < sc_.n_leaves; d++) n_unbounded += std::isinf(bound_[(size_t)d * 4 + 3]) ? 1 : 0;
     cand_per_ray_ = std::min<int>(std::max(sc_.n_leaves, 1), (int)env_size("GMLRT_CAND_PER_RAY", 4) + n_unbounded);
     const double cand_bytes = cand_per_ray_ * (8.0 + sizeof(R));
-    const double node_bytes = (2 * RAY_WORDS + NREC + 6) * sizeof(R) + 8 + nl;      // ray record (+ its staging copy), rec, child, hit, order, occl
+    const double node_bytes = (2 * RAY_WORDS + NREC + 8) * sizeof(R) + 12 + nl;      // ray record (+ its staging copy), rec, child, hit, order, occl
     const double shadow_bytes = nl * (8.0 * sizeof(R) + 16);
     const double per_sample = sum_mult * node_bytes + max_mult * (shadow_bytes + cand_bytes) + 3 * sizeof(R) + (kRobustPrimary ? 48 : 0);
     size_t free_b = 0, total_b = 0;
@@ -2415,7 +2467,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
         lo[l].cap = cap; max_cap = std::max(max_cap, cap);
         lo[l].ray = take(RAY_WORDS * cap * sizeof(R)); lo[l].parent = 0; lo[l].hit = take(cap * 4);
         if (l > 0) stage_cap = std::max(stage_cap, cap);
-        lo[l].t = take(cap * sizeof(R)); lo[l].order = take(cap * 4); lo[l].rec = take(NREC * cap * sizeof(R)); lo[l].child = take(6 * cap * sizeof(R));
+        lo[l].t = take(cap * sizeof(R)); lo[l].order = take(cap * 8); lo[l].rec = take(NREC * cap * sizeof(R)); lo[l].child = take(6 * cap * sizeof(R));
         lo[l].occl = take(cap * std::max(nl, 1));
     }
     const size_t sq_cap = max_cap * std::max(nl, 1);
@@ -2543,8 +2595,15 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
                     csrc, &ctr_->count[l], cull_eye_, frame_eye_, sc_.n_cull, cq_, ctr_, chunk_objs_, resident_);
                 MARK(KC_EXACT);
                 if (kRobustPrimary) {
-                    if (counting) k_exact_closest<R, kRobustPrimary, true, EXACT_ALL><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
-                    else k_exact_closest<R, kRobustPrimary, false, EXACT_ALL><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
+                    // float32 spheres inline; then the double-precision pass: other kinds + the spheres the first pass deferred
+                    if (counting) {
+                        if (have_spheres) k_exact_closest<R, kRobustPrimary, true, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
+                        k_exact_closest<R, kRobustPrimary, true, EXACT_REST><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
+                    } else {
+                        if (have_spheres) k_exact_closest<R, kRobustPrimary, false, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
+                        k_exact_closest<R, kRobustPrimary, false, EXACT_REST><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
+                    }
+                    totals_.launches += have_spheres ? 1 : 0;
                 } else {
                     int erc = exact_closest(l, counting);
                     if (erc) return erc;
@@ -2557,7 +2616,8 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
                 int erc = exact_closest(l, counting);
                 if (erc) return erc;
             }
-            k_closest_order<R><<<exact_grid, 256, 0, stream_>>>(sc_, levels_[l], cq_);
+            if (sizeof(R) == 8) k_closest_order<R><<<exact_grid, 256, 0, stream_>>>(sc_, levels_[l], cq_);
+            else totals_.launches--;
             k_closest_pick<R><<<exact_grid, 256, 0, stream_>>>(sc_, levels_[l], cq_);
             totals_.launches += 3;
             const bool spawn = l + 1 < depth_eff_;
@@ -2572,7 +2632,7 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
                 ShadowSource<R> ssrc{sq_, li * sq_.per_light};
                 CU_TRY(cudaMemsetAsync(cq_.count, 0, 2 * sizeof(int), stream_));
                 MARK(KC_SORT);
-                k_sort_hist<R><<<sms_ * 4, SORT_THREADS, 0, stream_>>>(sq_, li, sort_shift_, sort_nb_, sort_hist_);
+                k_sort_hist<R><<<sms_ * 4, SORT_THREADS, 0, stream_>>>(sq_, li, sort_shift_, sort_nb_, sort_hist_, ctr_);
                 k_sort_scan<<<1, 1024, 0, stream_>>>(sort_nb_, sort_hist_, sort_cursor_);
                 k_sort_scatter<R><<<sms_ * 4, SORT_THREADS, 0, stream_>>>(sq_, li, sort_shift_, sort_nb_, sort_cursor_);
                 totals_.launches += 3;
@@ -2584,13 +2644,13 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
                 MARK(KC_EXACT);
                 const int sbase = li * sq_.per_light;
                 if (counting) {
-                    if (have_spheres) k_exact_shadow<R, true, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, sq_, sbase, cq_, ctr_);
-                    if (have_rest) k_exact_shadow<R, true, EXACT_REST><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, sq_, sbase, cq_, ctr_);
+                    if (have_spheres) k_exact_shadow<R, true, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, sq_, sbase, cq_, ctr_, occl_[l]);
+                    if (have_rest) k_exact_shadow<R, true, EXACT_REST><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, sq_, sbase, cq_, ctr_, occl_[l]);
                     k_shadow_finish<R, true><<<wide, 256, 0, stream_>>>(sc_, sq_, li, occl_[l], ctr_);
-                } else {
-                    if (have_spheres) k_exact_shadow<R, false, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, sq_, sbase, cq_, ctr_);
-                    if (have_rest) k_exact_shadow<R, false, EXACT_REST><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, sq_, sbase, cq_, ctr_);
-                    k_shadow_finish<R, false><<<wide, 256, 0, stream_>>>(sc_, sq_, li, occl_[l], ctr_);
+                } else {                                   // the exact kernels set the occlusion flags themselves
+                    if (have_spheres) k_exact_shadow<R, false, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, sq_, sbase, cq_, ctr_, occl_[l]);
+                    if (have_rest) k_exact_shadow<R, false, EXACT_REST><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, sq_, sbase, cq_, ctr_, occl_[l]);
+                    totals_.launches--;
                 }
                 totals_.launches += (have_spheres && have_rest) ? 1 : 0;
                 totals_.launches += 3;
