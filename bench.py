@@ -157,7 +157,7 @@ def main():
     ap.add_argument("--depth", type=int, default=None)
     ap.add_argument("--precision", default="f32", choices=["f32", "f64"])
     ap.add_argument("--ref-crop", type=int, nargs=2, default=[240, 140])
-    ap.add_argument("--cpu-crop", type=int, nargs=2, default=[480, 260])
+    ap.add_argument("--cpu-crop", type=int, nargs=2, default=[1280, 720])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--parts", type=int, default=1, help="diagnostic (1 GPU): render only part 0 of PARTS row-band parts, i.e. one rank's share of an N-GPU frame")
     ap.add_argument("--gather", default="ipc", choices=["ipc", "nccl"],
@@ -235,7 +235,7 @@ def main():
     cst = ctx.trace()
     ctx.set_counting(False)
     counts = torch.tensor([cst.rays_primary, cst.rays_reflect, cst.rays_refract, cst.rays_shadow, cst.shadow_occluded,
-                           cst.leaf_tests, int(cst.flops_credited / 1e3), cst.cull_tests, cst.exact_tests, int(cst.flops_executed / 1e3), cst.packet_tests, cst.cull_tests_family[0], cst.cull_tests_family[1], cst.cull_tests_family[2]],
+                           cst.leaf_tests, int(cst.flops_credited / 1e3), cst.cull_tests, cst.exact_tests, int(cst.flops_executed / 1e3), cst.packet_tests, cst.cull_tests_family[0], cst.cull_tests_family[1], cst.cull_tests_family[2], cst.rays_hit, cst.exact_tests_shadow],
                           dtype=torch.int64, device=f"cuda:{local_rank}")
     if dist is not None:
         dist.all_reduce(counts)
@@ -340,32 +340,88 @@ def main():
     fp32_derived = props.multi_processor_count * 128 * 2 * sm_max_mhz * 1e6 / 1e12                  # TFLOP/s per GPU
     fp32_measured = cuda.measure_fp32_tflops(local_rank)                                           # FFMA-chain microbenchmark, this box
     fp32_peak = (fp32_measured if fp32_measured > 0 else fp32_derived) * world
-    # every scan kernel class (cull x3, exact, sort) and, for the roofline, the dominant single kernel
     names = cuda.Stats.KERNEL_CLASSES
+    hbm_peak = float(peaks.get("hbm_gbs") or 6447.5) * world                # GB/s: MEASURED_PEAKS.json (driver-written), else the recipe's figure
+    hbm_peak_kind = "MEASURED_PEAKS.json hbm_gbs (torch copy, read+write)" if peaks.get("hbm_gbs") else "fallback 6447.5 GB/s"
+    # ---- what every kernel class moves / executes per frame (the models are stated in DESIGN.md section 4) ----
+    import struct as _struct
+    nl = _struct.unpack_from("<I", blob, 120)[0]                           # gmlrt_blob_header.n_lights
+    wb = 4 if args.precision == "f32" else 8                               # bytes per word of the arithmetic type
+    P, RF, RR, S, NH = (float(counts[k]) for k in (0, 1, 2, 3, 14))
+    C, CH = P + RF + RR, RF + RR                                           # closest-hit queries; spawned (child) rays
+    Xs = float(counts[15]); Xc = float(counts[8]) - Xs                     # exact tests: shadow / closest candidates
+    model_bytes = {
+        0: P * (8 * wb + (48 if args.precision == "f32" else 0)),          # gen: ray record (+ the float64 copy the robust re-tests read)
+        4: C * (8 * wb + 4 + wb) + NH * (16 * wb + 6 * wb) + S * (8 * wb + 9) + CH * (8 * wb + 4),   # shade: ray, hit, T in; rec, child slots, shadow and child records out
+        5: C * (8 * wb + 4) + NH * (16 * wb + nl) + CH * 6 * wb + P * 3 * wb,                       # resolve: ray, hit, rec, flags in; colour to the parent / the samples
+        6: P * 3 * wb + P,                                                 # pixels: 4 samples x 3 channels in, RGBA8 out
+        7: Xc * ((8 + 8 * wb + 4 + wb) + (8 + wb + 8 + 4 + wb)) + Xs * (8 + 8 * wb + 8),           # exact: candidate + ray record + result; pick pass; shadow candidates
+        8: S * 12 + CH * (8 + 16 * wb),                                    # sort: keys twice + permutation; key sort moves the 8-word records
+    }
+    cull_flops_all = 15.0 * float(counts[11]) + 7.0 * float(counts[12] + counts[13]) + 20.0 * float(counts[10])
+    by_class = {}
+    for k in range(9):
+        ms = class_ms[k] / args.steps
+        if ms <= 0:
+            continue
+        if k in model_bytes:
+            gbs = model_bytes[k] / (ms * 1e-3) / 1e9
+            by_class[names[k]] = {"bound": "hbm", "ms_per_frame": ms, "bytes_per_frame": model_bytes[k], "achieved": gbs, "unit": "GB/s", "frac": gbs / hbm_peak}
+    cull_ms = sum(class_ms[k] for k in (1, 2, 3)) / args.steps
+    if cull_ms > 0:
+        tf = cull_flops_all / (cull_ms * 1e-3) / 1e12
+        by_class["cull (k_cull, all three families)"] = {"bound": "fp32", "ms_per_frame": cull_ms, "flops_per_frame": cull_flops_all, "achieved": tf,
+                                                         "unit": "TFLOP/s", "frac": tf / fp32_peak if fp32_peak else None}
+    if class_ms[2] > 0:       # k_cull<GENERAL> alone: its per-ray tests are counted separately (15 flops each); its packet tests are not, so this is a floor
+        tf = 15.0 * float(counts[11]) * args.steps / (class_ms[2] * 1e-3) / 1e12
+        by_class["cull_secondary (k_cull<GENERAL>), per-ray tests only"] = {"bound": "fp32", "ms_per_frame": class_ms[2] / args.steps, "achieved": tf,
+                                                                            "unit": "TFLOP/s", "frac": tf / fp32_peak if fp32_peak else None}
     scan_ms = sum(class_ms[k] for k in (1, 2, 3, 7, 8))
-    scan_launches = sum(class_launches[k] for k in (1, 2, 3, 7, 8))
-    scan_tflops = flops_frame * args.steps / (scan_ms * 1e-3) / 1e12 if scan_ms > 0 else 0.0
-    # per-ray cull kernels: flops per test 15 (GENERAL), 7 (PIVOT / AXIS); camera rays are all PIVOT, reflection /
-    # refraction rays all GENERAL; the shadow class mixes PIVOT and AXIS launches
-    cull_flops = {1: 7.0 * float(counts[12]) * (class_ms[1] / max(class_ms[1] + class_ms[3], 1e-9)), 2: 15.0 * float(counts[11])}
-    dom = max((1, 2, 3, 4, 5, 7, 8), key=lambda k: class_ms[k])
-    dom_kernel = {1: "k_cull<PIVOT> over camera rays", 2: "k_cull<GENERAL> over reflection / refraction rays", 3: "k_cull<PIVOT|AXIS> over shadow rays",
-                  4: "k_shade", 5: "k_resolve", 7: "k_exact_* (exact tests on the cull survivors)", 8: "k_sort_*"}[dom]
-    if dom == 2 and class_ms[2] > 0:
-        achieved = cull_flops[2] * args.steps / (class_ms[2] * 1e-3) / 1e12
-        dom_launch_ms = class_ms[2] / max(class_launches[2], 1)
-        dom_flops_launch = cull_flops[2] * args.steps / max(class_launches[2], 1)
-    elif world > 1:                         # per-kernel events are an N = 1 tool: quote the executed flops of the whole frame over N GPUs
-        dom_kernel = f"whole frame on {world} GPUs (per-kernel timing is off at N > 1; see the N = 1 line)"
-        achieved, dom_launch_ms, dom_flops_launch = flops_frame / (ms_step * 1e-3) / 1e12, ms_step, flops_frame
-    else:                                   # no single FP32-bound kernel dominates: quote the whole scan
-        achieved, dom_launch_ms, dom_flops_launch = scan_tflops, scan_ms / max(scan_launches, 1), flops_frame * args.steps / max(scan_launches, 1)
+    # ---- the dominant single kernel: classes 0, 1, 2, 4, 5, 6 are one kernel each (3, 7, 8 are groups of smaller ones) ----
+    kernel_of = {0: "k_gen", 1: "k_cull<PIVOT, ClosestSource> (camera rays)", 2: "k_cull<GENERAL, ClosestSource> (reflection / refraction rays)",
+                 4: "k_shade", 5: "k_resolve", 6: "k_pixels"}
     traffic = None
-    try:
-        if dom == 2 and args.config == "spheres1024" and (W, H, args.depth, world) == (3840, 2160, 3, 1):   # the captured workload
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "scan_traffic.json"))).get("dram_bytes_per_launch")
-    except Exception:
-        pass
+    if world > 1:             # per-kernel events are an N = 1 tool
+        dom = None
+        roof = {"bound": "hbm", "achieved": None, "peak": hbm_peak, "unit": "GB/s", "frac": None, "traffic": None,
+                "kernel": f"per-kernel timing is off at N = {world}; see the N = 1 line"}
+    else:
+        dom = max(kernel_of, key=lambda k: class_ms[k])
+        launches_dom = max(class_launches[dom], 1)
+        if dom in model_bytes:
+            per_launch = model_bytes[dom] * args.steps / launches_dom
+            ach = model_bytes[dom] * args.steps / (class_ms[dom] * 1e-3) / 1e9
+            roof = {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak, "peak_kind": hbm_peak_kind,
+                    "kernel_bytes_per_launch": per_launch}
+        else:
+            fl = (15.0 * float(counts[11])) if dom == 2 else 7.0 * float(P) * 0 + 7.0 * float(counts[12]) * (class_ms[1] / max(class_ms[1] + class_ms[3], 1e-9))
+            ach = fl * args.steps / (class_ms[dom] * 1e-3) / 1e12
+            roof = {"bound": "fp32", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach / fp32_peak if fp32_peak else None,
+                    "peak_kind": "measured: FFMA-chain microbenchmark on this GPU (gmlrt_measure_fp32_tflops)" if fp32_measured > 0 else "derived",
+                    "kernel_flops_per_launch": fl * args.steps / launches_dom}
+        roof.update({"kernel": kernel_of[dom], "kernel_ms_per_launch": class_ms[dom] / launches_dom,
+                     "kernel_share_of_step": class_ms[dom] / max(sum(class_ms), 1e-9)})
+        try:                  # DRAM bytes per launch of that kernel from the committed ncu --set full capture of this same workload
+            tj = json.load(open(os.path.join(ROOT, "profiles", "dominant_traffic.json")))
+            if tj.get("kernel_class") == names[dom] and args.config == "spheres1024" and (W, H, args.depth) == (3840, 2160, 3) and args.precision == "f32":
+                traffic = tj.get("dram_bytes_per_launch")
+        except Exception:
+            pass
+        roof["traffic"] = traffic
+    roof.update({
+        "note": "dominant single kernel by CUDA-event time inside the timed region (events before every launch on the library's stream).  HBM-bound "
+                "kernels: achieved = ALGORITHMIC bytes (per-ray record sizes x the frame's ray counts from the counting pass, DESIGN.md 4) / event "
+                "time, peak = measured copy bandwidth.  FP32-bound kernels (k_cull): achieved = flops EXECUTED (device counters: cull tests x 15 / 7 / 7 "
+                "flops GENERAL / PIVOT / AXIS, packet tests x 20) / event time, peak = FFMA microbenchmark.  by_class has every class.  The "
+                "reference's all-pairs scan would execute flops_bruteforce_equivalent for the same queries; the packet and cull stages remove "
+                "almost all of it, so bruteforce_equivalent_tflops is a speed-up figure, NOT a roofline fraction.",
+        "by_class": by_class,
+        "fp32_peak_tflops": fp32_peak, "fp32_peak_derived": fp32_derived * world,
+        "scan_counters_per_frame": {"cull_tests": int(counts[7]), "cull_tests_by_family": {"general": int(counts[11]), "pivot": int(counts[12]), "axis": int(counts[13])},
+                                    "packet_tests": int(counts[10]), "exact_tests": int(counts[8]), "exact_tests_shadow": int(counts[15]),
+                                    "flops_executed": flops_frame},
+        "flops_bruteforce_equivalent": flops_credited_frame, "leaf_tests_bruteforce_equivalent": int(counts[5]),
+        "bruteforce_equivalent_tflops": flops_credited_frame * args.steps / (scan_ms * 1e-3) / 1e12 if scan_ms > 0 else None})
     line = {
         "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_step, "frame_ms": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -377,30 +433,13 @@ def main():
                                    ("finished rows stored by k_pixels into GPU 0's frame over NVLink (CUDA IPC), no collective" if use_ipc
                                     else "NCCL reduce of disjoint bands to rank 0")) if world > 1 else "1 GPU"},
         "rays_per_frame": {"primary": int(counts[0]), "reflect": int(counts[1]), "refract": int(counts[2]), "shadow": int(counts[3]),
-                           "shadow_occluded": int(counts[4])},
+                           "shadow_occluded": int(counts[4]), "hit": int(counts[14])},
         "gpu_launches": launches,
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "frame_ms": e2e_ms, "h2d_bytes_per_step": len(blob), "d2h_bytes_per_step": W * H * 4,
                 "phase_ms": {k: v / e2e_steps for k, v in phase_ms.items()}, "upload_ms_each": [round(x, 3) for x in upload_each]},
         "kernel_ms_per_frame": {names[k]: class_ms[k] / args.steps for k in range(9)},
-        "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak if fp32_peak else None,
-                     "traffic": traffic,
-                     "kernel": dom_kernel, "kernel_ms_per_launch": dom_launch_ms, "kernel_flops_per_launch": dom_flops_launch,
-                     "kernel_share_of_step": class_ms[dom] / max(sum(class_ms), 1e-9),
-                     "peak_kind": "measured: FFMA-chain microbenchmark on this GPU (gmlrt_measure_fp32_tflops)" if fp32_measured > 0 else "derived",
-                     "peak_derived": fp32_derived * world,
-                     "note": "dominant kernel by CUDA-event time in the timed region.  achieved = flops it EXECUTES (device counters: "
-                             "per-ray cull tests x 15 flops for the GENERAL family = 7 FFMA + 1 FADD) / its event time.  whole_scan gives "
-                             "the same for all scan kernels together (cull: 15 / 7 / 7 flops per test GENERAL / PIVOT / AXIS; packet tests "
-                             "20; exact tests: SURVEY 8(d) table - sphere 56, plane 47, cube 81, cylinder 74, cone 70).  The reference's "
-                             "all-pairs scan would execute flops_bruteforce_equivalent for the same queries; the cull and packet stages "
-                             "remove most of it, so bruteforce_equivalent_tflops is a speed-up figure, NOT a roofline fraction.",
-                     "whole_scan": {"tflops": scan_tflops, "frac": scan_tflops / fp32_peak if fp32_peak else None, "ms_per_frame": scan_ms / args.steps,
-                                    "flops_per_frame": flops_frame, "cull_tests_per_frame": int(counts[7]),
-                                    "cull_tests_by_family": {"general": int(counts[11]), "pivot": int(counts[12]), "axis": int(counts[13])},
-                                    "packet_tests_per_frame": int(counts[10]), "exact_tests_per_frame": int(counts[8])},
-                     "flops_bruteforce_equivalent": flops_credited_frame, "leaf_tests_bruteforce_equivalent": int(counts[5]),
-                     "bruteforce_equivalent_tflops": flops_credited_frame * args.steps / (scan_ms * 1e-3) / 1e12 if scan_ms > 0 else None},
+        "roofline": roof,
     }
     if world == 1 and not args.no_cpu_baseline:
         import oracle

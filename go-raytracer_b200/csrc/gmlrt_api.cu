@@ -306,8 +306,8 @@ static int trace_once(gmlrt_ctx* c, gmlrt_stats* stats, bool& overflow) {
         int rc = r->fetch_totals(t, err);
         if (rc != GMLRT_OK) return fail(c, rc, err);
         sum.rays_primary += t.rays_primary; sum.rays_reflect += t.rays_reflect; sum.rays_refract += t.rays_refract;
-        sum.rays_shadow += t.rays_shadow; sum.shadow_occluded += t.shadow_occluded; sum.launches += t.launches;
-        sum.shadow_tests += t.shadow_tests; sum.shadow_flops += t.shadow_flops; sum.exact_tests += t.exact_tests; sum.exact_flops += t.exact_flops; sum.packet_tests += t.packet_tests;
+        sum.rays_shadow += t.rays_shadow; sum.shadow_occluded += t.shadow_occluded; sum.rays_hit += t.rays_hit; sum.launches += t.launches;
+        sum.shadow_tests += t.shadow_tests; sum.shadow_flops += t.shadow_flops; sum.exact_tests += t.exact_tests; sum.exact_tests_shadow += t.exact_tests_shadow; sum.exact_flops += t.exact_flops; sum.packet_tests += t.packet_tests;
         for (int k = 0; k < 3; k++) sum.cull_by_family[k] += t.cull_by_family[k];
         for (int k = 0; k < KC_COUNT; k++) { sum.ms_class[k] = std::max(sum.ms_class[k], t.ms_class[k]); sum.launches_class[k] += t.launches_class[k]; }
         sum.error |= t.error; overflow = overflow || t.overflow;
@@ -316,7 +316,7 @@ static int trace_once(gmlrt_ctx* c, gmlrt_stats* stats, bool& overflow) {
         std::memset(stats, 0, sizeof *stats);
         stats->ms_total = ms; stats->ms_kernels = ms;
         stats->rays_primary = sum.rays_primary; stats->rays_reflect = sum.rays_reflect; stats->rays_refract = sum.rays_refract;
-        stats->rays_shadow = sum.rays_shadow; stats->shadow_occluded = sum.shadow_occluded;
+        stats->rays_shadow = sum.rays_shadow; stats->shadow_occluded = sum.shadow_occluded; stats->rays_hit = sum.rays_hit;
         stats->kernel_launches = sum.launches; stats->n_devices = (uint32_t)nd; stats->n_leaves = (uint32_t)c->scene.n_objects;
         // credited work: a closest-hit query tests every leaf; a shadow query is credited
         // with the tests its lane ran up to its own first occluder (counting mode only)
@@ -334,7 +334,7 @@ static int trace_once(gmlrt_ctx* c, gmlrt_stats* stats, bool& overflow) {
         stats->cull_tests = sum.cull_by_family[0] + sum.cull_by_family[1] + sum.cull_by_family[2];
         stats->packet_tests = sum.packet_tests;
         for (int k = 0; k < 3; k++) stats->cull_tests_family[k] = sum.cull_by_family[k];
-        stats->exact_tests = sum.exact_tests;
+        stats->exact_tests = sum.exact_tests; stats->exact_tests_shadow = sum.exact_tests_shadow;
         stats->flops_executed = 15.0 * (double)sum.cull_by_family[0] + 7.0 * (double)(sum.cull_by_family[1] + sum.cull_by_family[2]) +
                                 20.0 * (double)sum.packet_tests + (double)sum.exact_flops;
         for (int k = 0; k < KC_COUNT; k++) { stats->ms_class[k] = sum.ms_class[k]; stats->launches_class[k] = sum.launches_class[k]; }

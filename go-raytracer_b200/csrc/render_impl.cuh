@@ -107,9 +107,10 @@ struct Counters {                  // device-resident, zeroed per trace
     unsigned long long cull_tests[3];   // executed per-ray cull tests by family (GENERAL, PIVOT, AXIS)
     unsigned long long packet_tests;    // executed per-warp packet tests (one lane x one object)
     unsigned long long dbg[8];          // GMLRT_DEBUG_PACKETS: warp blocks, usable, objects offered, survivors
-    unsigned long long rays_reflect, rays_refract, rays_shadow, shadow_occluded;
+    unsigned long long rays_reflect, rays_refract, rays_shadow, shadow_occluded, rays_hit;
     unsigned long long shadow_tests, shadow_flops;   // credited: the reference's scan up to its first occluder (counting mode)
     unsigned long long exact_tests, exact_flops;     // executed second-phase tests and their table flops (counting mode)
+    unsigned long long exact_tests_shadow;           // ... the part of exact_tests that k_exact_shadow ran
 };
 
 template <typename R> struct Ray { R ox, oy, oz, dx, dy, dz; };
@@ -1345,7 +1346,7 @@ __global__ void __launch_bounds__(EXACT_THREADS) k_exact_shadow(const __grid_con
             else if (atomicExch(&sq.first[q], 0) == 0x7fffffff) { occl[sq.target[q]] = 1; n_occluded++; }   // first occluder found: flag it here
         }
     }
-    if (COUNT) { warp_add(&ctr->exact_tests, n_exact); warp_add(&ctr->exact_flops, n_flops); }
+    if (COUNT) { warp_add(&ctr->exact_tests, n_exact); warp_add(&ctr->exact_flops, n_flops); warp_add(&ctr->exact_tests_shadow, n_exact); }
     else warp_add(&ctr->shadow_occluded, n_occluded);
 }
 
@@ -1939,8 +1940,9 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
 // sample buffer at level 0.
 template <typename R>
 __global__ void __launch_bounds__(SHADE_THREADS) k_resolve(DevScene<R> sc, Level<R> lv, Level<R> prev, const unsigned char* occl,
-                                                           const Counters* ctr, int level, R* samples, int sample_cap) {
+                                                           Counters* ctr, int level, R* samples, int sample_cap) {
     const int n = ctr->count[level];
+    unsigned long long n_hit = 0;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const int cap = lv.cap;
     Ray<R> wr;
@@ -1952,6 +1954,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_resolve(DevScene<R> sc, Level
         const V3<R> a = ld3(sc.bg0), b = ld3(sc.bg1);
         out = mk(a.x + (b.x - a.x) * t, a.y + (b.y - a.y) * t, a.z + (b.z - a.z) * t);
     } else {
+        n_hit++;
         const R* rec = lv.rec + i;
         const V3<R> P = mk(rec[(REC_P + 0) * cap], rec[(REC_P + 1) * cap], rec[(REC_P + 2) * cap]);
         const V3<R> N = mk(rec[(REC_N + 0) * cap], rec[(REC_N + 1) * cap], rec[(REC_N + 2) * cap]);
@@ -1993,6 +1996,8 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_resolve(DevScene<R> sc, Level
         prev.child[(base + 0) * pc + pi] = out.x; prev.child[(base + 1) * pc + pi] = out.y; prev.child[(base + 2) * pc + pi] = out.z;
     }
     }  // grid-stride loop
+    n_hit = warp_sum_u64(n_hit);                           // (every lane reaches this point)
+    if ((threadIdx.x & 31) == 0 && n_hit) atomicAdd(&ctr->rays_hit, n_hit);
 }
 
 // mean of the 4 samples and quantisation: img.Set(x, y, total*0.25) -> Vec3.RGBA -> RGBAModel
@@ -2090,8 +2095,8 @@ public:
         ev_used_ = 0; ev_cls_.clear();
         out = totals_;
         out.rays_reflect = c.rays_reflect; out.rays_refract = c.rays_refract;
-        out.rays_shadow = c.rays_shadow; out.shadow_occluded = c.shadow_occluded;
-        out.shadow_tests = c.shadow_tests; out.shadow_flops = c.shadow_flops; out.exact_tests = c.exact_tests; out.exact_flops = c.exact_flops;
+        out.rays_shadow = c.rays_shadow; out.shadow_occluded = c.shadow_occluded; out.rays_hit = c.rays_hit;
+        out.shadow_tests = c.shadow_tests; out.shadow_flops = c.shadow_flops; out.exact_tests = c.exact_tests; out.exact_flops = c.exact_flops; out.exact_tests_shadow = c.exact_tests_shadow;
         for (int k = 0; k < 3; k++) out.cull_by_family[k] = c.cull_tests[k];
         out.packet_tests = c.packet_tests;
         out.error = c.error; out.overflow = c.overflow;

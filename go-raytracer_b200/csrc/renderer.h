@@ -15,10 +15,10 @@ namespace gmlrt {
 enum KernelClass { KC_GEN = 0, KC_CLOSEST_PRIMARY = 1, KC_CLOSEST = 2, KC_SHADOW = 3, KC_SHADE = 4, KC_RESOLVE = 5, KC_PIXELS = 6, KC_EXACT = 7, KC_SORT = 8, KC_COUNT = 9 };
 
 struct TraceTotals {                   // summed over the tiles a device rendered
-    unsigned long long rays_primary = 0, rays_reflect = 0, rays_refract = 0, rays_shadow = 0, shadow_occluded = 0;
+    unsigned long long rays_primary = 0, rays_reflect = 0, rays_refract = 0, rays_shadow = 0, shadow_occluded = 0, rays_hit = 0;
     unsigned long long shadow_tests = 0, shadow_flops = 0;   // credited (reference scan order), counting mode
     unsigned long long cull_by_family[3] = {0, 0, 0}, packet_tests = 0;   // executed per-ray cull tests (GENERAL, PIVOT, AXIS) and per-warp packet tests
-    unsigned long long cull_tests = 0, exact_tests = 0, exact_flops = 0;   // executed: first-phase (all pairs) and second-phase tests
+    unsigned long long cull_tests = 0, exact_tests = 0, exact_flops = 0, exact_tests_shadow = 0;   // executed: first-phase (all pairs) and second-phase tests
     double ms_class[KC_COUNT] = {0, 0, 0, 0, 0, 0, 0, 0, 0};         // profiling mode: device time per kernel class
     unsigned long long launches_class[KC_COUNT] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
     unsigned long long launches = 0;

@@ -195,6 +195,8 @@ typedef struct gmlrt_stats {
     uint64_t launches_class[9]; /* ... and launches per class */
     uint64_t packet_tests;      /* executed: per-warp packet tests (one lane x one object) */
     uint64_t cull_tests_family[3]; /* cull_tests split by family: GENERAL (reflection / refraction rays), PIVOT, AXIS */
+    uint64_t rays_hit;          /* closest-hit queries (primary + reflect + refract) that hit something = rays shaded */
+    uint64_t exact_tests_shadow; /* the part of exact_tests run for shadow rays (counting mode) */
 } gmlrt_stats;
 
 /* Create a context on `n` devices (`devices` = CUDA ordinals; n >= 1).  With n > 1 the

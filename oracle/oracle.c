@@ -105,7 +105,7 @@ typedef struct {
 } scene_t;
 
 typedef struct {
-    uint64_t rays_primary, rays_reflect, rays_refract, rays_shadow, shadow_occluded, leaf_tests;
+    uint64_t rays_primary, rays_reflect, rays_refract, rays_shadow, shadow_occluded, leaf_tests, rays_hit;
     double flops;
     int surface_error;
 } counters_t;
@@ -544,6 +544,7 @@ static v3 trace_ray(const scene_t* s, ray_t ray, int depth, int kind, counters_t
         double t = 0.5 * (ray.d.y + 1.0);
         return vlerp(s->bg0, s->bg1, t);
     }
+    c->rays_hit++;
     const object_t* o = &s->objs[best.obj];
     if (o->kind < 0) o = &s->leaves[best.leaf];
     hitex_t ex;
@@ -796,7 +797,7 @@ static void* worker(void* arg) {
     pthread_mutex_lock(&job->mu);
     job->total.rays_primary += c.rays_primary; job->total.rays_reflect += c.rays_reflect;
     job->total.rays_refract += c.rays_refract; job->total.rays_shadow += c.rays_shadow;
-    job->total.shadow_occluded += c.shadow_occluded; job->total.leaf_tests += c.leaf_tests;
+    job->total.shadow_occluded += c.shadow_occluded; job->total.leaf_tests += c.leaf_tests; job->total.rays_hit += c.rays_hit;
     job->total.flops += c.flops; job->total.surface_error |= c.surface_error;
     pthread_mutex_unlock(&job->mu);
     return NULL;
@@ -831,7 +832,7 @@ int oracle_render(const void* blob, size_t blob_bytes, uint8_t* rgba, size_t rgb
         stats->rays_primary = job.total.rays_primary; stats->rays_reflect = job.total.rays_reflect;
         stats->rays_refract = job.total.rays_refract; stats->rays_shadow = job.total.rays_shadow;
         stats->shadow_occluded = job.total.shadow_occluded; stats->leaf_tests = job.total.leaf_tests;
-        stats->flops_credited = job.total.flops; stats->n_leaves = (uint32_t)s.n_objs;
+        stats->flops_credited = job.total.flops; stats->n_leaves = (uint32_t)s.n_objs; stats->rays_hit = job.total.rays_hit;
     }
     rc = job.total.surface_error ? GMLRT_E_SURFACE : 0;
     scene_free(&s);

@@ -45,8 +45,8 @@ def test_parity_mode_is_byte_exact_on_goldens(ctx64, name):
         oimg, ost, oids = oracle.render(blob, threads=THREADS, want_ids=True)
         assert np.array_equal(img, oimg)
         assert np.array_equal(ctx64.primary_hits(), oids)
-        assert (st.rays_primary, st.rays_reflect, st.rays_refract, st.rays_shadow, st.shadow_occluded) == \
-               (ost.rays_primary, ost.rays_reflect, ost.rays_refract, ost.rays_shadow, ost.shadow_occluded)
+        assert (st.rays_primary, st.rays_reflect, st.rays_refract, st.rays_shadow, st.shadow_occluded, st.rays_hit) == \
+               (ost.rays_primary, ost.rays_reflect, ost.rays_refract, ost.rays_shadow, ost.shadow_occluded, ost.rays_hit)
 
 
 @pytest.mark.parametrize("name,bar", [("cylinder", 0.999), ("sphere", 0.999), ("canned", 0.999)])
@@ -86,8 +86,8 @@ def test_synthetic_scenes_parity_and_tolerance(ctx64, ctx32, gen):
     img, st = ctx64.render(blob)
     assert np.array_equal(img, oimg)
     assert np.array_equal(ctx64.primary_hits(), oids)
-    assert st.rays_total == ost.rays_total
-    img32, _ = ctx32.render(blob)
+    assert st.rays_total == ost.rays_total and st.rays_hit == ost.rays_hit and st.shadow_occluded == ost.shadow_occluded
+    img32, st32 = ctx32.render(blob)
     # 320x180 is far denser in silhouettes and texture discontinuities (frac / floor steps amplify a
     # float32 ulp into a full colour step) than the 4K frames the north_star quotes 99.9% on
     bar = {"spheres": 0.999, "mixed": 0.998, "proctex": 0.998, "csg": 0.997}[gen]
