@@ -9,6 +9,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -195,6 +196,7 @@ int gmlrt_upload(gmlrt_ctx* c, const void* blob, size_t blob_bytes) {
     // large launches however many devices share the frame
     const int nd = (int)c->r.size() * c->n_parts;
     c->band_rows = nd > 1 ? 8 : c->scene.height;
+    if (const char* e = getenv("GMLRT_BAND_ROWS")) { const int v = atoi(e); if (v > 0 && nd > 1) c->band_rows = v; }
     IRenderer* r0 = c->r[0].get();
     for (size_t i = 0; i < c->r.size(); i++) {
         uint8_t* target = nullptr;

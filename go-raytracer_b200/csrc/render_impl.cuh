@@ -2077,7 +2077,10 @@ public:
     }
 
     static constexpr bool kRobustPrimary = std::is_same<R, float>::value;   // f32: double re-test of borderline primary hits
-    static constexpr int RPT_GENERAL = 2, RPT_FAMILY = 4;                   // rays per thread: 8 cull registers per ray vs 4
+#ifndef GMLRT_RPT_FAMILY
+#define GMLRT_RPT_FAMILY 4
+#endif
+    static constexpr int RPT_GENERAL = 2, RPT_FAMILY = GMLRT_RPT_FAMILY;                   // rays per thread: 8 cull registers per ray vs 4
 
     void reset_totals() override { totals_ = TraceTotals(); need_ctr_reset_ = true; ev_used_ = 0; ev_cls_.clear(); }
     void set_profiling(bool on) override { profile_ = on; }
