@@ -1384,11 +1384,18 @@ static __global__ void __launch_bounds__(1024) k_sort_scan(int nb, int* hist, in
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     if (tid == 0) carry_s = 0;
     __syncthreads();
-    for (int tile = 0; tile < nb; tile += 4096) {
+    auto load_tile = [&](int tile) {
         const int b = tile + 4 * tid;
         int4 v = make_int4(0, 0, 0, 0);
         if (b + 3 < nb) v = *reinterpret_cast<const int4*>(hist + b);
         else { if (b < nb) v.x = hist[b]; if (b + 1 < nb) v.y = hist[b + 1]; if (b + 2 < nb) v.z = hist[b + 2]; }
+        return v;
+    };
+    int4 nxt = load_tile(0);
+    for (int tile = 0; tile < nb; tile += 4096) {
+        const int b = tile + 4 * tid;
+        const int4 v = nxt;
+        if (tile + 4096 < nb) nxt = load_tile(tile + 4096);   // in flight while this tile is scanned (the loop is latency-bound)
         const int mine = v.x + v.y + v.z + v.w;
         int incl = mine;
 #pragma unroll
