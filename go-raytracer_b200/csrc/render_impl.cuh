@@ -894,60 +894,48 @@ template <typename R> __device__ __forceinline__ void publish_bound(R* slot, con
     slot[5] = b.ox; slot[6] = b.oy; slot[7] = b.oz; slot[8] = b.rho;
     slot[9] = b.usable ? R(1) : R(0); slot[10] = any_active ? R(1) : R(0);
 }
+// Evaluated by every warp on its own: lane w (mod 8) holds warp w's published bound, sums / minima / maxima go over
+// groups of 8 lanes with xor-shuffles, so the union costs a few dozen instructions per warp instead of 8x that per thread.
+template <typename R> __device__ __forceinline__ R oct_sum(R v) { for (int o = 4; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o); return v; }
+template <typename R> __device__ __forceinline__ R oct_min(R v) { for (int o = 4; o > 0; o >>= 1) { const R u = __shfl_xor_sync(0xffffffffu, v, o); v = u < v ? u : v; } return v; }
+template <typename R> __device__ __forceinline__ R oct_max(R v) { for (int o = 4; o > 0; o >>= 1) { const R u = __shfl_xor_sync(0xffffffffu, v, o); v = u > v ? u : v; } return v; }
+
 template <typename R, int FAMILY>
 __device__ __forceinline__ WarpBound<R> cta_bound(const R (*wbs)[WB_WORDS]) {
-    constexpr int NW = SCAN_THREADS / 32;
+    static_assert(SCAN_THREADS / 32 == 8, "one lane of each group of 8 per warp of the CTA");
+    const R* b = wbs[threadIdx.x & 7];
+    const bool act = b[10] != R(0);                         // false: a warp past the end of the queue
     WarpBound<R> c = {};
-    c.usable = true;
-    R sx = R(0), sy = R(0), sz = R(0), qx = R(0), qy = R(0), qz = R(0), cnt = R(0);
-#pragma unroll
-    for (int w = 0; w < NW; w++) {
-        const R* b = wbs[w];
-        if (b[10] == R(0)) continue;                         // a warp past the end of the queue
-        if (b[9] == R(0)) c.usable = false;
-        sx += b[0]; sy += b[1]; sz += b[2]; qx += b[5]; qy += b[6]; qz += b[7]; cnt += R(1);
-    }
-    if (!(cnt > R(0))) c.usable = false;
-    if (!c.usable) return c;
+    const R bad = oct_sum<R>(act && b[9] == R(0) ? R(1) : R(0));
+    const R cnt = oct_sum<R>(act ? R(1) : R(0));
+    c.usable = bad == R(0) && cnt > R(0);
+    if (!c.usable) return c;                                // uniform across the warp (and the CTA: every warp sees the same slots)
+    const R sx = oct_sum<R>(act ? b[0] : R(0)), sy = oct_sum<R>(act ? b[1] : R(0)), sz = oct_sum<R>(act ? b[2] : R(0));
     if (FAMILY == CULL_AXIS) {                               // discs in the plane orthogonal to the common direction
         c.ax = sx / cnt; c.ay = sy / cnt;
-        R rho = R(0);
-#pragma unroll
-        for (int w = 0; w < NW; w++) {
-            const R* b = wbs[w];
-            if (b[10] == R(0)) continue;
-            const R du = b[0] - c.ax, dv = b[1] - c.ay;
-            const R d = gm<R>::sqrt(fma_(du, du, dv * dv)) * R(1.0001) + b[3];
-            rho = d > rho ? d : rho;
-        }
+        const R du = b[0] - c.ax, dv = b[1] - c.ay;
+        const R rho = oct_max<R>(act ? gm<R>::sqrt(fma_(du, du, dv * dv)) * R(1.0001) + b[3] : R(0));
         c.cos_t = rho * R(1.0001) + R(1e-6) * (gm<R>::abs(c.ax) + gm<R>::abs(c.ay) + R(1));
         return c;
     }
+    const R qx = oct_sum<R>(act ? b[5] : R(0)), qy = oct_sum<R>(act ? b[6] : R(0)), qz = oct_sum<R>(act ? b[7] : R(0));
     const R len = gm<R>::sqrt(fma_(sx, sx, fma_(sy, sy, sz * sz)));
     if (!(len > R(0))) { c.usable = false; return c; }
     const R inv = R(1) / len;
     c.ax = sx * inv; c.ay = sy * inv; c.az = sz * inv;
     c.ox = qx / cnt; c.oy = qy / cnt; c.oz = qz / cnt;
-    R cmin = R(1), rho = R(0);
-#pragma unroll
-    for (int w = 0; w < NW; w++) {
-        const R* b = wbs[w];
-        if (b[10] == R(0)) continue;
-        R cw = fma_(b[0], c.ax, fma_(b[1], c.ay, b[2] * c.az));      // cos of the angle phi between the warp's axis and the CTA's
-        if (!(cw > R(0))) c.usable = false;                           // phi + theta must stay below pi for the sum formula
-        cw = cw < R(1) ? cw : R(1);
-        const R sw = gm<R>::sqrt(R(1) - cw * cw) + R(1e-5);
-        const R cs = cw * b[3] - sw * b[4];                           // cos(phi + theta_w)
-        cmin = cs < cmin ? cs : cmin;
-        const R ex = b[5] - c.ox, ey = b[6] - c.oy, ez = b[7] - c.oz;
-        const R d = gm<R>::sqrt(fma_(ex, ex, fma_(ey, ey, ez * ez))) * R(1.0001) + b[8];
-        rho = d > rho ? d : rho;
-    }
+    R cw = fma_(b[0], c.ax, fma_(b[1], c.ay, b[2] * c.az));           // cos of the angle phi between the warp's axis and the CTA's
+    const R neg = oct_sum<R>(act && !(cw > R(0)) ? R(1) : R(0));         // phi + theta must stay below pi for the sum formula
+    cw = cw < R(1) ? cw : R(1);
+    const R sw = gm<R>::sqrt(R(1) - cw * cw) + R(1e-5);
+    R cmin = oct_min<R>(act ? cw * b[3] - sw * b[4] : R(1));             // cos(phi + theta_w)
+    const R ex = b[5] - c.ox, ey = b[6] - c.oy, ez = b[7] - c.oz;
+    const R rho = oct_max<R>(act ? gm<R>::sqrt(fma_(ex, ex, fma_(ey, ey, ez * ez))) * R(1.0001) + b[8] : R(0));
     cmin -= R(1e-5);
     c.cos_t = cmin;
     c.sin_t = gm<R>::sqrt(R(1) - (cmin < R(1) ? cmin * cmin : R(1))) + R(1e-5);
     c.rho = rho * R(1.0001) + R(1e-6) * (gm<R>::abs(c.ox) + gm<R>::abs(c.oy) + gm<R>::abs(c.oz) + R(1));
-    c.usable = c.usable && cmin > R(0.2);
+    c.usable = neg == R(0) && cmin > R(0.2);
     return c;
 }
 
@@ -997,8 +985,10 @@ template <typename R> struct ShadowSource {                  // shadow rays of o
 template <typename R, int FAMILY, int RPT, typename Source>
 __global__ void __launch_bounds__(SCAN_THREADS, sizeof(R) == 4 ? 3 : 2)
 k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, const __grid_constant__ CullFrame<R> frame,
-       int n_cull, const __grid_constant__ CandQueue cq, Counters* ctr, int chunk_objs, int resident) {
+       int n_cull, const __grid_constant__ CandQueue cq, Counters* ctr, int chunk_objs, int resident_flags) {
     constexpr int RAYS_PER_BLOCK = SCAN_THREADS * RPT;
+    const int resident = resident_flags & 1;
+    const bool cta_pass = (resident_flags & 2) != 0;           // host switch: try the CTA-wide first packet pass
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ __align__(8) uint64_t bar[2];
     const int tid = threadIdx.x, lane = tid & 31;
@@ -1043,9 +1033,12 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
         int n_active = 0;
 #pragma unroll
         for (int r = 0; r < RPT; r++) n_active += active[r] ? 1 : 0;
-        if (lane == 0) publish_bound<R>(s_wb[tid >> 5], wb, ray0 + (tid >> 5) * RPT * 32 < n);
-        __syncthreads();
-        const WarpBound<R> cb = cta_bound<R, FAMILY>(s_wb);
+        WarpBound<R> cb = {};
+        if (cta_pass) {
+            if (lane == 0) publish_bound<R>(s_wb[tid >> 5], wb, ray0 + (tid >> 5) * RPT * 32 < n);
+            __syncthreads();
+            cb = cta_bound<R, FAMILY>(s_wb);
+        }
         unsigned long long fine = 0, packet = 0;           // this lane's executed tests
 #ifdef GMLRT_DEBUG_PACKETS
         if (lane == 0 && FAMILY != CULL_GENERAL) { atomicAdd(&ctr->dbg[0 + 4 * (FAMILY == CULL_AXIS)], 1ull); if (wb.usable) atomicAdd(&ctr->dbg[1 + 4 * (FAMILY == CULL_AXIS)], 1ull); }
@@ -2202,6 +2195,7 @@ private:
     bool need_ctr_reset_ = true;
     // scan kernel configuration
     int chunk_objs_ = GROUP, resident_ = 1; size_t table_smem_ = 0;
+    int cta_pass_ = 7;                                  // CTA-wide first packet pass for: 1 camera rays, 2 spawned rays, 4 shadow rays (GMLRT_CTA_PASS)
     struct Launch { int grid = 148; size_t smem = 0; };
     Launch l_primary_, l_closest_, l_shadow_pivot_, l_shadow_axis_;                      // the four k_cull instantiations
     CandQueue cq_{}; int cand_per_ray_ = 4, tile_shrink_ = 0;
@@ -2342,6 +2336,7 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     while ((size_t)(((std::max(n_all, 1) - 1) >> sc.key_shift) + 1) * 6 * sc.key_k * sc.key_k > (size_t)KEY_BINS_MAX) sc.key_shift++;
     key_nb_ = (((std::max(n_all, 1) - 1) >> sc.key_shift) + 1) * 6 * sc.key_k * sc.key_k;
     sort_spawned_ = env_size("GMLRT_SORT_SPAWNED", 1) != 0;
+    cta_pass_ = (int)env_size("GMLRT_CTA_PASS", 7);
     for (int k = 0; k < 3; k++) { sc.ambient[k] = (R)S.h.ambient[k]; sc.bg0[k] = (R)S.h.bg_start[k]; sc.bg1[k] = (R)S.h.bg_end[k]; }
     sc_ = sc;
     // cull tables: any ray; camera rays (their lines pass through the eye, raytracer.go:605-609); one per light
@@ -2607,7 +2602,7 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             if (l == 0) {                                  // camera rays: PIVOT family through the eye, robust re-tests in f32
                 MARK(KC_CLOSEST_PRIMARY);
                 k_cull<R, CULL_PIVOT, RPT_FAMILY, ClosestSource<R>><<<l_primary_.grid, SCAN_THREADS, l_primary_.smem, stream_>>>(
-                    csrc, &ctr_->count[l], cull_eye_, frame_eye_, sc_.n_cull, cq_, ctr_, chunk_objs_, resident_);
+                    csrc, &ctr_->count[l], cull_eye_, frame_eye_, sc_.n_cull, cq_, ctr_, chunk_objs_, resident_ | ((cta_pass_ & 1) ? 2 : 0));
                 MARK(KC_EXACT);
                 if (kRobustPrimary) {
                     // float32 spheres inline; then the double-precision pass: other kinds + the spheres the first pass deferred
@@ -2626,7 +2621,7 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             } else {
                 MARK(KC_CLOSEST);
                 k_cull<R, CULL_GENERAL, RPT_GENERAL, ClosestSource<R>><<<l_closest_.grid, SCAN_THREADS, l_closest_.smem, stream_>>>(
-                    csrc, &ctr_->count[l], cull_general_, frame_general_, sc_.n_cull, cq_, ctr_, chunk_objs_, resident_);
+                    csrc, &ctr_->count[l], cull_general_, frame_general_, sc_.n_cull, cq_, ctr_, chunk_objs_, resident_ | ((cta_pass_ & 2) ? 2 : 0));
                 MARK(KC_EXACT);
                 int erc = exact_closest(l, counting);
                 if (erc) return erc;
@@ -2653,9 +2648,9 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
                 totals_.launches += 3;
                 MARK(KC_SHADOW);
                 if (axis) k_cull<R, CULL_AXIS, RPT_FAMILY, ShadowSource<R>><<<l_shadow_axis_.grid, SCAN_THREADS, l_shadow_axis_.smem, stream_>>>(
-                    ssrc, &shadow_counts_[li], cull_light_[li], frame_light_[li], sc_.n_cull, cq_, ctr_, chunk_objs_, resident_);
+                    ssrc, &shadow_counts_[li], cull_light_[li], frame_light_[li], sc_.n_cull, cq_, ctr_, chunk_objs_, resident_ | ((cta_pass_ & 4) ? 2 : 0));
                 else k_cull<R, CULL_PIVOT, RPT_FAMILY, ShadowSource<R>><<<l_shadow_pivot_.grid, SCAN_THREADS, l_shadow_pivot_.smem, stream_>>>(
-                    ssrc, &shadow_counts_[li], cull_light_[li], frame_light_[li], sc_.n_cull, cq_, ctr_, chunk_objs_, resident_);
+                    ssrc, &shadow_counts_[li], cull_light_[li], frame_light_[li], sc_.n_cull, cq_, ctr_, chunk_objs_, resident_ | ((cta_pass_ & 4) ? 2 : 0));
                 MARK(KC_EXACT);
                 const int sbase = li * sq_.per_light;
                 if (counting) {

@@ -175,3 +175,19 @@ def test_surface_fault_is_an_error_code_not_a_crash(ctx64):
     with pytest.raises(cuda.GmlrtError) as ei:
         ctx64.render(lowering.lower(calls[0], st))
     assert ei.value.code == -7          # GMLRT_E_SURFACE; the reference panics (raytracer.go:499-501)
+
+
+def test_cli_writes_png_and_ppm_like_cmd_example(tmp_path):
+    """cmd/example's twin: GML file in, image file out; the P6 payload is the raster's RGB bytes."""
+    from go_raytracer_b200 import imageio
+    from go_raytracer_b200.__main__ import main
+    src = os.path.join(SCENES, "sphere.gml")
+    png, ppm = str(tmp_path / "s.png"), str(tmp_path / "s.ppm")
+    main(["--gml_file", src, "--out_file", png, "--precision", "f64"])
+    main(["--gml_file", src, "--out_file", ppm, "--precision", "f64"])
+    want = golden("example_sphere.png")
+    assert np.array_equal(imageio.read_png(png), want)
+    raw = open(ppm, "rb").read()
+    h, w = want.shape[:2]
+    head = f"P6\n{w} {h}\n255\n".encode()
+    assert raw.startswith(head) and raw[len(head):] == want[..., :3].tobytes()
