@@ -1289,7 +1289,7 @@ __global__ void __launch_bounds__(256) k_closest_order(const __grid_constant__ D
     const R* ct = reinterpret_cast<const R*>(cq.t);
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
         const int code = cq.obj[k];
-        if (code < 0) continue;
+        if (code < 0 || (code & HIT_LEAF_MASK) >= sc.n_all) continue;       // a miss, or a padding record (reached only by a NaN ray)
         const int ri = cq.ray[k];
         if (BitsOf<R>::of(ct[k]) == tbest[ri]) atomicMin(&lv.order[ri], sc.scan_of[code & HIT_LEAF_MASK]);
     }
@@ -1304,7 +1304,7 @@ __global__ void __launch_bounds__(256) k_closest_pick(const __grid_constant__ De
     const R* ct = reinterpret_cast<const R*>(cq.t);
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
         const int code = cq.obj[k];
-        if (code < 0) continue;
+        if (code < 0 || (code & HIT_LEAF_MASK) >= sc.n_all) continue;       // a miss, or a padding record (reached only by a NaN ray)
         const int ri = cq.ray[k];
         if constexpr (sizeof(R) == 4) {
             if (hit_key32(sc, ct[k], code) == reinterpret_cast<const unsigned long long*>(lv.order)[ri]) { lv.hit[ri] = code; lv.t[ri] = ct[k]; }
