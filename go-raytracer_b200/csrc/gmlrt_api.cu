@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <thread>
 #include <memory>
 #include <string>
 #include <vector>
@@ -264,30 +265,42 @@ static int trace_once(gmlrt_ctx* c, gmlrt_stats* stats, bool& overflow) {
     API_CU(cudaEventRecord(c->ev_a, r0->stream()));
     // the other devices start after ev_a so that ev_a..ev_b on device 0 brackets the whole job
     for (int i = 1; i < nd; i++) { API_CU(cudaSetDevice(c->r[i]->device())); API_CU(cudaStreamWaitEvent(c->r[i]->stream(), c->ev_a, 0)); }
-    for (int di = 0; di < nd; di++) {
+    // one launcher per device: a frame is ~60 launches per device, and issued from one thread the devices of an 8-GPU
+    // context would start one after the other (the launches, not the kernels, were the critical path)
+    std::vector<int> drc(nd, GMLRT_OK);
+    std::vector<std::string> derr(nd);
+    auto run_device = [&](int di) {
         IRenderer* r = c->r[di].get();
         RowMap map;
         map.band_rows = c->band_rows; map.n_parts = nd * c->n_parts; map.part = c->part * nd + di;
         const int vrows = map.count(H);
-        if (vrows == 0) continue;
-        int rc = r->trace_rows(0, vrows, map, c->counting, err);
-        if (rc != GMLRT_OK) return fail(c, rc, err);
-        if (di != 0) {   // gather on the producing device's stream: frame rows only when k_pixels could not store them itself
-            API_CU(cudaSetDevice(r->device()));
-            const size_t band = (size_t)c->band_rows * W * 4, pitch = band * map.n_parts, first = band * map.part;
-            const int full = vrows / c->band_rows, rest = vrows % c->band_rows;
-            auto gather = [&](uint8_t* dst, const uint8_t* src, size_t scale) -> cudaError_t {
-                cudaError_t e = cudaSuccess;
-                if (full) e = cudaMemcpy2DAsync(dst + first * scale, pitch * scale, src + first * scale, pitch * scale, band * scale, full, cudaMemcpyDefault, r->stream());
-                if (e == cudaSuccess && rest)
-                    e = cudaMemcpyAsync(dst + (first + pitch * full) * scale, src + (first + pitch * full) * scale, (size_t)rest * W * 4 * scale, cudaMemcpyDefault, r->stream());
-                return e;
-            };
-            if (!c->peer_ok[di] && !c->remote_frame) API_CU(gather(r0->frame(), r->frame(), 1));
-            if (c->counting && r->primary_ids() && r0->primary_ids())
-                API_CU(gather((uint8_t*)r0->primary_ids(), (const uint8_t*)r->primary_ids(), 4));
-        }
+        if (vrows == 0) return;
+        drc[di] = r->trace_rows(0, vrows, map, c->counting, derr[di]);
+        if (drc[di] != GMLRT_OK || di == 0) return;
+        // gather on the producing device's stream: frame rows only when k_pixels could not store them itself
+        cudaError_t e = cudaSetDevice(r->device());
+        const size_t band = (size_t)c->band_rows * W * 4, pitch = band * map.n_parts, first = band * map.part;
+        const int full = vrows / c->band_rows, rest = vrows % c->band_rows;
+        auto gather = [&](uint8_t* dst, const uint8_t* src, size_t scale) -> cudaError_t {
+            cudaError_t g = cudaSuccess;
+            if (full) g = cudaMemcpy2DAsync(dst + first * scale, pitch * scale, src + first * scale, pitch * scale, band * scale, full, cudaMemcpyDefault, r->stream());
+            if (g == cudaSuccess && rest)
+                g = cudaMemcpyAsync(dst + (first + pitch * full) * scale, src + (first + pitch * full) * scale, (size_t)rest * W * 4 * scale, cudaMemcpyDefault, r->stream());
+            return g;
+        };
+        if (e == cudaSuccess && !c->peer_ok[di] && !c->remote_frame) e = gather(r0->frame(), r->frame(), 1);
+        if (e == cudaSuccess && c->counting && r->primary_ids() && r0->primary_ids())
+            e = gather((uint8_t*)r0->primary_ids(), (const uint8_t*)r->primary_ids(), 4);
+        if (e != cudaSuccess) { drc[di] = GMLRT_E_CUDA; derr[di] = std::string("band gather: ") + cudaGetErrorString(e); }
+    };
+    if (nd == 1) run_device(0);
+    else {
+        std::vector<std::thread> launchers;
+        for (int di = 1; di < nd; di++) launchers.emplace_back(run_device, di);
+        run_device(0);
+        for (auto& t : launchers) t.join();
     }
+    for (int di = 0; di < nd; di++) if (drc[di] != GMLRT_OK) return fail(c, drc[di], derr[di]);
     for (int i = 1; i < nd; i++) {
         API_CU(cudaSetDevice(c->r[i]->device()));
         API_CU(cudaEventRecord(c->ev_done[i], c->r[i]->stream()));
