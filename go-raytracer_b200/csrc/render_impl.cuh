@@ -1648,8 +1648,9 @@ __device__ __forceinline__ int warp_append(int* counter, bool want) {
 
 // queue append with one atomic per CTA: every thread of the block must call it (block-uniform control flow).  All CTAs
 // of a launch append to the same counter; with one atomic per warp the wait for its return was 40% of k_shade's
-// stall samples (ncu r01c), a 256-thread CTA issues 8x fewer.  `scratch` = int[2][SHADE_WARPS + 1], toggled by `phase`.
-constexpr int SHADE_THREADS = 128, SHADE_WARPS = SHADE_THREADS / 32;
+// stall samples (ncu r01c); one reservation per CTA issues fewer (CTAs of 64 threads measured best: fewer atomics than per
+// warp, less barrier wait than 128 or 256 threads: shade 2.42 / 2.11 / 1.96 ms at 256 / 128 / 64).  `scratch` = int[2][SHADE_WARPS + 1], toggled by `phase`.
+constexpr int SHADE_THREADS = 64, SHADE_WARPS = SHADE_THREADS / 32;
 constexpr int SHADE_LIGHTS_PER_ROUND = 6, SHADE_Q_REFL = 6, SHADE_Q_REFR = 7, SHADE_QUEUES = 8;   // queues reserved per round trip in k_shade
 __device__ __forceinline__ int block_append(int* counter, bool want, int (*scratch)[SHADE_WARPS + 1], int& phase, unsigned long long* tally = nullptr) {
     int* s = scratch[phase & 1];
