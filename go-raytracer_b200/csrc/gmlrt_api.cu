@@ -8,6 +8,7 @@
 // into device 0's frame with cudaMemcpyPeerAsync (NVLink 5 through NVSwitch).  No collective.
 #include <algorithm>
 #include <chrono>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -373,6 +374,92 @@ int gmlrt_trace(gmlrt_ctx* c, gmlrt_stats* stats) {
             if (!r->shrink_tiles(c->scene, err)) return fail(c, GMLRT_E_OOM, "candidate queue overflow: " + err);
     }
     return fail(c, GMLRT_E_OOM, "candidate queue overflow persists after shrinking the tiles");
+}
+
+// ------------------------------------------------------------------ SSIM (internal/prim/ssim.go:27-182)
+// The reference's acceptance metric for a rendered image against a golden (raytracer_test.go:37-52): 11x11 Gaussian
+// window over 16-bit channel values, windows at x in [0, W-11), y in [0, H-11), mean over R, G, B of formula (13),
+// mean over the windows.  One thread per window, float64 like the reference (the Go version takes seconds at 4K: one
+// goroutine per column, 121 taps x 2 passes per window); a block's windows are summed in shared memory and the block
+// sums are added on the host in block order, so the result does not depend on scheduling.
+__constant__ double c_ssim_kernel[121];
+
+__global__ void __launch_bounds__(256) k_ssim(const uchar4* a, const uchar4* b, int w, int h, double* block_sums) {
+    __shared__ double part[256];
+    const int nx = w - 11, ny = h - 11;
+    const long long win = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    double val = 0.0;
+    if (win < (long long)nx * ny) {
+        const int xs = (int)(win % nx), ys = (int)(win / nx);
+        double m1[3] = {0, 0, 0}, m2[3] = {0, 0, 0};
+        for (int k2 = 0; k2 < 11; k2++)
+            for (int k1 = 0; k1 < 11; k1++) {
+                const uchar4 p = a[(size_t)(ys + k2) * w + xs + k1], q = b[(size_t)(ys + k2) * w + xs + k1];
+                const double wt = c_ssim_kernel[k1 * 11 + k2];
+                m1[0] += (double)(p.x * 257u) * wt; m1[1] += (double)(p.y * 257u) * wt; m1[2] += (double)(p.z * 257u) * wt;
+                m2[0] += (double)(q.x * 257u) * wt; m2[1] += (double)(q.y * 257u) * wt; m2[2] += (double)(q.z * 257u) * wt;
+            }
+        double v1[3] = {0, 0, 0}, v2[3] = {0, 0, 0}, cv[3] = {0, 0, 0};
+        for (int k2 = 0; k2 < 11; k2++)
+            for (int k1 = 0; k1 < 11; k1++) {
+                const uchar4 p = a[(size_t)(ys + k2) * w + xs + k1], q = b[(size_t)(ys + k2) * w + xs + k1];
+                const double wt = c_ssim_kernel[k1 * 11 + k2];
+                const double pa[3] = {(double)(p.x * 257u), (double)(p.y * 257u), (double)(p.z * 257u)};
+                const double qa[3] = {(double)(q.x * 257u), (double)(q.y * 257u), (double)(q.z * 257u)};
+#pragma unroll
+                for (int ch = 0; ch < 3; ch++) {
+                    const double d1 = pa[ch] - m1[ch], d2 = qa[ch] - m2[ch];
+                    v1[ch] += wt * (d1 * d1); v2[ch] += wt * (d2 * d2); cv[ch] += wt * d1 * d2;
+                }
+            }
+        const double c1 = (0.01 * 65535.0) * (0.01 * 65535.0), c2 = (0.03 * 65535.0) * (0.03 * 65535.0);
+#pragma unroll
+        for (int ch = 0; ch < 3; ch++)
+            val += ((2 * m1[ch] * m2[ch] + c1) * (2 * cv[ch] + c2)) / ((m1[ch] * m1[ch] + m2[ch] * m2[ch] + c1) * (v1[ch] + v2[ch] + c2));
+        val /= 3.0;
+    }
+    part[threadIdx.x] = val;
+    __syncthreads();
+    for (int off = 128; off > 0; off >>= 1) {
+        if ((int)threadIdx.x < off) part[threadIdx.x] += part[threadIdx.x + off];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) block_sums[blockIdx.x] = part[0];
+}
+
+int gmlrt_ssim(gmlrt_ctx* c, const uint8_t* rgba_a, const uint8_t* rgba_b, int width, int height, double* ssim) {
+    if (!c) return fail(nullptr, GMLRT_E_BAD_ARG, "ctx is null");
+    if (!rgba_a || !rgba_b || !ssim) return fail(c, GMLRT_E_BAD_ARG, "null image or result pointer");
+    if (width < 11 || height < 11) return fail(c, GMLRT_E_BAD_ARG, "images are too small");        // ssim.go:34-36
+    IRenderer* r0 = c->r[0].get();
+    API_CU(cudaSetDevice(r0->device()));
+    double kern[121], total = 0.0;
+    for (int i = 0; i < 11; i++)
+        for (int j = 0; j < 11; j++) { const double x = i - 5.0, y = j - 5.0; kern[i * 11 + j] = std::exp(-(x * x + y * y) / (2 * 1.5 * 1.5)); total += kern[i * 11 + j]; }
+    for (double& k : kern) k /= total;
+    API_CU(cudaMemcpyToSymbolAsync(c_ssim_kernel, kern, sizeof kern, 0, cudaMemcpyHostToDevice, r0->stream()));
+    const long long windows = (long long)(width - 11) * (height - 11);
+    if (windows == 0) { *ssim = std::nan(""); return GMLRT_OK; }                                  // the reference divides 0 by 0 here
+    const size_t bytes = (size_t)width * height * 4;
+    const int blocks = (int)((windows + 255) / 256);
+    uint8_t* d = nullptr;
+    API_CU(cudaMalloc(&d, 2 * bytes + (size_t)blocks * sizeof(double)));
+    double* d_sums = reinterpret_cast<double*>(d + 2 * bytes);
+    std::vector<double> sums(blocks);
+    cudaError_t e = cudaMemcpyAsync(d, rgba_a, bytes, cudaMemcpyHostToDevice, r0->stream());
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d + bytes, rgba_b, bytes, cudaMemcpyHostToDevice, r0->stream());
+    if (e == cudaSuccess) {
+        k_ssim<<<blocks, 256, 0, r0->stream()>>>(reinterpret_cast<const uchar4*>(d), reinterpret_cast<const uchar4*>(d + bytes), width, height, d_sums);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(sums.data(), d_sums, (size_t)blocks * sizeof(double), cudaMemcpyDeviceToHost, r0->stream());
+    if (e == cudaSuccess) e = cudaStreamSynchronize(r0->stream());
+    cudaFree(d);
+    if (e != cudaSuccess) return fail(c, GMLRT_E_CUDA, std::string("gmlrt_ssim: ") + cudaGetErrorString(e));
+    double sum = 0.0;
+    for (double v : sums) sum += v;
+    *ssim = sum / (double)windows;
+    return GMLRT_OK;
 }
 
 int gmlrt_download(gmlrt_ctx* c, uint8_t* rgba, size_t rgba_bytes) {

@@ -512,7 +512,10 @@ __device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem
 //          makes the lanes of a warp run their k-th exact tests side by side instead of one lane at a time.
 //
 // Each thread carries RPT rays so that the record load and the loop overhead are shared.
-constexpr int SCAN_THREADS = 256;
+#ifndef GMLRT_SCAN_THREADS
+#define GMLRT_SCAN_THREADS 256
+#endif
+constexpr int SCAN_THREADS = GMLRT_SCAN_THREADS, SCAN_WARPS = SCAN_THREADS / 32;
 constexpr int GROUP = 64;                   // objects per window: one 64-bit survivor mask per ray, kept in two registers
 constexpr int CULL_UNROLL = 8;              // objects per unrolled body of the cull loop
 enum CullFamily { CULL_GENERAL = 0, CULL_PIVOT = 1, CULL_AXIS = 2 };
@@ -896,14 +899,14 @@ template <typename R> __device__ __forceinline__ void publish_bound(R* slot, con
 }
 // Evaluated by every warp on its own: lane w (mod 8) holds warp w's published bound, sums / minima / maxima go over
 // groups of 8 lanes with xor-shuffles, so the union costs a few dozen instructions per warp instead of 8x that per thread.
-template <typename R> __device__ __forceinline__ R oct_sum(R v) { for (int o = 4; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o); return v; }
-template <typename R> __device__ __forceinline__ R oct_min(R v) { for (int o = 4; o > 0; o >>= 1) { const R u = __shfl_xor_sync(0xffffffffu, v, o); v = u < v ? u : v; } return v; }
-template <typename R> __device__ __forceinline__ R oct_max(R v) { for (int o = 4; o > 0; o >>= 1) { const R u = __shfl_xor_sync(0xffffffffu, v, o); v = u > v ? u : v; } return v; }
+template <typename R> __device__ __forceinline__ R oct_sum(R v) { for (int o = SCAN_WARPS / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o); return v; }
+template <typename R> __device__ __forceinline__ R oct_min(R v) { for (int o = SCAN_WARPS / 2; o > 0; o >>= 1) { const R u = __shfl_xor_sync(0xffffffffu, v, o); v = u < v ? u : v; } return v; }
+template <typename R> __device__ __forceinline__ R oct_max(R v) { for (int o = SCAN_WARPS / 2; o > 0; o >>= 1) { const R u = __shfl_xor_sync(0xffffffffu, v, o); v = u > v ? u : v; } return v; }
 
 template <typename R, int FAMILY>
 __device__ __forceinline__ WarpBound<R> cta_bound(const R (*wbs)[WB_WORDS]) {
-    static_assert(SCAN_THREADS / 32 == 8, "one lane of each group of 8 per warp of the CTA");
-    const R* b = wbs[threadIdx.x & 7];
+    static_assert((SCAN_WARPS & (SCAN_WARPS - 1)) == 0 && SCAN_WARPS <= 32, "one lane of each group of SCAN_WARPS lanes per warp of the CTA");
+    const R* b = wbs[threadIdx.x & (SCAN_WARPS - 1)];
     const bool act = b[10] != R(0);                         // false: a warp past the end of the queue
     WarpBound<R> c = {};
     const R bad = oct_sum<R>(act && b[9] == R(0) ? R(1) : R(0));
@@ -983,7 +986,7 @@ template <typename R> struct ShadowSource {                  // shadow rays of o
 };
 
 template <typename R, int FAMILY, int RPT, typename Source>
-__global__ void __launch_bounds__(SCAN_THREADS, sizeof(R) == 4 ? 3 : 2)
+__global__ void __launch_bounds__(SCAN_THREADS, (sizeof(R) == 4 ? 3 : 2) * 256 / SCAN_THREADS)
 k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, const __grid_constant__ CullFrame<R> frame,
        int n_cull, const __grid_constant__ CandQueue cq, Counters* ctr, int chunk_objs, int resident_flags) {
     constexpr int RAYS_PER_BLOCK = SCAN_THREADS * RPT;

@@ -46,7 +46,7 @@ class GmlrtError(RuntimeError):
         self.code = code
 
 
-EXPORTS = ("gmlrt_frame_ipc_export", "gmlrt_frame_ipc_attach", "gmlrt_measure_fp32_tflops", "gmlrt_set_profiling", "gmlrt_set_partition", "gmlrt_frame_device", "gmlrt_create", "gmlrt_render", "gmlrt_upload", "gmlrt_trace", "gmlrt_download", "gmlrt_set_counting",
+EXPORTS = ("gmlrt_ssim", "gmlrt_frame_ipc_export", "gmlrt_frame_ipc_attach", "gmlrt_measure_fp32_tflops", "gmlrt_set_profiling", "gmlrt_set_partition", "gmlrt_frame_device", "gmlrt_create", "gmlrt_render", "gmlrt_upload", "gmlrt_trace", "gmlrt_download", "gmlrt_set_counting",
            "gmlrt_primary_hits", "gmlrt_stream", "gmlrt_last_error", "gmlrt_destroy", "gmlrt_blob_version", "gmlrt_build_info")
 
 _lib = None
@@ -73,6 +73,7 @@ def load():
         L.gmlrt_stream.restype, L.gmlrt_stream.argtypes = p, [p]
         L.gmlrt_set_partition.restype, L.gmlrt_set_partition.argtypes = i, [p, i, i]
         L.gmlrt_frame_device.restype, L.gmlrt_frame_device.argtypes = p, [p]
+        L.gmlrt_ssim.restype, L.gmlrt_ssim.argtypes = i, [p, p, p, i, i, ctypes.POINTER(ctypes.c_double)]
         L.gmlrt_frame_ipc_export.restype, L.gmlrt_frame_ipc_export.argtypes = i, [p, p, sz]
         L.gmlrt_frame_ipc_attach.restype, L.gmlrt_frame_ipc_attach.argtypes = i, [p, p, sz]
         L.gmlrt_last_error.restype, L.gmlrt_last_error.argtypes = ctypes.c_char_p, [p]
@@ -160,6 +161,16 @@ class Context:
 
     def set_partition(self, part, n_parts):
         self._check(self._L.gmlrt_set_partition(self._h, part, n_parts))
+
+    def ssim(self, a, b):
+        """prim.SSIM (internal/prim/ssim.go:27-144) of two uint8 [H,W,4] rasters, computed on the GPU."""
+        a = np.ascontiguousarray(a, dtype=np.uint8)
+        b = np.ascontiguousarray(b, dtype=np.uint8)
+        if a.shape != b.shape or a.ndim != 3 or a.shape[2] != 4:
+            raise ValueError("images are not the same size")
+        out = ctypes.c_double()
+        self._check(self._L.gmlrt_ssim(self._h, a.ctypes.data, b.ctypes.data, a.shape[1], a.shape[0], ctypes.byref(out)))
+        return out.value
 
     def frame_ipc_export(self):
         """-> 64-byte CUDA IPC handle of this context's frame (after upload)."""

@@ -170,3 +170,24 @@ UNIT_CUBE_PLANES = (
     (Vec3(0, 1, 0), Vec3(0, +1, 0)),
     (Vec3(0, 0, 0), Vec3(0, -1, 0)),
 )
+
+
+def SSIM(img1, img2, ctx=None):
+    """prim.SSIM (internal/prim/ssim.go:27-144): structural similarity of two uint8 [H,W,4] rasters, computed on the
+    GPU through the C ABI (gmlrt_ssim).  `ctx`: an existing cuda.Context, else one is made on device 0.  Raises
+    ValueError like the reference's two error returns (different sizes :31-33, smaller than the window :34-36)."""
+    import numpy as np
+    from . import cuda
+    a, b = np.asarray(img1), np.asarray(img2)
+    if a.shape != b.shape:
+        raise ValueError("images are not the same size")
+    if a.shape[0] < 11 or a.shape[1] < 11:
+        raise ValueError("images are too small")
+    own = ctx is None
+    if own:
+        ctx = cuda.Context((0,), cuda.PRECISION_F32)
+    try:
+        return ctx.ssim(a, b)
+    finally:
+        if own:
+            ctx.close()

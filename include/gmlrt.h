@@ -258,6 +258,11 @@ double gmlrt_measure_fp32_tflops(int device);
 
 const char* gmlrt_last_error(gmlrt_ctx*);   /* text for the last non-OK code; never NULL */
 void gmlrt_destroy(gmlrt_ctx*);
+/* The reference's image-comparison metric, prim.SSIM (internal/prim/ssim.go:27-144; its golden tests accept
+ * >= 0.99, raytracer_test.go:37-52), computed on devices[0]: two host RGBA8 rasters of the same size in, the index
+ * out.  GMLRT_E_BAD_ARG when an image is smaller than the 11x11 window (the reference returns an error there too). */
+int gmlrt_ssim(gmlrt_ctx*, const uint8_t* rgba_a, const uint8_t* rgba_b, int width, int height, double* ssim);
+
 int  gmlrt_blob_version(void);
 const char* gmlrt_build_info(void);         /* arch, compiler, precision modes compiled in */
 

@@ -46,6 +46,8 @@ def lib():
         L.oracle_render.restype = ctypes.c_int
         L.oracle_render.argtypes = [p, ctypes.c_size_t, p, ctypes.c_size_t, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                     ctypes.c_int, ctypes.c_int, ctypes.POINTER(Stats), p]
+        L.oracle_ssim.restype = ctypes.c_int
+        L.oracle_ssim.argtypes = [p, p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(d)]
         L.oracle_eval_surface.restype = ctypes.c_int
         L.oracle_eval_surface.argtypes = [p, ctypes.c_size_t, ctypes.c_uint32, ctypes.c_int, d, d, ctypes.POINTER(d)]
         L.oracle_intersect.restype = ctypes.c_int
@@ -94,3 +96,16 @@ def eval_surface(blob, surface, face, u, v):
     if rc:
         raise OracleError(rc)
     return tuple(m)
+
+
+def ssim(a, b):
+    """prim.SSIM (internal/prim/ssim.go:27-144) of two uint8 [H,W,4] rasters -> float."""
+    a = np.ascontiguousarray(a, dtype=np.uint8)
+    b = np.ascontiguousarray(b, dtype=np.uint8)
+    if a.shape != b.shape:
+        raise ValueError("images are not the same size")
+    out = ctypes.c_double()
+    rc = lib().oracle_ssim(a.ctypes.data, b.ctypes.data, a.shape[1], a.shape[0], ctypes.byref(out))
+    if rc:
+        raise ValueError("images are too small")
+    return out.value

@@ -885,3 +885,59 @@ void oracle_pcg(uint64_t seed1, uint64_t seed2, int n, uint64_t* out) {
     go_pcg p; go_pcg_seed(&p, seed1, seed2);
     for (int i = 0; i < n; i++) out[i] = go_pcg_uint64(&p);
 }
+
+
+/* ------------------------------------------------------------------ SSIM (internal/prim/ssim.go:27-182)
+ * The reference's acceptance metric for golden images (raytracer_test.go:37-52, >= 0.99): 11x11 Gaussian
+ * window (sigma 1.5, weights normalised to 1, ssim.go:146-165) over the 16-bit channel values that
+ * image.Color.RGBA() returns (8-bit v -> v * 257), windows at x in [0, W-11), y in [0, H-11) - the last
+ * possible start is left out, as in the reference's loops (:53, :58) -, per window the mean over R, G, B of
+ * formula (13) with c1 = (0.01 * 65535)^2, c2 = (0.03 * 65535)^2, then the mean over all windows.  Column sums
+ * are added in x order (the reference adds them in channel-arrival order, so its own last bits vary).
+ * rgba: [H][W][4] bytes (image.RGBA.Pix).  Returns 0, or -1 (null / too small, ssim.go:31-36). */
+#define SSIM_K 11
+static double ssim_window(const uint8_t* a, const uint8_t* b, int w, int xs, int ys, const double* kern) {
+    double m1[3] = {0, 0, 0}, m2[3] = {0, 0, 0};
+    for (int k1 = 0; k1 < SSIM_K; k1++)
+        for (int k2 = 0; k2 < SSIM_K; k2++) {
+            const size_t at = ((size_t)(ys + k2) * w + (xs + k1)) * 4;
+            const double wt = kern[k1 * SSIM_K + k2];
+            for (int c = 0; c < 3; c++) { m1[c] += (double)(a[at + c] * 257u) * wt; m2[c] += (double)(b[at + c] * 257u) * wt; }
+        }
+    double v1[3] = {0, 0, 0}, v2[3] = {0, 0, 0}, cv[3] = {0, 0, 0};
+    for (int k1 = 0; k1 < SSIM_K; k1++)
+        for (int k2 = 0; k2 < SSIM_K; k2++) {
+            const size_t at = ((size_t)(ys + k2) * w + (xs + k1)) * 4;
+            const double wt = kern[k1 * SSIM_K + k2];
+            for (int c = 0; c < 3; c++) {
+                const double d1 = (double)(a[at + c] * 257u) - m1[c], d2 = (double)(b[at + c] * 257u) - m2[c];
+                v1[c] += wt * (d1 * d1); v2[c] += wt * (d2 * d2); cv[c] += wt * d1 * d2;
+            }
+        }
+    const double c1 = (0.01 * 65535.0) * (0.01 * 65535.0), c2 = (0.03 * 65535.0) * (0.03 * 65535.0);
+    double s[3];
+    for (int c = 0; c < 3; c++)
+        s[c] = ((2 * m1[c] * m2[c] + c1) * (2 * cv[c] + c2)) / ((m1[c] * m1[c] + m2[c] * m2[c] + c1) * (v1[c] + v2[c] + c2));
+    return (s[0] + s[1] + s[2]) / 3.0;
+}
+
+int oracle_ssim(const uint8_t* rgba_a, const uint8_t* rgba_b, int w, int h, double* out) {
+    if (!rgba_a || !rgba_b || !out || w < SSIM_K || h < SSIM_K) return -1;
+    double kern[SSIM_K * SSIM_K], total = 0.0;
+    const double center = (SSIM_K - 1) / 2.0;
+    for (int i = 0; i < SSIM_K; i++)
+        for (int j = 0; j < SSIM_K; j++) {
+            const double x = i - center, y = j - center;
+            const double v = exp(-(x * x + y * y) / (2 * 1.5 * 1.5));
+            kern[i * SSIM_K + j] = v; total += v;
+        }
+    for (int i = 0; i < SSIM_K * SSIM_K; i++) kern[i] /= total;
+    double sum = 0.0; long long n = 0;
+    for (int x = 0; x < w - SSIM_K; x++) {
+        double col = 0.0;
+        for (int y = 0; y < h - SSIM_K; y++) { col += ssim_window(rgba_a, rgba_b, w, x, y, kern); n++; }
+        sum += col;
+    }
+    *out = n ? sum / (double)n : 0.0 / 0.0;      /* W == 11 or H == 11: no window, the reference divides 0 by 0 */
+    return 0;
+}
