@@ -70,7 +70,14 @@ template <typename R> struct DevScene {
     const R* fpool; const int* itab; const uint32_t* code;
     int n_fpool, n_itab;
     int W, H, depth;
-    int key_shift, key_k;          // sort key of a spawned ray: (leaf >> key_shift) * 6 k^2 + cube-map cell of its direction
+    int key_shift, key_k;          // sort key of a spawned ray: (region >> key_shift) * 6 k^2 + cube-map cell of its direction
+    // Sort regions (what "rays that start close together" means for the two ray sorts): a small object is its own
+    // region; a point on a large object (an unbounded plane, or a bounding sphere much wider than a grid cell) belongs
+    // to the cell of a uniform grid over the bounded objects.  Small regions are numbered along a Morton curve, so
+    // that regions merged by a shift are neighbours in space.
+    const int* rid_of;             // [n_all] region of a small object (CSG member leaves: their object's), -1 = large
+    int n_small, grid_dim[3];
+    R grid_lo[3], grid_inv[3];
     double vw, vh;
     R ambient[3], bg0[3], bg1[3];
 };
@@ -94,6 +101,7 @@ template <typename R> struct ShadowQueue {      // one segment of `per_light` sl
                   //          the cull kernel reads the rays through the by-object permutation, one sector per ray)
     int* perm;    // [cap] per light segment: slots (relative to the segment) ordered by the shaded object
     int* skip;    // [cap] device leaf index of the shaded object (inShadow skips it)
+    int* key;     // [cap] sort region of the shaded point (region_of)
     int* target;  // [cap] node * n_lights + light
     int* first;   // [cap] scan result: smallest scan index of an occluder, 0x7fffffff = none
     int* count;   // [n_lights] queued rays per light
@@ -428,7 +436,14 @@ template <typename R> __device__ __noinline__ void spans_intersect(const Spans<R
 // `mats` = WorldToObject of every leaf in the arithmetic type of this instantiation.
 template <typename R>
 __device__ __noinline__ bool csg_hit(const int* prog, int len, const int* kinds, const R* mats, const Ray<R>& w, R& t, int& code) {
-    Spans<R> st[GMLRT_CSG_MAX_STACK], t1, t2;
+    // Stack of span lists without moving any list: `ids` is a permutation of the buffers, ids[0..sp) are the stack,
+    // the rest are free (two are always free for the temporaries of an operator).  A list is 97-193 words of local
+    // memory, so a result is adopted by swapping two indices, never by copying the struct.
+    Spans<R> buf[GMLRT_CSG_MAX_STACK + 2];
+    int ids[GMLRT_CSG_MAX_STACK + 2];
+#pragma unroll
+    for (int k = 0; k < GMLRT_CSG_MAX_STACK + 2; k++) ids[k] = k;
+    auto swap_ids = [&](int x, int y) { const int tmp = ids[x]; ids[x] = ids[y]; ids[y] = tmp; };
     int sp = 0;
     for (int k = 0; k < len; k++) {
         const int op = prog[k];
@@ -436,24 +451,26 @@ __device__ __noinline__ bool csg_hit(const int* prog, int len, const int* kinds,
             if (sp >= GMLRT_CSG_MAX_STACK) return false;
             Ray<R> o;
             to_object(mats + (size_t)op * 12, w, o);
-            leaf_spans<R>(kinds[op], op, o, st[sp++]);
+            leaf_spans<R>(kinds[op], op, o, buf[ids[sp++]]);
         } else {
             if (sp < 2) return false;
-            Spans<R>& a = st[sp - 2];
-            Spans<R>& b = st[sp - 1];
+            Spans<R>& a = buf[ids[sp - 2]];
+            Spans<R>& b = buf[ids[sp - 1]];
+            Spans<R>& t1 = buf[ids[sp]];
+            Spans<R>& t2 = buf[ids[sp + 1]];
             const int kind = -1 - op;
-            if (kind == GMLRT_NODE_INTERSECT) { spans_intersect(a, b, t1); a = t1; }
-            else if (kind == GMLRT_NODE_DIFFERENCE) { spans_complement(b, t1); spans_intersect(a, t1, t2); a = t2; }
+            if (kind == GMLRT_NODE_INTERSECT) { spans_intersect(a, b, t1); swap_ids(sp - 2, sp); }
+            else if (kind == GMLRT_NODE_DIFFERENCE) { spans_complement(b, t1); spans_intersect(a, t1, t2); swap_ids(sp - 2, sp + 1); }
             else {                                       // union = complement(complement a  intersect  complement b)
                 spans_complement(a, t1); spans_complement(b, t2);
                 spans_intersect(t1, t2, a);
-                spans_complement(a, t1); a = t1;
+                spans_complement(a, t1); swap_ids(sp - 2, sp);
             }
             sp--;
         }
     }
     if (sp != 1) return false;
-    const Spans<R>& L = st[0];
+    const Spans<R>& L = buf[ids[0]];
     for (int i = 0; i < L.n; i++) {
         int b = -1;
         if (L.t[2 * i] > R(0)) b = 2 * i;
@@ -1349,11 +1366,11 @@ __global__ void __launch_bounds__(EXACT_THREADS) k_exact_shadow(const __grid_con
 // ------------------------------------------------------------------ shadow rays by shaded object
 // The packet stage of k_cull only pays off when the 32 * RPT rays of a warp form a narrow beam.  In queue order
 // (= screen order of the rays that spawned them) a warp's shadow rays start on whatever objects a strip of pixels
-// happens to cross, at any depth; ordered by the SHADED OBJECT they start within one bounding sphere (small objects)
-// or stay in screen order within it (a ground plane).  Counting sort of slot indices, keys = sq.skip (the shaded
-// leaf; -1 for CSG members): block-private histograms, one scan, block-wise scatter.  Only the 4-byte permutation
+// happens to cross, at any depth; ordered by the REGION of the shaded point (DevScene::rid_of: the shaded object when
+// it is small, else the grid cell of the point) they start within one bounding sphere / one cell.  Counting sort of
+// slot indices, keys = sq.key: block-private histograms, one scan, block-wise scatter.  Only the 4-byte permutation
 // is written; the 32-byte ray records stay where k_shade put them.
-constexpr int SORT_BINS_MAX = 4096, SORT_CHUNK = 4096, SORT_THREADS = 256;
+constexpr int SORT_BINS_MAX = 8192, SORT_CHUNK = 4096, SORT_THREADS = 256;
 
 __device__ __forceinline__ int sort_bin(int key, int shift, int nb) { return key < 0 ? nb - 1 : min(key >> shift, nb - 2); }
 
@@ -1367,7 +1384,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k_sort_hist(const __grid_constan
     __syncthreads();
     for (int c = blockIdx.x; c < nchunks; c += gridDim.x)
         for (int i = c * SORT_CHUNK + threadIdx.x; i < min(n, (c + 1) * SORT_CHUNK); i += SORT_THREADS)
-            atomicAdd(&h[sort_bin(sq.skip[base + i], shift, nb)], 1);
+            atomicAdd(&h[sort_bin(sq.key[base + i], shift, nb)], 1);
     __syncthreads();
     for (int b = threadIdx.x; b < nb; b += SORT_THREADS) if (h[b]) atomicAdd(&hist[b], h[b]);
 }
@@ -1419,19 +1436,19 @@ static __global__ void __launch_bounds__(1024) k_sort_scan(int nb, int* hist, in
 
 template <typename R>
 __global__ void __launch_bounds__(SORT_THREADS) k_sort_scatter(const __grid_constant__ ShadowQueue<R> sq, int light, int shift, int nb, int* cursor) {
-    __shared__ int h[SORT_BINS_MAX], at[SORT_BINS_MAX];
+    __shared__ int h[SORT_BINS_MAX];                       // this chunk's count per bin, then (in place) its cursor in the bin
     const int n = sq.count[light], base = light * sq.per_light;
     const int nchunks = (n + SORT_CHUNK - 1) / SORT_CHUNK;
     for (int c = blockIdx.x; c < nchunks; c += gridDim.x) {
         for (int b = threadIdx.x; b < nb; b += SORT_THREADS) h[b] = 0;
         __syncthreads();
         const int i1 = min(n, (c + 1) * SORT_CHUNK);
-        for (int i = c * SORT_CHUNK + threadIdx.x; i < i1; i += SORT_THREADS) atomicAdd(&h[sort_bin(sq.skip[base + i], shift, nb)], 1);
+        for (int i = c * SORT_CHUNK + threadIdx.x; i < i1; i += SORT_THREADS) atomicAdd(&h[sort_bin(sq.key[base + i], shift, nb)], 1);
         __syncthreads();
-        for (int b = threadIdx.x; b < nb; b += SORT_THREADS) at[b] = h[b] ? atomicAdd(&cursor[b], h[b]) : 0;   // this chunk's range in bin b
+        for (int b = threadIdx.x; b < nb; b += SORT_THREADS) { const int c_b = h[b]; if (c_b) h[b] = atomicAdd(&cursor[b], c_b); }   // this chunk's range in bin b
         __syncthreads();
         for (int i = c * SORT_CHUNK + threadIdx.x; i < i1; i += SORT_THREADS)
-            sq.perm[base + atomicAdd(&at[sort_bin(sq.skip[base + i], shift, nb)], 1)] = i;
+            sq.perm[base + atomicAdd(&h[sort_bin(sq.key[base + i], shift, nb)], 1)] = i;
         __syncthreads();
     }
 }
@@ -1598,7 +1615,7 @@ __device__ __noinline__ bool run_surface(const DevScene<R>& sc, const DevSurface
 // ------------------------------------------------------------------ small vector helpers (Vec3, vec.go:23-116)
 template <typename R> struct V3 { R x, y, z; };
 // sort key of a spawned ray (see k_keysort_*)
-template <typename R> __device__ __forceinline__ int ray_sort_key(const DevScene<R>& sc, int leaf, const V3<R>& d) {
+template <typename R> __device__ __forceinline__ int ray_sort_key(const DevScene<R>& sc, int region, const V3<R>& d) {
     const R ax = gm<R>::abs(d.x), ay = gm<R>::abs(d.y), az = gm<R>::abs(d.z);
     int face; R m, u, v;
     if (ax >= ay && ax >= az) { face = d.x < R(0) ? 1 : 0; m = ax; u = d.y; v = d.z; }
@@ -1609,7 +1626,7 @@ template <typename R> __device__ __forceinline__ int ray_sort_key(const DevScene
     int cu = (int)fma_(u, s, half), cv = (int)fma_(v, s, half);
     cu = min(k - 1, max(0, cu)); cv = min(k - 1, max(0, cv));
     if (cu & 1) cv = k - 1 - cv;                           // boustrophedon: consecutive cells of a face are neighbours
-    return (leaf >> sc.key_shift) * (6 * k * k) + (face * k + cu) * k + cv;
+    return (region >> sc.key_shift) * (6 * k * k) + (face * k + cu) * k + cv;
 }
 
 template <typename R> __device__ __forceinline__ V3<R> mk(R x, R y, R z) { V3<R> v = {x, y, z}; return v; }
@@ -1628,6 +1645,15 @@ template <typename R> __device__ __forceinline__ V3<R> clamp3(V3<R> a) {
     return mk(gomath::clamp01(a.x), gomath::clamp01(a.y), gomath::clamp01(a.z));
 }
 template <typename R> __device__ __forceinline__ V3<R> ld3(const R* p) { return mk(p[0], p[1], p[2]); }
+// sort region of a point P on leaf `leaf` (DevScene::rid_of)
+template <typename R> __device__ __forceinline__ int region_of(const DevScene<R>& sc, int leaf, const V3<R>& P) {
+    const int r = sc.rid_of[leaf];
+    if (r >= 0) return r;
+    const R fx = (P.x - sc.grid_lo[0]) * sc.grid_inv[0], fy = (P.y - sc.grid_lo[1]) * sc.grid_inv[1], fz = (P.z - sc.grid_lo[2]) * sc.grid_inv[2];
+    auto cell = [](R f, int dim) { const R hi = (R)(dim - 1); return (int)(f > R(0) ? (f < hi ? f : hi) : R(0)); };   // clamped as reals (P on a plane may be far outside the grid; NaN -> 0)
+    const int cx = cell(fx, sc.grid_dim[0]), cy = cell(fy, sc.grid_dim[1]), cz = cell(fz, sc.grid_dim[2]);
+    return sc.n_small + (cx * sc.grid_dim[1] + cy) * sc.grid_dim[2] + cz;
+}
 // (M^T) v : NormalMat.MulDir with NormalMat = WorldToObject^T (raytracer.go:367, 790)
 template <typename R> __device__ __forceinline__ V3<R> mul_dir_t(const R* m, V3<R> v) {
     return mk(m[0] * v.x + m[4] * v.y + m[8] * v.z, m[1] * v.x + m[5] * v.y + m[9] * v.z, m[2] * v.x + m[6] * v.y + m[10] * v.z);
@@ -1819,6 +1845,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
     }
     const R refl = mat[3], fuzz = mat[4], transp = mat[5], ior = mat[6];
     const V3<R> D = mk(w.dx, w.dy, w.dz);
+    const int region = live ? region_of(sc, leaf, P) : 0;
     if (live) {
         R* rec = lv.rec + i;
         rec[(REC_P + 0) * cap] = P.x; rec[(REC_P + 1) * cap] = P.y; rec[(REC_P + 2) * cap] = P.z;
@@ -1913,6 +1940,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
             rec[0] = so.x; rec[1] = so.y; rec[2] = so.z; rec[3] = ldir.x; rec[4] = ldir.y; rec[5] = ldir.z;
             rec[6] = dist; rec[7] = length(D);
             sq.skip[slot] = leaf < sc.n_leaves ? leaf : -1;      // a CSG object may shadow itself (oracle.c in_shadow)
+            sq.key[slot] = region;
             sq.target[slot] = i * sc.n_lights + li;
             occl[i * sc.n_lights + li] = 0;
         }
@@ -1925,13 +1953,13 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
                 const V3<R> ro = P + N * R(1e-4);
                 rd = normalize(rd);
                 store_ray(spawn_to, slot, ro.x, ro.y, ro.z, rd.x, rd.y, rd.z, i);
-                next.hit[slot] = ray_sort_key(sc, leaf, rd);
+                next.hit[slot] = ray_sort_key(sc, region, rd);
             }
             if (want_refr) {                                                         // refraction child (:532-556)
                 const int slot = s[SHADE_Q_REFR][wid] + __popc(m_refr & lt);
                 const V3<R> ro = P - refr_n * R(1e-4);
                 store_ray(spawn_to, slot, ro.x, ro.y, ro.z, refr_d.x, refr_d.y, refr_d.z, (int)((unsigned)i | 0x80000000u));
-                next.hit[slot] = ray_sort_key(sc, leaf, refr_d);
+                next.hit[slot] = ray_sort_key(sc, region, refr_d);
             }
         }
     }
@@ -2035,6 +2063,13 @@ __global__ void __launch_bounds__(256) k_pixels(DevScene<R> sc, const R* samples
         }                                                                                              \
     } while (0)
 
+inline double env_double(const char* name, double dflt) {
+    const char* e = getenv(name);
+    if (!e || !*e) return dflt;
+    char* end = nullptr;
+    const double v = strtod(e, &end);
+    return end == e ? dflt : v;
+}
 inline size_t env_size(const char* name, size_t dflt) {
     const char* v = std::getenv(name);
     return (v && *v) ? (size_t)std::strtoull(v, nullptr, 10) : dflt;
@@ -2203,7 +2238,7 @@ private:
     struct Launch { int grid = 148; size_t smem = 0; };
     Launch l_primary_, l_closest_, l_shadow_pivot_, l_shadow_axis_;                      // the four k_cull instantiations
     CandQueue cq_{}; int cand_per_ray_ = 4, tile_shrink_ = 0;
-    int* sort_hist_ = nullptr; int* sort_cursor_ = nullptr; int sort_nb_ = 2, sort_shift_ = 0; bool sort_clear_ = true;
+    int* sort_hist_ = nullptr; int* sort_cursor_ = nullptr; int sort_nb_ = 2, sort_shift_ = 0, n_regions_ = 1; bool sort_clear_ = true;
     int* key_hist_ = nullptr; int* key_cursor_ = nullptr; int key_nb_ = 6;      // spawned rays by (origin leaf, direction cell); cleared with sort_hist_
     bool sort_spawned_ = true;
     R* spawn_stage_ = nullptr;
@@ -2291,6 +2326,61 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     for (int i = 1; i < n; i++) cum_flops[i] += cum_flops[i - 1];
     for (int k = 0; k < K_OBJ_KINDS; k++) sc.kind_begin[k + 1] += sc.kind_begin[k];
     kind_host_ = kind;
+    // Sort regions (DevScene::rid_of).  Grid over the bounded objects: about one cell per object, at most 4096 cells,
+    // flat extents get a single layer.  "Large" = unbounded, or a bounding sphere wider than 1.5 cell edges.
+    std::vector<int> rid_of(na, 0);
+    int n_regions = 1;
+    {
+        double lo3[3] = {INFINITY, INFINITY, INFINITY}, hi3[3] = {-INFINITY, -INFINITY, -INFINITY};
+        int n_fin = 0;
+        for (int d = 0; d < n; d++) {
+            const double* b = &bound_[(size_t)d * 4];
+            if (!std::isfinite(b[3])) continue;
+            n_fin++;
+            for (int k = 0; k < 3; k++) { lo3[k] = std::min(lo3[k], b[k] - b[3]); hi3[k] = std::max(hi3[k], b[k] + b[3]); }
+        }
+        if (n_fin == 0) for (int k = 0; k < 3; k++) { lo3[k] = -8.0; hi3[k] = 8.0; }
+        double ext[3], ext_max = 0;
+        for (int k = 0; k < 3; k++) { ext[k] = hi3[k] - lo3[k]; ext_max = std::max(ext_max, ext[k]); }
+        ext_max = std::max(ext_max, 1e-6);
+        for (int k = 0; k < 3; k++) ext[k] = std::max(ext[k], 1e-3 * ext_max);
+        const double target = (double)std::min(std::max(n, 64), 4096);
+        double edge = std::cbrt(ext[0] * ext[1] * ext[2] / target);
+        int dim[3];
+        for (;;) {
+            for (int k = 0; k < 3; k++) dim[k] = std::max(1, (int)std::ceil(ext[k] / edge));
+            if ((double)dim[0] * dim[1] * dim[2] <= 4096.0) break;
+            edge *= 1.05;
+        }
+        const double large_r = env_double("GMLRT_LARGE_CELLS", 1.5) * edge;
+        auto cell_of = [&](const double* c, int* out) {
+            for (int k = 0; k < 3; k++) out[k] = std::min(dim[k] - 1, std::max(0, (int)std::floor((c[k] - lo3[k]) / edge)));
+        };
+        auto morton = [](const int* c) {
+            unsigned long long m = 0;
+            for (int b = 0; b < 12; b++) for (int k = 0; k < 3; k++) m |= (unsigned long long)((c[k] >> b) & 1) << (3 * b + k);
+            return m;
+        };
+        std::vector<std::pair<unsigned long long, int>> small;
+        bool any_large = false;
+        for (int d = 0; d < n; d++) {
+            const double* b = &bound_[(size_t)d * 4];
+            if (!std::isfinite(b[3]) || b[3] > large_r) { rid_of[d] = -1; any_large = true; continue; }
+            int c[3];
+            cell_of(b, c);
+            small.emplace_back(morton(c), d);
+        }
+        std::stable_sort(small.begin(), small.end());
+        for (size_t k = 0; k < small.size(); k++) rid_of[small[k].second] = (int)k;
+        for (int c = 0; c < n_csg; c++) {                             // member leaves: their object's region
+            const int d = n_plain + c;
+            for (const HostCsgOp& op : S.csg[c].postfix) if (op.op < 0) rid_of[dev_of_host[op.leaf]] = rid_of[d];
+        }
+        sc.n_small = (int)small.size();
+        for (int k = 0; k < 3; k++) { sc.grid_dim[k] = dim[k]; sc.grid_lo[k] = (R)lo3[k]; sc.grid_inv[k] = (R)(1.0 / edge); }
+        n_regions = std::max(1, sc.n_small + (any_large ? dim[0] * dim[1] * dim[2] : 0));
+    }
+    n_regions_ = n_regions;
     std::vector<DevLight<R>> lights(S.lights.size());
     for (size_t i = 0; i < S.lights.size(); i++) {
         const gmlrt_light& l = S.lights[i];
@@ -2322,6 +2412,9 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
         (rc = to_device(csg_range, &d_range, err)) || (rc = to_device(obj_flops, &d_oflops, err))) return rc;
     sc.cum_flops = d_cum; sc.csg_prog = d_prog; sc.csg_range = d_range; sc.obj_flops = d_oflops;
     R *d_w2o, *d_o2w, *d_fn, *d_fpool; int *d_scan, *d_surf, *d_kind, *d_itab; uint32_t* d_code;
+    int* d_rid;
+    if ((rc = to_device(rid_of, &d_rid, err))) return rc;
+    sc.rid_of = d_rid;
     DevLight<R>* d_lights; DevSurface<R>* d_surfaces;
     if ((rc = to_device(w2o, &d_w2o, err)) || (rc = to_device(o2w, &d_o2w, err)) || (rc = to_device(fn, &d_fn, err)) ||
         (rc = to_device(scan_of, &d_scan, err)) || (rc = to_device(surface, &d_surf, err)) || (rc = to_device(kind, &d_kind, err)) ||
@@ -2337,8 +2430,8 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     // sort key of spawned rays: 6 k^2 direction cells per origin leaf, at most KEY_BINS_MAX bins in all
     sc.key_k = (int)env_size("GMLRT_KEY_K", 3); sc.key_k = std::max(1, std::min(sc.key_k, 8));
     sc.key_shift = 0;
-    while ((size_t)(((std::max(n_all, 1) - 1) >> sc.key_shift) + 1) * 6 * sc.key_k * sc.key_k > (size_t)KEY_BINS_MAX) sc.key_shift++;
-    key_nb_ = (((std::max(n_all, 1) - 1) >> sc.key_shift) + 1) * 6 * sc.key_k * sc.key_k;
+    while ((size_t)(((n_regions - 1) >> sc.key_shift) + 1) * 6 * sc.key_k * sc.key_k > (size_t)KEY_BINS_MAX) sc.key_shift++;
+    key_nb_ = (((n_regions - 1) >> sc.key_shift) + 1) * 6 * sc.key_k * sc.key_k;
     sort_spawned_ = env_size("GMLRT_SORT_SPAWNED", 1) != 0;
     cta_pass_ = (int)env_size("GMLRT_CTA_PASS", 7);
     for (int k = 0; k < 3; k++) { sc.ambient[k] = (R)S.h.ambient[k]; sc.bg0[k] = (R)S.h.bg_start[k]; sc.bg1[k] = (R)S.h.bg_end[k]; }
@@ -2456,7 +2549,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     cand_per_ray_ = std::min<int>(std::max(sc_.n_leaves, 1), (int)env_size("GMLRT_CAND_PER_RAY", 4) + n_unbounded);
     const double cand_bytes = cand_per_ray_ * (8.0 + sizeof(R));
     const double node_bytes = (2 * RAY_WORDS + NREC + 8) * sizeof(R) + 12 + nl;      // ray record (+ its staging copy), rec, child, hit, order, occl
-    const double shadow_bytes = nl * (8.0 * sizeof(R) + 16);
+    const double shadow_bytes = nl * (8.0 * sizeof(R) + 20);
     const double per_sample = sum_mult * node_bytes + max_mult * (shadow_bytes + cand_bytes) + 3 * sizeof(R) + (kRobustPrimary ? 48 : 0);
     size_t free_b = 0, total_b = 0;
     CU_TRY(cudaMemGetInfo(&free_b, &total_b));
@@ -2485,7 +2578,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
         lo[l].occl = take(cap * std::max(nl, 1));
     }
     const size_t sq_cap = max_cap * std::max(nl, 1);
-    size_t o_sq = take(8 * sq_cap * sizeof(R)), o_skip = take(sq_cap * 4), o_tgt = take(sq_cap * 4), o_first = take(sq_cap * 4), o_perm = take(sq_cap * 4), o_sort = take(2 * SORT_BINS_MAX * sizeof(int));
+    size_t o_sq = take(8 * sq_cap * sizeof(R)), o_skip = take(sq_cap * 4), o_key = take(sq_cap * 4), o_tgt = take(sq_cap * 4), o_first = take(sq_cap * 4), o_perm = take(sq_cap * 4), o_sort = take(2 * SORT_BINS_MAX * sizeof(int));
     size_t o_keysort = take(2 * (size_t)KEY_BINS_MAX * sizeof(int));
     size_t o_stage = take(RAY_WORDS * stage_cap * sizeof(R));         // spawned rays wait here until k_keysort_scatter stores them sorted
     const size_t cand_cap = std::min<size_t>((size_t)((double)max_cap * cand_per_ray_ * (double)(1 << tile_shrink_)), (size_t)2000000000);
@@ -2508,13 +2601,13 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
         occl_[l] = (unsigned char*)(base + lo[l].occl);
         L.ray64 = (kRobustPrimary && l == 0) ? (double*)(base + o_ray64) : nullptr;
     }
-    sq_.q = (R*)(base + o_sq); sq_.skip = (int*)(base + o_skip); sq_.target = (int*)(base + o_tgt); sq_.cap = (int)sq_cap;
+    sq_.q = (R*)(base + o_sq); sq_.skip = (int*)(base + o_skip); sq_.key = (int*)(base + o_key); sq_.target = (int*)(base + o_tgt); sq_.cap = (int)sq_cap;
     sq_.per_light = (int)max_cap; sq_.count = shadow_counts_; sq_.first = (int*)(base + o_first); sq_.perm = (int*)(base + o_perm);
     sort_hist_ = (int*)(base + o_sort); sort_cursor_ = sort_hist_ + SORT_BINS_MAX; sort_clear_ = true;
     key_hist_ = (int*)(base + o_keysort); key_cursor_ = key_hist_ + KEY_BINS_MAX;
     spawn_stage_ = (R*)(base + o_stage);
-    sort_nb_ = std::min(sc_.n_leaves + 1, SORT_BINS_MAX); sort_shift_ = 0;
-    while (((std::max(sc_.n_leaves, 1) - 1) >> sort_shift_) + 2 > sort_nb_) sort_shift_++;
+    sort_nb_ = std::min(n_regions_ + 1, SORT_BINS_MAX); sort_shift_ = 0;        // shadow rays by the region of the shaded point
+    while (((n_regions_ - 1) >> sort_shift_) + 2 > sort_nb_) sort_shift_++;
     cq_.ray = (int*)(base + o_cray); cq_.obj = (int*)(base + o_cobj); cq_.t = (void*)(base + o_ct); cq_.count = (int*)(base + o_ccount);
     cq_.cap = (int)cand_cap;
     samples_ = (R*)(base + o_samples); sample_cap_ = (int)S0;
