@@ -681,12 +681,37 @@ static __device__ __noinline__ bool hit_f64(const DevScene<R>& sc, int kind, int
     return h;
 }
 
+// Robust float32 plane test for camera rays (throughput mode).  Plane.Intersect (:164-180) decides on two signs: the
+// object-space height of the origin and of the direction (and |den| >= 1e-6).  Both are 3-4 term dot products; when
+// each is outside its rounding band (2^-20 of the sum of the magnitudes: the rounded ray, the rounded matrix and the
+// accumulation stay below 2^-22) float32 decides like float64, and T only needs float accuracy.  Camera rays start on
+// the screen plane, far from any ground plane, so the double-precision path is the rare exception.  Returns false
+// when the decision must be left to hit_f64.
+template <typename R>
+__device__ __forceinline__ bool plane_hit_robust32(const DevScene<R>& sc, int i, const Ray<R>& w, bool& hit, R& t) {
+    const R* m = sc.w2o + (size_t)i * 12;
+    const R a0 = m[4] * w.ox, a1 = m[5] * w.oy, a2 = m[6] * w.oz, a3 = m[7];
+    const R b0 = m[4] * w.dx, b1 = m[5] * w.dy, b2 = m[6] * w.dz;
+    const R oy = a0 + a1 + a2 + a3, dy = b0 + b1 + b2;
+    const R eps = R(9.5367431640625e-7);                // 2^-20
+    const R band_o = eps * (gm<R>::abs(a0) + gm<R>::abs(a1) + gm<R>::abs(a2) + gm<R>::abs(a3));
+    const R band_d = eps * (gm<R>::abs(b0) + gm<R>::abs(b1) + gm<R>::abs(b2));
+    if (!(gm<R>::abs(oy) > band_o && gm<R>::abs(gm<R>::abs(dy) - R(1e-6)) > band_d)) return false;
+    hit = false;
+    if (gm<R>::abs(dy) < R(1e-6)) return true;
+    const R tt = (R(0) - oy) / dy;
+    if (tt <= R(0)) return true;
+    t = tt; hit = true;
+    return true;
+}
+
 // the exact test of ray `w` against object i, exactly as <Type>.Intersect would decide it; `code` is the hit
 // code stored in Level::hit: leaf | flip << 27 | face << 28 (for a CSG object the member leaf that was hit)
 template <typename R, bool ROBUST>
 __device__ __noinline__ bool exact_hit(const DevScene<R>& sc, int i, const Ray<R>& w, const double* ray64, int cap, int ri, R& t, int& code) {
     const int kind = kind_of(sc.kind_begin, i);
     if constexpr (ROBUST) {
+        if (kind == K_PLANE) { bool h = false; if (plane_hit_robust32(sc, i, w, h, t)) { code = i; return h; } }
         if (kind != K_SPHERE) { float tf; const bool h = hit_f64<R>(sc, kind, i, ray64, cap, ri, tf, code); t = (R)tf; return h; }
     }
     if (kind == K_CSG) return csg_object_hit<R>(sc, i, sc.w2o, w, t, code);
@@ -1283,9 +1308,20 @@ __global__ void __launch_bounds__(EXACT_THREADS) k_exact_closest(const __grid_co
                 code = obj; h = false;
                 if (disc >= R(0)) { const R t0 = (-hb - gm<R>::sqrt(disc)) / a; if (t0 > R(0)) { t = t0; h = true; } }
             } else if constexpr (ROBUST) {                     // REST: every non-sphere kind, and the deferred spheres, in double
-                float tf = 0.f;
-                h = hit_f64<R>(sc, deferred ? (int)K_SPHERE : kind_of(sc.kind_begin, obj), obj, lv.ray64, lv.cap, ri, tf, code);
-                t = (R)tf;
+                const int kind = deferred ? (int)K_SPHERE : kind_of(sc.kind_begin, obj);
+                bool decided = false;
+                h = false;
+                if (kind == K_PLANE) {                         // float32 unless a sign is inside its rounding band
+                    Ray<R> w;
+                    load_ray(lv.ray, ri, w);
+                    decided = plane_hit_robust32(sc, obj, w, h, t);
+                    code = obj;
+                }
+                if (!decided) {
+                    float tf = 0.f;
+                    h = hit_f64<R>(sc, kind, obj, lv.ray64, lv.cap, ri, tf, code);
+                    t = (R)tf;
+                }
             } else {
                 Ray<R> w;
                 load_ray(lv.ray, ri, w);
@@ -1752,7 +1788,7 @@ __global__ void __launch_bounds__(256) k_gen(DevScene<R> sc, Level<R> lv, Counte
     const double ox = u, oy = -v, oz = 0.0;               // screen point; eye = (0,0,-1)
     const double ex = ox - 0.0, ey = oy - 0.0, ez = oz - (-1.0);
     const double m = sqrt(ex * ex + ey * ey + ez * ez);
-    const int cap = lv.cap;
+    const size_t cap = (size_t)lv.cap;                     // 64-bit strides: 15 * cap passes 2^31 on deep binary ray trees
     store_ray(lv.ray, i, (R)ox, (R)oy, (R)oz, (R)(ex / m), (R)(ey / m), (R)(ez / m), 0);
     if (lv.ray64) {
         lv.ray64[i] = ox; lv.ray64[cap + i] = oy; lv.ray64[2 * cap + i] = oz;
@@ -1773,7 +1809,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
     int append_phase = 0;
     for (int blk0 = blockIdx.x * blockDim.x; blk0 < n; blk0 += gridDim.x * blockDim.x) {   // uniform per block
     const int i = blk0 + threadIdx.x;
-    const int cap = lv.cap;
+    const size_t cap = (size_t)lv.cap;                     // 64-bit strides: 15 * cap passes 2^31 on deep binary ray trees
     bool live = i < n;
     int h = live ? lv.hit[i] : -1;
     if (ids && live) {                                     // level 0 only: primary hit ids in (y, x, sample) order
@@ -1916,7 +1952,14 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
             int base = 0;
             if (q < SHADE_LIGHTS_PER_ROUND) { if (total) base = atomicAdd(&sq.count[l0 + q], total); }
             else if (q == SHADE_Q_REFL) {
-                if (total + t_refr) base = atomicAdd(&ctr->count[level + 1], total + t_refr);
+                const int want = total + t_refr;
+                if (want) {
+                    base = atomicAdd(&ctr->count[level + 1], want);
+                    if (base + want > next.cap) {              // level full (plan_tiles sizes branching levels below 2^l): give back what does not fit
+                        atomicSub(&ctr->count[level + 1], base + want - max(base, next.cap));
+                        ctr->overflow = 1;
+                    }
+                }
                 if (total) atomicAdd(&ctr->rays_reflect, (unsigned long long)total);
                 if (t_refr) atomicAdd(&ctr->rays_refract, (unsigned long long)t_refr);
             }
@@ -1948,18 +1991,22 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
             const unsigned m_refl = __ballot_sync(0xffffffffu, want_refl), m_refr = __ballot_sync(0xffffffffu, want_refr);
             if (want_refl) {                                                         // reflection child (:512-529)
                 const int slot = s[SHADE_Q_REFL][wid] + __popc(m_refl & lt);
+                if (slot < next.cap) {
                 V3<R> rd = D - N * (R(2) * dot(D, N));
                 if (fuzz >= R(0)) rd = rd + mk(fuzz * gm<R>::cos(fuzz) * gm<R>::cos(fuzz), fuzz * gm<R>::sin(fuzz) * gm<R>::sin(fuzz), R(0));
                 const V3<R> ro = P + N * R(1e-4);
                 rd = normalize(rd);
                 store_ray(spawn_to, slot, ro.x, ro.y, ro.z, rd.x, rd.y, rd.z, i);
                 next.hit[slot] = ray_sort_key(sc, region, rd);
+                }
             }
             if (want_refr) {                                                         // refraction child (:532-556)
                 const int slot = s[SHADE_Q_REFR][wid] + __popc(m_refr & lt);
+                if (slot < next.cap) {
                 const V3<R> ro = P - refr_n * R(1e-4);
                 store_ray(spawn_to, slot, ro.x, ro.y, ro.z, refr_d.x, refr_d.y, refr_d.z, (int)((unsigned)i | 0x80000000u));
                 next.hit[slot] = ray_sort_key(sc, region, refr_d);
+                }
             }
         }
     }
@@ -1976,7 +2023,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_resolve(DevScene<R> sc, Level
     const int n = ctr->count[level];
     unsigned long long n_hit = 0;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const int cap = lv.cap;
+    const size_t cap = (size_t)lv.cap;                     // 64-bit strides: 15 * cap passes 2^31 on deep binary ray trees
     Ray<R> wr;
     load_ray(lv.ray, i, wr);
     const V3<R> D = mk(wr.dx, wr.dy, wr.dz);
@@ -2019,12 +2066,12 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_resolve(DevScene<R> sc, Level
         }
     }
     if (level == 0) {
-        samples[i] = out.x; samples[sample_cap + i] = out.y; samples[2 * sample_cap + i] = out.z;
+        samples[i] = out.x; samples[(size_t)sample_cap + i] = out.y; samples[2 * (size_t)sample_cap + i] = out.z;
     } else {
         const int p = ray_parent(lv.ray, i);
         const int pi = p & 0x7fffffff;
         const int base = (p < 0) ? 3 : 0;
-        const int pc = prev.cap;
+        const size_t pc = (size_t)prev.cap;
         prev.child[(base + 0) * pc + pi] = out.x; prev.child[(base + 1) * pc + pi] = out.y; prev.child[(base + 2) * pc + pi] = out.z;
     }
     }  // grid-stride loop
@@ -2237,7 +2284,7 @@ private:
     int cta_pass_ = 7;                                  // CTA-wide first packet pass for: 1 camera rays, 2 spawned rays, 4 shadow rays (GMLRT_CTA_PASS)
     struct Launch { int grid = 148; size_t smem = 0; };
     Launch l_primary_, l_closest_, l_shadow_pivot_, l_shadow_axis_;                      // the four k_cull instantiations
-    CandQueue cq_{}; int cand_per_ray_ = 4, tile_shrink_ = 0;
+    CandQueue cq_{}; int cand_per_ray_ = 4, tile_shrink_ = 0; unsigned long long scene_sig_ = ~0ull;
     int* sort_hist_ = nullptr; int* sort_cursor_ = nullptr; int sort_nb_ = 2, sort_shift_ = 0, n_regions_ = 1; bool sort_clear_ = true;
     int* key_hist_ = nullptr; int* key_cursor_ = nullptr; int key_nb_ = 6;      // spawned rays by (origin leaf, direction cell); cleared with sort_hist_
     bool sort_spawned_ = true;
@@ -2261,7 +2308,11 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     CU_TRY(cudaStreamSynchronize(stream_));
     free_scene();
     const double t_b = now();
-    tile_shrink_ = 0;
+    {   // a scene of the same shape as the last one keeps the tile height that last fitted (a frame loop re-uploads every frame)
+        const unsigned long long sig = ((unsigned long long)S.leaves.size() << 40) ^ ((unsigned long long)S.width << 24) ^ ((unsigned long long)S.height << 8) ^
+                                       ((unsigned long long)S.depth << 4) ^ (unsigned long long)S.lights.size();
+        if (sig != scene_sig_) { tile_shrink_ = 0; scene_sig_ = sig; }
+    }
     // Device layout.  Objects (what closestHit / inShadow scan): the plain leaves, stably sorted by kind so that
     // equal kinds keep scan order, then the CSG objects.  After them, the member leaves of the CSG objects.  Every
     // per-leaf array has n_all entries (a CSG object's own entry is unused filler).
@@ -2539,7 +2590,11 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     std::vector<double> mult(depth_eff_);
     double sum_mult = 0, max_mult = 0;
     for (int l = 0; l < depth_eff_; l++) {
-        mult[l] = S.may_branch ? std::ldexp(1.0, std::min(l, 30)) : 1.0;     // binary ray tree only when a material asks for it
+        // Binary ray tree only when a material asks for it - and then the levels are sized for `branch_cap` rays per
+        // camera ray, not for the worst case 2^l (which would cut an 8K depth-5 frame into 44 thin tiles): k_shade
+        // refuses children beyond a level's capacity and raises Counters::overflow, the frame is traced again with
+        // smaller tiles over the same buffers.
+        mult[l] = S.may_branch ? std::min(std::ldexp(1.0, std::min(l, 30)), std::max(1.0, env_double("GMLRT_BRANCH_CAP", 2.0))) : 1.0;
         sum_mult += mult[l]; max_mult = std::max(max_mult, mult[l]);
     }
     // candidate queue: (ray, object, T) per survivor of the cull phase.  Unbounded objects (planes) survive every ray;
@@ -2554,14 +2609,16 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     size_t free_b = 0, total_b = 0;
     CU_TRY(cudaMemGetInfo(&free_b, &total_b));
     free_b += pool_bytes_;
-    double budget = std::min((double)free_b * 0.6, (double)env_size("GMLRT_POOL_MB", 24 * 1024) * 1048576.0);
-    double max_samples = std::min(budget / per_sample, (double)env_size("GMLRT_TILE_SAMPLES", 16u << 20));
+    // One tile per frame when it fits: fewer launches, and the sorted bins of the spawned / shadow rays are as full as
+    // the frame allows (4K spheres1024: 11.6 ms in two tiles, 10.5 ms in one).  180 GB of HBM3e is there to be used.
+    double budget = std::min((double)free_b * 0.6, (double)env_size("GMLRT_POOL_MB", 96 * 1024) * 1048576.0);
+    double max_samples = std::min(budget / per_sample, (double)env_size("GMLRT_TILE_SAMPLES", 64u << 20));
     max_samples = std::min(max_samples, 2.0e9 / (max_mult * std::max(nl, 1)));       // int32 indexing of node*n_lights
-    int rows = (int)std::min<double>(H, std::floor(max_samples / (4.0 * W)));
-    if (rows < 1) { err = "image row does not fit the device queue budget"; return GMLRT_E_OOM; }
-    rows = std::max(1, rows >> tile_shrink_);                   // after a candidate-queue overflow: same buffers, fewer rays
+    const int rows_full = (int)std::min<double>(H, std::floor(max_samples / (4.0 * W)));
+    if (rows_full < 1) { err = "image row does not fit the device queue budget"; return GMLRT_E_OOM; }
+    const int rows = std::max(1, rows_full >> tile_shrink_);    // after an overflow: same buffers, fewer rays
     rows_per_tile_ = rows;
-    const size_t S0 = (size_t)rows * W * 4;
+    const size_t S0 = (size_t)rows * W * 4, S0_full = (size_t)rows_full * W * 4;
     // carve one pool
     auto align = [](size_t x) { return (x + 255) & ~(size_t)255; };
     size_t off = 0;
@@ -2570,7 +2627,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     std::vector<LvOff> lo(depth_eff_);
     size_t max_cap = 0, stage_cap = 0;
     for (int l = 0; l < depth_eff_; l++) {
-        size_t cap = (size_t)std::min((double)S0 * mult[l], 2.0e9);
+        size_t cap = (size_t)std::min(std::min((double)S0 * std::ldexp(1.0, std::min(l, 30)), (double)S0_full * mult[l]), 2.0e9);   // never above the true worst case
         lo[l].cap = cap; max_cap = std::max(max_cap, cap);
         lo[l].ray = take(RAY_WORDS * cap * sizeof(R)); lo[l].parent = 0; lo[l].hit = take(cap * 4);
         if (l > 0) stage_cap = std::max(stage_cap, cap);
@@ -2581,7 +2638,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     size_t o_sq = take(8 * sq_cap * sizeof(R)), o_skip = take(sq_cap * 4), o_key = take(sq_cap * 4), o_tgt = take(sq_cap * 4), o_first = take(sq_cap * 4), o_perm = take(sq_cap * 4), o_sort = take(2 * SORT_BINS_MAX * sizeof(int));
     size_t o_keysort = take(2 * (size_t)KEY_BINS_MAX * sizeof(int));
     size_t o_stage = take(RAY_WORDS * stage_cap * sizeof(R));         // spawned rays wait here until k_keysort_scatter stores them sorted
-    const size_t cand_cap = std::min<size_t>((size_t)((double)max_cap * cand_per_ray_ * (double)(1 << tile_shrink_)), (size_t)2000000000);
+    const size_t cand_cap = std::min<size_t>((size_t)((double)S0_full * max_mult * cand_per_ray_), (size_t)2000000000);
     size_t o_cray = take(cand_cap * 4), o_cobj = take(cand_cap * 4), o_ct = take(cand_cap * sizeof(R)), o_ccount = take(256);
     size_t o_samples = take(3 * S0 * sizeof(R));
     size_t o_ray64 = kRobustPrimary ? take(6 * S0 * sizeof(double)) : 0;

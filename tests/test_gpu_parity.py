@@ -110,6 +110,26 @@ def test_tiling_does_not_change_the_raster(ctx64):
     assert np.array_equal(whole, tiled)
 
 
+@pytest.mark.parametrize("branch_cap", ["1", "1.5", None])
+def test_level_overflow_retraces_with_smaller_tiles(ctx64, branch_cap):
+    """Branching levels are sized below the worst case 2^l (plan_tiles); when a level fills up k_shade refuses the
+    children, the frame is discarded and traced again with smaller tiles over the same buffers.  A scene whose ray
+    tree really is binary must come out byte-identical to the oracle whatever the sizing."""
+    blob = scenes.to_blob(scenes.glass(160, 100, depth=5))
+    want, ost = oracle.render(blob, threads=THREADS)
+    assert ost.rays_refract > 0 and ost.rays_reflect + ost.rays_refract > 1.5 * ost.rays_primary      # the tree does branch
+    if branch_cap is not None:
+        os.environ["GMLRT_BRANCH_CAP"] = branch_cap
+    try:
+        got, st = ctx64.render(blob)
+        again, st2 = ctx64.render(blob)                         # the same scene again keeps the tile height that fitted
+    finally:
+        os.environ.pop("GMLRT_BRANCH_CAP", None)
+    assert np.array_equal(got, want) and np.array_equal(again, want)
+    for s in (st, st2):
+        assert (s.rays_primary, s.rays_reflect, s.rays_refract, s.rays_shadow) == (ost.rays_primary, ost.rays_reflect, ost.rays_refract, ost.rays_shadow)
+
+
 @pytest.mark.parametrize("n_parts", [2, 3, 8])
 def test_row_band_partitions_tile_the_frame(ctx64, n_parts):
     """gmlrt_set_partition: part k renders the 8-row bands k, k + n, ... as one run of virtual rows and leaves the
