@@ -43,6 +43,8 @@ namespace gmlrt {
 using gomath::gm;
 
 #define GMLRT_MAX_DEPTH 64
+#define GMLRT_PLANE_GRIDS 2
+#define GMLRT_PLANE_GRID 64
 #define NREC 16   // per-node shading record: P(3) N(3) colour(3) refl transp kr kd ks n |d|
 
 template <typename R> struct DevLight { int kind; R pos[3], color[3], axis[3], cos_cutoff, exponent; };
@@ -75,9 +77,15 @@ template <typename R> struct DevScene {
     // region; a point on a large object (an unbounded plane, or a bounding sphere much wider than a grid cell) belongs
     // to the cell of a uniform grid over the bounded objects.  Small regions are numbered along a Morton curve, so
     // that regions merged by a shift are neighbours in space.
-    const int* rid_of;             // [n_all] region of a small object (CSG member leaves: their object's), -1 = large
+    const int* rid_of;             // [n_all] region of a small object (CSG member leaves: their object's), -1 = large (grid cell),
+                                   //         -2 - k = unbounded plane with its own 2-D grid k (below)
     int n_small, grid_dim[3];
     R grid_lo[3], grid_inv[3];
+    // An unbounded plane is visible far beyond the bounded objects (a ground plane runs to the horizon), where a
+    // clamped grid would lump everything into its border cells.  Its points are keyed in its own object-space (x, z)
+    // instead, through g(x) = x / (1 + |x|): PLANE_GRID^2 cells that are fine under the objects and grow with distance.
+    int plane_base[GMLRT_PLANE_GRIDS];      // first region of plane grid k
+    R plane_par[GMLRT_PLANE_GRIDS][3];      // object-space centre (x, z) and 1 / scale
     double vw, vh;
     R ambient[3], bg0[3], bg1[3];
 };
@@ -92,7 +100,6 @@ template <typename R> struct Level {
                   //               (bits of T) << 32 | scan index, folded by one atomicMin (fold_hit)
     R* rec;       // [NREC][cap]
     R* child;     // [6][cap] colour returned by the reflection / refraction child
-    double* ray64; // [6][cap] level 0 in f32 mode only: the camera ray before rounding to float
     int cap;
 };
 
@@ -557,7 +564,7 @@ __device__ __forceinline__ Cull4<double> load_cull(const double* sm, int i) {
 }
 
 // What a launch's cull table was built for (host: Renderer::build_cull_table).
-template <typename R> struct CullFrame { int family; R e1[3], e2[3]; };   // AXIS: orthonormal basis of the plane orthogonal to the common direction
+template <typename R> struct CullFrame { int family; R e1[3], e2[3], axis[3]; };   // AXIS: orthonormal basis of the plane orthogonal to the common direction `axis` (the way the rays travel)
 
 template <typename R, int FAMILY> struct CullRay;
 // slack(L) < 0 (sign bit set)  <=>  the object may be hit; > 0  <=>  certainly missed
@@ -650,6 +657,34 @@ template <typename R> __device__ __forceinline__ bool hit_any_kind(int kind, con
     }
 }
 
+// ------------------------------------------------------------------ the camera ray of sample i, in double
+// Render (raytracer.go:632-652): sample i of a tile = pixel i / 4 (row-major from virtual row y0), sample i % 4.  Go's
+// PCG-DXSM stream of the (column, 20-row batch) work item is entered by jump-ahead, so every sample draws exactly the
+// numbers the reference draws.  k_gen rounds the result to the arithmetic type; the double-precision re-tests of the
+// throughput mode call this again for the few candidates they see instead of reading a stored 48-byte copy per sample.
+__constant__ gomath::PcgJump c_pcg_jump[160];   // affine maps advancing the PCG stream by 0..159 draws
+struct CamSrc { int y0; RowMap map; };          // which rows the level-0 rays of the current tile are
+template <typename R>
+__device__ __forceinline__ void camera_ray64(const DevScene<R>& sc, const CamSrc& cam, int i, double (&o)[3], double (&d)[3]) {
+    const int s = i & 3, pix = i >> 2;
+    const int x = pix % sc.W, y = cam.map.actual(cam.y0 + pix / sc.W);
+    const int ymin = (y / 20) * 20;                       // work item = (column, 20-row batch), :663-672
+    const int q = 8 * (y - ymin) + 2 * s;                 // draws consumed before this sample
+    gomath::Pcg rng;
+    rng.hi = 0xDEADull ^ (uint64_t)x;                     // :632-634
+    rng.lo = 0xBEEFull ^ (uint64_t)ymin;
+    const gomath::PcgJump J = c_pcg_jump[q];
+    gomath::affine128(rng.hi, rng.lo, J.mh, J.ml, J.ih, J.il);
+    const double dx = gomath::pcg_float64(rng) - 0.5;     // dx is drawn before dy (:642-643)
+    const double dy = gomath::pcg_float64(rng) - 0.5;
+    const double u = ((double)x + dx) / (double)(sc.W - 1) * sc.vw - sc.vw / 2.0;
+    const double v = ((double)y + dy) / (double)(sc.H - 1) * sc.vh - sc.vh / 2.0;
+    o[0] = u; o[1] = -v; o[2] = 0.0;                      // screen point; eye = (0,0,-1)
+    const double ex = o[0] - 0.0, ey = o[1] - 0.0, ez = o[2] - (-1.0);
+    const double m = sqrt(ex * ex + ey * ey + ez * ez);
+    d[0] = ex / m; d[1] = ey / m; d[2] = ez / m;
+}
+
 // Robust primary-ray test (throughput mode only).  The north_star asks for ZERO hit/miss flips on
 // primary rays against the float64 reference.  A float32 sphere test is trusted unless its
 // discriminant is inside the rounding band |disc| < 2^-17 (hb^2 + |a c|) or the origin is that
@@ -662,10 +697,11 @@ __device__ __forceinline__ bool csg_object_hit(const DevScene<R>& sc, int i, con
 }
 
 template <typename R>
-static __device__ __noinline__ bool hit_f64(const DevScene<R>& sc, int kind, int i, const double* ray64, int cap, int ri, float& t, int& code) {
+static __device__ __noinline__ bool hit_f64(const DevScene<R>& sc, int kind, int i, const CamSrc& cam, int ri, float& t, int& code) {
     Ray<double> w, o;
-    w.ox = ray64[ri]; w.oy = ray64[cap + ri]; w.oz = ray64[2 * (size_t)cap + ri];
-    w.dx = ray64[3 * (size_t)cap + ri]; w.dy = ray64[4 * (size_t)cap + ri]; w.dz = ray64[5 * (size_t)cap + ri];
+    double o64[3], d64[3];
+    camera_ray64(sc, cam, ri, o64, d64);
+    w.ox = o64[0]; w.oy = o64[1]; w.oz = o64[2]; w.dx = d64[0]; w.dy = d64[1]; w.dz = d64[2];
     double td = 0.0;
     bool h;
     if (kind == K_CSG) {
@@ -708,11 +744,11 @@ __device__ __forceinline__ bool plane_hit_robust32(const DevScene<R>& sc, int i,
 // the exact test of ray `w` against object i, exactly as <Type>.Intersect would decide it; `code` is the hit
 // code stored in Level::hit: leaf | flip << 27 | face << 28 (for a CSG object the member leaf that was hit)
 template <typename R, bool ROBUST>
-__device__ __noinline__ bool exact_hit(const DevScene<R>& sc, int i, const Ray<R>& w, const double* ray64, int cap, int ri, R& t, int& code) {
+__device__ __noinline__ bool exact_hit(const DevScene<R>& sc, int i, const Ray<R>& w, const CamSrc& cam, int ri, R& t, int& code) {
     const int kind = kind_of(sc.kind_begin, i);
     if constexpr (ROBUST) {
         if (kind == K_PLANE) { bool h = false; if (plane_hit_robust32(sc, i, w, h, t)) { code = i; return h; } }
-        if (kind != K_SPHERE) { float tf; const bool h = hit_f64<R>(sc, kind, i, ray64, cap, ri, tf, code); t = (R)tf; return h; }
+        if (kind != K_SPHERE) { float tf; const bool h = hit_f64<R>(sc, kind, i, cam, ri, tf, code); t = (R)tf; return h; }
     }
     if (kind == K_CSG) return csg_object_hit<R>(sc, i, sc.w2o, w, t, code);
     Mat34<R> M;
@@ -728,7 +764,7 @@ __device__ __noinline__ bool exact_hit(const DevScene<R>& sc, int i, const Ray<R
         const R disc = hb * hb - p;
         const R band = R(7.62939453125e-6) * (hb * hb + gm<R>::abs(p));     // 2^-17
         if (gm<R>::abs(disc) < band || gm<R>::abs(c) < R(7.62939453125e-6) * (oo + R(1))) {
-            float tf; const bool h = hit_f64<R>(sc, K_SPHERE, i, ray64, cap, ri, tf, code); t = (R)tf; return h;
+            float tf; const bool h = hit_f64<R>(sc, K_SPHERE, i, cam, ri, tf, code); t = (R)tf; return h;
         }
         code = i;
         if (disc >= R(0)) {
@@ -901,12 +937,15 @@ template <typename R> __device__ __forceinline__ bool packet_survives(const Cull
     const R inv = R(1) / pp;
     const R s2 = r2 * inv;                               // sin^2 of the sphere's angular radius alpha seen from the pivot
     const R sa = gm<R>::sqrt(s2) * R(1.0001), ca = gm<R>::sqrt(R(1) - s2);
-    const R c = gm<R>::abs(fma_(L.x, b.ax, fma_(L.y, b.ay, L.z * b.az))) * gm<R>::sqrt(inv);     // |cos| of the angle to the axis
+    const R rs = gm<R>::sqrt(inv);
+    if (pp * rs * (R(1) - sa) > b.rho) return false;     // nearest point of the sphere is beyond the packet's reach from the pivot (shadow rays; rho = inf otherwise)
+    const R c = gm<R>::abs(fma_(L.x, b.ax, fma_(L.y, b.ay, L.z * b.az))) * rs;     // |cos| of the angle to the axis
     return !(c < b.cos_t * ca - b.sin_t * sa - R(1e-5));      // angle <= theta + alpha
 }
 template <typename R> __device__ __forceinline__ bool packet_survives(const Cull4<R>& L, const WarpBound<R>& b, CullRay<R, CULL_AXIS>*) {
     const R du = L.x - b.ax, dv = L.y - b.ay;
     const R rr = gm<R>::sqrt(-L.z) * R(1.0001) + b.cos_t;      // sqrt(R^2 + margin) + rho; -L.z = +inf for unbounded objects
+    if (L.k < b.sin_t) return false;                     // the object's front end (C.axis + R, record word 3) is behind every origin of the packet
     return !(fma_(du, du, dv * dv) > rr * rr);
 }
 // GENERAL record (C, K = |C|^2 - R^2 - margin).  A ray from o (|o - oc| <= rho) that hits the sphere (C, R) at T > 0 is,
@@ -961,6 +1000,7 @@ __device__ __forceinline__ WarpBound<R> cta_bound(const R (*wbs)[WB_WORDS]) {
         const R du = b[0] - c.ax, dv = b[1] - c.ay;
         const R rho = oct_max<R>(act ? gm<R>::sqrt(fma_(du, du, dv * dv)) * R(1.0001) + b[3] : R(0));
         c.cos_t = rho * R(1.0001) + R(1e-6) * (gm<R>::abs(c.ax) + gm<R>::abs(c.ay) + R(1));
+        c.sin_t = oct_min<R>(act ? b[4] : gm<R>::inf());      // rear-most origin along the axis over the CTA
         return c;
     }
     const R qx = oct_sum<R>(act ? b[5] : R(0)), qy = oct_sum<R>(act ? b[6] : R(0)), qz = oct_sum<R>(act ? b[7] : R(0));
@@ -1007,6 +1047,7 @@ template <typename R> struct ClosestSource {                 // rays of one recu
     Level<R> lv;                                              // (levels >= 1 are stored sorted by origin object and direction cell)
     __device__ __forceinline__ int id(int i) const { return i; }
     __device__ __forceinline__ void load(int i, Ray<R>& out) const { load_ray(lv.ray, i, out); }
+    static constexpr bool is_shadow = false;
     __device__ __forceinline__ void init(int i) const {       // no hit yet (see fold_hit)
         lv.hit[i] = -1;
         if constexpr (sizeof(R) == 4) reinterpret_cast<unsigned long long*>(lv.order)[i] = ~0ull;
@@ -1025,6 +1066,15 @@ template <typename R> struct ShadowSource {                  // shadow rays of o
         out.ox = rec[0]; out.oy = rec[1]; out.oz = rec[2]; out.dx = rec[3]; out.dy = rec[4]; out.dz = rec[5];
     }
     __device__ __forceinline__ void init(int i) const { sq.first[base + id(i)] = 0x7fffffff; }
+    static constexpr bool is_shadow = true;
+    // How far from the light an occluder of ray i can be: inShadow accepts T * |d_in| < dist (:424), T > 0, on a ray
+    // that starts `dist` from the light and points at it - so points up to dist away on the near side and, when the
+    // incoming direction is shorter than 1, up to dist / |d_in| - dist beyond the light.
+    __device__ __forceinline__ R reach(int i) const {
+        const R* rec = sq.q + (size_t)(base + id(i)) * 8;
+        const R dist = rec[6], beyond = rec[6] / rec[7] - rec[6];
+        return beyond > dist ? beyond : dist;
+    }
 };
 
 template <typename R, int FAMILY, int RPT, typename Source>
@@ -1065,6 +1115,7 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
         CullRay<R, FAMILY> cr[RPT];
         bool active[RPT];
         int rid[RPT];                                          // what the exact kernels index the ray source with
+        R far_reach = R(0), rear = gm<R>::inf();               // shadow packets: farthest reach from the light / rear-most origin along the axis
 #pragma unroll
         for (int r = 0; r < RPT; r++) {
             const int i = ray0 + ((tid >> 5) * RPT + r) * 32 + lane;      // a warp owns 32 * RPT consecutive rays: a narrow packet
@@ -1073,8 +1124,17 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
             rid[r] = active[r] ? src.id(i) : 0;
             if (active[r]) { src.load(i, w); src.init(i); }
             cr[r].init(w, frame);
+            if constexpr (Source::is_shadow && FAMILY == CULL_PIVOT) { if (active[r]) { const R q = src.reach(i); far_reach = !(q <= far_reach) ? (q == q ? q : gm<R>::inf()) : far_reach; } }
+            if constexpr (Source::is_shadow && FAMILY == CULL_AXIS) {
+                if (active[r]) { const R q = fma_(w.ox, frame.axis[0], fma_(w.oy, frame.axis[1], w.oz * frame.axis[2])); rear = !(q >= rear) ? (q == q ? q : -gm<R>::inf()) : rear; }
+            }
         }
-        const WarpBound<R> wb = warp_bound<R, RPT>(cr, active);
+        WarpBound<R> wb = warp_bound<R, RPT>(cr, active);
+        // Shadow rays stop at the light: an object farther from a point light than every origin of the packet (plus
+        // what inShadow's T * |d_in| < dist lets through beyond the light), or wholly behind every origin along a
+        // directional light's rays, cannot occlude any of them.
+        if constexpr (FAMILY == CULL_PIVOT) wb.rho = Source::is_shadow ? warp_max(far_reach) * R(1.001) + R(1e-3) : gm<R>::inf();
+        if constexpr (FAMILY == CULL_AXIS) { const R q = Source::is_shadow ? warp_min(rear) : -gm<R>::inf(); wb.sin_t = q - R(1e-3) * (gm<R>::abs(q) + R(1)); }
         int n_active = 0;
 #pragma unroll
         for (int r = 0; r < RPT; r++) n_active += active[r] ? 1 : 0;
@@ -1245,7 +1305,7 @@ __device__ __forceinline__ bool exact_hit_kinds(const DevScene<R>& sc, int obj, 
         code = obj;
         return hit_sphere<R>(o, t, face);
     } else {
-        return exact_hit<R, false>(sc, obj, w, nullptr, 0, 0, t, code);
+        return exact_hit<R, false>(sc, obj, w, CamSrc{}, 0, t, code);
     }
 }
 // does this flavour own candidate object `obj`?  (objects are sorted by kind: spheres first)
@@ -1272,7 +1332,7 @@ constexpr int CAND_DEFER = 0x40000000;   // robust camera-ray pass: a sphere can
 
 template <typename R, bool ROBUST, bool COUNT, int KINDS>
 __global__ void __launch_bounds__(EXACT_THREADS) k_exact_closest(const __grid_constant__ DevScene<R> sc, const __grid_constant__ Level<R> lv,
-                                                                const __grid_constant__ CandQueue cq, Counters* ctr) {
+                                                                const __grid_constant__ CandQueue cq, Counters* ctr, const __grid_constant__ CamSrc cam) {
     static_assert(!ROBUST || KINDS != EXACT_ALL, "the robust camera-ray test runs as SPHERES (float32, inline) then REST (double)");
     const int count = min(*cq.count, cq.cap);
     const int n_spheres = sc.kind_begin[K_SPHERE + 1];
@@ -1319,7 +1379,7 @@ __global__ void __launch_bounds__(EXACT_THREADS) k_exact_closest(const __grid_co
                 }
                 if (!decided) {
                     float tf = 0.f;
-                    h = hit_f64<R>(sc, kind, obj, lv.ray64, lv.cap, ri, tf, code);
+                    h = hit_f64<R>(sc, kind, obj, cam, ri, tf, code);
                     t = (R)tf;
                 }
             } else {
@@ -1682,9 +1742,18 @@ template <typename R> __device__ __forceinline__ V3<R> clamp3(V3<R> a) {
 }
 template <typename R> __device__ __forceinline__ V3<R> ld3(const R* p) { return mk(p[0], p[1], p[2]); }
 // sort region of a point P on leaf `leaf` (DevScene::rid_of)
-template <typename R> __device__ __forceinline__ int region_of(const DevScene<R>& sc, int leaf, const V3<R>& P) {
+template <typename R> __device__ __forceinline__ int region_of(const DevScene<R>& sc, int leaf, const V3<R>& P, R px, R pz) {
     const int r = sc.rid_of[leaf];
     if (r >= 0) return r;
+    if (r <= -2) {                                       // unbounded plane: its own (x, z) = (px, pz), compressed by g
+        const int k = -2 - r;
+        const R x = (px - sc.plane_par[k][0]) * sc.plane_par[k][2], z = (pz - sc.plane_par[k][1]) * sc.plane_par[k][2];
+        const R gx = x / (R(1) + gm<R>::abs(x)), gz = z / (R(1) + gm<R>::abs(z));
+        auto cell2 = [](R g) { const R f = (g + R(1)) * R(GMLRT_PLANE_GRID / 2); const R hi = R(GMLRT_PLANE_GRID - 1); return (int)(f > R(0) ? (f < hi ? f : hi) : R(0)); };
+        int cx = cell2(gx), cz = cell2(gz);
+        if (cx & 1) cz = GMLRT_PLANE_GRID - 1 - cz;          // boustrophedon: consecutive cells are neighbours
+        return sc.plane_base[k] + cx * GMLRT_PLANE_GRID + cz;
+    }
     const R fx = (P.x - sc.grid_lo[0]) * sc.grid_inv[0], fy = (P.y - sc.grid_lo[1]) * sc.grid_inv[1], fz = (P.z - sc.grid_lo[2]) * sc.grid_inv[2];
     auto cell = [](R f, int dim) { const R hi = (R)(dim - 1); return (int)(f > R(0) ? (f < hi ? f : hi) : R(0)); };   // clamped as reals (P on a plane may be far outside the grid; NaN -> 0)
     const int cx = cell(fx, sc.grid_dim[0]), cy = cell(fy, sc.grid_dim[1]), cz = cell(fz, sc.grid_dim[2]);
@@ -1760,7 +1829,6 @@ __device__ __forceinline__ bool light_at(const DevLight<R>& L, V3<R> P, V3<R>& l
 }
 
 // ------------------------------------------------------------------ gen: camera rays (Render, raytracer.go:632-652)
-__constant__ gomath::PcgJump c_pcg_jump[160];   // affine maps advancing the PCG stream by 0..159 draws
 
 
 template <typename R>
@@ -1772,28 +1840,9 @@ __global__ void __launch_bounds__(256) k_gen(DevScene<R> sc, Level<R> lv, Counte
         ctr->count[0] = S;
     }
     if (i >= S) return;
-    const int s = i & 3, pix = i >> 2;
-    const int x = pix % sc.W, y = map.actual(y0 + pix / sc.W);
-    const int ymin = (y / 20) * 20;                       // work item = (column, 20-row batch), :663-672
-    const int q = 8 * (y - ymin) + 2 * s;                 // draws consumed before this sample
-    gomath::Pcg rng;
-    rng.hi = 0xDEADull ^ (uint64_t)x;                     // :632-634
-    rng.lo = 0xBEEFull ^ (uint64_t)ymin;
-    const gomath::PcgJump J = c_pcg_jump[q];
-    gomath::affine128(rng.hi, rng.lo, J.mh, J.ml, J.ih, J.il);
-    const double dx = gomath::pcg_float64(rng) - 0.5;     // dx is drawn before dy (:642-643)
-    const double dy = gomath::pcg_float64(rng) - 0.5;
-    const double u = ((double)x + dx) / (double)(sc.W - 1) * sc.vw - sc.vw / 2.0;
-    const double v = ((double)y + dy) / (double)(sc.H - 1) * sc.vh - sc.vh / 2.0;
-    const double ox = u, oy = -v, oz = 0.0;               // screen point; eye = (0,0,-1)
-    const double ex = ox - 0.0, ey = oy - 0.0, ez = oz - (-1.0);
-    const double m = sqrt(ex * ex + ey * ey + ez * ez);
-    const size_t cap = (size_t)lv.cap;                     // 64-bit strides: 15 * cap passes 2^31 on deep binary ray trees
-    store_ray(lv.ray, i, (R)ox, (R)oy, (R)oz, (R)(ex / m), (R)(ey / m), (R)(ez / m), 0);
-    if (lv.ray64) {
-        lv.ray64[i] = ox; lv.ray64[cap + i] = oy; lv.ray64[2 * cap + i] = oz;
-        lv.ray64[3 * cap + i] = ex / m; lv.ray64[4 * cap + i] = ey / m; lv.ray64[5 * cap + i] = ez / m;
-    }
+    double o[3], d[3];
+    camera_ray64(sc, CamSrc{y0, map}, i, o, d);
+    store_ray(lv.ray, i, (R)o[0], (R)o[1], (R)o[2], (R)d[0], (R)d[1], (R)d[2], 0);
 }
 
 // ------------------------------------------------------------------ shade (traceRay :498-556 minus the recursion)
@@ -1822,6 +1871,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
     R mat[10];
     for (int k = 0; k < 10; k++) mat[k] = R(0);
     int leaf = 0;
+    R obj_x = R(0), obj_z = R(0);                          // object-space hit point (x, z): the sort region of a point on an unbounded plane
     if (live) {
         leaf = h & HIT_LEAF_MASK;
         int face = h >> 28;
@@ -1832,6 +1882,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
         Ray<R> o;
         to_object(Mw, w, o);
         const V3<R> p = mk(o.ox + o.dx * t, o.oy + o.dy * t, o.oz + o.dz * t);       // Hit.PointObj
+        obj_x = p.x; obj_z = p.z;
         const int kind = sc.kind[leaf];
         const DevSurface<R>& sf = sc.surfaces[sc.surface[leaf]];
         R u = R(0), v = R(0);
@@ -1881,7 +1932,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
     }
     const R refl = mat[3], fuzz = mat[4], transp = mat[5], ior = mat[6];
     const V3<R> D = mk(w.dx, w.dy, w.dz);
-    const int region = live ? region_of(sc, leaf, P) : 0;
+    const int region = live ? region_of(sc, leaf, P, obj_x, obj_z) : 0;
     if (live) {
         R* rec = lv.rec + i;
         rec[(REC_P + 0) * cap] = P.x; rec[(REC_P + 1) * cap] = P.y; rec[(REC_P + 2) * cap] = P.z;
@@ -1898,7 +1949,6 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
         rec[REC_KR * cap] = kr;
         rec[REC_KD * cap] = mat[7]; rec[REC_KS * cap] = mat[8]; rec[REC_NEXP * cap] = mat[9];
         rec[REC_INLEN * cap] = length(D);
-        for (int k = 0; k < 6; k++) lv.child[k * cap + i] = R(0);
     }
     // Children.  Every ray may append one shadow query per light that can reach P (inShadow :411-414), a reflection
     // child (:512-529) and a refraction child (:532-556).  All queues of a block iteration are reserved in ONE round
@@ -1922,6 +1972,13 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
                 if (refr_d.x == R(0) && refr_d.y == R(0) && refr_d.z == R(0)) want_refr = false;
             }
         }
+    }
+    // A child slot is written by the child's own resolve pass.  Only a slot the combine will read although no child
+    // was spawned needs a zero here: refraction lost to total internal reflection, or the reflection slot of a
+    // transparent surface that does not reflect.  (At the deepest level nothing is spawned and k_resolve reads none.)
+    if (spawn && live && transp > R(0)) {
+        if (!want_refl) for (int k = 0; k < 3; k++) lv.child[k * cap + i] = R(0);
+        if (!want_refr) for (int k = 3; k < 6; k++) lv.child[k * cap + i] = R(0);
     }
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const unsigned lt = (1u << lane) - 1u;
@@ -2019,7 +2076,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
 // sample buffer at level 0.
 template <typename R>
 __global__ void __launch_bounds__(SHADE_THREADS) k_resolve(DevScene<R> sc, Level<R> lv, Level<R> prev, const unsigned char* occl,
-                                                           Counters* ctr, int level, R* samples, int sample_cap) {
+                                                           Counters* ctr, int level, R* samples, int sample_cap, int has_children) {
     const int n = ctr->count[level];
     unsigned long long n_hit = 0;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
@@ -2056,11 +2113,12 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_resolve(DevScene<R> sc, Level
         if (refl == R(0) && transp == R(0)) {
             out = clamp3(hadamard(L, C));
         } else {
-            const V3<R> rc = mk(lv.child[i], lv.child[cap + i], lv.child[2 * cap + i]);
+            const V3<R> zero = mk(R(0), R(0), R(0));             // the deepest level has no children: traceRay returns black at depth 0 (:488-491)
+            const V3<R> rc = has_children ? mk(lv.child[i], lv.child[cap + i], lv.child[2 * cap + i]) : zero;
             if (transp == R(0)) {
                 out = clamp3(hadamard(L + rc * refl, C));
             } else {
-                const V3<R> fc = mk(lv.child[3 * cap + i], lv.child[4 * cap + i], lv.child[5 * cap + i]);
+                const V3<R> fc = has_children ? mk(lv.child[3 * cap + i], lv.child[4 * cap + i], lv.child[5 * cap + i]) : zero;
                 out = clamp3(hadamard(L * (R(1) - transp) + (rc * kr + fc * (R(1) - kr)), C));
             }
         }
@@ -2414,8 +2472,21 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
         };
         std::vector<std::pair<unsigned long long, int>> small;
         bool any_large = false;
+        int n_plane_grids = 0;
         for (int d = 0; d < n; d++) {
             const double* b = &bound_[(size_t)d * 4];
+            if (!std::isfinite(b[3]) && kind[d] == K_PLANE && n_plane_grids < GMLRT_PLANE_GRIDS) {
+                // centre = the middle of the bounded objects seen in the plane's object space; scale = 1.5 x their half extent there
+                const HostLeaf& L = S.leaves[order[d]];
+                const double mid[3] = {0.5 * (lo3[0] + hi3[0]), 0.5 * (lo3[1] + hi3[1]), 0.5 * (lo3[2] + hi3[2])};
+                const double cx = L.w2o[0] * mid[0] + L.w2o[1] * mid[1] + L.w2o[2] * mid[2] + L.w2o[3];
+                const double cz = L.w2o[8] * mid[0] + L.w2o[9] * mid[1] + L.w2o[10] * mid[2] + L.w2o[11];
+                const double stretch = std::sqrt(L.w2o[0] * L.w2o[0] + L.w2o[1] * L.w2o[1] + L.w2o[2] * L.w2o[2]);
+                const double scale = std::max(1e-9, 0.75 * ext_max * stretch);
+                sc.plane_par[n_plane_grids][0] = (R)cx; sc.plane_par[n_plane_grids][1] = (R)cz; sc.plane_par[n_plane_grids][2] = (R)(1.0 / scale);
+                rid_of[d] = -2 - n_plane_grids++;
+                continue;
+            }
             if (!std::isfinite(b[3]) || b[3] > large_r) { rid_of[d] = -1; any_large = true; continue; }
             int c[3];
             cell_of(b, c);
@@ -2430,6 +2501,11 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
         sc.n_small = (int)small.size();
         for (int k = 0; k < 3; k++) { sc.grid_dim[k] = dim[k]; sc.grid_lo[k] = (R)lo3[k]; sc.grid_inv[k] = (R)(1.0 / edge); }
         n_regions = std::max(1, sc.n_small + (any_large ? dim[0] * dim[1] * dim[2] : 0));
+        for (int k = 0; k < GMLRT_PLANE_GRIDS; k++) {
+            sc.plane_base[k] = n_regions;
+            if (k < n_plane_grids) n_regions += GMLRT_PLANE_GRID * GMLRT_PLANE_GRID;
+            else { sc.plane_par[k][0] = sc.plane_par[k][1] = R(0); sc.plane_par[k][2] = R(1); }
+        }
     }
     n_regions_ = n_regions;
     std::vector<DevLight<R>> lights(S.lights.size());
@@ -2479,7 +2555,7 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     sc.n_fpool = (int)fpool.size(); sc.n_itab = (int)S.itab.size();
     sc.W = S.width; sc.H = S.height; sc.depth = S.depth; sc.vw = S.vw; sc.vh = S.vh;
     // sort key of spawned rays: 6 k^2 direction cells per origin leaf, at most KEY_BINS_MAX bins in all
-    sc.key_k = (int)env_size("GMLRT_KEY_K", 3); sc.key_k = std::max(1, std::min(sc.key_k, 8));
+    sc.key_k = (int)env_size("GMLRT_KEY_K", 4); sc.key_k = std::max(1, std::min(sc.key_k, 8));
     sc.key_shift = 0;
     while ((size_t)(((n_regions - 1) >> sc.key_shift) + 1) * 6 * sc.key_k * sc.key_k > (size_t)KEY_BINS_MAX) sc.key_shift++;
     key_nb_ = (((n_regions - 1) >> sc.key_shift) + 1) * 6 * sc.key_k * sc.key_k;
@@ -2550,7 +2626,7 @@ int Renderer<R>::build_cull_table(int family, const double* v, double offset_abs
         normalize3(e1);
         e2[0] = v[1] * e1[2] - v[2] * e1[1]; e2[1] = v[2] * e1[0] - v[0] * e1[2]; e2[2] = v[0] * e1[1] - v[1] * e1[0];
         normalize3(e2);
-        for (int i = 0; i < 3; i++) { frame.e1[i] = (R)e1[i]; frame.e2[i] = (R)e2[i]; }
+        for (int i = 0; i < 3; i++) { frame.e1[i] = (R)e1[i]; frame.e2[i] = (R)e2[i]; frame.axis[i] = (R)v[i]; }
         for (int i = 0; i < 3; i++) { e1[i] = (double)frame.e1[i]; e2[i] = (double)frame.e2[i]; }      // what the device projects rays with
     }
     const double rel = CullMargin<R>::rel;
@@ -2566,7 +2642,11 @@ int Renderer<R>::build_cull_table(int family, const double* v, double offset_abs
             const R cu = (R)(C[0] * e1[0] + C[1] * e1[1] + C[2] * e1[2]), cv = (R)(C[0] * e2[0] + C[1] * e2[1] + C[2] * e2[2]);
             const double cc = C[0] * C[0] + C[1] * C[1] + C[2] * C[2];
             K = -(Rm * Rm) - rel * (cc + 1.0);
-            rec[0] = unbounded ? R(0) : cu; rec[1] = unbounded ? R(0) : cv; rec[3] = R(0);
+            rec[0] = unbounded ? R(0) : cu; rec[1] = unbounded ? R(0) : cv;
+            // word 3: how far along the rays' direction the object reaches (packet stage: nothing behind every origin can occlude)
+            const double front = C[0] * v[0] + C[1] * v[1] + C[2] * v[2] + Rm + 1e-3 * (std::sqrt(cc) + 1.0);
+            rec[3] = (unbounded || !(front == front)) ? (R)INFINITY : (R)front;
+            if ((double)rec[3] < front) rec[3] = std::nextafter(rec[3], (R)INFINITY);
             if (unbounded || !(K == K)) K = -INFINITY;
             rec[2] = (R)K;
             if ((double)rec[2] > K) rec[2] = std::nextafter(rec[2], (R)-INFINITY);
@@ -2605,7 +2685,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     const double cand_bytes = cand_per_ray_ * (8.0 + sizeof(R));
     const double node_bytes = (2 * RAY_WORDS + NREC + 8) * sizeof(R) + 12 + nl;      // ray record (+ its staging copy), rec, child, hit, order, occl
     const double shadow_bytes = nl * (8.0 * sizeof(R) + 20);
-    const double per_sample = sum_mult * node_bytes + max_mult * (shadow_bytes + cand_bytes) + 3 * sizeof(R) + (kRobustPrimary ? 48 : 0);
+    const double per_sample = sum_mult * node_bytes + max_mult * (shadow_bytes + cand_bytes) + 3 * sizeof(R);
     size_t free_b = 0, total_b = 0;
     CU_TRY(cudaMemGetInfo(&free_b, &total_b));
     free_b += pool_bytes_;
@@ -2641,7 +2721,6 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     const size_t cand_cap = std::min<size_t>((size_t)((double)S0_full * max_mult * cand_per_ray_), (size_t)2000000000);
     size_t o_cray = take(cand_cap * 4), o_cobj = take(cand_cap * 4), o_ct = take(cand_cap * sizeof(R)), o_ccount = take(256);
     size_t o_samples = take(3 * S0 * sizeof(R));
-    size_t o_ray64 = kRobustPrimary ? take(6 * S0 * sizeof(double)) : 0;
     if (off > pool_bytes_) {
         free_tiles();
         CU_TRY(cudaMalloc(&pool_, off));
@@ -2656,7 +2735,6 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
         L.ray = (R*)(base + lo[l].ray); L.hit = (int*)(base + lo[l].hit);
         L.t = (R*)(base + lo[l].t); L.order = (int*)(base + lo[l].order); L.rec = (R*)(base + lo[l].rec); L.child = (R*)(base + lo[l].child);
         occl_[l] = (unsigned char*)(base + lo[l].occl);
-        L.ray64 = (kRobustPrimary && l == 0) ? (double*)(base + o_ray64) : nullptr;
     }
     sq_.q = (R*)(base + o_sq); sq_.skip = (int*)(base + o_skip); sq_.key = (int*)(base + o_key); sq_.target = (int*)(base + o_tgt); sq_.cap = (int)sq_cap;
     sq_.per_light = (int)max_cap; sq_.count = shadow_counts_; sq_.first = (int*)(base + o_first); sq_.perm = (int*)(base + o_perm);
@@ -2704,17 +2782,18 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
         ids_n_ = (size_t)W * sc_.H * 4;
     }
     const int wide = sms_ * 16;
+    CamSrc cam{y0, map};                                    // rows of the current tile's camera rays (k_gen, double-precision re-tests)
     // exact kernels by kind (see ExactKinds): spheres inline at full occupancy, every other kind through exact_hit
     const bool have_spheres = sc_.kind_begin[K_SPHERE + 1] > 0, have_rest = sc_.kind_begin[K_SPHERE + 1] < sc_.n_leaves || sc_.n_leaves == 0;
     auto exact_closest = [&](int l, bool count) -> int {
         const int grid = sms_ * 16;
         if (have_spheres) {
-            if (count) k_exact_closest<R, false, true, EXACT_SPHERES><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
-            else k_exact_closest<R, false, false, EXACT_SPHERES><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
+            if (count) k_exact_closest<R, false, true, EXACT_SPHERES><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
+            else k_exact_closest<R, false, false, EXACT_SPHERES><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
         }
         if (have_rest) {
-            if (count) k_exact_closest<R, false, true, EXACT_REST><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
-            else k_exact_closest<R, false, false, EXACT_REST><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
+            if (count) k_exact_closest<R, false, true, EXACT_REST><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
+            else k_exact_closest<R, false, false, EXACT_REST><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
         }
         totals_.launches += (have_spheres && have_rest) ? 1 : 0;
         return GMLRT_OK;
@@ -2731,6 +2810,7 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
 #define MARK(cls) do { if ((mrc = mark(cls))) return mrc; } while (0)
     for (int ty = y0; ty < y1; ty += rows_per_tile_) {
         const int rows = std::min(rows_per_tile_, y1 - ty);
+        cam.y0 = ty;
         const int S = rows * W * 4;
         MARK(KC_GEN);
         k_gen<R><<<(S + 255) / 256, 256, 0, stream_>>>(sc_, levels_[0], ctr_, ty, rows, map);
@@ -2761,11 +2841,11 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
                 if (kRobustPrimary) {
                     // float32 spheres inline; then the double-precision pass: other kinds + the spheres the first pass deferred
                     if (counting) {
-                        if (have_spheres) k_exact_closest<R, kRobustPrimary, true, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
-                        k_exact_closest<R, kRobustPrimary, true, EXACT_REST><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
+                        if (have_spheres) k_exact_closest<R, kRobustPrimary, true, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
+                        k_exact_closest<R, kRobustPrimary, true, EXACT_REST><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
                     } else {
-                        if (have_spheres) k_exact_closest<R, kRobustPrimary, false, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
-                        k_exact_closest<R, kRobustPrimary, false, EXACT_REST><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
+                        if (have_spheres) k_exact_closest<R, kRobustPrimary, false, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
+                        k_exact_closest<R, kRobustPrimary, false, EXACT_REST><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
                     }
                     totals_.launches += have_spheres ? 1 : 0;
                 } else {
@@ -2825,7 +2905,7 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             const int cap_blocks = (levels_[l].cap + SHADE_THREADS - 1) / SHADE_THREADS;
             MARK(KC_RESOLVE);
             k_resolve<R><<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
-                sc_, levels_[l], l > 0 ? levels_[l - 1] : levels_[l], occl_[l], ctr_, l, samples_, sample_cap_);
+                sc_, levels_[l], l > 0 ? levels_[l - 1] : levels_[l], occl_[l], ctr_, l, samples_, sample_cap_, l + 1 < depth_eff_ ? 1 : 0);
             totals_.launches++;
         }
         MARK(KC_PIXELS);
