@@ -351,8 +351,8 @@ def main():
     C, CH = P + RF + RR, RF + RR                                           # closest-hit queries; spawned (child) rays
     Xs = float(counts[15]); Xc = float(counts[8]) - Xs                     # exact tests: shadow / closest candidates
     model_bytes = {
-        0: P * (8 * wb + (48 if args.precision == "f32" else 0)),          # gen: ray record (+ the float64 copy the robust re-tests read)
-        4: C * (8 * wb + 4 + wb) + NH * (16 * wb + 6 * wb) + S * (8 * wb + 9) + CH * (8 * wb + 4),   # shade: ray, hit, T in; rec, child slots, shadow and child records out
+        0: P * 8 * wb,                                                     # gen: one ray record per sample
+        4: C * 4 + NH * (8 * wb + wb) + NH * 16 * wb + S * (8 * wb + 13) + CH * (8 * wb + 4),        # shade: hit code of every ray, ray + T of the hits in; rec, shadow records (+ skip, key, target, flag) and child records (+ key) out
         5: C * (8 * wb + 4) + NH * (16 * wb + nl) + CH * 6 * wb + P * 3 * wb,                       # resolve: ray, hit, rec, flags in; colour to the parent / the samples
         6: P * 3 * wb + P,                                                 # pixels: 4 samples x 3 channels in, RGBA8 out
         7: Xc * ((8 + 8 * wb + 4 + wb) + (8 + wb + 8 + 4 + wb)) + Xs * (8 + 8 * wb + 8),           # exact: candidate + ray record + result; pick pass; shadow candidates
