@@ -242,8 +242,6 @@ def main():
     rays_frame = int(counts[:4].sum())
     flops_credited_frame = float(counts[6]) * 1e3       # what the reference's all-pairs scan would execute
     flops_frame = float(counts[9]) * 1e3                # what the scan kernels execute: 14 per cull test + table flops per exact test
-    ctx.set_profiling(world == 1)                       # an event before every launch: per-kernel-class device time, live (the roofline is an N = 1 figure)
-
     for _ in range(max(args.warmup, 3)):
         step()
     barrier()
@@ -258,15 +256,24 @@ def main():
     for _ in range(args.steps):
         st = step()
         launches += st.kernel_launches
-        kernel_ms += st.ms_kernels
-        for k in range(9):
-            class_ms[k] += st.ms_class[k]
-            class_launches[k] += st.launches_class[k]
     with torch.cuda.stream(ext):
         e1.record()
     barrier()
-    clocks = sampler.summary()
     ms_total = e0.elapsed_time(e1)
+    # Per-kernel times: the same K steps again with an event before every launch.  The timed steps above overlap the
+    # shadow queries of a level with the next level's closest-hit pipeline on a second stream, so a kernel's own
+    # duration can only be read with the launches serialised on one stream (which profiling mode does).  N = 1 only.
+    if world == 1:
+        ctx.set_profiling(True)
+        step()
+        for _ in range(args.steps):
+            st = step()
+            kernel_ms += st.ms_kernels
+            for k in range(9):
+                class_ms[k] += st.ms_class[k]
+                class_launches[k] += st.launches_class[k]
+        ctx.set_profiling(False)
+    clocks = sampler.summary()
     t = torch.tensor([ms_total, kernel_ms, float(launches)] + class_ms + [float(x) for x in class_launches], dtype=torch.float64,
                      device=f"cuda:{local_rank}")
     if dist is not None:
@@ -277,8 +284,8 @@ def main():
         ms_total, kernel_ms, launches = float(tmax[0]), float(tmax[1]), int(tsum[2])
         class_ms = [float(x) for x in tmax[3:12]]
         class_launches = [int(x) for x in tsum[12:21]]
-    ctx.set_profiling(False)
     ms_step = ms_total / args.steps
+    serial_ms_step = sum(class_ms) / args.steps if world == 1 else None
     value = rays_frame / (ms_step * 1e-3) / 1e6
 
     # end to end through the public C ABI: host blob in, host raster out, every step
@@ -409,7 +416,8 @@ def main():
             pass
         roof["traffic"] = traffic
     roof.update({
-        "note": "dominant single kernel by CUDA-event time inside the timed region (events before every launch on the library's stream).  HBM-bound "
+        "note": "dominant single kernel by CUDA-event time, measured live in this run (events before every launch on the library's stream, in the "
+                "serialised pass that follows the timed steps).  HBM-bound "
                 "kernels: achieved = ALGORITHMIC bytes (per-ray record sizes x the frame's ray counts from the counting pass, DESIGN.md 4) / event "
                 "time, peak = measured copy bandwidth.  FP32-bound kernels (k_cull): achieved = flops EXECUTED (device counters: cull tests x 15 / 7 / 7 "
                 "flops GENERAL / PIVOT / AXIS, packet tests x 20) / event time, peak = FFMA microbenchmark.  by_class has every class.  The "
@@ -439,6 +447,9 @@ def main():
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "frame_ms": e2e_ms, "h2d_bytes_per_step": len(blob), "d2h_bytes_per_step": W * H * 4,
                 "phase_ms": {k: v / e2e_steps for k, v in phase_ms.items()}, "upload_ms_each": [round(x, 3) for x in upload_each]},
         "kernel_ms_per_frame": {names[k]: class_ms[k] / args.steps for k in range(9)},
+        "kernel_ms_per_frame_note": "second pass of the same K steps with an event before every launch and all launches on one stream; "
+                                    "their sum (serialised_frame_ms) exceeds ms_per_step by what the two-stream overlap of the timed pass hides",
+        "serialised_frame_ms": serial_ms_step,
         "roofline": roof,
     }
     if world == 1 and not args.no_cpu_baseline:

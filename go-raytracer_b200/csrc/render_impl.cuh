@@ -2211,6 +2211,8 @@ public:
     int init(std::string& err) {
         CU_TRY(cudaSetDevice(dev_));
         CU_TRY(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
+        CU_TRY(cudaStreamCreateWithFlags(&shadow_stream_, cudaStreamNonBlocking));
+        overlap_shadows_ = env_size("GMLRT_OVERLAP_SHADOWS", 1) != 0;
         cudaDeviceProp prop;
         CU_TRY(cudaGetDeviceProperties(&prop, dev_));
         sms_ = prop.multiProcessorCount;
@@ -2321,6 +2323,11 @@ private:
         if (ctr_) cudaFree(ctr_);
         for (cudaEvent_t e : ev_pool_) cudaEventDestroy(e);
         ev_pool_.clear();
+        for (cudaEvent_t e : ev_shade_) cudaEventDestroy(e);
+        for (cudaEvent_t e : ev_shadow_) cudaEventDestroy(e);
+        ev_shade_.clear(); ev_shadow_.clear();
+        if (shadow_stream_) cudaStreamDestroy(shadow_stream_);
+        shadow_stream_ = nullptr;
         if (stream_) cudaStreamDestroy(stream_);
         frame_ = nullptr; ids_ = nullptr; ctr_ = nullptr; stream_ = nullptr;
     }
@@ -2335,6 +2342,14 @@ private:
 
     int dev_, sms_ = 148;
     cudaStream_t stream_ = nullptr;
+    // The shadow queries of level l (per light: sort, cull, exact) depend only on k_shade(l), like the closest-hit
+    // pipeline of level l + 1: they run on a second stream, so the issue-bound cull kernels of one overlap the
+    // memory-bound exact / shade kernels of the other and the tails of ~40 launches hide behind each other.
+    // k_shade(l + 1) reuses the shadow queue and waits for the shadows of level l; the resolve passes wait for all.
+    cudaStream_t shadow_stream_ = nullptr;
+    bool overlap_shadows_ = true;
+    std::vector<cudaEvent_t> ev_shade_, ev_shadow_;       // per level: k_shade done (main stream) / shadow queries done (shadow stream)
+    CandQueue cq_shadow_{};                                // the shadow stream's own candidate queue
     DevScene<R> sc_{};
     std::vector<void*> scene_allocs_;
     char* arena_ = nullptr; size_t arena_bytes_ = 0, arena_used_ = 0, arena_need_ = 1 << 20;
@@ -2358,7 +2373,7 @@ private:
     int cta_pass_ = 7;                                  // CTA-wide first packet pass for: 1 camera rays, 2 spawned rays, 4 shadow rays (GMLRT_CTA_PASS)
     struct Launch { int grid = 148; size_t smem = 0; };
     Launch l_primary_, l_closest_, l_shadow_pivot_, l_shadow_axis_;                      // the four k_cull instantiations
-    CandQueue cq_{}; int cand_per_ray_ = 4, tile_shrink_ = 0; unsigned long long scene_sig_ = ~0ull;
+    CandQueue cq_{}; int cand_per_ray_ = 4, tile_shrink_ = 0; unsigned long long scene_sig_ = ~0ull, planned_sig_ = ~0ull - 1; int planned_rows_full_ = 0;
     int* sort_hist_ = nullptr; int* sort_cursor_ = nullptr; int sort_nb_ = 2, sort_shift_ = 0, n_regions_ = 1; bool sort_clear_ = true;
     int* key_hist_ = nullptr; int* key_cursor_ = nullptr; int key_nb_ = 6;      // spawned rays by (origin leaf, direction cell); cleared with sort_hist_
     bool sort_spawned_ = true;
@@ -2699,7 +2714,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     int n_unbounded = 0;
     for (int d = 0; d < sc_.n_leaves; d++) n_unbounded += std::isinf(bound_[(size_t)d * 4 + 3]) ? 1 : 0;
     cand_per_ray_ = std::min<int>(std::max(sc_.n_leaves, 1), (int)env_size("GMLRT_CAND_PER_RAY", 4) + n_unbounded);
-    const double cand_bytes = cand_per_ray_ * (8.0 + sizeof(R));
+    const double cand_bytes = cand_per_ray_ * (16.0 + sizeof(R));            // two queues: closest (ray, object, T), shadow (ray, object)
     const double node_bytes = (2 * RAY_WORDS + NREC + 8) * sizeof(R) + 12 + nl;      // ray record (+ its staging copy), rec, child, hit, order, occl
     const double shadow_bytes = nl * (8.0 * sizeof(R) + 20);
     const double per_sample = sum_mult * node_bytes + max_mult * (shadow_bytes + cand_bytes) + 3 * sizeof(R);
@@ -2711,8 +2726,12 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     double budget = std::min((double)free_b * 0.6, (double)env_size("GMLRT_POOL_MB", 96 * 1024) * 1048576.0);
     double max_samples = std::min(budget / per_sample, (double)env_size("GMLRT_TILE_SAMPLES", 64u << 20));
     max_samples = std::min(max_samples, 2.0e9 / (max_mult * std::max(nl, 1)));       // int32 indexing of node*n_lights
-    const int rows_full = (int)std::min<double>(H, std::floor(max_samples / (4.0 * W)));
+    int rows_full = (int)std::min<double>(H, std::floor(max_samples / (4.0 * W)));
     if (rows_full < 1) { err = "image row does not fit the device queue budget"; return GMLRT_E_OOM; }
+    // A scene of the same shape as the last one keeps its plan: free memory wobbles by a few MB between uploads, and a
+    // budget-bound plan that grew by one row would free and reallocate the whole pool (~90 GB: 200 ms) inside a frame loop.
+    if (pool_ && planned_sig_ == scene_sig_ && planned_rows_full_ > 0) rows_full = planned_rows_full_;
+    planned_sig_ = scene_sig_; planned_rows_full_ = rows_full;
     const int rows = std::max(1, rows_full >> tile_shrink_);    // after an overflow: same buffers, fewer rays
     rows_per_tile_ = rows;
     const size_t S0 = (size_t)rows * W * 4, S0_full = (size_t)rows_full * W * 4;
@@ -2737,6 +2756,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     size_t o_stage = take(RAY_WORDS * stage_cap * sizeof(R));         // spawned rays wait here until k_keysort_scatter stores them sorted
     const size_t cand_cap = std::min<size_t>((size_t)((double)S0_full * max_mult * cand_per_ray_), (size_t)2000000000);
     size_t o_cray = take(cand_cap * 4), o_cobj = take(cand_cap * 4), o_ct = take(cand_cap * sizeof(R)), o_ccount = take(256);
+    size_t o_cray2 = take(cand_cap * 4), o_cobj2 = take(cand_cap * 4), o_ccount2 = take(256);      // shadow stream's queue (no T)
     size_t o_samples = take(3 * S0 * sizeof(R));
     if (off > pool_bytes_) {
         free_tiles();
@@ -2762,6 +2782,8 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     while (((n_regions_ - 1) >> sort_shift_) + 2 > sort_nb_) sort_shift_++;
     cq_.ray = (int*)(base + o_cray); cq_.obj = (int*)(base + o_cobj); cq_.t = (void*)(base + o_ct); cq_.count = (int*)(base + o_ccount);
     cq_.cap = (int)cand_cap;
+    cq_shadow_.ray = (int*)(base + o_cray2); cq_shadow_.obj = (int*)(base + o_cobj2); cq_shadow_.t = nullptr; cq_shadow_.count = (int*)(base + o_ccount2);
+    cq_shadow_.cap = (int)cand_cap;
     samples_ = (R*)(base + o_samples); sample_cap_ = (int)S0;
 
     // scan kernels: resident cull table when it fits, else two streaming buffers (chunks of whole groups)
@@ -2799,6 +2821,16 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
         ids_n_ = (size_t)W * sc_.H * 4;
     }
     const int wide = sms_ * 16;
+    // one stream when per-kernel events or the counting pass want the launches serialised
+    const bool two_streams = overlap_shadows_ && !profile_ && !counting && sc_.n_lights > 0;
+    cudaStream_t ss = two_streams ? shadow_stream_ : stream_;
+    const CandQueue& cqs = two_streams ? cq_shadow_ : cq_;
+    while (two_streams && (int)ev_shade_.size() < depth_eff_) {
+        cudaEvent_t a, b;
+        CU_TRY(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
+        CU_TRY(cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
+        ev_shade_.push_back(a); ev_shadow_.push_back(b);
+    }
     CamSrc cam{y0, map};                                    // rows of the current tile's camera rays (k_gen, double-precision re-tests)
     // exact kernels by kind (see ExactKinds): spheres inline at full occupancy, every other kind through exact_hit
     const bool have_spheres = sc_.kind_begin[K_SPHERE + 1] > 0, have_rest = sc_.kind_begin[K_SPHERE + 1] < sc_.n_leaves || sc_.n_leaves == 0;
@@ -2882,42 +2914,50 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             k_closest_pick<R><<<exact_grid, 256, 0, stream_>>>(sc_, levels_[l], cq_);
             totals_.launches += 3;
             const bool spawn = l + 1 < depth_eff_;
+            if (two_streams && l > 0) CU_TRY(cudaStreamWaitEvent(stream_, ev_shadow_[l - 1], 0));     // k_shade refills the shadow queue
             MARK(KC_SHADE);
             k_shade<R><<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
                 sc_, levels_[l], spawn ? levels_[l + 1] : levels_[l], sq_, occl_[l], ctr_, l, spawn ? 1 : 0,
                 (counting && l == 0) ? ids_ : nullptr, ty, map,
                 spawn ? (sort_spawned_ ? spawn_stage_ : levels_[l + 1].ray) : nullptr);
             totals_.launches += 2;
+            // shadow queries of this level: on the shadow stream, overlapping the next level's closest-hit pipeline
+            if (two_streams) {
+                CU_TRY(cudaEventRecord(ev_shade_[l], stream_));
+                CU_TRY(cudaStreamWaitEvent(ss, ev_shade_[l], 0));
+            }
             for (int li = 0; li < sc_.n_lights; li++) {    // per light: its shadow rays share a pivot (or an axis)
                 const bool axis = frame_light_[li].family == CULL_AXIS;
                 ShadowSource<R> ssrc{sq_, li * sq_.per_light};
-                CU_TRY(cudaMemsetAsync(cq_.count, 0, 2 * sizeof(int), stream_));
+                CU_TRY(cudaMemsetAsync(cqs.count, 0, 2 * sizeof(int), ss));
                 MARK(KC_SORT);
-                k_sort_hist<R><<<sms_ * 4, SORT_THREADS, 0, stream_>>>(sq_, li, sort_shift_, sort_nb_, sort_hist_, ctr_);
-                k_sort_scan<<<1, 1024, 0, stream_>>>(sort_nb_, sort_hist_, sort_cursor_);
-                k_sort_scatter<R><<<sms_ * 4, SORT_THREADS, 0, stream_>>>(sq_, li, sort_shift_, sort_nb_, sort_cursor_);
+                k_sort_hist<R><<<sms_ * 4, SORT_THREADS, 0, ss>>>(sq_, li, sort_shift_, sort_nb_, sort_hist_, ctr_);
+                k_sort_scan<<<1, 1024, 0, ss>>>(sort_nb_, sort_hist_, sort_cursor_);
+                k_sort_scatter<R><<<sms_ * 4, SORT_THREADS, 0, ss>>>(sq_, li, sort_shift_, sort_nb_, sort_cursor_);
                 totals_.launches += 3;
                 MARK(KC_SHADOW);
-                if (axis) k_cull<R, CULL_AXIS, RPT_FAMILY, ShadowSource<R>><<<l_shadow_axis_.grid, SCAN_THREADS, l_shadow_axis_.smem, stream_>>>(
-                    ssrc, &shadow_counts_[li], cull_light_[li], frame_light_[li], sc_.n_cull, cq_, ctr_, chunk_objs_, resident_ | ((cta_pass_ & 4) ? 2 : 0));
-                else k_cull<R, CULL_PIVOT, RPT_FAMILY, ShadowSource<R>><<<l_shadow_pivot_.grid, SCAN_THREADS, l_shadow_pivot_.smem, stream_>>>(
-                    ssrc, &shadow_counts_[li], cull_light_[li], frame_light_[li], sc_.n_cull, cq_, ctr_, chunk_objs_, resident_ | ((cta_pass_ & 4) ? 2 : 0));
+                if (axis) k_cull<R, CULL_AXIS, RPT_FAMILY, ShadowSource<R>><<<l_shadow_axis_.grid, SCAN_THREADS, l_shadow_axis_.smem, ss>>>(
+                    ssrc, &shadow_counts_[li], cull_light_[li], frame_light_[li], sc_.n_cull, cqs, ctr_, chunk_objs_, resident_ | ((cta_pass_ & 4) ? 2 : 0));
+                else k_cull<R, CULL_PIVOT, RPT_FAMILY, ShadowSource<R>><<<l_shadow_pivot_.grid, SCAN_THREADS, l_shadow_pivot_.smem, ss>>>(
+                    ssrc, &shadow_counts_[li], cull_light_[li], frame_light_[li], sc_.n_cull, cqs, ctr_, chunk_objs_, resident_ | ((cta_pass_ & 4) ? 2 : 0));
                 MARK(KC_EXACT);
                 const int sbase = li * sq_.per_light;
                 if (counting) {
-                    if (have_spheres) k_exact_shadow<R, true, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, sq_, sbase, cq_, ctr_, occl_[l]);
-                    if (have_rest) k_exact_shadow<R, true, EXACT_REST><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, sq_, sbase, cq_, ctr_, occl_[l]);
-                    k_shadow_finish<R, true><<<wide, 256, 0, stream_>>>(sc_, sq_, li, occl_[l], ctr_);
+                    if (have_spheres) k_exact_shadow<R, true, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_, sbase, cqs, ctr_, occl_[l]);
+                    if (have_rest) k_exact_shadow<R, true, EXACT_REST><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_, sbase, cqs, ctr_, occl_[l]);
+                    k_shadow_finish<R, true><<<wide, 256, 0, ss>>>(sc_, sq_, li, occl_[l], ctr_);
                 } else {                                   // the exact kernels set the occlusion flags themselves
-                    if (have_spheres) k_exact_shadow<R, false, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, sq_, sbase, cq_, ctr_, occl_[l]);
-                    if (have_rest) k_exact_shadow<R, false, EXACT_REST><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, sq_, sbase, cq_, ctr_, occl_[l]);
+                    if (have_spheres) k_exact_shadow<R, false, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_, sbase, cqs, ctr_, occl_[l]);
+                    if (have_rest) k_exact_shadow<R, false, EXACT_REST><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_, sbase, cqs, ctr_, occl_[l]);
                     totals_.launches--;
                 }
                 totals_.launches += (have_spheres && have_rest) ? 1 : 0;
                 totals_.launches += 3;
             }
-            if (sc_.n_lights > 0) CU_TRY(cudaMemsetAsync(shadow_counts_, 0, sizeof(int) * sc_.n_lights, stream_));
+            if (sc_.n_lights > 0) CU_TRY(cudaMemsetAsync(shadow_counts_, 0, sizeof(int) * sc_.n_lights, ss));
+            if (two_streams) CU_TRY(cudaEventRecord(ev_shadow_[l], ss));
         }
+        if (two_streams) CU_TRY(cudaStreamWaitEvent(stream_, ev_shadow_[depth_eff_ - 1], 0));       // the shadow stream is in order: every level is done
         for (int l = depth_eff_ - 1; l >= 0; l--) {
             const int cap_blocks = (levels_[l].cap + SHADE_THREADS - 1) / SHADE_THREADS;
             MARK(KC_RESOLVE);
