@@ -153,6 +153,16 @@ __device__ __forceinline__ void store_ray(double* rays, int i, double ox, double
     p[0] = make_double2(ox, oy); p[1] = make_double2(oz, dx); p[2] = make_double2(dy, dz);
     p[3] = make_double2(__longlong_as_double((long long)(unsigned)parent), 0.0);
 }
+// one 8-word record (a shadow ray: origin, direction, distance, |incoming direction|) as 16-byte vector stores
+__device__ __forceinline__ void store_rec8(float* recs, size_t i, float a, float b, float c, float d, float e, float f, float g, float h) {
+    float4* p = reinterpret_cast<float4*>(recs + i * 8);
+    p[0] = make_float4(a, b, c, d);
+    p[1] = make_float4(e, f, g, h);
+}
+__device__ __forceinline__ void store_rec8(double* recs, size_t i, double a, double b, double c, double d, double e, double f, double g, double h) {
+    double2* p = reinterpret_cast<double2*>(recs + i * 8);
+    p[0] = make_double2(a, b); p[1] = make_double2(c, d); p[2] = make_double2(e, f); p[3] = make_double2(g, h);
+}
 template <typename R> __device__ __forceinline__ int ray_parent(const R* rays, int i) {
     return reinterpret_cast<const int*>(rays + (size_t)i * RAY_WORDS + 6)[0];      // little-endian: the low word of word 6
 }
@@ -1935,7 +1945,11 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
         }
         if (ok) {
             if (sf.kind == GMLRT_SURFACE_CONST) { for (int k = 0; k < 10; k++) mat[k] = sf.material[k]; }
-            else ok = run_surface(sc, sf, face, u, v, mat);
+            else {                                       // the interpreter writes through a pointer: keep that array apart, so `mat` stays in registers on the constant path
+                R out[10];
+                ok = run_surface(sc, sf, face, u, v, out);
+                for (int k = 0; k < 10; k++) mat[k] = out[k];
+            }
         }
         if (!ok) {                                   // the reference panics here (:499-501)
             atomicExch(&ctr->error, 1);
@@ -2052,9 +2066,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
             light_at(sc.lights[li], P, ldir, dist, lcol);
             const int slot = li * sq.per_light + s[q][wid] + __popc(m & lt);
             const V3<R> so = P + N * R(1e-4);
-            R* rec = sq.q + (size_t)slot * 8;
-            rec[0] = so.x; rec[1] = so.y; rec[2] = so.z; rec[3] = ldir.x; rec[4] = ldir.y; rec[5] = ldir.z;
-            rec[6] = dist; rec[7] = length(D);
+            store_rec8(sq.q, (size_t)slot, so.x, so.y, so.z, ldir.x, ldir.y, ldir.z, dist, length(D));
             sq.skip[slot] = leaf < sc.n_leaves ? leaf : -1;      // a CSG object may shadow itself (oracle.c in_shadow)
             sq.key[slot] = region;
             sq.target[slot] = i * sc.n_lights + li;
@@ -2211,7 +2223,7 @@ public:
     int init(std::string& err) {
         CU_TRY(cudaSetDevice(dev_));
         CU_TRY(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
-        CU_TRY(cudaStreamCreateWithFlags(&shadow_stream_, cudaStreamNonBlocking));
+        for (int k = 0; k < SHADOW_STREAMS; k++) CU_TRY(cudaStreamCreateWithFlags(&shadow_stream_[k], cudaStreamNonBlocking));
         overlap_shadows_ = env_size("GMLRT_OVERLAP_SHADOWS", 1) != 0;
         cudaDeviceProp prop;
         CU_TRY(cudaGetDeviceProperties(&prop, dev_));
@@ -2324,10 +2336,13 @@ private:
         for (cudaEvent_t e : ev_pool_) cudaEventDestroy(e);
         ev_pool_.clear();
         for (cudaEvent_t e : ev_shade_) cudaEventDestroy(e);
-        for (cudaEvent_t e : ev_shadow_) cudaEventDestroy(e);
-        ev_shade_.clear(); ev_shadow_.clear();
-        if (shadow_stream_) cudaStreamDestroy(shadow_stream_);
-        shadow_stream_ = nullptr;
+        for (int k = 0; k < SHADOW_STREAMS; k++) {
+            for (cudaEvent_t e : ev_shadow_[k]) cudaEventDestroy(e);
+            ev_shadow_[k].clear();
+            if (shadow_stream_[k]) cudaStreamDestroy(shadow_stream_[k]);
+            shadow_stream_[k] = nullptr;
+        }
+        ev_shade_.clear();
         if (stream_) cudaStreamDestroy(stream_);
         frame_ = nullptr; ids_ = nullptr; ctr_ = nullptr; stream_ = nullptr;
     }
@@ -2343,13 +2358,16 @@ private:
     int dev_, sms_ = 148;
     cudaStream_t stream_ = nullptr;
     // The shadow queries of level l (per light: sort, cull, exact) depend only on k_shade(l), like the closest-hit
-    // pipeline of level l + 1: they run on a second stream, so the issue-bound cull kernels of one overlap the
-    // memory-bound exact / shade kernels of the other and the tails of ~40 launches hide behind each other.
+    // pipeline of level l + 1, and the lights are independent of each other: they run on SHADOW_STREAMS more streams
+    // (light li on stream li mod SHADOW_STREAMS), so the issue-bound cull kernels of one pipeline overlap the
+    // memory-bound exact / shade kernels of another and the tails of ~40 launches hide behind each other.
     // k_shade(l + 1) reuses the shadow queue and waits for the shadows of level l; the resolve passes wait for all.
-    cudaStream_t shadow_stream_ = nullptr;
+    static constexpr int SHADOW_STREAMS = 2;
+    cudaStream_t shadow_stream_[SHADOW_STREAMS] = {nullptr, nullptr};
     bool overlap_shadows_ = true;
-    std::vector<cudaEvent_t> ev_shade_, ev_shadow_;       // per level: k_shade done (main stream) / shadow queries done (shadow stream)
-    CandQueue cq_shadow_{};                                // the shadow stream's own candidate queue
+    std::vector<cudaEvent_t> ev_shade_, ev_shadow_[SHADOW_STREAMS];   // per level: k_shade done (main stream) / shadow queries done (shadow stream k)
+    CandQueue cq_shadow_[SHADOW_STREAMS] = {};             // each shadow stream's own candidate queue
+    int* sort_hist_sh_[SHADOW_STREAMS] = {nullptr, nullptr}; int* sort_cursor_sh_[SHADOW_STREAMS] = {nullptr, nullptr};
     DevScene<R> sc_{};
     std::vector<void*> scene_allocs_;
     char* arena_ = nullptr; size_t arena_bytes_ = 0, arena_used_ = 0, arena_need_ = 1 << 20;
@@ -2372,6 +2390,7 @@ private:
     int chunk_objs_ = GROUP, resident_ = 1; size_t table_smem_ = 0;
     int cta_pass_ = 7;                                  // CTA-wide first packet pass for: 1 camera rays, 2 spawned rays, 4 shadow rays (GMLRT_CTA_PASS)
     struct Launch { int grid = 148; size_t smem = 0; };
+    size_t cfg_smem_ = ~(size_t)0;
     Launch l_primary_, l_closest_, l_shadow_pivot_, l_shadow_axis_;                      // the four k_cull instantiations
     CandQueue cq_{}; int cand_per_ray_ = 4, tile_shrink_ = 0; unsigned long long scene_sig_ = ~0ull, planned_sig_ = ~0ull - 1; int planned_rows_full_ = 0;
     int* sort_hist_ = nullptr; int* sort_cursor_ = nullptr; int sort_nb_ = 2, sort_shift_ = 0, n_regions_ = 1; bool sort_clear_ = true;
@@ -2714,23 +2733,27 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     int n_unbounded = 0;
     for (int d = 0; d < sc_.n_leaves; d++) n_unbounded += std::isinf(bound_[(size_t)d * 4 + 3]) ? 1 : 0;
     cand_per_ray_ = std::min<int>(std::max(sc_.n_leaves, 1), (int)env_size("GMLRT_CAND_PER_RAY", 4) + n_unbounded);
-    const double cand_bytes = cand_per_ray_ * (16.0 + sizeof(R));            // two queues: closest (ray, object, T), shadow (ray, object)
+    const double cand_bytes = cand_per_ray_ * (8.0 + 8.0 * SHADOW_STREAMS + sizeof(R));   // queues: closest (ray, object, T), one (ray, object) per shadow stream
     const double node_bytes = (2 * RAY_WORDS + NREC + 8) * sizeof(R) + 12 + nl;      // ray record (+ its staging copy), rec, child, hit, order, occl
     const double shadow_bytes = nl * (8.0 * sizeof(R) + 20);
     const double per_sample = sum_mult * node_bytes + max_mult * (shadow_bytes + cand_bytes) + 3 * sizeof(R);
-    size_t free_b = 0, total_b = 0;
-    CU_TRY(cudaMemGetInfo(&free_b, &total_b));
-    free_b += pool_bytes_;
-    // One tile per frame when it fits: fewer launches, and the sorted bins of the spawned / shadow rays are as full as
-    // the frame allows (4K spheres1024: 11.6 ms in two tiles, 10.5 ms in one).  180 GB of HBM3e is there to be used.
-    double budget = std::min((double)free_b * 0.6, (double)env_size("GMLRT_POOL_MB", 96 * 1024) * 1048576.0);
-    double max_samples = std::min(budget / per_sample, (double)env_size("GMLRT_TILE_SAMPLES", 64u << 20));
-    max_samples = std::min(max_samples, 2.0e9 / (max_mult * std::max(nl, 1)));       // int32 indexing of node*n_lights
-    int rows_full = (int)std::min<double>(H, std::floor(max_samples / (4.0 * W)));
-    if (rows_full < 1) { err = "image row does not fit the device queue budget"; return GMLRT_E_OOM; }
     // A scene of the same shape as the last one keeps its plan: free memory wobbles by a few MB between uploads, and a
-    // budget-bound plan that grew by one row would free and reallocate the whole pool (~90 GB: 200 ms) inside a frame loop.
+    // budget-bound plan that grew by one row would free and reallocate the whole pool (~90 GB: 200 ms) inside a frame
+    // loop; cudaMemGetInfo itself was seen to take 6-30 ms now and then with a pool of that size.
+    int rows_full = 0;
     if (pool_ && planned_sig_ == scene_sig_ && planned_rows_full_ > 0) rows_full = planned_rows_full_;
+    else {
+        size_t free_b = 0, total_b = 0;
+        CU_TRY(cudaMemGetInfo(&free_b, &total_b));
+        free_b += pool_bytes_;
+        // One tile per frame when it fits: fewer launches, and the sorted bins of the spawned / shadow rays are as full as
+        // the frame allows (4K spheres1024: 11.6 ms in two tiles, 10.5 ms in one).  180 GB of HBM3e is there to be used.
+        double budget = std::min((double)free_b * 0.6, (double)env_size("GMLRT_POOL_MB", 96 * 1024) * 1048576.0);
+        double max_samples = std::min(budget / per_sample, (double)env_size("GMLRT_TILE_SAMPLES", 64u << 20));
+        max_samples = std::min(max_samples, 2.0e9 / (max_mult * std::max(nl, 1)));       // int32 indexing of node*n_lights
+        rows_full = (int)std::min<double>(H, std::floor(max_samples / (4.0 * W)));
+        if (rows_full < 1) { err = "image row does not fit the device queue budget"; return GMLRT_E_OOM; }
+    }
     planned_sig_ = scene_sig_; planned_rows_full_ = rows_full;
     const int rows = std::max(1, rows_full >> tile_shrink_);    // after an overflow: same buffers, fewer rays
     rows_per_tile_ = rows;
@@ -2751,12 +2774,13 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
         lo[l].occl = take(cap * std::max(nl, 1));
     }
     const size_t sq_cap = max_cap * std::max(nl, 1);
-    size_t o_sq = take(8 * sq_cap * sizeof(R)), o_skip = take(sq_cap * 4), o_key = take(sq_cap * 4), o_tgt = take(sq_cap * 4), o_first = take(sq_cap * 4), o_perm = take(sq_cap * 4), o_sort = take(2 * SORT_BINS_MAX * sizeof(int));
+    size_t o_sq = take(8 * sq_cap * sizeof(R)), o_skip = take(sq_cap * 4), o_key = take(sq_cap * 4), o_tgt = take(sq_cap * 4), o_first = take(sq_cap * 4), o_perm = take(sq_cap * 4), o_sort = take(2 * SHADOW_STREAMS * SORT_BINS_MAX * sizeof(int));
     size_t o_keysort = take(2 * (size_t)KEY_BINS_MAX * sizeof(int));
     size_t o_stage = take(RAY_WORDS * stage_cap * sizeof(R));         // spawned rays wait here until k_keysort_scatter stores them sorted
     const size_t cand_cap = std::min<size_t>((size_t)((double)S0_full * max_mult * cand_per_ray_), (size_t)2000000000);
     size_t o_cray = take(cand_cap * 4), o_cobj = take(cand_cap * 4), o_ct = take(cand_cap * sizeof(R)), o_ccount = take(256);
-    size_t o_cray2 = take(cand_cap * 4), o_cobj2 = take(cand_cap * 4), o_ccount2 = take(256);      // shadow stream's queue (no T)
+    size_t o_cray2[SHADOW_STREAMS], o_cobj2[SHADOW_STREAMS], o_ccount2[SHADOW_STREAMS];              // the shadow streams' queues (no T)
+    for (int k = 0; k < SHADOW_STREAMS; k++) { o_cray2[k] = take(cand_cap * 4); o_cobj2[k] = take(cand_cap * 4); o_ccount2[k] = take(256); }
     size_t o_samples = take(3 * S0 * sizeof(R));
     if (off > pool_bytes_) {
         free_tiles();
@@ -2782,8 +2806,11 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     while (((n_regions_ - 1) >> sort_shift_) + 2 > sort_nb_) sort_shift_++;
     cq_.ray = (int*)(base + o_cray); cq_.obj = (int*)(base + o_cobj); cq_.t = (void*)(base + o_ct); cq_.count = (int*)(base + o_ccount);
     cq_.cap = (int)cand_cap;
-    cq_shadow_.ray = (int*)(base + o_cray2); cq_shadow_.obj = (int*)(base + o_cobj2); cq_shadow_.t = nullptr; cq_shadow_.count = (int*)(base + o_ccount2);
-    cq_shadow_.cap = (int)cand_cap;
+    for (int k = 0; k < SHADOW_STREAMS; k++) {
+        cq_shadow_[k].ray = (int*)(base + o_cray2[k]); cq_shadow_[k].obj = (int*)(base + o_cobj2[k]); cq_shadow_[k].t = nullptr;
+        cq_shadow_[k].count = (int*)(base + o_ccount2[k]); cq_shadow_[k].cap = (int)cand_cap;
+        sort_hist_sh_[k] = sort_hist_ + (size_t)2 * k * SORT_BINS_MAX; sort_cursor_sh_[k] = sort_hist_sh_[k] + SORT_BINS_MAX;
+    }
     samples_ = (R*)(base + o_samples); sample_cap_ = (int)S0;
 
     // scan kernels: resident cull table when it fits, else two streaming buffers (chunks of whole groups)
@@ -2793,6 +2820,8 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     const size_t all = (size_t)sc_.n_cull * rec_bytes;
     if (all <= resident_max) { resident_ = 1; chunk_objs_ = sc_.n_cull; table_smem_ = all; }
     else { resident_ = 0; chunk_objs_ = (int)(chunk_bytes / rec_bytes) / GROUP * GROUP; table_smem_ = 2 * (size_t)chunk_objs_ * rec_bytes; }
+    if (cfg_smem_ == SURV_BYTES + table_smem_) return GMLRT_OK;      // launch shapes depend on the staged table size only
+    cfg_smem_ = SURV_BYTES + table_smem_;
     auto cfg = [&](auto kernel, Launch& L) -> int {
         int occ = 1;
         L.smem = SURV_BYTES + table_smem_;
@@ -2823,13 +2852,12 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
     const int wide = sms_ * 16;
     // one stream when per-kernel events or the counting pass want the launches serialised
     const bool two_streams = overlap_shadows_ && !profile_ && !counting && sc_.n_lights > 0;
-    cudaStream_t ss = two_streams ? shadow_stream_ : stream_;
-    const CandQueue& cqs = two_streams ? cq_shadow_ : cq_;
+    const int nss = two_streams ? std::min<int>(SHADOW_STREAMS, sc_.n_lights) : 1;       // shadow streams in use
     while (two_streams && (int)ev_shade_.size() < depth_eff_) {
-        cudaEvent_t a, b;
+        cudaEvent_t a;
         CU_TRY(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
-        CU_TRY(cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
-        ev_shade_.push_back(a); ev_shadow_.push_back(b);
+        ev_shade_.push_back(a);
+        for (int k = 0; k < SHADOW_STREAMS; k++) { CU_TRY(cudaEventCreateWithFlags(&a, cudaEventDisableTiming)); ev_shadow_[k].push_back(a); }
     }
     CamSrc cam{y0, map};                                    // rows of the current tile's camera rays (k_gen, double-precision re-tests)
     // exact kernels by kind (see ExactKinds): spheres inline at full occupancy, every other kind through exact_hit
@@ -2871,7 +2899,7 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             CU_TRY(cudaMemsetAsync(cq_.count, 0, 2 * sizeof(int), stream_));
             ClosestSource<R> csrc{levels_[l]};
             if (sort_clear_) {
-                CU_TRY(cudaMemsetAsync(sort_hist_, 0, SORT_BINS_MAX * sizeof(int), stream_));
+                CU_TRY(cudaMemsetAsync(sort_hist_, 0, 2 * SHADOW_STREAMS * SORT_BINS_MAX * sizeof(int), stream_));
                 CU_TRY(cudaMemsetAsync(key_hist_, 0, KEY_BINS_MAX * sizeof(int), stream_));
                 sort_clear_ = false;
             }
@@ -2914,7 +2942,7 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             k_closest_pick<R><<<exact_grid, 256, 0, stream_>>>(sc_, levels_[l], cq_);
             totals_.launches += 3;
             const bool spawn = l + 1 < depth_eff_;
-            if (two_streams && l > 0) CU_TRY(cudaStreamWaitEvent(stream_, ev_shadow_[l - 1], 0));     // k_shade refills the shadow queue
+            if (two_streams && l > 0) for (int k = 0; k < nss; k++) CU_TRY(cudaStreamWaitEvent(stream_, ev_shadow_[k][l - 1], 0));     // k_shade refills the shadow queue
             MARK(KC_SHADE);
             k_shade<R><<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
                 sc_, levels_[l], spawn ? levels_[l + 1] : levels_[l], sq_, occl_[l], ctr_, l, spawn ? 1 : 0,
@@ -2924,16 +2952,20 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             // shadow queries of this level: on the shadow stream, overlapping the next level's closest-hit pipeline
             if (two_streams) {
                 CU_TRY(cudaEventRecord(ev_shade_[l], stream_));
-                CU_TRY(cudaStreamWaitEvent(ss, ev_shade_[l], 0));
+                for (int k = 0; k < nss; k++) CU_TRY(cudaStreamWaitEvent(shadow_stream_[k], ev_shade_[l], 0));
             }
             for (int li = 0; li < sc_.n_lights; li++) {    // per light: its shadow rays share a pivot (or an axis)
                 const bool axis = frame_light_[li].family == CULL_AXIS;
+                const int sk = li % nss;
+                cudaStream_t ss = two_streams ? shadow_stream_[sk] : stream_;
+                const CandQueue& cqs = two_streams ? cq_shadow_[sk] : cq_;
+                int* const s_hist = sort_hist_sh_[sk]; int* const s_cursor = sort_cursor_sh_[sk];
                 ShadowSource<R> ssrc{sq_, li * sq_.per_light};
                 CU_TRY(cudaMemsetAsync(cqs.count, 0, 2 * sizeof(int), ss));
                 MARK(KC_SORT);
-                k_sort_hist<R><<<sms_ * 4, SORT_THREADS, 0, ss>>>(sq_, li, sort_shift_, sort_nb_, sort_hist_, ctr_);
-                k_sort_scan<<<1, 1024, 0, ss>>>(sort_nb_, sort_hist_, sort_cursor_);
-                k_sort_scatter<R><<<sms_ * 4, SORT_THREADS, 0, ss>>>(sq_, li, sort_shift_, sort_nb_, sort_cursor_);
+                k_sort_hist<R><<<sms_ * 4, SORT_THREADS, 0, ss>>>(sq_, li, sort_shift_, sort_nb_, s_hist, ctr_);
+                k_sort_scan<<<1, 1024, 0, ss>>>(sort_nb_, s_hist, s_cursor);
+                k_sort_scatter<R><<<sms_ * 4, SORT_THREADS, 0, ss>>>(sq_, li, sort_shift_, sort_nb_, s_cursor);
                 totals_.launches += 3;
                 MARK(KC_SHADOW);
                 if (axis) k_cull<R, CULL_AXIS, RPT_FAMILY, ShadowSource<R>><<<l_shadow_axis_.grid, SCAN_THREADS, l_shadow_axis_.smem, ss>>>(
@@ -2953,11 +2985,11 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
                 }
                 totals_.launches += (have_spheres && have_rest) ? 1 : 0;
                 totals_.launches += 3;
+                CU_TRY(cudaMemsetAsync(&shadow_counts_[li], 0, sizeof(int), ss));
             }
-            if (sc_.n_lights > 0) CU_TRY(cudaMemsetAsync(shadow_counts_, 0, sizeof(int) * sc_.n_lights, ss));
-            if (two_streams) CU_TRY(cudaEventRecord(ev_shadow_[l], ss));
+            if (two_streams) for (int k = 0; k < nss; k++) CU_TRY(cudaEventRecord(ev_shadow_[k][l], shadow_stream_[k]));
         }
-        if (two_streams) CU_TRY(cudaStreamWaitEvent(stream_, ev_shadow_[depth_eff_ - 1], 0));       // the shadow stream is in order: every level is done
+        if (two_streams) for (int k = 0; k < nss; k++) CU_TRY(cudaStreamWaitEvent(stream_, ev_shadow_[k][depth_eff_ - 1], 0));   // the shadow streams are in order: every level is done
         for (int l = depth_eff_ - 1; l >= 0; l--) {
             const int cap_blocks = (levels_[l].cap + SHADE_THREADS - 1) / SHADE_THREADS;
             MARK(KC_RESOLVE);

@@ -158,3 +158,17 @@ def test_bytecode_faults_like_the_reference():
         oracle.eval_surface(blob, 0, 5, 0.0, 0.0)         # index out of range -> evaluator.go:989-995
     with pytest.raises(gml.ErrArrayIndexOutOfBounds):
         gml.EvalSurfaceFn(5, 0.0, 0.0, st, calls[0].Scene.surface_fn)
+
+
+def test_glass_scene_really_branches():
+    """The level-overflow GPU test needs a scene whose ray tree is binary (a material may spawn a
+    reflection AND a refraction ray, raytracer.go:512, 532): more children than camera rays within two levels, so a
+    level sized for one ray per camera ray must overflow."""
+    from go_raytracer_b200 import scenes
+    blob = scenes.to_blob(scenes.glass(80, 50, depth=2))
+    _, st = oracle.render(blob, threads=4)
+    assert st.rays_refract > 0
+    assert st.rays_reflect + st.rays_refract > 1.2 * st.rays_primary
+    deep, st5 = oracle.render(scenes.to_blob(scenes.glass(80, 50, depth=5)), threads=4)
+    assert st5.rays_reflect + st5.rays_refract > 2.0 * st5.rays_primary
+    assert deep[..., 3].min() == 255
