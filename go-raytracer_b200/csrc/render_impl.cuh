@@ -1357,13 +1357,24 @@ __global__ void __launch_bounds__(EXACT_THREADS) k_exact_closest(const __grid_co
     const int n_spheres = sc.kind_begin[K_SPHERE + 1];
     R* ct = reinterpret_cast<R*>(cq.t);
     unsigned long long n_exact = 0, n_flops = 0;
-    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
-        const int ri = cq.ray[k];
-        int obj = cq.obj[k];
+    // The double-precision pass owns few candidates (the deferred spheres, the non-sphere kinds): it reads the object
+    // words four at a time, so that skipping what it does not own costs a quarter of the round trips, and fetches the
+    // ray index only for a candidate it keeps.
+    constexpr int U = (ROBUST && KINDS == EXACT_REST) ? 4 : 1;
+    for (int k0 = (blockIdx.x * blockDim.x + threadIdx.x) * U; k0 < count; k0 += gridDim.x * blockDim.x * U) {
+        int objs[U];
+        if (U == 4 && k0 + 4 <= count) { const int4 v = *reinterpret_cast<const int4*>(cq.obj + k0); objs[0] = v.x; objs[1 % U] = v.y; objs[2 % U] = v.z; objs[3 % U] = v.w; }
+        else { for (int u = 0; u < U; u++) objs[u] = k0 + u < count ? cq.obj[k0 + u] : -1; }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+        const int k = k0 + u;
+        if (k >= count) break;
+        int obj = objs[u];
         if (KINDS == EXACT_REST && obj < 0) continue;          // a sphere candidate the SPHERES pass has already resolved to a miss
         bool deferred = false;
         if (ROBUST && KINDS == EXACT_REST) { deferred = (obj & CAND_DEFER) != 0; obj &= ~CAND_DEFER; }
         if (KINDS != EXACT_ALL && obj < sc.n_leaves && !deferred && !exact_owns<KINDS>(obj, n_spheres)) continue;
+        const int ri = cq.ray[k];
         int code = -1; R t = R(0);
         if (obj < sc.n_leaves) {                               // a padding record can only be reached by a NaN ray
             if (COUNT && !deferred) { n_exact++; n_flops += (unsigned)sc.obj_flops[obj]; }
@@ -1410,6 +1421,7 @@ __global__ void __launch_bounds__(EXACT_THREADS) k_exact_closest(const __grid_co
             else code = -1;
         }
         cq.obj[k] = code; ct[k] = t;
+        }
     }
     if (COUNT) { warp_add(&ctr->exact_tests, n_exact); warp_add(&ctr->exact_flops, n_flops); }
 }
