@@ -360,8 +360,7 @@ def main():
     model_bytes = {
         0: P * 8 * wb,                                                     # gen: one ray record per sample
         4: C * 4 + NH * (8 * wb + wb) + NH * 16 * wb + S * (8 * wb + 13) + CH * (8 * wb + 4),        # shade: hit code of every ray, ray + T of the hits in; rec, shadow records (+ skip, key, target, flag) and child records (+ key) out
-        5: C * (8 * wb + 4) + NH * (16 * wb + nl) + CH * 6 * wb + P * 3 * wb,                       # resolve: ray, hit, rec, flags in; colour to the parent / the samples
-        6: P * 3 * wb + P,                                                 # pixels: 4 samples x 3 channels in, RGBA8 out
+        5: C * (8 * wb + 4) + NH * (16 * wb + nl) + CH * 6 * wb + P,                                # resolve: ray, hit, rec, flags in; colour to the parent; level 0 averages the 4 samples in registers and stores RGBA8
         7: Xc * ((8 + 8 * wb + 4 + wb) + (8 + wb + 8 + 4 + wb)) + Xs * (8 + 8 * wb + 8),           # exact: candidate + ray record + result; pick pass; shadow candidates
         8: S * 12 + CH * (8 + 16 * wb),                                    # sort: keys twice + permutation; key sort moves the 8-word records
     }
@@ -384,9 +383,9 @@ def main():
         by_class["cull_secondary (k_cull<GENERAL>), per-ray tests only"] = {"bound": "fp32", "ms_per_frame": class_ms[2] / args.steps, "achieved": tf,
                                                                             "unit": "TFLOP/s", "frac": tf / fp32_peak if fp32_peak else None}
     scan_ms = sum(class_ms[k] for k in (1, 2, 3, 7, 8))
-    # ---- the dominant single kernel: classes 0, 1, 2, 4, 5, 6 are one kernel each (3, 7, 8 are groups of smaller ones) ----
+    # ---- the dominant single kernel: classes 0, 1, 2, 4, 5 are one kernel each (3, 7, 8 are groups of smaller ones; 6 is gone: fused into k_resolve) ----
     kernel_of = {0: "k_gen", 1: "k_cull<PIVOT, ClosestSource> (camera rays)", 2: "k_cull<GENERAL, ClosestSource> (reflection / refraction rays)",
-                 4: "k_shade", 5: "k_resolve", 6: "k_pixels"}
+                 4: "k_shade", 5: "k_resolve"}
     traffic = None
     if world > 1:             # per-kernel events are an N = 1 tool
         dom = None

@@ -2116,15 +2116,19 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
 // sample buffer at level 0.
 template <typename R>
 __global__ void __launch_bounds__(SHADE_THREADS) k_resolve(DevScene<R> sc, Level<R> lv, Level<R> prev, const unsigned char* occl,
-                                                           Counters* ctr, int level, R* samples, int sample_cap, int has_children) {
+                                                           Counters* ctr, int level, uchar4* frame, int y0, RowMap map, int has_children) {
     const int n = ctr->count[level];
     unsigned long long n_hit = 0;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    // the loop bound is uniform per warp: every lane reaches the shuffles of the level-0 epilogue
+    for (int i0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31); i0 < n; i0 += gridDim.x * blockDim.x) {
+    const int i = i0 + (threadIdx.x & 31);
+    const bool valid = i < n;
     const size_t cap = (size_t)lv.cap;                     // 64-bit strides: 15 * cap passes 2^31 on deep binary ray trees
+    V3<R> out = mk(R(0), R(0), R(0));
+    if (valid) {
     Ray<R> wr;
     load_ray(lv.ray, i, wr);
     const V3<R> D = mk(wr.dx, wr.dy, wr.dz);
-    V3<R> out;
     if (lv.hit[i] < 0) {
         const R t = R(0.5) * (D.y + R(1));                                           // :495-496
         const V3<R> a = ld3(sc.bg0), b = ld3(sc.bg1);
@@ -2163,9 +2167,33 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_resolve(DevScene<R> sc, Level
             }
         }
     }
+    }  // valid
     if (level == 0) {
-        samples[i] = out.x; samples[(size_t)sample_cap + i] = out.y; samples[2 * (size_t)sample_cap + i] = out.z;
-    } else {
+        // img.Set(x, y, total * 0.25) -> Vec3.RGBA -> RGBAModel (raytracer.go:656, vec.go:104-107), fused: camera rays sit
+        // in (pixel, sample) order, so the 4 samples of a pixel are 4 neighbouring lanes (the grid stride and the ray
+        // count are multiples of 4: a quad is in the loop as a whole).  Lane 0 of the quad sums them in the reference's
+        // order - from zero, sample 0 first - quantises uint8(uint32(c * 65535) >> 8) and stores the pixel: no sample
+        // buffer, no separate pass.  The frame may be a peer device's (NVLink stores).
+        const unsigned quad = 0xffffffffu;
+        const int q0 = (threadIdx.x & 31) & ~3;
+        R c[3] = {out.x, out.y, out.z};
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            const R s1 = __shfl_sync(quad, c[k], q0 + 1), s2 = __shfl_sync(quad, c[k], q0 + 2), s3 = __shfl_sync(quad, c[k], q0 + 3);
+            R tot = R(0);
+            tot = tot + c[k]; tot = tot + s1; tot = tot + s2; tot = tot + s3;
+            c[k] = tot * R(0.25);
+        }
+        if (valid && (i & 3) == 0) {
+            const int pix = i >> 2;
+            uchar4 px;
+            px.x = (unsigned char)((unsigned)(c[0] * R(65535)) >> 8);
+            px.y = (unsigned char)((unsigned)(c[1] * R(65535)) >> 8);
+            px.z = (unsigned char)((unsigned)(c[2] * R(65535)) >> 8);
+            px.w = 0xFF;
+            frame[(size_t)map.actual(y0 + pix / sc.W) * sc.W + pix % sc.W] = px;
+        }
+    } else if (valid) {
         const int p = ray_parent(lv.ray, i);
         const int pi = p & 0x7fffffff;
         const int base = (p < 0) ? 3 : 0;
@@ -2177,26 +2205,6 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_resolve(DevScene<R> sc, Level
     if ((threadIdx.x & 31) == 0 && n_hit) atomicAdd(&ctr->rays_hit, n_hit);
 }
 
-// mean of the 4 samples and quantisation: img.Set(x, y, total*0.25) -> Vec3.RGBA -> RGBAModel
-// (raytracer.go:656, vec.go:104-107): uint8(uint32(c*65535) >> 8), alpha 0xFF.
-template <typename R>
-__global__ void __launch_bounds__(256) k_pixels(DevScene<R> sc, const R* samples, int sample_cap, uchar4* frame, int y0, int rows, RowMap map) {
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= rows * sc.W) return;
-    R c[3];
-    for (int k = 0; k < 3; k++) {
-        const R* s = samples + (size_t)k * sample_cap + 4 * p;
-        R tot = R(0);
-        tot = tot + s[0]; tot = tot + s[1]; tot = tot + s[2]; tot = tot + s[3];
-        c[k] = tot * R(0.25);
-    }
-    uchar4 px;
-    px.x = (unsigned char)((unsigned)(c[0] * R(65535)) >> 8);
-    px.y = (unsigned char)((unsigned)(c[1] * R(65535)) >> 8);
-    px.z = (unsigned char)((unsigned)(c[2] * R(65535)) >> 8);
-    px.w = 0xFF;
-    frame[(size_t)map.actual(y0 + p / sc.W) * sc.W + p % sc.W] = px;      // may be a peer device's frame (NVLink stores)
-}
 
 // ------------------------------------------------------------------ host side: one renderer per device
 #define CU_TRY(expr)                                                                                   \
@@ -2388,7 +2396,6 @@ private:
     std::vector<Level<R>> levels_;
     std::vector<unsigned char*> occl_;
     ShadowQueue<R> sq_{};
-    R* samples_ = nullptr; int sample_cap_ = 0;
     int rows_per_tile_ = 0, depth_eff_ = 1;
     uchar4* frame_ = nullptr; size_t frame_px_ = 0;
     uint8_t* frame_target_ = nullptr;       // where k_pixels stores instead of frame_ (a peer device's frame), or null
@@ -2793,7 +2800,6 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     size_t o_cray = take(cand_cap * 4), o_cobj = take(cand_cap * 4), o_ct = take(cand_cap * sizeof(R)), o_ccount = take(256);
     size_t o_cray2[SHADOW_STREAMS], o_cobj2[SHADOW_STREAMS], o_ccount2[SHADOW_STREAMS];              // the shadow streams' queues (no T)
     for (int k = 0; k < SHADOW_STREAMS; k++) { o_cray2[k] = take(cand_cap * 4); o_cobj2[k] = take(cand_cap * 4); o_ccount2[k] = take(256); }
-    size_t o_samples = take(3 * S0 * sizeof(R));
     if (off > pool_bytes_) {
         free_tiles();
         CU_TRY(cudaMalloc(&pool_, off));
@@ -2823,7 +2829,6 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
         cq_shadow_[k].count = (int*)(base + o_ccount2[k]); cq_shadow_[k].cap = (int)cand_cap;
         sort_hist_sh_[k] = sort_hist_ + (size_t)2 * k * SORT_BINS_MAX; sort_cursor_sh_[k] = sort_hist_sh_[k] + SORT_BINS_MAX;
     }
-    samples_ = (R*)(base + o_samples); sample_cap_ = (int)S0;
 
     // scan kernels: resident cull table when it fits, else two streaming buffers (chunks of whole groups)
     const size_t rec_bytes = 4 * sizeof(R);
@@ -3006,12 +3011,9 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             const int cap_blocks = (levels_[l].cap + SHADE_THREADS - 1) / SHADE_THREADS;
             MARK(KC_RESOLVE);
             k_resolve<R><<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
-                sc_, levels_[l], l > 0 ? levels_[l - 1] : levels_[l], occl_[l], ctr_, l, samples_, sample_cap_, l + 1 < depth_eff_ ? 1 : 0);
+                sc_, levels_[l], l > 0 ? levels_[l - 1] : levels_[l], occl_[l], ctr_, l, frame_target_ ? (uchar4*)frame_target_ : frame_, ty, map, l + 1 < depth_eff_ ? 1 : 0);
             totals_.launches++;
         }
-        MARK(KC_PIXELS);
-        k_pixels<R><<<(rows * W + 255) / 256, 256, 0, stream_>>>(sc_, samples_, sample_cap_, frame_target_ ? (uchar4*)frame_target_ : frame_, ty, rows, map);
-        totals_.launches++;
     }
     MARK(-1);
 #undef MARK
