@@ -203,7 +203,7 @@ def main():
         __cuda_array_interface__ = {"shape": (H, W, 4), "typestr": "|u1", "data": (ctx.frame_device_ptr, False), "version": 2}
     frame = torch.as_tensor(_Frame(), device=f"cuda:{local_rank}") if world > 1 else None
     use_ipc = world > 1 and args.gather == "ipc"
-    if use_ipc:     # rank 0 exports its frame once; the others map it and store their rows there from k_pixels
+    if use_ipc:     # rank 0 exports its frame once; the others map it and store their rows there from the level-0 k_resolve
         handle = torch.zeros(cuda.IPC_HANDLE_BYTES, dtype=torch.uint8, device=f"cuda:{local_rank}")
         if rank == 0:
             handle.copy_(torch.frombuffer(bytearray(ctx.frame_ipc_export()), dtype=torch.uint8))
@@ -437,7 +437,7 @@ def main():
                                (f" - DIAGNOSTIC: part 0 of {args.parts} only" if world == 1 and args.parts > 1 else ""), "precision": args.precision,
                    "l2": "inputs larger than L2: the per-level ray queues of one frame are GBs, no flush needed",
                    "parallelism": (f"8-row bands dealt round-robin over {world} GPU(s), scene replicated, " +
-                                   ("finished rows stored by k_pixels into GPU 0's frame over NVLink (CUDA IPC), no collective" if use_ipc
+                                   ("finished rows stored by the level-0 resolve kernel into GPU 0's frame over NVLink (CUDA IPC), no collective" if use_ipc
                                     else "NCCL reduce of disjoint bands to rank 0")) if world > 1 else "1 GPU"},
         "rays_per_frame": {"primary": int(counts[0]), "reflect": int(counts[1]), "refract": int(counts[2]), "shadow": int(counts[3]),
                            "shadow_occluded": int(counts[4]), "hit": int(counts[14])},

@@ -203,7 +203,7 @@ int gmlrt_upload(gmlrt_ctx* c, const void* blob, size_t blob_bytes) {
     for (size_t i = 0; i < c->r.size(); i++) {
         uint8_t* target = nullptr;
         if (c->remote_frame) target = c->remote_frame;                 // every device of this process stores into the remote frame
-        else if (i > 0 && c->peer_ok[i]) target = r0->frame();         // NVLink stores from k_pixels: the gather is fused
+        else if (i > 0 && c->peer_ok[i]) target = r0->frame();         // NVLink stores from the level-0 k_resolve: the gather is fused
         c->r[i]->set_frame_target(target);
     }
     if (c->n_parts > 1 && !c->remote_frame) {   // rows owned by other processes stay zero, so the rank frames can be summed
@@ -278,7 +278,7 @@ static int trace_once(gmlrt_ctx* c, gmlrt_stats* stats, bool& overflow) {
         if (vrows == 0) return;
         drc[di] = r->trace_rows(0, vrows, map, c->counting, derr[di]);
         if (drc[di] != GMLRT_OK || di == 0) return;
-        // gather on the producing device's stream: frame rows only when k_pixels could not store them itself
+        // gather on the producing device's stream: frame rows only when the resolve kernel could not store them itself
         cudaError_t e = cudaSetDevice(r->device());
         const size_t band = (size_t)c->band_rows * W * 4, pitch = band * map.n_parts, first = band * map.part;
         const int full = vrows / c->band_rows, rest = vrows % c->band_rows;

@@ -2398,7 +2398,7 @@ private:
     ShadowQueue<R> sq_{};
     int rows_per_tile_ = 0, depth_eff_ = 1;
     uchar4* frame_ = nullptr; size_t frame_px_ = 0;
-    uint8_t* frame_target_ = nullptr;       // where k_pixels stores instead of frame_ (a peer device's frame), or null
+    uint8_t* frame_target_ = nullptr;       // where the level-0 k_resolve stores instead of frame_ (a peer device's frame), or null
     int32_t* ids_ = nullptr; size_t ids_n_ = 0;
     Counters* ctr_ = nullptr;
     bool profile_ = false;

@@ -50,7 +50,7 @@ public:
     virtual int upload(const HostScene& S, std::string& err) = 0;
     // enqueue the kernels for virtual rows [v0, v1) of `map` on this device's stream (no host sync)
     virtual int trace_rows(int v0, int v1, const RowMap& map, bool counting, std::string& err) = 0;
-    // where k_pixels stores: this device's own frame (default) or a peer-mapped frame of the gathering device
+    // where the level-0 k_resolve stores its pixels: this device's own frame (default) or a peer-mapped frame of the gathering device
     virtual void set_frame_target(uint8_t* target) = 0;
     // after the stream is synchronised: fetch counters accumulated since reset_totals()
     virtual int fetch_totals(TraceTotals& out, std::string& err) = 0;

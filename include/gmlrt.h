@@ -228,7 +228,7 @@ int gmlrt_set_partition(gmlrt_ctx*, int part, int n_parts);
 void* gmlrt_frame_device(gmlrt_ctx*);
 
 /* One process per GPU without a collective: the gathering process exports its frame (after gmlrt_upload; the frame
- * keeps its address while width x height is unchanged), the others attach it, and from then on their pixel kernel
+ * keeps its address while width x height is unchanged), the others attach it, and from then on their level-0 resolve kernel
  * stores finished rows straight into that frame over NVLink (CUDA IPC peer mapping).  The caller orders "all
  * producers finished" before it reads the frame (a barrier).  attach(NULL, 0) detaches.                           */
 #define GMLRT_IPC_HANDLE_BYTES 64

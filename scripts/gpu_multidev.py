@@ -1,5 +1,5 @@
 """gmlrt_create on N devices of one process: rows dealt in 8-row bands, devices > 0 store into device 0's frame over
-NVLink from k_pixels.  Checks the raster against 1 device (parity mode: byte-exact, ids too) and times the f32 frame."""
+NVLink from the level-0 k_resolve.  Checks the raster against 1 device (parity mode: byte-exact, ids too) and times the f32 frame."""
 import sys
 import time
 
