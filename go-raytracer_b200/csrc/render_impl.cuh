@@ -61,6 +61,10 @@ template <typename R> struct DevScene {
     const unsigned long long* cum_flops;   // [n] credited flops of scan-order objects 0..s
     const R* w2o;                  // [n][12] rows 0..2 of WorldToObject
     const int* scan_of;            // device index -> scan-order index (tie-breaks, ids)
+    int pickless;                  // float32, spheres and planes only (face 0, no flip, no CSG): the scan folds (bits of T) << 32 | DEVICE index,
+                                   // which IS the closest hit - k_shade / k_resolve decode it, the exact kernels store no per-candidate
+                                   // result and the pick pass is not launched.  (Objects keep scan order within a kind, so the only tie the
+                                   // device index breaks differently from the reference is a sphere and a plane at bit-identical float32 T.)
     const double* w2o64;           // [n][12] the same matrices in double, for the robust primary-ray tests (f32 mode)
     const R* o2w;                  // [n][12]
     const R* fnormal;              // [n][18] world normals of plane / cube faces
@@ -1340,7 +1344,8 @@ template <int KINDS> __device__ __forceinline__ bool exact_owns(int obj, int n_s
 // whole rule at once - smaller T first, then the smaller scan index - so a single pick pass follows.  float64: T alone
 // fills the 64 bits, so the scan index is folded by a second pass over the candidates (k_closest_order).
 template <typename R> __device__ __forceinline__ unsigned long long hit_key32(const DevScene<R>& sc, float t, int code) {
-    return ((unsigned long long)__float_as_uint(t) << 32) | (unsigned)sc.scan_of[code & HIT_LEAF_MASK];
+    // pickless scenes (spheres and planes only) fold the device index itself, so the key IS the hit (DevScene::pickless)
+    return ((unsigned long long)__float_as_uint(t) << 32) | (unsigned)(sc.pickless ? (code & HIT_LEAF_MASK) : sc.scan_of[code & HIT_LEAF_MASK]);
 }
 template <typename R> __device__ __forceinline__ void fold_hit(const DevScene<R>& sc, const Level<R>& lv, int ri, R t, int code) {
     if constexpr (sizeof(R) == 4) atomicMin(&reinterpret_cast<unsigned long long*>(lv.order)[ri], hit_key32(sc, t, code));
@@ -1420,7 +1425,7 @@ __global__ void __launch_bounds__(EXACT_THREADS) k_exact_closest(const __grid_co
             if (h) fold_hit<R>(sc, lv, ri, t, code);
             else code = -1;
         }
-        cq.obj[k] = code; ct[k] = t;
+        if (!sc.pickless) { cq.obj[k] = code; ct[k] = t; }
         }
     }
     if (COUNT) { warp_add(&ctr->exact_tests, n_exact); warp_add(&ctr->exact_flops, n_flops); }
@@ -1772,6 +1777,22 @@ template <typename R> __device__ __forceinline__ V3<R> clamp3(V3<R> a) {
     return mk(gomath::clamp01(a.x), gomath::clamp01(a.y), gomath::clamp01(a.z));
 }
 template <typename R> __device__ __forceinline__ V3<R> ld3(const R* p) { return mk(p[0], p[1], p[2]); }
+// the closest hit of ray i of a level after the scan: hit code (or -1) and T.  PICKLESS: decoded from the folded key.
+template <typename R, bool PICKLESS> __device__ __forceinline__ void level_hit(const Level<R>& lv, int i, int& code, R& t) {
+    if constexpr (PICKLESS) {
+        const unsigned long long key = reinterpret_cast<const unsigned long long*>(lv.order)[i];
+        code = key == ~0ull ? -1 : (int)(unsigned)key;
+        t = (R)__uint_as_float((unsigned)(key >> 32));
+    } else { code = lv.hit[i]; t = R(0); }
+}
+template <typename R, bool PICKLESS> __device__ __forceinline__ bool level_is_miss(const Level<R>& lv, int i) {
+    if constexpr (PICKLESS) return reinterpret_cast<const unsigned long long*>(lv.order)[i] == ~0ull;
+    else return lv.hit[i] < 0;
+}
+template <typename R, bool PICKLESS> __device__ __forceinline__ void level_set_miss(const Level<R>& lv, int i) {
+    if constexpr (PICKLESS) reinterpret_cast<unsigned long long*>(lv.order)[i] = ~0ull;
+    else lv.hit[i] = -1;
+}
 // sort region of a point P on leaf `leaf` (DevScene::rid_of)
 template <typename R> __device__ __forceinline__ int region_of(const DevScene<R>& sc, int leaf, const V3<R>& P, R px, R pz) {
     const int r = sc.rid_of[leaf];
@@ -1880,7 +1901,7 @@ __global__ void __launch_bounds__(256) k_gen(DevScene<R> sc, Level<R> lv, Counte
 // rec slots
 enum { REC_P = 0, REC_N = 3, REC_COL = 6, REC_REFL = 9, REC_TRANSP = 10, REC_KR = 11, REC_KD = 12, REC_KS = 13, REC_NEXP = 14, REC_INLEN = 15 };
 
-template <typename R>
+template <typename R, bool PICKLESS>
 __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R> lv, Level<R> next, ShadowQueue<R> sq,
                                                          unsigned char* occl, Counters* ctr, int level, int spawn,
                                                          int32_t* ids, int y0, RowMap map, R* spawn_to) {
@@ -1892,13 +1913,16 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
     // slower: 11 more live registers spill at the 64 the kernel is held to.)
     const int stride = gridDim.x * blockDim.x;
     const int i_first = blockIdx.x * blockDim.x + threadIdx.x;
-    int h_nx = i_first < n ? lv.hit[i_first] : -1;
+    int h_nx = -1; R t_nx = R(0);
+    if (i_first < n) level_hit<R, PICKLESS>(lv, i_first, h_nx, t_nx);
     for (int blk0 = blockIdx.x * blockDim.x; blk0 < n; blk0 += stride) {   // uniform per block
     const int i = blk0 + threadIdx.x;
     const size_t cap = (size_t)lv.cap;                     // 64-bit strides: 15 * cap passes 2^31 on deep binary ray trees
     bool live = i < n;
     const int h = h_nx;                                    // = lv.hit[i], or -1 past the end
-    h_nx = (long long)i + stride < n ? lv.hit[i + stride] : -1;
+    const R t_pre = t_nx;
+    h_nx = -1;
+    if ((long long)i + stride < n) level_hit<R, PICKLESS>(lv, i + stride, h_nx, t_nx);
     if (ids && live) {                                     // level 0 only: primary hit ids in (y, x, sample) order
         const int pix = i >> 2;
         ids[((size_t)map.actual(y0 + pix / sc.W) * sc.W + pix % sc.W) * 4 + (i & 3)] = h < 0 ? -1 : sc.scan_of[h & HIT_LEAF_MASK];
@@ -1915,7 +1939,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
         int face = h >> 28;
         const bool flip = (h & HIT_FLIP_BIT) != 0;          // CSG: surface of a subtracted solid
         load_ray(lv.ray, i, w);
-        const R t = lv.t[i];
+        const R t = PICKLESS ? t_pre : lv.t[i];
         const R* Mw = sc.w2o + (size_t)leaf * 12;
         Ray<R> o;
         to_object(Mw, w, o);
@@ -1966,7 +1990,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
         if (!ok) {                                   // the reference panics here (:499-501)
             atomicExch(&ctr->error, 1);
             live = false;
-            lv.hit[i] = -1;
+            level_set_miss<R, PICKLESS>(lv, i);
         } else {
             P = mul_point(sc.o2w + (size_t)leaf * 12, p);
             if (flip) N = neg(N);
@@ -2114,7 +2138,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
 // computeLighting (:372-401) with the shadow flags, then the combine + clamp of traceRay
 // (:493-497, :506-508, :557-561); the result goes into the parent's child slot, or into the
 // sample buffer at level 0.
-template <typename R>
+template <typename R, bool PICKLESS>
 __global__ void __launch_bounds__(SHADE_THREADS) k_resolve(DevScene<R> sc, Level<R> lv, Level<R> prev, const unsigned char* occl,
                                                            Counters* ctr, int level, uchar4* frame, int y0, RowMap map, int has_children) {
     const int n = ctr->count[level];
@@ -2129,7 +2153,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_resolve(DevScene<R> sc, Level
     Ray<R> wr;
     load_ray(lv.ray, i, wr);
     const V3<R> D = mk(wr.dx, wr.dy, wr.dz);
-    if (lv.hit[i] < 0) {
+    if (level_is_miss<R, PICKLESS>(lv, i)) {
         const R t = R(0.5) * (D.y + R(1));                                           // :495-496
         const V3<R> a = ld3(sc.bg0), b = ld3(sc.bg1);
         out = mk(a.x + (b.x - a.x) * t, a.y + (b.y - a.y) * t, a.z + (b.z - a.z) * t);
@@ -2611,6 +2635,11 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     int* d_rid;
     if ((rc = to_device(rid_of, &d_rid, err))) return rc;
     sc.rid_of = d_rid;
+    {
+        bool simple = sizeof(R) == 4 && n_csg == 0 && env_size("GMLRT_PICKLESS", 1) != 0;
+        for (int d = 0; d < n; d++) simple = simple && (kind[d] == K_SPHERE || kind[d] == K_PLANE);
+        sc.pickless = simple ? 1 : 0;
+    }
     DevLight<R>* d_lights; DevSurface<R>* d_surfaces;
     if ((rc = to_device(w2o, &d_w2o, err)) || (rc = to_device(o2w, &d_o2w, err)) || (rc = to_device(fn, &d_fn, err)) ||
         (rc = to_device(scan_of, &d_scan, err)) || (rc = to_device(surface, &d_surf, err)) || (rc = to_device(kind, &d_kind, err)) ||
@@ -2956,12 +2985,14 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             }
             if (sizeof(R) == 8) k_closest_order<R><<<exact_grid, 256, 0, stream_>>>(sc_, levels_[l], cq_);
             else totals_.launches--;
-            k_closest_pick<R><<<exact_grid, 256, 0, stream_>>>(sc_, levels_[l], cq_);
+            if (!sc_.pickless) k_closest_pick<R><<<exact_grid, 256, 0, stream_>>>(sc_, levels_[l], cq_);
+            else totals_.launches--;
             totals_.launches += 3;
             const bool spawn = l + 1 < depth_eff_;
             if (two_streams && l > 0) for (int k = 0; k < nss; k++) CU_TRY(cudaStreamWaitEvent(stream_, ev_shadow_[k][l - 1], 0));     // k_shade refills the shadow queue
             MARK(KC_SHADE);
-            k_shade<R><<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
+            auto shade = sc_.pickless ? k_shade<R, sizeof(R) == 4> : k_shade<R, false>;
+            shade<<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
                 sc_, levels_[l], spawn ? levels_[l + 1] : levels_[l], sq_, occl_[l], ctr_, l, spawn ? 1 : 0,
                 (counting && l == 0) ? ids_ : nullptr, ty, map,
                 spawn ? (sort_spawned_ ? spawn_stage_ : levels_[l + 1].ray) : nullptr);
@@ -3010,7 +3041,8 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
         for (int l = depth_eff_ - 1; l >= 0; l--) {
             const int cap_blocks = (levels_[l].cap + SHADE_THREADS - 1) / SHADE_THREADS;
             MARK(KC_RESOLVE);
-            k_resolve<R><<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
+            auto resolve = sc_.pickless ? k_resolve<R, sizeof(R) == 4> : k_resolve<R, false>;
+            resolve<<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
                 sc_, levels_[l], l > 0 ? levels_[l - 1] : levels_[l], occl_[l], ctr_, l, frame_target_ ? (uchar4*)frame_target_ : frame_, ty, map, l + 1 < depth_eff_ ? 1 : 0);
             totals_.launches++;
         }
