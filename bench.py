@@ -409,8 +409,8 @@ def main():
                      "kernel_share_of_step": class_ms[dom] / max(sum(class_ms), 1e-9)})
         try:                  # DRAM bytes per launch of that kernel from the committed ncu --set full capture of this same workload
             tj = json.load(open(os.path.join(ROOT, "profiles", "dominant_traffic.json")))
-            if tj.get("kernel_class") == names[dom] and args.config == "spheres1024" and (W, H, args.depth) == (3840, 2160, 3) and args.precision == "f32":
-                traffic = tj.get("dram_bytes_per_launch")
+            if args.config == "spheres1024" and (W, H, args.depth) == (3840, 2160, 3) and args.precision == "f32":
+                traffic = tj.get("classes", {}).get(names[dom], {}).get("dram_bytes_per_launch")
         except Exception:
             pass
         roof["traffic"] = traffic

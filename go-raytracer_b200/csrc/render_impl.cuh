@@ -61,10 +61,12 @@ template <typename R> struct DevScene {
     const unsigned long long* cum_flops;   // [n] credited flops of scan-order objects 0..s
     const R* w2o;                  // [n][12] rows 0..2 of WorldToObject
     const int* scan_of;            // device index -> scan-order index (tie-breaks, ids)
-    int pickless;                  // float32, spheres and planes only (face 0, no flip, no CSG): the scan folds (bits of T) << 32 | DEVICE index,
-                                   // which IS the closest hit - k_shade / k_resolve decode it, the exact kernels store no per-candidate
-                                   // result and the pick pass is not launched.  (Objects keep scan order within a kind, so the only tie the
-                                   // device index breaks differently from the reference is a sphere and a plane at bit-identical float32 T.)
+    int pickless;                  // float32: the scan folds (bits of T) << 32 | leaf << 4 | flip << 3 | face (mode 2; mode 1, scenes of spheres
+                                   // and planes only: just the device index - measured 0.3 ms faster in k_shade), which IS the closest hit -
+                                   // k_shade / k_resolve decode it, the exact kernels store no per-candidate result and the pick pass is
+                                   // not launched.  A tie at bit-identical float32 T goes to the smaller device index (objects are sorted
+                                   // by kind and keep scan order within a kind; CSG members come last), where the reference takes the
+                                   // first object in scan order: the two differ only for coincident surfaces of different kinds.
     const double* w2o64;           // [n][12] the same matrices in double, for the robust primary-ray tests (f32 mode)
     const R* o2w;                  // [n][12]
     const R* fnormal;              // [n][18] world normals of plane / cube faces
@@ -1344,8 +1346,11 @@ template <int KINDS> __device__ __forceinline__ bool exact_owns(int obj, int n_s
 // whole rule at once - smaller T first, then the smaller scan index - so a single pick pass follows.  float64: T alone
 // fills the 64 bits, so the scan index is folded by a second pass over the candidates (k_closest_order).
 template <typename R> __device__ __forceinline__ unsigned long long hit_key32(const DevScene<R>& sc, float t, int code) {
-    // pickless scenes (spheres and planes only) fold the device index itself, so the key IS the hit (DevScene::pickless)
-    return ((unsigned long long)__float_as_uint(t) << 32) | (unsigned)(sc.pickless ? (code & HIT_LEAF_MASK) : sc.scan_of[code & HIT_LEAF_MASK]);
+    // pickless (DevScene::pickless): the low word is the hit code itself, rearranged as leaf << 4 | flip << 3 | face so
+    // that a tie in T goes to the smaller device index first - the key IS the hit
+    if (sc.pickless == 1) return ((unsigned long long)__float_as_uint(t) << 32) | (unsigned)(code & HIT_LEAF_MASK);      // spheres and planes: face 0, no flip
+    if (sc.pickless) return ((unsigned long long)__float_as_uint(t) << 32) | (unsigned)(((code & HIT_LEAF_MASK) << 4) | (((code >> 27) & 1) << 3) | ((code >> 28) & 7));
+    return ((unsigned long long)__float_as_uint(t) << 32) | (unsigned)sc.scan_of[code & HIT_LEAF_MASK];
 }
 template <typename R> __device__ __forceinline__ void fold_hit(const DevScene<R>& sc, const Level<R>& lv, int ri, R t, int code) {
     if constexpr (sizeof(R) == 4) atomicMin(&reinterpret_cast<unsigned long long*>(lv.order)[ri], hit_key32(sc, t, code));
@@ -1778,18 +1783,20 @@ template <typename R> __device__ __forceinline__ V3<R> clamp3(V3<R> a) {
 }
 template <typename R> __device__ __forceinline__ V3<R> ld3(const R* p) { return mk(p[0], p[1], p[2]); }
 // the closest hit of ray i of a level after the scan: hit code (or -1) and T.  PICKLESS: decoded from the folded key.
-template <typename R, bool PICKLESS> __device__ __forceinline__ void level_hit(const Level<R>& lv, int i, int& code, R& t) {
+template <typename R, int PICKLESS> __device__ __forceinline__ void level_hit(const Level<R>& lv, int i, int& code, R& t) {
     if constexpr (PICKLESS) {
         const unsigned long long key = reinterpret_cast<const unsigned long long*>(lv.order)[i];
-        code = key == ~0ull ? -1 : (int)(unsigned)key;
+        const unsigned low = (unsigned)key;                   // mode 1: the device index; mode 2: leaf << 4 | flip << 3 | face (hit_key32) -> leaf | flip << 27 | face << 28
+        if constexpr (PICKLESS == 1) code = key == ~0ull ? -1 : (int)low;
+        else code = key == ~0ull ? -1 : (int)((low >> 4) | ((low & 8u) << 24) | ((low & 7u) << 28));
         t = (R)__uint_as_float((unsigned)(key >> 32));
     } else { code = lv.hit[i]; t = R(0); }
 }
-template <typename R, bool PICKLESS> __device__ __forceinline__ bool level_is_miss(const Level<R>& lv, int i) {
+template <typename R, int PICKLESS> __device__ __forceinline__ bool level_is_miss(const Level<R>& lv, int i) {
     if constexpr (PICKLESS) return reinterpret_cast<const unsigned long long*>(lv.order)[i] == ~0ull;
     else return lv.hit[i] < 0;
 }
-template <typename R, bool PICKLESS> __device__ __forceinline__ void level_set_miss(const Level<R>& lv, int i) {
+template <typename R, int PICKLESS> __device__ __forceinline__ void level_set_miss(const Level<R>& lv, int i) {
     if constexpr (PICKLESS) reinterpret_cast<unsigned long long*>(lv.order)[i] = ~0ull;
     else lv.hit[i] = -1;
 }
@@ -1901,7 +1908,7 @@ __global__ void __launch_bounds__(256) k_gen(DevScene<R> sc, Level<R> lv, Counte
 // rec slots
 enum { REC_P = 0, REC_N = 3, REC_COL = 6, REC_REFL = 9, REC_TRANSP = 10, REC_KR = 11, REC_KD = 12, REC_KS = 13, REC_NEXP = 14, REC_INLEN = 15 };
 
-template <typename R, bool PICKLESS>
+template <typename R, int PICKLESS>
 __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R> lv, Level<R> next, ShadowQueue<R> sq,
                                                          unsigned char* occl, Counters* ctr, int level, int spawn,
                                                          int32_t* ids, int y0, RowMap map, R* spawn_to) {
@@ -1939,7 +1946,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
         int face = h >> 28;
         const bool flip = (h & HIT_FLIP_BIT) != 0;          // CSG: surface of a subtracted solid
         load_ray(lv.ray, i, w);
-        const R t = PICKLESS ? t_pre : lv.t[i];
+        const R t = PICKLESS != 0 ? t_pre : lv.t[i];
         const R* Mw = sc.w2o + (size_t)leaf * 12;
         Ray<R> o;
         to_object(Mw, w, o);
@@ -2138,7 +2145,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
 // computeLighting (:372-401) with the shadow flags, then the combine + clamp of traceRay
 // (:493-497, :506-508, :557-561); the result goes into the parent's child slot, or into the
 // sample buffer at level 0.
-template <typename R, bool PICKLESS>
+template <typename R, int PICKLESS>
 __global__ void __launch_bounds__(SHADE_THREADS) k_resolve(DevScene<R> sc, Level<R> lv, Level<R> prev, const unsigned char* occl,
                                                            Counters* ctr, int level, uchar4* frame, int y0, RowMap map, int has_children) {
     const int n = ctr->count[level];
@@ -2636,9 +2643,9 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     if ((rc = to_device(rid_of, &d_rid, err))) return rc;
     sc.rid_of = d_rid;
     {
-        bool simple = sizeof(R) == 4 && n_csg == 0 && env_size("GMLRT_PICKLESS", 1) != 0;
+        bool simple = n_csg == 0;                             // mode 1: spheres and planes only (face 0, no flip): the low word is the device index
         for (int d = 0; d < n; d++) simple = simple && (kind[d] == K_SPHERE || kind[d] == K_PLANE);
-        sc.pickless = simple ? 1 : 0;
+        sc.pickless = (sizeof(R) == 4 && n_all < (1 << 27) && env_size("GMLRT_PICKLESS", 1) != 0) ? (simple ? 1 : 2) : 0;
     }
     DevLight<R>* d_lights; DevSurface<R>* d_surfaces;
     if ((rc = to_device(w2o, &d_w2o, err)) || (rc = to_device(o2w, &d_o2w, err)) || (rc = to_device(fn, &d_fn, err)) ||
@@ -2991,7 +2998,7 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             const bool spawn = l + 1 < depth_eff_;
             if (two_streams && l > 0) for (int k = 0; k < nss; k++) CU_TRY(cudaStreamWaitEvent(stream_, ev_shadow_[k][l - 1], 0));     // k_shade refills the shadow queue
             MARK(KC_SHADE);
-            auto shade = sc_.pickless ? k_shade<R, sizeof(R) == 4> : k_shade<R, false>;
+            auto shade = sc_.pickless == 1 ? k_shade<R, sizeof(R) == 4 ? 1 : 0> : sc_.pickless ? k_shade<R, sizeof(R) == 4 ? 2 : 0> : k_shade<R, 0>;
             shade<<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
                 sc_, levels_[l], spawn ? levels_[l + 1] : levels_[l], sq_, occl_[l], ctr_, l, spawn ? 1 : 0,
                 (counting && l == 0) ? ids_ : nullptr, ty, map,
@@ -3041,7 +3048,7 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
         for (int l = depth_eff_ - 1; l >= 0; l--) {
             const int cap_blocks = (levels_[l].cap + SHADE_THREADS - 1) / SHADE_THREADS;
             MARK(KC_RESOLVE);
-            auto resolve = sc_.pickless ? k_resolve<R, sizeof(R) == 4> : k_resolve<R, false>;
+            auto resolve = sc_.pickless ? k_resolve<R, sizeof(R) == 4 ? 1 : 0> : k_resolve<R, 0>;
             resolve<<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
                 sc_, levels_[l], l > 0 ? levels_[l - 1] : levels_[l], occl_[l], ctr_, l, frame_target_ ? (uchar4*)frame_target_ : frame_, ty, map, l + 1 < depth_eff_ ? 1 : 0);
             totals_.launches++;
