@@ -160,6 +160,7 @@ def main():
     ap.add_argument("--cpu-crop", type=int, nargs=2, default=[1280, 720])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--parts", type=int, default=1, help="diagnostic (1 GPU): render only part 0 of PARTS row-band parts, i.e. one rank's share of an N-GPU frame")
+    ap.add_argument("--verify", action="store_true", help="N > 1: rank 0 also renders the whole frame alone and compares it with the gathered one")
     ap.add_argument("--gather", default="ipc", choices=["ipc", "nccl"],
                     help="N > 1: ipc = every rank's pixel kernel stores into rank 0's frame over NVLink (CUDA IPC peer mapping); "
                          "nccl = reduce(SUM) of the disjoint bands")
@@ -332,6 +333,18 @@ def main():
         e2e_ms = float(tt[0])
     e2e_value = rays_frame / (e2e_ms * 1e-3) / 1e6
 
+    gather_check = None
+    if args.verify and world > 1:       # the gathered frame of the last end-to-end step against the same frame rendered by one device alone
+        barrier()
+        if rank == 0:
+            solo = cuda.Context((local_rank,), prec)
+            whole, _ = solo.render(blob)
+            solo.close()
+            got = pinned.numpy()
+            same = (got == whole).all(axis=2)
+            gather_check = {"pixels_equal": float(same.mean()), "max_abs_diff": int(np.abs(got.astype(np.int16) - whole.astype(np.int16)).max())}
+        barrier()
+
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -451,6 +464,8 @@ def main():
         "serialised_frame_ms": serial_ms_step,
         "roofline": roof,
     }
+    if gather_check is not None:
+        line["gather_check"] = gather_check
     if world == 1 and not args.no_cpu_baseline:
         import oracle
         cores = os.cpu_count() or 8
