@@ -1397,16 +1397,23 @@ __global__ void __launch_bounds__(EXACT_THREADS) k_exact_closest(const __grid_co
                 Mat34<R> M;
                 load_w2o(sc.w2o, obj, M);
                 to_object(M.m, w, o);
+                // The textbook discriminant hb^2 - a c cancels two numbers of the size |o|^2 (a camera ray starts ~100 sphere
+                // radii away in object space), so its float32 rounding band is ~ +-7 % of the silhouette radius and one
+                // candidate in eight had to be redone in double.  The same quantity through the point of closest approach
+                // l = o + tc d,  disc = a (1 - |l|^2),  t0 = tc - sqrt((1 - |l|^2) / a)  has no such cancellation: the error of
+                // |l|^2 is ~ 20 eps |o| |l| (rounded matrix, rounded ray, the accumulation), the band 2^-17 (|o| |l| + 1) = 128 eps
+                // leaves a factor 6, and a deferral becomes the rare case it was meant to be.
                 const R a = o.dx * o.dx + o.dy * o.dy + o.dz * o.dz;
                 const R hb = o.ox * o.dx + o.oy * o.dy + o.oz * o.dz;
                 const R oo = o.ox * o.ox + o.oy * o.oy + o.oz * o.oz;
                 const R c = oo - R(1);
-                const R pr = a * c;
-                const R disc = hb * hb - pr;
-                const R band = R(7.62939453125e-6) * (hb * hb + gm<R>::abs(pr));     // 2^-17
-                if (gm<R>::abs(disc) < band || gm<R>::abs(c) < R(7.62939453125e-6) * (oo + R(1))) { cq.obj[k] = obj | CAND_DEFER; continue; }
+                const R tc = -hb / a;
+                const R lx = fma_(tc, o.dx, o.ox), ly = fma_(tc, o.dy, o.oy), lz = fma_(tc, o.dz, o.oz);
+                const R pp = lx * lx + ly * ly + lz * lz;
+                const R band = R(7.62939453125e-6) * (gm<R>::sqrt(oo * pp) + R(1));       // 2^-17
+                if (!(gm<R>::abs(R(1) - pp) >= band) || gm<R>::abs(c) < R(7.62939453125e-6) * (oo + R(1))) { cq.obj[k] = obj | CAND_DEFER; continue; }
                 code = obj; h = false;
-                if (disc >= R(0)) { const R t0 = (-hb - gm<R>::sqrt(disc)) / a; if (t0 > R(0)) { t = t0; h = true; } }
+                if (pp < R(1)) { const R t0 = tc - gm<R>::sqrt((R(1) - pp) / a); if (t0 > R(0)) { t = t0; h = true; } }
             } else if constexpr (ROBUST) {                     // REST: every non-sphere kind, and the deferred spheres, in double
                 const int kind = deferred ? (int)K_SPHERE : kind_of(sc.kind_begin, obj);
                 bool decided = false;
