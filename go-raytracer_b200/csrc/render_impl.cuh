@@ -1317,7 +1317,10 @@ constexpr int EXACT_THREADS = 128;
 // exact_hit (a call; 96-128 registers because of the CSG span lists), SPHERES only with the test inlined (the
 // candidates of other kinds are skipped) and REST = every kind but spheres, through exact_hit.  A scene of spheres
 // launches SPHERES alone, a mixed scene SPHERES then REST over the same candidate list.
-enum ExactKinds { EXACT_ALL = 0, EXACT_SPHERES = 1, EXACT_REST = 2 };
+enum ExactKinds { EXACT_ALL = 0, EXACT_SPHERES = 1, EXACT_REST = 2, EXACT_SIMPLE = 3, EXACT_CSG = 4 };
+// SIMPLE = the other plain kinds (plane, cube, cylinder, cone) with their tests inlined, CSG = the span-list objects only:
+// outside the double-precision camera-ray pass (which keeps REST = everything but spheres) a mixed scene runs SPHERES,
+// SIMPLE and CSG over the same candidate list, so that only CSG candidates pay for the 96-128 registers of csg_hit.
 
 template <typename R, int KINDS>
 __device__ __forceinline__ bool exact_hit_kinds(const DevScene<R>& sc, int obj, const Ray<R>& w, R& t, int& code) {
@@ -1329,13 +1332,28 @@ __device__ __forceinline__ bool exact_hit_kinds(const DevScene<R>& sc, int obj, 
         int face = 0;
         code = obj;
         return hit_sphere<R>(o, t, face);
+    } else if constexpr (KINDS == EXACT_SIMPLE) {
+        Mat34<R> M;
+        load_w2o(sc.w2o, obj, M);
+        Ray<R> o;
+        to_object(M.m, w, o);
+        int face = 0;
+        const bool h = hit_any_kind<R>(kind_of(sc.kind_begin, obj), o, t, face);
+        code = obj | (face << 28);
+        return h;
+    } else if constexpr (KINDS == EXACT_CSG) {
+        return csg_object_hit<R>(sc, obj, sc.w2o, w, t, code);
     } else {
         return exact_hit<R, false>(sc, obj, w, CamSrc{}, 0, t, code);
     }
 }
 // does this flavour own candidate object `obj`?  (objects are sorted by kind: spheres first)
-template <int KINDS> __device__ __forceinline__ bool exact_owns(int obj, int n_spheres) {
-    return KINDS == EXACT_ALL || (KINDS == EXACT_SPHERES ? obj < n_spheres : obj >= n_spheres);
+template <int KINDS> __device__ __forceinline__ bool exact_owns(int obj, int n_spheres, int csg_begin) {
+    if (KINDS == EXACT_ALL) return true;
+    if (KINDS == EXACT_SPHERES) return obj < n_spheres;
+    if (KINDS == EXACT_SIMPLE) return obj >= n_spheres && obj < csg_begin;
+    if (KINDS == EXACT_CSG) return obj >= csg_begin;
+    return obj >= n_spheres;
 }
 
 // closestHit (raytracer.go:469-483): strictly smaller T wins, equal T keeps the object that comes first in scan
@@ -1383,7 +1401,7 @@ __global__ void __launch_bounds__(EXACT_THREADS) k_exact_closest(const __grid_co
         if (KINDS == EXACT_REST && obj < 0) continue;          // a sphere candidate the SPHERES pass has already resolved to a miss
         bool deferred = false;
         if (ROBUST && KINDS == EXACT_REST) { deferred = (obj & CAND_DEFER) != 0; obj &= ~CAND_DEFER; }
-        if (KINDS != EXACT_ALL && obj < sc.n_leaves && !deferred && !exact_owns<KINDS>(obj, n_spheres)) continue;
+        if (KINDS != EXACT_ALL && obj < sc.n_leaves && !deferred && !exact_owns<KINDS>(obj, n_spheres, sc.kind_begin[K_CSG])) continue;
         const int ri = cq.ray[k];
         int code = -1; R t = R(0);
         if (obj < sc.n_leaves) {                               // a padding record can only be reached by a NaN ray
@@ -1490,7 +1508,7 @@ __global__ void __launch_bounds__(EXACT_THREADS) k_exact_shadow(const __grid_con
     unsigned long long n_exact = 0, n_flops = 0, n_occluded = 0;
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
         const int q = base + cq.ray[k], obj = cq.obj[k];
-        if (obj >= sc.n_leaves || !exact_owns<KINDS>(obj, sc.kind_begin[K_SPHERE + 1]) || obj == sq.skip[q]) continue;
+        if (obj >= sc.n_leaves || !exact_owns<KINDS>(obj, sc.kind_begin[K_SPHERE + 1], sc.kind_begin[K_CSG]) || obj == sq.skip[q]) continue;
         if (!COUNT && sq.first[q] != 0x7fffffff) continue;     // already occluded (a stale read only costs a test)
         if (COUNT) { n_exact++; n_flops += (unsigned)sc.obj_flops[obj]; }
         Ray<R> w;
@@ -2921,18 +2939,24 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
     }
     CamSrc cam{y0, map};                                    // rows of the current tile's camera rays (k_gen, double-precision re-tests)
     // exact kernels by kind (see ExactKinds): spheres inline at full occupancy, every other kind through exact_hit
-    const bool have_spheres = sc_.kind_begin[K_SPHERE + 1] > 0, have_rest = sc_.kind_begin[K_SPHERE + 1] < sc_.n_leaves || sc_.n_leaves == 0;
+    const bool have_spheres = sc_.kind_begin[K_SPHERE + 1] > 0;
+    const bool have_simple = sc_.kind_begin[K_CSG] > sc_.kind_begin[K_SPHERE + 1], have_csg = sc_.n_leaves > sc_.kind_begin[K_CSG] || sc_.n_leaves == 0;
+    const int n_exact_flavours = (have_spheres ? 1 : 0) + (have_simple ? 1 : 0) + (have_csg ? 1 : 0);
     auto exact_closest = [&](int l, bool count) -> int {
         const int grid = sms_ * 16;
         if (have_spheres) {
             if (count) k_exact_closest<R, false, true, EXACT_SPHERES><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
             else k_exact_closest<R, false, false, EXACT_SPHERES><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
         }
-        if (have_rest) {
-            if (count) k_exact_closest<R, false, true, EXACT_REST><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
-            else k_exact_closest<R, false, false, EXACT_REST><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
+        if (have_simple) {
+            if (count) k_exact_closest<R, false, true, EXACT_SIMPLE><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
+            else k_exact_closest<R, false, false, EXACT_SIMPLE><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
         }
-        totals_.launches += (have_spheres && have_rest) ? 1 : 0;
+        if (have_csg) {
+            if (count) k_exact_closest<R, false, true, EXACT_CSG><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
+            else k_exact_closest<R, false, false, EXACT_CSG><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
+        }
+        totals_.launches += n_exact_flavours - 1;
         return GMLRT_OK;
     };
     // profiling: one event before every launch; launches on one stream serialise, so consecutive events bracket a kernel
@@ -3038,14 +3062,16 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
                 const int sbase = li * sq_.per_light;
                 if (counting) {
                     if (have_spheres) k_exact_shadow<R, true, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_, sbase, cqs, ctr_, occl_[l]);
-                    if (have_rest) k_exact_shadow<R, true, EXACT_REST><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_, sbase, cqs, ctr_, occl_[l]);
+                    if (have_simple) k_exact_shadow<R, true, EXACT_SIMPLE><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_, sbase, cqs, ctr_, occl_[l]);
+                    if (have_csg) k_exact_shadow<R, true, EXACT_CSG><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_, sbase, cqs, ctr_, occl_[l]);
                     k_shadow_finish<R, true><<<wide, 256, 0, ss>>>(sc_, sq_, li, occl_[l], ctr_);
                 } else {                                   // the exact kernels set the occlusion flags themselves
                     if (have_spheres) k_exact_shadow<R, false, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_, sbase, cqs, ctr_, occl_[l]);
-                    if (have_rest) k_exact_shadow<R, false, EXACT_REST><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_, sbase, cqs, ctr_, occl_[l]);
+                    if (have_simple) k_exact_shadow<R, false, EXACT_SIMPLE><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_, sbase, cqs, ctr_, occl_[l]);
+                    if (have_csg) k_exact_shadow<R, false, EXACT_CSG><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_, sbase, cqs, ctr_, occl_[l]);
                     totals_.launches--;
                 }
-                totals_.launches += (have_spheres && have_rest) ? 1 : 0;
+                totals_.launches += n_exact_flavours - 1;
                 totals_.launches += 3;
                 CU_TRY(cudaMemsetAsync(&shadow_counts_[li], 0, sizeof(int), ss));
             }
