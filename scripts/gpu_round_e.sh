@@ -8,7 +8,7 @@ timeout 600 python bench.py --steps 10 --warmup 3 > gpurun_out/bench.json 2> gpu
 python - <<'PY'
 import json
 d = json.load(open("gpurun_out/bench.json"))
-print("value", d["value"], "ms", d["ms_per_step"], "serial", d["serialised_frame_ms"], "e2e", d["e2e"]["frame_ms"], d["e2e"]["phase_ms"], d["kernel_ms_per_frame"], d["cpu_baseline"], {k: d["roofline"][k] for k in ("kernel", "achieved", "peak", "frac", "traffic", "kernel_bytes_per_launch")})
+print("value", d["value"], "ms", d["ms_per_step"], "serial", d["serialised_frame_ms"], "e2e", d["e2e"]["frame_ms"], d["e2e"]["phase_ms"], d["kernel_ms_per_frame"], d["cpu_baseline"], {k: d["roofline"].get(k) for k in ("kernel", "achieved", "peak", "frac", "traffic")})
 PY
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"
 : > gpurun_out/configs.jsonl
