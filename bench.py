@@ -11,8 +11,11 @@ synthetic 1024-sphere reflective scene, 1 point + 1 directional light, depth 3, 
 A "step" = one full frame of the hot path.  `value` times gmlrt_trace (scene resident in HBM,
 raster left in HBM); `e2e` times gmlrt_render (host blob in, host raster out).  For N > 1 the
 driver launches one process per GPU with torchrun; each rank renders every N-th row band of the
-same frame (scene replicated, strong scaling) and the bands are summed onto rank 0 with one NCCL
-reduce over NVLink (frames are zero outside a rank's own bands).
+same frame (scene replicated, strong scaling) and stores its finished rows straight into rank 0's
+frame over NVLink (CUDA IPC peer mapping; `--gather nccl` keeps the reduce-of-disjoint-bands variant;
+`--verify` compares the gathered frame with a solo render).  The timed steps overlap the shadow
+queries with the closest-hit pipeline on separate streams; per-kernel times for the roofline come
+from a second, serialised pass of the same K steps (N = 1).
 """
 import argparse
 import json
