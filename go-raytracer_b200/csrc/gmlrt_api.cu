@@ -39,6 +39,7 @@ struct gmlrt_ctx {
     int part = 0, n_parts = 1;                               // multi-process sharding: this context renders bands part, part+n_parts, ...
     std::vector<char> peer_ok;                               // per device: it can store straight into devices[0]'s frame
     uint8_t* remote_frame = nullptr;                         // another process's frame opened over CUDA IPC (gmlrt_frame_ipc_attach)
+    bool frame_exported = false;                             // this context's frame is an IPC gather target (gmlrt_frame_ipc_export): uploads no longer clear it
 };
 
 static thread_local std::string g_last_error = "";
@@ -206,7 +207,10 @@ int gmlrt_upload(gmlrt_ctx* c, const void* blob, size_t blob_bytes) {
         else if (i > 0 && c->peer_ok[i]) target = r0->frame();         // NVLink stores from the level-0 k_resolve: the gather is fused
         c->r[i]->set_frame_target(target);
     }
-    if (c->n_parts > 1 && !c->remote_frame) {   // rows owned by other processes stay zero, so the rank frames can be summed
+    // Rows owned by other processes stay zero, so the rank frames can be summed (NCCL-reduce gather).  NOT when this
+    // frame has been exported as an IPC gather target: peer ranks store their rows into it from their own level-0
+    // resolve kernels, unordered with this process's uploads, and a clear enqueued here could land after their stores.
+    if (c->n_parts > 1 && !c->remote_frame && !c->frame_exported) {
         API_CU(cudaSetDevice(r0->device()));
         API_CU(cudaMemsetAsync(r0->frame(), 0, (size_t)c->scene.width * c->scene.height * 4, r0->stream()));
     }
@@ -232,6 +236,7 @@ int gmlrt_frame_ipc_export(gmlrt_ctx* c, void* handle, size_t handle_bytes) {
     cudaIpcMemHandle_t h;
     API_CU(cudaIpcGetMemHandle(&h, c->r[0]->frame()));
     std::memcpy(handle, &h, sizeof h);
+    c->frame_exported = true;
     return GMLRT_OK;
 }
 

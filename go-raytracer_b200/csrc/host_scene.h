@@ -159,6 +159,7 @@ inline int parse_blob(const void* blob, size_t nbytes, HostScene& S, std::string
     S.fpool.resize(h.n_fpool);     if (h.n_fpool) std::memcpy(S.fpool.data(), base + h.off_fpool, 8 * (size_t)h.n_fpool);
     S.itab.resize(h.n_itab);       if (h.n_itab) std::memcpy(S.itab.data(), base + h.off_itab, 4 * (size_t)h.n_itab);
     S.code.resize(h.n_code);       if (h.n_code) std::memcpy(S.code.data(), base + h.off_code, 4 * (size_t)h.n_code);
+    S.any_reflect = S.any_refract = S.may_branch = false;                 // a context parses many scenes: nothing carries over
     for (auto& l : S.lights) if (l.kind > GMLRT_LIGHT_SPOT) { err = "unknown light kind"; return GMLRT_E_UNSUPPORTED; }
     for (auto& sf : S.surfaces) {
         if (sf.kind > GMLRT_SURFACE_CODE) { err = "unknown surface kind"; return GMLRT_E_BAD_BLOB; }

@@ -1068,6 +1068,13 @@ struct CandQueue {
     int cap;
 };
 
+// entries of a finished cull launch.  After an overflow the queue has holes (a warp that did not fit reserved but never
+// wrote) whose stale (ray, object) words may belong to a larger level: the frame is discarded anyway, so skip them all.
+__device__ __forceinline__ int cand_count(const CandQueue& cq, const Counters* ctr) {
+    if (ctr->overflow) return 0;
+    return (int)min(*reinterpret_cast<const unsigned*>(cq.count), (unsigned)cq.cap);
+}
+
 template <typename R> struct ClosestSource {                 // rays of one recursion level
     Level<R> lv;                                              // (levels >= 1 are stored sorted by origin object and direction cell)
     __device__ __forceinline__ int id(int i) const { return i; }
@@ -1200,10 +1207,17 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
 #pragma unroll
                 for (int off = 1; off < 32; off <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, off); if (lane >= off) incl += v; }
                 const int total = __shfl_sync(0xffffffffu, incl, 31);
-                int at = 0;
-                if (lane == 31) at = atomicAdd(cq.count, total);
-                at = __shfl_sync(0xffffffffu, at, 31) + incl - mine;
-                if (at + mine > cq.cap) { if (mine) ctr->overflow = 1; return; }     // queue full: the host retries with smaller tiles
+                // The counter is unsigned and stops growing once the queue is full: a lattice seen along an axis can leave
+                // dozens of survivors per ray, and a signed counter that kept counting past 2^31 would turn `at` negative
+                // and the stores below into out-of-bounds writes instead of the overflow-and-retrace path.
+                unsigned at = 0;
+                if (lane == 31) {
+                    if (*reinterpret_cast<volatile unsigned*>(cq.count) >= (unsigned)cq.cap) at = 0xffffffffu;
+                    else at = atomicAdd(reinterpret_cast<unsigned*>(cq.count), (unsigned)total);
+                }
+                at = __shfl_sync(0xffffffffu, at, 31);
+                if (at == 0xffffffffu || at + (unsigned)total > (unsigned)cq.cap) { if (lane == 31) ctr->overflow = 1; return; }     // queue full: the host retries with smaller tiles
+                at += (unsigned)(incl - mine);
 #pragma unroll
                 for (int r = 0; r < RPT; r++) {
                     const int i = rid[r];
@@ -1381,7 +1395,7 @@ template <typename R, bool ROBUST, bool COUNT, int KINDS>
 __global__ void __launch_bounds__(EXACT_THREADS) k_exact_closest(const __grid_constant__ DevScene<R> sc, const __grid_constant__ Level<R> lv,
                                                                 const __grid_constant__ CandQueue cq, Counters* ctr, const __grid_constant__ CamSrc cam) {
     static_assert(!ROBUST || KINDS != EXACT_ALL, "the robust camera-ray test runs as SPHERES (float32, inline) then REST (double)");
-    const int count = min(*cq.count, cq.cap);
+    const int count = cand_count(cq, ctr);
     const int n_spheres = sc.kind_begin[K_SPHERE + 1];
     R* ct = reinterpret_cast<R*>(cq.t);
     unsigned long long n_exact = 0, n_flops = 0;
@@ -1464,9 +1478,9 @@ __global__ void __launch_bounds__(EXACT_THREADS) k_exact_closest(const __grid_co
 // float64 only: among the hits that have the ray's smallest T, the smallest scan index
 template <typename R>
 __global__ void __launch_bounds__(256) k_closest_order(const __grid_constant__ DevScene<R> sc, const __grid_constant__ Level<R> lv,
-                                                      const __grid_constant__ CandQueue cq) {
+                                                      const __grid_constant__ CandQueue cq, const Counters* ctr) {
     typedef typename BitsOf<R>::type UB;
-    const int count = min(*cq.count, cq.cap);
+    const int count = cand_count(cq, ctr);
     const UB* tbest = reinterpret_cast<const UB*>(lv.t);
     const R* ct = reinterpret_cast<const R*>(cq.t);
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
@@ -1480,9 +1494,9 @@ __global__ void __launch_bounds__(256) k_closest_order(const __grid_constant__ D
 // the winner writes its hit code (float32: and its T, which the key held until now)
 template <typename R>
 __global__ void __launch_bounds__(256) k_closest_pick(const __grid_constant__ DevScene<R> sc, const __grid_constant__ Level<R> lv,
-                                                     const __grid_constant__ CandQueue cq) {
+                                                     const __grid_constant__ CandQueue cq, const Counters* ctr) {
     typedef typename BitsOf<R>::type UB;
-    const int count = min(*cq.count, cq.cap);
+    const int count = cand_count(cq, ctr);
     const R* ct = reinterpret_cast<const R*>(cq.t);
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
         const int code = cq.obj[k];
@@ -1504,7 +1518,7 @@ __global__ void __launch_bounds__(256) k_closest_pick(const __grid_constant__ De
 template <typename R, bool COUNT, int KINDS>
 __global__ void __launch_bounds__(EXACT_THREADS) k_exact_shadow(const __grid_constant__ DevScene<R> sc, const __grid_constant__ ShadowQueue<R> sq,
                                                                int base, const __grid_constant__ CandQueue cq, Counters* ctr, unsigned char* occl) {
-    const int count = min(*cq.count, cq.cap);
+    const int count = cand_count(cq, ctr);
     unsigned long long n_exact = 0, n_flops = 0, n_occluded = 0;
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
         const int q = base + cq.ray[k], obj = cq.obj[k];
@@ -1699,7 +1713,7 @@ __global__ void __launch_bounds__(256) k_shadow_finish(const __grid_constant__ D
 // EvalSurfaceFn (internal/gml/evaluator.go:672-727) after host-side partial evaluation: typed
 // register code, see include/gmlrt.h.  Registers live in local memory (dynamic indexing).
 template <typename R> struct IntOf;
-template <> struct IntOf<float> { typedef int type; };
+template <> struct IntOf<float> { typedef long long type; };   // Go's VInt is int64 in both builds: integer-hash textures (muli by large primes) must not wrap at 32 bits
 template <> struct IntOf<double> { typedef long long type; };
 
 template <typename R> union Cell { R f; typename IntOf<R>::type i; };
@@ -2492,8 +2506,17 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     free_scene();
     const double t_b = now();
     {   // a scene of the same shape as the last one keeps the tile height that last fitted (a frame loop re-uploads every frame)
-        const unsigned long long sig = ((unsigned long long)S.leaves.size() << 40) ^ ((unsigned long long)S.width << 24) ^ ((unsigned long long)S.height << 8) ^
-                                       ((unsigned long long)S.depth << 4) ^ (unsigned long long)S.lights.size();
+        // everything plan_tiles sizes the pool from: a same-shape scene whose materials turn reflective / transparent, or
+        // that gains planes, must be planned afresh (its per-sample footprint grows)
+        int n_planes = 0;
+        for (const HostLeaf& L : S.leaves) n_planes += L.kind == K_PLANE ? 1 : 0;
+        unsigned long long sig = 1469598103934665603ull;
+        for (unsigned long long v : {(unsigned long long)S.leaves.size(), (unsigned long long)S.width, (unsigned long long)S.height, (unsigned long long)S.depth,
+                                     (unsigned long long)S.lights.size(), (unsigned long long)S.may_branch, (unsigned long long)S.any_reflect,
+                                     (unsigned long long)S.any_refract, (unsigned long long)n_planes, (unsigned long long)env_size("GMLRT_CAND_PER_RAY", 4),
+                                     (unsigned long long)(env_double("GMLRT_BRANCH_CAP", 2.0) * 1024.0),
+                                     (unsigned long long)env_size("GMLRT_TILE_SAMPLES", 64u << 20), (unsigned long long)env_size("GMLRT_POOL_MB", 96 * 1024)})
+            sig = (sig ^ v) * 1099511628211ull;
         if (sig != scene_sig_) { tile_shrink_ = 0; scene_sig_ = sig; }
     }
     // Device layout.  Objects (what closestHit / inShadow scan): the plain leaves, stably sorted by kind so that
@@ -3021,9 +3044,9 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
                 int erc = exact_closest(l, counting);
                 if (erc) return erc;
             }
-            if (sizeof(R) == 8) k_closest_order<R><<<exact_grid, 256, 0, stream_>>>(sc_, levels_[l], cq_);
+            if (sizeof(R) == 8) k_closest_order<R><<<exact_grid, 256, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
             else totals_.launches--;
-            if (!sc_.pickless) k_closest_pick<R><<<exact_grid, 256, 0, stream_>>>(sc_, levels_[l], cq_);
+            if (!sc_.pickless) k_closest_pick<R><<<exact_grid, 256, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
             else totals_.launches--;
             totals_.launches += 3;
             const bool spawn = l + 1 < depth_eff_;

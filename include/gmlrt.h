@@ -230,7 +230,9 @@ void* gmlrt_frame_device(gmlrt_ctx*);
 /* One process per GPU without a collective: the gathering process exports its frame (after gmlrt_upload; the frame
  * keeps its address while width x height is unchanged), the others attach it, and from then on their level-0 resolve kernel
  * stores finished rows straight into that frame over NVLink (CUDA IPC peer mapping).  The caller orders "all
- * producers finished" before it reads the frame (a barrier).  attach(NULL, 0) detaches.                           */
+ * producers finished" before it reads the frame (a barrier).  attach(NULL, 0) detaches.  Once exported, the frame is
+ * never cleared by gmlrt_upload again (the producers' stores are not ordered with the exporter's uploads): rows
+ * nobody renders keep whatever they held.                                                                        */
 #define GMLRT_IPC_HANDLE_BYTES 64
 int gmlrt_frame_ipc_export(gmlrt_ctx*, void* handle, size_t handle_bytes);
 int gmlrt_frame_ipc_attach(gmlrt_ctx*, const void* handle, size_t handle_bytes);

@@ -109,3 +109,28 @@ def ssim(a, b):
     if rc:
         raise ValueError("images are too small")
     return out.value
+
+
+def parity_window(blob, img, ids, crop, threads=8):
+    """The checker for throughput-mode frames at sizes the oracle cannot render whole: render the window
+    `crop` = (x0, y0, x1, y1) of the same blob with the oracle (all 4 samples per pixel, the reference's own PCG
+    streams) and compare it with the same window of a device frame `img` (uint8 [H,W,4]) and, when given, the device's
+    per-sample primary hit ids `ids` (int32 [H,W,4], scan order, -1 = miss).  The north_star's bar: <= 1/255 per
+    channel on >= 99.9% of pixels, zero hit/miss flips on primary rays (raytracer_test.go:37-52 is the reference's
+    own, looser, acceptance).  -> (dict of plain numbers, oracle Stats, bad-pixel mask of the window)."""
+    import time
+    x0, y0, x1, y1 = crop
+    t0 = time.perf_counter()
+    oimg, ost, oids = render(blob, threads=threads, crop=crop, want_ids=True)
+    dt = time.perf_counter() - t0
+    a = img[y0:y1, x0:x1, :3].astype(np.int32)
+    b = oimg[y0:y1, x0:x1, :3].astype(np.int32)
+    d = np.abs(a - b).max(axis=2)
+    out = {"crop": [int(x0), int(y0), int(x1), int(y1)], "pixels": int(d.size), "within_1_255": float((d <= 1).mean()),
+           "exact": float((d == 0).mean()), "max_abs_diff": int(d.max()), "oracle_seconds": round(dt, 2), "oracle_threads": int(threads)}
+    if ids is not None:
+        gi, oi = ids[y0:y1, x0:x1], oids[y0:y1, x0:x1]
+        out["primary_samples"] = int(gi.size)
+        out["primary_flips"] = int(((gi < 0) != (oi < 0)).sum())
+        out["id_mismatches"] = int((gi != oi).sum())
+    return out, ost, d > 1

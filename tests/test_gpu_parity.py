@@ -99,6 +99,30 @@ def test_synthetic_scenes_parity_and_tolerance(ctx64, ctx32, gen):
     assert st.flops_credited == ost.flops_credited and st.leaf_tests == ost.leaf_tests
 
 
+@pytest.mark.parametrize("name", ["spheres1024", "csg256", "proctex", "mixed4096"])
+def test_f32_tolerance_at_baseline_size(name):
+    """The frames bench.py times (BASELINE.json configs 2-5 at their stated 4K / 8K sizes), rendered whole on the
+    device in throughput mode, against the oracle on a window of the same frame (tests/baseline_windows.py): the
+    north_star's bar - within 1/255 per channel on >= 99.9% of the window's pixels and ZERO hit/miss flips among its
+    primary rays (per-sample ids, same PCG streams).  Reference: Render raytracer.go:589-682, acceptance
+    raytracer_test.go:37-52."""
+    from baseline_windows import WINDOWS, window_of
+    gen, (W, H), centre, size = WINDOWS[name]
+    blob = scenes.to_blob(gen(W, H))
+    c = cuda.Context((0,), cuda.PRECISION_F32)
+    try:
+        c.set_counting(True)
+        img, st = c.render(blob)
+        ids = c.primary_hits()
+    finally:
+        c.close()
+    assert st.rays_primary == 4 * W * H
+    res, ost, _ = oracle.parity_window(blob, img, ids, window_of(W, H, centre, size), threads=THREADS)
+    print(name, res)
+    assert res["within_1_255"] >= 0.999, res
+    assert res["primary_flips"] == 0, res
+
+
 def test_tiling_does_not_change_the_raster(ctx64):
     blob = scenes.to_blob(scenes.mixed(256, 150, grid=(4, 4, 4), depth=3))
     whole, _ = ctx64.render(blob)
