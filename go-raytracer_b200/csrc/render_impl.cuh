@@ -100,7 +100,7 @@ template <typename R> struct DevScene {
 // One recursion level of the wavefront (SoA, `cap` entries each).
 template <typename R> struct Level {
     R* ray;       // [cap][8] one record per ray: origin xyz, direction xyz, then (as raw bits of word 6) the parent: index in
-                  //          the previous level | (1<<31 for the refraction slot).  32 bytes in f32: one sector per random read
+                  //          the previous level | (1<<31 for the refraction slot), and (word 7) the class key.  32 bytes in f32: one sector per random read
     int* hit;     // [cap] device leaf index | face << 28, or -1
     R* t;         // [cap] T of the hit; during the scan: bit pattern of the smallest T so far (all ones = none)
     int* order;   // scan scratch.  f64: [cap] smallest scan index among the hits that have the smallest T; f32: [cap] 64-bit keys
@@ -149,15 +149,15 @@ __device__ __forceinline__ void load_ray(const double* rays, int i, Ray<double>&
     const double2 a = p[0], b = p[1], c = p[2];
     w.ox = a.x; w.oy = a.y; w.oz = b.x; w.dx = b.y; w.dy = c.x; w.dz = c.y;
 }
-__device__ __forceinline__ void store_ray(float* rays, int i, float ox, float oy, float oz, float dx, float dy, float dz, int parent) {
+__device__ __forceinline__ void store_ray(float* rays, int i, float ox, float oy, float oz, float dx, float dy, float dz, int parent, int key) {
     float4* p = reinterpret_cast<float4*>(rays + (size_t)i * RAY_WORDS);
     p[0] = make_float4(ox, oy, oz, dx);
-    p[1] = make_float4(dy, dz, __int_as_float(parent), 0.f);
+    p[1] = make_float4(dy, dz, __int_as_float(parent), __int_as_float(key));
 }
-__device__ __forceinline__ void store_ray(double* rays, int i, double ox, double oy, double oz, double dx, double dy, double dz, int parent) {
+__device__ __forceinline__ void store_ray(double* rays, int i, double ox, double oy, double oz, double dx, double dy, double dz, int parent, int key) {
     double2* p = reinterpret_cast<double2*>(rays + (size_t)i * RAY_WORDS);
     p[0] = make_double2(ox, oy); p[1] = make_double2(oz, dx); p[2] = make_double2(dy, dz);
-    p[3] = make_double2(__longlong_as_double((long long)(unsigned)parent), 0.0);
+    p[3] = make_double2(__longlong_as_double((long long)(unsigned)parent), __longlong_as_double((long long)(unsigned)key));
 }
 // one 8-word record (a shadow ray: origin, direction, distance, |incoming direction|) as 16-byte vector stores
 __device__ __forceinline__ void store_rec8(float* recs, size_t i, float a, float b, float c, float d, float e, float f, float g, float h) {
@@ -171,6 +171,11 @@ __device__ __forceinline__ void store_rec8(double* recs, size_t i, double a, dou
 }
 template <typename R> __device__ __forceinline__ int ray_parent(const R* rays, int i) {
     return reinterpret_cast<const int*>(rays + (size_t)i * RAY_WORDS + 6)[0];      // little-endian: the low word of word 6
+}
+// word 7: the class key of a spawned ray (its sort key: region of the origin x cube-map cell of the direction); it travels
+// with the record through the key sort, so the cull kernel finds the ray's candidate list without a side array
+template <typename R> __device__ __forceinline__ int ray_key(const R* rays, int i) {
+    return reinterpret_cast<const int*>(rays + (size_t)i * RAY_WORDS + 7)[0];
 }
 
 
@@ -532,34 +537,36 @@ __device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem
 }
 
 // ------------------------------------------------------------------ two-phase scan: cull, then exact test
-// closestHit / inShadow visit every object for every ray (raytracer.go:469-483, 411-429).  The scan
-// kernels keep that all-pairs structure (no hierarchy), but split each ray x object test in two:
+// closestHit / inShadow visit every object for every ray (raytracer.go:469-483, 411-429).  The device keeps that
+// all-pairs semantics - no object is ever dropped that a ray could hit - but splits the work in three, cheapest first:
 //
-//   cull   a few FFMA + 1 compare against the object's bounding sphere (centre C, radius R), from a
-//          16-byte (f32) record in shared memory; the radius carries a rounding margin so that a reject
-//          is always a true miss.  Three record/ray "families", by what the rays of a launch share:
+//   classes  (once per upload) rays are classified by where they start and where they point ("bins": a camera ray by
+//          its screen tile; a reflection / refraction ray by the sort region of its origin and the cube-map cell of its
+//          direction; a shadow ray by the sort region of the shaded point and its light).  Every class has a bound that
+//          holds ALL rays it can ever contain, so the objects that some ray of the class could hit are a property of the
+//          scene: one list per class, built by k_list_count / k_list_fill (every object is offered to every class, in
+//          double).  This replaces the per-warp / per-CTA packet bounds of round 1, which recomputed the same
+//          kind of bound from the rays of every warp in every launch (ballots, shared-memory lists, two CTA barriers).
+//   cull   (per ray x object of its class list) a few FFMA against the object's bounding sphere (centre C, radius R)
+//          from a 16-byte (f32) record in shared memory; the radius carries a rounding margin so that a reject is always
+//          a true miss.  Three record / ray "families", by what the rays of a launch share:
 //            GENERAL  any ray (o, d^):  reject iff |C-o|^2 - ((C-o).d^)^2 > R^2, expanded so that
 //                     everything per-ray is hoisted:  A = C.(-2o) + K,  K = |C|^2 - R^2 - margin,
-//                     B = C.d^ - o.d^,  reject <=> A - B^2 > -|o|^2 + margin          7 FFMA + compare
+//                     B = C.d^ - o.d^,  reject <=> A - B^2 > -|o|^2 + margin          7 FFMA + 1 FADD
 //            PIVOT    rays whose LINE passes through one point V (camera rays: the eye; shadow rays of a
 //                     point / spot light: the light):  record p = C - V, K = |p|^2 - R^2 - margin,
-//                     B = p.d^,  reject <=> K - B^2 > 0                                 4 FP + compare
+//                     B = p.d^,  reject <=> K - B^2 > 0                                 FMUL + 3 FFMA
 //            AXIS     rays with one common direction (shadow rays of a directional light): project on
 //                     the plane orthogonal to it,  du = Cu - ou, dv = Cv - ov,
-//                     reject <=> du^2 + dv^2 - R^2 > 0                                  4 FP + compare
-//          The survivors of a window of GROUP = 64 objects are collected as one 64-bit mask per ray.
-//   exact  after each window every ray walks the set bits of its mask and runs the reference's own test
-//          (<Type>.Intersect, or the CSG span lists) on those objects.  Deferring to the end of the window
-//          makes the lanes of a warp run their k-th exact tests side by side instead of one lane at a time.
-//
-// Each thread carries RPT rays so that the record load and the loop overhead are shared.
-#ifndef GMLRT_SCAN_THREADS
-#define GMLRT_SCAN_THREADS 256
-#endif
-constexpr int SCAN_THREADS = GMLRT_SCAN_THREADS, SCAN_WARPS = SCAN_THREADS / 32;
-constexpr int GROUP = 64;                   // objects per window: one 64-bit survivor mask per ray, kept in two registers
-constexpr int CULL_UNROLL = 8;              // objects per unrolled body of the cull loop
+//                     reject <=> du^2 + dv^2 - R^2 > 0                                  3 FADD + 2 FFMA
+//          One thread per ray; the survivors of a window of GROUP = 64 list entries are one 64-bit mask.
+//   exact  the survivors go to a candidate queue in HBM as (ray, object) pairs and a second kernel runs the
+//          reference's own test (<Type>.Intersect, or the CSG span lists) on them, one thread per candidate.
+constexpr int CULL_THREADS = 256;
+constexpr int GROUP = 64;                   // list entries per window: one 64-bit survivor mask per ray, kept in two registers
 enum CullFamily { CULL_GENERAL = 0, CULL_PIVOT = 1, CULL_AXIS = 2 };
+// class of a shadow ray: the sort region of the shaded point, merged by `shift`; the last bin collects invalid keys
+__device__ __forceinline__ int sort_bin(int key, int shift, int nb) { return key < 0 ? nb - 1 : min(key >> shift, nb - 2); }
 
 __device__ __forceinline__ float fma_(float a, float b, float c) { return __fmaf_rn(a, b, c); }
 __device__ __forceinline__ double fma_(double a, double b, double c) { return __fma_rn(a, b, c); }
@@ -629,34 +636,6 @@ template <typename R> struct CullRay<R, CULL_AXIS> {
 // shift the sign bit of `s` into the low end of a 32-bit mask: one funnel shift per test
 __device__ __forceinline__ uint32_t push_sign(uint32_t mask, float s) { return __funnelshift_l(__float_as_uint(s), mask, 1); }
 __device__ __forceinline__ uint32_t push_sign(uint32_t mask, double s) { return __funnelshift_l((uint32_t)__double2hiint(s), mask, 1); }
-
-// one window: objects first .. first + GROUP - 1 of the staged table `sm`; test j of each half lands in bit 31 - j
-// of lo / hi (the masks are shifted left once per test), set = object survives ray r
-template <typename R, int FAMILY, int RPT>
-__device__ __forceinline__ void cull_window(const R* sm, int first, const CullRay<R, FAMILY> (&cr)[RPT], uint32_t (&lo)[RPT], uint32_t (&hi)[RPT]) {
-#pragma unroll
-    for (int r = 0; r < RPT; r++) { lo[r] = 0; hi[r] = 0; }
-    // unrolled by CULL_UNROLL only: the fully unrolled window (1300+ instructions) missed the instruction cache
-    // ("no_instruction" was the top stall); the masks are built by shifting, so the body needs no immediates
-#pragma unroll 1
-    for (int j0 = 0; j0 < 32; j0 += CULL_UNROLL) {
-#pragma unroll
-        for (int j = 0; j < CULL_UNROLL; j++) {
-            const Cull4<R> L = load_cull(sm, first + j0 + j);
-#pragma unroll
-            for (int r = 0; r < RPT; r++) lo[r] = push_sign(lo[r], cr[r].slack(L));
-        }
-    }
-#pragma unroll 1
-    for (int j0 = 32; j0 < 64; j0 += CULL_UNROLL) {
-#pragma unroll
-        for (int j = 0; j < CULL_UNROLL; j++) {
-            const Cull4<R> L = load_cull(sm, first + j0 + j);
-#pragma unroll
-            for (int r = 0; r < RPT; r++) hi[r] = push_sign(hi[r], cr[r].slack(L));
-        }
-    }
-}
 
 template <typename R> __device__ __forceinline__ void load_w2o(const R* w2o, int i, Mat34<R>& M) { load_mat(w2o, i, M); }   // global, same layout
 
@@ -825,237 +804,224 @@ template <> struct BitsOf<double> {
     static __device__ __forceinline__ double back(unsigned long long b) { return __longlong_as_double((long long)b); }
 };
 
-// the same window over an index list: objects idx[k0 .. k0 + cnt - 1] (indices into `sm`; cnt a multiple of 8, at most
-// GROUP), 8 indices per 16-byte load.  A short list costs what it holds, not a whole window: the masks are shifted
-// up afterwards so that test j still sits in bit 31 - j.
-template <typename R, int FAMILY, int RPT>
-__device__ __forceinline__ void cull_window_indirect(const R* sm, const uint16_t* idx, int k0, int cnt, const CullRay<R, FAMILY> (&cr)[RPT],
-                                                     uint32_t (&lo)[RPT], uint32_t (&hi)[RPT]) {
-#pragma unroll
-    for (int r = 0; r < RPT; r++) { lo[r] = 0; hi[r] = 0; }
-    const int n_lo = min(cnt, 32);
-#pragma unroll 1
-    for (int j0 = 0; j0 < n_lo; j0 += 8) {
-        const uint4 pk = *reinterpret_cast<const uint4*>(idx + k0 + j0);
-        const uint32_t w[4] = {pk.x, pk.y, pk.z, pk.w};
-#pragma unroll
-        for (int j = 0; j < 8; j++) {
-            const Cull4<R> L = load_cull(sm, (int)((w[j >> 1] >> (16 * (j & 1))) & 0xffffu));
-#pragma unroll
-            for (int r = 0; r < RPT; r++) lo[r] = push_sign(lo[r], cr[r].slack(L));
+// ------------------------------------------------------------------ ray classes: one candidate list per bin
+// A bin's list holds, as byte offsets into the family's cull table, every object whose (margin-inflated) bounding
+// sphere some ray of the bin could touch, padded to whole groups of four with the table's padding record (always
+// rejected).  Built in double from the objects' bounds, whatever the arithmetic type of the renderer: the per-ray
+// test that follows is the conservative one, the list only has to be a superset of what it would keep.
+struct BinLists {
+    const int2* bin;            // [n_bins] (first entry, entries); both multiples of 4
+    const uint32_t* entry;      // byte offsets of cull records
+    int n_bins;
+};
+
+// what the rays of a bin have in common (all in double)
+struct BinBound {
+    double ax, ay, az;          // GENERAL / PIVOT: unit axis of the cone of directions; AXIS: (u, v) centre of the disc in ax, ay
+    double cos_t, sin_t;        // the cone's half angle
+    double ox, oy, oz, rho;     // GENERAL: sphere holding every origin.  PIVOT: rho = how far from the pivot an occluder can be.  AXIS: rho = disc radius
+    double rear;                // AXIS: rear-most origin along the rays' direction
+    bool usable;                // false: no bound (an unbounded region, the pivot inside it, ...) - every object is listed
+};
+
+enum BinKind { BIN_CAMERA = 0, BIN_SPAWN = 1, BIN_SHADOW_PIVOT = 2, BIN_SHADOW_AXIS = 3 };
+
+struct BinParams {
+    int kind, n_bins;
+    // the objects: [n][4] centre + radius (inf = unbounded), the family's margins (Renderer::build_cull_table)
+    const double* bound; int n_objects; double radius_rel, offset_abs, rel;
+    double pivot[3];                    // PIVOT families: the eye / the light
+    double e1[3], e2[3], axis[3];       // AXIS: the frame the device projects with
+    // BIN_SPAWN: bin = region * n_cells + cell;  BIN_SHADOW_*: bin = region (the last bin collects invalid keys: no bound)
+    const double* region;               // [n_regions][4] sphere holding every ray origin of the region (radius inf = unbounded)
+    const double* cell;                 // [n_cells][5] unit axis, cos, sin of the cone holding every direction of the cell
+    int n_regions, n_cells;
+    int limit_reach;                    // BIN_SHADOW_PIVOT: |incoming direction| is 1 for every ray, so occluders lie between the point and the light
+    // BIN_CAMERA: bin = tile; tiles of tile_w x tile_h pixels
+    int W, H, tile_w, tile_h, tiles_x;
+    double cam_su, cam_sv, vw, vh;
+};
+
+__device__ __forceinline__ BinBound bin_bound(const BinParams& p, int b) {
+    BinBound B = {};
+    B.usable = false;
+    B.rho = INFINITY; B.rear = -INFINITY;
+    if (p.kind == BIN_CAMERA) {
+        // Render (raytracer.go:639-649): sample (x + dx, y + dy), |dx|, |dy| <= 0.5, is the ray from the eye (0, 0, -1) through
+        // (u, -v, 0): direction ~ (u, -v, 1).  The directions of a tile are a rectangle on the plane z = 1; the farthest from
+        // the centre direction is a corner.
+        const int tx = b % p.tiles_x, ty = b / p.tiles_x;
+        const double x0 = tx * p.tile_w - 0.5 - 1e-6, x1 = fmin((double)(tx + 1) * p.tile_w, (double)p.W) - 0.5 + 1e-6;
+        const double y0 = ty * p.tile_h - 0.5 - 1e-6, y1 = fmin((double)(ty + 1) * p.tile_h, (double)p.H) - 0.5 + 1e-6;
+        const double u0 = x0 * p.cam_su - 0.5 * p.vw, u1 = x1 * p.cam_su - 0.5 * p.vw;
+        const double v0 = -(y0 * p.cam_sv - 0.5 * p.vh), v1 = -(y1 * p.cam_sv - 0.5 * p.vh);
+        const double cu = 0.5 * (u0 + u1), cv = 0.5 * (v0 + v1);
+        const double il = 1.0 / sqrt(cu * cu + cv * cv + 1.0);
+        B.ax = cu * il; B.ay = cv * il; B.az = il;
+        double c = 1.0;
+        const double us[2] = {u0, u1}, vs[2] = {v0, v1};
+        for (int k = 0; k < 4; k++) {
+            const double u = us[k & 1], v = vs[k >> 1];
+            const double d = (u * B.ax + v * B.ay + B.az) / sqrt(u * u + v * v + 1.0);
+            c = fmin(c, d);
         }
+        c -= 1e-9;                                       // (the float32 camera ray is the double one rounded: 1e-7 relative)
+        const double th = acos(fmin(c, 1.0)) + 4e-7;
+        B.cos_t = cos(th); B.sin_t = sin(th);
+        B.usable = true;
+        return B;
     }
-    if (n_lo < 32) {
-#pragma unroll
-        for (int r = 0; r < RPT; r++) lo[r] <<= 32 - n_lo;
-        return;
+    const int nreg = p.n_regions;
+    const int region = p.kind == BIN_SPAWN ? b / p.n_cells : b;
+    if (region >= nreg) return B;                        // shadow rays with an invalid key
+    const double* rg = p.region + (size_t)region * 4;
+    if (!(rg[3] < INFINITY)) return B;                    // unbounded region (or NaN)
+    // origins: P +- N * 1e-4 (raytracer.go:412, 525, 551) with P inside the region's sphere, as rounded by the device
+    const double rho = rg[3] * (1.0 + 1e-5) + 3e-4 + 1e-5 * (fabs(rg[0]) + fabs(rg[1]) + fabs(rg[2]));
+    if (p.kind == BIN_SPAWN) {
+        const double* cl = p.cell + (size_t)(b % p.n_cells) * 5;
+        B.ax = cl[0]; B.ay = cl[1]; B.az = cl[2]; B.cos_t = cl[3]; B.sin_t = cl[4];
+        B.ox = rg[0]; B.oy = rg[1]; B.oz = rg[2]; B.rho = rho;
+        B.usable = true;
+    } else if (p.kind == BIN_SHADOW_PIVOT) {
+        // the rays point from their origins at the light: their lines pass the light within 1e-4 (folded into the table),
+        // their directions lie in the cone from the light that holds the region
+        const double vx = rg[0] - p.pivot[0], vy = rg[1] - p.pivot[1], vz = rg[2] - p.pivot[2];
+        const double dist = sqrt(vx * vx + vy * vy + vz * vz);
+        if (!(dist > rho * 1.0001)) return B;            // the light is inside the region
+        B.ax = vx / dist; B.ay = vy / dist; B.az = vz / dist;
+        const double th = asin(fmin(rho / dist, 1.0)) + 4e-7;
+        B.cos_t = cos(th); B.sin_t = sin(th);
+        B.rho = p.limit_reach ? (dist + rho) * 1.001 + 1e-3 : INFINITY;
+        B.usable = true;
+    } else {                                             // BIN_SHADOW_AXIS
+        B.ax = rg[0] * p.e1[0] + rg[1] * p.e1[1] + rg[2] * p.e1[2];
+        B.ay = rg[0] * p.e2[0] + rg[1] * p.e2[1] + rg[2] * p.e2[2];
+        B.rho = rho * 1.0001 + 1e-6 * (fabs(B.ax) + fabs(B.ay) + 1.0);
+        const double q = rg[0] * p.axis[0] + rg[1] * p.axis[1] + rg[2] * p.axis[2] - rho;
+        B.rear = q - 1e-3 * (fabs(q) + 1.0);
+        B.usable = true;
     }
-#pragma unroll 1
-    for (int j0 = 32; j0 < cnt; j0 += 8) {
-        const uint4 pk = *reinterpret_cast<const uint4*>(idx + k0 + j0);
-        const uint32_t w[4] = {pk.x, pk.y, pk.z, pk.w};
-#pragma unroll
-        for (int j = 0; j < 8; j++) {
-            const Cull4<R> L = load_cull(sm, (int)((w[j >> 1] >> (16 * (j & 1))) & 0xffffu));
-#pragma unroll
-            for (int r = 0; r < RPT; r++) hi[r] = push_sign(hi[r], cr[r].slack(L));
+    return B;
+}
+
+// may object o be hit by ANY ray inside the bin's bound?  (conservative; mirrors the per-ray families)
+__device__ __forceinline__ bool bin_keeps(const BinParams& p, const BinBound& B, int o) {
+    const double* ob = p.bound + (size_t)o * 4;
+    const double Rw = ob[3];
+    if (!(Rw < INFINITY)) return true;                    // unbounded (plane) or NaN: never culled
+    if (!B.usable) return true;
+    const double Rm = Rw * (1.0 + p.radius_rel) + p.offset_abs;
+    if (p.kind == BIN_SHADOW_AXIS) {
+        const double cu = ob[0] * p.e1[0] + ob[1] * p.e1[1] + ob[2] * p.e1[2], cv = ob[0] * p.e2[0] + ob[1] * p.e2[1] + ob[2] * p.e2[2];
+        const double cc = ob[0] * ob[0] + ob[1] * ob[1] + ob[2] * ob[2];
+        const double r = sqrt(Rm * Rm + 2.0 * p.rel * (cc + 1.0)) * (1.0 + 1e-9) + B.rho;
+        const double front = ob[0] * p.axis[0] + ob[1] * p.axis[1] + ob[2] * p.axis[2] + Rm + 1e-3 * (sqrt(cc) + 1.0);
+        if (front < B.rear) return false;                // wholly behind every origin along the rays' direction
+        const double du = cu - B.ax, dv = cv - B.ay;
+        return !(du * du + dv * dv > r * r);
+    }
+    const bool general = p.kind == BIN_SPAWN;
+    const double px = ob[0] - (general ? B.ox : p.pivot[0]), py = ob[1] - (general ? B.oy : p.pivot[1]), pz = ob[2] - (general ? B.oz : p.pivot[2]);
+    const double pp = px * px + py * py + pz * pz;
+    const double cc = general ? ob[0] * ob[0] + ob[1] * ob[1] + ob[2] * ob[2] : pp;
+    // the radius the per-ray test works with (K = |C|^2 - Rm^2 - rel (|C|^2 + 1), rounded down to R, and its own
+    // rounding allowance on the ray side), plus - GENERAL - the radius of the sphere of origins
+    double r = sqrt(Rm * Rm + 4.0 * p.rel * (cc + 1.0)) * (1.0 + 1e-9);
+    if (general) r += B.rho;
+    if (!(r * r < pp)) return true;                      // an origin (the pivot) may be inside the sphere
+    const double dist = sqrt(pp);
+    const double sa = r / dist, ca = sqrt(1.0 - sa * sa);
+    double c = (px * B.ax + py * B.ay + pz * B.az) / dist;
+    if (!general) {
+        if (dist - r > B.rho) return false;              // nearer to the pivot than this an occluder must be (shadow rays stop at the light)
+        c = fabs(c);                                     // the LINE passes through the pivot: a double cone
+    }
+    return !(c < B.cos_t * ca - B.sin_t * sa - 1e-9);      // angle(C - origin, axis) <= theta + alpha; GENERAL is forward only (T > 0, raytracer.go:98)
+}
+
+// one warp per bin: count (FILL = false) or write (FILL = true) the bin's list
+template <bool FILL>
+__global__ void __launch_bounds__(256) k_list_build(const __grid_constant__ BinParams p, int* count, const int* first, int2* bins, uint32_t* entry,
+                                                    uint32_t rec_bytes, unsigned long long* tests) {
+    const int lane = threadIdx.x & 31;
+    const int warps = (gridDim.x * blockDim.x) >> 5;
+    const unsigned lt = (1u << lane) - 1u;
+    unsigned long long mine = 0;
+    for (int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < p.n_bins; b += warps) {
+        const BinBound B = bin_bound(p, b);
+        int n = 0;
+        const int base = FILL ? first[b] : 0;
+        for (int o0 = 0; o0 < p.n_objects; o0 += 32) {
+            const int o = o0 + lane;
+            const bool keep = o < p.n_objects && bin_keeps(p, B, o);
+            const unsigned bal = __ballot_sync(0xffffffffu, keep);
+            if (FILL && keep) entry[base + n + __popc(bal & lt)] = (uint32_t)o * rec_bytes;
+            n += __popc(bal);
         }
+        mine += (unsigned long long)((p.n_objects + 31) / 32);
+        const int padded = (n + 3) & ~3;
+        if (FILL) {
+            if (lane < padded - n) entry[base + n + lane] = (uint32_t)p.n_objects * rec_bytes;     // the table's first padding record: always rejected
+            if (lane == 0) bins[b] = make_int2(base, padded);
+        } else if (lane == 0) count[b] = padded;
     }
-    if (cnt > 32 && cnt < 64) {
-#pragma unroll
-        for (int r = 0; r < RPT; r++) hi[r] <<= 64 - cnt;
-    }
+    if (!FILL && tests && mine) atomicAdd(tests, mine);
 }
 
-// What the rays of one warp (RPT per lane) have in common, for the packet stage of the PIVOT / AXIS families:
-//   PIVOT  a double cone around `axis` (unit) with half-angle theta that contains every ray's line through the pivot
-//   AXIS   a disc (centre mu, mv; radius rho) in the plane orthogonal to the common direction that contains every ray
-//   GENERAL (rays sorted by origin object and direction cell) a sphere (centre o, radius rho) that holds every origin
-//          and a cone around `axis` with half-angle theta that holds every direction
-template <typename R> struct WarpBound { R ax, ay, az, cos_t, sin_t; bool usable; R ox, oy, oz, rho; };
-
-template <typename R>
-__device__ __forceinline__ R warp_sum(R v) { for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o); return v; }
-template <typename R>
-__device__ __forceinline__ R warp_min(R v) { for (int o = 16; o > 0; o >>= 1) { const R u = __shfl_xor_sync(0xffffffffu, v, o); v = u < v ? u : v; } return v; }
-template <typename R>
-__device__ __forceinline__ R warp_max(R v) { for (int o = 16; o > 0; o >>= 1) { const R u = __shfl_xor_sync(0xffffffffu, v, o); v = u > v ? u : v; } return v; }
-
-__device__ __forceinline__ unsigned long long warp_sum_u64(unsigned long long v) { for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o); return v; }
-
-template <typename R, int RPT>
-__device__ __forceinline__ WarpBound<R> warp_bound(const CullRay<R, CULL_PIVOT> (&cr)[RPT], const bool (&active)[RPT]) {
-    R sx = R(0), sy = R(0), sz = R(0);
-#pragma unroll
-    for (int r = 0; r < RPT; r++) if (active[r]) { sx += cr[r].dx; sy += cr[r].dy; sz += cr[r].dz; }
-    sx = warp_sum(sx); sy = warp_sum(sy); sz = warp_sum(sz);
-    const R len = gm<R>::sqrt(fma_(sx, sx, fma_(sy, sy, sz * sz)));
-    WarpBound<R> b = {};
-    b.usable = len > R(0);
-    const R inv = b.usable ? R(1) / len : R(0);
-    b.ax = sx * inv; b.ay = sy * inv; b.az = sz * inv;
-    R c = R(1);
-#pragma unroll
-    for (int r = 0; r < RPT; r++) if (active[r]) { const R d = fma_(cr[r].dx, b.ax, fma_(cr[r].dy, b.ay, cr[r].dz * b.az)); c = d < c ? d : c; }
-    c = warp_min(c) - R(1e-5);                          // a slightly wider cone absorbs the rounding of axis and dot products
-    b.cos_t = c;
-    b.sin_t = gm<R>::sqrt(R(1) - (c < R(1) ? c * c : R(1))) + R(1e-5);
-    b.usable = b.usable && c > R(0.5);                   // a wide cone culls little: use the plain scan
-    return b;
-}
-template <typename R, int RPT>
-__device__ __forceinline__ WarpBound<R> warp_bound(const CullRay<R, CULL_AXIS> (&cr)[RPT], const bool (&active)[RPT]) {
-    R su = R(0), sv = R(0), cnt = R(0);
-#pragma unroll
-    for (int r = 0; r < RPT; r++) if (active[r]) { su += cr[r].ou; sv += cr[r].ov; cnt += R(1); }
-    su = warp_sum(su); sv = warp_sum(sv); cnt = warp_sum(cnt);
-    WarpBound<R> b = {};
-    b.usable = cnt > R(0);
-    b.ax = b.usable ? su / cnt : R(0); b.ay = b.usable ? sv / cnt : R(0); b.az = R(0);
-    R d2 = R(0);
-#pragma unroll
-    for (int r = 0; r < RPT; r++) if (active[r]) { const R du = cr[r].ou - b.ax, dv = cr[r].ov - b.ay; const R d = fma_(du, du, dv * dv); d2 = d > d2 ? d : d2; }
-    d2 = warp_max(d2);
-    b.cos_t = gm<R>::sqrt(d2) * R(1.0001) + R(1e-6) * (gm<R>::abs(b.ax) + gm<R>::abs(b.ay) + R(1));      // rho, widened for rounding
-    b.sin_t = R(0);
-    return b;
-}
-template <typename R, int RPT>
-__device__ __forceinline__ WarpBound<R> warp_bound(const CullRay<R, CULL_GENERAL> (&cr)[RPT], const bool (&active)[RPT]) {
-    R sx = R(0), sy = R(0), sz = R(0), qx = R(0), qy = R(0), qz = R(0), cnt = R(0);
-#pragma unroll
-    for (int r = 0; r < RPT; r++) if (active[r]) {
-        sx += cr[r].dx; sy += cr[r].dy; sz += cr[r].dz;
-        qx += cr[r].o2x; qy += cr[r].o2y; qz += cr[r].o2z; cnt += R(1);          // o2 = -2 o
-    }
-    sx = warp_sum(sx); sy = warp_sum(sy); sz = warp_sum(sz);
-    qx = warp_sum(qx); qy = warp_sum(qy); qz = warp_sum(qz); cnt = warp_sum(cnt);
-    const R len = gm<R>::sqrt(fma_(sx, sx, fma_(sy, sy, sz * sz)));
-    WarpBound<R> b;
-    b.usable = len > R(0) && cnt > R(0);
-    const R inv = b.usable ? R(1) / len : R(0), icnt = b.usable ? R(-0.5) / cnt : R(0);
-    b.ax = sx * inv; b.ay = sy * inv; b.az = sz * inv;
-    b.ox = qx * icnt; b.oy = qy * icnt; b.oz = qz * icnt;
-    R c = R(1), d2 = R(0);
-#pragma unroll
-    for (int r = 0; r < RPT; r++) if (active[r]) {
-        const R d = fma_(cr[r].dx, b.ax, fma_(cr[r].dy, b.ay, cr[r].dz * b.az));
-        c = d < c ? d : c;
-        const R ex = fma_(R(-0.5), cr[r].o2x, -b.ox), ey = fma_(R(-0.5), cr[r].o2y, -b.oy), ez = fma_(R(-0.5), cr[r].o2z, -b.oz);
-        const R e = fma_(ex, ex, fma_(ey, ey, ez * ez));
-        d2 = e > d2 ? e : d2;
-    }
-    c = warp_min(c) - R(1e-5);
-    d2 = warp_max(d2);
-    b.cos_t = c;
-    b.sin_t = gm<R>::sqrt(R(1) - (c < R(1) ? c * c : R(1))) + R(1e-5);
-    b.rho = gm<R>::sqrt(d2) * R(1.0001) + R(1e-6) * (gm<R>::abs(b.ox) + gm<R>::abs(b.oy) + gm<R>::abs(b.oz) + R(1));
-    b.usable = b.usable && c > R(0.2);                   // NaN rays make c NaN: not usable, the plain scan handles them
-    return b;
-}
-
-// may object record L be hit by ANY ray inside the warp's bound?  (conservative)
-template <typename R> __device__ __forceinline__ bool packet_survives(const Cull4<R>& L, const WarpBound<R>& b, CullRay<R, CULL_PIVOT>*) {
-    const R pp = fma_(L.x, L.x, fma_(L.y, L.y, L.z * L.z));
-    const R r2 = pp - L.k;                               // >= R^2 (the record's K carries the margins)
-    if (!(r2 < pp)) return true;                         // pivot inside the sphere, unbounded object (K = -inf), NaN
-    const R inv = R(1) / pp;
-    const R s2 = r2 * inv;                               // sin^2 of the sphere's angular radius alpha seen from the pivot
-    const R sa = gm<R>::sqrt(s2) * R(1.0001), ca = gm<R>::sqrt(R(1) - s2);
-    const R rs = gm<R>::sqrt(inv);
-    if (pp * rs * (R(1) - sa) > b.rho) return false;     // nearest point of the sphere is beyond the packet's reach from the pivot (shadow rays; rho = inf otherwise)
-    const R c = gm<R>::abs(fma_(L.x, b.ax, fma_(L.y, b.ay, L.z * b.az))) * rs;     // |cos| of the angle to the axis
-    return !(c < b.cos_t * ca - b.sin_t * sa - R(1e-5));      // angle <= theta + alpha
-}
-template <typename R> __device__ __forceinline__ bool packet_survives(const Cull4<R>& L, const WarpBound<R>& b, CullRay<R, CULL_AXIS>*) {
-    const R du = L.x - b.ax, dv = L.y - b.ay;
-    const R rr = gm<R>::sqrt(-L.z) * R(1.0001) + b.cos_t;      // sqrt(R^2 + margin) + rho; -L.z = +inf for unbounded objects
-    if (L.k < b.sin_t) return false;                     // the object's front end (C.axis + R, record word 3) is behind every origin of the packet
-    return !(fma_(du, du, dv * dv) > rr * rr);
-}
-// GENERAL record (C, K = |C|^2 - R^2 - margin).  A ray from o (|o - oc| <= rho) that hits the sphere (C, R) at T > 0 is,
-// moved to oc, a ray that hits a sphere of the same radius whose centre is within rho of C: so test the sphere
-// (C, R + rho) against the cone of directions from oc - forward only, the reference accepts T > 0 alone.
-template <typename R> __device__ __forceinline__ bool packet_survives(const Cull4<R>& L, const WarpBound<R>& b, CullRay<R, CULL_GENERAL>*) {
-    const R cc = fma_(L.x, L.x, fma_(L.y, L.y, L.z * L.z));
-    const R r2 = fma_(cc, R(9.5367431640625e-7), cc - L.k);       // R^2 + margins + 2^-20 |C|^2 for the cancellation in |C|^2 - K
-    const R rr = gm<R>::sqrt(r2) * R(1.0001) + b.rho;
-    const R rr2 = rr * rr;
-    const R px = L.x - b.ox, py = L.y - b.oy, pz = L.z - b.oz;
-    const R pp = fma_(px, px, fma_(py, py, pz * pz));
-    if (!(rr2 < pp)) return true;                        // an origin may be inside the sphere; unbounded object; NaN / padding
-    const R inv = R(1) / pp;
-    const R s2 = rr2 * inv;
-    const R sa = gm<R>::sqrt(s2) * R(1.0001), ca = gm<R>::sqrt(R(1) - s2);
-    const R c = fma_(px, b.ax, fma_(py, b.ay, pz * b.az)) * gm<R>::sqrt(inv);      // signed: behind the packet = miss
-    return !(c < b.cos_t * ca - b.sin_t * sa - R(1e-5));      // angle(C - oc, axis) <= theta + alpha
-}
-
-constexpr int PCHUNK = 1024;                // objects per packet pass = survivor list capacity per warp (uint16 indices)
-constexpr size_t SURV_BYTES = (size_t)(SCAN_THREADS / 32 + 1) * PCHUNK * sizeof(uint16_t);    // one list per warp + the CTA's
-
-// The bound of a whole CTA's rays = the union of its warps' bounds (published in shared memory by lane 0 of each warp;
-// every thread evaluates the same union).  Used for a first packet pass shared by the CTA: 256 threads x 4 objects
-// instead of 32 lanes x 32, after which a warp only looks at what the CTA kept.
-constexpr int WB_WORDS = 12;      // ax ay az cos sin ox oy oz rho usable active
-template <typename R> __device__ __forceinline__ void publish_bound(R* slot, const WarpBound<R>& b, bool any_active) {
-    slot[0] = b.ax; slot[1] = b.ay; slot[2] = b.az; slot[3] = b.cos_t; slot[4] = b.sin_t;
-    slot[5] = b.ox; slot[6] = b.oy; slot[7] = b.oz; slot[8] = b.rho;
-    slot[9] = b.usable ? R(1) : R(0); slot[10] = any_active ? R(1) : R(0);
-}
-// Evaluated by every warp on its own: lane w (mod 8) holds warp w's published bound, sums / minima / maxima go over
-// groups of 8 lanes with xor-shuffles, so the union costs a few dozen instructions per warp instead of 8x that per thread.
-template <typename R> __device__ __forceinline__ R oct_sum(R v) { for (int o = SCAN_WARPS / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o); return v; }
-template <typename R> __device__ __forceinline__ R oct_min(R v) { for (int o = SCAN_WARPS / 2; o > 0; o >>= 1) { const R u = __shfl_xor_sync(0xffffffffu, v, o); v = u < v ? u : v; } return v; }
-template <typename R> __device__ __forceinline__ R oct_max(R v) { for (int o = SCAN_WARPS / 2; o > 0; o >>= 1) { const R u = __shfl_xor_sync(0xffffffffu, v, o); v = u > v ? u : v; } return v; }
-
-template <typename R, int FAMILY>
-__device__ __forceinline__ WarpBound<R> cta_bound(const R (*wbs)[WB_WORDS]) {
-    static_assert((SCAN_WARPS & (SCAN_WARPS - 1)) == 0 && SCAN_WARPS <= 32, "one lane of each group of SCAN_WARPS lanes per warp of the CTA");
-    const R* b = wbs[threadIdx.x & (SCAN_WARPS - 1)];
-    const bool act = b[10] != R(0);                         // false: a warp past the end of the queue
-    WarpBound<R> c = {};
-    const R bad = oct_sum<R>(act && b[9] == R(0) ? R(1) : R(0));
-    const R cnt = oct_sum<R>(act ? R(1) : R(0));
-    c.usable = bad == R(0) && cnt > R(0);
-    if (!c.usable) return c;                                // uniform across the warp (and the CTA: every warp sees the same slots)
-    const R sx = oct_sum<R>(act ? b[0] : R(0)), sy = oct_sum<R>(act ? b[1] : R(0)), sz = oct_sum<R>(act ? b[2] : R(0));
-    if (FAMILY == CULL_AXIS) {                               // discs in the plane orthogonal to the common direction
-        c.ax = sx / cnt; c.ay = sy / cnt;
-        const R du = b[0] - c.ax, dv = b[1] - c.ay;
-        const R rho = oct_max<R>(act ? gm<R>::sqrt(fma_(du, du, dv * dv)) * R(1.0001) + b[3] : R(0));
-        c.cos_t = rho * R(1.0001) + R(1e-6) * (gm<R>::abs(c.ax) + gm<R>::abs(c.ay) + R(1));
-        c.sin_t = oct_min<R>(act ? b[4] : gm<R>::inf());      // rear-most origin along the axis over the CTA
-        return c;
-    }
-    const R qx = oct_sum<R>(act ? b[5] : R(0)), qy = oct_sum<R>(act ? b[6] : R(0)), qz = oct_sum<R>(act ? b[7] : R(0));
-    const R len = gm<R>::sqrt(fma_(sx, sx, fma_(sy, sy, sz * sz)));
-    if (!(len > R(0))) { c.usable = false; return c; }
-    const R inv = R(1) / len;
-    c.ax = sx * inv; c.ay = sy * inv; c.az = sz * inv;
-    c.ox = qx / cnt; c.oy = qy / cnt; c.oz = qz / cnt;
-    R cw = fma_(b[0], c.ax, fma_(b[1], c.ay, b[2] * c.az));           // cos of the angle phi between the warp's axis and the CTA's
-    const R neg = oct_sum<R>(act && !(cw > R(0)) ? R(1) : R(0));         // phi + theta must stay below pi for the sum formula
-    cw = cw < R(1) ? cw : R(1);
-    const R sw = gm<R>::sqrt(R(1) - cw * cw) + R(1e-5);
-    R cmin = oct_min<R>(act ? cw * b[3] - sw * b[4] : R(1));             // cos(phi + theta_w)
-    const R ex = b[5] - c.ox, ey = b[6] - c.oy, ez = b[7] - c.oz;
-    const R rho = oct_max<R>(act ? gm<R>::sqrt(fma_(ex, ex, fma_(ey, ey, ez * ez))) * R(1.0001) + b[8] : R(0));
-    cmin -= R(1e-5);
-    c.cos_t = cmin;
-    c.sin_t = gm<R>::sqrt(R(1) - (cmin < R(1) ? cmin * cmin : R(1))) + R(1e-5);
-    c.rho = rho * R(1.0001) + R(1e-6) * (gm<R>::abs(c.ox) + gm<R>::abs(c.oy) + gm<R>::abs(c.oz) + R(1));
-    c.usable = neg == R(0) && cmin > R(0.2);
+// one window of a ray's list: entries ent[0 .. cnt) (cnt a multiple of 4, at most GROUP), 4 entries per 16-byte load;
+// test j lands in bit 31 - j of lo (j < 32) / hi (set = object survives)
+template <typename R> __device__ __forceinline__ Cull4<R> load_cull_at(const unsigned char* tab, uint32_t off);
+template <> __device__ __forceinline__ Cull4<float> load_cull_at<float>(const unsigned char* tab, uint32_t off) {
+    const float4 v = *reinterpret_cast<const float4*>(tab + off);
+    Cull4<float> c = {v.x, v.y, v.z, v.w};
     return c;
 }
+template <> __device__ __forceinline__ Cull4<double> load_cull_at<double>(const unsigned char* tab, uint32_t off) {
+    const double2 a = *reinterpret_cast<const double2*>(tab + off), b = *reinterpret_cast<const double2*>(tab + off + 16);
+    Cull4<double> c = {a.x, a.y, b.x, b.y};
+    return c;
+}
+template <typename R, int FAMILY>
+__device__ __forceinline__ void cull_list_window(const unsigned char* tab, const uint32_t* ent, int cnt, const CullRay<R, FAMILY>& cr, uint32_t& lo, uint32_t& hi) {
+    lo = 0; hi = 0;
+    if (cnt <= 0) return;
+    const int n_lo = min(cnt, 32);
+    uint4 e = __ldg(reinterpret_cast<const uint4*>(ent));
+#pragma unroll 1
+    for (int j = 0; j < n_lo; j += 4) {
+        const uint4 c = e;
+        if (j + 4 < cnt) e = __ldg(reinterpret_cast<const uint4*>(ent + j + 4));       // the next four offsets are in flight while these are tested
+        lo = push_sign(lo, cr.slack(load_cull_at<R>(tab, c.x)));
+        lo = push_sign(lo, cr.slack(load_cull_at<R>(tab, c.y)));
+        lo = push_sign(lo, cr.slack(load_cull_at<R>(tab, c.z)));
+        lo = push_sign(lo, cr.slack(load_cull_at<R>(tab, c.w)));
+    }
+    if (n_lo < 32) { lo <<= 32 - n_lo; return; }
+#pragma unroll 1
+    for (int j = 32; j < cnt; j += 4) {
+        const uint4 c = e;
+        if (j + 4 < cnt) e = __ldg(reinterpret_cast<const uint4*>(ent + j + 4));
+        hi = push_sign(hi, cr.slack(load_cull_at<R>(tab, c.x)));
+        hi = push_sign(hi, cr.slack(load_cull_at<R>(tab, c.y)));
+        hi = push_sign(hi, cr.slack(load_cull_at<R>(tab, c.z)));
+        hi = push_sign(hi, cr.slack(load_cull_at<R>(tab, c.w)));
+    }
+    if (cnt > 32 && cnt < 64) hi <<= 64 - cnt;
+}
+
+template <typename R>
+__device__ __forceinline__ R warp_max(R v) { for (int o = 16; o > 0; o >>= 1) { const R u = __shfl_xor_sync(0xffffffffu, v, o); v = u > v ? u : v; } return v; }
+__device__ __forceinline__ unsigned long long warp_sum_u64(unsigned long long v) { for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o); return v; }
 
 // ------------------------------------------------------------------ scan = cull kernel + exact kernels
-// Phase 1, k_cull: persistent CTAs over blocks of SCAN_THREADS * RPT rays; the cull table is staged once per
-// CTA when it fits ("resident"), else streamed through two buffers per block of rays.  Each thread carries RPT
-// rays in registers, culls a window of GROUP objects into survivor masks, and the warp appends every set bit to
-// the launch's candidate queue in HBM as a (ray, object) pair - one atomic per warp and window.
-// Phase 2, k_exact_*: one thread per candidate runs the reference's own test - every lane busy, instead of the
-// few lanes of a warp that happen to have a survivor in the same window - and folds the result into the ray's
+// Phase 1, k_cull: one thread per ray.  The thread looks up the list of its ray's class and tests the ray against the
+// listed bounding spheres, GROUP entries per window; the warp appends every survivor to the launch's candidate queue
+// in HBM as a (ray, object) pair - one atomic per warp and window.  The lanes of a warp usually share a class (camera
+// rays: a tile; sorted spawned rays: a bin; shadow rays of neighbouring pixels: one region), so their list and record
+// loads are broadcasts; where they differ the hardware serialises only the distinct addresses.  The family's cull
+// table is staged once per CTA into shared memory by one TMA bulk copy when it fits (TABLE_SMEM), else read through L1.
+// Phase 2, k_exact_*: one thread per candidate runs the reference's own test and folds the result into the ray's
 // record with atomics.
 //
 // The queue is sized from the scene (Renderer::plan_tiles); if a launch overflows it, `Counters::overflow`
@@ -1064,7 +1030,7 @@ struct CandQueue {
     int* ray;        // [cap] ray index within the launch's ray source
     int* obj;        // [cap] object index; k_exact_closest overwrites it with the hit code (or -1)
     void* t;         // [cap] R: T of the hit (closest only)
-    int* count;      // [0] entries appended by the current launch, [1] blocks of rays handed out beyond the first wave
+    int* count;      // [0] entries appended by the current launch
     int cap;
 };
 
@@ -1075,249 +1041,123 @@ __device__ __forceinline__ int cand_count(const CandQueue& cq, const Counters* c
     return (int)min(*reinterpret_cast<const unsigned*>(cq.count), (unsigned)cq.cap);
 }
 
-template <typename R> struct ClosestSource {                 // rays of one recursion level
-    Level<R> lv;                                              // (levels >= 1 are stored sorted by origin object and direction cell)
+template <typename R> __device__ __forceinline__ void level_init_ray(const Level<R>& lv, int i) {       // no hit yet (see fold_hit)
+    lv.hit[i] = -1;
+    if constexpr (sizeof(R) == 4) reinterpret_cast<unsigned long long*>(lv.order)[i] = ~0ull;
+    else {
+        reinterpret_cast<unsigned long long*>(lv.t)[i] = ~0ull;
+        lv.order[i] = 0x7fffffff;
+    }
+}
+
+template <typename R> struct CameraSource {                  // level 0: camera rays in (pixel, sample) order over the virtual rows of a tile
+    Level<R> lv; int W, y0; RowMap map; int tile_w, tile_h, tiles_x;
     __device__ __forceinline__ int id(int i) const { return i; }
     __device__ __forceinline__ void load(int i, Ray<R>& out) const { load_ray(lv.ray, i, out); }
-    static constexpr bool is_shadow = false;
-    __device__ __forceinline__ void init(int i) const {       // no hit yet (see fold_hit)
-        lv.hit[i] = -1;
-        if constexpr (sizeof(R) == 4) reinterpret_cast<unsigned long long*>(lv.order)[i] = ~0ull;
-        else {
-            reinterpret_cast<unsigned long long*>(lv.t)[i] = ~0ull;
-            lv.order[i] = 0x7fffffff;
-        }
+    __device__ __forceinline__ void init(int i) const { level_init_ray(lv, i); }
+    __device__ __forceinline__ int bin(int i) const {
+        const int pix = i >> 2;
+        return (map.actual(y0 + pix / W) / tile_h) * tiles_x + (pix % W) / tile_w;
     }
+    static constexpr bool is_shadow = false;
+};
+
+template <typename R> struct SpawnSource {                   // levels >= 1: reflection / refraction rays; the class key travels in the record
+    Level<R> lv;
+    __device__ __forceinline__ int id(int i) const { return i; }
+    __device__ __forceinline__ void load(int i, Ray<R>& out) const { load_ray(lv.ray, i, out); }
+    __device__ __forceinline__ void init(int i) const { level_init_ray(lv, i); }
+    __device__ __forceinline__ int bin(int i) const { return ray_key(lv.ray, i); }
+    static constexpr bool is_shadow = false;
 };
 
 template <typename R> struct ShadowSource {                  // shadow rays of one light: slots [base, base + n)
-    ShadowQueue<R> sq; int base;
-    __device__ __forceinline__ int id(int i) const { return sq.perm[base + i]; }          // i-th ray in by-object order -> slot in the segment
+    ShadowQueue<R> sq; int base; const int* perm;            // perm: by-region order of the slots (null: queue order)
+    int shift, nb;                                           // class = sort_bin(region of the shaded point)
+    __device__ __forceinline__ int id(int i) const { return perm ? perm[base + i] : i; }
     __device__ __forceinline__ void load(int i, Ray<R>& out) const {
         const R* rec = sq.q + (size_t)(base + id(i)) * 8;
-        out.ox = rec[0]; out.oy = rec[1]; out.oz = rec[2]; out.dx = rec[3]; out.dy = rec[4]; out.dz = rec[5];
+        load_ray(rec, 0, out);
     }
     __device__ __forceinline__ void init(int i) const { sq.first[base + id(i)] = 0x7fffffff; }
+    __device__ __forceinline__ int bin(int i) const { return sort_bin(sq.key[base + id(i)], shift, nb); }
     static constexpr bool is_shadow = true;
-    // How far from the light an occluder of ray i can be: inShadow accepts T * |d_in| < dist (:424), T > 0, on a ray
-    // that starts `dist` from the light and points at it - so points up to dist away on the near side and, when the
-    // incoming direction is shorter than 1, up to dist / |d_in| - dist beyond the light.
-    __device__ __forceinline__ R reach(int i) const {
-        const R* rec = sq.q + (size_t)(base + id(i)) * 8;
-        const R dist = rec[6], beyond = rec[6] / rec[7] - rec[6];
-        return beyond > dist ? beyond : dist;
-    }
 };
 
-template <typename R, int FAMILY, int RPT, typename Source>
-__global__ void __launch_bounds__(SCAN_THREADS, (sizeof(R) == 4 ? 3 : 2) * 256 / SCAN_THREADS)
+template <typename R, int FAMILY, typename Source, bool TABLE_SMEM>
+__global__ void __launch_bounds__(CULL_THREADS)
 k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, const __grid_constant__ CullFrame<R> frame,
-       int n_cull, const __grid_constant__ CandQueue cq, Counters* ctr, int chunk_objs, int resident_flags) {
-    constexpr int RAYS_PER_BLOCK = SCAN_THREADS * RPT;
-    const int resident = resident_flags & 1;
-    const bool cta_pass = (resident_flags & 2) != 0;           // host switch: try the CTA-wide first packet pass
+       int n_cull, const __grid_constant__ BinLists bl, const __grid_constant__ CandQueue cq, Counters* ctr) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    __shared__ __align__(8) uint64_t bar[2];
+    __shared__ __align__(8) uint64_t bar;
     const int tid = threadIdx.x, lane = tid & 31;
-    uint16_t* const csurv = reinterpret_cast<uint16_t*>(smem_raw);                              // what the CTA's bound keeps (packet stage, first pass)
-    uint16_t* const surv = csurv + ((tid >> 5) + 1) * PCHUNK;                                  // what this warp's bound keeps of it
-    __shared__ R s_wb[SCAN_THREADS / 32][WB_WORDS];
-    __shared__ int s_cn[2];                                                                    // entries of the CTA's list, by pass parity
-    int pass_no = 0;
-    R* const tab = reinterpret_cast<R*>(smem_raw + SURV_BYTES);   // buffer b starts at tab + b * chunk_objs * 4
     const int n = *n_ptr;
-    const int nblocks = (n + RAYS_PER_BLOCK - 1) / RAYS_PER_BLOCK;
+    const int nblocks = (n + CULL_THREADS - 1) / CULL_THREADS;
     if ((int)blockIdx.x >= nblocks) return;
-    const int NP = n_cull;                                     // padded to a multiple of GROUP
-    const int nchunks = (NP + chunk_objs - 1) / chunk_objs;
-    if (tid == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_fence_init(); s_cn[0] = 0; s_cn[1] = 0; }
-    __syncthreads();
-    uint32_t phase[2] = {0, 0};
-    if (resident && NP > 0) {
-        if (tid == 0) stage_cull(table, 0, NP, tab, &bar[0]);
-        mbar_wait(&bar[0], 0);
+    if (Source::is_shadow && blockIdx.x == 0 && tid == 0) atomicAdd(&ctr->rays_shadow, (unsigned long long)n);
+    if (TABLE_SMEM) {
+        if (tid == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
+        __syncthreads();
+        if (tid == 0) stage_cull(table, 0, n_cull, reinterpret_cast<R*>(smem_raw), &bar);
+        mbar_wait(&bar, 0);
     }
-    // blocks of rays are handed out dynamically (their cost varies with what survives the packet stage): a CTA starts
-    // on block blockIdx.x and fetches the following ones from a device counter, one iteration ahead
-    __shared__ int next_blk[2];
-    int iter = 0;
-    for (int blk = blockIdx.x; blk < nblocks; blk = next_blk[iter++ & 1]) {
-        if (tid == 0) next_blk[iter & 1] = (int)gridDim.x + atomicAdd(cq.count + 1, 1);
-        const int ray0 = blk * RAYS_PER_BLOCK;
-        CullRay<R, FAMILY> cr[RPT];
-        bool active[RPT];
-        int rid[RPT];                                          // what the exact kernels index the ray source with
-        R far_reach = R(0), rear = gm<R>::inf();               // shadow packets: farthest reach from the light / rear-most origin along the axis
+    const unsigned char* tab = TABLE_SMEM ? smem_raw : reinterpret_cast<const unsigned char*>(table);
+    unsigned long long fine = 0;
+    for (int blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
+        const int i = blk * CULL_THREADS + tid;
+        const bool active = i < n;
+        Ray<R> w = {R(0), R(0), R(0), R(0), R(0), R(1)};
+        int rid = 0, first = 0, len = 0;
+        if (active) {
+            rid = src.id(i);
+            src.load(i, w); src.init(i);
+            const int b = src.bin(i);
+            const int2 rec = __ldg(bl.bin + min(max(b, 0), bl.n_bins - 1));
+            first = rec.x; len = rec.y;
+        }
+        CullRay<R, FAMILY> cr;
+        cr.init(w, frame);
+        const int len_max = warp_max(len);
+        for (int k0 = 0; k0 < len_max; k0 += GROUP) {          // uniform across the warp
+            const int cnt = min(max(len - k0, 0), GROUP);
+            uint32_t lo, hi;
+            cull_list_window<R, FAMILY>(tab, bl.entry + first + k0, cnt, cr, lo, hi);
+            fine += (unsigned long long)cnt;
+            // warp-aggregated append of the set bits: inclusive scan of the lanes' counts, one atomic for the warp
+            const int mine = __popc(lo) + __popc(hi);
+            if (!__any_sync(0xffffffffu, mine != 0)) continue;
+            int incl = mine;
 #pragma unroll
-        for (int r = 0; r < RPT; r++) {
-            const int i = ray0 + ((tid >> 5) * RPT + r) * 32 + lane;      // a warp owns 32 * RPT consecutive rays: a narrow packet
-            Ray<R> w = {R(0), R(0), R(0), R(0), R(0), R(1)};
-            active[r] = i < n;
-            rid[r] = active[r] ? src.id(i) : 0;
-            if (active[r]) { src.load(i, w); src.init(i); }
-            cr[r].init(w, frame);
-            if constexpr (Source::is_shadow && FAMILY == CULL_PIVOT) { if (active[r]) { const R q = src.reach(i); far_reach = !(q <= far_reach) ? (q == q ? q : gm<R>::inf()) : far_reach; } }
-            if constexpr (Source::is_shadow && FAMILY == CULL_AXIS) {
-                if (active[r]) { const R q = fma_(w.ox, frame.axis[0], fma_(w.oy, frame.axis[1], w.oz * frame.axis[2])); rear = !(q >= rear) ? (q == q ? q : -gm<R>::inf()) : rear; }
+            for (int off = 1; off < 32; off <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, off); if (lane >= off) incl += v; }
+            const int total = __shfl_sync(0xffffffffu, incl, 31);
+            // The counter is unsigned and stops growing once the queue is full: a lattice seen along an axis can leave
+            // dozens of survivors per ray, and a signed counter that kept counting past 2^31 would turn `at` negative
+            // and the stores below into out-of-bounds writes instead of the overflow-and-retrace path.
+            unsigned at = 0;
+            if (lane == 31) {
+                if (*reinterpret_cast<volatile unsigned*>(cq.count) >= (unsigned)cq.cap) at = 0xffffffffu;
+                else at = atomicAdd(reinterpret_cast<unsigned*>(cq.count), (unsigned)total);
+            }
+            at = __shfl_sync(0xffffffffu, at, 31);
+            if (at == 0xffffffffu || at + (unsigned)total > (unsigned)cq.cap) { if (lane == 31) ctr->overflow = 1; continue; }     // queue full: the host retries with smaller tiles
+            at += (unsigned)(incl - mine);
+            const uint32_t* ent = bl.entry + first + k0;
+            uint32_t m = lo;
+            while (m) {
+                const int j = __clz(m);
+                m &= ~(0x80000000u >> j);
+                cq.ray[at] = rid; cq.obj[at] = (int)(ent[j] / (uint32_t)(4 * sizeof(R))); at++;
+            }
+            m = hi;
+            while (m) {
+                const int j = __clz(m);
+                m &= ~(0x80000000u >> j);
+                cq.ray[at] = rid; cq.obj[at] = (int)(ent[32 + j] / (uint32_t)(4 * sizeof(R))); at++;
             }
         }
-        WarpBound<R> wb = warp_bound<R, RPT>(cr, active);
-        // Shadow rays stop at the light: an object farther from a point light than every origin of the packet (plus
-        // what inShadow's T * |d_in| < dist lets through beyond the light), or wholly behind every origin along a
-        // directional light's rays, cannot occlude any of them.
-        if constexpr (FAMILY == CULL_PIVOT) wb.rho = Source::is_shadow ? warp_max(far_reach) * R(1.001) + R(1e-3) : gm<R>::inf();
-        if constexpr (FAMILY == CULL_AXIS) { const R q = Source::is_shadow ? warp_min(rear) : -gm<R>::inf(); wb.sin_t = q - R(1e-3) * (gm<R>::abs(q) + R(1)); }
-        int n_active = 0;
-#pragma unroll
-        for (int r = 0; r < RPT; r++) n_active += active[r] ? 1 : 0;
-        WarpBound<R> cb = {};
-        if (cta_pass) {
-            if (lane == 0) publish_bound<R>(s_wb[tid >> 5], wb, ray0 + (tid >> 5) * RPT * 32 < n);
-            __syncthreads();
-            cb = cta_bound<R, FAMILY>(s_wb);
-        }
-        unsigned long long fine = 0, packet = 0;           // this lane's executed tests
-#ifdef GMLRT_DEBUG_PACKETS
-        if (lane == 0 && FAMILY != CULL_GENERAL) { atomicAdd(&ctr->dbg[0 + 4 * (FAMILY == CULL_AXIS)], 1ull); if (wb.usable) atomicAdd(&ctr->dbg[1 + 4 * (FAMILY == CULL_AXIS)], 1ull); }
-#endif
-        if (!resident) {
-            __syncthreads();                                   // (re)staging must not overtake readers of the previous block of rays
-            if (tid == 0) {
-                stage_cull(table, 0, min(chunk_objs, NP), tab, &bar[0]);
-                if (nchunks > 1) stage_cull(table, chunk_objs, min(chunk_objs, NP - chunk_objs), tab + (size_t)chunk_objs * 4, &bar[1]);
-            }
-        }
-        for (int c = 0; c < (resident ? 1 : nchunks); c++) {   // a resident table is one chunk that is already staged
-            const int b = c & 1;
-            if (!resident) { mbar_wait(&bar[b], phase[b]); phase[b] ^= 1; }
-            const int base = resident ? 0 : c * chunk_objs;
-            const R* sm = resident ? tab : tab + (size_t)b * chunk_objs * 4;
-            const int end = resident ? NP : base + min(chunk_objs, NP - base);
-            // append the survivors in (lo, hi)[r] to the candidate queue; bit 31 - j of lo = object id_of(j), of hi = id_of(32 + j)
-            auto append = [&](uint32_t (&lo)[RPT], uint32_t (&hi)[RPT], auto id_of) __attribute__((always_inline)) {
-                int mine = 0;
-#pragma unroll
-                for (int r = 0; r < RPT; r++) {
-                    if (!active[r]) { lo[r] = 0; hi[r] = 0; }
-                    mine += __popc(lo[r]) + __popc(hi[r]);
-                }
-                if (!__any_sync(0xffffffffu, mine != 0)) return;            // nothing survived in this warp
-                // warp-aggregated append: inclusive scan of the lanes' counts, one atomic for the warp
-                int incl = mine;
-#pragma unroll
-                for (int off = 1; off < 32; off <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, off); if (lane >= off) incl += v; }
-                const int total = __shfl_sync(0xffffffffu, incl, 31);
-                // The counter is unsigned and stops growing once the queue is full: a lattice seen along an axis can leave
-                // dozens of survivors per ray, and a signed counter that kept counting past 2^31 would turn `at` negative
-                // and the stores below into out-of-bounds writes instead of the overflow-and-retrace path.
-                unsigned at = 0;
-                if (lane == 31) {
-                    if (*reinterpret_cast<volatile unsigned*>(cq.count) >= (unsigned)cq.cap) at = 0xffffffffu;
-                    else at = atomicAdd(reinterpret_cast<unsigned*>(cq.count), (unsigned)total);
-                }
-                at = __shfl_sync(0xffffffffu, at, 31);
-                if (at == 0xffffffffu || at + (unsigned)total > (unsigned)cq.cap) { if (lane == 31) ctr->overflow = 1; return; }     // queue full: the host retries with smaller tiles
-                at += (unsigned)(incl - mine);
-#pragma unroll
-                for (int r = 0; r < RPT; r++) {
-                    const int i = rid[r];
-                    uint32_t m = lo[r];
-                    while (m) {
-                        const int j = __clz(m);
-                        m &= ~(0x80000000u >> j);
-                        cq.ray[at] = i; cq.obj[at] = id_of(j); at++;
-                    }
-                    m = hi[r];
-                    while (m) {
-                        const int j = __clz(m);
-                        m &= ~(0x80000000u >> j);
-                        cq.ray[at] = i; cq.obj[at] = id_of(32 + j); at++;
-                    }
-                }
-            };
-            if (cb.usable || wb.usable) {
-                // packet stage.  First pass (when the CTA's rays are coherent as a whole): the 256 threads test the pass's
-                // objects against the CTA's bound, 32 per warp and step, and compact what it keeps into the CTA's list.
-                // Second pass: the lanes of each warp test that list (or, without a CTA bound, every object) against the
-                // warp's own bound and compact into the warp's list; only those objects are tested per ray.
-                const bool warp_has_rays = __any_sync(0xffffffffu, n_active != 0);
-                const unsigned lt = (1u << lane) - 1u;
-                for (int p0 = base; p0 < end; p0 += PCHUNK) {
-                    const int pn = min(PCHUNK, end - p0);
-                    int cn = pn;
-                    if (cb.usable) {                                                 // uniform across the CTA
-                        int* const cnt = &s_cn[pass_no & 1];
-                        for (int o = tid & ~31; o < pn; o += SCAN_THREADS) {
-                            const int k = p0 - base + o + lane;
-                            const bool in = o + lane < pn;
-                            packet += in ? 1 : 0;
-                            const bool sv = in && packet_survives<R>(load_cull(sm, k), cb, (CullRay<R, FAMILY>*)nullptr);
-                            const unsigned bal = __ballot_sync(0xffffffffu, sv);
-                            int at = 0;
-                            if (lane == 0 && bal) at = atomicAdd(cnt, __popc(bal));
-                            at = __shfl_sync(0xffffffffu, at, 0);
-                            if (sv) csurv[at + __popc(bal & lt)] = (uint16_t)k;
-                        }
-                        __syncthreads();
-                        cn = *cnt;
-                        if (tid == 0) s_cn[(pass_no + 1) & 1] = 0;                    // free since the end of the previous pass
-                        pass_no++;
-                    }
-                    int ns = 0;
-                    if (warp_has_rays && wb.usable) {
-                        for (int o = 0; o < cn; o += 32) {
-                            const bool in = o + lane < cn;
-                            const int k = cb.usable ? (in ? (int)csurv[o + lane] : 0) : p0 - base + o + lane;
-                            packet += in ? 1 : 0;
-                            const bool sv = in && packet_survives<R>(load_cull(sm, k), wb, (CullRay<R, FAMILY>*)nullptr);
-                            const unsigned bal = __ballot_sync(0xffffffffu, sv);
-                            if (sv) surv[ns + __popc(bal & lt)] = (uint16_t)k;
-                            ns += __popc(bal);
-                        }
-                    } else if (warp_has_rays) {                                      // (a warp bound can only be unusable here if the CTA's is)
-                        for (int o = lane; o < cn; o += 32) surv[o] = cb.usable ? csurv[o] : (uint16_t)(p0 - base + o);
-                        ns = cn;
-                    }
-#ifdef GMLRT_DEBUG_PACKETS
-                    if (lane == 0) { atomicAdd(&ctr->dbg[2 + 4 * (FAMILY == CULL_AXIS)], (unsigned long long)pn); atomicAdd(&ctr->dbg[3 + 4 * (FAMILY == CULL_AXIS)], (unsigned long long)ns); }
-#endif
-                    const int padded = (ns + 7) & ~7;                                   // whole 16-byte loads of 8 indices
-                    if (ns + lane < padded) surv[ns + lane] = (uint16_t)(p0 - base);     // any valid record; masked off below
-                    __syncwarp();
-                    for (int k0 = 0; k0 < padded; k0 += GROUP) {
-                        uint32_t lo[RPT], hi[RPT];
-                        cull_window_indirect<R, FAMILY, RPT>(sm, surv, k0, min(GROUP, padded - k0), cr, lo, hi);
-                        const int valid = ns - k0;                                 // entries of this window that are real
-                        fine += (unsigned long long)(n_active * min(valid, GROUP));
-                        const uint32_t mlo = valid >= 32 ? 0xffffffffu : ~(0xffffffffu >> valid);
-                        const uint32_t mhi = valid >= 64 ? 0xffffffffu : (valid <= 32 ? 0u : ~(0xffffffffu >> (valid - 32)));
-#pragma unroll
-                        for (int r = 0; r < RPT; r++) { lo[r] &= mlo; hi[r] &= mhi; }
-                        append(lo, hi, [&](int j) { return base + (int)surv[k0 + j]; });
-                    }
-                    if (cb.usable) __syncthreads();                                  // the CTA's list is rewritten by the next pass
-                    else __syncwarp();                                               // the warp's list likewise
-                }
-            } else {
-                for (int first = base; first < end; first += GROUP) {      // one window of GROUP objects
-                    uint32_t lo[RPT], hi[RPT];
-                    cull_window<R, FAMILY, RPT>(sm, first - base, cr, lo, hi);
-                    fine += (unsigned long long)(n_active * GROUP);
-                    append(lo, hi, [&](int j) { return first + j; });
-                }
-            }
-            if (!resident) {
-                __syncthreads();                               // everyone is done reading buffer b
-                if (tid == 0 && c + 2 < nchunks) {
-                    const int nb = (c + 2) * chunk_objs;
-                    stage_cull(table, nb, min(chunk_objs, NP - nb), tab + (size_t)b * chunk_objs * 4, &bar[b]);
-                }
-            }
-        }
-        fine = warp_sum_u64(fine); packet = warp_sum_u64(packet);
-        if (lane == 0) { atomicAdd(&ctr->cull_tests[FAMILY], fine); if (packet) atomicAdd(&ctr->packet_tests, packet); }
-        __syncthreads();                                       // next_blk[iter & 1] is visible; slot (iter + 1) & 1 is free again
     }
+    fine = warp_sum_u64(fine);
+    if (lane == 0 && fine) atomicAdd(&ctr->cull_tests[FAMILY], fine);
 }
 
 __device__ __forceinline__ void warp_add(unsigned long long* dst, unsigned long long v) {
@@ -1548,13 +1388,11 @@ __global__ void __launch_bounds__(EXACT_THREADS) k_exact_shadow(const __grid_con
 // is written; the 32-byte ray records stay where k_shade put them.
 constexpr int SORT_BINS_MAX = 8192, SORT_CHUNK = 4096, SORT_THREADS = 256;
 
-__device__ __forceinline__ int sort_bin(int key, int shift, int nb) { return key < 0 ? nb - 1 : min(key >> shift, nb - 2); }
 
 template <typename R>
-__global__ void __launch_bounds__(SORT_THREADS) k_sort_hist(const __grid_constant__ ShadowQueue<R> sq, int light, int shift, int nb, int* hist, Counters* ctr) {
+__global__ void __launch_bounds__(SORT_THREADS) k_sort_hist(const __grid_constant__ ShadowQueue<R> sq, int light, int shift, int nb, int* hist) {
     __shared__ int h[SORT_BINS_MAX];
     const int n = sq.count[light], base = light * sq.per_light;
-    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&ctr->rays_shadow, (unsigned long long)n);
     const int nchunks = (n + SORT_CHUNK - 1) / SORT_CHUNK;
     for (int b = threadIdx.x; b < nb; b += SORT_THREADS) h[b] = 0;
     __syncthreads();
@@ -1567,7 +1405,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k_sort_hist(const __grid_constan
 
 // exclusive prefix of hist[0..nb) into cursor[0..nb); hist is cleared for the next use (one block; tiles of 4096
 // bins read as int4, so the 55k bins of the key sort are 14 coalesced rounds)
-static __global__ void __launch_bounds__(1024) k_sort_scan(int nb, int* hist, int* cursor) {
+static __global__ void __launch_bounds__(1024) k_sort_scan(int nb, int* hist, int* cursor, int clear = 1) {
     __shared__ int warp_tot[32];
     __shared__ int carry_s;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -1600,10 +1438,10 @@ static __global__ void __launch_bounds__(1024) k_sort_scan(int nb, int* hist, in
         __syncthreads();
         const int carry = carry_s;
         int run = carry + warp_tot[wid] + incl - mine;
-        if (b < nb) { cursor[b] = run; hist[b] = 0; } run += v.x;
-        if (b + 1 < nb) { cursor[b + 1] = run; hist[b + 1] = 0; } run += v.y;
-        if (b + 2 < nb) { cursor[b + 2] = run; hist[b + 2] = 0; } run += v.z;
-        if (b + 3 < nb) { cursor[b + 3] = run; hist[b + 3] = 0; } run += v.w;
+        if (b < nb) { cursor[b] = run; if (clear) hist[b] = 0; } run += v.x;
+        if (b + 1 < nb) { cursor[b + 1] = run; if (clear) hist[b + 1] = 0; } run += v.y;
+        if (b + 2 < nb) { cursor[b + 2] = run; if (clear) hist[b + 2] = 0; } run += v.z;
+        if (b + 3 < nb) { cursor[b + 3] = run; if (clear) hist[b + 3] = 0; } run += v.w;
         __syncthreads();
         if (tid == 1023) carry_s = run;                    // inclusive total through this tile
         __syncthreads();
@@ -1940,7 +1778,7 @@ __global__ void __launch_bounds__(256) k_gen(DevScene<R> sc, Level<R> lv, Counte
     if (i >= S) return;
     double o[3], d[3];
     camera_ray64(sc, CamSrc{y0, map}, i, o, d);
-    store_ray(lv.ray, i, (R)o[0], (R)o[1], (R)o[2], (R)d[0], (R)d[1], (R)d[2], 0);
+    store_ray(lv.ray, i, (R)o[0], (R)o[1], (R)o[2], (R)d[0], (R)d[1], (R)d[2], 0, 0);
 }
 
 // ------------------------------------------------------------------ shade (traceRay :498-556 minus the recursion)
@@ -2163,16 +2001,18 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
                 if (fuzz >= R(0)) rd = rd + mk(fuzz * gm<R>::cos(fuzz) * gm<R>::cos(fuzz), fuzz * gm<R>::sin(fuzz) * gm<R>::sin(fuzz), R(0));
                 const V3<R> ro = P + N * R(1e-4);
                 rd = normalize(rd);
-                store_ray(spawn_to, slot, ro.x, ro.y, ro.z, rd.x, rd.y, rd.z, i);
-                next.hit[slot] = ray_sort_key(sc, region, rd);
+                const int key = ray_sort_key(sc, region, rd);
+                store_ray(spawn_to, slot, ro.x, ro.y, ro.z, rd.x, rd.y, rd.z, i, key);
+                next.hit[slot] = key;
                 }
             }
             if (want_refr) {                                                         // refraction child (:532-556)
                 const int slot = s[SHADE_Q_REFR][wid] + __popc(m_refr & lt);
                 if (slot < next.cap) {
                 const V3<R> ro = P - refr_n * R(1e-4);
-                store_ray(spawn_to, slot, ro.x, ro.y, ro.z, refr_d.x, refr_d.y, refr_d.z, (int)((unsigned)i | 0x80000000u));
-                next.hit[slot] = ray_sort_key(sc, region, refr_d);
+                const int key = ray_sort_key(sc, region, refr_d);
+                store_ray(spawn_to, slot, ro.x, ro.y, ro.z, refr_d.x, refr_d.y, refr_d.z, (int)((unsigned)i | 0x80000000u), key);
+                next.hit[slot] = key;
                 }
             }
         }
@@ -2334,18 +2174,13 @@ public:
         const int smem_max = 200 * 1024;
         auto allow = [&](auto kernel) -> int { CU_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max)); return GMLRT_OK; };
         int rc;
-        if ((rc = allow(k_cull<R, CULL_PIVOT, RPT_FAMILY, ClosestSource<R>>)) || (rc = allow(k_cull<R, CULL_GENERAL, RPT_GENERAL, ClosestSource<R>>)) ||
-            (rc = allow(k_cull<R, CULL_PIVOT, RPT_FAMILY, ShadowSource<R>>)) || (rc = allow(k_cull<R, CULL_AXIS, RPT_FAMILY, ShadowSource<R>>)))
+        if ((rc = allow(k_cull<R, CULL_PIVOT, CameraSource<R>, true>)) || (rc = allow(k_cull<R, CULL_GENERAL, SpawnSource<R>, true>)) ||
+            (rc = allow(k_cull<R, CULL_PIVOT, ShadowSource<R>, true>)) || (rc = allow(k_cull<R, CULL_AXIS, ShadowSource<R>, true>)))
             return rc;
         return GMLRT_OK;
     }
 
     static constexpr bool kRobustPrimary = std::is_same<R, float>::value;   // f32: double re-test of borderline primary hits
-#ifndef GMLRT_RPT_FAMILY
-#define GMLRT_RPT_FAMILY 4
-#endif
-    static constexpr int RPT_GENERAL = 2, RPT_FAMILY = GMLRT_RPT_FAMILY;                   // rays per thread: 8 cull registers per ray vs 4
-
     void reset_totals() override { totals_ = TraceTotals(); need_ctr_reset_ = true; ev_used_ = 0; ev_cls_.clear(); }
     void set_profiling(bool on) override { profile_ = on; }
 
@@ -2476,11 +2311,17 @@ private:
     TraceTotals totals_;
     bool need_ctr_reset_ = true;
     // scan kernel configuration
-    int chunk_objs_ = GROUP, resident_ = 1; size_t table_smem_ = 0;
-    int cta_pass_ = 7;                                  // CTA-wide first packet pass for: 1 camera rays, 2 spawned rays, 4 shadow rays (GMLRT_CTA_PASS)
+    int resident_ = 1; size_t table_smem_ = 0;
     struct Launch { int grid = 148; size_t smem = 0; };
     size_t cfg_smem_ = ~(size_t)0;
     Launch l_primary_, l_closest_, l_shadow_pivot_, l_shadow_axis_;                      // the four k_cull instantiations
+    // ray classes (see "ray classes" above): one candidate list per bin, built once per upload
+    static constexpr int TILE_W = 32, TILE_H = 8;                // camera-ray class = screen tile (a warp's 8 pixels x 4 samples share one)
+    BinLists lists_camera_{}, lists_spawn_{}; std::vector<BinLists> lists_light_;
+    std::vector<double> region_bound_;                           // host: [n_regions][4] sphere holding every point of the region (inf = unbounded)
+    unsigned long long* list_tests_dev_ = nullptr; unsigned long long list_tests_ = 0;
+    bool sort_shadows_ = false;                                  // GMLRT_SORT_SHADOWS: order the shadow rays of a light by class before the cull
+    int build_lists(const HostScene& S, std::string& err);
     CandQueue cq_{}; int cand_per_ray_ = 4, tile_shrink_ = 0; unsigned long long scene_sig_ = ~0ull, planned_sig_ = ~0ull - 1; int planned_rows_full_ = 0;
     int* sort_hist_ = nullptr; int* sort_cursor_ = nullptr; int sort_nb_ = 2, sort_shift_ = 0, n_regions_ = 1; bool sort_clear_ = true;
     int* key_hist_ = nullptr; int* key_cursor_ = nullptr; int key_nb_ = 6;      // spawned rays by (origin leaf, direction cell); cleared with sort_hist_
@@ -2535,7 +2376,7 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     std::vector<R> w2o(na * 12, R(0)), o2w(na * 12, R(0)), fn(na * 18, R(0));
     std::vector<double> w2o64(kRobustPrimary ? na * 12 : 0, 0.0);
     std::vector<int> scan_of(na, 0), surface(na, 0), kind(na, K_SPHERE), obj_flops(std::max(n, 1), 0);
-    const int n_cull = std::max((n + GROUP - 1) / GROUP * GROUP, GROUP);
+    const int n_cull = std::max((n + 1 + GROUP - 1) / GROUP * GROUP, GROUP);     // always at least one padding record: the candidate lists pad with it
     std::vector<unsigned long long> cum_flops(std::max(n, 1), 0ull);
     DevScene<R> sc{};
     sc.n_leaves = n; sc.n_cull = n_cull; sc.n_all = n_all;
@@ -2654,6 +2495,52 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
             if (k < n_plane_grids) n_regions += GMLRT_PLANE_GRID * GMLRT_PLANE_GRID;
             else { sc.plane_par[k][0] = sc.plane_par[k][1] = R(0); sc.plane_par[k][2] = R(1); }
         }
+        // What every region holds (for the ray classes, build_lists): a sphere around every point region_of() can map to it.
+        region_bound_.assign((size_t)n_regions * 4, 0.0);
+        auto set_region = [&](int r, double x, double y, double z, double rad) {
+            double* q = &region_bound_[(size_t)r * 4];
+            q[0] = x; q[1] = y; q[2] = z; q[3] = rad;
+        };
+        for (size_t k = 0; k < small.size(); k++) {                  // a small object: its bounding sphere
+            const double* b = &bound_[(size_t)small[k].second * 4];
+            set_region((int)k, b[0], b[1], b[2], b[3]);
+        }
+        if (any_large) {                                             // grid cells; points outside the grid are clamped into its border cells
+            bool open_border = false;                                // ... which only unbounded objects have
+            for (int d = 0; d < n; d++) if (rid_of[d] == -1 && !std::isfinite(bound_[(size_t)d * 4 + 3])) open_border = true;
+            for (int cx = 0; cx < dim[0]; cx++) for (int cy = 0; cy < dim[1]; cy++) for (int cz = 0; cz < dim[2]; cz++) {
+                const int r = sc.n_small + (cx * dim[1] + cy) * dim[2] + cz;
+                const bool border = cx == 0 || cy == 0 || cz == 0 || cx == dim[0] - 1 || cy == dim[1] - 1 || cz == dim[2] - 1;
+                set_region(r, lo3[0] + (cx + 0.5) * edge, lo3[1] + (cy + 0.5) * edge, lo3[2] + (cz + 0.5) * edge,
+                           (border && open_border) ? INFINITY : edge * 0.8660254037844387 * 1.001);
+            }
+        }
+        for (int k = 0; k < n_plane_grids; k++) {                    // cells of a plane's own (x, z) grid, see region_of()
+            int dplane = -1;
+            for (int d = 0; d < n; d++) if (rid_of[d] == -2 - k) dplane = d;
+            const HostLeaf& L = S.leaves[order[dplane]];
+            const double par0 = (double)sc.plane_par[k][0], par1 = (double)sc.plane_par[k][1], par2 = (double)sc.plane_par[k][2];
+            const int G = GMLRT_PLANE_GRID;
+            auto edge_of = [&](int c, double par_c) {                // object-space coordinate where cell c begins: g = 2 c / G - 1, x = g / (1 - |g|)
+                const double g = 2.0 * c / G - 1.0;
+                return g / (1.0 - std::fabs(g)) / par2 + par_c;
+            };
+            for (int cx = 0; cx < G; cx++) for (int cz = 0; cz < G; cz++) {
+                const int r = sc.plane_base[k] + cx * G + ((cx & 1) ? G - 1 - cz : cz);
+                if (cx == 0 || cz == 0 || cx == G - 1 || cz == G - 1) { set_region(r, 0, 0, 0, INFINITY); continue; }     // the outer ring runs to infinity
+                double x0 = edge_of(cx, par0), x1 = edge_of(cx + 1, par0), z0 = edge_of(cz, par1), z1 = edge_of(cz + 1, par1);
+                const double mx = 1e-3 * (x1 - x0) + 1e-5 * (std::fabs(x0) + std::fabs(x1)), mz = 1e-3 * (z1 - z0) + 1e-5 * (std::fabs(z0) + std::fabs(z1));
+                x0 -= mx; x1 += mx; z0 -= mz; z1 += mz;
+                double c[4][3], mid[3] = {0, 0, 0};
+                for (int q = 0; q < 4; q++) {
+                    const double px = (q & 1) ? x1 : x0, pz = (q & 2) ? z1 : z0;
+                    for (int a = 0; a < 3; a++) { c[q][a] = L.o2w[4 * a] * px + L.o2w[4 * a + 2] * pz + L.o2w[4 * a + 3]; mid[a] += 0.25 * c[q][a]; }
+                }
+                double rad = 0;
+                for (int q = 0; q < 4; q++) rad = std::max(rad, std::sqrt((c[q][0] - mid[0]) * (c[q][0] - mid[0]) + (c[q][1] - mid[1]) * (c[q][1] - mid[1]) + (c[q][2] - mid[2]) * (c[q][2] - mid[2])));
+                set_region(r, mid[0], mid[1], mid[2], rad * 1.0001);
+            }
+        }
     }
     n_regions_ = n_regions;
     std::vector<DevLight<R>> lights(S.lights.size());
@@ -2714,7 +2601,6 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     while ((size_t)(((n_regions - 1) >> sc.key_shift) + 1) * 6 * sc.key_k * sc.key_k > (size_t)KEY_BINS_MAX) sc.key_shift++;
     key_nb_ = (((n_regions - 1) >> sc.key_shift) + 1) * 6 * sc.key_k * sc.key_k;
     sort_spawned_ = env_size("GMLRT_SORT_SPAWNED", 1) != 0;
-    cta_pass_ = (int)env_size("GMLRT_CTA_PASS", 7);
     for (int k = 0; k < 3; k++) { sc.ambient[k] = (R)S.h.ambient[k]; sc.bg0[k] = (R)S.h.bg_start[k]; sc.bg1[k] = (R)S.h.bg_end[k]; }
     sc_ = sc;
     // cull tables: any ray; camera rays (their lines pass through the eye, raytracer.go:605-609); one per light
@@ -2736,6 +2622,10 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
         }
         if (rc) return rc;
     }
+    sort_nb_ = std::min(n_regions_ + 1, SORT_BINS_MAX); sort_shift_ = 0;        // class of a shadow ray: the region of the shaded point
+    while (((n_regions_ - 1) >> sort_shift_) + 2 > sort_nb_) sort_shift_++;
+    sort_shadows_ = env_size("GMLRT_SORT_SHADOWS", 0) != 0;
+    if ((rc = build_lists(S, err))) return rc;
     {
         void* p = nullptr;
         if ((rc = scene_alloc(std::max<size_t>(S.lights.size(), 1) * sizeof(int), &p, err))) return rc;
@@ -2815,6 +2705,123 @@ int Renderer<R>::build_cull_table(int family, const double* v, double offset_abs
         }
     }
     return to_device(tab, out, err);
+}
+
+// The candidate lists of the ray classes (see "ray classes"): camera rays by screen tile, spawned rays by (region, direction
+// cell), the shadow rays of each light by region.  Two passes per set (count, scan, fill); the totals of all sets come
+// back in one synchronisation.
+template <typename R>
+int Renderer<R>::build_lists(const HostScene& S, std::string& err) {
+    const int n = sc_.n_leaves;
+    int rc;
+    // regions merged the way the keys merge them
+    auto merged = [&](int shift, int total) {
+        const int groups = std::min(((n_regions_ - 1) >> shift) + 1, total);
+        std::vector<double> out((size_t)total * 4, 0.0);
+        for (int g = 0; g < total; g++) out[(size_t)g * 4 + 3] = INFINITY;          // bins beyond the regions (unused, invalid keys): no bound
+        for (int g = 0; g < groups; g++) {
+            double C[3] = {0, 0, 0}, Rr = -1.0;
+            for (int r = g << shift; r < std::min(n_regions_, (g + 1) << shift); r++) {
+                const double* q = &region_bound_[(size_t)r * 4];
+                if (Rr < 0) { C[0] = q[0]; C[1] = q[1]; C[2] = q[2]; Rr = q[3]; }
+                else { double C2[3], R2; sphere_union(C, Rr, q, q[3], C2, R2); C[0] = C2[0]; C[1] = C2[1]; C[2] = C2[2]; Rr = R2; }
+            }
+            double* o = &out[(size_t)g * 4];
+            o[0] = C[0]; o[1] = C[1]; o[2] = C[2]; o[3] = (Rr >= 0 && Rr == Rr) ? Rr : INFINITY;
+        }
+        return out;
+    };
+    // the cone of directions of every cube-map cell of ray_sort_key()
+    const int k = sc_.key_k, n_cells = 6 * k * k;
+    std::vector<double> cells((size_t)n_cells * 5);
+    for (int face = 0; face < 6; face++) for (int cu = 0; cu < k; cu++) for (int cv = 0; cv < k; cv++) {
+        auto dir = [&](double U, double V, double* d) {
+            const double sgn = (face & 1) ? -1.0 : 1.0;
+            if (face < 2) { d[0] = sgn; d[1] = U; d[2] = V; } else if (face < 4) { d[0] = U; d[1] = sgn; d[2] = V; } else { d[0] = U; d[1] = V; d[2] = sgn; }
+            normalize3(d);
+        };
+        const double u0 = 2.0 * cu / k - 1.0, u1 = 2.0 * (cu + 1) / k - 1.0, v0 = 2.0 * cv / k - 1.0, v1 = 2.0 * (cv + 1) / k - 1.0;
+        double ax[3], c = 1.0;
+        dir(0.5 * (u0 + u1), 0.5 * (v0 + v1), ax);
+        for (int q = 0; q < 4; q++) {
+            double d[3];
+            dir((q & 1) ? u1 : u0, (q & 2) ? v1 : v0, d);
+            c = std::min(c, ax[0] * d[0] + ax[1] * d[1] + ax[2] * d[2]);
+        }
+        const double th = std::acos(std::min(c, 1.0)) + 2e-6;          // the key is taken from the rounded direction: a cell is that much fuzzy
+        double* o = &cells[(size_t)((face * k + cu) * k + ((cu & 1) ? k - 1 - cv : cv)) * 5];
+        o[0] = ax[0]; o[1] = ax[1]; o[2] = ax[2]; o[3] = std::cos(th); o[4] = std::sin(th);
+    }
+    const std::vector<double> reg_spawn = merged(sc_.key_shift, key_nb_ / n_cells), reg_shadow = merged(sort_shift_, sort_nb_);
+    double *d_bound, *d_cells, *d_reg_spawn, *d_reg_shadow;
+    if ((rc = to_device(bound_, &d_bound, err)) || (rc = to_device(cells, &d_cells, err)) || (rc = to_device(reg_spawn, &d_reg_spawn, err)) ||
+        (rc = to_device(reg_shadow, &d_reg_shadow, err))) return rc;
+    if (!list_tests_dev_) { CU_TRY(cudaMalloc(&list_tests_dev_, sizeof(unsigned long long))); }
+    CU_TRY(cudaMemsetAsync(list_tests_dev_, 0, sizeof(unsigned long long), stream_));
+
+    struct Pending { BinParams p; BinLists* out; int* count; int* first; };
+    std::vector<Pending> sets;
+    auto base_params = [&](int kind, int n_bins, double offset_abs) {
+        BinParams p{};
+        p.kind = kind; p.n_bins = n_bins;
+        p.bound = d_bound; p.n_objects = n; p.radius_rel = CullMargin<R>::radius; p.offset_abs = offset_abs; p.rel = CullMargin<R>::rel;
+        return p;
+    };
+    lists_light_.assign(S.lights.size(), BinLists{});
+    {   // camera rays (the eye, raytracer.go:605-609)
+        const int tx = (S.width + TILE_W - 1) / TILE_W, ty = (S.height + TILE_H - 1) / TILE_H;
+        BinParams p = base_params(BIN_CAMERA, tx * ty, 1e-5);
+        p.pivot[0] = 0.0; p.pivot[1] = 0.0; p.pivot[2] = -1.0;
+        p.W = S.width; p.H = S.height; p.tile_w = TILE_W; p.tile_h = TILE_H; p.tiles_x = tx;
+        p.cam_su = sc_.cam_su; p.cam_sv = sc_.cam_sv; p.vw = sc_.vw; p.vh = sc_.vh;
+        sets.push_back({p, &lists_camera_, nullptr, nullptr});
+    }
+    {   // reflection / refraction rays
+        BinParams p = base_params(BIN_SPAWN, key_nb_, 0.0);
+        p.region = d_reg_spawn; p.n_regions = (int)(reg_spawn.size() / 4); p.cell = d_cells; p.n_cells = n_cells;
+        sets.push_back({p, &lists_spawn_, nullptr, nullptr});
+    }
+    for (size_t i = 0; i < S.lights.size(); i++) {
+        const gmlrt_light& l = S.lights[i];
+        const bool axis = l.kind == GMLRT_LIGHT_DIRECTIONAL;
+        BinParams p = base_params(axis ? BIN_SHADOW_AXIS : BIN_SHADOW_PIVOT, sort_nb_, axis ? 1e-5 : 1.5e-4);
+        p.region = d_reg_shadow; p.n_regions = (int)(reg_shadow.size() / 4);
+        for (int a = 0; a < 3; a++) {
+            p.pivot[a] = l.pos[a];
+            p.e1[a] = (double)frame_light_[i].e1[a]; p.e2[a] = (double)frame_light_[i].e2[a]; p.axis[a] = (double)frame_light_[i].axis[a];
+        }
+        // inShadow accepts T * |incoming direction| < dist (:424): with |incoming direction| = 1 (camera and reflection rays
+        // are normalised) an occluder lies between the point and the light; refraction rays are not normalised (:438-450)
+        p.limit_reach = S.any_refract ? 0 : 1;
+        sets.push_back({p, &lists_light_[i], nullptr, nullptr});
+    }
+    std::vector<int> tails(sets.size() * 2, 0);
+    for (size_t s = 0; s < sets.size(); s++) {
+        Pending& ps = sets[s];
+        void *pc = nullptr, *pf = nullptr;
+        if ((rc = scene_alloc((size_t)ps.p.n_bins * sizeof(int), &pc, err)) || (rc = scene_alloc((size_t)ps.p.n_bins * sizeof(int), &pf, err))) return rc;
+        ps.count = (int*)pc; ps.first = (int*)pf;
+        const int grid = std::min((ps.p.n_bins + 7) / 8, sms_ * 32);
+        k_list_build<false><<<grid, 256, 0, stream_>>>(ps.p, ps.count, nullptr, nullptr, nullptr, 0u, list_tests_dev_);
+        k_sort_scan<<<1, 1024, 0, stream_>>>(ps.p.n_bins, ps.count, ps.first, 0);
+        CU_TRY(cudaMemcpyAsync(&tails[2 * s], ps.count + ps.p.n_bins - 1, sizeof(int), cudaMemcpyDeviceToHost, stream_));
+        CU_TRY(cudaMemcpyAsync(&tails[2 * s + 1], ps.first + ps.p.n_bins - 1, sizeof(int), cudaMemcpyDeviceToHost, stream_));
+    }
+    CU_TRY(cudaMemcpyAsync(&list_tests_, list_tests_dev_, sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream_));
+    CU_TRY(cudaStreamSynchronize(stream_));
+    list_tests_ *= 2;                                                  // the fill pass repeats the tests
+    for (size_t s = 0; s < sets.size(); s++) {
+        Pending& ps = sets[s];
+        const long long total = (long long)tails[2 * s] + tails[2 * s + 1];
+        if (total < 0 || tails[2 * s + 1] < 0) { err = "candidate lists of the ray classes exceed 2^31 entries"; return GMLRT_E_UNSUPPORTED; }
+        void *pe = nullptr, *pb = nullptr;
+        if ((rc = scene_alloc(std::max<size_t>((size_t)total, 4) * sizeof(uint32_t), &pe, err)) || (rc = scene_alloc((size_t)ps.p.n_bins * sizeof(int2), &pb, err))) return rc;
+        const int grid = std::min((ps.p.n_bins + 7) / 8, sms_ * 32);
+        k_list_build<true><<<grid, 256, 0, stream_>>>(ps.p, nullptr, ps.first, (int2*)pb, (uint32_t*)pe, (uint32_t)(4 * sizeof(R)), nullptr);
+        ps.out->bin = (const int2*)pb; ps.out->entry = (const uint32_t*)pe; ps.out->n_bins = ps.p.n_bins;
+    }
+    CU_TRY(cudaGetLastError());
+    return GMLRT_OK;
 }
 
 template <typename R>
@@ -2904,8 +2911,6 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     sort_hist_ = (int*)(base + o_sort); sort_cursor_ = sort_hist_ + SORT_BINS_MAX; sort_clear_ = true;
     key_hist_ = (int*)(base + o_keysort); key_cursor_ = key_hist_ + KEY_BINS_MAX;
     spawn_stage_ = (R*)(base + o_stage);
-    sort_nb_ = std::min(n_regions_ + 1, SORT_BINS_MAX); sort_shift_ = 0;        // shadow rays by the region of the shaded point
-    while (((n_regions_ - 1) >> sort_shift_) + 2 > sort_nb_) sort_shift_++;
     cq_.ray = (int*)(base + o_cray); cq_.obj = (int*)(base + o_cobj); cq_.t = (void*)(base + o_ct); cq_.count = (int*)(base + o_ccount);
     cq_.cap = (int)cand_cap;
     for (int k = 0; k < SHADOW_STREAMS; k++) {
@@ -2914,28 +2919,31 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
         sort_hist_sh_[k] = sort_hist_ + (size_t)2 * k * SORT_BINS_MAX; sort_cursor_sh_[k] = sort_hist_sh_[k] + SORT_BINS_MAX;
     }
 
-    // scan kernels: resident cull table when it fits, else two streaming buffers (chunks of whole groups)
+    // cull kernels: the family's table staged into shared memory when it fits, else read through L1
     const size_t rec_bytes = 4 * sizeof(R);
     const size_t resident_max = env_size("GMLRT_RESIDENT_KB", 128) * 1024;
-    const size_t chunk_bytes = std::max<size_t>(env_size("GMLRT_CHUNK_KB", 32) * 1024, GROUP * rec_bytes);
     const size_t all = (size_t)sc_.n_cull * rec_bytes;
-    if (all <= resident_max) { resident_ = 1; chunk_objs_ = sc_.n_cull; table_smem_ = all; }
-    else { resident_ = 0; chunk_objs_ = (int)(chunk_bytes / rec_bytes) / GROUP * GROUP; table_smem_ = 2 * (size_t)chunk_objs_ * rec_bytes; }
-    if (cfg_smem_ == SURV_BYTES + table_smem_) return GMLRT_OK;      // launch shapes depend on the staged table size only
-    cfg_smem_ = SURV_BYTES + table_smem_;
+    resident_ = all <= resident_max ? 1 : 0;
+    table_smem_ = resident_ ? all : 0;
+    if (cfg_smem_ == table_smem_ + (size_t)resident_) return GMLRT_OK;      // launch shapes depend on the staged table size only
+    cfg_smem_ = table_smem_ + (size_t)resident_;
     auto cfg = [&](auto kernel, Launch& L) -> int {
         int occ = 1;
-        L.smem = SURV_BYTES + table_smem_;
-        CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, SCAN_THREADS, L.smem));
+        L.smem = table_smem_;
+        CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, CULL_THREADS, L.smem));
         L.grid = sms_ * std::max(occ, 1);
         return GMLRT_OK;
     };
     int rc;
-    if ((rc = cfg(k_cull<R, CULL_PIVOT, RPT_FAMILY, ClosestSource<R>>, l_primary_)) ||
-        (rc = cfg(k_cull<R, CULL_GENERAL, RPT_GENERAL, ClosestSource<R>>, l_closest_)) ||
-        (rc = cfg(k_cull<R, CULL_PIVOT, RPT_FAMILY, ShadowSource<R>>, l_shadow_pivot_)) ||
-        (rc = cfg(k_cull<R, CULL_AXIS, RPT_FAMILY, ShadowSource<R>>, l_shadow_axis_)))
-        return rc;
+    if (resident_) {
+        if ((rc = cfg(k_cull<R, CULL_PIVOT, CameraSource<R>, true>, l_primary_)) || (rc = cfg(k_cull<R, CULL_GENERAL, SpawnSource<R>, true>, l_closest_)) ||
+            (rc = cfg(k_cull<R, CULL_PIVOT, ShadowSource<R>, true>, l_shadow_pivot_)) || (rc = cfg(k_cull<R, CULL_AXIS, ShadowSource<R>, true>, l_shadow_axis_)))
+            return rc;
+    } else {
+        if ((rc = cfg(k_cull<R, CULL_PIVOT, CameraSource<R>, false>, l_primary_)) || (rc = cfg(k_cull<R, CULL_GENERAL, SpawnSource<R>, false>, l_closest_)) ||
+            (rc = cfg(k_cull<R, CULL_PIVOT, ShadowSource<R>, false>, l_shadow_pivot_)) || (rc = cfg(k_cull<R, CULL_AXIS, ShadowSource<R>, false>, l_shadow_axis_)))
+            return rc;
+    }
     return GMLRT_OK;
 }
 
@@ -3004,7 +3012,6 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             const int cap_blocks = (levels_[l].cap + SHADE_THREADS - 1) / SHADE_THREADS;
             const int exact_grid = sms_ * 16;
             CU_TRY(cudaMemsetAsync(cq_.count, 0, 2 * sizeof(int), stream_));
-            ClosestSource<R> csrc{levels_[l]};
             if (sort_clear_) {
                 CU_TRY(cudaMemsetAsync(sort_hist_, 0, 2 * SHADOW_STREAMS * SORT_BINS_MAX * sizeof(int), stream_));
                 CU_TRY(cudaMemsetAsync(key_hist_, 0, KEY_BINS_MAX * sizeof(int), stream_));
@@ -3019,8 +3026,11 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             }
             if (l == 0) {                                  // camera rays: PIVOT family through the eye, robust re-tests in f32
                 MARK(KC_CLOSEST_PRIMARY);
-                k_cull<R, CULL_PIVOT, RPT_FAMILY, ClosestSource<R>><<<l_primary_.grid, SCAN_THREADS, l_primary_.smem, stream_>>>(
-                    csrc, &ctr_->count[l], cull_eye_, frame_eye_, sc_.n_cull, cq_, ctr_, chunk_objs_, resident_ | ((cta_pass_ & 1) ? 2 : 0));
+                CameraSource<R> cams{levels_[l], W, ty, map, TILE_W, TILE_H, (W + TILE_W - 1) / TILE_W};
+                if (resident_) k_cull<R, CULL_PIVOT, CameraSource<R>, true><<<l_primary_.grid, CULL_THREADS, l_primary_.smem, stream_>>>(
+                    cams, &ctr_->count[l], cull_eye_, frame_eye_, sc_.n_cull, lists_camera_, cq_, ctr_);
+                else k_cull<R, CULL_PIVOT, CameraSource<R>, false><<<l_primary_.grid, CULL_THREADS, 0, stream_>>>(
+                    cams, &ctr_->count[l], cull_eye_, frame_eye_, sc_.n_cull, lists_camera_, cq_, ctr_);
                 MARK(KC_EXACT);
                 if (kRobustPrimary) {
                     // float32 spheres inline; then the double-precision pass: other kinds + the spheres the first pass deferred
@@ -3038,8 +3048,11 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
                 }
             } else {
                 MARK(KC_CLOSEST);
-                k_cull<R, CULL_GENERAL, RPT_GENERAL, ClosestSource<R>><<<l_closest_.grid, SCAN_THREADS, l_closest_.smem, stream_>>>(
-                    csrc, &ctr_->count[l], cull_general_, frame_general_, sc_.n_cull, cq_, ctr_, chunk_objs_, resident_ | ((cta_pass_ & 2) ? 2 : 0));
+                SpawnSource<R> spws{levels_[l]};
+                if (resident_) k_cull<R, CULL_GENERAL, SpawnSource<R>, true><<<l_closest_.grid, CULL_THREADS, l_closest_.smem, stream_>>>(
+                    spws, &ctr_->count[l], cull_general_, frame_general_, sc_.n_cull, lists_spawn_, cq_, ctr_);
+                else k_cull<R, CULL_GENERAL, SpawnSource<R>, false><<<l_closest_.grid, CULL_THREADS, 0, stream_>>>(
+                    spws, &ctr_->count[l], cull_general_, frame_general_, sc_.n_cull, lists_spawn_, cq_, ctr_);
                 MARK(KC_EXACT);
                 int erc = exact_closest(l, counting);
                 if (erc) return erc;
@@ -3069,18 +3082,28 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
                 cudaStream_t ss = two_streams ? shadow_stream_[sk] : stream_;
                 const CandQueue& cqs = two_streams ? cq_shadow_[sk] : cq_;
                 int* const s_hist = sort_hist_sh_[sk]; int* const s_cursor = sort_cursor_sh_[sk];
-                ShadowSource<R> ssrc{sq_, li * sq_.per_light};
+                ShadowSource<R> ssrc{sq_, li * sq_.per_light, sort_shadows_ ? sq_.perm : nullptr, sort_shift_, sort_nb_};
                 CU_TRY(cudaMemsetAsync(cqs.count, 0, 2 * sizeof(int), ss));
-                MARK(KC_SORT);
-                k_sort_hist<R><<<sms_ * 4, SORT_THREADS, 0, ss>>>(sq_, li, sort_shift_, sort_nb_, s_hist, ctr_);
-                k_sort_scan<<<1, 1024, 0, ss>>>(sort_nb_, s_hist, s_cursor);
-                k_sort_scatter<R><<<sms_ * 4, SORT_THREADS, 0, ss>>>(sq_, li, sort_shift_, sort_nb_, s_cursor);
-                totals_.launches += 3;
+                if (sort_shadows_) {       // optional: the shadow rays of neighbouring pixels mostly share a class already
+                    MARK(KC_SORT);
+                    k_sort_hist<R><<<sms_ * 4, SORT_THREADS, 0, ss>>>(sq_, li, sort_shift_, sort_nb_, s_hist);
+                    k_sort_scan<<<1, 1024, 0, ss>>>(sort_nb_, s_hist, s_cursor);
+                    k_sort_scatter<R><<<sms_ * 4, SORT_THREADS, 0, ss>>>(sq_, li, sort_shift_, sort_nb_, s_cursor);
+                    totals_.launches += 3;
+                }
                 MARK(KC_SHADOW);
-                if (axis) k_cull<R, CULL_AXIS, RPT_FAMILY, ShadowSource<R>><<<l_shadow_axis_.grid, SCAN_THREADS, l_shadow_axis_.smem, ss>>>(
-                    ssrc, &shadow_counts_[li], cull_light_[li], frame_light_[li], sc_.n_cull, cqs, ctr_, chunk_objs_, resident_ | ((cta_pass_ & 4) ? 2 : 0));
-                else k_cull<R, CULL_PIVOT, RPT_FAMILY, ShadowSource<R>><<<l_shadow_pivot_.grid, SCAN_THREADS, l_shadow_pivot_.smem, ss>>>(
-                    ssrc, &shadow_counts_[li], cull_light_[li], frame_light_[li], sc_.n_cull, cqs, ctr_, chunk_objs_, resident_ | ((cta_pass_ & 4) ? 2 : 0));
+                const BinLists& bls = lists_light_[li];
+                if (axis) {
+                    if (resident_) k_cull<R, CULL_AXIS, ShadowSource<R>, true><<<l_shadow_axis_.grid, CULL_THREADS, l_shadow_axis_.smem, ss>>>(
+                        ssrc, &shadow_counts_[li], cull_light_[li], frame_light_[li], sc_.n_cull, bls, cqs, ctr_);
+                    else k_cull<R, CULL_AXIS, ShadowSource<R>, false><<<l_shadow_axis_.grid, CULL_THREADS, 0, ss>>>(
+                        ssrc, &shadow_counts_[li], cull_light_[li], frame_light_[li], sc_.n_cull, bls, cqs, ctr_);
+                } else {
+                    if (resident_) k_cull<R, CULL_PIVOT, ShadowSource<R>, true><<<l_shadow_pivot_.grid, CULL_THREADS, l_shadow_pivot_.smem, ss>>>(
+                        ssrc, &shadow_counts_[li], cull_light_[li], frame_light_[li], sc_.n_cull, bls, cqs, ctr_);
+                    else k_cull<R, CULL_PIVOT, ShadowSource<R>, false><<<l_shadow_pivot_.grid, CULL_THREADS, 0, ss>>>(
+                        ssrc, &shadow_counts_[li], cull_light_[li], frame_light_[li], sc_.n_cull, bls, cqs, ctr_);
+                }
                 MARK(KC_EXACT);
                 const int sbase = li * sq_.per_light;
                 if (counting) {
