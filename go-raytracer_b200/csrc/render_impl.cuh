@@ -205,12 +205,28 @@ template <typename R> __device__ __forceinline__ void to_object(const R* m, cons
     o.dz = m[8] * w.dx + m[9] * w.dy + m[10] * w.dz;
 }
 
+__device__ __forceinline__ float fma_(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+__device__ __forceinline__ double fma_(double a, double b, double c) { return __fma_rn(a, b, c); }
+
 // ------------------------------------------------------------------ first-hit rule per primitive
 // Each returns true and (t, face) exactly as <Type>.Intersect would.
 
 template <typename R> __device__ __forceinline__ bool hit_sphere(const Ray<R>& r, R& t, int& face) {   // :78-103
     R a = r.dx * r.dx + r.dy * r.dy + r.dz * r.dz;
     R hb = r.ox * r.dx + r.oy * r.dy + r.oz * r.dz;
+    if (!GMLRT_PARITY_TU) {
+        // Throughput mode: the same roots through the point of closest approach l = o + tc d:  disc = a (1 - |l|^2),
+        // t0 = tc - sqrt((1 - |l|^2) / a).  The textbook hb^2 - a c cancels two numbers of the size |o|^2 (an origin tens of
+        // radii away in object space), which in float32 moves silhouettes - and, worse, the hit point and with it the normal
+        // of a mirror sphere - by 1e-4 of the radius; here every quantity after l is of order one.
+        const R tc = -hb / a;
+        const R lx = fma_(tc, r.dx, r.ox), ly = fma_(tc, r.dy, r.oy), lz = fma_(tc, r.dz, r.oz);
+        const R pp = lx * lx + ly * ly + lz * lz;
+        if (!(pp <= R(1))) return false;
+        const R t0 = tc - gm<R>::sqrt((R(1) - pp) / a);
+        if (t0 > R(0)) { t = t0; face = 0; return true; }
+        return false;
+    }
     R c = r.ox * r.ox + r.oy * r.oy + r.oz * r.oz - R(1);
     R disc = hb * hb - a * c;
     if (disc < R(0)) return false;
@@ -563,13 +579,12 @@ __device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem
 //   exact  the survivors go to a candidate queue in HBM as (ray, object) pairs and a second kernel runs the
 //          reference's own test (<Type>.Intersect, or the CSG span lists) on them, one thread per candidate.
 constexpr int CULL_THREADS = 256;
+constexpr int CULL_STAGE = 256;               // candidates a warp stages in shared memory between two reservations on the queue
 constexpr int GROUP = 64;                   // list entries per window: one 64-bit survivor mask per ray, kept in two registers
 enum CullFamily { CULL_GENERAL = 0, CULL_PIVOT = 1, CULL_AXIS = 2 };
 // class of a shadow ray: the sort region of the shaded point, merged by `shift`; the last bin collects invalid keys
 __device__ __forceinline__ int sort_bin(int key, int shift, int nb) { return key < 0 ? nb - 1 : min(key >> shift, nb - 2); }
 
-__device__ __forceinline__ float fma_(float a, float b, float c) { return __fmaf_rn(a, b, c); }
-__device__ __forceinline__ double fma_(double a, double b, double c) { return __fma_rn(a, b, c); }
 
 template <typename R> struct CullMargin;
 template <> struct CullMargin<float> { static constexpr double rel = 7.62939453125e-6;  /* 2^-17 */ static constexpr double radius = 9.765625e-4; /* 2^-10 */ };
@@ -1103,6 +1118,31 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
     }
     const unsigned char* tab = TABLE_SMEM ? smem_raw : reinterpret_cast<const unsigned char*>(table);
     unsigned long long fine = 0;
+    __shared__ int2 s_stage[CULL_THREADS / 32][CULL_STAGE];
+    int2* const stage = s_stage[tid >> 5];
+    int staged = 0;                                            // entries in this warp's stage (uniform across the warp)
+    // reserve `cnt` queue entries for the warp (every lane calls it): the first one, or all ones when the queue is full.
+    // The counter is unsigned and stops growing once the queue is full: a lattice seen along an axis can leave dozens of
+    // survivors per ray, and a signed counter that kept counting past 2^31 would turn the index negative and the stores
+    // into out-of-bounds writes instead of the overflow-and-retrace path.
+    auto reserve = [&](int cnt) -> unsigned {
+        unsigned at = 0;
+        if (lane == 0) {
+            if (*reinterpret_cast<volatile unsigned*>(cq.count) >= (unsigned)cq.cap) at = 0xffffffffu;
+            else at = atomicAdd(reinterpret_cast<unsigned*>(cq.count), (unsigned)cnt);
+            if (at != 0xffffffffu && at + (unsigned)cnt > (unsigned)cq.cap) at = 0xffffffffu;
+            if (at == 0xffffffffu) ctr->overflow = 1;              // queue full: the host retries with smaller tiles
+        }
+        return __shfl_sync(0xffffffffu, at, 0);
+    };
+    auto flush = [&]() {
+        if (staged == 0) return;
+        const unsigned at = reserve(staged);
+        if (at != 0xffffffffu)
+            for (int k = lane; k < staged; k += 32) { const int2 e = stage[k]; cq.ray[at + k] = e.x; cq.obj[at + k] = e.y; }
+        staged = 0;
+        __syncwarp();
+    };
     for (int blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
         const int i = blk * CULL_THREADS + tid;
         const bool active = i < n;
@@ -1123,39 +1163,53 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
             uint32_t lo, hi;
             cull_list_window<R, FAMILY>(tab, bl.entry + first + k0, cnt, cr, lo, hi);
             fine += (unsigned long long)cnt;
-            // warp-aggregated append of the set bits: inclusive scan of the lanes' counts, one atomic for the warp
+            // Survivors are staged per warp in shared memory and flushed to the queue STAGE at a time: one atomic on the
+            // queue's counter per flush.  (One atomic per warp and window - a million and more per launch, all on one
+            // address - serialised in L2 and was ALL of this kernel's time when first measured.)
             const int mine = __popc(lo) + __popc(hi);
             if (!__any_sync(0xffffffffu, mine != 0)) continue;
             int incl = mine;
 #pragma unroll
             for (int off = 1; off < 32; off <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, off); if (lane >= off) incl += v; }
             const int total = __shfl_sync(0xffffffffu, incl, 31);
-            // The counter is unsigned and stops growing once the queue is full: a lattice seen along an axis can leave
-            // dozens of survivors per ray, and a signed counter that kept counting past 2^31 would turn `at` negative
-            // and the stores below into out-of-bounds writes instead of the overflow-and-retrace path.
-            unsigned at = 0;
-            if (lane == 31) {
-                if (*reinterpret_cast<volatile unsigned*>(cq.count) >= (unsigned)cq.cap) at = 0xffffffffu;
-                else at = atomicAdd(reinterpret_cast<unsigned*>(cq.count), (unsigned)total);
-            }
-            at = __shfl_sync(0xffffffffu, at, 31);
-            if (at == 0xffffffffu || at + (unsigned)total > (unsigned)cq.cap) { if (lane == 31) ctr->overflow = 1; continue; }     // queue full: the host retries with smaller tiles
-            at += (unsigned)(incl - mine);
+            if (staged + total > CULL_STAGE) { flush(); }
             const uint32_t* ent = bl.entry + first + k0;
-            uint32_t m = lo;
-            while (m) {
-                const int j = __clz(m);
-                m &= ~(0x80000000u >> j);
-                cq.ray[at] = rid; cq.obj[at] = (int)(ent[j] / (uint32_t)(4 * sizeof(R))); at++;
-            }
-            m = hi;
-            while (m) {
-                const int j = __clz(m);
-                m &= ~(0x80000000u >> j);
-                cq.ray[at] = rid; cq.obj[at] = (int)(ent[32 + j] / (uint32_t)(4 * sizeof(R))); at++;
+            if (total <= CULL_STAGE) {
+                int at = staged + incl - mine;
+                uint32_t m = lo;
+                while (m) {
+                    const int j = __clz(m);
+                    m &= ~(0x80000000u >> j);
+                    stage[at++] = make_int2(rid, (int)(ent[j] / (uint32_t)(4 * sizeof(R))));
+                }
+                m = hi;
+                while (m) {
+                    const int j = __clz(m);
+                    m &= ~(0x80000000u >> j);
+                    stage[at++] = make_int2(rid, (int)(ent[32 + j] / (uint32_t)(4 * sizeof(R))));
+                }
+                staged += total;
+                __syncwarp();
+            } else {                                           // more survivors in one window than the stage holds: straight to the queue
+                unsigned at = reserve(total);
+                if (at == 0xffffffffu) continue;
+                at += (unsigned)(incl - mine);
+                uint32_t m = lo;
+                while (m) {
+                    const int j = __clz(m);
+                    m &= ~(0x80000000u >> j);
+                    cq.ray[at] = rid; cq.obj[at] = (int)(ent[j] / (uint32_t)(4 * sizeof(R))); at++;
+                }
+                m = hi;
+                while (m) {
+                    const int j = __clz(m);
+                    m &= ~(0x80000000u >> j);
+                    cq.ray[at] = rid; cq.obj[at] = (int)(ent[32 + j] / (uint32_t)(4 * sizeof(R))); at++;
+                }
             }
         }
     }
+    flush();
     fine = warp_sum_u64(fine);
     if (lane == 0 && fine) atomicAdd(&ctr->cull_tests[FAMILY], fine);
 }
@@ -1781,15 +1835,51 @@ __global__ void __launch_bounds__(256) k_gen(DevScene<R> sc, Level<R> lv, Counte
     store_ray(lv.ray, i, (R)o[0], (R)o[1], (R)o[2], (R)d[0], (R)d[1], (R)d[2], 0, 0);
 }
 
-// ------------------------------------------------------------------ shade (traceRay :498-556 minus the recursion)
 // rec slots
 enum { REC_P = 0, REC_N = 3, REC_COL = 6, REC_REFL = 9, REC_TRANSP = 10, REC_KR = 11, REC_KD = 12, REC_KS = 13, REC_NEXP = 14, REC_INLEN = 15 };
+
+// ------------------------------------------------------------------ camera rays: hit points in double (throughput mode)
+// A float32 frame differs from the float64 reference mostly where a tiny error of the FIRST hit is amplified: the
+// normal of a small mirror sphere turns an error of 1e-5 radii into a reflected ray that misses a silhouette the
+// reference hits; a ground plane seen at a grazing angle turns an ulp of T into a texture cell.  The unrounded
+// double-precision camera ray is one PCG jump away (camera_ray64), so for the winning object of every camera ray the
+// reference's own test is run once more in double and the object-space hit point - of order one for a sphere, so
+// float32 holds it to 1e-7 - is left in the P slots of the shading record, where k_shade picks it up instead of
+// forming o + d T from numbers tens of radii long.  About 100 double operations per hit, a few % of a frame.
+template <typename R, int PICKLESS>
+__global__ void __launch_bounds__(256) k_primary_points(const __grid_constant__ DevScene<R> sc, const __grid_constant__ Level<R> lv,
+                                                        const Counters* ctr, const __grid_constant__ CamSrc cam) {
+    const int n = ctr->count[0];
+    const size_t cap = (size_t)lv.cap;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        int h; R t_pre;
+        level_hit<R, PICKLESS>(lv, i, h, t_pre);
+        if (h < 0) continue;
+        const int leaf = h & HIT_LEAF_MASK, face = (h >> 28) & 7;
+        double td = (double)(PICKLESS != 0 ? t_pre : lv.t[i]);
+        double o64[3], d64[3];
+        camera_ray64(sc, cam, i, o64, d64);
+        Ray<double> w = {o64[0], o64[1], o64[2], d64[0], d64[1], d64[2]}, o;
+        to_object(sc.w2o64 + (size_t)leaf * 12, w, o);
+        if (leaf < sc.n_leaves) {                          // a plain object: its own test again, in double (a CSG member keeps the T of the span evaluation, itself double)
+            double t2 = 0.0; int f2 = 0;
+            if (hit_any_kind<double>(sc.kind[leaf], o, t2, f2) && f2 == face) td = t2;
+        }
+        lv.rec[(REC_P + 0) * cap + i] = (R)(o.ox + o.dx * td);
+        lv.rec[(REC_P + 1) * cap + i] = (R)(o.oy + o.dy * td);
+        lv.rec[(REC_P + 2) * cap + i] = (R)(o.oz + o.dz * td);
+    }
+}
+
+// ------------------------------------------------------------------ shade (traceRay :498-556 minus the recursion)
+// rec slots
 
 template <typename R, int PICKLESS>
 __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R> lv, Level<R> next, ShadowQueue<R> sq,
                                                          unsigned char* occl, Counters* ctr, int level, int spawn,
-                                                         int32_t* ids, int y0, RowMap map, R* spawn_to) {
+                                                         int32_t* ids, int y0, RowMap map, R* spawn_to, int points) {
     const int n = ctr->count[level];
+    const bool use_points = points != 0;                   // level 0, throughput mode: object-space hit points precomputed in double
     __shared__ int s_append[2][SHADE_QUEUES][SHADE_WARPS];
     int append_phase = 0;
     // The hit code of the next iteration is fetched one iteration ahead, so that an iteration's dependent chain starts
@@ -1827,9 +1917,22 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
         const R* Mw = sc.w2o + (size_t)leaf * 12;
         Ray<R> o;
         to_object(Mw, w, o);
-        const V3<R> p = mk(o.ox + o.dx * t, o.oy + o.dy * t, o.oz + o.dz * t);       // Hit.PointObj
-        obj_x = p.x; obj_z = p.z;
         const int kind = sc.kind[leaf];
+        V3<R> p = mk(o.ox + o.dx * t, o.oy + o.dy * t, o.oz + o.dz * t);             // Hit.PointObj
+        if (!GMLRT_PARITY_TU) {
+            if (use_points) p = mk(lv.rec[(REC_P + 0) * cap + i], lv.rec[(REC_P + 1) * cap + i], lv.rec[(REC_P + 2) * cap + i]);   // camera rays: k_primary_points
+            else if (kind == K_SPHERE) {
+                // o + d t adds two vectors tens of radii long to get one of length one (the normal of a sphere IS this point,
+                // :119): go through the point of closest approach instead, where every term is of order one (see hit_sphere)
+                const R a = o.dx * o.dx + o.dy * o.dy + o.dz * o.dz, hb = o.ox * o.dx + o.oy * o.dy + o.oz * o.dz;
+                const R tc = -hb / a;
+                const R lx = fma_(tc, o.dx, o.ox), ly = fma_(tc, o.dy, o.oy), lz = fma_(tc, o.dz, o.oz);
+                const R pp = lx * lx + ly * ly + lz * lz;
+                const R sr = gm<R>::sqrt(gomath::max0(R(1) - pp) / a);
+                p = mk(fma_(-sr, o.dx, lx), fma_(-sr, o.dy, ly), fma_(-sr, o.dz, lz));
+            }
+        }
+        obj_x = p.x; obj_z = p.z;
         const DevSurface<R>& sf = sc.surfaces[sc.surface[leaf]];
         R u = R(0), v = R(0);
         bool ok = true;
@@ -1840,9 +1943,15 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
                 if (!GMLRT_PARITY_TU) py = fminf(fmaxf((float)py, -1.0f), 1.0f);      // float rounding can leave |y| = 1 + ulp at the poles: clamp instead of the reference's error
                 if (gm<R>::abs(py) > R(1)) ok = false;                                // raytracer.go:142-144
                 v = (py + R(1)) / R(2);
-                R ca = p.z / gm<R>::sqrt(R(1) - py * py);
-                if (!GMLRT_PARITY_TU) ca = fminf(fmaxf((float)ca, -1.0f), 1.0f);   // float rounding can leave |ca| = 1 + ulp on the x = 0 meridian
-                u = gm<R>::acos(ca) / (R(2) * R(GM_PI));
+                if (GMLRT_PARITY_TU) {
+                    const R ca = p.z / gm<R>::sqrt(R(1) - py * py);
+                    u = gm<R>::acos(ca) / (R(2) * R(GM_PI));
+                } else {
+                    // acos(z / sqrt(1 - y^2)) = atan2(|x|, z) on the unit sphere.  acos is infinitely steep at +-1: in float32 it
+                    // turns an ulp of its argument into 5e-5 of u on the x = 0 meridians - where u = 0 / 0.5 is exactly where
+                    // textures put their seams (frac of a multiple of u).  atan2 is well conditioned everywhere.
+                    u = gm<R>::atan2(gm<R>::abs(p.x), p.z) / (R(2) * R(GM_PI));
+                }
             }
             N = p;                                                                   // :119 (sic: object-space point)
         } else if (kind == K_PLANE) {                                                // :182-205
@@ -2320,6 +2429,7 @@ private:
     BinLists lists_camera_{}, lists_spawn_{}; std::vector<BinLists> lists_light_;
     std::vector<double> region_bound_;                           // host: [n_regions][4] sphere holding every point of the region (inf = unbounded)
     unsigned long long* list_tests_dev_ = nullptr; unsigned long long list_tests_ = 0;
+    bool primary_points_ = false;                                // throughput mode: k_primary_points before the level-0 k_shade (GMLRT_PRIMARY_POINTS)
     bool sort_shadows_ = false;                                  // GMLRT_SORT_SHADOWS: order the shadow rays of a light by class before the cull
     int build_lists(const HostScene& S, std::string& err);
     CandQueue cq_{}; int cand_per_ray_ = 4, tile_shrink_ = 0; unsigned long long scene_sig_ = ~0ull, planned_sig_ = ~0ull - 1; int planned_rows_full_ = 0;
@@ -2625,6 +2735,7 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     sort_nb_ = std::min(n_regions_ + 1, SORT_BINS_MAX); sort_shift_ = 0;        // class of a shadow ray: the region of the shaded point
     while (((n_regions_ - 1) >> sort_shift_) + 2 > sort_nb_) sort_shift_++;
     sort_shadows_ = env_size("GMLRT_SORT_SHADOWS", 0) != 0;
+    primary_points_ = kRobustPrimary && env_size("GMLRT_PRIMARY_POINTS", 1) != 0;
     if ((rc = build_lists(S, err))) return rc;
     {
         void* p = nullptr;
@@ -3065,11 +3176,17 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             const bool spawn = l + 1 < depth_eff_;
             if (two_streams && l > 0) for (int k = 0; k < nss; k++) CU_TRY(cudaStreamWaitEvent(stream_, ev_shadow_[k][l - 1], 0));     // k_shade refills the shadow queue
             MARK(KC_SHADE);
+            if (primary_points_ && l == 0) {
+                if (sc_.pickless == 1) k_primary_points<R, sizeof(R) == 4 ? 1 : 0><<<wide, 256, 0, stream_>>>(sc_, levels_[0], ctr_, cam);
+                else if (sc_.pickless) k_primary_points<R, sizeof(R) == 4 ? 2 : 0><<<wide, 256, 0, stream_>>>(sc_, levels_[0], ctr_, cam);
+                else k_primary_points<R, 0><<<wide, 256, 0, stream_>>>(sc_, levels_[0], ctr_, cam);
+                totals_.launches++;
+            }
             auto shade = sc_.pickless == 1 ? k_shade<R, sizeof(R) == 4 ? 1 : 0> : sc_.pickless ? k_shade<R, sizeof(R) == 4 ? 2 : 0> : k_shade<R, 0>;
             shade<<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
                 sc_, levels_[l], spawn ? levels_[l + 1] : levels_[l], sq_, occl_[l], ctr_, l, spawn ? 1 : 0,
                 (counting && l == 0) ? ids_ : nullptr, ty, map,
-                spawn ? (sort_spawned_ ? spawn_stage_ : levels_[l + 1].ray) : nullptr);
+                spawn ? (sort_spawned_ ? spawn_stage_ : levels_[l + 1].ray) : nullptr, (primary_points_ && l == 0) ? 1 : 0);
             totals_.launches += 2;
             // shadow queries of this level: on the shadow stream, overlapping the next level's closest-hit pipeline
             if (two_streams) {
