@@ -111,6 +111,15 @@ class ClockSampler(threading.Thread):
                 "samples": len(self.rows), "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
+LEAVES = {"spheres1024": "1024 leaves", "spheres1024p": "1024 leaves", "csg256": "256 leaves in 64 CSG objects + a ground plane",
+          "proctex": "64 spheres + a ground plane, closure surfaces", "mixed4096": "4096 leaves"}
+
+
+def workload_name(args):
+    """The same string on both arms (the driver compares them)."""
+    return f"{args.config} {args.width}x{args.height} depth {args.depth}, 4 spp, {LEAVES.get(args.config, '')}"
+
+
 def central_crop(w, h, cw, ch):
     x0, y0 = (w - cw) // 2, (h - ch) // 2
     y0 -= y0 % 20                      # keep whole PCG work items (20-row batches)
@@ -137,7 +146,7 @@ def run_reference(args, blob):
         "impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"{args.config} {args.width}x{args.height} depth {args.depth}, 4 spp"},
+        "config": {"workload": workload_name(args)},
         "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": "port",
                          "sample": f"central {crop[2]-crop[0]}x{crop[3]-crop[1]} px crop of the frame, all 4 spp, per step"},
         "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -159,8 +168,9 @@ def main():
     ap.add_argument("--height", type=int, default=2160)
     ap.add_argument("--depth", type=int, default=None)
     ap.add_argument("--precision", default="f32", choices=["f32", "f64"])
-    ap.add_argument("--ref-crop", type=int, nargs=2, default=[240, 140])
-    ap.add_argument("--cpu-crop", type=int, nargs=2, default=[1280, 720])
+    ap.add_argument("--ref-crop", type=int, nargs=2, default=None, help="CPU timing sample (both --impl reference and cpu_baseline): central crop, default 640x360 (320x180 for mixed4096)")
+    ap.add_argument("--parity-crop", type=int, nargs=2, default=None, help="window of the timed frame the oracle re-renders for the float32 parity check, default 1280x720 (640x360 for mixed4096)")
+    ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--parts", type=int, default=1, help="diagnostic (1 GPU): render only part 0 of PARTS row-band parts, i.e. one rank's share of an N-GPU frame")
     ap.add_argument("--verify", action="store_true", help="N > 1: rank 0 also renders the whole frame alone and compares it with the gathered one")
@@ -173,6 +183,10 @@ def main():
     if args.config == "mixed4096" and "--width" not in sys.argv:
         args.width, args.height = 7680, 4320
     args.warmup = max(args.warmup, 0)
+    if args.ref_crop is None:
+        args.ref_crop = [320, 180] if args.config == "mixed4096" else [640, 360]
+    if args.parity_crop is None:
+        args.parity_crop = [640, 360] if args.config == "mixed4096" else [1280, 720]
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -292,49 +306,73 @@ def main():
     serial_ms_step = sum(class_ms) / args.steps if world == 1 else None
     value = rays_frame / (ms_step * 1e-3) / 1e6
 
-    # end to end through the public C ABI: host blob in, host raster out, every step
-    host = np.empty((H, W, 4), dtype=np.uint8)
-    pinned = torch.empty((H, W, 4), dtype=torch.uint8, pin_memory=True) if rank == 0 else None
+    # end to end through the public C ABI: host blob in, host raster out, every step.  Twice: into a page-locked raster
+    # from gmlrt_alloc_host (what INTEGRATION.md's bridge hands out as image.RGBA.Pix) and into an ordinary pageable
+    # numpy array (what an unmodified caller of image.NewRGBA has, raytracer.go:590; gmlrt_download stages it in chunks).
+    host_frame = cuda.HostFrame(W, H) if rank == 0 else None
+    pageable = np.empty((H, W, 4), dtype=np.uint8) if rank == 0 else None
+    pinned_t = torch.from_numpy(host_frame.array) if rank == 0 else None
 
-    phase_ms = {"upload": 0.0, "trace": 0.0, "download": 0.0}
-    upload_each = []
+    def run_e2e(dest_pageable):
+        phase_ms = {"upload": 0.0, "trace": 0.0, "download": 0.0}
+        upload_each = []
 
-    def e2e_step():
-        ta = time.perf_counter()
-        ctx.upload(blob)                                    # H2D of this step's input
-        tb = time.perf_counter()
-        step()
-        if use_ipc:
-            dist.barrier()                                  # every producer's stores have landed in rank 0's frame
-        tc = time.perf_counter()
-        phase_ms["upload"] += (tb - ta) * 1e3
-        upload_each.append((tb - ta) * 1e3)
-        phase_ms["trace"] += (tc - tb) * 1e3
-        if rank == 0:                                       # D2H of the step's result
-            if dist is None:
-                ctx.download(pinned.numpy())
-            else:
-                with torch.cuda.stream(ext):
-                    pinned.copy_(gathered[0], non_blocking=True)
-                ext.synchronize()
-        phase_ms["download"] += (time.perf_counter() - tc) * 1e3
-    for _ in range(2):
-        e2e_step()
-    barrier()
-    for k in phase_ms:
-        phase_ms[k] = 0.0
-    upload_each.clear()
-    t0 = time.perf_counter()
-    e2e_steps = max(3, min(args.steps, 10))
-    for _ in range(e2e_steps):
-        e2e_step()
-    barrier()
-    e2e_ms = (time.perf_counter() - t0) / e2e_steps * 1e3
-    if dist is not None:
-        tt = torch.tensor([e2e_ms], dtype=torch.float64, device=f"cuda:{local_rank}")
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        e2e_ms = float(tt[0])
+        def e2e_step():
+            ta = time.perf_counter()
+            ctx.upload(blob)                                    # H2D of this step's input
+            tb = time.perf_counter()
+            step()
+            if use_ipc:
+                dist.barrier()                                  # every producer's stores have landed in rank 0's frame
+            tc = time.perf_counter()
+            phase_ms["upload"] += (tb - ta) * 1e3
+            upload_each.append((tb - ta) * 1e3)
+            phase_ms["trace"] += (tc - tb) * 1e3
+            if rank == 0:                                       # D2H of the step's result
+                if dist is None or use_ipc:
+                    ctx.download(pageable if dest_pageable else host_frame.array)
+                else:
+                    with torch.cuda.stream(ext):
+                        pinned_t.copy_(gathered[0], non_blocking=True)
+                    ext.synchronize()
+                    if dest_pageable:
+                        pageable[...] = host_frame.array
+            phase_ms["download"] += (time.perf_counter() - tc) * 1e3
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        for k in phase_ms:
+            phase_ms[k] = 0.0
+        upload_each.clear()
+        t0 = time.perf_counter()
+        n_steps = max(3, min(args.steps, 10))
+        for _ in range(n_steps):
+            e2e_step()
+        barrier()
+        ms = (time.perf_counter() - t0) / n_steps * 1e3
+        if dist is not None:
+            tt = torch.tensor([ms], dtype=torch.float64, device=f"cuda:{local_rank}")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            ms = float(tt[0])
+        return ms, {k: v / n_steps for k, v in phase_ms.items()}, [round(x, 3) for x in upload_each]
+
+    e2e_pg_ms, e2e_pg_phase, _ = run_e2e(True)
+    e2e_ms, e2e_phase, upload_each = run_e2e(False)
     e2e_value = rays_frame / (e2e_ms * 1e-3) / 1e6
+
+    # N > 1: the timed loop above lets every rank run ahead (value = the slowest rank's share); the same K steps again
+    # with a cross-rank barrier after every frame = the latency of COMPLETED frames
+    frame_ms_barrier = None
+    if dist is not None:
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            step()
+            dist.barrier()
+        torch.cuda.synchronize()
+        tt = torch.tensor([(time.perf_counter() - t0) / args.steps * 1e3], dtype=torch.float64, device=f"cuda:{local_rank}")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        frame_ms_barrier = float(tt[0])
 
     gather_check = None
     if args.verify and world > 1:       # the gathered frame of the last end-to-end step against the same frame rendered by one device alone
@@ -343,7 +381,7 @@ def main():
             solo = cuda.Context((local_rank,), prec)
             whole, _ = solo.render(blob)
             solo.close()
-            got = pinned.numpy()
+            got = host_frame.array
             same = (got == whole).all(axis=2)
             gather_check = {"pixels_equal": float(same.mean()), "max_abs_diff": int(np.abs(got.astype(np.int16) - whole.astype(np.int16)).max())}
         barrier()
@@ -400,7 +438,7 @@ def main():
                                                                             "unit": "TFLOP/s", "frac": tf / fp32_peak if fp32_peak else None}
     scan_ms = sum(class_ms[k] for k in (1, 2, 3, 7, 8))
     # ---- the dominant single kernel: classes 0, 1, 2, 4, 5 are one kernel each (3, 7, 8 are groups of smaller ones; 6 is gone: fused into k_resolve) ----
-    kernel_of = {0: "k_gen", 1: "k_cull<PIVOT, ClosestSource> (camera rays)", 2: "k_cull<GENERAL, ClosestSource> (reflection / refraction rays)",
+    kernel_of = {0: "k_gen", 1: "k_cull<PIVOT, CameraSource> (camera rays)", 2: "k_cull<GENERAL, SpawnSource> (reflection / refraction rays)",
                  4: "k_shade", 5: "k_resolve"}
     traffic = None
     if world > 1:             # per-kernel events are an N = 1 tool
@@ -416,7 +454,7 @@ def main():
             roof = {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak, "peak_kind": hbm_peak_kind,
                     "kernel_bytes_per_launch": per_launch}
         else:
-            fl = (15.0 * float(counts[11])) if dom == 2 else 7.0 * float(P) * 0 + 7.0 * float(counts[12]) * (class_ms[1] / max(class_ms[1] + class_ms[3], 1e-9))
+            fl = (15.0 * float(counts[11])) if dom == 2 else 7.0 * float(counts[12]) * (class_ms[1] / max(class_ms[1] + class_ms[3], 1e-9))
             ach = fl * args.steps / (class_ms[dom] * 1e-3) / 1e12
             roof = {"bound": "fp32", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach / fp32_peak if fp32_peak else None,
                     "peak_kind": "measured: FFMA-chain microbenchmark on this GPU (gmlrt_measure_fp32_tflops)" if fp32_measured > 0 else "derived",
@@ -449,7 +487,7 @@ def main():
         "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_step, "frame_ms": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": args.precision, "data": "synthetic",
-        "config": {"workload": f"{args.config} {W}x{H} depth {args.depth}, 4 spp, {cst.n_leaves} leaves" +
+        "config": {"workload": workload_name(args) +
                                (f" - DIAGNOSTIC: part 0 of {args.parts} only" if world == 1 and args.parts > 1 else ""), "precision": args.precision,
                    "l2": "inputs larger than L2: the per-level ray queues of one frame are GBs, no flush needed",
                    "parallelism": (f"8-row bands dealt round-robin over {world} GPU(s), scene replicated, " +
@@ -460,7 +498,11 @@ def main():
         "gpu_launches": launches,
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "frame_ms": e2e_ms, "h2d_bytes_per_step": len(blob), "d2h_bytes_per_step": W * H * 4,
-                "phase_ms": {k: v / e2e_steps for k, v in phase_ms.items()}, "upload_ms_each": [round(x, 3) for x in upload_each]},
+                "destination": "page-locked raster from gmlrt_alloc_host (the bridge of INTEGRATION.md)",
+                "phase_ms": e2e_phase, "upload_ms_each": upload_each},
+        "e2e_pageable": {"value": rays_frame / (e2e_pg_ms * 1e-3) / 1e6, "unit": "Mrays/s", "frame_ms": e2e_pg_ms, "phase_ms": e2e_pg_phase,
+                         "destination": "pageable host array (image.NewRGBA of an unmodified caller): staged in 2 MB chunks by gmlrt_download",
+                         "slower_than_page_locked": e2e_pg_ms / e2e_ms - 1.0},
         "kernel_ms_per_frame": {names[k]: class_ms[k] / args.steps for k in range(9)},
         "kernel_ms_per_frame_note": "second pass of the same K steps with an event before every launch and all launches on one stream; "
                                     "their sum (serialised_frame_ms) exceeds ms_per_step by what the two-stream overlap of the timed pass hides",
@@ -469,16 +511,37 @@ def main():
     }
     if gather_check is not None:
         line["gather_check"] = gather_check
+    if frame_ms_barrier is not None:
+        line["frame_ms_with_barrier"] = frame_ms_barrier       # every frame completed on every rank before the next starts
     if world == 1 and not args.no_cpu_baseline:
         import oracle
         cores = os.cpu_count() or 8
-        crop = central_crop(W, H, args.cpu_crop[0], args.cpu_crop[1])
+        crop = central_crop(W, H, args.ref_crop[0], args.ref_crop[1])
         t0 = time.perf_counter()
         _, ost = oracle.render(blob, threads=cores, crop=crop)
         dt = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        _, ost8 = oracle.render(blob, threads=8, crop=crop)          # the reference hard-codes 8 render goroutines (raytracer.go:725)
+        dt8 = time.perf_counter() - t0
         line["cpu_baseline"] = {"value": ost.rays_total / dt / 1e6, "unit": "Mrays/s", "cores": cores, "kind": "port",
                                 "sample": f"central {crop[2]-crop[0]}x{crop[3]-crop[1]} px crop of the same frame, all 4 spp, {dt:.1f} s",
+                                "value_8_threads": ost8.rays_total / dt8 / 1e6,
+                                "sample_8_threads": f"the same crop with 8 threads = the reference's numRenderThreads (raytracer.go:725), {dt8:.1f} s",
                                 "note": "float64 C restatement of the reference (oracle/); the Go renderer is unavailable on this box"}
+    if world == 1 and not args.no_parity:
+        # The frame that was just timed, against the oracle on a window of it: per-channel tolerance and primary hit ids
+        # (north_star: <= 1/255 on >= 99.9% of pixels, zero primary hit/miss flips).  Scenes with cubes carry the
+        # reference's own float64 face-rejection chaos: compared where the reference itself is stable.
+        import oracle
+        ctx.set_counting(True)
+        ctx.trace()
+        ctx.set_counting(False)
+        got = ctx.download()
+        ids = ctx.primary_hits()
+        pc = central_crop(W, H, args.parity_crop[0], args.parity_crop[1])
+        res, _, _ = oracle.parity_window(blob, got, ids, pc, threads=os.cpu_count() or 8, chaos=args.config == "mixed4096")
+        res["precision"] = args.precision
+        line["parity"] = res
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()

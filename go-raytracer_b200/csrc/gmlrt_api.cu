@@ -32,7 +32,8 @@ struct gmlrt_ctx {
     HostScene scene;
     bool have_scene = false, have_frame = false, counting = false;
     std::string err;
-    uint8_t* pinned = nullptr; size_t pinned_bytes = 0;     // staging for pageable caller buffers
+    uint8_t* pinned = nullptr; size_t pinned_bytes = 0;     // staging for pageable caller buffers (gmlrt_download)
+    std::vector<cudaEvent_t> ev_chunk;                       // ... one event per staged chunk
     cudaEvent_t ev_a = nullptr, ev_b = nullptr;
     std::vector<cudaEvent_t> ev_done;                        // per device: its bands are in device 0's frame
     int band_rows = 0;
@@ -161,6 +162,7 @@ void gmlrt_destroy(gmlrt_ctx* c) {
     if (c->ev_a) cudaEventDestroy(c->ev_a);
     if (c->ev_b) cudaEventDestroy(c->ev_b);
     for (auto ev : c->ev_done) if (ev) cudaEventDestroy(ev);
+    for (auto ev : c->ev_chunk) cudaEventDestroy(ev);
     c->r.clear();
     delete c;
 }
@@ -467,6 +469,14 @@ int gmlrt_ssim(gmlrt_ctx* c, const uint8_t* rgba_a, const uint8_t* rgba_b, int w
     return GMLRT_OK;
 }
 
+void* gmlrt_alloc_host(size_t bytes) {
+    void* p = nullptr;
+    if (bytes == 0 || cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+
+void gmlrt_free_host(void* p) { if (p) cudaFreeHost(p); }
+
 int gmlrt_download(gmlrt_ctx* c, uint8_t* rgba, size_t rgba_bytes) {
     if (!c) return fail(nullptr, GMLRT_E_BAD_ARG, "ctx is null");
     if (!c->have_frame) return fail(c, GMLRT_E_BAD_ARG, "gmlrt_download before a successful gmlrt_trace");
@@ -474,8 +484,52 @@ int gmlrt_download(gmlrt_ctx* c, uint8_t* rgba, size_t rgba_bytes) {
     if (!rgba || rgba_bytes != need) return fail(c, GMLRT_E_BAD_ARG, "rgba buffer must be exactly 4*width*height bytes");
     IRenderer* r0 = c->r[0].get();
     API_CU(cudaSetDevice(r0->device()));
-    API_CU(cudaMemcpyAsync(rgba, r0->frame(), need, cudaMemcpyDeviceToHost, r0->stream()));
-    API_CU(cudaStreamSynchronize(r0->stream()));
+    // A page-locked destination (gmlrt_alloc_host, or anything the caller registered) takes the DMA directly.  A pageable
+    // one - image.RGBA.Pix of the reference's caller is Go heap memory (raytracer.go:590) - would make the driver stage
+    // the whole copy through its own small bounce buffer, synchronously; instead the frame is cut into chunks that are
+    // DMA'd into this context's page-locked staging buffer and copied out by a few host threads while later chunks are
+    // still in flight.
+    cudaPointerAttributes attr;
+    const bool locked = cudaPointerGetAttributes(&attr, rgba) == cudaSuccess && (attr.type == cudaMemoryTypeHost || attr.type == cudaMemoryTypeManaged);
+    cudaGetLastError();
+    if (locked) {
+        API_CU(cudaMemcpyAsync(rgba, r0->frame(), need, cudaMemcpyDeviceToHost, r0->stream()));
+        API_CU(cudaStreamSynchronize(r0->stream()));
+        return GMLRT_OK;
+    }
+    if (c->pinned_bytes < need) {
+        if (c->pinned) cudaFreeHost(c->pinned);
+        c->pinned = nullptr; c->pinned_bytes = 0;
+        API_CU(cudaHostAlloc((void**)&c->pinned, need, cudaHostAllocDefault));
+        c->pinned_bytes = need;
+    }
+    const size_t chunk = (size_t)2 << 20;
+    const int n_chunks = (int)((need + chunk - 1) / chunk);
+    while ((int)c->ev_chunk.size() < n_chunks) {
+        cudaEvent_t e;
+        API_CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        c->ev_chunk.push_back(e);
+    }
+    for (int k = 0; k < n_chunks; k++) {
+        const size_t off = (size_t)k * chunk, len = std::min(chunk, need - off);
+        API_CU(cudaMemcpyAsync(c->pinned + off, r0->frame() + off, len, cudaMemcpyDeviceToHost, r0->stream()));
+        API_CU(cudaEventRecord(c->ev_chunk[k], r0->stream()));
+    }
+    const int n_threads = std::min(4, n_chunks);
+    std::vector<cudaError_t> terr(n_threads, cudaSuccess);
+    auto drain = [&](int t) {
+        for (int k = t; k < n_chunks; k += n_threads) {
+            const cudaError_t e = cudaEventSynchronize(c->ev_chunk[k]);
+            if (e != cudaSuccess) { terr[t] = e; return; }
+            const size_t off = (size_t)k * chunk;
+            std::memcpy(rgba + off, c->pinned + off, std::min(chunk, need - off));
+        }
+    };
+    std::vector<std::thread> workers;
+    for (int t = 1; t < n_threads; t++) workers.emplace_back(drain, t);
+    drain(0);
+    for (auto& w : workers) w.join();
+    for (cudaError_t e : terr) if (e != cudaSuccess) return fail(c, GMLRT_E_CUDA, std::string("gmlrt_download: ") + cudaGetErrorString(e));
     return GMLRT_OK;
 }
 

@@ -843,8 +843,9 @@ enum BinKind { BIN_CAMERA = 0, BIN_SPAWN = 1, BIN_SHADOW_PIVOT = 2, BIN_SHADOW_A
 
 struct BinParams {
     int kind, n_bins;
-    // the objects: [n][4] centre + radius (inf = unbounded), the family's margins (Renderer::build_cull_table)
-    const double* bound; int n_objects; double radius_rel, offset_abs, rel;
+    // the objects as this family's per-ray test sees them, [n][4]: centre relative to the pivot (PIVOT), absolute (GENERAL),
+    // or (u, v, front end along the rays) (AXIS); then the radius with every margin of the per-ray test folded in (inf = unbounded)
+    const double* obj; int n_objects;
     double pivot[3];                    // PIVOT families: the eye / the light
     double e1[3], e2[3], axis[3];       // AXIS: the frame the device projects with
     // BIN_SPAWN: bin = region * n_cells + cell;  BIN_SHADOW_*: bin = region (the last bin collects invalid keys: no bound)
@@ -920,39 +921,34 @@ __device__ __forceinline__ BinBound bin_bound(const BinParams& p, int b) {
     return B;
 }
 
-// may object o be hit by ANY ray inside the bin's bound?  (conservative; mirrors the per-ray families)
+// may object o be hit by ANY ray inside the bin's bound?  (conservative; mirrors the per-ray families; no square root,
+// no division: the angle test  angle(C - origin, axis) <= theta + alpha,  sin alpha = r / |C - origin|,  is
+// dot + sin(theta) r >= cos(theta) sqrt(|C - origin|^2 - r^2), squared)
 __device__ __forceinline__ bool bin_keeps(const BinParams& p, const BinBound& B, int o) {
-    const double* ob = p.bound + (size_t)o * 4;
-    const double Rw = ob[3];
-    if (!(Rw < INFINITY)) return true;                    // unbounded (plane) or NaN: never culled
+    const double* ob = p.obj + (size_t)o * 4;
+    const double r0 = ob[3];
+    if (!(r0 < INFINITY)) return true;                    // unbounded (plane) or NaN: never culled
     if (!B.usable) return true;
-    const double Rm = Rw * (1.0 + p.radius_rel) + p.offset_abs;
     if (p.kind == BIN_SHADOW_AXIS) {
-        const double cu = ob[0] * p.e1[0] + ob[1] * p.e1[1] + ob[2] * p.e1[2], cv = ob[0] * p.e2[0] + ob[1] * p.e2[1] + ob[2] * p.e2[2];
-        const double cc = ob[0] * ob[0] + ob[1] * ob[1] + ob[2] * ob[2];
-        const double r = sqrt(Rm * Rm + 2.0 * p.rel * (cc + 1.0)) * (1.0 + 1e-9) + B.rho;
-        const double front = ob[0] * p.axis[0] + ob[1] * p.axis[1] + ob[2] * p.axis[2] + Rm + 1e-3 * (sqrt(cc) + 1.0);
-        if (front < B.rear) return false;                // wholly behind every origin along the rays' direction
-        const double du = cu - B.ax, dv = cv - B.ay;
+        if (ob[2] < B.rear) return false;                // wholly behind every origin along the rays' direction
+        const double du = ob[0] - B.ax, dv = ob[1] - B.ay, r = r0 + B.rho;
         return !(du * du + dv * dv > r * r);
     }
     const bool general = p.kind == BIN_SPAWN;
-    const double px = ob[0] - (general ? B.ox : p.pivot[0]), py = ob[1] - (general ? B.oy : p.pivot[1]), pz = ob[2] - (general ? B.oz : p.pivot[2]);
+    const double px = general ? ob[0] - B.ox : ob[0], py = general ? ob[1] - B.oy : ob[1], pz = general ? ob[2] - B.oz : ob[2];
+    const double r = general ? r0 + B.rho : r0;
     const double pp = px * px + py * py + pz * pz;
-    const double cc = general ? ob[0] * ob[0] + ob[1] * ob[1] + ob[2] * ob[2] : pp;
-    // the radius the per-ray test works with (K = |C|^2 - Rm^2 - rel (|C|^2 + 1), rounded down to R, and its own
-    // rounding allowance on the ray side), plus - GENERAL - the radius of the sphere of origins
-    double r = sqrt(Rm * Rm + 4.0 * p.rel * (cc + 1.0)) * (1.0 + 1e-9);
-    if (general) r += B.rho;
-    if (!(r * r < pp)) return true;                      // an origin (the pivot) may be inside the sphere
-    const double dist = sqrt(pp);
-    const double sa = r / dist, ca = sqrt(1.0 - sa * sa);
-    double c = (px * B.ax + py * B.ay + pz * B.az) / dist;
+    const double q = pp - r * r;
+    if (!(q > 0.0)) return true;                         // an origin (the pivot) may be inside the sphere
+    double dot = px * B.ax + py * B.ay + pz * B.az;
     if (!general) {
-        if (dist - r > B.rho) return false;              // nearer to the pivot than this an occluder must be (shadow rays stop at the light)
-        c = fabs(c);                                     // the LINE passes through the pivot: a double cone
+        const double far = B.rho + r;                    // shadow rays stop at the light: nearer to the pivot than this an occluder must be
+        if (pp > far * far) return false;
+        dot = fabs(dot);                                 // the LINE passes through the pivot: a double cone
     }
-    return !(c < B.cos_t * ca - B.sin_t * sa - 1e-9);      // angle(C - origin, axis) <= theta + alpha; GENERAL is forward only (T > 0, raytracer.go:98)
+    const double A = dot + B.sin_t * r;                  // GENERAL is forward only (T > 0, raytracer.go:98)
+    if (A < 0.0) return false;
+    return A * A * (1.0 + 1e-12) >= B.cos_t * B.cos_t * q;
 }
 
 // one warp per bin: count (FILL = false) or write (FILL = true) the bin's list
@@ -2864,38 +2860,61 @@ int Renderer<R>::build_lists(const HostScene& S, std::string& err) {
         o[0] = ax[0]; o[1] = ax[1]; o[2] = ax[2]; o[3] = std::cos(th); o[4] = std::sin(th);
     }
     const std::vector<double> reg_spawn = merged(sc_.key_shift, key_nb_ / n_cells), reg_shadow = merged(sort_shift_, sort_nb_);
-    double *d_bound, *d_cells, *d_reg_spawn, *d_reg_shadow;
-    if ((rc = to_device(bound_, &d_bound, err)) || (rc = to_device(cells, &d_cells, err)) || (rc = to_device(reg_spawn, &d_reg_spawn, err)) ||
+    double *d_cells, *d_reg_spawn, *d_reg_shadow;
+    if ((rc = to_device(cells, &d_cells, err)) || (rc = to_device(reg_spawn, &d_reg_spawn, err)) ||
         (rc = to_device(reg_shadow, &d_reg_shadow, err))) return rc;
     if (!list_tests_dev_) { CU_TRY(cudaMalloc(&list_tests_dev_, sizeof(unsigned long long))); }
     CU_TRY(cudaMemsetAsync(list_tests_dev_, 0, sizeof(unsigned long long), stream_));
 
     struct Pending { BinParams p; BinLists* out; int* count; int* first; };
     std::vector<Pending> sets;
-    auto base_params = [&](int kind, int n_bins, double offset_abs) {
+    // The objects as a family's per-ray test sees them (build_cull_table): the radius grown by the relative inflation, the
+    // absolute widening and the rounding allowance relative to the squared magnitudes (taken four times over).
+    auto base_params = [&](int kind, int n_bins, double offset_abs, const double* pivot, const CullFrame<R>* fr, int& prc) {
         BinParams p{};
-        p.kind = kind; p.n_bins = n_bins;
-        p.bound = d_bound; p.n_objects = n; p.radius_rel = CullMargin<R>::radius; p.offset_abs = offset_abs; p.rel = CullMargin<R>::rel;
+        p.kind = kind; p.n_bins = n_bins; p.n_objects = n;
+        std::vector<double> rec((size_t)std::max(n, 1) * 4, 0.0);
+        for (int d = 0; d < n; d++) {
+            const double* b = &bound_[(size_t)d * 4];
+            double* o = &rec[(size_t)d * 4];
+            if (!std::isfinite(b[3])) { o[3] = INFINITY; continue; }
+            const double Rm = b[3] * (1.0 + CullMargin<R>::radius) + offset_abs;
+            const double c[3] = {b[0] - (pivot ? pivot[0] : 0.0), b[1] - (pivot ? pivot[1] : 0.0), b[2] - (pivot ? pivot[2] : 0.0)};
+            const double cc = c[0] * c[0] + c[1] * c[1] + c[2] * c[2];
+            o[3] = std::sqrt(Rm * Rm + 4.0 * CullMargin<R>::rel * (cc + 1.0)) * (1.0 + 1e-9);
+            if (kind == BIN_SHADOW_AXIS) {
+                o[0] = b[0] * (double)fr->e1[0] + b[1] * (double)fr->e1[1] + b[2] * (double)fr->e1[2];
+                o[1] = b[0] * (double)fr->e2[0] + b[1] * (double)fr->e2[1] + b[2] * (double)fr->e2[2];
+                o[2] = b[0] * (double)fr->axis[0] + b[1] * (double)fr->axis[1] + b[2] * (double)fr->axis[2] + Rm + 1e-3 * (std::sqrt(cc) + 1.0);
+            } else { o[0] = c[0]; o[1] = c[1]; o[2] = c[2]; }
+        }
+        double* d_rec = nullptr;
+        prc = to_device(rec, &d_rec, err);
+        p.obj = d_rec;
         return p;
     };
     lists_light_.assign(S.lights.size(), BinLists{});
     {   // camera rays (the eye, raytracer.go:605-609)
         const int tx = (S.width + TILE_W - 1) / TILE_W, ty = (S.height + TILE_H - 1) / TILE_H;
-        BinParams p = base_params(BIN_CAMERA, tx * ty, 1e-5);
+        const double eye[3] = {0.0, 0.0, -1.0};
+        BinParams p = base_params(BIN_CAMERA, tx * ty, 1e-5, eye, nullptr, rc);
+        if (rc) return rc;
         p.pivot[0] = 0.0; p.pivot[1] = 0.0; p.pivot[2] = -1.0;
         p.W = S.width; p.H = S.height; p.tile_w = TILE_W; p.tile_h = TILE_H; p.tiles_x = tx;
         p.cam_su = sc_.cam_su; p.cam_sv = sc_.cam_sv; p.vw = sc_.vw; p.vh = sc_.vh;
         sets.push_back({p, &lists_camera_, nullptr, nullptr});
     }
     {   // reflection / refraction rays
-        BinParams p = base_params(BIN_SPAWN, key_nb_, 0.0);
+        BinParams p = base_params(BIN_SPAWN, key_nb_, 0.0, nullptr, nullptr, rc);
+        if (rc) return rc;
         p.region = d_reg_spawn; p.n_regions = (int)(reg_spawn.size() / 4); p.cell = d_cells; p.n_cells = n_cells;
         sets.push_back({p, &lists_spawn_, nullptr, nullptr});
     }
     for (size_t i = 0; i < S.lights.size(); i++) {
         const gmlrt_light& l = S.lights[i];
         const bool axis = l.kind == GMLRT_LIGHT_DIRECTIONAL;
-        BinParams p = base_params(axis ? BIN_SHADOW_AXIS : BIN_SHADOW_PIVOT, sort_nb_, axis ? 1e-5 : 1.5e-4);
+        BinParams p = base_params(axis ? BIN_SHADOW_AXIS : BIN_SHADOW_PIVOT, sort_nb_, axis ? 1e-5 : 1.5e-4, axis ? nullptr : l.pos, &frame_light_[i], rc);
+        if (rc) return rc;
         p.region = d_reg_shadow; p.n_regions = (int)(reg_shadow.size() / 4);
         for (int a = 0; a < 3; a++) {
             p.pivot[a] = l.pos[a];
@@ -3175,13 +3194,14 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             totals_.launches += 3;
             const bool spawn = l + 1 < depth_eff_;
             if (two_streams && l > 0) for (int k = 0; k < nss; k++) CU_TRY(cudaStreamWaitEvent(stream_, ev_shadow_[k][l - 1], 0));     // k_shade refills the shadow queue
-            MARK(KC_SHADE);
+            if (primary_points_ && l == 0) MARK(KC_PIXELS);          // (class 6: the camera rays' hit points in double)
             if (primary_points_ && l == 0) {
                 if (sc_.pickless == 1) k_primary_points<R, sizeof(R) == 4 ? 1 : 0><<<wide, 256, 0, stream_>>>(sc_, levels_[0], ctr_, cam);
                 else if (sc_.pickless) k_primary_points<R, sizeof(R) == 4 ? 2 : 0><<<wide, 256, 0, stream_>>>(sc_, levels_[0], ctr_, cam);
                 else k_primary_points<R, 0><<<wide, 256, 0, stream_>>>(sc_, levels_[0], ctr_, cam);
                 totals_.launches++;
             }
+            MARK(KC_SHADE);
             auto shade = sc_.pickless == 1 ? k_shade<R, sizeof(R) == 4 ? 1 : 0> : sc_.pickless ? k_shade<R, sizeof(R) == 4 ? 2 : 0> : k_shade<R, 0>;
             shade<<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
                 sc_, levels_[l], spawn ? levels_[l + 1] : levels_[l], sq_, occl_[l], ctr_, l, spawn ? 1 : 0,

@@ -30,7 +30,7 @@ class Stats(ctypes.Structure):
                 ("packet_tests", ctypes.c_uint64), ("cull_tests_family", ctypes.c_uint64 * 3),
                 ("rays_hit", ctypes.c_uint64), ("exact_tests_shadow", ctypes.c_uint64)]
 
-    KERNEL_CLASSES = ("gen", "cull_primary", "cull_secondary", "cull_shadow", "shade", "resolve", "pixels", "exact", "sort")
+    KERNEL_CLASSES = ("gen", "cull_primary", "cull_secondary", "cull_shadow", "shade", "resolve", "primary_points", "exact", "sort")
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -46,7 +46,7 @@ class GmlrtError(RuntimeError):
         self.code = code
 
 
-EXPORTS = ("gmlrt_ssim", "gmlrt_frame_ipc_export", "gmlrt_frame_ipc_attach", "gmlrt_measure_fp32_tflops", "gmlrt_set_profiling", "gmlrt_set_partition", "gmlrt_frame_device", "gmlrt_create", "gmlrt_render", "gmlrt_upload", "gmlrt_trace", "gmlrt_download", "gmlrt_set_counting",
+EXPORTS = ("gmlrt_alloc_host", "gmlrt_free_host", "gmlrt_ssim", "gmlrt_frame_ipc_export", "gmlrt_frame_ipc_attach", "gmlrt_measure_fp32_tflops", "gmlrt_set_profiling", "gmlrt_set_partition", "gmlrt_frame_device", "gmlrt_create", "gmlrt_render", "gmlrt_upload", "gmlrt_trace", "gmlrt_download", "gmlrt_set_counting",
            "gmlrt_primary_hits", "gmlrt_stream", "gmlrt_last_error", "gmlrt_destroy", "gmlrt_blob_version", "gmlrt_build_info")
 
 _lib = None
@@ -76,6 +76,8 @@ def load():
         L.gmlrt_ssim.restype, L.gmlrt_ssim.argtypes = i, [p, p, p, i, i, ctypes.POINTER(ctypes.c_double)]
         L.gmlrt_frame_ipc_export.restype, L.gmlrt_frame_ipc_export.argtypes = i, [p, p, sz]
         L.gmlrt_frame_ipc_attach.restype, L.gmlrt_frame_ipc_attach.argtypes = i, [p, p, sz]
+        L.gmlrt_alloc_host.restype, L.gmlrt_alloc_host.argtypes = p, [sz]
+        L.gmlrt_free_host.restype, L.gmlrt_free_host.argtypes = None, [p]
         L.gmlrt_last_error.restype, L.gmlrt_last_error.argtypes = ctypes.c_char_p, [p]
         L.gmlrt_destroy.restype, L.gmlrt_destroy.argtypes = None, [p]
         L.gmlrt_blob_version.restype, L.gmlrt_blob_version.argtypes = i, []
@@ -87,6 +89,27 @@ def load():
 def measure_fp32_tflops(device=0):
     """FFMA-chain microbenchmark on `device` (TFLOP/s): the measured FP32 roofline denominator."""
     return float(load().gmlrt_measure_fp32_tflops(int(device)))
+
+
+class HostFrame:
+    """A page-locked RGBA8 raster (gmlrt_alloc_host) viewed as a numpy array: the destination the bridge hands to
+    gmlrt_render / gmlrt_download so that the copy-back is one direct DMA."""
+
+    def __init__(self, width, height):
+        L = load()
+        self._L, self.nbytes = L, width * height * 4
+        self._p = L.gmlrt_alloc_host(self.nbytes)
+        if not self._p:
+            raise GmlrtError(-6, "gmlrt_alloc_host failed")
+        self.array = np.ctypeslib.as_array((ctypes.c_uint8 * self.nbytes).from_address(self._p)).reshape(height, width, 4)
+
+    def free(self):
+        if self._p:
+            self.array = None
+            self._L.gmlrt_free_host(self._p)
+            self._p = None
+
+    __del__ = free
 
 
 class Context:

@@ -217,6 +217,13 @@ int gmlrt_upload(gmlrt_ctx*, const void* blob, size_t blob_bytes);
 int gmlrt_trace(gmlrt_ctx*, gmlrt_stats* stats /* nullable */);
 int gmlrt_download(gmlrt_ctx*, uint8_t* rgba, size_t rgba_bytes);
 
+/* Page-locked host memory for the raster (cudaHostAlloc): a frame buffer from here takes the device-to-host DMA
+ * directly.  The reference allocates its raster with image.NewRGBA (raytracer.go:590), i.e. pageable Go heap memory;
+ * gmlrt_download / gmlrt_render accept that too and stage it through the context's own page-locked buffer in
+ * pipelined chunks (a little slower).  INTEGRATION.md's bridge wraps a gmlrt_alloc_host buffer as image.RGBA.Pix.   */
+void* gmlrt_alloc_host(size_t bytes);
+void  gmlrt_free_host(void* p);
+
 /* Multi-process sharding (one process per GPU, e.g. under torchrun): this context renders only the
  * row bands (8 rows each)  part, part + n_parts, ...  of the frame and leaves the other rows zero, so that the
  * per-process frames can be summed / gathered by the caller (NCCL), or stored into one frame (gmlrt_frame_ipc_*).  Call before

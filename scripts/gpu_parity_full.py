@@ -13,7 +13,7 @@ import oracle
 from go_raytracer_b200 import cuda, imageio, scenes
 
 sys.path.insert(0, os.path.join(ROOT, "tests"))
-from baseline_windows import WINDOWS, window_of
+from baseline_windows import CHAOS, WINDOWS, window_of
 
 only = sys.argv[1:] or list(WINDOWS)
 ctx = cuda.Context((0,), cuda.PRECISION_F32)
@@ -27,7 +27,7 @@ for name in only:
     img, st = ctx.render(blob)
     ids = ctx.primary_hits()
     crop = window_of(W, H, frac, size)
-    res, ost, bad = oracle.parity_window(blob, img, ids, crop, threads=os.cpu_count() or 8)
+    res, ost, bad = oracle.parity_window(blob, img, ids, crop, threads=os.cpu_count() or 8, chaos=name in CHAOS)
     res.update({"config": name, "size": [W, H], "lower_s": round(t1 - t0, 1), "gpu_ms": st.ms_kernels})
     print(json.dumps(res), flush=True)
     x0, y0, x1, y1 = crop

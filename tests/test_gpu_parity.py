@@ -117,9 +117,14 @@ def test_f32_tolerance_at_baseline_size(name):
     finally:
         c.close()
     assert st.rays_primary == 4 * W * H
-    res, ost, _ = oracle.parity_window(blob, img, ids, window_of(W, H, centre, size), threads=THREADS)
+    from baseline_windows import CHAOS
+    res, ost, _ = oracle.parity_window(blob, img, ids, window_of(W, H, centre, size), threads=THREADS, chaos=name in CHAOS)
     print(name, res)
-    assert res["within_1_255"] >= 0.999, res
+    if name in CHAOS:       # cubes: the reference's own face-rejection chaos is masked out, and the mask must stay small
+        assert res["stable_fraction"] >= 0.95, res
+        assert res["within_1_255_stable"] >= 0.999, res
+    else:
+        assert res["within_1_255"] >= 0.999, res
     assert res["primary_flips"] == 0, res
 
 
