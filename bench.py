@@ -535,9 +535,9 @@ def main():
         import oracle
         ctx.set_counting(True)
         ctx.trace()
-        ctx.set_counting(False)
         got = ctx.download()
         ids = ctx.primary_hits()
+        ctx.set_counting(False)
         pc = central_crop(W, H, args.parity_crop[0], args.parity_crop[1])
         res, _, _ = oracle.parity_window(blob, got, ids, pc, threads=os.cpu_count() or 8, chaos=args.config == "mixed4096")
         res["precision"] = args.precision

@@ -107,6 +107,9 @@ template <typename R> struct Level {
                   //               (bits of T) << 32 | scan index, folded by one atomicMin (fold_hit)
     R* rec;       // [NREC][cap]
     R* child;     // [6][cap] colour returned by the reflection / refraction child
+    int* hits;    // [cap] the rays of the level that hit something (k_hitlist): everything per HIT - rec, child, the occlusion flags -
+                  //       is indexed by the position in this list, so the shading kernels run on dense warps and stream
+    R* samp;      // level 0 only: [3][cap] colour of a camera ray that hit (by ray index), for the pixel pass
     int cap;
 };
 
@@ -124,6 +127,7 @@ template <typename R> struct ShadowQueue {      // one segment of `per_light` sl
 
 struct Counters {                  // device-resident, zeroed per trace
     int count[GMLRT_MAX_DEPTH + 1];     // rays per level
+    int hits[GMLRT_MAX_DEPTH + 1];      // ... of which hit something (entries of Level::hits)
     int error;
     int overflow;                       // a cull launch ran out of candidate queue: retrace with smaller tiles
     unsigned long long cull_tests[3];   // executed per-ray cull tests by family (GENERAL, PIVOT, AXIS)
@@ -982,43 +986,64 @@ __global__ void __launch_bounds__(256) k_list_build(const __grid_constant__ BinP
 
 // one window of a ray's list: entries ent[0 .. cnt) (cnt a multiple of 4, at most GROUP), 4 entries per 16-byte load;
 // test j lands in bit 31 - j of lo (j < 32) / hi (set = object survives)
-template <typename R> __device__ __forceinline__ Cull4<R> load_cull_at(const unsigned char* tab, uint32_t off);
-template <> __device__ __forceinline__ Cull4<float> load_cull_at<float>(const unsigned char* tab, uint32_t off) {
-    const float4 v = *reinterpret_cast<const float4*>(tab + off);
+// A cull record by its byte offset in the family's table.  SMEM: `tab` is the table's 32-bit shared-memory address, so the
+// load is ld.shared with the base folded in as an immediate (through a generic pointer every load paid an extra
+// add of the shared window's base); else `gtab` is the table in global memory, read through L1.
+template <typename R, bool SMEM> __device__ __forceinline__ Cull4<R> load_cull_at(uint32_t tab, const unsigned char* gtab, uint32_t off);
+template <> __device__ __forceinline__ Cull4<float> load_cull_at<float, true>(uint32_t tab, const unsigned char*, uint32_t off) {
+    Cull4<float> c;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(c.x), "=f"(c.y), "=f"(c.z), "=f"(c.k) : "r"(tab + off));
+    return c;
+}
+template <> __device__ __forceinline__ Cull4<double> load_cull_at<double, true>(uint32_t tab, const unsigned char*, uint32_t off) {
+    Cull4<double> c;
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(c.x), "=d"(c.y) : "r"(tab + off));
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(c.z), "=d"(c.k) : "r"(tab + off + 16u));
+    return c;
+}
+template <> __device__ __forceinline__ Cull4<float> load_cull_at<float, false>(uint32_t, const unsigned char* gtab, uint32_t off) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(gtab + off));
     Cull4<float> c = {v.x, v.y, v.z, v.w};
     return c;
 }
-template <> __device__ __forceinline__ Cull4<double> load_cull_at<double>(const unsigned char* tab, uint32_t off) {
-    const double2 a = *reinterpret_cast<const double2*>(tab + off), b = *reinterpret_cast<const double2*>(tab + off + 16);
+template <> __device__ __forceinline__ Cull4<double> load_cull_at<double, false>(uint32_t, const unsigned char* gtab, uint32_t off) {
+    const double2 a = __ldg(reinterpret_cast<const double2*>(gtab + off)), b = __ldg(reinterpret_cast<const double2*>(gtab + off + 16));
     Cull4<double> c = {a.x, a.y, b.x, b.y};
     return c;
 }
-template <typename R, int FAMILY>
-__device__ __forceinline__ void cull_list_window(const unsigned char* tab, const uint32_t* ent, int cnt, const CullRay<R, FAMILY>& cr, uint32_t& lo, uint32_t& hi) {
+// one window of a ray's list: entries ent[0 .. cnt) (cnt a multiple of 4, at most GROUP), 4 entries per 16-byte load, 8 tests
+// per loop body; test j lands in bit 31 - j of lo (j < 32) / hi (set = object survives)
+template <typename R, int FAMILY, bool SMEM>
+__device__ __forceinline__ void cull_list_window(uint32_t tab, const unsigned char* gtab, const uint32_t* ent, int cnt, const CullRay<R, FAMILY>& cr, uint32_t& lo, uint32_t& hi) {
     lo = 0; hi = 0;
     if (cnt <= 0) return;
-    const int n_lo = min(cnt, 32);
-    uint4 e = __ldg(reinterpret_cast<const uint4*>(ent));
+    auto four = [&](uint32_t m, const uint4& c) {
+        m = push_sign(m, cr.slack(load_cull_at<R, SMEM>(tab, gtab, c.x)));
+        m = push_sign(m, cr.slack(load_cull_at<R, SMEM>(tab, gtab, c.y)));
+        m = push_sign(m, cr.slack(load_cull_at<R, SMEM>(tab, gtab, c.z)));
+        return push_sign(m, cr.slack(load_cull_at<R, SMEM>(tab, gtab, c.w)));
+    };
+    const uint4* e4 = reinterpret_cast<const uint4*>(ent);
+    const int n4 = cnt >> 2;                                   // groups of four
+    // half a window (8 groups) at a time; the offsets of the next two groups are in flight while two are tested
+    auto half = [&](int g0, int g1) -> uint32_t {
+        uint32_t m = 0;
+        int g = g0;
+        uint4 a = __ldg(e4 + g), b = (g + 1 < g1) ? __ldg(e4 + g + 1) : a;
 #pragma unroll 1
-    for (int j = 0; j < n_lo; j += 4) {
-        const uint4 c = e;
-        if (j + 4 < cnt) e = __ldg(reinterpret_cast<const uint4*>(ent + j + 4));       // the next four offsets are in flight while these are tested
-        lo = push_sign(lo, cr.slack(load_cull_at<R>(tab, c.x)));
-        lo = push_sign(lo, cr.slack(load_cull_at<R>(tab, c.y)));
-        lo = push_sign(lo, cr.slack(load_cull_at<R>(tab, c.z)));
-        lo = push_sign(lo, cr.slack(load_cull_at<R>(tab, c.w)));
-    }
-    if (n_lo < 32) { lo <<= 32 - n_lo; return; }
-#pragma unroll 1
-    for (int j = 32; j < cnt; j += 4) {
-        const uint4 c = e;
-        if (j + 4 < cnt) e = __ldg(reinterpret_cast<const uint4*>(ent + j + 4));
-        hi = push_sign(hi, cr.slack(load_cull_at<R>(tab, c.x)));
-        hi = push_sign(hi, cr.slack(load_cull_at<R>(tab, c.y)));
-        hi = push_sign(hi, cr.slack(load_cull_at<R>(tab, c.z)));
-        hi = push_sign(hi, cr.slack(load_cull_at<R>(tab, c.w)));
-    }
-    if (cnt > 32 && cnt < 64) hi <<= 64 - cnt;
+        for (; g + 1 < g1; g += 2) {
+            const uint4 ca = a, cb = b;
+            if (g + 2 < g1) a = __ldg(e4 + g + 2);
+            if (g + 3 < g1) b = __ldg(e4 + g + 3);
+            m = four(m, ca);
+            m = four(m, cb);
+        }
+        if (g < g1) m = four(m, a);
+        const int tested = 4 * (g1 - g0);
+        return tested < 32 ? m << (32 - tested) : m;
+    };
+    lo = half(0, min(n4, 8));
+    if (n4 > 8) hi = half(8, n4);
 }
 
 template <typename R>
@@ -1112,7 +1137,8 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
         if (tid == 0) stage_cull(table, 0, n_cull, reinterpret_cast<R*>(smem_raw), &bar);
         mbar_wait(&bar, 0);
     }
-    const unsigned char* tab = TABLE_SMEM ? smem_raw : reinterpret_cast<const unsigned char*>(table);
+    const uint32_t tab_s = smem_u32(smem_raw);
+    const unsigned char* const tab_g = reinterpret_cast<const unsigned char*>(table);
     unsigned long long fine = 0;
     __shared__ int2 s_stage[CULL_THREADS / 32][CULL_STAGE];
     int2* const stage = s_stage[tid >> 5];
@@ -1157,7 +1183,7 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
         for (int k0 = 0; k0 < len_max; k0 += GROUP) {          // uniform across the warp
             const int cnt = min(max(len - k0, 0), GROUP);
             uint32_t lo, hi;
-            cull_list_window<R, FAMILY>(tab, bl.entry + first + k0, cnt, cr, lo, hi);
+            cull_list_window<R, FAMILY, TABLE_SMEM>(tab_s, tab_g, bl.entry + first + k0, cnt, cr, lo, hi);
             fine += (unsigned long long)cnt;
             // Survivors are staged per warp in shared memory and flushed to the queue STAGE at a time: one atomic on the
             // queue's counter per flush.  (One atomic per warp and window - a million and more per launch, all on one
@@ -1823,12 +1849,86 @@ __global__ void __launch_bounds__(256) k_gen(DevScene<R> sc, Level<R> lv, Counte
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i == 0) {
         for (int l = 1; l <= GMLRT_MAX_DEPTH; l++) ctr->count[l] = 0;
+        for (int l = 0; l <= GMLRT_MAX_DEPTH; l++) ctr->hits[l] = 0;
         ctr->count[0] = S;
     }
     if (i >= S) return;
     double o[3], d[3];
     camera_ray64(sc, CamSrc{y0, map}, i, o, d);
     store_ray(lv.ray, i, (R)o[0], (R)o[1], (R)o[2], (R)d[0], (R)d[1], (R)d[2], 0, 0);
+}
+
+// Background of a ray that hit nothing: Lerp(BgStart, BgEnd, 0.5 (dir.Y + 1)) (raytracer.go:493-497)
+template <typename R> __device__ __forceinline__ V3<R> background(const DevScene<R>& sc, R dy) {
+    const R t = R(0.5) * (dy + R(1));
+    const V3<R> a = ld3(sc.bg0), b = ld3(sc.bg1);
+    return mk(a.x + (b.x - a.x) * t, a.y + (b.y - a.y) * t, a.z + (b.z - a.z) * t);
+}
+
+// ------------------------------------------------------------------ hit list (stream compaction between scan and shading)
+// After the scan of a level a third to two thirds of its rays have hit nothing (4K spheres1024: 64 % of the camera rays), and
+// in ray order hits and misses share warps: k_shade ran with 22 of 32 lanes busy, k_resolve with 13-16 (ncu, round 1).
+// This pass splits them: the indices of the rays that hit are appended to Level::hits (__ballot_sync / __popc within the
+// warp, one shared-memory scan per block, ONE atomic on the level's counter per block of HITLIST_RAYS rays), and a miss is
+// finished here and now - on levels >= 1 its background colour goes straight into the parent's child slot (on level 0 the
+// pixel pass looks at the fold key again).  Everything after this runs on dense warps over per-hit arrays.
+constexpr int HITLIST_THREADS = 256, HITLIST_PER_THREAD = 8, HITLIST_RAYS = HITLIST_THREADS * HITLIST_PER_THREAD;
+template <typename R, int PICKLESS>
+__global__ void __launch_bounds__(HITLIST_THREADS) k_hitlist(const __grid_constant__ DevScene<R> sc, const __grid_constant__ Level<R> lv, const __grid_constant__ Level<R> prev,
+                                                            Counters* ctr, int level, int32_t* ids, int y0, const __grid_constant__ RowMap map) {
+    const int n = ctr->count[level];
+    __shared__ int s_warp[HITLIST_THREADS / 32];
+    __shared__ int s_base;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const unsigned lt = (1u << lane) - 1u;
+    unsigned long long n_hit = 0;
+    for (int blk0 = blockIdx.x * HITLIST_RAYS; blk0 < n; blk0 += gridDim.x * HITLIST_RAYS) {       // uniform per block
+        unsigned bal[HITLIST_PER_THREAD];
+        int mine = 0;
+#pragma unroll
+        for (int k = 0; k < HITLIST_PER_THREAD; k++) {
+            const int i = blk0 + (wid * HITLIST_PER_THREAD + k) * 32 + lane;      // a warp owns 32 * HITLIST_PER_THREAD consecutive rays: its hits stay in order
+            bool hit = false;
+            if (i < n) {
+                int h; R t;
+                level_hit<R, PICKLESS>(lv, i, h, t);
+                hit = h >= 0;
+                if (ids) {                                     // level 0, counting mode: primary hit ids in (y, x, sample) order
+                    const int pix = i >> 2;
+                    ids[((size_t)map.actual(y0 + pix / sc.W) * sc.W + pix % sc.W) * 4 + (i & 3)] = h < 0 ? -1 : sc.scan_of[h & HIT_LEAF_MASK];
+                }
+                if (!hit && level > 0) {                       // a miss is finished here: background into the parent's child slot
+                    Ray<R> w;
+                    load_ray(lv.ray, i, w);
+                    const V3<R> c = background(sc, w.dy);
+                    const int p = ray_parent(lv.ray, i);
+                    const size_t pi = (size_t)(p & 0x7fffffff), pc = (size_t)prev.cap;
+                    const int base = (p < 0) ? 3 : 0;
+                    prev.child[(base + 0) * pc + pi] = c.x; prev.child[(base + 1) * pc + pi] = c.y; prev.child[(base + 2) * pc + pi] = c.z;
+                }
+            }
+            bal[k] = __ballot_sync(0xffffffffu, hit);
+            mine += __popc(bal[k]);
+        }
+        if (lane == 0) s_warp[wid] = mine;                    // (every lane of a warp holds the same ballots)
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int tot = 0;
+#pragma unroll
+            for (int w = 0; w < HITLIST_THREADS / 32; w++) { const int c = s_warp[w]; s_warp[w] = tot; tot += c; }
+            s_base = tot ? atomicAdd(&ctr->hits[level], tot) : 0;
+            n_hit += (unsigned long long)tot;
+        }
+        __syncthreads();
+        int at = s_base + s_warp[wid];
+#pragma unroll
+        for (int k = 0; k < HITLIST_PER_THREAD; k++) {
+            if ((bal[k] >> lane) & 1u) lv.hits[at + __popc(bal[k] & lt)] = blk0 + (wid * HITLIST_PER_THREAD + k) * 32 + lane;
+            at += __popc(bal[k]);
+        }
+        __syncthreads();                                       // s_warp / s_base are rewritten by the next block of rays
+    }
+    if (threadIdx.x == 0 && n_hit) atomicAdd(&ctr->rays_hit, n_hit);
 }
 
 // rec slots
@@ -1845,12 +1945,12 @@ enum { REC_P = 0, REC_N = 3, REC_COL = 6, REC_REFL = 9, REC_TRANSP = 10, REC_KR 
 template <typename R, int PICKLESS>
 __global__ void __launch_bounds__(256) k_primary_points(const __grid_constant__ DevScene<R> sc, const __grid_constant__ Level<R> lv,
                                                         const Counters* ctr, const __grid_constant__ CamSrc cam) {
-    const int n = ctr->count[0];
+    const int n = ctr->hits[0];
     const size_t cap = (size_t)lv.cap;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    for (int hs = blockIdx.x * blockDim.x + threadIdx.x; hs < n; hs += gridDim.x * blockDim.x) {      // hs: position in the hit list
+        const int i = lv.hits[hs];
         int h; R t_pre;
         level_hit<R, PICKLESS>(lv, i, h, t_pre);
-        if (h < 0) continue;
         const int leaf = h & HIT_LEAF_MASK, face = (h >> 28) & 7;
         double td = (double)(PICKLESS != 0 ? t_pre : lv.t[i]);
         double o64[3], d64[3];
@@ -1861,9 +1961,9 @@ __global__ void __launch_bounds__(256) k_primary_points(const __grid_constant__ 
             double t2 = 0.0; int f2 = 0;
             if (hit_any_kind<double>(sc.kind[leaf], o, t2, f2) && f2 == face) td = t2;
         }
-        lv.rec[(REC_P + 0) * cap + i] = (R)(o.ox + o.dx * td);
-        lv.rec[(REC_P + 1) * cap + i] = (R)(o.oy + o.dy * td);
-        lv.rec[(REC_P + 2) * cap + i] = (R)(o.oz + o.dz * td);
+        lv.rec[(REC_P + 0) * cap + hs] = (R)(o.ox + o.dx * td);
+        lv.rec[(REC_P + 1) * cap + hs] = (R)(o.oy + o.dy * td);
+        lv.rec[(REC_P + 2) * cap + hs] = (R)(o.oz + o.dz * td);
     }
 }
 
@@ -1873,30 +1973,25 @@ __global__ void __launch_bounds__(256) k_primary_points(const __grid_constant__ 
 template <typename R, int PICKLESS>
 __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R> lv, Level<R> next, ShadowQueue<R> sq,
                                                          unsigned char* occl, Counters* ctr, int level, int spawn,
-                                                         int32_t* ids, int y0, RowMap map, R* spawn_to, int points) {
-    const int n = ctr->count[level];
+                                                         R* spawn_to, int points) {
+    const int n = ctr->hits[level];                        // the rays that hit something (Level::hits): every lane has work
     const bool use_points = points != 0;                   // level 0, throughput mode: object-space hit points precomputed in double
     __shared__ int s_append[2][SHADE_QUEUES][SHADE_WARPS];
     int append_phase = 0;
-    // The hit code of the next iteration is fetched one iteration ahead, so that an iteration's dependent chain starts
-    // at the ray record instead of one DRAM round trip earlier.  (Fetching the record ahead as well was measured
-    // slower: 11 more live registers spill at the 64 the kernel is held to.)
+    // The ray index of the next iteration is fetched one iteration ahead, so that an iteration's dependent chain starts
+    // at the fold key / ray record instead of one DRAM round trip earlier.
     const int stride = gridDim.x * blockDim.x;
-    const int i_first = blockIdx.x * blockDim.x + threadIdx.x;
-    int h_nx = -1; R t_nx = R(0);
-    if (i_first < n) level_hit<R, PICKLESS>(lv, i_first, h_nx, t_nx);
+    const int hs_first = blockIdx.x * blockDim.x + threadIdx.x;
+    int i_nx = hs_first < n ? lv.hits[hs_first] : -1;
     for (int blk0 = blockIdx.x * blockDim.x; blk0 < n; blk0 += stride) {   // uniform per block
-    const int i = blk0 + threadIdx.x;
+    const int hs = blk0 + threadIdx.x;                     // position in the hit list = index of everything per hit (rec, child, occl)
     const size_t cap = (size_t)lv.cap;                     // 64-bit strides: 15 * cap passes 2^31 on deep binary ray trees
-    bool live = i < n;
-    const int h = h_nx;                                    // = lv.hit[i], or -1 past the end
-    const R t_pre = t_nx;
-    h_nx = -1;
-    if ((long long)i + stride < n) level_hit<R, PICKLESS>(lv, i + stride, h_nx, t_nx);
-    if (ids && live) {                                     // level 0 only: primary hit ids in (y, x, sample) order
-        const int pix = i >> 2;
-        ids[((size_t)map.actual(y0 + pix / sc.W) * sc.W + pix % sc.W) * 4 + (i & 3)] = h < 0 ? -1 : sc.scan_of[h & HIT_LEAF_MASK];
-    }
+    bool live = hs < n;
+    const int i = i_nx;                                    // the ray
+    i_nx = -1;
+    if ((long long)hs + stride < n) i_nx = lv.hits[hs + stride];
+    int h = -1; R t_pre = R(0);
+    if (live) level_hit<R, PICKLESS>(lv, i, h, t_pre);
     live = live && h >= 0;
     Ray<R> w = {R(0), R(0), R(0), R(0), R(0), R(1)};
     V3<R> P = mk(R(0), R(0), R(0)), N = P;
@@ -1916,7 +2011,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
         const int kind = sc.kind[leaf];
         V3<R> p = mk(o.ox + o.dx * t, o.oy + o.dy * t, o.oz + o.dz * t);             // Hit.PointObj
         if (!GMLRT_PARITY_TU) {
-            if (use_points) p = mk(lv.rec[(REC_P + 0) * cap + i], lv.rec[(REC_P + 1) * cap + i], lv.rec[(REC_P + 2) * cap + i]);   // camera rays: k_primary_points
+            if (use_points) p = mk(lv.rec[(REC_P + 0) * cap + hs], lv.rec[(REC_P + 1) * cap + hs], lv.rec[(REC_P + 2) * cap + hs]);   // camera rays: k_primary_points
             else if (kind == K_SPHERE) {
                 // o + d t adds two vectors tens of radii long to get one of length one (the normal of a sphere IS this point,
                 // :119): go through the point of closest approach instead, where every term is of order one (see hit_sphere)
@@ -1977,9 +2072,8 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
             }
         }
         if (!ok) {                                   // the reference panics here (:499-501)
-            atomicExch(&ctr->error, 1);
+            atomicExch(&ctr->error, 1);                  // the frame is discarded (GMLRT_E_SURFACE); the record below stays zero: no children, black
             live = false;
-            level_set_miss<R, PICKLESS>(lv, i);
         } else {
             P = mul_point(sc.o2w + (size_t)leaf * 12, p);
             if (flip) N = neg(N);
@@ -1989,7 +2083,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
     const V3<R> D = mk(w.dx, w.dy, w.dz);
     const int region = live ? region_of(sc, leaf, P, obj_x, obj_z) : 0;
     if (live) {
-        R* rec = lv.rec + i;
+        R* rec = lv.rec + hs;
         rec[(REC_P + 0) * cap] = P.x; rec[(REC_P + 1) * cap] = P.y; rec[(REC_P + 2) * cap] = P.z;
         rec[(REC_N + 0) * cap] = N.x; rec[(REC_N + 1) * cap] = N.y; rec[(REC_N + 2) * cap] = N.z;
         rec[(REC_COL + 0) * cap] = mat[0]; rec[(REC_COL + 1) * cap] = mat[1]; rec[(REC_COL + 2) * cap] = mat[2];
@@ -2032,8 +2126,8 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
     // was spawned needs a zero here: refraction lost to total internal reflection, or the reflection slot of a
     // transparent surface that does not reflect.  (At the deepest level nothing is spawned and k_resolve reads none.)
     if (spawn && live && transp > R(0)) {
-        if (!want_refl) for (int k = 0; k < 3; k++) lv.child[k * cap + i] = R(0);
-        if (!want_refr) for (int k = 3; k < 6; k++) lv.child[k * cap + i] = R(0);
+        if (!want_refl) for (int k = 0; k < 3; k++) lv.child[k * cap + hs] = R(0);
+        if (!want_refr) for (int k = 3; k < 6; k++) lv.child[k * cap + hs] = R(0);
     }
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const unsigned lt = (1u << lane) - 1u;
@@ -2094,8 +2188,8 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
             store_rec8(sq.q, (size_t)slot, so.x, so.y, so.z, ldir.x, ldir.y, ldir.z, dist, length(D));
             sq.skip[slot] = leaf < sc.n_leaves ? leaf : -1;      // a CSG object may shadow itself (oracle.c in_shadow)
             sq.key[slot] = region;
-            sq.target[slot] = i * sc.n_lights + li;
-            occl[i * sc.n_lights + li] = 0;
+            sq.target[slot] = hs * sc.n_lights + li;
+            occl[hs * sc.n_lights + li] = 0;
         }
         if (l0 == 0 && spawn) {
             const unsigned m_refl = __ballot_sync(0xffffffffu, want_refl), m_refr = __ballot_sync(0xffffffffu, want_refr);
@@ -2107,7 +2201,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
                 const V3<R> ro = P + N * R(1e-4);
                 rd = normalize(rd);
                 const int key = ray_sort_key(sc, region, rd);
-                store_ray(spawn_to, slot, ro.x, ro.y, ro.z, rd.x, rd.y, rd.z, i, key);
+                store_ray(spawn_to, slot, ro.x, ro.y, ro.z, rd.x, rd.y, rd.z, hs, key);
                 next.hit[slot] = key;
                 }
             }
@@ -2116,7 +2210,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
                 if (slot < next.cap) {
                 const V3<R> ro = P - refr_n * R(1e-4);
                 const int key = ray_sort_key(sc, region, refr_d);
-                store_ray(spawn_to, slot, ro.x, ro.y, ro.z, refr_d.x, refr_d.y, refr_d.z, (int)((unsigned)i | 0x80000000u), key);
+                store_ray(spawn_to, slot, ro.x, ro.y, ro.z, refr_d.x, refr_d.y, refr_d.z, (int)((unsigned)hs | 0x80000000u), key);
                 next.hit[slot] = key;
                 }
             }
@@ -2126,31 +2220,20 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
 }
 
 // ------------------------------------------------------------------ resolve one level (deepest first)
-// computeLighting (:372-401) with the shadow flags, then the combine + clamp of traceRay
-// (:493-497, :506-508, :557-561); the result goes into the parent's child slot, or into the
-// sample buffer at level 0.
-template <typename R, int PICKLESS>
+// computeLighting (:372-401) with the shadow flags, then the combine + clamp of traceRay (:506-508, :557-561), for the
+// rays of the level that hit (one thread per entry of the hit list: dense warps, per-hit arrays read as streams).  The
+// result goes into the parent's child slot, or - level 0 - into the sample colour of the camera ray.
+template <typename R>
 __global__ void __launch_bounds__(SHADE_THREADS) k_resolve(DevScene<R> sc, Level<R> lv, Level<R> prev, const unsigned char* occl,
-                                                           Counters* ctr, int level, uchar4* frame, int y0, RowMap map, int has_children) {
-    const int n = ctr->count[level];
-    unsigned long long n_hit = 0;
-    // the loop bound is uniform per warp: every lane reaches the shuffles of the level-0 epilogue
-    for (int i0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31); i0 < n; i0 += gridDim.x * blockDim.x) {
-    const int i = i0 + (threadIdx.x & 31);
-    const bool valid = i < n;
+                                                           const Counters* ctr, int level, int has_children) {
+    const int n = ctr->hits[level];
     const size_t cap = (size_t)lv.cap;                     // 64-bit strides: 15 * cap passes 2^31 on deep binary ray trees
-    V3<R> out = mk(R(0), R(0), R(0));
-    if (valid) {
-    Ray<R> wr;
-    load_ray(lv.ray, i, wr);
-    const V3<R> D = mk(wr.dx, wr.dy, wr.dz);
-    if (level_is_miss<R, PICKLESS>(lv, i)) {
-        const R t = R(0.5) * (D.y + R(1));                                           // :495-496
-        const V3<R> a = ld3(sc.bg0), b = ld3(sc.bg1);
-        out = mk(a.x + (b.x - a.x) * t, a.y + (b.y - a.y) * t, a.z + (b.z - a.z) * t);
-    } else {
-        n_hit++;
-        const R* rec = lv.rec + i;
+    for (int hs = blockIdx.x * blockDim.x + threadIdx.x; hs < n; hs += gridDim.x * blockDim.x) {
+        const int i = lv.hits[hs];
+        Ray<R> wr;
+        load_ray(lv.ray, i, wr);
+        const V3<R> D = mk(wr.dx, wr.dy, wr.dz);
+        const R* rec = lv.rec + hs;
         const V3<R> P = mk(rec[(REC_P + 0) * cap], rec[(REC_P + 1) * cap], rec[(REC_P + 2) * cap]);
         const V3<R> N = mk(rec[(REC_N + 0) * cap], rec[(REC_N + 1) * cap], rec[(REC_N + 2) * cap]);
         const V3<R> C = mk(rec[(REC_COL + 0) * cap], rec[(REC_COL + 1) * cap], rec[(REC_COL + 2) * cap]);
@@ -2161,7 +2244,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_resolve(DevScene<R> sc, Level
         for (int li = 0; li < sc.n_lights; li++) {
             V3<R> ldir, lcol; R dist;
             if (!light_at(sc.lights[li], P, ldir, dist, lcol)) continue;
-            if (occl[i * sc.n_lights + li]) continue;
+            if (occl[(size_t)hs * sc.n_lights + li]) continue;
             const R nDotL = gomath::max0(dot(N, ldir));
             const V3<R> diffuse = lcol * (nDotL * kd);
             const V3<R> H = normalize(Vv + ldir);
@@ -2169,32 +2252,55 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_resolve(DevScene<R> sc, Level
             const V3<R> specular = lcol * (ks * gm<R>::pow(spec, nexp));
             L = (L + diffuse) + specular;
         }
+        V3<R> out;
         if (refl == R(0) && transp == R(0)) {
             out = clamp3(hadamard(L, C));
         } else {
             const V3<R> zero = mk(R(0), R(0), R(0));             // the deepest level has no children: traceRay returns black at depth 0 (:488-491)
-            const V3<R> rc = has_children ? mk(lv.child[i], lv.child[cap + i], lv.child[2 * cap + i]) : zero;
+            const V3<R> rc = has_children ? mk(lv.child[hs], lv.child[cap + hs], lv.child[2 * cap + hs]) : zero;
             if (transp == R(0)) {
                 out = clamp3(hadamard(L + rc * refl, C));
             } else {
-                const V3<R> fc = has_children ? mk(lv.child[3 * cap + i], lv.child[4 * cap + i], lv.child[5 * cap + i]) : zero;
+                const V3<R> fc = has_children ? mk(lv.child[3 * cap + hs], lv.child[4 * cap + hs], lv.child[5 * cap + hs]) : zero;
                 out = clamp3(hadamard(L * (R(1) - transp) + (rc * kr + fc * (R(1) - kr)), C));
             }
         }
+        if (level == 0) {
+            lv.samp[i] = out.x; lv.samp[cap + i] = out.y; lv.samp[2 * cap + i] = out.z;
+        } else {
+            const int p = ray_parent(lv.ray, i);
+            const size_t pi = (size_t)(p & 0x7fffffff), pc = (size_t)prev.cap;
+            const int base = (p < 0) ? 3 : 0;
+            prev.child[(base + 0) * pc + pi] = out.x; prev.child[(base + 1) * pc + pi] = out.y; prev.child[(base + 2) * pc + pi] = out.z;
+        }
     }
-    }  // valid
-    if (level == 0) {
-        // img.Set(x, y, total * 0.25) -> Vec3.RGBA -> RGBAModel (raytracer.go:656, vec.go:104-107), fused: camera rays sit
-        // in (pixel, sample) order, so the 4 samples of a pixel are 4 neighbouring lanes (the grid stride and the ray
-        // count are multiples of 4: a quad is in the loop as a whole).  Lane 0 of the quad sums them in the reference's
-        // order - from zero, sample 0 first - quantises uint8(uint32(c * 65535) >> 8) and stores the pixel: no sample
-        // buffer, no separate pass.  The frame may be a peer device's (NVLink stores).
-        const unsigned quad = 0xffffffffu;
+}
+
+// ------------------------------------------------------------------ pixels (img.Set, raytracer.go:656; Vec3.RGBA, vec.go:104-107)
+// One thread per camera ray; rays sit in (pixel, sample) order, so the 4 samples of a pixel are 4 neighbouring lanes.  A
+// sample that hit has its colour in Level::samp (k_resolve), one that missed is the background of its direction.  Lane 0
+// of the quad collects the four with shuffles, sums them in the reference's order - from zero, sample 0 first - scales
+// by 0.25, quantises uint8(uint32(c * 65535) >> 8) and stores the RGBA8 pixel: into this device's frame or, in a
+// multi-GPU frame, straight into the gathering GPU's (NVLink stores).
+template <typename R, int PICKLESS>
+__global__ void __launch_bounds__(256) k_pixels(DevScene<R> sc, Level<R> lv, const Counters* ctr, uchar4* frame, int y0, RowMap map) {
+    const int n = ctr->count[0];
+    const size_t cap = (size_t)lv.cap;
+    // the loop bound is uniform per warp (the ray count and the grid stride are multiples of 32 / 4): every lane reaches the shuffles
+    for (int i0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31); i0 < n; i0 += gridDim.x * blockDim.x) {
+        const int i = i0 + (threadIdx.x & 31);
+        const bool valid = i < n;
+        R c[3] = {R(0), R(0), R(0)};
+        if (valid) {
+            if (level_is_miss<R, PICKLESS>(lv, i)) {
+                const V3<R> bg = background(sc, lv.ray[(size_t)i * RAY_WORDS + 4]);       // word 4: direction y
+                c[0] = bg.x; c[1] = bg.y; c[2] = bg.z;
+            } else { c[0] = lv.samp[i]; c[1] = lv.samp[cap + i]; c[2] = lv.samp[2 * cap + i]; }
+        }
         const int q0 = (threadIdx.x & 31) & ~3;
-        R c[3] = {out.x, out.y, out.z};
 #pragma unroll
         for (int k = 0; k < 3; k++) {
-            const R s1 = __shfl_sync(quad, c[k], q0 + 1), s2 = __shfl_sync(quad, c[k], q0 + 2), s3 = __shfl_sync(quad, c[k], q0 + 3);
+            const R s1 = __shfl_sync(0xffffffffu, c[k], q0 + 1), s2 = __shfl_sync(0xffffffffu, c[k], q0 + 2), s3 = __shfl_sync(0xffffffffu, c[k], q0 + 3);
             R tot = R(0);
             tot = tot + c[k]; tot = tot + s1; tot = tot + s2; tot = tot + s3;
             c[k] = tot * R(0.25);
@@ -2208,16 +2314,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_resolve(DevScene<R> sc, Level
             px.w = 0xFF;
             frame[(size_t)map.actual(y0 + pix / sc.W) * sc.W + pix % sc.W] = px;
         }
-    } else if (valid) {
-        const int p = ray_parent(lv.ray, i);
-        const int pi = p & 0x7fffffff;
-        const int base = (p < 0) ? 3 : 0;
-        const size_t pc = (size_t)prev.cap;
-        prev.child[(base + 0) * pc + pi] = out.x; prev.child[(base + 1) * pc + pi] = out.y; prev.child[(base + 2) * pc + pi] = out.z;
     }
-    }  // grid-stride loop
-    n_hit = warp_sum_u64(n_hit);                           // (every lane reaches this point)
-    if ((threadIdx.x & 31) == 0 && n_hit) atomicAdd(&ctr->rays_hit, n_hit);
 }
 
 
@@ -2974,7 +3071,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     for (int d = 0; d < sc_.n_leaves; d++) n_unbounded += std::isinf(bound_[(size_t)d * 4 + 3]) ? 1 : 0;
     cand_per_ray_ = std::min<int>(std::max(sc_.n_leaves, 1), (int)env_size("GMLRT_CAND_PER_RAY", 4) + n_unbounded);
     const double cand_bytes = cand_per_ray_ * (8.0 + 8.0 * SHADOW_STREAMS + sizeof(R));   // queues: closest (ray, object, T), one (ray, object) per shadow stream
-    const double node_bytes = (2 * RAY_WORDS + NREC + 8) * sizeof(R) + 12 + nl;      // ray record (+ its staging copy), rec, child, hit, order, occl
+    const double node_bytes = (2 * RAY_WORDS + NREC + 8) * sizeof(R) + 16 + nl;      // ray record (+ its staging copy), rec, child, hit, order, hit list, occl
     const double shadow_bytes = nl * (8.0 * sizeof(R) + 20);
     const double per_sample = sum_mult * node_bytes + max_mult * (shadow_bytes + cand_bytes) + 3 * sizeof(R);
     // A scene of the same shape as the last one keeps its plan: free memory wobbles by a few MB between uploads, and a
@@ -3002,7 +3099,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     auto align = [](size_t x) { return (x + 255) & ~(size_t)255; };
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off = align(off + bytes); return o; };
-    struct LvOff { size_t ray, parent, hit, t, order, rec, child, occl; size_t cap; };
+    struct LvOff { size_t ray, parent, hit, t, order, rec, child, occl, hits, samp; size_t cap; };
     std::vector<LvOff> lo(depth_eff_);
     size_t max_cap = 0, stage_cap = 0;
     for (int l = 0; l < depth_eff_; l++) {
@@ -3012,6 +3109,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
         if (l > 0) stage_cap = std::max(stage_cap, cap);
         lo[l].t = take(cap * sizeof(R)); lo[l].order = take(cap * 8); lo[l].rec = take(NREC * cap * sizeof(R)); lo[l].child = take(6 * cap * sizeof(R));
         lo[l].occl = take(cap * std::max(nl, 1));
+        lo[l].hits = take(cap * 4); lo[l].samp = l == 0 ? take(3 * cap * sizeof(R)) : 0;
     }
     const size_t sq_cap = max_cap * std::max(nl, 1);
     size_t o_sq = take(8 * sq_cap * sizeof(R)), o_skip = take(sq_cap * 4), o_key = take(sq_cap * 4), o_tgt = take(sq_cap * 4), o_first = take(sq_cap * 4), o_perm = take(sq_cap * 4), o_sort = take(2 * SHADOW_STREAMS * SORT_BINS_MAX * sizeof(int));
@@ -3035,6 +3133,7 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
         L.ray = (R*)(base + lo[l].ray); L.hit = (int*)(base + lo[l].hit);
         L.t = (R*)(base + lo[l].t); L.order = (int*)(base + lo[l].order); L.rec = (R*)(base + lo[l].rec); L.child = (R*)(base + lo[l].child);
         occl_[l] = (unsigned char*)(base + lo[l].occl);
+        L.hits = (int*)(base + lo[l].hits); L.samp = l == 0 ? (R*)(base + lo[l].samp) : nullptr;
     }
     sq_.q = (R*)(base + o_sq); sq_.skip = (int*)(base + o_skip); sq_.key = (int*)(base + o_key); sq_.target = (int*)(base + o_tgt); sq_.cap = (int)sq_cap;
     sq_.per_light = (int)max_cap; sq_.count = shadow_counts_; sq_.first = (int*)(base + o_first); sq_.perm = (int*)(base + o_perm);
@@ -3192,6 +3291,16 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             if (!sc_.pickless) k_closest_pick<R><<<exact_grid, 256, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
             else totals_.launches--;
             totals_.launches += 3;
+            {   // hit list of the level; misses of levels >= 1 are finished here
+                MARK(KC_SORT);
+                const int hl_grid = std::min((levels_[l].cap + HITLIST_RAYS - 1) / HITLIST_RAYS, sms_ * 8);
+                int32_t* const hl_ids = (counting && l == 0) ? ids_ : nullptr;
+                const Level<R>& hl_prev = l > 0 ? levels_[l - 1] : levels_[l];
+                if (sc_.pickless == 1) k_hitlist<R, sizeof(R) == 4 ? 1 : 0><<<hl_grid, HITLIST_THREADS, 0, stream_>>>(sc_, levels_[l], hl_prev, ctr_, l, hl_ids, ty, map);
+                else if (sc_.pickless) k_hitlist<R, sizeof(R) == 4 ? 2 : 0><<<hl_grid, HITLIST_THREADS, 0, stream_>>>(sc_, levels_[l], hl_prev, ctr_, l, hl_ids, ty, map);
+                else k_hitlist<R, 0><<<hl_grid, HITLIST_THREADS, 0, stream_>>>(sc_, levels_[l], hl_prev, ctr_, l, hl_ids, ty, map);
+                totals_.launches++;
+            }
             const bool spawn = l + 1 < depth_eff_;
             if (two_streams && l > 0) for (int k = 0; k < nss; k++) CU_TRY(cudaStreamWaitEvent(stream_, ev_shadow_[k][l - 1], 0));     // k_shade refills the shadow queue
             if (primary_points_ && l == 0) MARK(KC_PIXELS);          // (class 6: the camera rays' hit points in double)
@@ -3205,7 +3314,6 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             auto shade = sc_.pickless == 1 ? k_shade<R, sizeof(R) == 4 ? 1 : 0> : sc_.pickless ? k_shade<R, sizeof(R) == 4 ? 2 : 0> : k_shade<R, 0>;
             shade<<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
                 sc_, levels_[l], spawn ? levels_[l + 1] : levels_[l], sq_, occl_[l], ctr_, l, spawn ? 1 : 0,
-                (counting && l == 0) ? ids_ : nullptr, ty, map,
                 spawn ? (sort_spawned_ ? spawn_stage_ : levels_[l + 1].ray) : nullptr, (primary_points_ && l == 0) ? 1 : 0);
             totals_.launches += 2;
             // shadow queries of this level: on the shadow stream, overlapping the next level's closest-hit pipeline
@@ -3264,9 +3372,14 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
         for (int l = depth_eff_ - 1; l >= 0; l--) {
             const int cap_blocks = (levels_[l].cap + SHADE_THREADS - 1) / SHADE_THREADS;
             MARK(KC_RESOLVE);
-            auto resolve = sc_.pickless ? k_resolve<R, sizeof(R) == 4 ? 1 : 0> : k_resolve<R, 0>;
-            resolve<<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
-                sc_, levels_[l], l > 0 ? levels_[l - 1] : levels_[l], occl_[l], ctr_, l, frame_target_ ? (uchar4*)frame_target_ : frame_, ty, map, l + 1 < depth_eff_ ? 1 : 0);
+            k_resolve<R><<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
+                sc_, levels_[l], l > 0 ? levels_[l - 1] : levels_[l], occl_[l], ctr_, l, l + 1 < depth_eff_ ? 1 : 0);
+            totals_.launches++;
+        }
+        {   // the level-0 colours are final: average the samples, store the pixels
+            uchar4* const target = frame_target_ ? (uchar4*)frame_target_ : frame_;
+            if (sc_.pickless) k_pixels<R, sizeof(R) == 4 ? 1 : 0><<<wide, 256, 0, stream_>>>(sc_, levels_[0], ctr_, target, ty, map);
+            else k_pixels<R, 0><<<wide, 256, 0, stream_>>>(sc_, levels_[0], ctr_, target, ty, map);
             totals_.launches++;
         }
     }

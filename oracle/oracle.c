@@ -218,6 +218,8 @@ static inline int plane_isect(v3 n, double D, ray_t r, double* t, v3* p) {
     return 1;
 }
 
+static __thread unsigned long long tl_chaos;   /* cube-face rejections decided by rounding alone (see the cube case below) */
+
 /* First-hit rule of each primitive, exactly as <Type>.Intersect.  Returns 1 on hit. */
 static int leaf_intersect(const object_t* o, ray_t wray, double* t_out, v3* p_out, int* face_out) {
     ray_t r;
@@ -250,7 +252,14 @@ static int leaf_intersect(const object_t* o, ray_t wray, double* t_out, v3* p_ou
             double t; v3 p;
             double D = -vdot(CUBE_N[f], CUBE_P[f]);
             if (!plane_isect(CUBE_N[f], D, r, &t, &p) || t < 0.0) continue;
-            if (p.x < 0 || p.x > 1 || p.y < 0 || p.y > 1 || p.z < 0 || p.z > 1) continue;
+            if (p.x < 0 || p.x > 1 || p.y < 0 || p.y > 1 || p.z < 0 || p.z > 1) {
+                /* the bounds test includes the face's own axis, where p is 0 or 1 only up to rounding, so a face
+                 * is randomly rejected when o + d t lands at -1e-17.  Count the rejections that rounding alone decided
+                 * (the point is inside the face to 1e-9): a pixel that saw one is rounding chaos in the reference itself. */
+                const double e = 1e-9;
+                if (p.x >= -e && p.x <= 1 + e && p.y >= -e && p.y <= 1 + e && p.z >= -e && p.z <= 1 + e) tl_chaos++;
+                continue;
+            }
             if (!found || t < *t_out) { found = 1; *t_out = t; *p_out = p; *face_out = f; }
         }
         return found;
@@ -742,6 +751,7 @@ typedef struct {
     const scene_t* s;
     uint8_t* rgba;
     int32_t* primary_ids;     /* nullable: [H][W][4] */
+    uint8_t* chaos;           /* nullable: [H][W] 1 = some ray of the pixel's tree saw a cube face rejected by rounding alone */
     int x0, y0, x1, y1;       /* crop, half-open */
     atomic_int next_item;
     int n_items, items_per_col;
@@ -761,6 +771,7 @@ static void render_item(job_t* job, int x, int ymin, counters_t* c) {
             continue;
         }
         v3 total = V(0, 0, 0);
+        const unsigned long long chaos0 = tl_chaos;
         for (int sidx = 0; sidx < 4; sidx++) {
             double dx = go_pcg_float64(&rng) - 0.5;
             double dy = go_pcg_float64(&rng) - 0.5;
@@ -772,6 +783,7 @@ static void render_item(job_t* job, int x, int ymin, counters_t* c) {
             int32_t* pid = job->primary_ids ? &job->primary_ids[((size_t)y * s->width + x) * 4 + sidx] : NULL;
             total = vadd(total, trace_ray(s, ray, s->depth, 0, c, pid));
         }
+        if (job->chaos) job->chaos[(size_t)y * s->width + x] = tl_chaos != chaos0;
         v3 px = vscale(total, 1.0 / 4.0);
         uint8_t* o = job->rgba + ((size_t)y * s->width + x) * 4;
         /* Vec3.RGBA + color.RGBAModel (vec.go:104-107): uint8(uint32(c*65535) >> 8) */
@@ -805,15 +817,22 @@ static void* worker(void* arg) {
 
 /* Renders pixels [x0,x1) x [y0,y1) (pass 0,0,W,H for the whole frame) into a full-frame RGBA
  * buffer with `threads` workers (the reference uses 8, raytracer.go:725).  stats may be NULL. */
+int oracle_render2(const void* blob, size_t blob_bytes, uint8_t* rgba, size_t rgba_bytes, int threads,
+                   int x0, int y0, int x1, int y1, gmlrt_stats* stats, int32_t* primary_ids, uint8_t* chaos);
 int oracle_render(const void* blob, size_t blob_bytes, uint8_t* rgba, size_t rgba_bytes, int threads,
                   int x0, int y0, int x1, int y1, gmlrt_stats* stats, int32_t* primary_ids) {
+    return oracle_render2(blob, blob_bytes, rgba, rgba_bytes, threads, x0, y0, x1, y1, stats, primary_ids, NULL);
+}
+/* ... `chaos` (nullable, [H][W]): 1 where the pixel's value depends on a cube face rejected by rounding alone */
+int oracle_render2(const void* blob, size_t blob_bytes, uint8_t* rgba, size_t rgba_bytes, int threads,
+                   int x0, int y0, int x1, int y1, gmlrt_stats* stats, int32_t* primary_ids, uint8_t* chaos) {
     scene_t s;
     int rc = scene_init(&s, blob, blob_bytes);
     if (rc) { scene_free(&s); return rc; }
     if (!rgba || rgba_bytes != (size_t)4 * s.width * s.height) { scene_free(&s); return GMLRT_E_BAD_ARG; }
     if (x0 < 0) x0 = 0; if (y0 < 0) y0 = 0; if (x1 > s.width) x1 = s.width; if (y1 > s.height) y1 = s.height;
     job_t job; memset(&job, 0, sizeof job);
-    job.s = &s; job.rgba = rgba; job.primary_ids = primary_ids;
+    job.s = &s; job.rgba = rgba; job.primary_ids = primary_ids; job.chaos = chaos;
     job.x0 = x0; job.y0 = y0; job.x1 = x1; job.y1 = y1;
     if (x1 > x0 && y1 > y0) {
         job.items_per_col = (y1 - 1) / 20 - y0 / 20 + 1;
