@@ -2829,7 +2829,9 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     while (((n_regions_ - 1) >> sort_shift_) + 2 > sort_nb_) sort_shift_++;
     sort_shadows_ = env_size("GMLRT_SORT_SHADOWS", 0) != 0;
     primary_points_ = kRobustPrimary && env_size("GMLRT_PRIMARY_POINTS", 1) != 0;
+    const double t_l0 = now();
     if ((rc = build_lists(S, err))) return rc;
+    const double t_l1 = now();
     {
         void* p = nullptr;
         if ((rc = scene_alloc(std::max<size_t>(S.lights.size(), 1) * sizeof(int), &p, err))) return rc;
@@ -2849,8 +2851,8 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
         frame_px_ = px;
     }
     const int prc = plan_tiles(S, err);
-    if (dbg_t) fprintf(stderr, "[gmlrt upload dev %d] sync+free %.3f  host build + enqueue copies %.3f  copy sync %.3f  frame+plan_tiles %.3f ms\n",
-                       dev_, t_b - t_a, t_c - t_b, t_d - t_c, now() - t_d);
+    if (dbg_t) fprintf(stderr, "[gmlrt upload dev %d] sync+free %.3f  host build + enqueue copies %.3f (of which ray-class lists %.3f)  copy sync %.3f  frame+plan_tiles %.3f ms\n",
+                       dev_, t_b - t_a, t_c - t_b, t_l1 - t_l0, t_d - t_c, now() - t_d);
     return prc;
 }
 
@@ -2956,6 +2958,9 @@ int Renderer<R>::build_lists(const HostScene& S, std::string& err) {
         double* o = &cells[(size_t)((face * k + cu) * k + ((cu & 1) ? k - 1 - cv : cv)) * 5];
         o[0] = ax[0]; o[1] = ax[1]; o[2] = ax[2]; o[3] = std::cos(th); o[4] = std::sin(th);
     }
+    const bool dbg_t = getenv("GMLRT_DEBUG_UPLOAD") != nullptr;
+    auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t0 = now();
     const std::vector<double> reg_spawn = merged(sc_.key_shift, key_nb_ / n_cells), reg_shadow = merged(sort_shift_, sort_nb_);
     double *d_cells, *d_reg_spawn, *d_reg_shadow;
     if ((rc = to_device(cells, &d_cells, err)) || (rc = to_device(reg_spawn, &d_reg_spawn, err)) ||
@@ -3034,8 +3039,10 @@ int Renderer<R>::build_lists(const HostScene& S, std::string& err) {
         CU_TRY(cudaMemcpyAsync(&tails[2 * s], ps.count + ps.p.n_bins - 1, sizeof(int), cudaMemcpyDeviceToHost, stream_));
         CU_TRY(cudaMemcpyAsync(&tails[2 * s + 1], ps.first + ps.p.n_bins - 1, sizeof(int), cudaMemcpyDeviceToHost, stream_));
     }
+    const double t1 = now();
     CU_TRY(cudaMemcpyAsync(&list_tests_, list_tests_dev_, sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream_));
     CU_TRY(cudaStreamSynchronize(stream_));
+    const double t2 = now();
     list_tests_ *= 2;                                                  // the fill pass repeats the tests
     for (size_t s = 0; s < sets.size(); s++) {
         Pending& ps = sets[s];
@@ -3046,6 +3053,14 @@ int Renderer<R>::build_lists(const HostScene& S, std::string& err) {
         const int grid = std::min((ps.p.n_bins + 7) / 8, sms_ * 32);
         k_list_build<true><<<grid, 256, 0, stream_>>>(ps.p, nullptr, ps.first, (int2*)pb, (uint32_t*)pe, (uint32_t)(4 * sizeof(R)), nullptr);
         ps.out->bin = (const int2*)pb; ps.out->entry = (const uint32_t*)pe; ps.out->n_bins = ps.p.n_bins;
+    }
+    if (dbg_t) {
+        const double t3 = now();
+        cudaStreamSynchronize(stream_);
+        fprintf(stderr, "[gmlrt lists dev %d] host prep + count/scan enqueue %.3f  wait %.3f  alloc + fill enqueue %.3f  fill wait %.3f ms; bins %d / %d / %d, entries", dev_,
+                t1 - t0, t2 - t1, t3 - t2, now() - t3, lists_camera_.n_bins, lists_spawn_.n_bins, sort_nb_);
+        for (size_t q = 0; q < sets.size(); q++) fprintf(stderr, " %lld", (long long)tails[2 * q] + tails[2 * q + 1]);
+        fprintf(stderr, "\n");
     }
     CU_TRY(cudaGetLastError());
     return GMLRT_OK;
