@@ -253,7 +253,7 @@ def main():
     cst = ctx.trace()
     ctx.set_counting(False)
     counts = torch.tensor([cst.rays_primary, cst.rays_reflect, cst.rays_refract, cst.rays_shadow, cst.shadow_occluded,
-                           cst.leaf_tests, int(cst.flops_credited / 1e3), cst.cull_tests, cst.exact_tests, int(cst.flops_executed / 1e3), cst.packet_tests, cst.cull_tests_family[0], cst.cull_tests_family[1], cst.cull_tests_family[2], cst.rays_hit, cst.exact_tests_shadow],
+                           cst.leaf_tests, int(cst.flops_credited / 1e3), cst.cull_tests, cst.exact_tests, int(cst.flops_executed / 1e3), cst.packet_tests, cst.cull_tests_family[0], cst.cull_tests_family[1], cst.cull_tests_family[2], cst.rays_hit, cst.exact_tests_shadow, cst.rays_hit_primary],
                           dtype=torch.int64, device=f"cuda:{local_rank}")
     if dist is not None:
         dist.all_reduce(counts)
@@ -408,15 +408,18 @@ def main():
     import struct as _struct
     nl = _struct.unpack_from("<I", blob, 120)[0]                           # gmlrt_blob_header.n_lights
     wb = 4 if args.precision == "f32" else 8                               # bytes per word of the arithmetic type
-    P, RF, RR, S, NH = (float(counts[k]) for k in (0, 1, 2, 3, 14))
+    P, RF, RR, S, NH, NH0 = (float(counts[k]) for k in (0, 1, 2, 3, 14, 16))
     C, CH = P + RF + RR, RF + RR                                           # closest-hit queries; spawned (child) rays
+    MISS_DEEP = CH - (NH - NH0)                                            # rays of levels >= 1 that hit nothing: finished by k_hitlist
     Xs = float(counts[15]); Xc = float(counts[8]) - Xs                     # exact tests: shadow / closest candidates
+    key = 8                                                                # fold key (f32) / hit code + T (f64): 8 bytes per ray either way
     model_bytes = {
         0: P * 8 * wb,                                                     # gen: one ray record per sample
-        4: C * 4 + NH * (8 * wb + wb) + NH * 16 * wb + S * (8 * wb + 13) + CH * (8 * wb + 4),        # shade: hit code of every ray, ray + T of the hits in; rec, shadow records (+ skip, key, target, flag) and child records (+ key) out
-        5: C * (8 * wb + 4) + NH * (16 * wb + nl) + CH * 6 * wb + P,                                # resolve: ray, hit, rec, flags in; colour to the parent; level 0 averages the 4 samples in registers and stores RGBA8
+        6: NH0 * (4 + key + 3 * wb) if args.precision == "f32" else 0.0,   # primary points: hit index + fold key in, object-space point out
+        4: NH * (4 + key + 8 * wb + 16 * wb) + NH0 * 3 * wb * (1 if args.precision == "f32" else 0) + S * (8 * wb + 13) + CH * (8 * wb + 4),   # shade: per hit the index, key, ray in and the record out; shadow records (+ skip, key, target, flag) and child records (+ sort key) out
+        5: NH * (4 + 8 * wb + 15 * wb + nl + 3 * wb) + CH * 3 * wb + P * key + (P - NH0) * 8 * wb + NH0 * 3 * wb + P,   # resolve: per hit the index, ray, record, flags in, colour out; children's colours in; pixel pass: keys, the records of the misses, sample colours in, RGBA8 out
         7: Xc * ((8 + 8 * wb + 4 + wb) + (8 + wb + 8 + 4 + wb)) + Xs * (8 + 8 * wb + 8),           # exact: candidate + ray record + result; pick pass; shadow candidates
-        8: S * 12 + CH * (8 + 16 * wb),                                    # sort: keys twice + permutation; key sort moves the 8-word records
+        8: CH * (8 + 16 * wb) + C * key + NH * 4 + MISS_DEEP * (8 * wb + 3 * wb),                  # sort + compaction: key sort moves the 8-word records; hit list reads every key, writes the hits, finishes the deep misses
     }
     cull_flops_all = 15.0 * float(counts[11]) + 7.0 * float(counts[12] + counts[13]) + 20.0 * float(counts[10])
     by_class = {}
@@ -437,9 +440,9 @@ def main():
         by_class["cull_secondary (k_cull<GENERAL>), per-ray tests only"] = {"bound": "fp32", "ms_per_frame": class_ms[2] / args.steps, "achieved": tf,
                                                                             "unit": "TFLOP/s", "frac": tf / fp32_peak if fp32_peak else None}
     scan_ms = sum(class_ms[k] for k in (1, 2, 3, 7, 8))
-    # ---- the dominant single kernel: classes 0, 1, 2, 4, 5 are one kernel each (3, 7, 8 are groups of smaller ones; 6 is gone: fused into k_resolve) ----
-    kernel_of = {0: "k_gen", 1: "k_cull<PIVOT, CameraSource> (camera rays)", 2: "k_cull<GENERAL, SpawnSource> (reflection / refraction rays)",
-                 4: "k_shade", 5: "k_resolve"}
+    # ---- the dominant single kernel: classes 0, 1, 2, 4, 6 are one kernel each (3, 5, 7, 8 are groups of smaller ones) ----
+    kernel_of = {0: "k_gen", 6: "k_primary_points", 1: "k_cull<PIVOT, CameraSource> (camera rays)", 2: "k_cull<GENERAL, SpawnSource> (reflection / refraction rays)",
+                 4: "k_shade", 5: "k_resolve (x levels) + k_pixels"}
     traffic = None
     if world > 1:             # per-kernel events are an N = 1 tool
         dom = None
@@ -501,7 +504,7 @@ def main():
                 "destination": "page-locked raster from gmlrt_alloc_host (the bridge of INTEGRATION.md)",
                 "phase_ms": e2e_phase, "upload_ms_each": upload_each},
         "e2e_pageable": {"value": rays_frame / (e2e_pg_ms * 1e-3) / 1e6, "unit": "Mrays/s", "frame_ms": e2e_pg_ms, "phase_ms": e2e_pg_phase,
-                         "destination": "pageable host array (image.NewRGBA of an unmodified caller): staged in 2 MB chunks by gmlrt_download",
+                         "destination": "pageable host array (image.NewRGBA of an unmodified caller): staged in 1 MB chunks by gmlrt_download",
                          "slower_than_page_locked": e2e_pg_ms / e2e_ms - 1.0},
         "kernel_ms_per_frame": {names[k]: class_ms[k] / args.steps for k in range(9)},
         "kernel_ms_per_frame_note": "second pass of the same K steps with an event before every launch and all launches on one stream; "

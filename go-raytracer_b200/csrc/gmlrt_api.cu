@@ -331,6 +331,7 @@ static int trace_once(gmlrt_ctx* c, gmlrt_stats* stats, bool& overflow) {
         sum.rays_primary += t.rays_primary; sum.rays_reflect += t.rays_reflect; sum.rays_refract += t.rays_refract;
         sum.rays_shadow += t.rays_shadow; sum.shadow_occluded += t.shadow_occluded; sum.rays_hit += t.rays_hit; sum.launches += t.launches;
         sum.shadow_tests += t.shadow_tests; sum.shadow_flops += t.shadow_flops; sum.exact_tests += t.exact_tests; sum.exact_tests_shadow += t.exact_tests_shadow; sum.exact_flops += t.exact_flops; sum.packet_tests += t.packet_tests;
+        sum.rays_hit_primary += t.rays_hit_primary; sum.list_tests = std::max(sum.list_tests, t.list_tests);
         for (int k = 0; k < 3; k++) sum.cull_by_family[k] += t.cull_by_family[k];
         for (int k = 0; k < KC_COUNT; k++) { sum.ms_class[k] = std::max(sum.ms_class[k], t.ms_class[k]); sum.launches_class[k] += t.launches_class[k]; }
         sum.error |= t.error; overflow = overflow || t.overflow;
@@ -358,6 +359,7 @@ static int trace_once(gmlrt_ctx* c, gmlrt_stats* stats, bool& overflow) {
         stats->packet_tests = sum.packet_tests;
         for (int k = 0; k < 3; k++) stats->cull_tests_family[k] = sum.cull_by_family[k];
         stats->exact_tests = sum.exact_tests; stats->exact_tests_shadow = sum.exact_tests_shadow;
+        stats->rays_hit_primary = sum.rays_hit_primary; stats->list_tests = sum.list_tests;
         stats->flops_executed = 15.0 * (double)sum.cull_by_family[0] + 7.0 * (double)(sum.cull_by_family[1] + sum.cull_by_family[2]) +
                                 20.0 * (double)sum.packet_tests + (double)sum.exact_flops;
         for (int k = 0; k < KC_COUNT; k++) { stats->ms_class[k] = sum.ms_class[k]; stats->launches_class[k] = sum.launches_class[k]; }
@@ -503,7 +505,7 @@ int gmlrt_download(gmlrt_ctx* c, uint8_t* rgba, size_t rgba_bytes) {
         API_CU(cudaHostAlloc((void**)&c->pinned, need, cudaHostAllocDefault));
         c->pinned_bytes = need;
     }
-    const size_t chunk = (size_t)2 << 20;
+    const size_t chunk = (size_t)1 << 20;
     const int n_chunks = (int)((need + chunk - 1) / chunk);
     while ((int)c->ev_chunk.size() < n_chunks) {
         cudaEvent_t e;
@@ -515,7 +517,7 @@ int gmlrt_download(gmlrt_ctx* c, uint8_t* rgba, size_t rgba_bytes) {
         API_CU(cudaMemcpyAsync(c->pinned + off, r0->frame() + off, len, cudaMemcpyDeviceToHost, r0->stream()));
         API_CU(cudaEventRecord(c->ev_chunk[k], r0->stream()));
     }
-    const int n_threads = std::min(4, n_chunks);
+    const int n_threads = std::min(8, n_chunks);
     std::vector<cudaError_t> terr(n_threads, cudaSuccess);
     auto drain = [&](int t) {
         for (int k = t; k < n_chunks; k += n_threads) {

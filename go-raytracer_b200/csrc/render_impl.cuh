@@ -137,6 +137,7 @@ struct Counters {                  // device-resident, zeroed per trace
     unsigned long long shadow_tests, shadow_flops;   // credited: the reference's scan up to its first occluder (counting mode)
     unsigned long long exact_tests, exact_flops;     // executed second-phase tests and their table flops (counting mode)
     unsigned long long exact_tests_shadow;           // ... the part of exact_tests that k_exact_shadow ran
+    unsigned long long rays_hit_primary;             // camera rays that hit
 };
 
 template <typename R> struct Ray { R ox, oy, oz, dx, dy, dz; };
@@ -981,7 +982,7 @@ __global__ void __launch_bounds__(256) k_list_build(const __grid_constant__ BinP
             if (lane == 0) bins[b] = make_int2(base, padded);
         } else if (lane == 0) count[b] = padded;
     }
-    if (!FILL && tests && mine) atomicAdd(tests, mine);
+    if (!FILL && tests && lane == 0 && mine) atomicAdd(tests, mine * 32ull);      // (every lane counted the warp's rounds: one atomic per warp)
 }
 
 // one window of a ray's list: entries ent[0 .. cnt) (cnt a multiple of 4, at most GROUP), 4 entries per 16-byte load;
@@ -1928,7 +1929,7 @@ __global__ void __launch_bounds__(HITLIST_THREADS) k_hitlist(const __grid_consta
         }
         __syncthreads();                                       // s_warp / s_base are rewritten by the next block of rays
     }
-    if (threadIdx.x == 0 && n_hit) atomicAdd(&ctr->rays_hit, n_hit);
+    if (threadIdx.x == 0 && n_hit) { atomicAdd(&ctr->rays_hit, n_hit); if (level == 0) atomicAdd(&ctr->rays_hit_primary, n_hit); }
 }
 
 // rec slots
@@ -2403,6 +2404,7 @@ public:
         out.shadow_tests = c.shadow_tests; out.shadow_flops = c.shadow_flops; out.exact_tests = c.exact_tests; out.exact_flops = c.exact_flops; out.exact_tests_shadow = c.exact_tests_shadow;
         for (int k = 0; k < 3; k++) out.cull_by_family[k] = c.cull_tests[k];
         out.packet_tests = c.packet_tests;
+        out.rays_hit_primary = c.rays_hit_primary; out.list_tests = list_tests_;
         out.error = c.error; out.overflow = c.overflow;
 #ifdef GMLRT_DEBUG_PACKETS
         std::fprintf(stderr, "packets pivot: blocks %llu usable %llu offered %llu survivors %llu | axis: blocks %llu usable %llu offered %llu survivors %llu\n",

@@ -18,6 +18,7 @@ struct TraceTotals {                   // summed over the tiles a device rendere
     unsigned long long rays_primary = 0, rays_reflect = 0, rays_refract = 0, rays_shadow = 0, shadow_occluded = 0, rays_hit = 0;
     unsigned long long shadow_tests = 0, shadow_flops = 0;   // credited (reference scan order), counting mode
     unsigned long long cull_by_family[3] = {0, 0, 0}, packet_tests = 0;   // executed per-ray cull tests (GENERAL, PIVOT, AXIS) and per-warp packet tests
+    unsigned long long rays_hit_primary = 0, list_tests = 0;
     unsigned long long cull_tests = 0, exact_tests = 0, exact_flops = 0, exact_tests_shadow = 0;   // executed: first-phase (all pairs) and second-phase tests
     double ms_class[KC_COUNT] = {0, 0, 0, 0, 0, 0, 0, 0, 0};         // profiling mode: device time per kernel class
     unsigned long long launches_class[KC_COUNT] = {0, 0, 0, 0, 0, 0, 0, 0, 0};

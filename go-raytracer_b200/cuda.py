@@ -28,7 +28,8 @@ class Stats(ctypes.Structure):
                 ("cull_tests", ctypes.c_uint64), ("exact_tests", ctypes.c_uint64), ("flops_executed", ctypes.c_double),
                 ("ms_class", ctypes.c_double * 9), ("launches_class", ctypes.c_uint64 * 9),
                 ("packet_tests", ctypes.c_uint64), ("cull_tests_family", ctypes.c_uint64 * 3),
-                ("rays_hit", ctypes.c_uint64), ("exact_tests_shadow", ctypes.c_uint64)]
+                ("rays_hit", ctypes.c_uint64), ("exact_tests_shadow", ctypes.c_uint64),
+                ("rays_hit_primary", ctypes.c_uint64), ("list_tests", ctypes.c_uint64)]
 
     KERNEL_CLASSES = ("gen", "cull_primary", "cull_secondary", "cull_shadow", "shade", "resolve", "primary_points", "exact", "sort")
 

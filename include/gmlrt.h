@@ -197,6 +197,8 @@ typedef struct gmlrt_stats {
     uint64_t cull_tests_family[3]; /* cull_tests split by family: GENERAL (reflection / refraction rays), PIVOT, AXIS */
     uint64_t rays_hit;          /* closest-hit queries (primary + reflect + refract) that hit something = rays shaded */
     uint64_t exact_tests_shadow; /* the part of exact_tests run for shadow rays (counting mode) */
+    uint64_t rays_hit_primary;  /* camera rays that hit something (the level-0 part of rays_hit) */
+    uint64_t list_tests;        /* class x object tests of the last upload's candidate lists (not per frame) */
 } gmlrt_stats;
 
 /* Create a context on `n` devices (`devices` = CUDA ordinals; n >= 1).  With n > 1 the

@@ -20,7 +20,8 @@ class Stats(ctypes.Structure):
                 ("cull_tests", ctypes.c_uint64), ("exact_tests", ctypes.c_uint64), ("flops_executed", ctypes.c_double),
                 ("ms_class", ctypes.c_double * 9), ("launches_class", ctypes.c_uint64 * 9),
                 ("packet_tests", ctypes.c_uint64), ("cull_tests_family", ctypes.c_uint64 * 3),
-                ("rays_hit", ctypes.c_uint64), ("exact_tests_shadow", ctypes.c_uint64)]     # = gmlrt_stats, include/gmlrt.h
+                ("rays_hit", ctypes.c_uint64), ("exact_tests_shadow", ctypes.c_uint64),
+                ("rays_hit_primary", ctypes.c_uint64), ("list_tests", ctypes.c_uint64)]     # = gmlrt_stats, include/gmlrt.h
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
