@@ -191,6 +191,7 @@ int gmlrt_upload(gmlrt_ctx* c, const void* blob, size_t blob_bytes) {
     if (rc != GMLRT_OK) return fail(c, rc, err);
     int min_rows = c->scene.height;
     for (auto& r : c->r) {
+        r->set_share((int)c->r.size() * c->n_parts);
         rc = r->upload(c->scene, err);
         if (rc != GMLRT_OK) return fail(c, rc, err);
         min_rows = std::min(min_rows, r->max_rows_per_tile());

@@ -1480,48 +1480,47 @@ __global__ void __launch_bounds__(SORT_THREADS) k_sort_hist(const __grid_constan
     for (int b = threadIdx.x; b < nb; b += SORT_THREADS) if (h[b]) atomicAdd(&hist[b], h[b]);
 }
 
-// exclusive prefix of hist[0..nb) into cursor[0..nb); hist is cleared for the next use (one block; tiles of 4096
-// bins read as int4, so the 55k bins of the key sort are 14 coalesced rounds)
+// exclusive prefix of hist[0..nb) into cursor[0..nb); hist is cleared for the next use unless clear == 0.  One block: every
+// thread owns a contiguous run of bins (a multiple of 4, read as int4), sums it, the 1024 sums are scanned across the
+// block, then the thread walks its run again (now in L1) and writes the prefixes.  Two block barriers in all - the
+// tile-by-tile version this replaces paid four per 4096 bins and took 61 us for the 98k bins of the key sort.
 static __global__ void __launch_bounds__(1024) k_sort_scan(int nb, int* hist, int* cursor, int clear = 1) {
     __shared__ int warp_tot[32];
-    __shared__ int carry_s;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    if (tid == 0) carry_s = 0;
-    __syncthreads();
-    auto load_tile = [&](int tile) {
-        const int b = tile + 4 * tid;
+    const int seg = (((nb + 1023) >> 10) + 3) & ~3;
+    const int b0 = min(tid * seg, nb), b1 = min(b0 + seg, nb);
+    auto load4 = [&](int b) {
         int4 v = make_int4(0, 0, 0, 0);
         if (b + 3 < nb) v = *reinterpret_cast<const int4*>(hist + b);
         else { if (b < nb) v.x = hist[b]; if (b + 1 < nb) v.y = hist[b + 1]; if (b + 2 < nb) v.z = hist[b + 2]; }
         return v;
     };
-    int4 nxt = load_tile(0);
-    for (int tile = 0; tile < nb; tile += 4096) {
-        const int b = tile + 4 * tid;
-        const int4 v = nxt;
-        if (tile + 4096 < nb) nxt = load_tile(tile + 4096);   // in flight while this tile is scanned (the loop is latency-bound)
-        const int mine = v.x + v.y + v.z + v.w;
-        int incl = mine;
+    int mine = 0;
+    for (int b = b0; b < b1; b += 4) { const int4 v = load4(b); mine += v.x + v.y + v.z + v.w; }
+    int incl = mine;
 #pragma unroll
-        for (int off = 1; off < 32; off <<= 1) { const int u = __shfl_up_sync(0xffffffffu, incl, off); if (lane >= off) incl += u; }
-        if (lane == 31) warp_tot[wid] = incl;
-        __syncthreads();
-        if (wid == 0) {
-            int t = warp_tot[lane], ti = t;
+    for (int off = 1; off < 32; off <<= 1) { const int u = __shfl_up_sync(0xffffffffu, incl, off); if (lane >= off) incl += u; }
+    if (lane == 31) warp_tot[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        int t = warp_tot[lane], ti = t;
 #pragma unroll
-            for (int off = 1; off < 32; off <<= 1) { const int u = __shfl_up_sync(0xffffffffu, ti, off); if (lane >= off) ti += u; }
-            warp_tot[lane] = ti - t;                       // exclusive prefix of the warp totals
+        for (int off = 1; off < 32; off <<= 1) { const int u = __shfl_up_sync(0xffffffffu, ti, off); if (lane >= off) ti += u; }
+        warp_tot[lane] = ti - t;                           // exclusive prefix of the warp totals
+    }
+    __syncthreads();
+    int run = warp_tot[wid] + incl - mine;
+    for (int b = b0; b < b1; b += 4) {
+        const int4 v = load4(b);
+        if (b + 3 < nb) {
+            *reinterpret_cast<int4*>(cursor + b) = make_int4(run, run + v.x, run + v.x + v.y, run + v.x + v.y + v.z);
+            if (clear) *reinterpret_cast<int4*>(hist + b) = make_int4(0, 0, 0, 0);
+        } else {
+            if (b < nb) { cursor[b] = run; if (clear) hist[b] = 0; }
+            if (b + 1 < nb) { cursor[b + 1] = run + v.x; if (clear) hist[b + 1] = 0; }
+            if (b + 2 < nb) { cursor[b + 2] = run + v.x + v.y; if (clear) hist[b + 2] = 0; }
         }
-        __syncthreads();
-        const int carry = carry_s;
-        int run = carry + warp_tot[wid] + incl - mine;
-        if (b < nb) { cursor[b] = run; if (clear) hist[b] = 0; } run += v.x;
-        if (b + 1 < nb) { cursor[b + 1] = run; if (clear) hist[b + 1] = 0; } run += v.y;
-        if (b + 2 < nb) { cursor[b + 2] = run; if (clear) hist[b + 2] = 0; } run += v.z;
-        if (b + 3 < nb) { cursor[b + 3] = run; if (clear) hist[b + 3] = 0; } run += v.w;
-        __syncthreads();
-        if (tid == 1023) carry_s = run;                    // inclusive total through this tile
-        __syncthreads();
+        run += v.x + v.y + v.z + v.w;
     }
 }
 
@@ -1845,9 +1844,10 @@ __device__ __forceinline__ bool light_at(const DevLight<R>& L, V3<R> P, V3<R>& l
 
 
 template <typename R>
-__global__ void __launch_bounds__(256) k_gen(DevScene<R> sc, Level<R> lv, Counters* ctr, int y0, int rows, RowMap map) {
+__global__ void __launch_bounds__(256) k_gen(DevScene<R> sc, Level<R> lv, Counters* ctr, int y0, int rows, RowMap map, int* slots, int n_slots) {
     const int S = rows * sc.W * 4;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    for (int k = i; k < n_slots; k += gridDim.x * blockDim.x) slots[k] = 0;     // the frame's queue counters (one per launch that appends: trace_rows)
     if (i == 0) {
         for (int l = 1; l <= GMLRT_MAX_DEPTH; l++) ctr->count[l] = 0;
         for (int l = 0; l <= GMLRT_MAX_DEPTH; l++) ctr->hits[l] = 0;
@@ -2416,6 +2416,7 @@ public:
     int upload(const HostScene& S, std::string& err) override;
     int trace_rows(int v0, int v1, const RowMap& map, bool counting, std::string& err) override;
     void set_frame_target(uint8_t* target) override { frame_target_ = target; }
+    void set_share(int n_parts) override { share_ = std::max(1, n_parts); }
 
 private:
     // Scene arrays are bump-allocated from one arena that survives across uploads (cudaMalloc / cudaFree cost more than
@@ -2536,7 +2537,8 @@ private:
     std::vector<double> bound_;                                  // host: [n][4] bounding spheres (centre, radius) of the objects
     R* cull_general_ = nullptr; R* cull_eye_ = nullptr; std::vector<R*> cull_light_;
     CullFrame<R> frame_general_{}, frame_eye_{}; std::vector<CullFrame<R>> frame_light_;
-    int* shadow_counts_ = nullptr;
+    int share_ = 1;                                              // devices sharing the frame (set_share)
+    int* slots_ = nullptr; int n_slots_ = 0;                     // per-frame queue counters: per level 1 (closest candidates) + per light (shadow candidates, shadow rays)
     int build_cull_table(int family, const double* v, double offset_abs, R** out, CullFrame<R>& frame, std::string& err);
     std::vector<int> kind_host_;
 };
@@ -2801,7 +2803,15 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     sc.W = S.width; sc.H = S.height; sc.depth = S.depth; sc.vw = S.vw; sc.vh = S.vh;
     sc.cam_su = S.vw / (double)(S.width - 1); sc.cam_sv = S.vh / (double)(S.height - 1);
     // sort key of spawned rays: 6 k^2 direction cells per origin leaf, at most KEY_BINS_MAX bins in all
-    sc.key_k = (int)env_size("GMLRT_KEY_K", 4); sc.key_k = std::max(1, std::min(sc.key_k, 8));
+    // Direction cells per cube-map face edge: finer cells = shorter candidate lists per class, but a class should still hold
+    // a warp or so of rays, or the lanes of a warp walk different lists.  6 x 6 measured best for a whole 4K frame of
+    // 1024 spheres (6.09 -> 5.99 ms against 4 x 4); a device that renders 1 / n of the frame has 1 / n of the rays to bin.
+    {
+        const double spawned = 0.4 * 4.0 * (double)S.width * (double)S.height / (double)share_;
+        int k = 6;
+        while (k > 2 && spawned / ((double)n_regions * 6.0 * k * k) < 16.0) k--;
+        sc.key_k = (int)env_size("GMLRT_KEY_K", (size_t)k); sc.key_k = std::max(1, std::min(sc.key_k, 8));
+    }
     sc.key_shift = 0;
     while ((size_t)(((n_regions - 1) >> sc.key_shift) + 1) * 6 * sc.key_k * sc.key_k > (size_t)KEY_BINS_MAX) sc.key_shift++;
     key_nb_ = (((n_regions - 1) >> sc.key_shift) + 1) * 6 * sc.key_k * sc.key_k;
@@ -2829,17 +2839,18 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     }
     sort_nb_ = std::min(n_regions_ + 1, SORT_BINS_MAX); sort_shift_ = 0;        // class of a shadow ray: the region of the shaded point
     while (((n_regions_ - 1) >> sort_shift_) + 2 > sort_nb_) sort_shift_++;
-    sort_shadows_ = env_size("GMLRT_SORT_SHADOWS", 0) != 0;
+    // Shadow rays reach the cull in queue order: the order of the hits that spawned them, i.e. of neighbouring pixels or of
+    // sorted spawned rays, which mostly share a class already (4K spheres1024: sorting them again costs 0.4 ms and gains
+    // nothing).  With thousands of small objects a warp's 32 rays straddle many classes and every lane walks its own
+    // list: then the counting sort by class pays for itself (8K mixed4096: 143 -> 116 ms per frame).
+    {
+        const size_t mode = env_size("GMLRT_SORT_SHADOWS", 2);
+        sort_shadows_ = mode == 2 ? sc.n_leaves >= 2048 : mode != 0;
+    }
     primary_points_ = kRobustPrimary && env_size("GMLRT_PRIMARY_POINTS", 1) != 0;
     const double t_l0 = now();
     if ((rc = build_lists(S, err))) return rc;
     const double t_l1 = now();
-    {
-        void* p = nullptr;
-        if ((rc = scene_alloc(std::max<size_t>(S.lights.size(), 1) * sizeof(int), &p, err))) return rc;
-        shadow_counts_ = reinterpret_cast<int*>(p);
-        CU_TRY(cudaMemsetAsync(shadow_counts_, 0, std::max<size_t>(S.lights.size(), 1) * sizeof(int), stream_));
-    }
     const double t_c = now();
     CU_TRY(cudaStreamSynchronize(stream_));      // host vectors go out of scope
     const double t_d = now();
@@ -3131,6 +3142,8 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     const size_t sq_cap = max_cap * std::max(nl, 1);
     size_t o_sq = take(8 * sq_cap * sizeof(R)), o_skip = take(sq_cap * 4), o_key = take(sq_cap * 4), o_tgt = take(sq_cap * 4), o_first = take(sq_cap * 4), o_perm = take(sq_cap * 4), o_sort = take(2 * SHADOW_STREAMS * SORT_BINS_MAX * sizeof(int));
     size_t o_keysort = take(2 * (size_t)KEY_BINS_MAX * sizeof(int));
+    n_slots_ = depth_eff_ * (1 + 2 * std::max(nl, 0)) + 4;
+    size_t o_slots = take((size_t)n_slots_ * sizeof(int));
     size_t o_stage = take(RAY_WORDS * stage_cap * sizeof(R));         // spawned rays wait here until k_keysort_scatter stores them sorted
     const size_t cand_cap = std::min<size_t>((size_t)((double)S0_full * max_mult * cand_per_ray_), (size_t)2000000000);
     size_t o_cray = take(cand_cap * 4), o_cobj = take(cand_cap * 4), o_ct = take(cand_cap * sizeof(R)), o_ccount = take(256);
@@ -3153,10 +3166,11 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
         L.hits = (int*)(base + lo[l].hits); L.samp = l == 0 ? (R*)(base + lo[l].samp) : nullptr;
     }
     sq_.q = (R*)(base + o_sq); sq_.skip = (int*)(base + o_skip); sq_.key = (int*)(base + o_key); sq_.target = (int*)(base + o_tgt); sq_.cap = (int)sq_cap;
-    sq_.per_light = (int)max_cap; sq_.count = shadow_counts_; sq_.first = (int*)(base + o_first); sq_.perm = (int*)(base + o_perm);
+    sq_.per_light = (int)max_cap; sq_.count = nullptr; sq_.first = (int*)(base + o_first); sq_.perm = (int*)(base + o_perm);
     sort_hist_ = (int*)(base + o_sort); sort_cursor_ = sort_hist_ + SORT_BINS_MAX; sort_clear_ = true;
     key_hist_ = (int*)(base + o_keysort); key_cursor_ = key_hist_ + KEY_BINS_MAX;
     spawn_stage_ = (R*)(base + o_stage);
+    slots_ = (int*)(base + o_slots);
     cq_.ray = (int*)(base + o_cray); cq_.obj = (int*)(base + o_cobj); cq_.t = (void*)(base + o_ct); cq_.count = (int*)(base + o_ccount);
     cq_.cap = (int)cand_cap;
     for (int k = 0; k < SHADOW_STREAMS; k++) {
@@ -3219,19 +3233,19 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
     const bool have_spheres = sc_.kind_begin[K_SPHERE + 1] > 0;
     const bool have_simple = sc_.kind_begin[K_CSG] > sc_.kind_begin[K_SPHERE + 1], have_csg = sc_.n_leaves > sc_.kind_begin[K_CSG] || sc_.n_leaves == 0;
     const int n_exact_flavours = (have_spheres ? 1 : 0) + (have_simple ? 1 : 0) + (have_csg ? 1 : 0);
-    auto exact_closest = [&](int l, bool count) -> int {
+    auto exact_closest = [&](int l, bool count, const CandQueue& cq_l) -> int {
         const int grid = sms_ * 16;
         if (have_spheres) {
-            if (count) k_exact_closest<R, false, true, EXACT_SPHERES><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
-            else k_exact_closest<R, false, false, EXACT_SPHERES><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
+            if (count) k_exact_closest<R, false, true, EXACT_SPHERES><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_l, ctr_, cam);
+            else k_exact_closest<R, false, false, EXACT_SPHERES><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_l, ctr_, cam);
         }
         if (have_simple) {
-            if (count) k_exact_closest<R, false, true, EXACT_SIMPLE><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
-            else k_exact_closest<R, false, false, EXACT_SIMPLE><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
+            if (count) k_exact_closest<R, false, true, EXACT_SIMPLE><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_l, ctr_, cam);
+            else k_exact_closest<R, false, false, EXACT_SIMPLE><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_l, ctr_, cam);
         }
         if (have_csg) {
-            if (count) k_exact_closest<R, false, true, EXACT_CSG><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
-            else k_exact_closest<R, false, false, EXACT_CSG><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
+            if (count) k_exact_closest<R, false, true, EXACT_CSG><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_l, ctr_, cam);
+            else k_exact_closest<R, false, false, EXACT_CSG><<<grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_l, ctr_, cam);
         }
         totals_.launches += n_exact_flavours - 1;
         return GMLRT_OK;
@@ -3251,13 +3265,16 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
         cam.y0 = ty;
         const int S = rows * W * 4;
         MARK(KC_GEN);
-        k_gen<R><<<(S + 255) / 256, 256, 0, stream_>>>(sc_, levels_[0], ctr_, ty, rows, map);
+        k_gen<R><<<(S + 255) / 256, 256, 0, stream_>>>(sc_, levels_[0], ctr_, ty, rows, map, slots_, n_slots_);
         totals_.launches++;
         totals_.rays_primary += (unsigned long long)S;
         for (int l = 0; l < depth_eff_; l++) {
             const int cap_blocks = (levels_[l].cap + SHADE_THREADS - 1) / SHADE_THREADS;
             const int exact_grid = sms_ * 16;
-            CU_TRY(cudaMemsetAsync(cq_.count, 0, 2 * sizeof(int), stream_));
+            // every launch of the frame that counts into a queue has its own counter (zeroed by k_gen): no memsets between launches
+            int* const slot = slots_ + (size_t)l * (1 + 2 * sc_.n_lights);
+            CandQueue cq_l = cq_; cq_l.count = slot;
+            ShadowQueue<R> sq_l = sq_; sq_l.count = slot + 1 + sc_.n_lights;
             if (sort_clear_) {
                 CU_TRY(cudaMemsetAsync(sort_hist_, 0, 2 * SHADOW_STREAMS * SORT_BINS_MAX * sizeof(int), stream_));
                 CU_TRY(cudaMemsetAsync(key_hist_, 0, KEY_BINS_MAX * sizeof(int), stream_));
@@ -3274,38 +3291,38 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
                 MARK(KC_CLOSEST_PRIMARY);
                 CameraSource<R> cams{levels_[l], W, ty, map, TILE_W, TILE_H, (W + TILE_W - 1) / TILE_W};
                 if (resident_) k_cull<R, CULL_PIVOT, CameraSource<R>, true><<<l_primary_.grid, CULL_THREADS, l_primary_.smem, stream_>>>(
-                    cams, &ctr_->count[l], cull_eye_, frame_eye_, sc_.n_cull, lists_camera_, cq_, ctr_);
+                    cams, &ctr_->count[l], cull_eye_, frame_eye_, sc_.n_cull, lists_camera_, cq_l, ctr_);
                 else k_cull<R, CULL_PIVOT, CameraSource<R>, false><<<l_primary_.grid, CULL_THREADS, 0, stream_>>>(
-                    cams, &ctr_->count[l], cull_eye_, frame_eye_, sc_.n_cull, lists_camera_, cq_, ctr_);
+                    cams, &ctr_->count[l], cull_eye_, frame_eye_, sc_.n_cull, lists_camera_, cq_l, ctr_);
                 MARK(KC_EXACT);
                 if (kRobustPrimary) {
                     // float32 spheres inline; then the double-precision pass: other kinds + the spheres the first pass deferred
                     if (counting) {
-                        if (have_spheres) k_exact_closest<R, kRobustPrimary, true, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
-                        k_exact_closest<R, kRobustPrimary, true, EXACT_REST><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
+                        if (have_spheres) k_exact_closest<R, kRobustPrimary, true, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_l, ctr_, cam);
+                        k_exact_closest<R, kRobustPrimary, true, EXACT_REST><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_l, ctr_, cam);
                     } else {
-                        if (have_spheres) k_exact_closest<R, kRobustPrimary, false, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
-                        k_exact_closest<R, kRobustPrimary, false, EXACT_REST><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_, ctr_, cam);
+                        if (have_spheres) k_exact_closest<R, kRobustPrimary, false, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_l, ctr_, cam);
+                        k_exact_closest<R, kRobustPrimary, false, EXACT_REST><<<exact_grid, EXACT_THREADS, 0, stream_>>>(sc_, levels_[l], cq_l, ctr_, cam);
                     }
                     totals_.launches += have_spheres ? 1 : 0;
                 } else {
-                    int erc = exact_closest(l, counting);
+                    int erc = exact_closest(l, counting, cq_l);
                     if (erc) return erc;
                 }
             } else {
                 MARK(KC_CLOSEST);
                 SpawnSource<R> spws{levels_[l]};
                 if (resident_) k_cull<R, CULL_GENERAL, SpawnSource<R>, true><<<l_closest_.grid, CULL_THREADS, l_closest_.smem, stream_>>>(
-                    spws, &ctr_->count[l], cull_general_, frame_general_, sc_.n_cull, lists_spawn_, cq_, ctr_);
+                    spws, &ctr_->count[l], cull_general_, frame_general_, sc_.n_cull, lists_spawn_, cq_l, ctr_);
                 else k_cull<R, CULL_GENERAL, SpawnSource<R>, false><<<l_closest_.grid, CULL_THREADS, 0, stream_>>>(
-                    spws, &ctr_->count[l], cull_general_, frame_general_, sc_.n_cull, lists_spawn_, cq_, ctr_);
+                    spws, &ctr_->count[l], cull_general_, frame_general_, sc_.n_cull, lists_spawn_, cq_l, ctr_);
                 MARK(KC_EXACT);
-                int erc = exact_closest(l, counting);
+                int erc = exact_closest(l, counting, cq_l);
                 if (erc) return erc;
             }
-            if (sizeof(R) == 8) k_closest_order<R><<<exact_grid, 256, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
+            if (sizeof(R) == 8) k_closest_order<R><<<exact_grid, 256, 0, stream_>>>(sc_, levels_[l], cq_l, ctr_);
             else totals_.launches--;
-            if (!sc_.pickless) k_closest_pick<R><<<exact_grid, 256, 0, stream_>>>(sc_, levels_[l], cq_, ctr_);
+            if (!sc_.pickless) k_closest_pick<R><<<exact_grid, 256, 0, stream_>>>(sc_, levels_[l], cq_l, ctr_);
             else totals_.launches--;
             totals_.launches += 3;
             {   // hit list of the level; misses of levels >= 1 are finished here
@@ -3330,7 +3347,7 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             MARK(KC_SHADE);
             auto shade = sc_.pickless == 1 ? k_shade<R, sizeof(R) == 4 ? 1 : 0> : sc_.pickless ? k_shade<R, sizeof(R) == 4 ? 2 : 0> : k_shade<R, 0>;
             shade<<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
-                sc_, levels_[l], spawn ? levels_[l + 1] : levels_[l], sq_, occl_[l], ctr_, l, spawn ? 1 : 0,
+                sc_, levels_[l], spawn ? levels_[l + 1] : levels_[l], sq_l, occl_[l], ctr_, l, spawn ? 1 : 0,
                 spawn ? (sort_spawned_ ? spawn_stage_ : levels_[l + 1].ray) : nullptr, (primary_points_ && l == 0) ? 1 : 0);
             totals_.launches += 2;
             // shadow queries of this level: on the shadow stream, overlapping the next level's closest-hit pipeline
@@ -3342,46 +3359,45 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
                 const bool axis = frame_light_[li].family == CULL_AXIS;
                 const int sk = li % nss;
                 cudaStream_t ss = two_streams ? shadow_stream_[sk] : stream_;
-                const CandQueue& cqs = two_streams ? cq_shadow_[sk] : cq_;
+                CandQueue cqs = two_streams ? cq_shadow_[sk] : cq_;
+                cqs.count = slot + 1 + li;
                 int* const s_hist = sort_hist_sh_[sk]; int* const s_cursor = sort_cursor_sh_[sk];
-                ShadowSource<R> ssrc{sq_, li * sq_.per_light, sort_shadows_ ? sq_.perm : nullptr, sort_shift_, sort_nb_};
-                CU_TRY(cudaMemsetAsync(cqs.count, 0, 2 * sizeof(int), ss));
+                ShadowSource<R> ssrc{sq_l, li * sq_.per_light, sort_shadows_ ? sq_.perm : nullptr, sort_shift_, sort_nb_};
                 if (sort_shadows_) {       // optional: the shadow rays of neighbouring pixels mostly share a class already
                     MARK(KC_SORT);
-                    k_sort_hist<R><<<sms_ * 4, SORT_THREADS, 0, ss>>>(sq_, li, sort_shift_, sort_nb_, s_hist);
+                    k_sort_hist<R><<<sms_ * 4, SORT_THREADS, 0, ss>>>(sq_l, li, sort_shift_, sort_nb_, s_hist);
                     k_sort_scan<<<1, 1024, 0, ss>>>(sort_nb_, s_hist, s_cursor);
-                    k_sort_scatter<R><<<sms_ * 4, SORT_THREADS, 0, ss>>>(sq_, li, sort_shift_, sort_nb_, s_cursor);
+                    k_sort_scatter<R><<<sms_ * 4, SORT_THREADS, 0, ss>>>(sq_l, li, sort_shift_, sort_nb_, s_cursor);
                     totals_.launches += 3;
                 }
                 MARK(KC_SHADOW);
                 const BinLists& bls = lists_light_[li];
                 if (axis) {
                     if (resident_) k_cull<R, CULL_AXIS, ShadowSource<R>, true><<<l_shadow_axis_.grid, CULL_THREADS, l_shadow_axis_.smem, ss>>>(
-                        ssrc, &shadow_counts_[li], cull_light_[li], frame_light_[li], sc_.n_cull, bls, cqs, ctr_);
+                        ssrc, &sq_l.count[li], cull_light_[li], frame_light_[li], sc_.n_cull, bls, cqs, ctr_);
                     else k_cull<R, CULL_AXIS, ShadowSource<R>, false><<<l_shadow_axis_.grid, CULL_THREADS, 0, ss>>>(
-                        ssrc, &shadow_counts_[li], cull_light_[li], frame_light_[li], sc_.n_cull, bls, cqs, ctr_);
+                        ssrc, &sq_l.count[li], cull_light_[li], frame_light_[li], sc_.n_cull, bls, cqs, ctr_);
                 } else {
                     if (resident_) k_cull<R, CULL_PIVOT, ShadowSource<R>, true><<<l_shadow_pivot_.grid, CULL_THREADS, l_shadow_pivot_.smem, ss>>>(
-                        ssrc, &shadow_counts_[li], cull_light_[li], frame_light_[li], sc_.n_cull, bls, cqs, ctr_);
+                        ssrc, &sq_l.count[li], cull_light_[li], frame_light_[li], sc_.n_cull, bls, cqs, ctr_);
                     else k_cull<R, CULL_PIVOT, ShadowSource<R>, false><<<l_shadow_pivot_.grid, CULL_THREADS, 0, ss>>>(
-                        ssrc, &shadow_counts_[li], cull_light_[li], frame_light_[li], sc_.n_cull, bls, cqs, ctr_);
+                        ssrc, &sq_l.count[li], cull_light_[li], frame_light_[li], sc_.n_cull, bls, cqs, ctr_);
                 }
                 MARK(KC_EXACT);
                 const int sbase = li * sq_.per_light;
                 if (counting) {
-                    if (have_spheres) k_exact_shadow<R, true, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_, sbase, cqs, ctr_, occl_[l]);
-                    if (have_simple) k_exact_shadow<R, true, EXACT_SIMPLE><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_, sbase, cqs, ctr_, occl_[l]);
-                    if (have_csg) k_exact_shadow<R, true, EXACT_CSG><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_, sbase, cqs, ctr_, occl_[l]);
-                    k_shadow_finish<R, true><<<wide, 256, 0, ss>>>(sc_, sq_, li, occl_[l], ctr_);
+                    if (have_spheres) k_exact_shadow<R, true, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_l, sbase, cqs, ctr_, occl_[l]);
+                    if (have_simple) k_exact_shadow<R, true, EXACT_SIMPLE><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_l, sbase, cqs, ctr_, occl_[l]);
+                    if (have_csg) k_exact_shadow<R, true, EXACT_CSG><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_l, sbase, cqs, ctr_, occl_[l]);
+                    k_shadow_finish<R, true><<<wide, 256, 0, ss>>>(sc_, sq_l, li, occl_[l], ctr_);
                 } else {                                   // the exact kernels set the occlusion flags themselves
-                    if (have_spheres) k_exact_shadow<R, false, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_, sbase, cqs, ctr_, occl_[l]);
-                    if (have_simple) k_exact_shadow<R, false, EXACT_SIMPLE><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_, sbase, cqs, ctr_, occl_[l]);
-                    if (have_csg) k_exact_shadow<R, false, EXACT_CSG><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_, sbase, cqs, ctr_, occl_[l]);
+                    if (have_spheres) k_exact_shadow<R, false, EXACT_SPHERES><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_l, sbase, cqs, ctr_, occl_[l]);
+                    if (have_simple) k_exact_shadow<R, false, EXACT_SIMPLE><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_l, sbase, cqs, ctr_, occl_[l]);
+                    if (have_csg) k_exact_shadow<R, false, EXACT_CSG><<<exact_grid, EXACT_THREADS, 0, ss>>>(sc_, sq_l, sbase, cqs, ctr_, occl_[l]);
                     totals_.launches--;
                 }
                 totals_.launches += n_exact_flavours - 1;
                 totals_.launches += 3;
-                CU_TRY(cudaMemsetAsync(&shadow_counts_[li], 0, sizeof(int), ss));
             }
             if (two_streams) for (int k = 0; k < nss; k++) CU_TRY(cudaEventRecord(ev_shadow_[k][l], shadow_stream_[k]));
         }

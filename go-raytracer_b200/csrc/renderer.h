@@ -53,6 +53,8 @@ public:
     virtual int trace_rows(int v0, int v1, const RowMap& map, bool counting, std::string& err) = 0;
     // where the level-0 k_resolve stores its pixels: this device's own frame (default) or a peer-mapped frame of the gathering device
     virtual void set_frame_target(uint8_t* target) = 0;
+    // how many devices share the frame (before upload): a device that renders 1 / n of the rays sorts them into coarser classes
+    virtual void set_share(int n_parts) = 0;
     // after the stream is synchronised: fetch counters accumulated since reset_totals()
     virtual int fetch_totals(TraceTotals& out, std::string& err) = 0;
     virtual void reset_totals() = 0;
