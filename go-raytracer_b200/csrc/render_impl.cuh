@@ -851,6 +851,7 @@ struct BinParams {
     // the objects as this family's per-ray test sees them, [n][4]: centre relative to the pivot (PIVOT), absolute (GENERAL),
     // or (u, v, front end along the rays) (AXIS); then the radius with every margin of the per-ray test folded in (inf = unbounded)
     const double* obj; int n_objects;
+    const float4* objf;                 // the same records in float32, radius grown by another 0.1 % + 1e-4: the screening pass (null: none)
     double pivot[3];                    // PIVOT families: the eye / the light
     double e1[3], e2[3], axis[3];       // AXIS: the frame the device projects with
     // BIN_SPAWN: bin = region * n_cells + cell;  BIN_SHADOW_*: bin = region (the last bin collects invalid keys: no bound)
@@ -956,25 +957,87 @@ __device__ __forceinline__ bool bin_keeps(const BinParams& p, const BinBound& B,
     return A * A * (1.0 + 1e-12) >= B.cos_t * B.cos_t * q;
 }
 
-// one warp per bin: count (FILL = false) or write (FILL = true) the bin's list
+// The same question in float32, answered "no" only when it is no by a wide margin (cone widened by 1e-3 rad, radii by
+// 0.1 %, rounding allowances on every comparison): almost every class x object pair is far from the bound, and
+// only what passes here is looked at in double.
+struct BinBoundF { float ox, oy, oz, rho, ax, ay, az, cos_t, sin_t, reach; bool general, usable, use; };
+__device__ __forceinline__ BinBoundF bin_bound_f(const BinParams& p, const BinBound& B) {
+    BinBoundF F = {};
+    F.use = p.kind != BIN_SHADOW_AXIS && p.objf != nullptr;
+    F.general = p.kind == BIN_SPAWN; F.usable = B.usable;
+    if (!F.use || !B.usable) return F;
+    F.ox = F.general ? (float)B.ox : 0.f; F.oy = F.general ? (float)B.oy : 0.f; F.oz = F.general ? (float)B.oz : 0.f;
+    F.rho = F.general ? (float)(B.rho * 1.001 + 1e-4 + 1e-6 * (fabs(B.ox) + fabs(B.oy) + fabs(B.oz))) : 0.f;
+    F.ax = (float)B.ax; F.ay = (float)B.ay; F.az = (float)B.az;
+    F.cos_t = (float)(B.cos_t * 0.9999995 - B.sin_t * 1e-3 - 1e-6);          // cos / sin of (theta + 1e-3)
+    F.sin_t = (float)(B.sin_t * 0.9999995 + B.cos_t * 1e-3 + 1e-6);
+    F.reach = F.general ? INFINITY : (float)(B.rho * 1.001 + 1e-3);
+    if (!(F.cos_t > 0.f)) F.usable = false;                                  // a cone that wide: everything goes to the double test
+    return F;
+}
+__device__ __forceinline__ bool bin_maybe(const BinParams& p, const BinBoundF& F, int o) {
+    if (!F.use || !F.usable) return true;
+    const float4 c = p.objf[o];
+    if (!(c.w < INFINITY)) return true;
+    const float px = c.x - F.ox, py = c.y - F.oy, pz = c.z - F.oz;
+    const float rr = c.w + F.rho;
+    const float pp = px * px + py * py + pz * pz;
+    const float q = pp - rr * rr;
+    if (!(q > 1e-3f * pp)) return true;                  // close to (inside) the sphere: decide in double
+    float dot = px * F.ax + py * F.ay + pz * F.az;
+    if (!F.general) {
+        const float far = F.reach + rr;
+        if (pp > far * far * 1.001f) return false;
+        dot = fabsf(dot);
+    }
+    const float A = dot + F.sin_t * rr + 4e-6f * (fabsf(px) + fabsf(py) + fabsf(pz));
+    if (A < 0.f) return false;
+    return !(A * A * 1.001f < F.cos_t * F.cos_t * q);
+}
+
+// one warp per bin: count (FILL = false) or write (FILL = true) the bin's list.  Objects are screened 32 at a time in
+// float32; the few that pass wait in a per-warp queue until 32 of them can take the double-precision test side by side
+// (tested where they pass, one or two lanes at a time, the double path would run for nearly every round of 32).
 template <bool FILL>
 __global__ void __launch_bounds__(256) k_list_build(const __grid_constant__ BinParams p, int* count, const int* first, int2* bins, uint32_t* entry,
                                                     uint32_t rec_bytes, unsigned long long* tests) {
+    __shared__ int s_queue[8][64];
     const int lane = threadIdx.x & 31;
+    int* const qu = s_queue[threadIdx.x >> 5];
     const int warps = (gridDim.x * blockDim.x) >> 5;
     const unsigned lt = (1u << lane) - 1u;
     unsigned long long mine = 0;
     for (int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < p.n_bins; b += warps) {
         const BinBound B = bin_bound(p, b);
-        int n = 0;
+        const BinBoundF F = bin_bound_f(p, B);
+        int n = 0, qn = 0;
         const int base = FILL ? first[b] : 0;
-        for (int o0 = 0; o0 < p.n_objects; o0 += 32) {
-            const int o = o0 + lane;
-            const bool keep = o < p.n_objects && bin_keeps(p, B, o);
+        auto drain = [&](int cnt) {                       // the double test for queue entries [0, cnt), cnt <= 32
+            const int o = lane < cnt ? qu[lane] : -1;
+            const bool keep = o >= 0 && bin_keeps(p, B, o);
             const unsigned bal = __ballot_sync(0xffffffffu, keep);
             if (FILL && keep) entry[base + n + __popc(bal & lt)] = (uint32_t)o * rec_bytes;
             n += __popc(bal);
+        };
+        for (int o0 = 0; o0 < p.n_objects; o0 += 32) {
+            const int o = o0 + lane;
+            const bool maybe = o < p.n_objects && bin_maybe(p, F, o);
+            const unsigned bal = __ballot_sync(0xffffffffu, maybe);
+            if (maybe) qu[qn + __popc(bal & lt)] = o;
+            qn += __popc(bal);
+            __syncwarp();
+            if (qn >= 32) {
+                drain(32);
+                __syncwarp();
+                const int rest = lane < qn - 32 ? qu[32 + lane] : 0;
+                __syncwarp();
+                if (lane < qn - 32) qu[lane] = rest;
+                qn -= 32;
+                __syncwarp();
+            }
         }
+        if (qn) drain(qn);
+        __syncwarp();
         mine += (unsigned long long)((p.n_objects + 31) / 32);
         const int padded = (n + 3) & ~3;
         if (FILL) {
@@ -985,8 +1048,6 @@ __global__ void __launch_bounds__(256) k_list_build(const __grid_constant__ BinP
     if (!FILL && tests && lane == 0 && mine) atomicAdd(tests, mine * 32ull);      // (every lane counted the warp's rounds: one atomic per warp)
 }
 
-// one window of a ray's list: entries ent[0 .. cnt) (cnt a multiple of 4, at most GROUP), 4 entries per 16-byte load;
-// test j lands in bit 31 - j of lo (j < 32) / hi (set = object survives)
 // A cull record by its byte offset in the family's table.  SMEM: `tab` is the table's 32-bit shared-memory address, so the
 // load is ld.shared with the base folded in as an immediate (through a generic pointer every load paid an extra
 // add of the shared window's base); else `gtab` is the table in global memory, read through L1.
@@ -1521,6 +1582,57 @@ static __global__ void __launch_bounds__(1024) k_sort_scan(int nb, int* hist, in
             if (b + 2 < nb) { cursor[b + 2] = run + v.x + v.y; if (clear) hist[b + 2] = 0; }
         }
         run += v.x + v.y + v.z + v.w;
+    }
+}
+
+// The same scan over many bins (the key sort has 10^5 - 5 10^5): one block per tile of SCAN_TILE bins, all co-resident
+// (the host launches at most one block per SM).  A block sums its tile, publishes the sum with a flag that carries the
+// launch's epoch (so nothing needs resetting), waits for the sums of the tiles before it and writes its prefixes.
+constexpr int SCAN_TILE = 4096;
+static __global__ void __launch_bounds__(1024) k_sort_scan_tiles(int nb, int* hist, int* cursor, int clear, volatile int* tile_sum, volatile int* tile_flag, int epoch) {
+    __shared__ int warp_tot[32];
+    __shared__ int s_base;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int b = blockIdx.x * SCAN_TILE + 4 * tid;
+    int4 v = make_int4(0, 0, 0, 0);
+    if (b + 3 < nb) v = *reinterpret_cast<const int4*>(hist + b);
+    else { if (b < nb) v.x = hist[b]; if (b + 1 < nb) v.y = hist[b + 1]; if (b + 2 < nb) v.z = hist[b + 2]; }
+    const int mine = v.x + v.y + v.z + v.w;
+    int incl = mine;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) { const int u = __shfl_up_sync(0xffffffffu, incl, off); if (lane >= off) incl += u; }
+    if (lane == 31) warp_tot[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        int t = warp_tot[lane], ti = t;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) { const int u = __shfl_up_sync(0xffffffffu, ti, off); if (lane >= off) ti += u; }
+        warp_tot[lane] = ti - t;
+        if (lane == 31) {                                  // this tile's total: publish, then the flag
+            tile_sum[blockIdx.x] = ti;
+            __threadfence();
+            tile_flag[blockIdx.x] = epoch;
+        }
+        // the tiles before this one: lane k looks after tiles k, k + 32, ...
+        int before = 0;
+        for (int t0 = lane; t0 < (int)blockIdx.x; t0 += 32) {
+            while (tile_flag[t0] != epoch) { }
+            __threadfence();
+            before += tile_sum[t0];
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) before += __shfl_xor_sync(0xffffffffu, before, off);
+        if (lane == 0) s_base = before;
+    }
+    __syncthreads();
+    int run = s_base + warp_tot[wid] + incl - mine;
+    if (b + 3 < nb) {
+        *reinterpret_cast<int4*>(cursor + b) = make_int4(run, run + v.x, run + v.x + v.y, run + v.x + v.y + v.z);
+        if (clear) *reinterpret_cast<int4*>(hist + b) = make_int4(0, 0, 0, 0);
+    } else {
+        if (b < nb) { cursor[b] = run; if (clear) hist[b] = 0; }
+        if (b + 1 < nb) { cursor[b + 1] = run + v.x; if (clear) hist[b + 1] = 0; }
+        if (b + 2 < nb) { cursor[b + 2] = run + v.x + v.y; if (clear) hist[b + 2] = 0; }
     }
 }
 
@@ -2374,6 +2486,8 @@ public:
         CU_TRY(cudaMemcpyToSymbol(c_pcg_jump, tab, sizeof tab));
         CU_TRY(cudaMalloc(&ctr_, sizeof(Counters)));
         CU_TRY(cudaMemset(ctr_, 0, sizeof(Counters)));
+        CU_TRY(cudaMalloc(&scan_tiles_, 512 * sizeof(int)));
+        CU_TRY(cudaMemset(scan_tiles_, 0, 512 * sizeof(int)));
         const int smem_max = 200 * 1024;
         auto allow = [&](auto kernel) -> int { CU_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max)); return GMLRT_OK; };
         int rc;
@@ -2463,6 +2577,8 @@ private:
         if (frame_) cudaFree(frame_);
         if (ids_) cudaFree(ids_);
         if (ctr_) cudaFree(ctr_);
+        if (scan_tiles_) cudaFree(scan_tiles_);
+        scan_tiles_ = nullptr;
         for (cudaEvent_t e : ev_pool_) cudaEventDestroy(e);
         ev_pool_.clear();
         for (cudaEvent_t e : ev_shade_) cudaEventDestroy(e);
@@ -2528,6 +2644,14 @@ private:
     bool primary_points_ = false;                                // throughput mode: k_primary_points before the level-0 k_shade (GMLRT_PRIMARY_POINTS)
     bool sort_shadows_ = false;                                  // GMLRT_SORT_SHADOWS: order the shadow rays of a light by class before the cull
     int build_lists(const HostScene& S, std::string& err);
+    // exclusive scan of a histogram on `st`: tiles across co-resident blocks when there are many bins, else one block
+    void launch_scan(int nb, int* hist, int* cursor, int clear, cudaStream_t st) {
+        const int tiles = (nb + SCAN_TILE - 1) / SCAN_TILE;
+        if (tiles > 2 && tiles <= sms_ && scan_tiles_ && st == stream_) {
+            k_sort_scan_tiles<<<tiles, 1024, 0, st>>>(nb, hist, cursor, clear, scan_tiles_, scan_tiles_ + 256, ++scan_epoch_);
+        } else k_sort_scan<<<1, 1024, 0, st>>>(nb, hist, cursor, clear);
+    }
+    int* scan_tiles_ = nullptr; int scan_epoch_ = 0;             // tile sums + flags of k_sort_scan_tiles (main stream only)
     CandQueue cq_{}; int cand_per_ray_ = 4, tile_shrink_ = 0; unsigned long long scene_sig_ = ~0ull, planned_sig_ = ~0ull - 1; int planned_rows_full_ = 0;
     int* sort_hist_ = nullptr; int* sort_cursor_ = nullptr; int sort_nb_ = 2, sort_shift_ = 0, n_regions_ = 1; bool sort_clear_ = true;
     int* key_hist_ = nullptr; int* key_cursor_ = nullptr; int key_nb_ = 6;      // spawned rays by (origin leaf, direction cell); cleared with sort_hist_
@@ -3006,6 +3130,15 @@ int Renderer<R>::build_lists(const HostScene& S, std::string& err) {
         double* d_rec = nullptr;
         prc = to_device(rec, &d_rec, err);
         p.obj = d_rec;
+        std::vector<float4> recf((size_t)std::max(n, 1));
+        for (int d = 0; d < n; d++) {
+            const double* o = &rec[(size_t)d * 4];
+            const double mag = std::fabs(o[0]) + std::fabs(o[1]) + std::fabs(o[2]);
+            recf[d] = make_float4((float)o[0], (float)o[1], (float)o[2], std::isfinite(o[3]) ? (float)(o[3] * 1.001 + 1e-4 + 1e-6 * mag) : INFINITY);
+        }
+        float4* d_recf = nullptr;
+        if (!prc) prc = to_device(recf, &d_recf, err);
+        p.objf = d_recf;
         return p;
     };
     lists_light_.assign(S.lights.size(), BinLists{});
@@ -3048,7 +3181,7 @@ int Renderer<R>::build_lists(const HostScene& S, std::string& err) {
         ps.count = (int*)pc; ps.first = (int*)pf;
         const int grid = std::min((ps.p.n_bins + 7) / 8, sms_ * 32);
         k_list_build<false><<<grid, 256, 0, stream_>>>(ps.p, ps.count, nullptr, nullptr, nullptr, 0u, list_tests_dev_);
-        k_sort_scan<<<1, 1024, 0, stream_>>>(ps.p.n_bins, ps.count, ps.first, 0);
+        launch_scan(ps.p.n_bins, ps.count, ps.first, 0, stream_);
         CU_TRY(cudaMemcpyAsync(&tails[2 * s], ps.count + ps.p.n_bins - 1, sizeof(int), cudaMemcpyDeviceToHost, stream_));
         CU_TRY(cudaMemcpyAsync(&tails[2 * s + 1], ps.first + ps.p.n_bins - 1, sizeof(int), cudaMemcpyDeviceToHost, stream_));
     }
@@ -3283,7 +3416,7 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             if (l > 0 && sort_spawned_) {                  // rays by (origin leaf, direction cell): keys in lv.hit, records in the staging buffer
                 MARK(KC_SORT);
                 k_keysort_hist<<<sms_ * 8, 256, 0, stream_>>>(levels_[l].hit, &ctr_->count[l], key_nb_, key_hist_);
-                k_sort_scan<<<1, 1024, 0, stream_>>>(key_nb_, key_hist_, key_cursor_);
+                launch_scan(key_nb_, key_hist_, key_cursor_, 1, stream_);
                 k_keysort_scatter<R><<<sms_ * 8, 256, 0, stream_>>>(levels_[l].hit, &ctr_->count[l], key_nb_, key_cursor_, spawn_stage_, levels_[l].ray);
                 totals_.launches += 3;
             }
