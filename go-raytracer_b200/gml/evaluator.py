@@ -270,6 +270,9 @@ def _tname(t):
 
 # ------------------------------------------------------------------ evaluator
 
+_NO_ENV = object()      # frame marker: nothing to restore when the frame ends
+
+
 class EvalState:
     """evaluator.go:43-50.  ``Render`` is the drop-in hook: a callable
     ``(state, RenderArgs) -> None`` that raises on error."""
@@ -281,6 +284,7 @@ class EvalState:
         self.Env = {}
         self.Render = None
         self.Debugger = None
+        self._frames = None       # Eval's explicit work stack while a program runs
 
     # -- parsing ----------------------------------------------------------
     def Parse(self, text):
@@ -327,8 +331,29 @@ class EvalState:
 
     # -- evaluation -------------------------------------------------------
     def Eval(self, program):
-        for tok in program:
-            self.EvalOneStep(tok)
+        """evalProgram (evaluator.go:345-363).  The reference recurses through EvalClosure on Go's growable stack; here
+        closure calls are frames on an explicit work stack, so GML recursion (large.gml nests thousands of applies)
+        is not bounded by the Python stack: `apply` / `if` push a frame (EvalClosure below) and this loop runs it."""
+        outer = self._frames
+        frames = self._frames = [[program, 0, _NO_ENV]]
+        try:
+            while frames:
+                fr = frames[-1]
+                code, pc = fr[0], fr[1]
+                if pc >= len(code):
+                    frames.pop()
+                    if fr[2] is not _NO_ENV:
+                        self.Env = fr[2]                      # EvalClosure's deferred restore (evaluator.go:433-438)
+                    continue
+                fr[1] = pc + 1
+                self.EvalOneStep(code[pc])
+        except BaseException:
+            for fr in reversed(frames):                       # the deferred restores run on the way out of an error too
+                if fr[2] is not _NO_ENV:
+                    self.Env = fr[2]
+            raise
+        finally:
+            self._frames = outer
 
     def EvalOneStep(self, tok):
         self.CurrToken = tok
@@ -368,7 +393,16 @@ class EvalState:
         if self.Debugger is not None and self.Debugger() == 1:
             raise GMLError("evaluation was aborted by the user")
 
+    def CallClosure(self, closure):
+        """`apply` / `if` (evaluator.go:604-610, 1005-1019): nothing follows the call in the builtin, so inside Eval's loop
+        the closure becomes a new frame instead of a Python-level recursion."""
+        if self._frames is None:
+            return self.EvalClosure(closure)
+        self._frames.append([closure.code, 0, self.Env])
+        self.Env = dict(closure.env)
+
     def EvalClosure(self, closure):
+        """evaluator.go:433-438: runs the closure to completion, then restores the environment."""
         saved = self.Env
         self.Env = dict(closure.env)
         try:
@@ -522,14 +556,14 @@ def _sqrt(e, x):
 
 
 def _apply(e):
-    e.EvalClosure(e.PopValue(VClosure))
+    e.CallClosure(e.PopValue(VClosure))
 
 
 def _if(e):
     f = e.PopValue(VClosure)
     t = e.PopValue(VClosure)
     c = e.PopValue(bool)
-    e.EvalClosure(t if c else f)
+    e.CallClosure(t if c else f)
 
 
 def _get(e):

@@ -240,3 +240,96 @@ def test_cli_writes_png_and_ppm_like_cmd_example(tmp_path):
     h, w = want.shape[:2]
     head = f"P6\n{w} {h}\n255\n".encode()
     assert raw.startswith(head) and raw[len(head):] == want[..., :3].tobytes()
+
+
+# The ICFP-2000 sample scenes of internal/gml/testdata (testdata/README.md:1-3: most of them need builtins the reference
+# lacks - cone, intersect / difference, light, spotlight, real, acos, asin - so the reference itself cannot render them;
+# the oracle and the device implement those from the ICFP task text).  Every `render` of every file, at its
+# scripted size: parity mode byte for byte against the oracle, throughput mode within the tolerance.
+ICFP_SCENES = ["checked-cube", "chess", "cone", "cone-fractal", "cube2", "dice", "ellipsoid", "fov", "fractal", "golf", "holes", "house",
+               "intercyl", "large", "pipe", "rotate", "snowgoon", "spheres", "spotlight"]
+
+
+@pytest.mark.parametrize("name", ICFP_SCENES)
+def test_icfp_fixture_scenes_end_to_end(ctx64, ctx32, name):
+    blobs = scene_blobs(name)
+    assert blobs, name
+    for file, blob in blobs:
+        want, ost, oids, chaos = oracle.render(blob, threads=THREADS, want_ids=True, want_chaos=True)
+        got, st = ctx64.render(blob)
+        assert np.array_equal(got, want), (name, file)
+        assert np.array_equal(ctx64.primary_hits(), oids), (name, file)
+        assert st.rays_total == ost.rays_total and st.rays_hit == ost.rays_hit, (name, file)
+        got32, _ = ctx32.render(blob)
+        ids32 = ctx32.primary_hits()
+        d = np.abs(got32[..., :3].astype(np.int32) - want[..., :3].astype(np.int32)).max(axis=2)
+        stable = ~chaos                        # pixels whose reference value does not hang on a cube face rejected by rounding
+        assert stable.mean() >= 0.8, (name, file, float(stable.mean()))
+        within = float((d[stable] <= 1).mean())
+        # these are 300 x 200 frames of a few large objects: an edge pixel in a thousand may differ by one sample
+        assert within >= 0.998, (name, file, within)
+        flips = int((((ids32 < 0) != (oids < 0)) & stable[..., None]).sum())
+        assert flips <= 2, (name, file, flips)
+        assert ctx32.ssim(got32, want) >= 0.99, (name, file)          # the reference's own acceptance (raytracer_test.go:37-52)
+
+
+def _blob(text):
+    return scenes.to_blob(text)
+
+
+def test_candidate_queue_overflow_retraces_and_never_writes_out_of_bounds(ctx64):
+    """48 nested spheres around one centre - every ray that meets the outermost bound survives the cull of
+    all 48 - with one candidate slot per ray.  The queue overflows, its counter stops at the cap (it used to wrap past
+    2^31 on large frames), the frame is discarded and traced again with smaller tiles until it fits; the result is the
+    oracle's, byte for byte."""
+    parts = ["{ /v /u /face 0.8 0.3 0.2 point 0.7 0.2 8.0 } sphere 0.0 0.0 4.0 translate 2.0 uscale\n"]
+    for k in range(47):
+        parts.append(f"{{ /v /u /face 0.2 0.{k % 9 + 1} 0.8 point 0.7 0.2 8.0 }} sphere 0.0 0.0 4.0 translate {1.99 - 0.02 * k:.4f} uscale\nunion\n")
+    text = "".join(parts) + "/scene\n-4.0 6.0 -2.0 point 1.0 1.0 1.0 point pointlight /l1\n[ l1 ] /lights\n" \
+        "0.3 0.3 0.3 point\nlights\nscene\n2\n90.0\n200 120\n\"nested.ppm\"\nrender\n"
+    blob = _blob(text)
+    want, ost = oracle.render(blob, threads=THREADS)
+    os.environ["GMLRT_CAND_PER_RAY"] = "1"
+    try:
+        got, st = ctx64.render(blob)
+    finally:
+        del os.environ["GMLRT_CAND_PER_RAY"]
+    assert np.array_equal(got, want)
+    assert st.rays_total == ost.rays_total
+
+
+def test_f32_deviation_ties_between_kinds_stay_inside_the_coincident_surface(ctx64, ctx32):
+    """DESIGN section 2, float32 deviation: two hits at bit-identical T resolve by device index (objects are sorted by
+    kind), where closestHit keeps the first in scan order (raytracer.go:476).  Built to trip it: a cylinder, first in scan
+    order, whose top cap lies in the plane of a cube's top face (same transform, same formula for T, different
+    colours).  Parity mode follows the reference exactly; throughput mode may differ on the shared face only."""
+    place = "0.0 -0.8 2.5 translate 25.0 rotatex 30.0 rotatey"
+    text = (f"{{ /v /u /face 0.9 0.2 0.2 point 0.8 0.1 4.0 }} cylinder {place} 0.5 0.0 0.5 translate 0.4 1.0 0.4 scale\n"
+            f"{{ /v /u /face 0.2 0.9 0.2 point 0.8 0.1 4.0 }} cube {place}\nunion\n/scene\n"
+            "-3.0 6.0 -2.0 point 1.0 1.0 1.0 point pointlight /l1\n[ l1 ] /lights\n"
+            "0.4 0.4 0.4 point\nlights\nscene\n1\n90.0\n320 200\n\"ties.ppm\"\nrender\n")
+    blob = _blob(text)
+    want, ost, oids = oracle.render(blob, threads=THREADS, want_ids=True)
+    got, _ = ctx64.render(blob)
+    assert np.array_equal(got, want)
+    got32, _ = ctx32.render(blob)
+    ids32 = ctx32.primary_hits()
+    bad = np.abs(got32[..., :3].astype(int) - want[..., :3].astype(int)).max(axis=2) > 1
+    # a pixel may differ only where the reference saw the cylinder (id 0) and float32 the cube (id 1) or vice versa: the shared cap
+    swapped = ((oids == 0) & (ids32 == 1)) | ((oids == 1) & (ids32 == 0))
+    assert not (bad & ~swapped.any(axis=2)).any()
+    assert int(((ids32 < 0) != (oids < 0)).sum()) == 0            # never a hit/miss flip
+    print("ties: pixels on the shared cap that differ:", int(bad.sum()), "of", bad.size)
+
+
+def test_f32_deviation_sphere_pole_is_clamped_not_a_fault(ctx32):
+    """at a pole of a textured sphere float32 rounding can leave |y| = 1 + ulp, where the reference
+    returns an error (raytracer.go:142-144) that it can never reach in float64.  Throughput mode clamps instead: the
+    frame renders, and agrees with the oracle."""
+    text = ("{ /v /u /face u 8.0 mulf frac v 8.0 mulf frac 0.5 point 0.8 0.2 8.0 } sphere 0.0 0.0 3.0 translate 90.0 rotatex 1.5 uscale\n/scene\n"
+            "-3.0 6.0 -2.0 point 1.0 1.0 1.0 point pointlight /l1\n[ l1 ] /lights\n"
+            "0.4 0.4 0.4 point\nlights\nscene\n1\n90.0\n320 200\n\"pole.ppm\"\nrender\n")
+    blob = _blob(text)
+    want, _ = oracle.render(blob, threads=THREADS)
+    got32, _ = ctx32.render(blob)                                  # must not raise GMLRT_E_SURFACE
+    assert agreement(got32, want, tol=1) >= 0.995                  # the texture's seams converge on the pole in the middle of the frame

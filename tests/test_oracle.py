@@ -172,3 +172,18 @@ def test_glass_scene_really_branches():
     deep, st5 = oracle.render(scenes.to_blob(scenes.glass(80, 50, depth=5)), threads=4)
     assert st5.rays_reflect + st5.rays_refract > 2.0 * st5.rays_primary
     assert deep[..., 3].min() == 255
+
+
+def test_every_icfp_fixture_evaluates_lowers_and_renders():
+    """internal/gml/testdata: every runnable sample scene goes through the front end (large.gml needs the
+    iterative evaluator: thousands of nested applies), lowers to a blob and renders with the oracle."""
+    from util import scene_blobs
+    n = 0
+    for name in ["checked-cube", "chess", "cone", "cone-fractal", "cube2", "dice", "ellipsoid", "fov", "fractal", "golf", "holes", "house",
+                 "intercyl", "large", "pipe", "rotate", "snowgoon", "spheres", "spotlight"]:
+        for file, blob in scene_blobs(name):
+            img, st = oracle.render(blob, threads=8)
+            assert st.rays_primary == 4 * img.shape[0] * img.shape[1], (name, file)
+            assert (img[..., 3] == 255).all()
+            n += 1
+    assert n >= 30
