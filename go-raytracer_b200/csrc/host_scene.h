@@ -6,6 +6,7 @@
 // set-up of Render (:592-603).  The reference repeats this 8 times (once per goroutine,
 // :738-751); here it runs once per gmlrt_upload.
 #pragma once
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -20,6 +21,7 @@ namespace gmlrt {
 // device-order kind slots (scan kernels walk the leaves kind by kind)
 enum Kind { K_SPHERE = 0, K_CUBE = 1, K_CYLINDER = 2, K_CONE = 3, K_PLANE = 4, K_COUNT = 5,
             K_CSG = 5, K_OBJ_KINDS = 6 };   // K_CSG: a scan-order object that is an intersect/difference subtree (EXTENSION)
+#define GMLRT_CSG_SWAPPED 8                 // operator flag in a postfix program: the operands were evaluated b first, a is on top
 #define GMLRT_CSG_MAX_STACK 6               // span-list stack depth of the device evaluator (left-deep trees need 2)
 static const double kFlopsByKind[K_COUNT] = {56, 81, 74, 70, 47};
 
@@ -199,6 +201,27 @@ inline int parse_blob(const void* blob, size_t nbytes, HostScene& S, std::string
         } else if (n.kind == GMLRT_NODE_INTERSECT || n.kind == GMLRT_NODE_DIFFERENCE) {
             // EXTENSION: the reference rejects these (raytracer.go:825-826).  Postfix walk, no recursion.
             HostCsgObject obj; obj.scan_index = (int)S.object_of_scan.size(); obj.max_stack = 0;
+            // Postfix order with the deeper operand first (Sethi-Ullman numbering): the span stack of the device evaluator
+            // then needs log2(leaves) + 1 lists instead of the depth of the tree as written (chess.gml nests 9 deep, its
+            // pieces need 3).  When that puts b before a, the operator carries GMLRT_CSG_SWAPPED: a is then on top.
+            std::vector<int> need(h.n_nodes, 0);
+            {
+                struct F2 { uint32_t node; int state; };
+                std::vector<F2> st2{{ni, 0}};
+                size_t seen = 0;
+                while (!st2.empty()) {
+                    F2& f = st2.back();
+                    if (++seen > 4 * (size_t)h.n_nodes + 8) { err = "scene graph is not a tree"; return GMLRT_E_BAD_BLOB; }
+                    const gmlrt_node& m = nodes[f.node];
+                    if (is_leaf_kind(m.kind)) { need[f.node] = 1; st2.pop_back(); }
+                    else if (m.kind <= GMLRT_NODE_DIFFERENCE) {
+                        if (m.a >= h.n_nodes || m.b >= h.n_nodes) { err = "child index out of range"; return GMLRT_E_BAD_BLOB; }
+                        if (f.state == 0) { f.state = 1; st2.push_back({m.a, 0}); }
+                        else if (f.state == 1) { f.state = 2; st2.push_back({m.b, 0}); }
+                        else { const int na = need[m.a], nb2 = need[m.b]; need[f.node] = na == nb2 ? na + 1 : std::max(na, nb2); st2.pop_back(); }
+                    } else { err = "unknown scene object type"; return GMLRT_E_UNSUPPORTED; }
+                }
+            }
             struct Frame { uint32_t node; int state; };
             std::vector<Frame> st{{ni, 0}};
             int depth = 0;
@@ -217,9 +240,10 @@ inline int parse_blob(const void* blob, size_t nbytes, HostScene& S, std::string
                     st.pop_back();
                 } else if (m.kind <= GMLRT_NODE_DIFFERENCE) {
                     if (m.a >= h.n_nodes || m.b >= h.n_nodes) { err = "child index out of range"; return GMLRT_E_BAD_BLOB; }
-                    if (f.state == 0) { f.state = 1; st.push_back({m.a, 0}); }
-                    else if (f.state == 1) { f.state = 2; st.push_back({m.b, 0}); }
-                    else { obj.postfix.push_back({(int)m.kind, -1}); depth--; st.pop_back(); }
+                    const bool swapped = need[m.b] > need[m.a];
+                    if (f.state == 0) { f.state = 1; st.push_back({swapped ? m.b : m.a, 0}); }
+                    else if (f.state == 1) { f.state = 2; st.push_back({swapped ? m.a : m.b, 0}); }
+                    else { obj.postfix.push_back({(int)m.kind | (swapped ? GMLRT_CSG_SWAPPED : 0), -1}); depth--; st.pop_back(); }
                 } else { err = "unknown scene object type"; return GMLRT_E_UNSUPPORTED; }
             }
             S.object_of_scan.push_back(-(int)S.csg.size() - 1);
@@ -247,9 +271,11 @@ inline int parse_blob(const void* blob, size_t nbytes, HostScene& S, std::string
             } else {
                 B b = st.back(); st.pop_back();
                 B a = st.back(); st.pop_back();
+                if (op.op & GMLRT_CSG_SWAPPED) std::swap(a, b);
                 B r;
-                if (op.op == GMLRT_NODE_DIFFERENCE) r = a;                                   // a - b lies inside a
-                else if (op.op == GMLRT_NODE_INTERSECT) r = (b.R < a.R) ? b : a;            // inside both: keep the smaller bound
+                const int kind = op.op & ~GMLRT_CSG_SWAPPED;
+                if (kind == GMLRT_NODE_DIFFERENCE) r = a;                                   // a - b lies inside a
+                else if (kind == GMLRT_NODE_INTERSECT) r = (b.R < a.R) ? b : a;            // inside both: keep the smaller bound
                 else sphere_union(a.C, a.R, b.C, b.R, r.C, r.R);
                 st.push_back(r);
             }

@@ -504,11 +504,12 @@ __device__ __noinline__ bool csg_hit(const int* prog, int len, const int* kinds,
             leaf_spans<R>(kinds[op], op, o, buf[ids[sp++]]);
         } else {
             if (sp < 2) return false;
-            Spans<R>& a = buf[ids[sp - 2]];
-            Spans<R>& b = buf[ids[sp - 1]];
             Spans<R>& t1 = buf[ids[sp]];
             Spans<R>& t2 = buf[ids[sp + 1]];
-            const int kind = -1 - op;
+            if ((-1 - op) & GMLRT_CSG_SWAPPED) swap_ids(sp - 2, sp - 1);      // the operands were evaluated b first (host_scene.h)
+            const int kind = (-1 - op) & ~GMLRT_CSG_SWAPPED;
+            Spans<R>& a = buf[ids[sp - 2]];
+            Spans<R>& b = buf[ids[sp - 1]];
             if (kind == GMLRT_NODE_INTERSECT) { spans_intersect(a, b, t1); swap_ids(sp - 2, sp); }
             else if (kind == GMLRT_NODE_DIFFERENCE) { spans_complement(b, t1); spans_intersect(a, t1, t2); swap_ids(sp - 2, sp + 1); }
             else {                                       // union = complement(complement a  intersect  complement b)
@@ -2132,8 +2133,9 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
                 const R tc = -hb / a;
                 const R lx = fma_(tc, o.dx, o.ox), ly = fma_(tc, o.dy, o.oy), lz = fma_(tc, o.dz, o.oz);
                 const R pp = lx * lx + ly * ly + lz * lz;
-                const R sr = gm<R>::sqrt(gomath::max0(R(1) - pp) / a);
-                p = mk(fma_(-sr, o.dx, lx), fma_(-sr, o.dy, ly), fma_(-sr, o.dz, lz));
+                R sr = gm<R>::sqrt(gomath::max0(R(1) - pp) / a);
+                if (t < tc) sr = -sr;                     // near root (a plain sphere: always; :98-102), far root: the inside of a sphere a CSG difference cut away
+                p = mk(fma_(sr, o.dx, lx), fma_(sr, o.dy, ly), fma_(sr, o.dz, lz));
             }
         }
         obj_x = p.x; obj_z = p.z;
@@ -2163,6 +2165,9 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
             N = ld3(sc.fnormal + (size_t)leaf * 18);
         } else if (kind == K_CUBE) {                                                 // :242-260
             u = p.x; v = p.z;
+            if (!GMLRT_PARITY_TU) {                       // float rounding can leave a face point an ulp outside [0, 1): textures index arrays with floor(u n)
+                u = fminf(fmaxf((float)u, 0.0f), 0.99999994f); v = fminf(fmaxf((float)v, 0.0f), 0.99999994f);
+            }
             N = ld3(sc.fnormal + (size_t)leaf * 18 + 3 * face);
         } else if (kind == K_CYLINDER) {                                             // :339-370
             V3<R> no;
@@ -2927,15 +2932,10 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     sc.W = S.width; sc.H = S.height; sc.depth = S.depth; sc.vw = S.vw; sc.vh = S.vh;
     sc.cam_su = S.vw / (double)(S.width - 1); sc.cam_sv = S.vh / (double)(S.height - 1);
     // sort key of spawned rays: 6 k^2 direction cells per origin leaf, at most KEY_BINS_MAX bins in all
-    // Direction cells per cube-map face edge: finer cells = shorter candidate lists per class, but a class should still hold
-    // a warp or so of rays, or the lanes of a warp walk different lists.  6 x 6 measured best for a whole 4K frame of
-    // 1024 spheres (6.09 -> 5.99 ms against 4 x 4); a device that renders 1 / n of the frame has 1 / n of the rays to bin.
-    {
-        const double spawned = 0.4 * 4.0 * (double)S.width * (double)S.height / (double)share_;
-        int k = 6;
-        while (k > 2 && spawned / ((double)n_regions * 6.0 * k * k) < 16.0) k--;
-        sc.key_k = (int)env_size("GMLRT_KEY_K", (size_t)k); sc.key_k = std::max(1, std::min(sc.key_k, 8));
-    }
+    // Direction cells per cube-map face edge: finer cells = shorter candidate lists per class.  6 x 6 measured best both for a
+    // whole 4K frame of 1024 spheres (5.95 ms; 4 x 4: 6.09) and for one device's eighth of it (1.01 ms; 4 x 4: 1.05, 3 x 3:
+    // 1.10), where a class holds only a handful of rays: shorter lists win over lanes that share a list.
+    sc.key_k = (int)env_size("GMLRT_KEY_K", 6); sc.key_k = std::max(1, std::min(sc.key_k, 8));
     sc.key_shift = 0;
     while ((size_t)(((n_regions - 1) >> sc.key_shift) + 1) * 6 * sc.key_k * sc.key_k > (size_t)KEY_BINS_MAX) sc.key_shift++;
     key_nb_ = (((n_regions - 1) >> sc.key_shift) + 1) * 6 * sc.key_k * sc.key_k;
