@@ -852,6 +852,7 @@ struct BinParams {
     // the objects as this family's per-ray test sees them, [n][4]: centre relative to the pivot (PIVOT), absolute (GENERAL),
     // or (u, v, front end along the rays) (AXIS); then the radius with every margin of the per-ray test folded in (inf = unbounded)
     const double* obj; int n_objects;
+    int no_bounds;                      // GMLRT_NO_CLASS_BOUNDS (debug): every class lists every object
     const float4* objf;                 // the same records in float32, radius grown by another 0.1 % + 1e-4: the screening pass (null: none)
     double pivot[3];                    // PIVOT families: the eye / the light
     double e1[3], e2[3], axis[3];       // AXIS: the frame the device projects with
@@ -869,6 +870,7 @@ __device__ __forceinline__ BinBound bin_bound(const BinParams& p, int b) {
     BinBound B = {};
     B.usable = false;
     B.rho = INFINITY; B.rear = -INFINITY;
+    if (p.no_bounds) return B;
     if (p.kind == BIN_CAMERA) {
         // Render (raytracer.go:639-649): sample (x + dx, y + dy), |dx|, |dy| <= 0.5, is the ray from the eye (0, 0, -1) through
         // (u, -v, 0): direction ~ (u, -v, 1).  The directions of a tile are a rectangle on the plane z = 1; the farthest from
@@ -3112,6 +3114,7 @@ int Renderer<R>::build_lists(const HostScene& S, std::string& err) {
     auto base_params = [&](int kind, int n_bins, double offset_abs, const double* pivot, const CullFrame<R>* fr, int& prc) {
         BinParams p{};
         p.kind = kind; p.n_bins = n_bins; p.n_objects = n;
+        p.no_bounds = env_size("GMLRT_NO_CLASS_BOUNDS", 0) != 0;
         std::vector<double> rec((size_t)std::max(n, 1) * 4, 0.0);
         for (int d = 0; d < n; d++) {
             const double* b = &bound_[(size_t)d * 4];
@@ -3138,7 +3141,7 @@ int Renderer<R>::build_lists(const HostScene& S, std::string& err) {
         }
         float4* d_recf = nullptr;
         if (!prc) prc = to_device(recf, &d_recf, err);
-        p.objf = d_recf;
+        p.objf = env_size("GMLRT_NO_SCREEN", 0) != 0 ? nullptr : d_recf;
         return p;
     };
     lists_light_.assign(S.lights.size(), BinLists{});
