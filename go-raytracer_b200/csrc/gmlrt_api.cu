@@ -14,6 +14,7 @@
 #include <cstring>
 #include <thread>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -468,6 +469,57 @@ int gmlrt_ssim(gmlrt_ctx* c, const uint8_t* rgba_a, const uint8_t* rgba_b, int w
     if (e != cudaSuccess) return fail(c, GMLRT_E_CUDA, std::string("gmlrt_ssim: ") + cudaGetErrorString(e));
     double sum = 0.0;
     for (double v : sums) sum += v;
+    *ssim = sum / (double)windows;
+    return GMLRT_OK;
+}
+
+// ------------------------------------------------------------------ SSIM without allocations
+// No counterpart in the reference: for callers that must not call cudaMalloc (CUDA graph capture, serving loops).
+// The per-block sums of k_ssim go into a file-scope device array instead of a cudaMalloc'ed buffer; the two rasters are
+// DEVICE pointers the caller owns (e.g. gmlrt_frame_device).  In host code `g_ssim_scratch` is only a stand-in for the
+// symbol, not a device address: its address is looked up once per device with cudaGetSymbolAddress (that device
+// current) and that pointer is what the kernel gets.  Every call on a device shares the array and it keeps the last
+// call's block sums; nothing has to start at zero because k_ssim overwrites block_sums[0, blocks) and only those are read
+// back.  Calls are serialised by a process-wide mutex; calls from different processes on one GPU have their own copy.
+static __device__ __align__(256) double g_ssim_scratch[GMLRT_SSIM_NOALLOC_MAX_WINDOWS / 256];       // 1 MiB per GPU
+static double      g_ssim_host_sums[GMLRT_SSIM_NOALLOC_MAX_WINDOWS / 256];                          // host side of the read-back
+static double*     g_ssim_scratch_ptr[64];                                                          // device address, by CUDA ordinal
+static std::mutex  g_ssim_mutex;
+
+int gmlrt_ssim_device_noalloc(gmlrt_ctx* c, const void* d_rgba_a, const void* d_rgba_b, int width, int height, double* ssim) {
+    if (!c) return fail(nullptr, GMLRT_E_BAD_ARG, "ctx is null");
+    if (!d_rgba_a || !d_rgba_b || !ssim) return fail(c, GMLRT_E_BAD_ARG, "null image or result pointer");
+    if (width < 11 || height < 11) return fail(c, GMLRT_E_BAD_ARG, "images are too small");        // ssim.go:34-36
+    const long long windows = (long long)(width - 11) * (height - 11);
+    if (windows > (long long)GMLRT_SSIM_NOALLOC_MAX_WINDOWS)
+        return fail(c, GMLRT_E_BAD_ARG, "gmlrt_ssim_device_noalloc: (width-11)*(height-11) = " + std::to_string(windows) +
+                                        " windows exceed the static scratch (GMLRT_SSIM_NOALLOC_MAX_WINDOWS = " +
+                                        std::to_string((long long)GMLRT_SSIM_NOALLOC_MAX_WINDOWS) + "); use gmlrt_ssim");
+    IRenderer* r0 = c->r[0].get();
+    const int dev = r0->device();
+    if (dev < 0 || dev >= 64) return fail(c, GMLRT_E_BAD_ARG, "device ordinal out of range");
+    std::lock_guard<std::mutex> lock(g_ssim_mutex);
+    API_CU(cudaSetDevice(dev));
+    if (!g_ssim_scratch_ptr[dev]) {                                                                // set-up, once per device
+        double* p = nullptr;
+        API_CU(cudaGetSymbolAddress((void**)&p, g_ssim_scratch));
+        g_ssim_scratch_ptr[dev] = p;
+    }
+    double* d_sums = g_ssim_scratch_ptr[dev];
+    double kern[121], total = 0.0;
+    for (int i = 0; i < 11; i++)
+        for (int j = 0; j < 11; j++) { const double x = i - 5.0, y = j - 5.0; kern[i * 11 + j] = std::exp(-(x * x + y * y) / (2 * 1.5 * 1.5)); total += kern[i * 11 + j]; }
+    for (double& k : kern) k /= total;
+    API_CU(cudaMemcpyToSymbolAsync(c_ssim_kernel, kern, sizeof kern, 0, cudaMemcpyHostToDevice, r0->stream()));
+    if (windows == 0) { *ssim = std::nan(""); return GMLRT_OK; }
+    const int blocks = (int)((windows + 255) / 256);
+    k_ssim<<<blocks, 256, 0, r0->stream()>>>(static_cast<const uchar4*>(d_rgba_a), static_cast<const uchar4*>(d_rgba_b), width, height, d_sums);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(g_ssim_host_sums, d_sums, (size_t)blocks * sizeof(double), cudaMemcpyDeviceToHost, r0->stream());
+    if (e == cudaSuccess) e = cudaStreamSynchronize(r0->stream());
+    if (e != cudaSuccess) return fail(c, GMLRT_E_CUDA, std::string("gmlrt_ssim_device_noalloc: ") + cudaGetErrorString(e));
+    double sum = 0.0;
+    for (int i = 0; i < blocks; i++) sum += g_ssim_host_sums[i];                                   // block order, like gmlrt_ssim
     *ssim = sum / (double)windows;
     return GMLRT_OK;
 }

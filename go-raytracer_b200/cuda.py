@@ -47,7 +47,7 @@ class GmlrtError(RuntimeError):
         self.code = code
 
 
-EXPORTS = ("gmlrt_alloc_host", "gmlrt_free_host", "gmlrt_ssim", "gmlrt_frame_ipc_export", "gmlrt_frame_ipc_attach", "gmlrt_measure_fp32_tflops", "gmlrt_set_profiling", "gmlrt_set_partition", "gmlrt_frame_device", "gmlrt_create", "gmlrt_render", "gmlrt_upload", "gmlrt_trace", "gmlrt_download", "gmlrt_set_counting",
+EXPORTS = ("gmlrt_ssim_device_noalloc", "gmlrt_alloc_host", "gmlrt_free_host", "gmlrt_ssim", "gmlrt_frame_ipc_export", "gmlrt_frame_ipc_attach", "gmlrt_measure_fp32_tflops", "gmlrt_set_profiling", "gmlrt_set_partition", "gmlrt_frame_device", "gmlrt_create", "gmlrt_render", "gmlrt_upload", "gmlrt_trace", "gmlrt_download", "gmlrt_set_counting",
            "gmlrt_primary_hits", "gmlrt_stream", "gmlrt_last_error", "gmlrt_destroy", "gmlrt_blob_version", "gmlrt_build_info")
 
 _lib = None
@@ -75,6 +75,7 @@ def load():
         L.gmlrt_set_partition.restype, L.gmlrt_set_partition.argtypes = i, [p, i, i]
         L.gmlrt_frame_device.restype, L.gmlrt_frame_device.argtypes = p, [p]
         L.gmlrt_ssim.restype, L.gmlrt_ssim.argtypes = i, [p, p, p, i, i, ctypes.POINTER(ctypes.c_double)]
+        L.gmlrt_ssim_device_noalloc.restype, L.gmlrt_ssim_device_noalloc.argtypes = i, [p, p, p, i, i, ctypes.POINTER(ctypes.c_double)]
         L.gmlrt_frame_ipc_export.restype, L.gmlrt_frame_ipc_export.argtypes = i, [p, p, sz]
         L.gmlrt_frame_ipc_attach.restype, L.gmlrt_frame_ipc_attach.argtypes = i, [p, p, sz]
         L.gmlrt_alloc_host.restype, L.gmlrt_alloc_host.argtypes = p, [sz]
@@ -194,6 +195,12 @@ class Context:
             raise ValueError("images are not the same size")
         out = ctypes.c_double()
         self._check(self._L.gmlrt_ssim(self._h, a.ctypes.data, b.ctypes.data, a.shape[1], a.shape[0], ctypes.byref(out)))
+        return out.value
+
+    def ssim_device_noalloc(self, d_a, d_b, width, height):
+        """gmlrt_ssim_device_noalloc: SSIM of two DEVICE rasters (addresses as ints), no allocation anywhere."""
+        out = ctypes.c_double()
+        self._check(self._L.gmlrt_ssim_device_noalloc(self._h, ctypes.c_void_p(d_a), ctypes.c_void_p(d_b), width, height, ctypes.byref(out)))
         return out.value
 
     def frame_ipc_export(self):

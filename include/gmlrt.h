@@ -274,6 +274,19 @@ void gmlrt_destroy(gmlrt_ctx*);
  * out.  GMLRT_E_BAD_ARG when an image is smaller than the 11x11 window (the reference returns an error there too). */
 int gmlrt_ssim(gmlrt_ctx*, const uint8_t* rgba_a, const uint8_t* rgba_b, int width, int height, double* ssim);
 
+/* gmlrt_ssim without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The two rasters are DEVICE pointers on devices[0] (RGBA8, 4*width*height bytes each, e.g. gmlrt_frame_device of two
+ * contexts); the result goes to a host double.  The kernel's per-block sums live in a file-scope __device__ array of
+ * GMLRT_SSIM_NOALLOC_MAX_WINDOWS / 256 doubles (1 MiB, held by every GPU that loads the library until exit), so
+ * (width-11)*(height-11) must not exceed GMLRT_SSIM_NOALLOC_MAX_WINDOWS (an 8K frame fits): larger images are
+ * rejected with GMLRT_E_BAD_ARG and a message naming the limit.  Calls no cudaMalloc / cudaFree / allocating library
+ * routine.  All calls share the array (it keeps the last call's sums; every entry that is read is overwritten first):
+ * within one process calls are serialised by a mutex, anything else that overlaps on the GPU races.  Same result, bit
+ * for bit, as gmlrt_ssim on the same pixels.                                                                        */
+#define GMLRT_SSIM_NOALLOC_MAX_WINDOWS (1 << 25)
+int gmlrt_ssim_device_noalloc(gmlrt_ctx*, const void* d_rgba_a, const void* d_rgba_b, int width, int height, double* ssim);
+
 int  gmlrt_blob_version(void);
 const char* gmlrt_build_info(void);         /* arch, compiler, precision modes compiled in */
 
