@@ -358,7 +358,76 @@ def main():
 
     e2e_pg_ms, e2e_pg_phase, _ = run_e2e(True)
     e2e_ms, e2e_phase, upload_each = run_e2e(False)
+    # gmlrt_upload recognises a blob that is byte-identical to the last one (memcmp) and then only copies the blob to the
+    # device again, keeping everything derived from it.  The same loop with that shortcut off = a NEW scene every step
+    # (parse, convert, cull tables and class lists rebuilt on the device each time).
+    os.environ["GMLRT_NO_UPLOAD_CACHE"] = "1"
+    e2e_new_ms, e2e_new_phase, _ = run_e2e(False)
+    del os.environ["GMLRT_NO_UPLOAD_CACHE"]
+    ctx.upload(blob)
     e2e_value = rays_frame / (e2e_ms * 1e-3) / 1e6
+
+    # N > 1, gather on the HOST: every rank copies the rows it rendered into ONE raster that all ranks map (a file in
+    # /dev/shm, page-locked in each process), each over its own PCIe link (gmlrt_download_rows), then a barrier.  The
+    # IPC variant above pulls the whole frame through GPU 0's link after the NVLink gather.
+    e2e_host = None
+    if dist is not None:
+        shm_path = f"/dev/shm/gmlrt_frame_{os.environ.get('MASTER_PORT', '0')}"
+        if rank == 0:
+            with open(shm_path, "wb") as f:
+                f.truncate(W * H * 4)
+        dist.barrier()
+        shared = np.memmap(shm_path, dtype=np.uint8, mode="r+", shape=(H, W, 4))
+        rt = torch.cuda.cudart()
+        reg = rt.cudaHostRegister(shared.ctypes.data, W * H * 4, 0)
+        if use_ipc and rank != 0:
+            ctx.frame_ipc_attach(None)                          # rows go to this rank's own frame again
+        ctx.upload(blob)
+        hphase = {"upload": 0.0, "trace": 0.0, "download_rows+barrier": 0.0}
+
+        def host_step():
+            ta = time.perf_counter()
+            ctx.upload(blob)
+            tb = time.perf_counter()
+            ctx.trace()
+            tc = time.perf_counter()
+            ctx.download_rows(shared)
+            dist.barrier()                                      # the raster is complete in host memory
+            td = time.perf_counter()
+            hphase["upload"] += (tb - ta) * 1e3; hphase["trace"] += (tc - tb) * 1e3; hphase["download_rows+barrier"] += (td - tc) * 1e3
+        for _ in range(2):
+            host_step()
+        barrier()
+        for k in hphase:
+            hphase[k] = 0.0
+        n_steps = max(3, min(args.steps, 10))
+        t0 = time.perf_counter()
+        for _ in range(n_steps):
+            host_step()
+        barrier()
+        tt = torch.tensor([(time.perf_counter() - t0) / n_steps * 1e3], dtype=torch.float64, device=f"cuda:{local_rank}")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e_host = {"value": rays_frame / (float(tt[0]) * 1e-3) / 1e6, "unit": "Mrays/s", "frame_ms": float(tt[0]),
+                    "phase_ms": {k: v / n_steps for k, v in hphase.items()}, "h2d_bytes_per_step": len(blob) * world, "d2h_bytes_per_step": W * H * 4,
+                    "destination": "one raster in shared host memory (page-locked in every rank, cudaHostRegister rc %s): each rank copies its own bands over its own PCIe link" % str(reg)}
+        if args.verify:
+            barrier()
+            if rank == 0:
+                solo = cuda.Context((local_rank,), prec)
+                whole, _ = solo.render(blob)
+                solo.close()
+                same = (np.asarray(shared) == whole).all(axis=2)
+                e2e_host["gather_check"] = {"pixels_equal": float(same.mean())}
+            barrier()
+        rt.cudaHostUnregister(shared.ctypes.data)
+        del shared
+        dist.barrier()
+        if rank == 0:
+            os.unlink(shm_path)
+        if use_ipc and rank != 0:                               # back to the NVLink gather for what follows
+            ctx.frame_ipc_attach(bytes(handle.cpu().numpy().tobytes()))
+        ctx.upload(blob)
+        dist.barrier()
 
     # N > 1: the timed loop above lets every rank run ahead (value = the slowest rank's share); the same K steps again
     # with a cross-rank barrier after every frame = the latency of COMPLETED frames
@@ -502,7 +571,11 @@ def main():
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "frame_ms": e2e_ms, "h2d_bytes_per_step": len(blob), "d2h_bytes_per_step": W * H * 4,
                 "destination": "page-locked raster from gmlrt_alloc_host (the bridge of INTEGRATION.md)",
-                "phase_ms": e2e_phase, "upload_ms_each": upload_each},
+                "phase_ms": e2e_phase, "upload_ms_each": upload_each,
+                "upload": "the blob is byte-identical from step to step: gmlrt_upload copies it to the device (h2d_bytes_per_step) and keeps the "
+                          "tables derived from it; e2e_new_scene has the full rebuild in every step"},
+        "e2e_new_scene": {"value": rays_frame / (e2e_new_ms * 1e-3) / 1e6, "unit": "Mrays/s", "frame_ms": e2e_new_ms, "phase_ms": e2e_new_phase,
+                          "note": "GMLRT_NO_UPLOAD_CACHE=1: every step parses the blob and rebuilds cull tables and class lists, as for a scene never seen before"},
         "e2e_pageable": {"value": rays_frame / (e2e_pg_ms * 1e-3) / 1e6, "unit": "Mrays/s", "frame_ms": e2e_pg_ms, "phase_ms": e2e_pg_phase,
                          "destination": "pageable host array (image.NewRGBA of an unmodified caller): staged in 1 MB chunks by gmlrt_download",
                          "slower_than_page_locked": e2e_pg_ms / e2e_ms - 1.0},
@@ -512,6 +585,13 @@ def main():
         "serialised_frame_ms": serial_ms_step,
         "roofline": roof,
     }
+    if e2e_host is not None:
+        # two end-to-end gathers were timed; the headline `e2e` is the faster one, the other stays beside it
+        line["e2e_ipc_gather"] = dict(line["e2e"], gather="rows stored into GPU 0's frame over NVLink by the pixel kernel, whole frame D2H from GPU 0")
+        if e2e_host["frame_ms"] < line["e2e"]["frame_ms"]:
+            line["e2e"] = dict(e2e_host, gather="host")
+        else:
+            line["e2e_host_gather"] = e2e_host
     if gather_check is not None:
         line["gather_check"] = gather_check
     if frame_ms_barrier is not None:

@@ -34,6 +34,25 @@ def rows_of(part, n_parts, height, band_rows=BAND_ROWS):
     return np.array([actual_row(v, part, n_parts, band_rows) for v in range(n_rows(part, n_parts, height, band_rows))], dtype=np.int64)
 
 
+def own_row_blocks(part, n_parts, height, band_rows=BAND_ROWS):
+    """The rows of `part` as gmlrt_download_rows copies them: one strided 2-D copy of the full bands plus the partial band
+    at the bottom when `part` owns it -> ((first_row, pitch_rows, rows_per_band, n_bands), (tail_first_row, tail_rows))."""
+    full, rest = divmod(height, band_rows)
+    mine = full // n_parts + (1 if full % n_parts > part else 0)
+    tail = (full * band_rows, rest) if rest and full % n_parts == part else (0, 0)
+    return (part * band_rows, n_parts * band_rows, band_rows, mine), tail
+
+
+def copy_own_rows(dst, src, part, n_parts, band_rows=BAND_ROWS):
+    """Host statement of gmlrt_download_rows: rows of `part` from `src` into `dst` ([H, ...] arrays), others untouched."""
+    (first, pitch, br, nb), (t0, tn) = own_row_blocks(part, n_parts, dst.shape[0], band_rows)
+    for b in range(nb):
+        y = first + b * pitch
+        dst[y:y + br] = src[y:y + br]
+    dst[t0:t0 + tn] = src[t0:t0 + tn]
+    return dst
+
+
 def owner_of(y, n_parts, band_rows=BAND_ROWS):
     return (y // band_rows) % n_parts
 

@@ -1396,7 +1396,13 @@ __global__ void __launch_bounds__(EXACT_THREADS) k_exact_closest(const __grid_co
         if (KINDS == EXACT_REST && obj < 0) continue;          // a sphere candidate the SPHERES pass has already resolved to a miss
         bool deferred = false;
         if (ROBUST && KINDS == EXACT_REST) { deferred = (obj & CAND_DEFER) != 0; obj &= ~CAND_DEFER; }
-        if (KINDS != EXACT_ALL && obj < sc.n_leaves && !deferred && !exact_owns<KINDS>(obj, n_spheres, sc.kind_begin[K_CSG])) continue;
+        if (KINDS != EXACT_ALL && !deferred) {
+            // Without the pickless fold an earlier flavour has overwritten the object word of ITS candidates with the hit code
+            // (or -1): a code with face / flip bits is >= 2^27 and must not be taken for a padding record and reset to a miss
+            // (chess.gml: the board, a plain cube hit on faces 1-5, vanished in parity mode once a CSG flavour ran after SIMPLE).
+            if (obj < 0 || obj > sc.n_leaves) continue;
+            if (obj < sc.n_leaves && !exact_owns<KINDS>(obj, n_spheres, sc.kind_begin[K_CSG])) continue;
+        }
         const int ri = cq.ray[k];
         int code = -1; R t = R(0);
         if (obj < sc.n_leaves) {                               // a padding record can only be reached by a NaN ray

@@ -47,7 +47,7 @@ class GmlrtError(RuntimeError):
         self.code = code
 
 
-EXPORTS = ("gmlrt_ssim_device_noalloc", "gmlrt_alloc_host", "gmlrt_free_host", "gmlrt_ssim", "gmlrt_frame_ipc_export", "gmlrt_frame_ipc_attach", "gmlrt_measure_fp32_tflops", "gmlrt_set_profiling", "gmlrt_set_partition", "gmlrt_frame_device", "gmlrt_create", "gmlrt_render", "gmlrt_upload", "gmlrt_trace", "gmlrt_download", "gmlrt_set_counting",
+EXPORTS = ("gmlrt_download_rows", "gmlrt_ssim_device_noalloc", "gmlrt_alloc_host", "gmlrt_free_host", "gmlrt_ssim", "gmlrt_frame_ipc_export", "gmlrt_frame_ipc_attach", "gmlrt_measure_fp32_tflops", "gmlrt_set_profiling", "gmlrt_set_partition", "gmlrt_frame_device", "gmlrt_create", "gmlrt_render", "gmlrt_upload", "gmlrt_trace", "gmlrt_download", "gmlrt_set_counting",
            "gmlrt_primary_hits", "gmlrt_stream", "gmlrt_last_error", "gmlrt_destroy", "gmlrt_blob_version", "gmlrt_build_info")
 
 _lib = None
@@ -67,6 +67,7 @@ def load():
         L.gmlrt_upload.restype, L.gmlrt_upload.argtypes = i, [p, p, sz]
         L.gmlrt_trace.restype, L.gmlrt_trace.argtypes = i, [p, ctypes.POINTER(Stats)]
         L.gmlrt_download.restype, L.gmlrt_download.argtypes = i, [p, p, sz]
+        L.gmlrt_download_rows.restype, L.gmlrt_download_rows.argtypes = i, [p, p, sz]
         L.gmlrt_set_counting.restype, L.gmlrt_set_counting.argtypes = i, [p, i]
         L.gmlrt_measure_fp32_tflops.restype, L.gmlrt_measure_fp32_tflops.argtypes = ctypes.c_double, [i]
         L.gmlrt_set_profiling.restype, L.gmlrt_set_profiling.argtypes = i, [p, i]
@@ -170,6 +171,11 @@ class Context:
         if out is None:
             out = np.empty((h, w, 4), dtype=np.uint8)
         self._check(self._L.gmlrt_download(self._h, out.ctypes.data, out.nbytes))
+        return out
+
+    def download_rows(self, out):
+        """Only the rows this context rendered (its partition's bands) into the full-size raster `out` (uint8 [H,W,4])."""
+        self._check(self._L.gmlrt_download_rows(self._h, out.ctypes.data, out.nbytes))
         return out
 
     def set_counting(self, enabled):

@@ -215,9 +215,18 @@ int gmlrt_render(gmlrt_ctx*, const void* blob, size_t blob_bytes,
 
 /* The same three steps separately, for callers that keep the scene resident:
  * upload (validate + H2D), trace (kernels only; raster stays in HBM), download (D2H). */
-int gmlrt_upload(gmlrt_ctx*, const void* blob, size_t blob_bytes);
+int gmlrt_upload(gmlrt_ctx*, const void* blob, size_t blob_bytes);   /* a blob byte-identical to the last one (same partition, same GMLRT_* environment) is only copied
+                                                                         to the device again: what was derived from it is kept (GMLRT_NO_UPLOAD_CACHE=1 turns that off) */
 int gmlrt_trace(gmlrt_ctx*, gmlrt_stats* stats /* nullable */);
 int gmlrt_download(gmlrt_ctx*, uint8_t* rgba, size_t rgba_bytes);
+
+/* Multi-process gather on the HOST (the alternative SURVEY.md section 8e names): copy only the rows THIS context rendered - the
+ * bands of its partition - into the full-size raster `rgba` and leave every other row untouched.  N processes that map one
+ * raster (shared memory, page-locked in each process with cudaHostRegister) each call it after their own gmlrt_trace and then
+ * meet at a barrier: the frame crosses N PCIe links at once instead of one.  The reference has one address space and
+ * writes pixels with img.Set from its 8 goroutines (raytracer.go:656): this is that, across processes.  Not for a context
+ * that has attached another process's frame (its rows are not in its own frame).  Partition (0, 1): same as gmlrt_download. */
+int gmlrt_download_rows(gmlrt_ctx*, uint8_t* rgba, size_t rgba_bytes);
 
 /* Page-locked host memory for the raster (cudaHostAlloc): a frame buffer from here takes the device-to-host DMA
  * directly.  The reference allocates its raster with image.NewRGBA (raytracer.go:590), i.e. pageable Go heap memory;

@@ -161,4 +161,7 @@ def parity_window(blob, img, ids, crop, threads=8, chaos=False):
         out["primary_samples"] = int(gi.size)
         out["primary_flips"] = int(((gi < 0) != (oi < 0)).sum())
         out["id_mismatches"] = int((gi != oi).sum())
+        if chaos:   # ... and the flips that are not the reference's own face-rejection chaos
+            out["primary_flips_stable"] = int((((gi < 0) != (oi < 0)) & st[..., None]).sum())
+            out["id_mismatches_stable"] = int(((gi != oi) & st[..., None]).sum())
     return out, ost, d > 1

@@ -481,6 +481,9 @@ static int in_shadow(const scene_t* s, const hit_t* hit, const hitex_t* ex, v3 l
         c->leaf_tests++; c->flops += s->objs[i].flops;
         hit_t sh;
         if (!object_intersect(s, i, sr, &sh)) continue;
+        /* a decision inside float32's reach of a tie (an occluder AT the light's distance: dice.gml puts its light on the
+         * mirror's plane) is rounding chaos for any other arithmetic: flagged like the cube faces below */
+        if (dist < INFINITY && fabs(sh.t * in_len - dist) <= 1e-5 * (dist + 1.0)) tl_chaos++;
         if (sh.t * in_len < dist) { c->shadow_occluded++; return 1; }
     }
     return 0;

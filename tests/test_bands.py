@@ -30,6 +30,20 @@ def test_parts_partition_the_rows(height, n_parts):
         assert max(sizes) - min(sizes) <= bands.BAND_ROWS
 
 
+@pytest.mark.parametrize("height", [1, 7, 8, 9, 77, 150, 2160])
+@pytest.mark.parametrize("n_parts", [1, 2, 3, 8])
+def test_row_blocks_of_the_host_gather_are_exactly_the_owned_rows(height, n_parts):
+    """gmlrt_download_rows copies a part's rows as one strided 2-D copy + a tail: together the parts rebuild the frame."""
+    src = np.arange(height * 3, dtype=np.int64).reshape(height, 3) + 1
+    dst = np.zeros_like(src)
+    for part in range(n_parts):
+        one = bands.copy_own_rows(np.zeros_like(src), src, part, n_parts)
+        rows = bands.rows_of(part, n_parts, height)
+        assert (one[rows] == src[rows]).all() and one.sum() == src[rows].sum()      # its rows and nothing else
+        bands.copy_own_rows(dst, src, part, n_parts)
+    assert np.array_equal(dst, src)
+
+
 def test_row_map_matches_the_header_constants():
     src = open(os.path.join(HERE, "..", "go-raytracer_b200", "csrc", "gmlrt_api.cu")).read()
     assert "c->band_rows = nd > 1 ? %d : c->scene.height" % bands.BAND_ROWS in src
@@ -72,6 +86,38 @@ def _worker(rank, world, port, out_path):
             np.save(out_path, t.numpy())
     finally:
         dist.destroy_process_group()
+
+
+def _worker_shared(rank, world, port, path, h, w):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    sys.path.insert(0, os.path.join(HERE, ".."))
+    import torch.distributed as dist
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        shared = np.memmap(path, dtype=np.uint8, mode="r+", shape=(h, w, 4))
+        mine = np.zeros((h, w, 4), np.uint8)                     # this rank's "device frame": only its own rows are valid
+        rows = bands.rows_of(rank, world, h)
+        mine[rows] = (rows[:, None, None] * 7 + np.arange(w)[None, :, None] + np.arange(4)[None, None, :]) % 251
+        bands.copy_own_rows(shared, mine, rank, world)           # what gmlrt_download_rows does over this rank's PCIe link
+        shared.flush()
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_ranks_fill_one_shared_host_raster(tmp_path):
+    """The host gather of bench.py (N > 1): every rank writes only its bands into one raster all ranks map; after the
+    barrier the raster is complete - no collective on the data path."""
+    import torch.multiprocessing as mp
+    h, w = 77, 12
+    path = str(tmp_path / "frame.bin")
+    with open(path, "wb") as f:
+        f.truncate(h * w * 4)
+    mp.spawn(_worker_shared, args=(2, _free_port(), path, h, w), nprocs=2, join=True)
+    got = np.memmap(path, dtype=np.uint8, mode="r", shape=(h, w, 4))
+    y = np.arange(h)
+    want = ((y[:, None, None] * 7 + np.arange(w)[None, :, None] + np.arange(4)[None, None, :]) % 251).astype(np.uint8)
+    assert np.array_equal(np.asarray(got), want)
 
 
 def test_two_ranks_gather_the_golden_over_gloo(tmp_path):
