@@ -78,6 +78,7 @@ template <typename R> struct DevScene {
     const R* fpool; const int* itab; const uint32_t* code;
     int n_fpool, n_itab;
     int W, H, depth;
+    unsigned w_mul; int w_shift;   // n / W for n < 2^31 as (n * w_mul) >> w_shift (FastDiv): pixel index -> (row, column) without a runtime division
     int key_shift, key_k;          // sort key of a spawned ray: (region >> key_shift) * 6 k^2 + cube-map cell of its direction
     // Sort regions (what "rays that start close together" means for the two ray sorts): a small object is its own
     // region; a point on a large object (an unbounded plane, or a bounding sphere much wider than a grid cell) belongs
@@ -679,12 +680,25 @@ template <typename R> __device__ __forceinline__ bool hit_any_kind(int kind, con
 // PCG-DXSM stream of the (column, 20-row batch) work item is entered by jump-ahead, so every sample draws exactly the
 // numbers the reference draws.  k_gen rounds the result to the arithmetic type; the double-precision re-tests of the
 // throughput mode call this again for the few candidates they see instead of reading a stored 48-byte copy per sample.
+// n / d for n < 2^31 and a divisor known on the host: mul = ceil(2^(31 + s) / d), s = ceil(log2 d) (Granlund - Montgomery)
+struct FastDiv { unsigned mul; int shift; };
+inline FastDiv fast_div_of(int d) {
+    int s = 0;
+    while ((1ll << s) < (long long)d) s++;
+    FastDiv f;
+    f.shift = 31 + s;
+    f.mul = (unsigned)((((unsigned long long)1 << f.shift) + (unsigned long long)d - 1) / (unsigned long long)d);
+    return f;
+}
+__host__ __device__ __forceinline__ int fast_div(int n, unsigned mul, int shift) { return (int)(((unsigned long long)(unsigned)n * mul) >> shift); }
+
 __constant__ gomath::PcgJump c_pcg_jump[160];   // affine maps advancing the PCG stream by 0..159 draws
 struct CamSrc { int y0; RowMap map; };          // which rows the level-0 rays of the current tile are
 template <typename R>
 __device__ __forceinline__ void camera_ray64(const DevScene<R>& sc, const CamSrc& cam, int i, double (&o)[3], double (&d)[3]) {
     const int s = i & 3, pix = i >> 2;
-    const int x = pix % sc.W, y = cam.map.actual(cam.y0 + pix / sc.W);
+    const int row = fast_div(pix, sc.w_mul, sc.w_shift);
+    const int x = pix - row * sc.W, y = cam.map.actual(cam.y0 + row);
     const int ymin = (y / 20) * 20;                       // work item = (column, 20-row batch), :663-672
     const int q = 8 * (y - ymin) + 2 * s;                 // draws consumed before this sample
     gomath::Pcg rng;
@@ -1152,13 +1166,14 @@ template <typename R> __device__ __forceinline__ void level_init_ray(const Level
 }
 
 template <typename R> struct CameraSource {                  // level 0: camera rays in (pixel, sample) order over the virtual rows of a tile
-    Level<R> lv; int W, y0; RowMap map; int tile_w, tile_h, tiles_x;
+    Level<R> lv; int W, y0; RowMap map; int tile_w_log2, tile_h_log2, tiles_x; unsigned w_mul; int w_shift;
     __device__ __forceinline__ int id(int i) const { return i; }
     __device__ __forceinline__ void load(int i, Ray<R>& out) const { load_ray(lv.ray, i, out); }
     __device__ __forceinline__ void init(int i) const { level_init_ray(lv, i); }
     __device__ __forceinline__ int bin(int i) const {
         const int pix = i >> 2;
-        return (map.actual(y0 + pix / W) / tile_h) * tiles_x + (pix % W) / tile_w;
+        const int row = fast_div(pix, w_mul, w_shift);
+        return (map.actual(y0 + row) >> tile_h_log2) * tiles_x + ((pix - row * W) >> tile_w_log2);
     }
     static constexpr bool is_shadow = false;
 };
@@ -2438,7 +2453,8 @@ __global__ void __launch_bounds__(256) k_pixels(DevScene<R> sc, Level<R> lv, con
             px.y = (unsigned char)((unsigned)(c[1] * R(65535)) >> 8);
             px.z = (unsigned char)((unsigned)(c[2] * R(65535)) >> 8);
             px.w = 0xFF;
-            frame[(size_t)map.actual(y0 + pix / sc.W) * sc.W + pix % sc.W] = px;
+            const int row = fast_div(pix, sc.w_mul, sc.w_shift);
+            frame[(size_t)map.actual(y0 + row) * sc.W + (pix - row * sc.W)] = px;
         }
     }
 }
@@ -2517,7 +2533,9 @@ public:
     int fetch_totals(TraceTotals& out, std::string& err) override {
         CU_TRY(cudaSetDevice(dev_));
         Counters c;
-        CU_TRY(cudaMemcpy(&c, ctr_, sizeof c, cudaMemcpyDeviceToHost));
+        if (ctr_host_valid_) c = *ctr_host_;                 // copied behind the last kernel of the trace (trace_rows); the stream has been synchronised by the caller
+        else CU_TRY(cudaMemcpy(&c, ctr_, sizeof c, cudaMemcpyDeviceToHost));
+        ctr_host_valid_ = false;
         for (size_t k = 0; k + 1 < ev_used_; k++) {          // the stream has been synchronised by the caller
             if (ev_cls_[k] < 0) continue;
             float ms = 0;
@@ -2590,6 +2608,8 @@ private:
         if (frame_) cudaFree(frame_);
         if (ids_) cudaFree(ids_);
         if (ctr_) cudaFree(ctr_);
+        if (ctr_host_) cudaFreeHost(ctr_host_);
+        ctr_host_ = nullptr;
         if (scan_tiles_) cudaFree(scan_tiles_);
         scan_tiles_ = nullptr;
         for (cudaEvent_t e : ev_pool_) cudaEventDestroy(e);
@@ -2674,6 +2694,7 @@ private:
     std::vector<double> bound_;                                  // host: [n][4] bounding spheres (centre, radius) of the objects
     R* cull_general_ = nullptr; R* cull_eye_ = nullptr; std::vector<R*> cull_light_;
     CullFrame<R> frame_general_{}, frame_eye_{}; std::vector<CullFrame<R>> frame_light_;
+    Counters* ctr_host_ = nullptr; bool ctr_host_valid_ = false;   // page-locked copy of the frame's counters (trace_rows -> fetch_totals)
     int share_ = 1;                                              // devices sharing the frame (set_share)
     int* slots_ = nullptr; int n_slots_ = 0;                     // per-frame queue counters: per level 1 (closest candidates) + per light (shadow candidates, shadow rays)
     int build_cull_table(int family, const double* v, double offset_abs, R** out, CullFrame<R>& frame, std::string& err);
@@ -2938,6 +2959,7 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     sc.fpool = d_fpool; sc.itab = d_itab; sc.code = d_code;
     sc.n_fpool = (int)fpool.size(); sc.n_itab = (int)S.itab.size();
     sc.W = S.width; sc.H = S.height; sc.depth = S.depth; sc.vw = S.vw; sc.vh = S.vh;
+    { const FastDiv fd = fast_div_of(S.width); sc.w_mul = fd.mul; sc.w_shift = fd.shift; }
     sc.cam_su = S.vw / (double)(S.width - 1); sc.cam_sv = S.vh / (double)(S.height - 1);
     // sort key of spawned rays: 6 k^2 direction cells per origin leaf, at most KEY_BINS_MAX bins in all
     // Direction cells per cube-map face edge: finer cells = shorter candidate lists per class.  6 x 6 measured best both for a
@@ -3431,7 +3453,8 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             }
             if (l == 0) {                                  // camera rays: PIVOT family through the eye, robust re-tests in f32
                 MARK(KC_CLOSEST_PRIMARY);
-                CameraSource<R> cams{levels_[l], W, ty, map, TILE_W, TILE_H, (W + TILE_W - 1) / TILE_W};
+                static_assert(TILE_W == 32 && TILE_H == 8, "CameraSource::bin shifts by log2 of the tile size");
+                CameraSource<R> cams{levels_[l], W, ty, map, 5, 3, (W + TILE_W - 1) / TILE_W, sc_.w_mul, sc_.w_shift};
                 if (resident_) k_cull<R, CULL_PIVOT, CameraSource<R>, true><<<l_primary_.grid, CULL_THREADS, l_primary_.smem, stream_>>>(
                     cams, &ctr_->count[l], cull_eye_, frame_eye_, sc_.n_cull, lists_camera_, cq_l, ctr_);
                 else k_cull<R, CULL_PIVOT, CameraSource<R>, false><<<l_primary_.grid, CULL_THREADS, 0, stream_>>>(
@@ -3560,6 +3583,11 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
     }
     MARK(-1);
 #undef MARK
+    // the frame's counters follow the last kernel into page-locked memory: the caller's one stream synchronisation covers them
+    // (a blocking cudaMemcpy after it was a second round trip per frame)
+    if (!ctr_host_) CU_TRY(cudaHostAlloc((void**)&ctr_host_, sizeof(Counters), cudaHostAllocDefault));
+    CU_TRY(cudaMemcpyAsync(ctr_host_, ctr_, sizeof(Counters), cudaMemcpyDeviceToHost, stream_));
+    ctr_host_valid_ = true;
     CU_TRY(cudaGetLastError());
     return GMLRT_OK;
 }
