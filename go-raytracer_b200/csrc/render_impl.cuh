@@ -1165,38 +1165,42 @@ template <typename R> __device__ __forceinline__ void level_init_ray(const Level
     }
 }
 
+// A ray source hands a thread everything it needs of ray i in ONE call, fetch(): the loads of the next iteration's ray are
+// issued before the current ray's list is walked (k_cull), so their DRAM latency hides behind it (ncu, r02q: a third of the
+// camera-ray launch's stall samples sat on the first use of the ray record).
 template <typename R> struct CameraSource {                  // level 0: camera rays in (pixel, sample) order over the virtual rows of a tile
     Level<R> lv; int W, y0; RowMap map; int tile_w_log2, tile_h_log2, tiles_x; unsigned w_mul; int w_shift;
-    __device__ __forceinline__ int id(int i) const { return i; }
-    __device__ __forceinline__ void load(int i, Ray<R>& out) const { load_ray(lv.ray, i, out); }
-    __device__ __forceinline__ void init(int i) const { level_init_ray(lv, i); }
-    __device__ __forceinline__ int bin(int i) const {
+    __device__ __forceinline__ void fetch(int i, int& rid, Ray<R>& out, int& b) const {
+        rid = i;
+        load_ray(lv.ray, i, out);
         const int pix = i >> 2;
         const int row = fast_div(pix, w_mul, w_shift);
-        return (map.actual(y0 + row) >> tile_h_log2) * tiles_x + ((pix - row * W) >> tile_w_log2);
+        b = (map.actual(y0 + row) >> tile_h_log2) * tiles_x + ((pix - row * W) >> tile_w_log2);
     }
+    __device__ __forceinline__ void init(int rid) const { level_init_ray(lv, rid); }
     static constexpr bool is_shadow = false;
 };
 
 template <typename R> struct SpawnSource {                   // levels >= 1: reflection / refraction rays; the class key travels in the record
     Level<R> lv;
-    __device__ __forceinline__ int id(int i) const { return i; }
-    __device__ __forceinline__ void load(int i, Ray<R>& out) const { load_ray(lv.ray, i, out); }
-    __device__ __forceinline__ void init(int i) const { level_init_ray(lv, i); }
-    __device__ __forceinline__ int bin(int i) const { return ray_key(lv.ray, i); }
+    __device__ __forceinline__ void fetch(int i, int& rid, Ray<R>& out, int& b) const {
+        rid = i;
+        load_ray(lv.ray, i, out);
+        b = ray_key(lv.ray, i);
+    }
+    __device__ __forceinline__ void init(int rid) const { level_init_ray(lv, rid); }
     static constexpr bool is_shadow = false;
 };
 
 template <typename R> struct ShadowSource {                  // shadow rays of one light: slots [base, base + n)
     ShadowQueue<R> sq; int base; const int* perm;            // perm: by-region order of the slots (null: queue order)
     int shift, nb;                                           // class = sort_bin(region of the shaded point)
-    __device__ __forceinline__ int id(int i) const { return perm ? perm[base + i] : i; }
-    __device__ __forceinline__ void load(int i, Ray<R>& out) const {
-        const R* rec = sq.q + (size_t)(base + id(i)) * 8;
-        load_ray(rec, 0, out);
+    __device__ __forceinline__ void fetch(int i, int& rid, Ray<R>& out, int& b) const {
+        rid = perm ? perm[base + i] : i;
+        load_ray(sq.q + (size_t)(base + rid) * 8, 0, out);
+        b = sort_bin(sq.key[base + rid], shift, nb);
     }
-    __device__ __forceinline__ void init(int i) const { sq.first[base + id(i)] = 0x7fffffff; }
-    __device__ __forceinline__ int bin(int i) const { return sort_bin(sq.key[base + id(i)], shift, nb); }
+    __device__ __forceinline__ void init(int rid) const { sq.first[base + rid] = 0x7fffffff; }
     static constexpr bool is_shadow = true;
 };
 
@@ -1227,15 +1231,19 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
     // The counter is unsigned and stops growing once the queue is full: a lattice seen along an axis can leave dozens of
     // survivors per ray, and a signed counter that kept counting past 2^31 would turn the index negative and the stores
     // into out-of-bounds writes instead of the overflow-and-retrace path.
+    // (A warp that has seen the queue full never adds again, so the counter overshoots the capacity by at most one
+    // reservation per warp of the grid; a look at the counter before every atomic - a second L2 round trip - was 29 % of the
+    // shadow launches' stall samples.)
+    bool queue_full = false;                                    // uniform across the warp
     auto reserve = [&](int cnt) -> unsigned {
-        unsigned at = 0;
-        if (lane == 0) {
-            if (*reinterpret_cast<volatile unsigned*>(cq.count) >= (unsigned)cq.cap) at = 0xffffffffu;
-            else at = atomicAdd(reinterpret_cast<unsigned*>(cq.count), (unsigned)cnt);
-            if (at != 0xffffffffu && at + (unsigned)cnt > (unsigned)cq.cap) at = 0xffffffffu;
-            if (at == 0xffffffffu) ctr->overflow = 1;              // queue full: the host retries with smaller tiles
+        unsigned at = 0xffffffffu;
+        if (lane == 0 && !queue_full) {
+            at = atomicAdd(reinterpret_cast<unsigned*>(cq.count), (unsigned)cnt);
+            if (at >= (unsigned)cq.cap || (unsigned)cnt > (unsigned)cq.cap - at) { at = 0xffffffffu; ctr->overflow = 1; }   // queue full: the host retries with smaller tiles
         }
-        return __shfl_sync(0xffffffffu, at, 0);
+        at = __shfl_sync(0xffffffffu, at, 0);
+        queue_full = queue_full || at == 0xffffffffu;
+        return at;
     };
     auto flush = [&]() {
         if (staged == 0) return;
@@ -1245,17 +1253,25 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
         staged = 0;
         __syncwarp();
     };
+    const Ray<R> idle = {R(0), R(0), R(0), R(0), R(0), R(1)};
+    Ray<R> w_nx = idle;
+    int rid_nx = 0, b_nx = 0;
+    if ((int)blockIdx.x * CULL_THREADS + tid < n) src.fetch((int)blockIdx.x * CULL_THREADS + tid, rid_nx, w_nx, b_nx);
     for (int blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
         const int i = blk * CULL_THREADS + tid;
         const bool active = i < n;
-        Ray<R> w = {R(0), R(0), R(0), R(0), R(0), R(1)};
-        int rid = 0, first = 0, len = 0;
+        const Ray<R> w = w_nx;
+        const int rid = rid_nx;
+        int first = 0, len = 0;
         if (active) {
-            rid = src.id(i);
-            src.load(i, w); src.init(i);
-            const int b = src.bin(i);
-            const int2 rec = __ldg(bl.bin + min(max(b, 0), bl.n_bins - 1));
+            src.init(rid);
+            const int2 rec = __ldg(bl.bin + min(max(b_nx, 0), bl.n_bins - 1));
             first = rec.x; len = rec.y;
+        }
+        {   // the next iteration's ray: in flight while this one's list is walked
+            const int i2 = i + (int)gridDim.x * CULL_THREADS;
+            w_nx = idle; rid_nx = 0; b_nx = 0;
+            if (blk + (int)gridDim.x < nblocks && i2 < n) src.fetch(i2, rid_nx, w_nx, b_nx);
         }
         CullRay<R, FAMILY> cr;
         cr.init(w, frame);
@@ -1403,6 +1419,9 @@ __global__ void __launch_bounds__(EXACT_THREADS) k_exact_closest(const __grid_co
         int objs[U];
         if (U == 4 && k0 + 4 <= count) { const int4 v = *reinterpret_cast<const int4*>(cq.obj + k0); objs[0] = v.x; objs[1 % U] = v.y; objs[2 % U] = v.z; objs[3 % U] = v.w; }
         else { for (int u = 0; u < U; u++) objs[u] = k0 + u < count ? cq.obj[k0 + u] : -1; }
+        // one candidate per thread: its ray index is fetched with the object word, not after the ownership test on it (the
+        // kernel is a chain of dependent DRAM round trips - candidate, ray record, fold - and this takes one link out)
+        const int ri_first = U == 1 ? cq.ray[k0] : 0;
 #pragma unroll
         for (int u = 0; u < U; u++) {
         const int k = k0 + u;
@@ -1418,7 +1437,7 @@ __global__ void __launch_bounds__(EXACT_THREADS) k_exact_closest(const __grid_co
             if (obj < 0 || obj > sc.n_leaves) continue;
             if (obj < sc.n_leaves && !exact_owns<KINDS>(obj, n_spheres, sc.kind_begin[K_CSG])) continue;
         }
-        const int ri = cq.ray[k];
+        const int ri = U == 1 ? ri_first : cq.ray[k];
         int code = -1; R t = R(0);
         if (obj < sc.n_leaves) {                               // a padding record can only be reached by a NaN ray
             if (COUNT && !deferred) { n_exact++; n_flops += (unsigned)sc.obj_flops[obj]; }
@@ -1989,10 +2008,12 @@ __global__ void __launch_bounds__(256) k_gen(DevScene<R> sc, Level<R> lv, Counte
         for (int l = 0; l <= GMLRT_MAX_DEPTH; l++) ctr->hits[l] = 0;
         ctr->count[0] = S;
     }
-    if (i >= S) return;
-    double o[3], d[3];
-    camera_ray64(sc, CamSrc{y0, map}, i, o, d);
-    store_ray(lv.ray, i, (R)o[0], (R)o[1], (R)o[2], (R)d[0], (R)d[1], (R)d[2], 0, 0);
+    const CamSrc cam{y0, map};
+    for (int k = i; k < S; k += gridDim.x * blockDim.x) {                        // a few thousand resident blocks walk the tile (one block per 256 samples spent a fifth of its stall samples on its own start-up)
+        double o[3], d[3];
+        camera_ray64(sc, cam, k, o, d);
+        store_ray(lv.ray, k, (R)o[0], (R)o[1], (R)o[2], (R)d[0], (R)d[1], (R)d[2], 0, 0);
+    }
 }
 
 // Background of a ray that hit nothing: Lerp(BgStart, BgEnd, 0.5 (dir.Y + 1)) (raytracer.go:493-497)
@@ -3429,7 +3450,7 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
         cam.y0 = ty;
         const int S = rows * W * 4;
         MARK(KC_GEN);
-        k_gen<R><<<(S + 255) / 256, 256, 0, stream_>>>(sc_, levels_[0], ctr_, ty, rows, map, slots_, n_slots_);
+        k_gen<R><<<std::min((S + 255) / 256, sms_ * 32), 256, 0, stream_>>>(sc_, levels_[0], ctr_, ty, rows, map, slots_, n_slots_);
         totals_.launches++;
         totals_.rays_primary += (unsigned long long)S;
         for (int l = 0; l < depth_eff_; l++) {

@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgmlrt.so")
+LIB_PATH = os.environ.get("GMLRT_LIB") or os.path.join(_HERE, "libgmlrt.so")      # GMLRT_LIB: another build of the same library (A/B measurements)
 
 IPC_HANDLE_BYTES = 64
 PRECISION_F32 = 0
