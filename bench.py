@@ -375,9 +375,20 @@ def main():
         shm_path = f"/dev/shm/gmlrt_frame_{os.environ.get('MASTER_PORT', '0')}"
         if rank == 0:
             with open(shm_path, "wb") as f:
-                f.truncate(W * H * 4)
+                f.truncate(W * H * 4 + 4096)
         dist.barrier()
         shared = np.memmap(shm_path, dtype=np.uint8, mode="r+", shape=(H, W, 4))
+        # "the raster is complete" = every rank has finished its copy: one 8-byte slot per rank after the raster, each written by
+        # its owner only and polled by all (a host-side barrier of a few microseconds; a NCCL barrier is a kernel launch and a stream
+        # synchronisation per frame, longer than a rank's whole copy)
+        slots = np.memmap(shm_path, dtype=np.int64, mode="r+", offset=W * H * 4, shape=(512,))
+        epoch = [0]
+
+        def host_barrier():
+            epoch[0] += 1
+            slots[rank * 8] = epoch[0]                          # one cache line per rank
+            while int(slots[0:world * 8:8].min()) < epoch[0]:
+                pass
         rt = torch.cuda.cudart()
         reg = rt.cudaHostRegister(shared.ctypes.data, W * H * 4, 0)
         if use_ipc and rank != 0:
@@ -392,7 +403,7 @@ def main():
             ctx.trace()
             tc = time.perf_counter()
             ctx.download_rows(shared)
-            dist.barrier()                                      # the raster is complete in host memory
+            host_barrier()                                      # the raster is complete in host memory
             td = time.perf_counter()
             hphase["upload"] += (tb - ta) * 1e3; hphase["trace"] += (tc - tb) * 1e3; hphase["download_rows+barrier"] += (td - tc) * 1e3
         for _ in range(2):
@@ -420,7 +431,7 @@ def main():
                 e2e_host["gather_check"] = {"pixels_equal": float(same.mean())}
             barrier()
         rt.cudaHostUnregister(shared.ctypes.data)
-        del shared
+        del shared, slots
         dist.barrier()
         if rank == 0:
             os.unlink(shm_path)

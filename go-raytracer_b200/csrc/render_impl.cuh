@@ -1170,8 +1170,8 @@ template <typename R> __device__ __forceinline__ void level_init_ray(const Level
 // camera-ray launch's stall samples sat on the first use of the ray record).
 template <typename R> struct CameraSource {                  // level 0: camera rays in (pixel, sample) order over the virtual rows of a tile
     Level<R> lv; int W, y0; RowMap map; int tile_w_log2, tile_h_log2, tiles_x; unsigned w_mul; int w_shift;
-    __device__ __forceinline__ void fetch(int i, int& rid, Ray<R>& out, int& b) const {
-        rid = i;
+    __device__ __forceinline__ void fetch(int i, int& rid, Ray<R>& out, int& b, int& skip) const {
+        rid = i; skip = -1;
         load_ray(lv.ray, i, out);
         const int pix = i >> 2;
         const int row = fast_div(pix, w_mul, w_shift);
@@ -1183,8 +1183,8 @@ template <typename R> struct CameraSource {                  // level 0: camera 
 
 template <typename R> struct SpawnSource {                   // levels >= 1: reflection / refraction rays; the class key travels in the record
     Level<R> lv;
-    __device__ __forceinline__ void fetch(int i, int& rid, Ray<R>& out, int& b) const {
-        rid = i;
+    __device__ __forceinline__ void fetch(int i, int& rid, Ray<R>& out, int& b, int& skip) const {
+        rid = i; skip = -1;
         load_ray(lv.ray, i, out);
         b = ray_key(lv.ray, i);
     }
@@ -1195,10 +1195,11 @@ template <typename R> struct SpawnSource {                   // levels >= 1: ref
 template <typename R> struct ShadowSource {                  // shadow rays of one light: slots [base, base + n)
     ShadowQueue<R> sq; int base; const int* perm;            // perm: by-region order of the slots (null: queue order)
     int shift, nb;                                           // class = sort_bin(region of the shaded point)
-    __device__ __forceinline__ void fetch(int i, int& rid, Ray<R>& out, int& b) const {
+    __device__ __forceinline__ void fetch(int i, int& rid, Ray<R>& out, int& b, int& skip) const {
         rid = perm ? perm[base + i] : i;
         load_ray(sq.q + (size_t)(base + rid) * 8, 0, out);
         b = sort_bin(sq.key[base + rid], shift, nb);
+        skip = sq.skip[base + rid];                          // the shaded object: inShadow passes over it (:418), and its bound holds the ray's origin - a sure survivor
     }
     __device__ __forceinline__ void init(int rid) const { sq.first[base + rid] = 0x7fffffff; }
     static constexpr bool is_shadow = true;
@@ -1255,13 +1256,14 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
     };
     const Ray<R> idle = {R(0), R(0), R(0), R(0), R(0), R(1)};
     Ray<R> w_nx = idle;
-    int rid_nx = 0, b_nx = 0;
-    if ((int)blockIdx.x * CULL_THREADS + tid < n) src.fetch((int)blockIdx.x * CULL_THREADS + tid, rid_nx, w_nx, b_nx);
+    int rid_nx = 0, b_nx = 0, skip_nx = -1;
+    if ((int)blockIdx.x * CULL_THREADS + tid < n) src.fetch((int)blockIdx.x * CULL_THREADS + tid, rid_nx, w_nx, b_nx, skip_nx);
     for (int blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
         const int i = blk * CULL_THREADS + tid;
         const bool active = i < n;
         const Ray<R> w = w_nx;
         const int rid = rid_nx;
+        const uint32_t skip_off = skip_nx < 0 ? 0xffffffffu : (uint32_t)skip_nx * (uint32_t)(4 * sizeof(R));      // the skipped object as a list entry
         int first = 0, len = 0;
         if (active) {
             src.init(rid);
@@ -1270,8 +1272,8 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
         }
         {   // the next iteration's ray: in flight while this one's list is walked
             const int i2 = i + (int)gridDim.x * CULL_THREADS;
-            w_nx = idle; rid_nx = 0; b_nx = 0;
-            if (blk + (int)gridDim.x < nblocks && i2 < n) src.fetch(i2, rid_nx, w_nx, b_nx);
+            w_nx = idle; rid_nx = 0; b_nx = 0; skip_nx = -1;
+            if (blk + (int)gridDim.x < nblocks && i2 < n) src.fetch(i2, rid_nx, w_nx, b_nx, skip_nx);
         }
         CullRay<R, FAMILY> cr;
         cr.init(w, frame);
@@ -1284,6 +1286,11 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
             // Survivors are staged per warp in shared memory and flushed to the queue STAGE at a time: one atomic on the
             // queue's counter per flush.  (One atomic per warp and window - a million and more per launch, all on one
             // address - serialised in L2 and was ALL of this kernel's time when first measured.)
+            if (Source::is_shadow && skip_off != 0xffffffffu) {    // a shadow ray never asks about the object it starts on: half of all shadow candidates, dropped here instead of in k_exact_shadow
+                const uint32_t* e0 = bl.entry + first + k0;
+                for (uint32_t m = lo; m; ) { const int j = __clz(m); m &= ~(0x80000000u >> j); if (e0[j] == skip_off) lo &= ~(0x80000000u >> j); }
+                for (uint32_t m = hi; m; ) { const int j = __clz(m); m &= ~(0x80000000u >> j); if (e0[32 + j] == skip_off) hi &= ~(0x80000000u >> j); }
+            }
             const int mine = __popc(lo) + __popc(hi);
             if (!__any_sync(0xffffffffu, mine != 0)) continue;
             int incl = mine;
@@ -1628,15 +1635,18 @@ static __global__ void __launch_bounds__(1024) k_sort_scan(int nb, int* hist, in
     }
 }
 
-// The same scan over many bins (the key sort has 10^5 - 5 10^5): one block per tile of SCAN_TILE bins, all co-resident
-// (the host launches at most one block per SM).  A block sums its tile, publishes the sum with a flag that carries the
-// launch's epoch (so nothing needs resetting), waits for the sums of the tiles before it and writes its prefixes.
-constexpr int SCAN_TILE = 4096;
+// The same scan over many bins (the key sort has 10^5 - 2 10^6): tiles of SCAN_TILE bins dealt round-robin to co-resident blocks
+// (the host launches at most one block per SM; a block takes its tiles in ascending order, so the tiles a tile waits for are
+// finished or in progress on a running block).  A block sums its tile, publishes the sum with a flag that carries the launch's
+// epoch (so nothing needs resetting), waits for the sums of the tiles before it and writes its prefixes.
+constexpr int SCAN_TILE = 4096, SCAN_TILES_MAX = 1024;
 static __global__ void __launch_bounds__(1024) k_sort_scan_tiles(int nb, int* hist, int* cursor, int clear, volatile int* tile_sum, volatile int* tile_flag, int epoch) {
     __shared__ int warp_tot[32];
     __shared__ int s_base;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int b = blockIdx.x * SCAN_TILE + 4 * tid;
+    const int n_tiles = (nb + SCAN_TILE - 1) / SCAN_TILE;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int b = tile * SCAN_TILE + 4 * tid;
     int4 v = make_int4(0, 0, 0, 0);
     if (b + 3 < nb) v = *reinterpret_cast<const int4*>(hist + b);
     else { if (b < nb) v.x = hist[b]; if (b + 1 < nb) v.y = hist[b + 1]; if (b + 2 < nb) v.z = hist[b + 2]; }
@@ -1652,13 +1662,13 @@ static __global__ void __launch_bounds__(1024) k_sort_scan_tiles(int nb, int* hi
         for (int off = 1; off < 32; off <<= 1) { const int u = __shfl_up_sync(0xffffffffu, ti, off); if (lane >= off) ti += u; }
         warp_tot[lane] = ti - t;
         if (lane == 31) {                                  // this tile's total: publish, then the flag
-            tile_sum[blockIdx.x] = ti;
+            tile_sum[tile] = ti;
             __threadfence();
-            tile_flag[blockIdx.x] = epoch;
+            tile_flag[tile] = epoch;
         }
         // the tiles before this one: lane k looks after tiles k, k + 32, ...
         int before = 0;
-        for (int t0 = lane; t0 < (int)blockIdx.x; t0 += 32) {
+        for (int t0 = lane; t0 < tile; t0 += 32) {
             while (tile_flag[t0] != epoch) { }
             __threadfence();
             before += tile_sum[t0];
@@ -1676,6 +1686,8 @@ static __global__ void __launch_bounds__(1024) k_sort_scan_tiles(int nb, int* hi
         if (b < nb) { cursor[b] = run; if (clear) hist[b] = 0; }
         if (b + 1 < nb) { cursor[b + 1] = run + v.x; if (clear) hist[b + 1] = 0; }
         if (b + 2 < nb) { cursor[b + 2] = run + v.x + v.y; if (clear) hist[b + 2] = 0; }
+    }
+    __syncthreads();                                       // warp_tot / s_base are rewritten by the block's next tile
     }
 }
 
@@ -1705,7 +1717,7 @@ __global__ void __launch_bounds__(SORT_THREADS) k_sort_scatter(const __grid_cons
 // point into one cone, so the packet stage applies to them too.  Up to 2^17 bins: histogram and cursors in global
 // memory, one warp-aggregated atomic per distinct key of a warp.  The order inside a bin is not deterministic; the
 // result of a ray does not depend on which warp tests it.
-constexpr int KEY_BINS_MAX = 1 << 19;
+constexpr int KEY_BINS_MAX = 1 << 21;        // histogram / cursor arrays of the key sort are sized for this; GMLRT_KEY_BINS (default 2^19) is the limit in use
 
 __device__ __forceinline__ void key_peers(int key, bool valid, unsigned& peers, int& rank, int& leader) {
     const unsigned act = __ballot_sync(0xffffffffu, valid);
@@ -2536,8 +2548,8 @@ public:
         CU_TRY(cudaMemcpyToSymbol(c_pcg_jump, tab, sizeof tab));
         CU_TRY(cudaMalloc(&ctr_, sizeof(Counters)));
         CU_TRY(cudaMemset(ctr_, 0, sizeof(Counters)));
-        CU_TRY(cudaMalloc(&scan_tiles_, 512 * sizeof(int)));
-        CU_TRY(cudaMemset(scan_tiles_, 0, 512 * sizeof(int)));
+        CU_TRY(cudaMalloc(&scan_tiles_, 2 * SCAN_TILES_MAX * sizeof(int)));
+        CU_TRY(cudaMemset(scan_tiles_, 0, 2 * SCAN_TILES_MAX * sizeof(int)));
         const int smem_max = 200 * 1024;
         auto allow = [&](auto kernel) -> int { CU_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max)); return GMLRT_OK; };
         int rc;
@@ -2701,8 +2713,8 @@ private:
     // exclusive scan of a histogram on `st`: tiles across co-resident blocks when there are many bins, else one block
     void launch_scan(int nb, int* hist, int* cursor, int clear, cudaStream_t st) {
         const int tiles = (nb + SCAN_TILE - 1) / SCAN_TILE;
-        if (tiles > 2 && tiles <= sms_ && scan_tiles_ && st == stream_) {
-            k_sort_scan_tiles<<<tiles, 1024, 0, st>>>(nb, hist, cursor, clear, scan_tiles_, scan_tiles_ + 256, ++scan_epoch_);
+        if (tiles > 2 && tiles <= SCAN_TILES_MAX && scan_tiles_ && st == stream_) {
+            k_sort_scan_tiles<<<std::min(tiles, sms_), 1024, 0, st>>>(nb, hist, cursor, clear, scan_tiles_, scan_tiles_ + SCAN_TILES_MAX, ++scan_epoch_);
         } else k_sort_scan<<<1, 1024, 0, st>>>(nb, hist, cursor, clear);
     }
     int* scan_tiles_ = nullptr; int scan_epoch_ = 0;             // tile sums + flags of k_sort_scan_tiles (main stream only)
@@ -2988,7 +3000,8 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     // 1.10), where a class holds only a handful of rays: shorter lists win over lanes that share a list.
     sc.key_k = (int)env_size("GMLRT_KEY_K", 6); sc.key_k = std::max(1, std::min(sc.key_k, 8));
     sc.key_shift = 0;
-    while ((size_t)(((n_regions - 1) >> sc.key_shift) + 1) * 6 * sc.key_k * sc.key_k > (size_t)KEY_BINS_MAX) sc.key_shift++;
+    const size_t key_bins_limit = std::min<size_t>(std::max<size_t>(env_size("GMLRT_KEY_BINS", (size_t)1 << 19), 6 * 64), (size_t)KEY_BINS_MAX);
+    while ((size_t)(((n_regions - 1) >> sc.key_shift) + 1) * 6 * sc.key_k * sc.key_k > key_bins_limit) sc.key_shift++;
     key_nb_ = (((n_regions - 1) >> sc.key_shift) + 1) * 6 * sc.key_k * sc.key_k;
     sort_spawned_ = env_size("GMLRT_SORT_SPAWNED", 1) != 0;
     for (int k = 0; k < 3; k++) { sc.ambient[k] = (R)S.h.ambient[k]; sc.bg0[k] = (R)S.h.bg_start[k]; sc.bg1[k] = (R)S.h.bg_end[k]; }
