@@ -588,7 +588,7 @@ def main():
         "e2e_new_scene": {"value": rays_frame / (e2e_new_ms * 1e-3) / 1e6, "unit": "Mrays/s", "frame_ms": e2e_new_ms, "phase_ms": e2e_new_phase,
                           "note": "GMLRT_NO_UPLOAD_CACHE=1: every step parses the blob and rebuilds cull tables and class lists, as for a scene never seen before"},
         "e2e_pageable": {"value": rays_frame / (e2e_pg_ms * 1e-3) / 1e6, "unit": "Mrays/s", "frame_ms": e2e_pg_ms, "phase_ms": e2e_pg_phase,
-                         "destination": "pageable host array (image.NewRGBA of an unmodified caller): staged in 1 MB chunks by gmlrt_download",
+                         "destination": "pageable host array (image.NewRGBA of an unmodified caller): staged in 4 MB chunks by gmlrt_download, copied out by 8 host threads",
                          "slower_than_page_locked": e2e_pg_ms / e2e_ms - 1.0},
         "kernel_ms_per_frame": {names[k]: class_ms[k] / args.steps for k in range(9)},
         "kernel_ms_per_frame_note": "second pass of the same K steps with an event before every launch and all launches on one stream; "

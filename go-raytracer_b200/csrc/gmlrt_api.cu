@@ -592,7 +592,9 @@ int gmlrt_download(gmlrt_ctx* c, uint8_t* rgba, size_t rgba_bytes) {
         API_CU(cudaHostAlloc((void**)&c->pinned, need, cudaHostAllocDefault));
         c->pinned_bytes = need;
     }
-    const size_t chunk = (size_t)1 << 20;
+    // 4 MB DMA chunks (32 one-megabyte copies cost more in per-copy overhead than they gained in overlap); every chunk is copied
+    // out by ALL the host threads, an eighth each, as soon as its event fires: the tail after the last DMA is one eighth of a chunk
+    const size_t chunk = (size_t)4 << 20;
     const int n_chunks = (int)((need + chunk - 1) / chunk);
     while ((int)c->ev_chunk.size() < n_chunks) {
         cudaEvent_t e;
@@ -604,14 +606,15 @@ int gmlrt_download(gmlrt_ctx* c, uint8_t* rgba, size_t rgba_bytes) {
         API_CU(cudaMemcpyAsync(c->pinned + off, r0->frame() + off, len, cudaMemcpyDeviceToHost, r0->stream()));
         API_CU(cudaEventRecord(c->ev_chunk[k], r0->stream()));
     }
-    const int n_threads = std::min(8, n_chunks);
+    const int n_threads = (int)std::max(1u, std::min(8u, std::thread::hardware_concurrency()));
     std::vector<cudaError_t> terr(n_threads, cudaSuccess);
     auto drain = [&](int t) {
-        for (int k = t; k < n_chunks; k += n_threads) {
+        for (int k = 0; k < n_chunks; k++) {
             const cudaError_t e = cudaEventSynchronize(c->ev_chunk[k]);
             if (e != cudaSuccess) { terr[t] = e; return; }
-            const size_t off = (size_t)k * chunk;
-            std::memcpy(rgba + off, c->pinned + off, std::min(chunk, need - off));
+            const size_t off = (size_t)k * chunk, len = std::min(chunk, need - off);
+            const size_t a = len * (size_t)t / (size_t)n_threads, b = len * (size_t)(t + 1) / (size_t)n_threads;
+            std::memcpy(rgba + off + a, c->pinned + off + a, b - a);
         }
     };
     std::vector<std::thread> workers;

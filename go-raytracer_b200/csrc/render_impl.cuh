@@ -535,6 +535,9 @@ __device__ __noinline__ bool csg_hit(const int* prog, int len, const int* kinds,
     return false;
 }
 
+// a line on its way to L2 two iterations before it is loaded: costs no register, so the compiler cannot sink it to the use
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 // ------------------------------------------------------------------ TMA bulk copy + mbarrier (sm_90+/sm_100a)
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
@@ -1177,6 +1180,8 @@ template <typename R> struct CameraSource {                  // level 0: camera 
         const int row = fast_div(pix, w_mul, w_shift);
         b = (map.actual(y0 + row) >> tile_h_log2) * tiles_x + ((pix - row * W) >> tile_w_log2);
     }
+    __device__ __forceinline__ void ahead(int i) const { prefetch_l2(lv.ray + (size_t)i * RAY_WORDS); }
+    __device__ __forceinline__ int cls(int b) const { return b; }
     __device__ __forceinline__ void init(int rid) const { level_init_ray(lv, rid); }
     static constexpr bool is_shadow = false;
 };
@@ -1188,6 +1193,8 @@ template <typename R> struct SpawnSource {                   // levels >= 1: ref
         load_ray(lv.ray, i, out);
         b = ray_key(lv.ray, i);
     }
+    __device__ __forceinline__ void ahead(int i) const { prefetch_l2(lv.ray + (size_t)i * RAY_WORDS); }
+    __device__ __forceinline__ int cls(int b) const { return b; }
     __device__ __forceinline__ void init(int rid) const { level_init_ray(lv, rid); }
     static constexpr bool is_shadow = false;
 };
@@ -1198,10 +1205,16 @@ template <typename R> struct ShadowSource {                  // shadow rays of o
     __device__ __forceinline__ void fetch(int i, int& rid, Ray<R>& out, int& b, int& skip) const {
         rid = perm ? perm[base + i] : i;
         load_ray(sq.q + (size_t)(base + rid) * 8, 0, out);
-        b = sort_bin(sq.key[base + rid], shift, nb);
+        b = sq.key[base + rid];                              // raw: sort_bin() at the use (cls), or the fetch would wait for the load it was issued early for
         skip = sq.skip[base + rid];                          // the shaded object: inShadow passes over it (:418), and its bound holds the ray's origin - a sure survivor
     }
     __device__ __forceinline__ void init(int rid) const { sq.first[base + rid] = 0x7fffffff; }
+    __device__ __forceinline__ void ahead(int i) const {
+        if (perm) return;                                    // (sorted: the slot is a load away)
+        prefetch_l2(sq.q + (size_t)(base + i) * 8);
+        if ((i & 7) == 0) { prefetch_l2(sq.key + base + i); prefetch_l2(sq.skip + base + i); }      // 8 four-byte entries per 32-byte sector
+    }
+    __device__ __forceinline__ int cls(int b) const { return sort_bin(b, shift, nb); }
     static constexpr bool is_shadow = true;
 };
 
@@ -1267,13 +1280,15 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
         int first = 0, len = 0;
         if (active) {
             src.init(rid);
-            const int2 rec = __ldg(bl.bin + min(max(b_nx, 0), bl.n_bins - 1));
+            const int2 rec = __ldg(bl.bin + min(max(src.cls(b_nx), 0), bl.n_bins - 1));
             first = rec.x; len = rec.y;
         }
         {   // the next iteration's ray: in flight while this one's list is walked
             const int i2 = i + (int)gridDim.x * CULL_THREADS;
             w_nx = idle; rid_nx = 0; b_nx = 0; skip_nx = -1;
             if (blk + (int)gridDim.x < nblocks && i2 < n) src.fetch(i2, rid_nx, w_nx, b_nx, skip_nx);
+            const int i3 = i2 + (int)gridDim.x * CULL_THREADS;
+            if (i3 < n) src.ahead(i3);                         // ... and the one after it on its way to L2
         }
         CullRay<R, FAMILY> cr;
         cr.init(w, frame);
@@ -2161,9 +2176,13 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
     i_nx = -1;
     if ((long long)hs + stride < n) i_nx = lv.hits[hs + stride];
     int h = -1; R t_pre = R(0);
-    if (live) level_hit<R, PICKLESS>(lv, i, h, t_pre);
-    live = live && h >= 0;
     Ray<R> w = {R(0), R(0), R(0), R(0), R(0), R(1)};
+    if (live) { load_ray(lv.ray, i, w); level_hit<R, PICKLESS>(lv, i, h, t_pre); }     // both need only i: two loads in flight, not one behind the other
+    if (i_nx >= 0) {                                       // the next iteration's record and key on their way to L2
+        prefetch_l2(lv.ray + (size_t)i_nx * RAY_WORDS);
+        if (PICKLESS != 0) prefetch_l2(reinterpret_cast<const unsigned long long*>(lv.order) + i_nx);
+    }
+    live = live && h >= 0;
     V3<R> P = mk(R(0), R(0), R(0)), N = P;
     R mat[10];
     for (int k = 0; k < 10; k++) mat[k] = R(0);
@@ -2173,7 +2192,6 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
         leaf = h & HIT_LEAF_MASK;
         int face = h >> 28;
         const bool flip = (h & HIT_FLIP_BIT) != 0;          // CSG: surface of a subtracted solid
-        load_ray(lv.ray, i, w);
         const R t = PICKLESS != 0 ? t_pre : lv.t[i];
         const R* Mw = sc.w2o + (size_t)leaf * 12;
         Ray<R> o;

@@ -14,7 +14,7 @@ GMLRT_FUSE_EXACT=0 run nofuse
 run fuse
 GMLRT_FUSE_EXACT=0 run nofuse
 run fuse
-for c in csg256 proctex mixed4096; do
+for c in nothing; do
   for f in 0 1; do
   GMLRT_FUSE_EXACT=$f timeout 600 python bench.py --config $c --steps 5 --warmup 3 --no-cpu-baseline --no-parity 2>/dev/null | python -c "
 import json,sys

@@ -128,6 +128,36 @@ def test_f32_tolerance_at_baseline_size(name):
     assert res["primary_flips"] == 0, res
 
 
+def test_upload_cache_reuses_and_invalidates(ctx64):
+    """gmlrt_upload keeps what it derived from a blob when the next blob is byte-identical (same partition, same GMLRT_*
+    environment) and rebuilds otherwise: A, A again, B, A in one context give the rasters fresh uploads give, and a
+    tuning variable set between two uploads of A takes effect."""
+    a = scenes.to_blob(scenes.mixed(128, 80, grid=(4, 4, 2), depth=3))
+    b = scenes.to_blob(scenes.spheres_lattice(128, 80, grid=(4, 2, 2)))
+    want_a, _ = oracle.render(a, threads=THREADS)
+    want_b, _ = oracle.render(b, threads=THREADS)
+    c = cuda.Context((0,), cuda.PRECISION_F64_PARITY)
+    try:
+        for blob, want in ((a, want_a), (a, want_a), (b, want_b), (a, want_a)):
+            got, st = c.render(blob)
+            assert np.array_equal(got, want)
+        c.upload(a); n1 = c.trace().kernel_launches
+        c.upload(a); n2 = c.trace().kernel_launches              # cache hit: same launches, same raster
+        assert n1 == n2 and np.array_equal(c.download(), want_a)
+        os.environ["GMLRT_TILE_SAMPLES"] = str(4 * 128 * 16)      # 16-row tiles: five tiles instead of one
+        try:
+            c.upload(a)
+            n3 = c.trace().kernel_launches
+            tiled = c.download()
+        finally:
+            del os.environ["GMLRT_TILE_SAMPLES"]
+        assert n3 > n2 and np.array_equal(tiled, want_a)
+        c.upload(a)
+        assert c.trace().kernel_launches == n1
+    finally:
+        c.close()
+
+
 def test_tiling_does_not_change_the_raster(ctx64):
     blob = scenes.to_blob(scenes.mixed(256, 150, grid=(4, 4, 4), depth=3))
     whole, _ = ctx64.render(blob)
