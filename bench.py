@@ -493,12 +493,15 @@ def main():
     MISS_DEEP = CH - (NH - NH0)                                            # rays of levels >= 1 that hit nothing: finished by k_hitlist
     Xs = float(counts[15]); Xc = float(counts[8]) - Xs                     # exact tests: shadow / closest candidates
     key = 8                                                                # fold key (f32) / hit code + T (f64): 8 bytes per ray either way
+    from go_raytracer_b200 import lowering as _lowering
+    compact = all(sf["kind"] == 0 for sf in _lowering.describe(blob)["surfaces"])   # constant materials only: the shading record holds the surface index
+    rec_w, rec_r = (9, 8) if compact else (16, 15)                         # words of the shading record k_shade writes / k_resolve reads per hit
     model_bytes = {
         0: P * 8 * wb,                                                     # gen: one ray record per sample
         6: NH0 * (4 + key + 3 * wb) if args.precision == "f32" else 0.0,   # primary points: hit index + fold key in, object-space point out
-        4: NH * (4 + key + 8 * wb + 16 * wb) + NH0 * 3 * wb * (1 if args.precision == "f32" else 0) + S * (8 * wb + 13) + CH * (8 * wb + 4),   # shade: per hit the index, key, ray in and the record out; shadow records (+ skip, key, target, flag) and child records (+ sort key) out
-        5: NH * (4 + 8 * wb + 15 * wb + nl + 3 * wb) + CH * 3 * wb + P * key + (P - NH0) * 8 * wb + NH0 * 3 * wb + P,   # resolve: per hit the index, ray, record, flags in, colour out; children's colours in; pixel pass: keys, the records of the misses, sample colours in, RGBA8 out
-        7: Xc * ((8 + 8 * wb + 4 + wb) + (8 + wb + 8 + 4 + wb)) + Xs * (8 + 8 * wb + 8),           # exact: candidate + ray record + result; pick pass; shadow candidates
+        4: NH * (4 + key + 8 * wb + rec_w * wb) + NH0 * 3 * wb * (1 if args.precision == "f32" else 0) + S * (8 * wb + 13) + CH * (8 * wb + 4),   # shade: per hit the index, key, ray in and the record out; shadow records (+ skip, key, target, flag) and child records (+ sort key) out
+        5: NH * (4 + 8 * wb + rec_r * wb + nl + 3 * wb) + CH * 3 * wb + P * key + (P - NH0) * 8 * wb + NH0 * 3 * wb + P,   # resolve: per hit the index, ray, record, flags in, colour out; children's colours in; pixel pass: keys, the records of the misses, sample colours in, RGBA8 out
+        7: Xc * ((8 + 8 * wb + 8) if args.precision == "f32" else ((8 + 8 * wb + 4 + wb) + (8 + wb + 8 + 4 + wb))) + Xs * (8 + 8 * wb + 8),   # exact: candidate + ray record + the fold's 8 bytes (f32, pickless: the folded key is the result); f64: + per-candidate result and the order / pick passes; shadow: candidate, record, skip + first
         8: CH * (8 + 16 * wb) + C * key + NH * 4 + MISS_DEEP * (8 * wb + 3 * wb),                  # sort + compaction: key sort moves the 8-word records; hit list reads every key, writes the hits, finishes the deep misses
     }
     cull_flops_all = 15.0 * float(counts[11]) + 7.0 * float(counts[12] + counts[13]) + 20.0 * float(counts[10])

@@ -61,6 +61,7 @@ template <typename R> struct DevScene {
     const unsigned long long* cum_flops;   // [n] credited flops of scan-order objects 0..s
     const R* w2o;                  // [n][12] rows 0..2 of WorldToObject
     const int* scan_of;            // device index -> scan-order index (tie-breaks, ids)
+    int rec_compact;               // every surface is a constant material: the shading record holds the surface index instead of its 9 material words
     int pickless;                  // float32: the scan folds (bits of T) << 32 | leaf << 4 | flip << 3 | face (mode 2; mode 1, scenes of spheres
                                    // and planes only: just the device index - measured 0.3 ms faster in k_shade), which IS the closest hit -
                                    // k_shade / k_resolve decode it, the exact kernels store no per-candidate result and the pick pass is
@@ -2069,14 +2070,22 @@ __global__ void __launch_bounds__(HITLIST_THREADS) k_hitlist(const __grid_consta
     unsigned long long n_hit = 0;
     for (int blk0 = blockIdx.x * HITLIST_RAYS; blk0 < n; blk0 += gridDim.x * HITLIST_RAYS) {       // uniform per block
         unsigned bal[HITLIST_PER_THREAD];
+        int hs[HITLIST_PER_THREAD];
         int mine = 0;
+        // the fold keys of the thread's rays first, all loads in flight together (behind the stores of the miss handling below
+        // the compiler has to keep them in program order: the pointers may alias)
 #pragma unroll
         for (int k = 0; k < HITLIST_PER_THREAD; k++) {
             const int i = blk0 + (wid * HITLIST_PER_THREAD + k) * 32 + lane;      // a warp owns 32 * HITLIST_PER_THREAD consecutive rays: its hits stay in order
+            hs[k] = -1;
+            if (i < n) { R t; level_hit<R, PICKLESS>(lv, i, hs[k], t); }
+        }
+#pragma unroll
+        for (int k = 0; k < HITLIST_PER_THREAD; k++) {
+            const int i = blk0 + (wid * HITLIST_PER_THREAD + k) * 32 + lane;
             bool hit = false;
             if (i < n) {
-                int h; R t;
-                level_hit<R, PICKLESS>(lv, i, h, t);
+                const int h = hs[k];
                 hit = h >= 0;
                 if (ids) {                                     // level 0, counting mode: primary hit ids in (y, x, sample) order
                     const int pix = i >> 2;
@@ -2278,8 +2287,13 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
         R* rec = lv.rec + hs;
         rec[(REC_P + 0) * cap] = P.x; rec[(REC_P + 1) * cap] = P.y; rec[(REC_P + 2) * cap] = P.z;
         rec[(REC_N + 0) * cap] = N.x; rec[(REC_N + 1) * cap] = N.y; rec[(REC_N + 2) * cap] = N.z;
-        rec[(REC_COL + 0) * cap] = mat[0]; rec[(REC_COL + 1) * cap] = mat[1]; rec[(REC_COL + 2) * cap] = mat[2];
-        rec[REC_REFL * cap] = refl; rec[REC_TRANSP * cap] = transp;
+        // constant materials (folded at lowering, maybeSimplifySurfaceFn): the record names the surface and k_resolve reads the 9
+        // words from the surface table (in L1 / L2) instead of 36 bytes per hit written here and read back there
+        if (sc.rec_compact) *reinterpret_cast<int*>(rec + (REC_COL + 0) * cap) = sc.surface[leaf];
+        else {
+            rec[(REC_COL + 0) * cap] = mat[0]; rec[(REC_COL + 1) * cap] = mat[1]; rec[(REC_COL + 2) * cap] = mat[2];
+            rec[REC_REFL * cap] = refl; rec[REC_TRANSP * cap] = transp;
+        }
         R kr = R(0);
         if (transp > R(0)) {                                                         // fresnel :456-467
             R cosi = dot(D, N) / (length(D) * length(N));
@@ -2288,7 +2302,7 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(DevScene<R> sc, Level<R
             kr = r0 + (R(1) - r0) * gm<R>::pow(R(1) - gm<R>::abs(cosi), R(5));
         }
         rec[REC_KR * cap] = kr;
-        rec[REC_KD * cap] = mat[7]; rec[REC_KS * cap] = mat[8]; rec[REC_NEXP * cap] = mat[9];
+        if (!sc.rec_compact) { rec[REC_KD * cap] = mat[7]; rec[REC_KS * cap] = mat[8]; rec[REC_NEXP * cap] = mat[9]; }
         rec[REC_INLEN * cap] = length(D);
     }
     // Children.  Every ray may append one shadow query per light that can reach P (inShadow :411-414), a reflection
@@ -2428,9 +2442,16 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_resolve(DevScene<R> sc, Level
         const R* rec = lv.rec + hs;
         const V3<R> P = mk(rec[(REC_P + 0) * cap], rec[(REC_P + 1) * cap], rec[(REC_P + 2) * cap]);
         const V3<R> N = mk(rec[(REC_N + 0) * cap], rec[(REC_N + 1) * cap], rec[(REC_N + 2) * cap]);
-        const V3<R> C = mk(rec[(REC_COL + 0) * cap], rec[(REC_COL + 1) * cap], rec[(REC_COL + 2) * cap]);
-        const R refl = rec[REC_REFL * cap], transp = rec[REC_TRANSP * cap], kr = rec[REC_KR * cap];
-        const R kd = rec[REC_KD * cap], ks = rec[REC_KS * cap], nexp = rec[REC_NEXP * cap];
+        V3<R> C; R refl, transp, kd, ks, nexp;
+        const R kr = rec[REC_KR * cap];
+        if (sc.rec_compact) {                                  // the surface's constant material (k_shade stored its index)
+            const R* m = sc.surfaces[*reinterpret_cast<const int*>(rec + (REC_COL + 0) * cap)].material;
+            C = mk(m[0], m[1], m[2]); refl = m[3]; transp = m[5]; kd = m[7]; ks = m[8]; nexp = m[9];
+        } else {
+            C = mk(rec[(REC_COL + 0) * cap], rec[(REC_COL + 1) * cap], rec[(REC_COL + 2) * cap]);
+            refl = rec[REC_REFL * cap]; transp = rec[REC_TRANSP * cap];
+            kd = rec[REC_KD * cap]; ks = rec[REC_KS * cap]; nexp = rec[REC_NEXP * cap];
+        }
         const V3<R> Vv = neg(D);
         V3<R> L = ld3(sc.ambient) * kd;
         for (int li = 0; li < sc.n_lights; li++) {
@@ -2997,6 +3018,9 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
         bool simple = n_csg == 0;                             // mode 1: spheres and planes only (face 0, no flip): the low word is the device index
         for (int d = 0; d < n; d++) simple = simple && (kind[d] == K_SPHERE || kind[d] == K_PLANE);
         sc.pickless = (sizeof(R) == 4 && n_all < (1 << 27) && env_size("GMLRT_PICKLESS", 1) != 0) ? (simple ? 1 : 2) : 0;
+        bool all_const = true;
+        for (const gmlrt_surface& sf : S.surfaces) all_const = all_const && sf.kind == GMLRT_SURFACE_CONST;
+        sc.rec_compact = (all_const && env_size("GMLRT_COMPACT_REC", 1) != 0) ? 1 : 0;
     }
     DevLight<R>* d_lights; DevSurface<R>* d_surfaces;
     if ((rc = to_device(w2o, &d_w2o, err)) || (rc = to_device(o2w, &d_o2w, err)) || (rc = to_device(fn, &d_fn, err)) ||

@@ -12,7 +12,7 @@ GMLRT_LIB=$PWD/go-raytracer_b200/libgmlrt_base.so run base
 run new
 GMLRT_LIB=$PWD/go-raytracer_b200/libgmlrt_base.so run base
 run new
-for c in csg256 mixed4096; do
+for c in csg256 proctex; do
   for lib in base new; do
   if [ $lib = base ]; then export GMLRT_LIB=$PWD/go-raytracer_b200/libgmlrt_base.so; else unset GMLRT_LIB; fi
   timeout 600 python bench.py --config $c --steps 4 --warmup 3 --no-cpu-baseline --no-parity 2>/dev/null | python -c "
