@@ -1187,6 +1187,27 @@ template <typename R> struct CameraSource {                  // level 0: camera 
     static constexpr bool is_shadow = false;
 };
 
+// Camera rays MADE by the cull kernel (GMLRT_FUSE_GEN, default): fetch() draws the sample's jitter, forms the ray (camera_ray64,
+// exactly what k_gen does), stores its record for the kernels that follow and hands it to the cull in registers - the 32-byte
+// record is written once and not read back by the next launch, and the two issue-bound kernels share one set of resident warps.
+template <typename R> struct GenCameraSource {
+    DevScene<R> sc; Level<R> lv; int W; CamSrc cam; int tile_w_log2, tile_h_log2, tiles_x;
+    __device__ __forceinline__ void fetch(int i, int& rid, Ray<R>& out, int& b, int& skip) const {
+        rid = i; skip = -1;
+        double o[3], d[3];
+        camera_ray64(sc, cam, i, o, d);
+        out.ox = (R)o[0]; out.oy = (R)o[1]; out.oz = (R)o[2]; out.dx = (R)d[0]; out.dy = (R)d[1]; out.dz = (R)d[2];
+        store_ray(lv.ray, i, out.ox, out.oy, out.oz, out.dx, out.dy, out.dz, 0, 0);
+        const int pix = i >> 2;
+        const int row = fast_div(pix, sc.w_mul, sc.w_shift);
+        b = (cam.map.actual(cam.y0 + row) >> tile_h_log2) * tiles_x + ((pix - row * W) >> tile_w_log2);
+    }
+    __device__ __forceinline__ void init(int rid) const { level_init_ray(lv, rid); }
+    __device__ __forceinline__ void ahead(int) const {}
+    __device__ __forceinline__ int cls(int b) const { return b; }
+    static constexpr bool is_shadow = false;
+};
+
 template <typename R> struct SpawnSource {                   // levels >= 1: reflection / refraction rays; the class key travels in the record
     Level<R> lv;
     __device__ __forceinline__ void fetch(int i, int& rid, Ray<R>& out, int& b, int& skip) const {
@@ -2026,6 +2047,17 @@ __device__ __forceinline__ bool light_at(const DevLight<R>& L, V3<R> P, V3<R>& l
 // ------------------------------------------------------------------ gen: camera rays (Render, raytracer.go:632-652)
 
 
+// the per-frame counters alone (when the camera rays are made by the cull kernel, GenCameraSource)
+static __global__ void __launch_bounds__(256) k_frame_init(Counters* ctr, int S, int* slots, int n_slots) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    for (int k = i; k < n_slots; k += gridDim.x * blockDim.x) slots[k] = 0;
+    if (i == 0) {
+        for (int l = 1; l <= GMLRT_MAX_DEPTH; l++) ctr->count[l] = 0;
+        for (int l = 0; l <= GMLRT_MAX_DEPTH; l++) ctr->hits[l] = 0;
+        ctr->count[0] = S;
+    }
+}
+
 template <typename R>
 __global__ void __launch_bounds__(256) k_gen(DevScene<R> sc, Level<R> lv, Counters* ctr, int y0, int rows, RowMap map, int* slots, int n_slots) {
     const int S = rows * sc.W * 4;
@@ -2571,6 +2603,7 @@ public:
         CU_TRY(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
         for (int k = 0; k < SHADOW_STREAMS; k++) CU_TRY(cudaStreamCreateWithFlags(&shadow_stream_[k], cudaStreamNonBlocking));
         overlap_shadows_ = env_size("GMLRT_OVERLAP_SHADOWS", 1) != 0;
+        fuse_gen_ = env_size("GMLRT_FUSE_GEN", 1) != 0;
         cudaDeviceProp prop;
         CU_TRY(cudaGetDeviceProperties(&prop, dev_));
         sms_ = prop.multiProcessorCount;
@@ -2592,7 +2625,7 @@ public:
         const int smem_max = 200 * 1024;
         auto allow = [&](auto kernel) -> int { CU_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max)); return GMLRT_OK; };
         int rc;
-        if ((rc = allow(k_cull<R, CULL_PIVOT, CameraSource<R>, true>)) || (rc = allow(k_cull<R, CULL_GENERAL, SpawnSource<R>, true>)) ||
+        if ((rc = allow(k_cull<R, CULL_PIVOT, GenCameraSource<R>, true>)) || (rc = allow(k_cull<R, CULL_PIVOT, CameraSource<R>, true>)) || (rc = allow(k_cull<R, CULL_GENERAL, SpawnSource<R>, true>)) ||
             (rc = allow(k_cull<R, CULL_PIVOT, ShadowSource<R>, true>)) || (rc = allow(k_cull<R, CULL_AXIS, ShadowSource<R>, true>)))
             return rc;
         return GMLRT_OK;
@@ -2740,6 +2773,7 @@ private:
     int resident_ = 1; size_t table_smem_ = 0;
     struct Launch { int grid = 148; size_t smem = 0; };
     size_t cfg_smem_ = ~(size_t)0;
+    Launch l_gen_; bool fuse_gen_ = true;                                                // camera rays made by the cull kernel (GMLRT_FUSE_GEN, read at context creation)
     Launch l_primary_, l_closest_, l_shadow_pivot_, l_shadow_axis_;                      // the four k_cull instantiations
     // ray classes (see "ray classes" above): one candidate list per bin, built once per upload
     static constexpr int TILE_W = 32, TILE_H = 8;                // camera-ray class = screen tile (a warp's 8 pixels x 4 samples share one)
@@ -3436,11 +3470,11 @@ int Renderer<R>::plan_tiles(const HostScene& S, std::string& err) {
     };
     int rc;
     if (resident_) {
-        if ((rc = cfg(k_cull<R, CULL_PIVOT, CameraSource<R>, true>, l_primary_)) || (rc = cfg(k_cull<R, CULL_GENERAL, SpawnSource<R>, true>, l_closest_)) ||
+        if ((rc = cfg(k_cull<R, CULL_PIVOT, GenCameraSource<R>, true>, l_gen_)) || (rc = cfg(k_cull<R, CULL_PIVOT, CameraSource<R>, true>, l_primary_)) || (rc = cfg(k_cull<R, CULL_GENERAL, SpawnSource<R>, true>, l_closest_)) ||
             (rc = cfg(k_cull<R, CULL_PIVOT, ShadowSource<R>, true>, l_shadow_pivot_)) || (rc = cfg(k_cull<R, CULL_AXIS, ShadowSource<R>, true>, l_shadow_axis_)))
             return rc;
     } else {
-        if ((rc = cfg(k_cull<R, CULL_PIVOT, CameraSource<R>, false>, l_primary_)) || (rc = cfg(k_cull<R, CULL_GENERAL, SpawnSource<R>, false>, l_closest_)) ||
+        if ((rc = cfg(k_cull<R, CULL_PIVOT, GenCameraSource<R>, false>, l_gen_)) || (rc = cfg(k_cull<R, CULL_PIVOT, CameraSource<R>, false>, l_primary_)) || (rc = cfg(k_cull<R, CULL_GENERAL, SpawnSource<R>, false>, l_closest_)) ||
             (rc = cfg(k_cull<R, CULL_PIVOT, ShadowSource<R>, false>, l_shadow_pivot_)) || (rc = cfg(k_cull<R, CULL_AXIS, ShadowSource<R>, false>, l_shadow_axis_)))
             return rc;
     }
@@ -3505,7 +3539,8 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
         cam.y0 = ty;
         const int S = rows * W * 4;
         MARK(KC_GEN);
-        k_gen<R><<<std::min((S + 255) / 256, sms_ * 32), 256, 0, stream_>>>(sc_, levels_[0], ctr_, ty, rows, map, slots_, n_slots_);
+        if (fuse_gen_) k_frame_init<<<std::max(1, std::min((n_slots_ + 255) / 256, 64)), 256, 0, stream_>>>(ctr_, S, slots_, n_slots_);
+        else k_gen<R><<<std::min((S + 255) / 256, sms_ * 32), 256, 0, stream_>>>(sc_, levels_[0], ctr_, ty, rows, map, slots_, n_slots_);
         totals_.launches++;
         totals_.rays_primary += (unsigned long long)S;
         for (int l = 0; l < depth_eff_; l++) {
@@ -3531,6 +3566,13 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
                 MARK(KC_CLOSEST_PRIMARY);
                 static_assert(TILE_W == 32 && TILE_H == 8, "CameraSource::bin shifts by log2 of the tile size");
                 CameraSource<R> cams{levels_[l], W, ty, map, 5, 3, (W + TILE_W - 1) / TILE_W, sc_.w_mul, sc_.w_shift};
+                if (fuse_gen_) {
+                    GenCameraSource<R> gens{sc_, levels_[l], W, cam, 5, 3, (W + TILE_W - 1) / TILE_W};
+                    if (resident_) k_cull<R, CULL_PIVOT, GenCameraSource<R>, true><<<l_gen_.grid, CULL_THREADS, l_gen_.smem, stream_>>>(
+                        gens, &ctr_->count[l], cull_eye_, frame_eye_, sc_.n_cull, lists_camera_, cq_l, ctr_);
+                    else k_cull<R, CULL_PIVOT, GenCameraSource<R>, false><<<l_gen_.grid, CULL_THREADS, 0, stream_>>>(
+                        gens, &ctr_->count[l], cull_eye_, frame_eye_, sc_.n_cull, lists_camera_, cq_l, ctr_);
+                } else
                 if (resident_) k_cull<R, CULL_PIVOT, CameraSource<R>, true><<<l_primary_.grid, CULL_THREADS, l_primary_.smem, stream_>>>(
                     cams, &ctr_->count[l], cull_eye_, frame_eye_, sc_.n_cull, lists_camera_, cq_l, ctr_);
                 else k_cull<R, CULL_PIVOT, CameraSource<R>, false><<<l_primary_.grid, CULL_THREADS, 0, stream_>>>(
