@@ -1160,8 +1160,8 @@ __device__ __forceinline__ int cand_count(const CandQueue& cq, const Counters* c
     return (int)min(*reinterpret_cast<const unsigned*>(cq.count), (unsigned)cq.cap);
 }
 
-template <typename R> __device__ __forceinline__ void level_init_ray(const Level<R>& lv, int i) {       // no hit yet (see fold_hit)
-    lv.hit[i] = -1;
+template <typename R> __device__ __forceinline__ void level_init_ray(const Level<R>& lv, int i, bool pickless = false) {       // no hit yet (see fold_hit)
+    if (!pickless) lv.hit[i] = -1;                           // (pickless: nobody reads the hit code word, the folded key is the hit)
     if constexpr (sizeof(R) == 4) reinterpret_cast<unsigned long long*>(lv.order)[i] = ~0ull;
     else {
         reinterpret_cast<unsigned long long*>(lv.t)[i] = ~0ull;
@@ -1173,7 +1173,7 @@ template <typename R> __device__ __forceinline__ void level_init_ray(const Level
 // issued before the current ray's list is walked (k_cull), so their DRAM latency hides behind it (ncu, r02q: a third of the
 // camera-ray launch's stall samples sat on the first use of the ray record).
 template <typename R> struct CameraSource {                  // level 0: camera rays in (pixel, sample) order over the virtual rows of a tile
-    Level<R> lv; int W, y0; RowMap map; int tile_w_log2, tile_h_log2, tiles_x; unsigned w_mul; int w_shift;
+    Level<R> lv; int W, y0; RowMap map; int tile_w_log2, tile_h_log2, tiles_x; unsigned w_mul; int w_shift; bool pickless;
     __device__ __forceinline__ void fetch(int i, int& rid, Ray<R>& out, int& b, int& skip) const {
         rid = i; skip = -1;
         load_ray(lv.ray, i, out);
@@ -1183,7 +1183,7 @@ template <typename R> struct CameraSource {                  // level 0: camera 
     }
     __device__ __forceinline__ void ahead(int i) const { prefetch_l2(lv.ray + (size_t)i * RAY_WORDS); }
     __device__ __forceinline__ int cls(int b) const { return b; }
-    __device__ __forceinline__ void init(int rid) const { level_init_ray(lv, rid); }
+    __device__ __forceinline__ void init(int rid) const { level_init_ray(lv, rid, pickless); }
     static constexpr bool is_shadow = false;
 };
 
@@ -1191,7 +1191,7 @@ template <typename R> struct CameraSource {                  // level 0: camera 
 // exactly what k_gen does), stores its record for the kernels that follow and hands it to the cull in registers - the 32-byte
 // record is written once and not read back by the next launch, and the two issue-bound kernels share one set of resident warps.
 template <typename R> struct GenCameraSource {
-    DevScene<R> sc; Level<R> lv; int W; CamSrc cam; int tile_w_log2, tile_h_log2, tiles_x;
+    DevScene<R> sc; Level<R> lv; int W; CamSrc cam; int tile_w_log2, tile_h_log2, tiles_x; bool pickless;
     __device__ __forceinline__ void fetch(int i, int& rid, Ray<R>& out, int& b, int& skip) const {
         rid = i; skip = -1;
         double o[3], d[3];
@@ -1202,14 +1202,14 @@ template <typename R> struct GenCameraSource {
         const int row = fast_div(pix, sc.w_mul, sc.w_shift);
         b = (cam.map.actual(cam.y0 + row) >> tile_h_log2) * tiles_x + ((pix - row * W) >> tile_w_log2);
     }
-    __device__ __forceinline__ void init(int rid) const { level_init_ray(lv, rid); }
+    __device__ __forceinline__ void init(int rid) const { level_init_ray(lv, rid, pickless); }
     __device__ __forceinline__ void ahead(int) const {}
     __device__ __forceinline__ int cls(int b) const { return b; }
     static constexpr bool is_shadow = false;
 };
 
 template <typename R> struct SpawnSource {                   // levels >= 1: reflection / refraction rays; the class key travels in the record
-    Level<R> lv;
+    Level<R> lv; bool pickless;
     __device__ __forceinline__ void fetch(int i, int& rid, Ray<R>& out, int& b, int& skip) const {
         rid = i; skip = -1;
         load_ray(lv.ray, i, out);
@@ -1217,7 +1217,7 @@ template <typename R> struct SpawnSource {                   // levels >= 1: ref
     }
     __device__ __forceinline__ void ahead(int i) const { prefetch_l2(lv.ray + (size_t)i * RAY_WORDS); }
     __device__ __forceinline__ int cls(int b) const { return b; }
-    __device__ __forceinline__ void init(int rid) const { level_init_ray(lv, rid); }
+    __device__ __forceinline__ void init(int rid) const { level_init_ray(lv, rid, pickless); }
     static constexpr bool is_shadow = false;
 };
 
@@ -3565,9 +3565,9 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             if (l == 0) {                                  // camera rays: PIVOT family through the eye, robust re-tests in f32
                 MARK(KC_CLOSEST_PRIMARY);
                 static_assert(TILE_W == 32 && TILE_H == 8, "CameraSource::bin shifts by log2 of the tile size");
-                CameraSource<R> cams{levels_[l], W, ty, map, 5, 3, (W + TILE_W - 1) / TILE_W, sc_.w_mul, sc_.w_shift};
+                CameraSource<R> cams{levels_[l], W, ty, map, 5, 3, (W + TILE_W - 1) / TILE_W, sc_.w_mul, sc_.w_shift, sc_.pickless != 0};
                 if (fuse_gen_) {
-                    GenCameraSource<R> gens{sc_, levels_[l], W, cam, 5, 3, (W + TILE_W - 1) / TILE_W};
+                    GenCameraSource<R> gens{sc_, levels_[l], W, cam, 5, 3, (W + TILE_W - 1) / TILE_W, sc_.pickless != 0};
                     if (resident_) k_cull<R, CULL_PIVOT, GenCameraSource<R>, true><<<l_gen_.grid, CULL_THREADS, l_gen_.smem, stream_>>>(
                         gens, &ctr_->count[l], cull_eye_, frame_eye_, sc_.n_cull, lists_camera_, cq_l, ctr_);
                     else k_cull<R, CULL_PIVOT, GenCameraSource<R>, false><<<l_gen_.grid, CULL_THREADS, 0, stream_>>>(
@@ -3594,7 +3594,7 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
                 }
             } else {
                 MARK(KC_CLOSEST);
-                SpawnSource<R> spws{levels_[l]};
+                SpawnSource<R> spws{levels_[l], sc_.pickless != 0};
                 if (resident_) k_cull<R, CULL_GENERAL, SpawnSource<R>, true><<<l_closest_.grid, CULL_THREADS, l_closest_.smem, stream_>>>(
                     spws, &ctr_->count[l], cull_general_, frame_general_, sc_.n_cull, lists_spawn_, cq_l, ctr_);
                 else k_cull<R, CULL_GENERAL, SpawnSource<R>, false><<<l_closest_.grid, CULL_THREADS, 0, stream_>>>(
