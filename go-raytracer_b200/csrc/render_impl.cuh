@@ -1174,8 +1174,9 @@ template <typename R> __device__ __forceinline__ void level_init_ray(const Level
 // camera-ray launch's stall samples sat on the first use of the ray record).
 template <typename R> struct CameraSource {                  // level 0: camera rays in (pixel, sample) order over the virtual rows of a tile
     Level<R> lv; int W, y0; RowMap map; int tile_w_log2, tile_h_log2, tiles_x; unsigned w_mul; int w_shift; bool pickless;
-    __device__ __forceinline__ void fetch(int i, int& rid, Ray<R>& out, int& b, int& skip) const {
-        rid = i; skip = -1;
+    __device__ __forceinline__ int slot(int i) const { return i; }
+    __device__ __forceinline__ void fetch(int i, Ray<R>& out, int& b, int& skip) const {
+        skip = -1;
         load_ray(lv.ray, i, out);
         const int pix = i >> 2;
         const int row = fast_div(pix, w_mul, w_shift);
@@ -1192,8 +1193,9 @@ template <typename R> struct CameraSource {                  // level 0: camera 
 // record is written once and not read back by the next launch, and the two issue-bound kernels share one set of resident warps.
 template <typename R> struct GenCameraSource {
     DevScene<R> sc; Level<R> lv; int W; CamSrc cam; int tile_w_log2, tile_h_log2, tiles_x; bool pickless;
-    __device__ __forceinline__ void fetch(int i, int& rid, Ray<R>& out, int& b, int& skip) const {
-        rid = i; skip = -1;
+    __device__ __forceinline__ int slot(int i) const { return i; }
+    __device__ __forceinline__ void fetch(int i, Ray<R>& out, int& b, int& skip) const {
+        skip = -1;
         double o[3], d[3];
         camera_ray64(sc, cam, i, o, d);
         out.ox = (R)o[0]; out.oy = (R)o[1]; out.oz = (R)o[2]; out.dx = (R)d[0]; out.dy = (R)d[1]; out.dz = (R)d[2];
@@ -1209,13 +1211,14 @@ template <typename R> struct GenCameraSource {
 };
 
 template <typename R> struct SpawnSource {                   // levels >= 1: reflection / refraction rays; the class key travels in the record
-    Level<R> lv; bool pickless;
-    __device__ __forceinline__ void fetch(int i, int& rid, Ray<R>& out, int& b, int& skip) const {
-        rid = i; skip = -1;
-        load_ray(lv.ray, i, out);
-        b = ray_key(lv.ray, i);
+    Level<R> lv; bool pickless; const int* perm;             // perm: the rays in class order (the key sort moved indices, not records); null: the level is stored sorted
+    __device__ __forceinline__ int slot(int i) const { return perm ? perm[i] : i; }
+    __device__ __forceinline__ void fetch(int rid, Ray<R>& out, int& b, int& skip) const {
+        skip = -1;
+        load_ray(lv.ray, rid, out);
+        b = ray_key(lv.ray, rid);
     }
-    __device__ __forceinline__ void ahead(int i) const { prefetch_l2(lv.ray + (size_t)i * RAY_WORDS); }
+    __device__ __forceinline__ void ahead(int i) const { if (!perm) prefetch_l2(lv.ray + (size_t)i * RAY_WORDS); }
     __device__ __forceinline__ int cls(int b) const { return b; }
     __device__ __forceinline__ void init(int rid) const { level_init_ray(lv, rid, pickless); }
     static constexpr bool is_shadow = false;
@@ -1224,8 +1227,8 @@ template <typename R> struct SpawnSource {                   // levels >= 1: ref
 template <typename R> struct ShadowSource {                  // shadow rays of one light: slots [base, base + n)
     ShadowQueue<R> sq; int base; const int* perm;            // perm: by-region order of the slots (null: queue order)
     int shift, nb;                                           // class = sort_bin(region of the shaded point)
-    __device__ __forceinline__ void fetch(int i, int& rid, Ray<R>& out, int& b, int& skip) const {
-        rid = perm ? perm[base + i] : i;
+    __device__ __forceinline__ int slot(int i) const { return perm ? perm[base + i] : i; }
+    __device__ __forceinline__ void fetch(int rid, Ray<R>& out, int& b, int& skip) const {
         load_ray(sq.q + (size_t)(base + rid) * 8, 0, out);
         b = sq.key[base + rid];                              // raw: sort_bin() at the use (cls), or the fetch would wait for the load it was issued early for
         skip = sq.skip[base + rid];                          // the shaded object: inShadow passes over it (:418), and its bound holds the ray's origin - a sure survivor
@@ -1292,7 +1295,10 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
     const Ray<R> idle = {R(0), R(0), R(0), R(0), R(0), R(1)};
     Ray<R> w_nx = idle;
     int rid_nx = 0, b_nx = 0, skip_nx = -1;
-    if ((int)blockIdx.x * CULL_THREADS + tid < n) src.fetch((int)blockIdx.x * CULL_THREADS + tid, rid_nx, w_nx, b_nx, skip_nx);
+    const int step = (int)gridDim.x * CULL_THREADS;
+    const int i_first = (int)blockIdx.x * CULL_THREADS + tid;
+    if (i_first < n) { rid_nx = src.slot(i_first); src.fetch(rid_nx, w_nx, b_nx, skip_nx); }
+    int rid_nx2 = (long long)i_first + step < n ? src.slot(i_first + step) : 0;      // where a sort left only a permutation, the slot of a ray is a load of its own: one more iteration ahead
     for (int blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
         const int i = blk * CULL_THREADS + tid;
         const bool active = i < n;
@@ -1306,11 +1312,12 @@ k_cull(const __grid_constant__ Source src, const int* n_ptr, const R* table, con
             first = rec.x; len = rec.y;
         }
         {   // the next iteration's ray: in flight while this one's list is walked
-            const int i2 = i + (int)gridDim.x * CULL_THREADS;
+            const int i2 = i + step;
             w_nx = idle; rid_nx = 0; b_nx = 0; skip_nx = -1;
-            if (blk + (int)gridDim.x < nblocks && i2 < n) src.fetch(i2, rid_nx, w_nx, b_nx, skip_nx);
-            const int i3 = i2 + (int)gridDim.x * CULL_THREADS;
-            if (i3 < n) src.ahead(i3);                         // ... and the one after it on its way to L2
+            if (blk + (int)gridDim.x < nblocks && i2 < n) { rid_nx = rid_nx2; src.fetch(rid_nx, w_nx, b_nx, skip_nx); }
+            const long long i3 = (long long)i2 + step;
+            rid_nx2 = 0;
+            if (i3 < n) { rid_nx2 = src.slot((int)i3); src.ahead((int)i3); }      // ... and the one after it: its slot, and (stored in order) its record on the way to L2
         }
         CullRay<R, FAMILY> cr;
         cr.init(w, frame);
@@ -1779,7 +1786,7 @@ static __global__ void __launch_bounds__(256) k_keysort_hist(const int* keys, co
 }
 
 template <typename R>
-__global__ void __launch_bounds__(256) k_keysort_scatter(const int* keys, const int* n_ptr, int nb, int* cursor, const R* stage, R* out) {
+__global__ void __launch_bounds__(256) k_keysort_scatter(const int* keys, const int* n_ptr, int nb, int* cursor, const R* stage, R* out, int* perm_out) {
     const int n = *n_ptr;
     const int rounds = (n + gridDim.x * blockDim.x - 1) / (gridDim.x * blockDim.x);
     for (int r = 0; r < rounds; r++) {
@@ -1791,7 +1798,8 @@ __global__ void __launch_bounds__(256) k_keysort_scatter(const int* keys, const 
         int at = 0;
         if (valid && rank == 0) at = atomicAdd(&cursor[key], __popc(peers));
         at = __shfl_sync(0xffffffffu, at, leader);
-        if (valid) {                                       // move the whole record: the level is STORED in sorted order
+        if (valid && perm_out) perm_out[at + rank] = i;    // permutation only: the records stay where k_shade wrote them, the cull kernel gathers them (one 32-byte sector each)
+        else if (valid) {                                  // move the whole record: the level is STORED in sorted order
             const uint4* src = reinterpret_cast<const uint4*>(stage + (size_t)i * RAY_WORDS);
             uint4* dst = reinterpret_cast<uint4*>(out + (size_t)(at + rank) * RAY_WORDS);
 #pragma unroll
@@ -2795,6 +2803,7 @@ private:
     int* sort_hist_ = nullptr; int* sort_cursor_ = nullptr; int sort_nb_ = 2, sort_shift_ = 0, n_regions_ = 1; bool sort_clear_ = true;
     int* key_hist_ = nullptr; int* key_cursor_ = nullptr; int key_nb_ = 6;      // spawned rays by (origin leaf, direction cell); cleared with sort_hist_
     bool sort_spawned_ = true;
+    bool sort_perm_ = true;                                      // GMLRT_SORT_PERM: the key sort of spawned rays leaves a permutation (in spawn_stage_), the records stay in queue order
     R* spawn_stage_ = nullptr;
     // cull tables (device) and what they were built for: any ray, camera rays, one per light
     std::vector<double> bound_;                                  // host: [n][4] bounding spheres (centre, radius) of the objects
@@ -3080,6 +3089,12 @@ int Renderer<R>::upload(const HostScene& S, std::string& err) {
     while ((size_t)(((n_regions - 1) >> sc.key_shift) + 1) * 6 * sc.key_k * sc.key_k > key_bins_limit) sc.key_shift++;
     key_nb_ = (((n_regions - 1) >> sc.key_shift) + 1) * 6 * sc.key_k * sc.key_k;
     sort_spawned_ = env_size("GMLRT_SORT_SPAWNED", 1) != 0;
+    {   // Permutation only (the records stay in queue order, the cull kernel gathers them one sector each) saves the staging
+        // buffer's round trip: 4K spheres1024 4.94 -> 4.72 ms.  In a deep, large scene the candidates of a warp then point at
+        // records all over the level and the exact kernels lose more than the sort gains (8K mixed4096, depth 5: 102.3 -> 105.3 ms).
+        const size_t mode = env_size("GMLRT_SORT_PERM", 2);
+        sort_perm_ = mode == 2 ? sc.n_leaves < 2048 : mode != 0;
+    }
     for (int k = 0; k < 3; k++) { sc.ambient[k] = (R)S.h.ambient[k]; sc.bg0[k] = (R)S.h.bg_start[k]; sc.bg1[k] = (R)S.h.bg_end[k]; }
     sc_ = sc;
     // cull tables: any ray; camera rays (their lines pass through the eye, raytracer.go:605-609); one per light
@@ -3559,7 +3574,8 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
                 MARK(KC_SORT);
                 k_keysort_hist<<<sms_ * 8, 256, 0, stream_>>>(levels_[l].hit, &ctr_->count[l], key_nb_, key_hist_);
                 launch_scan(key_nb_, key_hist_, key_cursor_, 1, stream_);
-                k_keysort_scatter<R><<<sms_ * 8, 256, 0, stream_>>>(levels_[l].hit, &ctr_->count[l], key_nb_, key_cursor_, spawn_stage_, levels_[l].ray);
+                k_keysort_scatter<R><<<sms_ * 8, 256, 0, stream_>>>(levels_[l].hit, &ctr_->count[l], key_nb_, key_cursor_, spawn_stage_, levels_[l].ray,
+                                                                    sort_perm_ ? reinterpret_cast<int*>(spawn_stage_) : nullptr);
                 totals_.launches += 3;
             }
             if (l == 0) {                                  // camera rays: PIVOT family through the eye, robust re-tests in f32
@@ -3594,7 +3610,7 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
                 }
             } else {
                 MARK(KC_CLOSEST);
-                SpawnSource<R> spws{levels_[l], sc_.pickless != 0};
+                SpawnSource<R> spws{levels_[l], sc_.pickless != 0, (sort_spawned_ && sort_perm_) ? reinterpret_cast<const int*>(spawn_stage_) : nullptr};
                 if (resident_) k_cull<R, CULL_GENERAL, SpawnSource<R>, true><<<l_closest_.grid, CULL_THREADS, l_closest_.smem, stream_>>>(
                     spws, &ctr_->count[l], cull_general_, frame_general_, sc_.n_cull, lists_spawn_, cq_l, ctr_);
                 else k_cull<R, CULL_GENERAL, SpawnSource<R>, false><<<l_closest_.grid, CULL_THREADS, 0, stream_>>>(
@@ -3631,7 +3647,7 @@ int Renderer<R>::trace_rows(int y0, int y1, const RowMap& map, bool counting, st
             auto shade = sc_.pickless == 1 ? k_shade<R, sizeof(R) == 4 ? 1 : 0> : sc_.pickless ? k_shade<R, sizeof(R) == 4 ? 2 : 0> : k_shade<R, 0>;
             shade<<<std::min(cap_blocks, wide), SHADE_THREADS, 0, stream_>>>(
                 sc_, levels_[l], spawn ? levels_[l + 1] : levels_[l], sq_l, occl_[l], ctr_, l, spawn ? 1 : 0,
-                spawn ? (sort_spawned_ ? spawn_stage_ : levels_[l + 1].ray) : nullptr, (primary_points_ && l == 0) ? 1 : 0);
+                spawn ? ((sort_spawned_ && !sort_perm_) ? spawn_stage_ : levels_[l + 1].ray) : nullptr, (primary_points_ && l == 0) ? 1 : 0);
             totals_.launches += 2;
             // shadow queries of this level: on the shadow stream, overlapping the next level's closest-hit pipeline
             if (two_streams) {
