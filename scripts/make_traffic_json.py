@@ -7,7 +7,7 @@ hdr, units, data = rows[0], rows[1], rows[2:]
 c = {n: hdr.index(n) for n in ("Kernel Name", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum")}
 scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}
 tscale = {"ms": 1e3, "us": 1.0, "ns": 1e-3, "s": 1e6}
-classes = {"shade": r"k_shade<", "resolve": r"k_resolve<|k_pixels<", "cull_secondary": r"k_cull<float, 0, SpawnSource", "cull_primary": r"k_cull<float, 1, CameraSource",
+classes = {"shade": r"k_shade<", "resolve": r"k_resolve<|k_pixels<", "cull_secondary": r"k_cull<float, 0, SpawnSource", "cull_primary": r"k_cull<float, 1, (Gen)?CameraSource",
            "gen": r"k_gen<", "primary_points": r"k_primary_points<"}
 out = {"source": note, "note": "per kernel class: mean of dram__bytes_read.sum + dram__bytes_write.sum over the captured launches of that kernel "
        "(one per recursion level of a frame); "
