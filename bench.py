@@ -495,6 +495,7 @@ def main():
     key = 8                                                                # fold key (f32) / hit code + T (f64): 8 bytes per ray either way
     from go_raytracer_b200 import lowering as _lowering
     compact = all(sf["kind"] == 0 for sf in _lowering.describe(blob)["surfaces"])   # constant materials only: the shading record holds the surface index
+    sort_perm = int(os.environ.get("GMLRT_SORT_PERM", "2")) == 1 or (int(os.environ.get("GMLRT_SORT_PERM", "2")) == 2 and cst.n_leaves < 2048)   # the library's own rule
     rec_w, rec_r = (9, 8) if compact else (16, 15)                         # words of the shading record k_shade writes / k_resolve reads per hit
     model_bytes = {
         0: P * 8 * wb,                                                     # gen: one ray record per sample
@@ -502,7 +503,7 @@ def main():
         4: NH * (4 + key + 8 * wb + rec_w * wb) + NH0 * 3 * wb * (1 if args.precision == "f32" else 0) + S * (8 * wb + 13) + CH * (8 * wb + 4),   # shade: per hit the index, key, ray in and the record out; shadow records (+ skip, key, target, flag) and child records (+ sort key) out
         5: NH * (4 + 8 * wb + rec_r * wb + nl + 3 * wb) + CH * 3 * wb + P * key + (P - NH0) * 8 * wb + NH0 * 3 * wb + P,   # resolve: per hit the index, ray, record, flags in, colour out; children's colours in; pixel pass: keys, the records of the misses, sample colours in, RGBA8 out
         7: Xc * ((8 + 8 * wb + 8) if args.precision == "f32" else ((8 + 8 * wb + 4 + wb) + (8 + wb + 8 + 4 + wb))) + Xs * (8 + 8 * wb + 8),   # exact: candidate + ray record + the fold's 8 bytes (f32, pickless: the folded key is the result); f64: + per-candidate result and the order / pick passes; shadow: candidate, record, skip + first
-        8: CH * (8 + 16 * wb) + C * key + NH * 4 + MISS_DEEP * (8 * wb + 3 * wb),                  # sort + compaction: key sort moves the 8-word records; hit list reads every key, writes the hits, finishes the deep misses
+        8: CH * (12 if sort_perm else 8 + 16 * wb) + C * key + NH * 4 + MISS_DEEP * (8 * wb + 3 * wb),   # sort + compaction: the key sort leaves a permutation (small scenes: key read twice, index written) or moves the 8-word records; hit list reads every key, writes the hits, finishes the deep misses
     }
     # the camera rays are made by the camera-ray cull kernel (GenCameraSource): class 0 is then only the counters' reset and the
     # records' bytes belong to class 1
