@@ -158,6 +158,44 @@ def test_upload_cache_reuses_and_invalidates(ctx64):
         c.close()
 
 
+@pytest.mark.parametrize("switch", ["GMLRT_SORT_PERM=0", "GMLRT_SORT_PERM=1", "GMLRT_FUSE_GEN=0", "GMLRT_COMPACT_REC=0", "GMLRT_SORT_SHADOWS=1",
+                                    "GMLRT_OVERLAP_SHADOWS=0", "GMLRT_SORT_SPAWNED=0", "GMLRT_KEY_K=3", "GMLRT_KEY_BINS=4096", "GMLRT_PICKLESS=0"])
+def test_pipeline_switches_do_not_change_the_result(switch):
+    """Every tuning switch of DESIGN.md 5a selects another route through the same arithmetic: parity mode stays byte-identical
+    to the oracle (raster, primary ids, ray counts) and throughput mode renders the very same float32 raster, whichever way the
+    rays are sorted, generated, recorded or folded."""
+    name, value = switch.split("=")
+    blob = scenes.to_blob(scenes.mixed(160, 100, grid=(6, 4, 3), depth=4))
+    want, ost, oids = oracle.render(blob, threads=THREADS, want_ids=True)
+    ref32 = cuda.Context((0,), cuda.PRECISION_F32)
+    try:
+        base32, _ = ref32.render(blob)
+    finally:
+        ref32.close()
+    os.environ[name] = value
+    try:
+        for prec in (cuda.PRECISION_F64_PARITY, cuda.PRECISION_F32):
+            c = cuda.Context((0,), prec)                         # (some switches are read when the context is created)
+            try:
+                c.set_counting(True)
+                got, st = c.render(blob)
+                if prec == cuda.PRECISION_F64_PARITY:
+                    assert np.array_equal(got, want), switch
+                    assert np.array_equal(c.primary_hits(), oids), switch
+                    assert st.rays_total == ost.rays_total and st.shadow_occluded == ost.shadow_occluded, switch
+                else:
+                    c.set_counting(False)
+                    got, _ = c.render(blob)
+                    if name == "GMLRT_PICKLESS":                 # the two folds break a tie at bit-identical float32 T differently (DESIGN.md 2)
+                        assert (got != base32).any(axis=2).mean() <= 1e-4, switch
+                    else:
+                        assert np.array_equal(got, base32), switch
+            finally:
+                c.close()
+    finally:
+        del os.environ[name]
+
+
 def test_tiling_does_not_change_the_raster(ctx64):
     blob = scenes.to_blob(scenes.mixed(256, 150, grid=(4, 4, 4), depth=3))
     whole, _ = ctx64.render(blob)
