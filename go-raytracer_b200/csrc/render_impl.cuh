@@ -1129,6 +1129,7 @@ __device__ __forceinline__ void cull_list_window(uint32_t tab, const unsigned ch
     if (n4 > 8) hi = half(8, n4);
 }
 
+__device__ __forceinline__ int warp_max(int v) { return __reduce_max_sync(0xffffffffu, v); }      // one REDUX instead of five shuffles
 template <typename R>
 __device__ __forceinline__ R warp_max(R v) { for (int o = 16; o > 0; o >>= 1) { const R u = __shfl_xor_sync(0xffffffffu, v, o); v = u > v ? u : v; } return v; }
 __device__ __forceinline__ unsigned long long warp_sum_u64(unsigned long long v) { for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o); return v; }
