@@ -82,20 +82,18 @@ def test_synthetic_scenes_parity_and_tolerance(ctx64, ctx32, gen):
             "proctex": scenes.proctex(320, 180, n_spheres=16),
             "csg": scenes.csg(320, 180, groups=(4, 4))}[gen]
     blob = scenes.to_blob(text)
-    oimg, ost, oids = oracle.render(blob, threads=THREADS, want_ids=True)
+    oimg, ost, oids, chaos = oracle.render(blob, threads=THREADS, want_ids=True, want_chaos=True)
     img, st = ctx64.render(blob)
     assert np.array_equal(img, oimg)
     assert np.array_equal(ctx64.primary_hits(), oids)
     assert st.rays_total == ost.rays_total and st.rays_hit == ost.rays_hit and st.shadow_occluded == ost.shadow_occluded
     img32, st32 = ctx32.render(blob)
-    # 320x180 is far denser in silhouettes and texture discontinuities (frac / floor steps amplify a
-    # float32 ulp into a full colour step) than the 4K frames the north_star quotes 99.9% on
-    bar = {"spheres": 0.999, "mixed": 0.998, "proctex": 0.998, "csg": 0.997}[gen]
-    assert agreement(img32, oimg, tol=1) >= bar
-    flips = int(((ctx32.primary_hits() < 0) != (oids < 0)).sum())
-    # zero primary hit/miss flips; scenes with cubes inherit the reference's own float64 face
-    # speckle (a face is randomly missed), which float32 cannot and should not copy
-    assert flips <= (0 if gen not in ("mixed",) else 3), f"{flips} primary hit/miss flips in float32"
+    # the north_star's bar as it stands - within 1/255 on >= 99.9% of the pixels, zero primary hit/miss flips - also on these
+    # 320x180 frames (measured: 1.0 / 0.99946 / 1.0 / 1.0).  The one flip `mixed` shows sits in a pixel of the oracle's chaos map: a
+    # cube face the reference itself rejects by rounding alone, which float32 cannot and should not copy.
+    assert agreement(img32, oimg, tol=1) >= 0.999
+    flips = ((ctx32.primary_hits() < 0) != (oids < 0)) & ~chaos[..., None]
+    assert int(flips.sum()) == 0, f"{int(flips.sum())} primary hit/miss flips in float32 outside the reference's own chaos"
     assert st.flops_credited == ost.flops_credited and st.leaf_tests == ost.leaf_tests
 
 
@@ -372,10 +370,10 @@ def test_icfp_fixture_scenes_end_to_end(ctx64, ctx32, name):
         stable = ~chaos
         assert stable.mean() >= (0.5 if name == "dice" else 0.8), (name, file, float(stable.mean()))
         within = float((d[stable] <= 1).mean())
-        # these are 300 x 200 frames of a few large objects: an edge pixel in a thousand may differ by one sample
-        assert within >= 0.998, (name, file, within)
+        # the north_star's bar as it stands (measured: >= 0.99993 on every scene, no flip outside the chaos map)
+        assert within >= 0.999, (name, file, within)
         flips = int((((ids32 < 0) != (oids < 0)) & stable[..., None]).sum())
-        assert flips <= 2, (name, file, flips)
+        assert flips == 0, (name, file, flips)
         # the reference's own acceptance (raytracer_test.go:37-52), with the pixels the reference itself leaves to rounding taken from it
         assert ctx32.ssim(np.where(stable[..., None], got32, want), want) >= 0.99, (name, file)
 
