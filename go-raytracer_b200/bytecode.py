@@ -7,9 +7,15 @@ clone the environment map twice, walk the token list, pop a Material or
 host: the compiler runs the same token list over an *abstract* stack whose entries
 are either compile-time constants (numbers, points, arrays, closures from the
 captured environment) or virtual registers that will hold run-time values.
-``apply`` and ``if`` need their closure operands at compile time (true of every
-scene in the reference's testdata); an ``if`` on a run-time condition becomes a
-forward jump with both arms merged into common registers.  What is left for the
+An ``if`` on a run-time condition becomes a forward jump with both arms merged into
+common registers.  A closure that is only known at run time - the two arms of such an
+``if`` leave different closures, or ``get`` picks one out of an array of closures with a
+run-time index - is a *choice*: a selector register plus the candidate closures, and
+``apply`` / ``if`` on it unfold into a chain of branches, one inlined body per candidate
+(the reference interprets whichever closure it finds on the stack,
+internal/gml/evaluator.go:604-610, :1005-1019).  Recursion is unrolled; a chain of
+applications deeper than MAX_INLINE_DEPTH becomes a run-time fault (the device has no
+call stack: bounded depth -> GMLRT_E_SURFACE).  What is left for the
 device is typed three-address code with no closures, no environment and no stack.
 
 Constant folding uses the evaluator's own builtin implementations, so a folded
@@ -23,6 +29,9 @@ from .prim import Vec3
 
 MAX_REGS = 128
 MAX_INLINE_DEPTH = 64
+MAX_CODE_WORDS = 1 << 16
+MERGE_DEBT = 3                    # ... and what every open branch is assumed to need for its merge
+RECURSION_RESERVE = 24            # registers an unrolled recursion leaves to the rest of the surface function
 
 OP = dict(RET=0, LDK=1, LDI=2, MOV=3, ADDF=4, SUBF=5, MULF=6, DIVF=7, NEGF=8, ADDI=9, SUBI=10, MULI=11, DIVI=12,
           MODI=13, NEGI=14, EQF=15, LESSF=16, EQI=17, LESSI=18, SIN=19, COS=20, SQRT=21, CLAMPF=22, FLOOR=23, FRAC=24,
@@ -34,14 +43,19 @@ class SurfaceCompileError(Exception):
     """The closure uses something the static compiler cannot resolve."""
 
 
+class _OutOfRegisters(SurfaceCompileError):
+    pass
+
+
 class A:
     """Abstract value.  kind: i f b (scalars) | p (point: comps) | mat (10 comps) |
     arr (items: list[A]) | clos (body, env) | other (opaque compile-time value)."""
-    __slots__ = ("kind", "const", "reg", "comps", "items", "body", "env", "pooled")
+    __slots__ = ("kind", "const", "reg", "comps", "items", "body", "env", "pooled", "exhaustive")
 
     def __init__(self, kind, const=None, reg=None, comps=None, items=None, body=None, env=None):
         self.kind, self.const, self.reg, self.comps, self.items = kind, const, reg, comps, items
         self.body, self.env, self.pooled = body, env, None
+        self.exhaustive = True       # choice: the selector is known to be one of 0 .. len(items) - 1
 
     @property
     def is_const(self):
@@ -51,6 +65,8 @@ class A:
             return all(c.is_const for c in self.comps)
         if self.kind == "arr":
             return self.reg is None
+        if self.kind == "choice":
+            return False
         return True
 
 
@@ -129,18 +145,26 @@ class _Compiler:
         self.code = []
         self.nreg = 3
         self.depth = 0
+        self.emitted = 0
+        self.active = []             # bodies of the closures being inlined, outermost first
+        self.branch_depth = 0        # run-time branches whose arms are being compiled
+        self.reg_limit = MAX_REGS    # lowered while a recursion is being unrolled, so that what follows it still finds registers
         self._folder = ev.EvalState()
 
     # ---- code emission
     def emit(self, op, d=0, a=0, b=0, *imm):
+        self.emitted += 1 + len(imm)
+        if self.emitted > MAX_CODE_WORDS:
+            raise SurfaceCompileError(f"surface function unrolls to more than {MAX_CODE_WORDS} words of code")
         self.code.append(OP[op] | (d << 8) | (a << 16) | (b << 24))
         self.code.extend(x & 0xFFFFFFFF for x in imm)
 
     def new_reg(self, n=1):
         r = self.nreg
         self.nreg += n
-        if self.nreg > MAX_REGS:
-            raise SurfaceCompileError(f"surface function needs more than {MAX_REGS} registers")
+        # while a recursion is being unrolled every branch still open will want registers to merge its arms when it closes
+        if self.nreg + (MERGE_DEBT * self.branch_depth if self.reg_limit < MAX_REGS else 0) > self.reg_limit:
+            raise _OutOfRegisters(f"surface function needs more than {MAX_REGS} registers")
         return r
 
     def reg_of(self, a):
@@ -227,7 +251,10 @@ class _Compiler:
     def run(self, code, env, stack):
         self.depth += 1
         if self.depth > MAX_INLINE_DEPTH:
-            raise SurfaceCompileError("closure recursion is too deep to unroll at compile time")
+            # the device has no call stack: applications nested deeper than this fault at run time (GMLRT_E_SURFACE)
+            self.depth -= 1
+            self.emit("ERR")
+            raise _DeadCode()
         for tok in code:
             t = type(tok)
             if t is IntLiteral:
@@ -323,8 +350,7 @@ class _Compiler:
         elif name == "get":
             self.get(stack)
         elif name == "apply":
-            c = pop(stack, "clos")
-            self.run(c.body, c.env.fork(), stack)
+            self.apply_value(self.pop_callable(stack), stack)
         elif name == "if":
             self.if_(stack)
         else:
@@ -338,6 +364,16 @@ class _Compiler:
                 self.emit("ERR")     # the reference fails here at render time (evaluator.go:990-995)
                 raise _DeadCode()
             stack.append(a.items[i.const])
+            return
+        if a.reg is None and a.items and all(x.kind in ("clos", "choice") for x in a.items):
+            # a closure picked at run time: bounds-checked here, like the reference's get (evaluator.go:989-995), and
+            # carried as a choice until something applies it
+            ir = self.reg_of(i)
+            below = self.scalar_op("LESSI", "b", A("i", reg=ir), A("i", const=len(a.items)))
+            self.branch(below.reg, lambda st: None, self.fault, stack)
+            negative = self.scalar_op("LESSI", "b", A("i", reg=ir), A("i", const=0))
+            self.branch(negative.reg, self.fault, lambda st: None, stack)
+            stack.append(A("choice", reg=ir, items=list(a.items)))
             return
         ar, et = self.arr_regs(a)
         ir = self.reg_of(i)
@@ -360,23 +396,73 @@ class _Compiler:
             out.const = et[1]   # element type of the fetched inner array
             stack.append(out)
 
-    def if_(self, stack):
-        f, t, c = self.pop(stack, "clos"), self.pop(stack, "clos"), self.pop(stack, "b")
-        if c.is_const:
-            chosen = t if c.const else f
-            self.run(chosen.body, chosen.env.fork(), stack)
-            return
-        cr = self.reg_of(c)
-        outer, depth0 = self.code, self.depth
-        arms = []
-        for clos in (t, f):
-            self.code = []
-            st, dead = list(stack), False
+    def pop_callable(self, stack):
+        a = self.pop(stack)
+        if a.kind not in ("clos", "choice"):
+            raise SurfaceCompileError(f"type mismatch: expected a closure, got {a.kind}")
+        return a
+
+    def fault(self, stack):
+        self.emit("ERR")
+        raise _DeadCode()
+
+    def apply_value(self, v, stack):
+        """Inline the application of a closure value: a closure known at compile time, or a run-time choice among some."""
+        if v.kind == "clos":
+            recursive = any(b is v.body for b in self.active)
+            n_active, depth0, nreg0, code0, limit0 = len(self.active), self.depth, self.nreg, self.code, self.reg_limit
+            self.active.append(v.body)
+            if recursive:
+                self.reg_limit = min(self.reg_limit, MAX_REGS - RECURSION_RESERVE)
             try:
-                self.run(clos.body, clos.env.fork(), st)
-            except _DeadCode:
-                dead, self.depth = True, depth0
-            arms.append((self.code, st, dead))
+                try:
+                    self.run(v.body, v.env.fork(), stack)
+                except _OutOfRegisters:
+                    if not recursive:
+                        raise
+                    # an unrolled recursion has used up the register file: from this depth on it is a run-time fault, like
+                    # the depth bound (registers are not reused across the levels of an unrolling)
+                    self.depth, self.nreg, self.code = depth0, nreg0, code0      # (branches inside the abandoned level had swapped the code buffer)
+                    self.fault(stack)
+            finally:
+                del self.active[n_active:]
+                self.reg_limit = limit0
+        else:
+            self.apply_chain(v, 0, stack)
+
+    def apply_chain(self, v, k, stack):
+        n = len(v.items)
+        if k == n:                                   # (a selector outside 0 .. n-1: get has already faulted)
+            self.fault(stack)
+        if k == n - 1 and v.exhaustive:
+            self.apply_value(v.items[k], stack)
+            return
+        hit = self.scalar_op("EQI", "b", A("i", reg=v.reg), A("i", const=k))
+        self.branch(hit.reg, lambda st: self.apply_value(v.items[k], st), lambda st: self.apply_chain(v, k + 1, st), stack)
+
+    def if_(self, stack):
+        f, t, c = self.pop_callable(stack), self.pop_callable(stack), self.pop(stack, "b")
+        if c.is_const:
+            self.apply_value(t if c.const else f, stack)
+            return
+        self.branch(self.reg_of(c), lambda st: self.apply_value(t, st), lambda st: self.apply_value(f, st), stack)
+
+    def branch(self, cr, run_t, run_f, stack):
+        """Run-time two-way branch on register `cr`: each arm is compiled over a copy of the stack, then the stacks are merged."""
+        outer, depth0, bd0 = self.code, self.depth, self.branch_depth
+        arms = []
+        self.branch_depth += 1
+        try:
+            for arm in (run_t, run_f):
+                self.code = []
+                st, dead = list(stack), False
+                try:
+                    arm(st)
+                except _DeadCode:
+                    dead, self.depth = True, depth0
+                arms.append((self.code, st, dead))
+        finally:
+            self.branch_depth = bd0
         self.code = outer
         (code_t, st_t, dead_t), (code_f, st_f, dead_f) = arms
         if dead_t and dead_f:
@@ -427,9 +513,9 @@ class _Compiler:
     def merge(self, x, y, mv_t, mv_f):
         if x is y:
             return x
-        if x.kind != y.kind:
+        if x.kind != y.kind and not {x.kind, y.kind} <= {"clos", "choice"}:
             raise SurfaceCompileError(f"the two arms of `if` leave different types ({x.kind} vs {y.kind})")
-        k = x.kind
+        k = x.kind if x.kind == y.kind else "choice"
         if k in "ifb":
             if x.is_const and y.is_const and x.const == y.const and (k != "f" or struct.pack("<d", x.const) == struct.pack("<d", y.const)):
                 return x
@@ -441,10 +527,14 @@ class _Compiler:
             return A(k, comps=[self.merge(a, b, mv_t, mv_f) for a, b in zip(x.comps, y.comps)])
         if k == "arr":
             raise SurfaceCompileError("`if` arms that yield different arrays are not supported")
-        if k == "clos":
-            if x.body is y.body:
-                return x
-            raise SurfaceCompileError("`if` arms that yield different closures are not supported")
+        if k == "clos" and x.body is y.body and x.env == y.env:
+            return x
+        if k in ("clos", "choice"):
+            # which closure it is will only be known at run time: a selector register, 0 = this arm's, 1 = the other's
+            r = self.new_reg()
+            mv_t.append((r, A("i", const=0)))
+            mv_f.append((r, A("i", const=1)))
+            return A("choice", reg=r, items=[x, y])
         if x.const == y.const:
             return x
         raise SurfaceCompileError("`if` arms yield different opaque values")

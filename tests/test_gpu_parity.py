@@ -382,6 +382,26 @@ def _blob(text):
     return scenes.to_blob(text)
 
 
+def test_closures_chosen_at_run_time_render_like_the_oracle(ctx64, ctx32):
+    """A surface function that picks its closure per hit - out of an array by floor(u n), and by a run-time `if` - and a
+    recursive one with a run-time exit (tests/test_oracle.py pins their bytecode against EvalSurfaceFn on the CPU): the
+    device interpreter renders them byte for byte like the oracle's in parity mode, within tolerance in float32."""
+    text = ('[ { /q 1.0 q 0.2 point } { /q 0.2 1.0 q point } { /q q 0.3 1.0 point } ] /tab\n'
+            '{ /v /u /face tab u 5.9 mulf floor get /f v f apply 0.8 0.3 6.0 } sphere 0.0 0.0 3.0 translate\n'
+            '{ /self /x /n x 0.1 lessf { n } { n 1 addi x 0.5 mulf self self apply } if } /loop\n'
+            '{ /v /u /face 0 u v addf 0.5 mulf loop loop apply real 0.2 mulf /s  u 0.25 lessf { { s 0.1 0.1 point } } { { 0.1 s 0.9 point } } if /pick pick apply 0.9 0.1 2.0 }\n'
+            'sphere -1.6 0.4 3.5 translate union\n/scene\n'
+            '-3.0 4.0 -2.0 point 1.0 1.0 1.0 point pointlight /l1\n[ l1 ] /lights\n'
+            '0.3 0.3 0.3 point\nlights\nscene\n2\n90.0\n240 160\n"closures.ppm"\nrender\n')
+    blob = _blob(text)
+    want, ost = oracle.render(blob, threads=THREADS)
+    got, st = ctx64.render(blob)
+    assert np.array_equal(got, want)
+    assert st.rays_total == ost.rays_total
+    got32, _ = ctx32.render(blob)
+    assert agreement(got32, want, tol=1) >= 0.999
+
+
 def test_candidate_queue_overflow_retraces_and_never_writes_out_of_bounds(ctx64):
     """48 nested spheres around one centre - every ray that meets the outermost bound survives the cull of
     all 48 - with one candidate slot per ray.  The queue overflows, its counter stops at the cap (it used to wrap past

@@ -146,6 +146,66 @@ def test_bytecode_equals_reference_closure_semantics(name):
     assert checked > 0
 
 
+_TAIL = ' cube /c 1.0 1.0 1.0 point [] c 1 90.0 4 4 "x" render'
+RUNTIME_CLOSURES = {
+    # the two arms of a run-time `if` leave different closures; the survivor is applied later
+    "if_picks_a_closure": '{ /v /u /face u 0.5 lessf { { 1.0 0.0 0.0 point } } { { 0.0 v 1.0 point } } if /pick pick apply 0.8 0.2 4.0 }',
+    # `get` with a run-time index into an array of closures (faces 3-5 are out of range: the reference faults, evaluator.go:989-995)
+    "get_picks_a_closure": '[ { /q 1.0 0.0 0.0 point } { /q 0.0 q 0.0 point } { /q 0.0 0.0 1.0 point } ] /tab '
+                           '{ /v /u /face tab face get /f u f apply 0.7 0.3 2.0 }',
+    # a run-time-selected closure as an operand of `if`
+    "choice_as_if_operand": '{ /v /u /face u v lessf { { 0.2 } } { { 0.9 } } if /g  face 2 lessi g { 0.5 } if /r r r r point 1.0 0.0 1.0 }',
+    # recursion through apply with a run-time exit: halve x until it is below 0.1, count the steps
+    "recursion_with_runtime_exit": '{ /self /x /n x 0.1 lessf { n } { n 1 addi x 0.5 mulf self self apply } if } /loop '
+                                   '{ /v /u /face 0 u loop loop apply real 0.1 mulf /s s s s point 1.0 0.0 1.0 }',
+}
+
+
+@pytest.mark.parametrize("case", sorted(RUNTIME_CLOSURES))
+def test_bytecode_runs_closures_chosen_at_run_time(case):
+    """apply / if on a closure that is only known per hit (evaluator.go:604-610, :1005-1019): the compiler carries it as a
+    choice - a selector register and the candidate closures - and unfolds the application into a chain of branches; the
+    compiled code, run by the oracle's interpreter, equals EvalSurfaceFn on the closure itself, fault for fault."""
+    st = gml.NewEvalState()
+    calls = []
+    st.Render = lambda e, a: calls.append(a)
+    st.ParseAndEval(RUNTIME_CLOSURES[case] + _TAIL)
+    blob = lowering.lower(calls[0], st)
+    assert lowering.describe(blob)["surfaces"][0]["kind"] == 1          # bytecode, not a folded constant
+    fn = calls[0].Scene.surface_fn
+    rng = random.Random(7)
+    ok = faults = 0
+    for _ in range(500):
+        face, u, v = rng.randrange(6), rng.random(), rng.random()
+        try:
+            want = gml.EvalSurfaceFn(face, u, v, st, fn).as_tuple()
+        except gml.ErrArrayIndexOutOfBounds:
+            del st.Stack[:]
+            with pytest.raises(oracle.OracleError):
+                oracle.eval_surface(blob, 0, face, u, v)
+            faults += 1
+            continue
+        assert oracle.eval_surface(blob, 0, face, u, v) == want, (face, u, v)
+        ok += 1
+    assert ok > 100 and (faults > 100) == (case == "get_picks_a_closure")
+
+
+def test_bytecode_recursion_beyond_the_bound_is_a_run_time_fault():
+    """No call stack on the device: an unrolled recursion that runs out of levels (registers) faults at run time instead of
+    failing to compile - the paths that stay within the bound still give the reference's values."""
+    st = gml.NewEvalState()
+    calls = []
+    st.Render = lambda e, a: calls.append(a)
+    # count down from floor(u * 1000), adding 0.001 per level: up to 999 levels deep
+    st.ParseAndEval('{ /self /acc /n n 1 lessi { acc } { n 1 subi acc 0.001 addf self self apply } if } /down '
+                    '{ /v /u /face u 1000.0 mulf floor 0.0 down down apply /s s s s point 1.0 0.0 1.0 }' + _TAIL)
+    blob = lowering.lower(calls[0], st)
+    fn = calls[0].Scene.surface_fn
+    assert oracle.eval_surface(blob, 0, 0, 0.0035, 0.0) == gml.EvalSurfaceFn(0, 0.0035, 0.0, st, fn).as_tuple()      # 3 levels
+    with pytest.raises(oracle.OracleError):
+        oracle.eval_surface(blob, 0, 0, 0.9, 0.0)                                                                    # 900 levels
+
+
 def test_bytecode_faults_like_the_reference():
     st = gml.NewEvalState()
     calls = []
