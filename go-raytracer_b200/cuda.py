@@ -136,7 +136,7 @@ class Context:
     def close(self):
         if self._h:
             self._L.gmlrt_destroy(self._h)
-            self._h = ctypes.c_void_p()
+            self._h = None               # (not ctypes.c_void_p(): at interpreter shutdown the module may already be gone)
 
     __del__ = close
 
