@@ -1,20 +1,24 @@
-// render_impl.cuh - the wavefront ray tracer, templated on the arithmetic type.
+// render_impl.cuh - the kernels of the wavefront ray tracer, templated on the arithmetic type (the per-device Renderer that
+// launches them is render_host.cuh, included at the end).
 //
 // Replaces Render / traceRay / closestHit / computeLighting / inShadow and the per-primitive
 // Intersect / ComputeSurfaceProps of /root/reference/raytracer.go (line references at each
-// function).  The reference is a recursive tracer run by 8 goroutines; this is a wavefront:
+// function).  The reference is a recursive tracer run by 8 goroutines; this is a wavefront, per recursion level:
 //
-//   gen        camera rays for a band of rows, PCG jitter by jump-ahead        (Render :632-652)
-//   closest    every ray x every leaf, leaves staged in shared memory by TMA   (closestHit :469-483)
-//   shade      surface function (bytecode), material, shadow + child rays      (traceRay :498-556)
-//   shadow     any-hit scan with early exit                                    (inShadow :411-429)
-//   resolve    lighting + clamp per recursion level, deepest level first       (:372-401, :506-561)
-//   pixels     mean of 4 samples -> RGBA8                                      (:656, vec.go:104-107)
+//   cull       one thread per ray walks the candidate list of the ray's CLASS (built once per upload, k_list_build)
+//              and tests the listed bounding spheres from 16-byte records staged in shared memory by one TMA bulk
+//              copy; at level 0 the same kernel makes the camera rays (PCG jitter by jump-ahead)   (Render :632-652)
+//   exact      the reference's own <Type>.Intersect on the survivors, folded per ray                 (closestHit :469-483)
+//   hit list   the rays that hit, compacted (__ballot_sync / __popc); misses are finished here       (traceRay :493-497)
+//   shade      surface function (bytecode), material, shadow + child rays                            (traceRay :498-556)
+//   shadow     cull + exact again for the shadow rays of each light, any-hit                         (inShadow :411-429)
+//   resolve    lighting + clamp per recursion level, deepest level first                             (:372-401, :506-561)
+//   pixels     mean of 4 samples -> RGBA8                                                            (:656, vec.go:104-107)
 //
-// Rays of one recursion level live in SoA queues; children are appended with warp-aggregated
-// (__ballot_sync/__popc) atomics, so the scan kernels always run on dense queues.  Colour is
+// Rays of one recursion level live in queues; children are appended with warp-aggregated
+// (__ballot_sync/__popc) atomics, so every kernel runs on dense queues.  Colour is
 // clamped at every level in the reference, hence the per-level records and the
-// back-to-front resolve instead of a throughput-weighted accumulation.
+// back-to-front resolve instead of a throughput-weighted accumulation.  DESIGN.md section 4 has the whole story.
 //
 // This header is compiled twice: render_f64.cu (R = double, -fmad=false: reference operation
 // order, bit-parity mode) and render_f32.cu (R = float, FMA contraction: throughput mode).
