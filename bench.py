@@ -120,6 +120,28 @@ def workload_name(args):
     return f"{args.config} {args.width}x{args.height} depth {args.depth}, 4 spp, {LEAVES.get(args.config, '')}"
 
 
+def other_config_line(cuda, name, device, steps=3):
+    """BASELINE.json's other GPU configs in the same run, so that the driver's record holds them too: device-timed frames
+    (scene resident, CUDA events inside gmlrt_trace) of one config at its stated size, float32, after two warm-up frames."""
+    import types
+    a = types.SimpleNamespace(config=name, width=7680 if name == "mixed4096" else 3840, height=4320 if name == "mixed4096" else 2160,
+                              depth={"mixed4096": 5, "proctex": 2, "csg256": 2}[name])
+    blob = build_blob(a)
+    ctx = cuda.Context((device,), cuda.PRECISION_F32)
+    try:
+        ctx.upload(blob)
+        ctx.set_counting(True)
+        cst = ctx.trace()
+        ctx.set_counting(False)
+        for _ in range(2):
+            ctx.trace()
+        ms = sorted(ctx.trace().ms_total for _ in range(steps))
+    finally:
+        ctx.close()
+    return {"workload": workload_name(a), "frame_ms": ms[len(ms) // 2], "frames": steps, "rays_per_frame": int(cst.rays_total),
+            "value": cst.rays_total / (ms[len(ms) // 2] * 1e-3) / 1e6, "unit": "Mrays/s"}
+
+
 def central_crop(w, h, cw, ch):
     x0, y0 = (w - cw) // 2, (h - ch) // 2
     y0 -= y0 % 20                      # keep whole PCG work items (20-row batches)
@@ -172,6 +194,7 @@ def main():
     ap.add_argument("--parity-crop", type=int, nargs=2, default=None, help="window of the timed frame the oracle re-renders for the float32 parity check, default 1280x720 (640x360 for mixed4096)")
     ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-other-configs", action="store_true", help="default workload, 1 GPU: skip the short device-timed lines of BASELINE.json's configs 3-5")
     ap.add_argument("--parts", type=int, default=1, help="diagnostic (1 GPU): render only part 0 of PARTS row-band parts, i.e. one rank's share of an N-GPU frame")
     ap.add_argument("--verify", action="store_true", help="N > 1: rank 0 also renders the whole frame alone and compares it with the gathered one")
     ap.add_argument("--gather", default="ipc", choices=["ipc", "nccl"],
@@ -646,6 +669,11 @@ def main():
         res, _, _ = oracle.parity_window(blob, got, ids, pc, threads=os.cpu_count() or 8, chaos=args.config == "mixed4096")
         res["precision"] = args.precision
         line["parity"] = res
+    if world == 1 and args.parts <= 1 and args.config == "spheres1024" and not args.no_other_configs:
+        # configs 3-5 of BASELINE.json ride along (median of 3 device-timed frames each; their float32 parity at these sizes is
+        # tests/test_gpu_parity.py::test_f32_tolerance_at_baseline_size, their full lines profiles/r02z_configs_3_4_5.jsonl)
+        ctx.close()
+        line["other_configs"] = {name: other_config_line(cuda, name, local_rank) for name in ("csg256", "proctex", "mixed4096")}
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()

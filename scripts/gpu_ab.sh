@@ -5,7 +5,7 @@ mkdir -p gpurun_out
 for lib in base new base new; do
   if [ $lib = base ]; then export GMLRT_LIB=$PWD/go-raytracer_b200/libgmlrt_base.so; else unset GMLRT_LIB; fi
   for parts in 1 8; do
-  timeout 300 python bench.py --steps 20 --warmup 3 --parts $parts --no-cpu-baseline --no-parity 2>/dev/null | python -c "
+  timeout 300 python bench.py --steps 20 --warmup 3 --parts $parts --no-cpu-baseline --no-parity --no-other-configs 2>/dev/null | python -c "
 import json,sys
 b=json.loads(sys.stdin.read()); print('$lib parts $parts', round(b['ms_per_step'],3), 'serial', round(b['serialised_frame_ms'],3), {k:round(v,3) for k,v in b['kernel_ms_per_frame'].items()})"
   done

@@ -12,7 +12,7 @@ timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/$
 for c in csg256 proctex mixed4096; do
   timeout 600 python bench.py --config $c --steps 5 --warmup 3 --no-cpu-baseline >> gpurun_out/${T}_configs_3_4_5.jsonl 2>> gpurun_out/${T}_configs.err
 done
-timeout 600 python bench.py --precision f64 --steps 5 --warmup 3 --no-cpu-baseline --no-parity > gpurun_out/${T}_bench_f64_parity_mode.json 2>> gpurun_out/${T}_bench.err
+timeout 600 python bench.py --precision f64 --steps 5 --warmup 3 --no-cpu-baseline --no-parity --no-other-configs > gpurun_out/${T}_bench_f64_parity_mode.json 2>> gpurun_out/${T}_bench.err
 timeout 300 python scripts/gpu_one_frame.py spheres1024 1 && \
 timeout 900 ncu --set full --clock-control none --profile-from-start off -o gpurun_out/${T}_frame_full -f python scripts/gpu_one_frame.py spheres1024 1 > gpurun_out/${T}_ncu_full.log 2>&1; echo "ncu full rc=$?"
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file gpurun_out/${T}_launches_spheres1024_4k.csv python scripts/gpu_one_frame.py spheres1024 1 > /dev/null 2>&1
