@@ -120,26 +120,43 @@ def workload_name(args):
     return f"{args.config} {args.width}x{args.height} depth {args.depth}, 4 spp, {LEAVES.get(args.config, '')}"
 
 
-def other_config_line(cuda, name, device, steps=3):
+def other_config_line(cuda, name, device, steps=3, rank=0, world=1, dist=None):
     """BASELINE.json's other GPU configs in the same run, so that the driver's record holds them too: device-timed frames
-    (scene resident, CUDA events inside gmlrt_trace) of one config at its stated size, float32, after two warm-up frames."""
+    (scene resident, CUDA events inside gmlrt_trace) of one config at its stated size, float32, after two warm-up frames.
+    world > 1: every rank renders its bands of the frame (no gather: the rows stay on the ranks), the frame time is the
+    slowest rank's, the rays are summed over the ranks."""
     import types
     a = types.SimpleNamespace(config=name, width=7680 if name == "mixed4096" else 3840, height=4320 if name == "mixed4096" else 2160,
                               depth={"mixed4096": 5, "proctex": 2, "csg256": 2}[name])
     blob = build_blob(a)
     ctx = cuda.Context((device,), cuda.PRECISION_F32)
     try:
+        if world > 1:
+            ctx.set_partition(rank, world)
         ctx.upload(blob)
         ctx.set_counting(True)
         cst = ctx.trace()
         ctx.set_counting(False)
         for _ in range(2):
             ctx.trace()
-        ms = sorted(ctx.trace().ms_total for _ in range(steps))
+        times = []
+        for _ in range(steps):
+            if dist is not None:
+                dist.barrier()
+            times.append(ctx.trace().ms_total)
+        ms = sorted(times)
     finally:
         ctx.close()
-    return {"workload": workload_name(a), "frame_ms": ms[len(ms) // 2], "frames": steps, "rays_per_frame": int(cst.rays_total),
-            "value": cst.rays_total / (ms[len(ms) // 2] * 1e-3) / 1e6, "unit": "Mrays/s"}
+    frame_ms, rays = ms[len(ms) // 2], int(cst.rays_total)
+    if dist is not None:
+        import torch
+        t = torch.tensor([frame_ms], dtype=torch.float64, device=f"cuda:{device}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        r = torch.tensor([rays], dtype=torch.int64, device=f"cuda:{device}")
+        dist.all_reduce(r)
+        frame_ms, rays = float(t[0]), int(r[0])
+    return {"workload": workload_name(a), "frame_ms": frame_ms, "frames": steps, "rays_per_frame": rays,
+            "value": rays / (frame_ms * 1e-3) / 1e6, "unit": "Mrays/s"}
 
 
 def central_crop(w, h, cw, ch):
@@ -489,6 +506,15 @@ def main():
             gather_check = {"pixels_equal": float(same.mean()), "max_abs_diff": int(np.abs(got.astype(np.int16) - whole.astype(np.int16)).max())}
         barrier()
 
+    other_n = None
+    if dist is not None and args.config == "spheres1024" and not args.no_other_configs:
+        # N > 1: the 8K scene of BASELINE.json (config 5, the north_star's multi-GPU scene) rides along, device-timed, every rank its bands
+        if rank != 0:
+            ctx.close()                                         # (the ranks that mapped rank 0's frame let go of it before rank 0 frees it)
+        dist.barrier()
+        if rank == 0:
+            ctx.close()
+        other_n = {"mixed4096": other_config_line(cuda, "mixed4096", local_rank, rank=rank, world=world, dist=dist)}
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -669,6 +695,8 @@ def main():
         res, _, _ = oracle.parity_window(blob, got, ids, pc, threads=os.cpu_count() or 8, chaos=args.config == "mixed4096")
         res["precision"] = args.precision
         line["parity"] = res
+    if other_n is not None:
+        line["other_configs"] = other_n
     if world == 1 and args.parts <= 1 and args.config == "spheres1024" and not args.no_other_configs:
         # configs 3-5 of BASELINE.json ride along (median of 3 device-timed frames each; their float32 parity at these sizes is
         # tests/test_gpu_parity.py::test_f32_tolerance_at_baseline_size, their full lines profiles/r02z_configs_3_4_5.jsonl)
