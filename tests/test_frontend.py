@@ -93,3 +93,26 @@ def test_include_guard_and_cycle(tmp_path):
         gml.NewEvalState().ParseAndEvalFile(str(tmp_path / "c1.gml"))
     with pytest.raises(gml.GMLSyntaxError, match="#include"):
         gml.NewEvalState().ParseAndEval('#include "does-not-exist.ins"')
+
+
+def test_mul_mat_reference_vector_and_affine_inverse():
+    """TestMulMat (internal/prim/vec_test.go:188-226): the one matrix vector the reference holds; and the affine cofactor
+    inverse (vec.go:319-365, untested in the reference) against the transforms it is used on: M * M^-1 = I to rounding, and
+    a point sent through ObjectToWorld and back comes home."""
+    from go_raytracer_b200 import prim
+    a = tuple(tuple(float(4 * i + j + 1) for j in range(4)) for i in range(4))
+    want = ((90, 100, 110, 120), (202, 228, 254, 280), (314, 356, 398, 440), (426, 484, 542, 600))
+    assert prim.mul_mat(a, a) == tuple(tuple(float(x) for x in row) for row in want)
+    m = prim.identity()
+    for t in (prim.scale(2.0, 0.5, 3.0), prim.rotate_x(30.0), prim.rotate_y(-75.0), prim.rotate_z(120.0), prim.translate(1.5, -2.0, 7.0)):
+        m = prim.mul_mat(t, m)
+    inv = prim.inverse(m)
+    eye = prim.mul_mat(m, inv)
+    for i in range(4):
+        for j in range(4):
+            assert abs(eye[i][j] - (1.0 if i == j else 0.0)) < 1e-12
+    p = prim.Vec3(0.3, -0.7, 0.9)
+    q = prim.mul_point(inv, prim.mul_point(m, p))
+    assert abs(q.x - p.x) < 1e-12 and abs(q.y - p.y) < 1e-12 and abs(q.z - p.z) < 1e-12
+    d = prim.mul_dir(m, prim.Vec3(0.0, 0.0, 0.0))
+    assert (d.x, d.y, d.z) == (0.0, 0.0, 0.0)                      # directions ignore the translation column
