@@ -349,6 +349,13 @@ def main():
     # end to end through the public C ABI: host blob in, host raster out, every step.  Twice: into a page-locked raster
     # from gmlrt_alloc_host (what INTEGRATION.md's bridge hands out as image.RGBA.Pix) and into an ordinary pageable
     # numpy array (what an unmodified caller of image.NewRGBA has, raytracer.go:590; gmlrt_download stages it in chunks).
+    # this step's input in page-locked host memory (gmlrt_alloc_host), copied to the device by every step's gmlrt_upload
+    L = cuda.load()
+    blob_pinned = L.gmlrt_alloc_host(len(blob))
+    if not blob_pinned:
+        raise SystemExit("gmlrt_alloc_host failed")
+    import ctypes as _ct
+    _ct.memmove(blob_pinned, blob, len(blob))
     host_frame = cuda.HostFrame(W, H) if rank == 0 else None
     pageable = np.empty((H, W, 4), dtype=np.uint8) if rank == 0 else None
     pinned_t = torch.from_numpy(host_frame.array) if rank == 0 else None
@@ -359,7 +366,7 @@ def main():
 
         def e2e_step():
             ta = time.perf_counter()
-            ctx.upload(blob)                                    # H2D of this step's input
+            ctx.upload_from(blob_pinned, len(blob), (W, H))     # H2D of this step's input, from page-locked memory
             tb = time.perf_counter()
             step()
             if use_ipc:
@@ -438,7 +445,7 @@ def main():
 
         def host_step():
             ta = time.perf_counter()
-            ctx.upload(blob)
+            ctx.upload_from(blob_pinned, len(blob), (W, H))
             tb = time.perf_counter()
             ctx.trace()
             tc = time.perf_counter()
@@ -641,6 +648,7 @@ def main():
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "frame_ms": e2e_ms, "h2d_bytes_per_step": len(blob), "d2h_bytes_per_step": W * H * 4,
                 "destination": "page-locked raster from gmlrt_alloc_host (the bridge of INTEGRATION.md)",
+                "source": "the blob in page-locked host memory (gmlrt_alloc_host)",
                 "phase_ms": e2e_phase, "upload_ms_each": upload_each,
                 "upload": "the blob is byte-identical from step to step: gmlrt_upload copies it to the device (h2d_bytes_per_step) and keeps the "
                           "tables derived from it; e2e_new_scene has the full rebuild in every step"},

@@ -161,6 +161,12 @@ class Context:
         self._check(self._L.gmlrt_upload(self._h, buf, len(blob)))
         self._size = self._blob_size(blob)
 
+    def upload_from(self, address, nbytes, size):
+        """gmlrt_upload of a blob that already sits at a host address (e.g. page-locked memory from gmlrt_alloc_host, so that
+        the copy to the device is one DMA); size = (width, height) of its frame."""
+        self._check(self._L.gmlrt_upload(self._h, ctypes.c_void_p(address), nbytes))
+        self._size = tuple(size)
+
     def trace(self):
         st = Stats()
         self._check(self._L.gmlrt_trace(self._h, ctypes.byref(st)))
